@@ -1,0 +1,413 @@
+"""Autograd wiring of the SVPC operators.
+
+Each ``torch.autograd.Function`` here pairs one forward operator of ``svpc_b200.backend`` with its hand-written
+backward operator; torch is only the tape (and the owner of device memory).  Nothing in this file computes on the
+host: every tensor operation on activations is a backend (CUDA) call.
+"""
+from __future__ import annotations
+
+import torch
+from torch.autograd import Function
+
+from . import backend as B
+from .backend import ACT_NONE, ACT_RELU, ACT_GELU, ACT_SIGMOID
+
+
+def be():
+    return B.get()
+
+
+# ------------------------------------------------------------------------------------------------
+# weights in GEMM layout / dtype, refreshed when the optimiser has touched the parameters
+# ------------------------------------------------------------------------------------------------
+class WeightCache:
+    """Concatenated (along the output dim) copies of weight parameters in the compute dtype.
+
+    Keyed by the identity of the parameters, invalidated by their autograd version counters (an in-place optimiser
+    update bumps them), so the cast / concat kernels run once per optimiser step, not once per use."""
+
+    def __init__(self):
+        self.store = {}
+
+    def get(self, ws, dtype):
+        if len(ws) == 1 and ws[0].dtype == dtype and ws[0].is_contiguous():
+            return ws[0].detach()
+        key = tuple(id(w) for w in ws) + (dtype,)
+        ver = tuple(w._version for w in ws) + tuple(w.data_ptr() for w in ws)
+        hit = self.store.get(key)
+        if hit is not None and hit[0] == ver:
+            return hit[1]
+        with torch.no_grad():
+            parts = [be().cast(w.detach().contiguous(), dtype) for w in ws]
+            t = parts[0] if len(parts) == 1 else torch.cat(parts, dim=0)
+        self.store[key] = (ver, t)
+        return t
+
+    def clear(self):
+        self.store.clear()
+
+
+WEIGHTS = WeightCache()
+
+
+class _LinMeta:
+    __slots__ = ("n_x", "n_w", "has_bias", "act", "out_dtype", "cd", "w_is_kn", "has_res")
+
+    def __init__(self, **kw):
+        for k, v in kw.items():
+            setattr(self, k, v)
+
+
+class LinearFn(Function):
+    """y = act([x_0 | x_1 | ...] @ [w_0 ; w_1 ; ...]^T + [b_0 ; ...]) (+ residual).
+
+    Inputs are concatenated along K, weights along N (fused QKV / KV projections; ``W2`` of the reasoner takes the
+    two-piece input [h ; ac], reference model.py:803).  ``w_is_kn``: the single weight is stored (K, N) and used
+    untransposed (``x @ W``; the action-embedding table, model.py:798)."""
+
+    @staticmethod
+    def forward(ctx, meta, residual, *args):
+        xs = args[:meta.n_x]
+        ws = args[meta.n_x:meta.n_x + meta.n_w]
+        bs = args[meta.n_x + meta.n_w:]
+        cd = meta.cd
+        W = WEIGHTS.get(ws, cd)
+        bias = None
+        if meta.has_bias:
+            bias = bs[0].detach() if len(bs) == 1 else WEIGHTS.get(bs, torch.float32)
+        xs_c = [x if x.dtype == cd else be().cast(x, cd) for x in xs]
+        want_pre = meta.act == ACT_GELU
+        if meta.w_is_kn:
+            assert meta.n_x == 1 and meta.n_w == 1
+            out = be().gemm(xs_c[0], W.t(), meta.out_dtype, bias, meta.act, residual, want_pre=want_pre)
+        elif meta.n_x == 1:
+            out = be().gemm(xs_c[0], W, meta.out_dtype, bias, meta.act, residual, want_pre=want_pre)
+        else:
+            assert meta.act == ACT_NONE and residual is None
+            k0 = 0
+            out = None
+            for j, x in enumerate(xs_c):
+                k1 = k0 + x.shape[1]
+                if j == 0:
+                    out = be().gemm(x, W[:, k0:k1], meta.out_dtype, bias)
+                else:
+                    be().gemm(x, W[:, k0:k1], meta.out_dtype, None, out=out, accumulate=True)
+                k0 = k1
+        pre = None
+        if want_pre:
+            out, pre = out
+        ctx.meta = meta
+        ctx.shapes = [tuple(w.shape) for w in ws]
+        ctx.x_dtypes = [x.dtype for x in xs]
+        ref = pre if meta.act == ACT_GELU else (out if meta.act in (ACT_RELU, ACT_SIGMOID) else None)
+        ctx.save_for_backward(W, ref, *xs_c)
+        return out
+
+    @staticmethod
+    def backward(ctx, dy):
+        meta = ctx.meta
+        W, ref, *xs_c = ctx.saved_tensors
+        cd = meta.cd
+        dy = dy.contiguous()
+        need = ctx.needs_input_grad
+        d_res = dy if (meta.has_res and need[1]) else None
+        if meta.act != ACT_NONE:
+            dz, dbias = be().act_bwd(dy, ref, meta.act)
+        else:
+            dz = dy
+            dbias = be().colsum(dy) if meta.has_bias else None
+        dzc = dz if dz.dtype == cd else be().cast(dz, cd)
+        n_x, n_w = meta.n_x, meta.n_w
+        # ---- input gradients
+        dxs = [None] * n_x
+        k0 = 0
+        for j, x in enumerate(xs_c):
+            k1 = k0 + x.shape[1]
+            if need[2 + j]:
+                if meta.w_is_kn:
+                    dxs[j] = be().gemm(dzc, W, ctx.x_dtypes[j])                     # dz (M,N) @ W(K,N)^T
+                else:
+                    dxs[j] = be().gemm(dzc, W[:, k0:k1].t(), ctx.x_dtypes[j])      # dz (M,N) @ W(N,K)
+            k0 = k1
+        # ---- weight gradients (fp32, written straight into one buffer in the parameters' layout)
+        dws = [None] * n_w
+        if any(need[2 + n_x:2 + n_x + n_w]):
+            if meta.w_is_kn:
+                dws[0] = be().gemm(xs_c[0].t(), dzc.t(), torch.float32)            # (K,N) = x^T dz
+            else:
+                Ntot = W.shape[0]
+                Ktot = W.shape[1]
+                dW = torch.empty(Ntot, Ktot, dtype=torch.float32, device=dy.device)
+                k0 = 0
+                for x in xs_c:
+                    k1 = k0 + x.shape[1]
+                    be().gemm(dzc.t(), x.t(), torch.float32, out=dW[:, k0:k1])
+                    k0 = k1
+                n0 = 0
+                for i, shp in enumerate(ctx.shapes):
+                    dws[i] = dW[n0:n0 + shp[0]]
+                    n0 += shp[0]
+        dbs = []
+        if meta.has_bias:
+            n0 = 0
+            for i, shp in enumerate(ctx.shapes):
+                dbs.append(dbias[n0:n0 + shp[0]])
+                n0 += shp[0]
+        return (None, d_res, *dxs, *dws, *dbs)
+
+
+def linear(xs, ws, bs, *, act=ACT_NONE, out_dtype=None, cd=torch.float32, residual=None, w_is_kn=False):
+    xs = list(xs) if isinstance(xs, (list, tuple)) else [xs]
+    ws = list(ws) if isinstance(ws, (list, tuple)) else [ws]
+    bs = [] if bs is None else (list(bs) if isinstance(bs, (list, tuple)) else [bs])
+    meta = _LinMeta(n_x=len(xs), n_w=len(ws), has_bias=len(bs) > 0, act=act, out_dtype=out_dtype or cd, cd=cd,
+                    w_is_kn=w_is_kn, has_res=residual is not None)
+    return LinearFn.apply(meta, residual, *xs, *ws, *bs)
+
+
+# ------------------------------------------------------------------------------------------------
+class LayerNormFn(Function):
+    """y = LN(x (+ res)) * gamma + beta (+ pe[row % period]) (+ tt[tt_ids[row]])  (reference model.py:152-156)."""
+
+    @staticmethod
+    def forward(ctx, x, res, gamma, beta, eps, out_dtype, pe, pe_period, tt, tt_ids):
+        y, pre, mean, rstd = be().ln_fwd(x, res, gamma.detach(), beta.detach(), eps, out_dtype, pe, pe_period,
+                                         None if tt is None else tt.detach(), tt_ids)
+        ctx.save_for_backward(pre, mean, rstd, gamma.detach(), tt_ids)
+        ctx.has_res = res is not None
+        ctx.has_tt = tt is not None
+        ctx.n_tt = 0 if tt is None else tt.shape[0]
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        pre, mean, rstd, gamma, tt_ids = ctx.saved_tensors
+        dy = dy.contiguous()
+        dpre, dgamma, dbeta = be().ln_bwd(dy, pre, mean, rstd, gamma)
+        dtt = be().index_colsum(dy, tt_ids, ctx.n_tt) if ctx.has_tt else None
+        return dpre, (dpre if ctx.has_res else None), dgamma, dbeta, None, None, None, None, dtt, None
+
+
+def layer_norm(x, res, gamma, beta, eps, out_dtype=None, pe=None, pe_period=0, tt=None, tt_ids=None):
+    return LayerNormFn.apply(x, res, gamma, beta, eps, out_dtype or x.dtype, pe, pe_period, tt, tt_ids)
+
+
+class EmbedLNFn(Function):
+    """LN_W(table[ids])  (reference model.py:492-494 / 519-521); row ``padding_idx`` of the table gets no gradient."""
+
+    @staticmethod
+    def forward(ctx, table, ids, gamma, beta, eps, out_dtype, padding_idx):
+        y, mean, rstd = be().embed_ln_fwd(table.detach(), ids, gamma.detach(), beta.detach(), eps, out_dtype)
+        ctx.save_for_backward(table.detach(), ids, mean, rstd, gamma.detach())
+        ctx.eps, ctx.padding_idx = eps, padding_idx
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        table, ids, mean, rstd, gamma = ctx.saved_tensors
+        dtable, dgamma, dbeta = be().embed_ln_bwd(dy.contiguous(), table, ids, mean, rstd, gamma, ctx.eps, ctx.padding_idx)
+        return dtable, None, dgamma, dbeta, None, None, None
+
+
+class AttentionFn(Function):
+    """softmax(QK^T/sqrt(dh) + (1-mask)*-1e4) V over ragged short sequences (reference model.py:181-220).
+
+    q / k / v are column blocks (width D) of projection outputs: ``qsrc[:, q_col:q_col+D]`` and, from ``kvsrc``
+    (``qsrc`` itself when None, i.e. a fused QKV projection), the blocks at ``k_col`` / ``v_col``.  The gradient
+    comes back in the same packing, so the fused projection's backward sees one contiguous tensor."""
+
+    @staticmethod
+    def forward(ctx, qsrc, kvsrc, cols, lay, key_mask, causal, n_heads, out_dtype):
+        D = lay["D"]
+        src2 = qsrc if kvsrc is None else kvsrc
+        q = qsrc[:, cols[0]:cols[0] + D]
+        k = src2[:, cols[1]:cols[1] + D]
+        v = src2[:, cols[2]:cols[2] + D]
+        out = be().attn_fwd(q, k, v, lay["q_off"], lay["q_len"], lay["k_off"], lay["k_len"], key_mask, causal, n_heads,
+                            lay["max_lq"], lay["max_lk"], out_dtype)
+        ctx.save_for_backward(qsrc, kvsrc, key_mask)
+        ctx.lay, ctx.causal, ctx.n_heads, ctx.cols = lay, causal, n_heads, cols
+        return out
+
+    @staticmethod
+    def backward(ctx, dctx):
+        qsrc, kvsrc, key_mask = ctx.saved_tensors
+        lay, cols, D = ctx.lay, ctx.cols, ctx.lay["D"]
+        src2 = qsrc if kvsrc is None else kvsrc
+        dqsrc = torch.empty_like(qsrc)
+        dkvsrc = dqsrc if kvsrc is None else torch.empty_like(kvsrc)
+        sl = lambda t, c: t[:, c:c + D]
+        be().attn_bwd(dctx.contiguous(), sl(qsrc, cols[0]), sl(src2, cols[1]), sl(src2, cols[2]), lay["q_off"], lay["q_len"],
+                      lay["k_off"], lay["k_len"], key_mask, ctx.causal, ctx.n_heads, lay["max_lq"], lay["max_lk"],
+                      sl(dqsrc, cols[0]), sl(dkvsrc, cols[1]), sl(dkvsrc, cols[2]))
+        return dqsrc, (None if kvsrc is None else dkvsrc), None, None, None, None, None, None
+
+
+def attention(qsrc, kvsrc, cols, lay, key_mask, causal, n_heads, out_dtype):
+    return AttentionFn.apply(qsrc, kvsrc, cols, lay, key_mask, causal, n_heads, out_dtype)
+
+
+class SegMeanFn(Function):
+    """Ingredient vectors: mean of the token vectors between [SEP]s, + pe[j]  (reference model.py:116-140)."""
+
+    @staticmethod
+    def forward(ctx, x, sep_mask, cu_ingr, pe):
+        ctx.save_for_backward(sep_mask, cu_ingr)
+        ctx.Li, ctx.dt = sep_mask.shape[1], x.dtype
+        return be().segmean_fwd(x, sep_mask, cu_ingr, pe)
+
+    @staticmethod
+    def backward(ctx, dE):
+        sep_mask, cu_ingr = ctx.saved_tensors
+        return be().segmean_bwd(dE.contiguous(), sep_mask, cu_ingr, ctx.Li, ctx.dt), None, None, None
+
+
+class RaggedMeanFn(Function):
+    @staticmethod
+    def forward(ctx, x, cu):
+        ctx.save_for_backward(cu)
+        return be().ragged_mean_fwd(x, cu)
+
+    @staticmethod
+    def backward(ctx, dy):
+        return be().ragged_mean_bwd(dy.contiguous(), ctx.saved_tensors[0]), None
+
+
+class RowNormalizeFn(Function):
+    """x / sum(x, -1)  (reference model.py:798)."""
+
+    @staticmethod
+    def forward(ctx, x):
+        ctx.save_for_backward(x)
+        return be().row_normalize_fwd(x)
+
+    @staticmethod
+    def backward(ctx, dy):
+        return be().row_normalize_bwd(dy.contiguous(), ctx.saved_tensors[0])
+
+
+class ReasonerFn(Function):
+    """The sequential entity-state recurrence of EntitiyReasoningNetwork.forward (reference model.py:792-820)."""
+
+    @staticmethod
+    def forward(ctx, E0, w2v, clog, w4s, lay):
+        ent, ebar, Es, saved = be().reasoner_fwd(E0, lay["cu_ingr"], lay["cu_steps"], lay["clip_ent_off"], w2v, clog, w4s)
+        ctx.lay = lay
+        ctx.n_saved = len(saved)
+        ctx.save_for_backward(E0, w2v, clog, w4s, ent, ebar, Es, *saved)
+        return ent, ebar, Es
+
+    @staticmethod
+    def backward(ctx, d_ent, d_ebar, d_Es):
+        E0, w2v, clog, w4s, ent, ebar, Es, *saved = ctx.saved_tensors
+        lay = ctx.lay
+        z = lambda g, like: torch.zeros_like(like) if g is None else g.contiguous()
+        dE0, dw2v, dclog, dw4s = be().reasoner_bwd(z(d_ent, ent), z(d_ebar, ebar), z(d_Es, Es), E0, lay["cu_ingr"],
+                                                   lay["cu_steps"], lay["clip_ent_off"], w2v, clog, w4s, ent, ebar, Es,
+                                                   tuple(saved))
+        return dE0, dw2v, dclog, dw4s, None
+
+
+class PointerFn(Function):
+    """pointer_generator_network + LabelSmoothingLoss (reference model.py:896-923, 37-55) -> (P flat, caption loss)."""
+
+    @staticmethod
+    def forward(ctx, dec, G, Esrc, wpgen, bpgen, logits, lay):
+        P, rows, saved = be().pointer_fwd(dec, G, Esrc, wpgen.detach(), bpgen.detach(), logits, lay)
+        ctx.lay = lay
+        ctx.save_for_backward(dec, G, Esrc, wpgen.detach(), bpgen.detach(), logits, P, *saved)
+        return P, be().sum_all(rows)
+
+    @staticmethod
+    def backward(ctx, dP, dloss):
+        dec, G, Esrc, wpgen, bpgen, logits, P, *saved = ctx.saved_tensors
+        if dloss is None:
+            dloss = torch.zeros((), dtype=torch.float32, device=P.device)
+        ddec, dG, dE, dw, db, dlog = be().pointer_bwd(None if dP is None else dP.contiguous(), dloss, dec, G, Esrc,
+                                                      wpgen, bpgen, logits, ctx.lay, P, tuple(saved))
+        return ddec, dG, dE, dw, db, dlog, None
+
+
+class SoftmaxLSFn(Function):
+    """softmax over the vocabulary + LabelSmoothingLoss on probabilities ('video' mode, reference model.py:1011-1014)."""
+
+    @staticmethod
+    def forward(ctx, logits, labels, V, smoothing):
+        P, rows = be().softmax_ls_fwd(logits, labels, V, smoothing)
+        ctx.save_for_backward(logits, labels, P)
+        ctx.V, ctx.smoothing = V, smoothing
+        return P, be().sum_all(rows)
+
+    @staticmethod
+    def backward(ctx, dP, dloss):
+        logits, labels, P = ctx.saved_tensors
+        if dloss is None:
+            dloss = torch.zeros((), dtype=torch.float32, device=P.device)
+        return be().softmax_ls_bwd(None if dP is None else dP.contiguous(), dloss, logits, labels, ctx.V, ctx.smoothing, P), None, None, None
+
+
+class GumbelBowFn(Function):
+    """Hard Gumbel-softmax word samples (injected noise) -> masked mean of their word vectors
+    (reference model.py:1018-1021)."""
+
+    @staticmethod
+    def forward(ctx, P, g, emb, lay, text_mask):
+        x, idx, yval = be().gumbel_fwd(P, g, emb.detach(), lay, text_mask)
+        ctx.lay = lay
+        ctx.save_for_backward(P, g, emb.detach(), text_mask, idx, yval)
+        return x
+
+    @staticmethod
+    def backward(ctx, dx):
+        P, g, emb, text_mask, idx, yval = ctx.saved_tensors
+        dP, demb = be().gumbel_bwd(dx.contiguous(), P, g, emb, ctx.lay, text_mask, idx, yval)
+        return dP, None, demb, None, None
+
+
+class BiLSTMFn(Function):
+    """nn.LSTM(W->D, bidirectional), batch of ragged sequences, directions summed (reference model.py:865, 1022-1024)."""
+
+    @staticmethod
+    def forward(ctx, x, lay, keys, *params):
+        p = {k: v.detach() for k, v in zip(keys, params)}
+        out, saved = be().bilstm_fwd(x, lay["cu_steps"], lay["steps"], p)
+        ctx.lay, ctx.keys, ctx.n_p = lay, keys, len(params)
+        ctx.save_for_backward(x, *[v.detach() for v in params], *saved)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        x, *rest = ctx.saved_tensors
+        params, saved = rest[:ctx.n_p], rest[ctx.n_p:]
+        p = dict(zip(ctx.keys, params))
+        dx, grads = be().bilstm_bwd(dout.contiguous(), x, ctx.lay["cu_steps"], ctx.lay["steps"], p, tuple(saved))
+        return (dx, None, None, *[grads[k] for k in ctx.keys])
+
+
+class BCEFn(Function):
+    """nn.BCELoss(reduction='sum') on probabilities (reference model.py:871)."""
+
+    @staticmethod
+    def forward(ctx, p, y):
+        ctx.save_for_backward(p, y)
+        return be().bce_fwd(p, y)
+
+    @staticmethod
+    def backward(ctx, g):
+        p, y = ctx.saved_tensors
+        return be().bce_bwd(p, y, g.contiguous()), None
+
+
+class ASLFn(Function):
+    """AsymmetricLoss on probabilities over the rows with >=1 positive (reference libs/ASL/.../losses.py:15-50,
+    model.py:1103-1104)."""
+
+    @staticmethod
+    def forward(ctx, p, y):
+        ctx.save_for_backward(p, y)
+        return be().asl_fwd(p, y)
+
+    @staticmethod
+    def backward(ctx, g):
+        p, y = ctx.saved_tensors
+        return be().asl_bwd(p, y, g.contiguous()), None
