@@ -1,0 +1,170 @@
+/* svpc_b200 - C ABI of the B200-native SVPC hot path (libsvpc_b200.so, hand-written sm_100a CUDA).
+ *
+ * The reference (awkrail/svpc) has no FFI: its hot path is the Python object protocol of
+ * StateAwareRecursiveTransformer (src/rtransformer/model.py:826-1189) and everything below it is a stock
+ * ATen/cuBLAS/cuDNN call.  Each entry point here replaces the library calls of one piece of that path; the
+ * reference lines it stands for are cited per function.  The reference-side binding is svpc_b200/cuda_backend.py
+ * (ctypes) - see INTEGRATION.md.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer owned by the caller (torch); nothing is allocated or freed here;
+ *   - no entry point synchronises; work is enqueued on `stream` (a cudaStream_t);
+ *   - return 0 (SVPC_OK) or a negative SVPC_ERR_*; svpc_last_error() gives the message (thread local);
+ *   - activations are fp32 (SVPC_F32) or bf16 (SVPC_BF16), selected by a dtype code; parameters, statistics,
+ *     probabilities and losses are always fp32; ids / offsets are int32;
+ *   - "ragged" arrays are concatenations over videos / clips described by offset arrays (svpc_b200/model.py StepPlan).
+ */
+#ifndef SVPC_B200_H
+#define SVPC_B200_H
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SVPC_OK 0
+#define SVPC_ERR_ARG (-1)
+#define SVPC_ERR_CUDA (-2)
+#define SVPC_ERR_UNSUPPORTED (-3)
+
+#define SVPC_F32 0
+#define SVPC_BF16 1
+
+#define SVPC_ACT_NONE 0
+#define SVPC_ACT_RELU 1
+#define SVPC_ACT_GELU 2     /* erf GELU, model.py:58-64 */
+#define SVPC_ACT_SIGMOID 3
+
+#define SVPC_GEMM_AUTO 0
+#define SVPC_GEMM_SIMT 1    /* fp32 FFMA tiles (parity path, odd shapes) */
+#define SVPC_GEMM_TC 2      /* tcgen05 / TMEM / TMA bf16 (fails if the shape / layout is not eligible) */
+
+typedef void* svpc_stream_t; /* cudaStream_t */
+
+const char* svpc_last_error(void);
+int svpc_abi_version(void);
+/* which kernel svpc_gemm would pick for this problem: SVPC_GEMM_SIMT or SVPC_GEMM_TC */
+int svpc_gemm_route(int M, int N, int K, int dtA, long long sa_m, long long sa_k, int dtB, long long sb_n, long long sb_k,
+                    int dtD, long long ldd);
+/* counters: number of kernels launched by this library since the last reset (bench.py "gpu_launches") */
+long long svpc_launch_count(void);
+void svpc_reset_launch_count(void);
+
+/* D[M,N] = act(A[M,K] . B[N,K]^T + bias[N]) + residual[M,N]  (+ D when accumulate); optional copy of the
+ * pre-activation.  A and B are addressed by element strides (one of each pair must be 1).  Replaces every
+ * nn.Linear / matmul on the path: model.py:195-197,230,263,286,496,551,706-708,738,797-811,899,939-940 and their
+ * autograd dgrad / wgrad. */
+int svpc_gemm(int M, int N, int K,
+              const void* A, int dtA, long long sa_m, long long sa_k,
+              const void* B, int dtB, long long sb_n, long long sb_k,
+              void* D, int dtD, long long ldd,
+              const float* bias, int act,
+              const void* residual, long long ldr,
+              void* pre, long long ldp,
+              int accumulate, int route, svpc_stream_t stream);
+
+/* dz = dy * act'(ref), dbias[c] = sum_r dz[r,c].  ref = output for RELU/SIGMOID, pre-activation for GELU. */
+int svpc_act_bwd(int rows, int cols, const void* dy, const void* ref, int dt, int act, void* dz, float* dbias,
+                 svpc_stream_t stream);
+int svpc_colsum(int rows, int cols, const void* x, int dt, float* out, svpc_stream_t stream);
+int svpc_cast(long long n, const void* src, int dts, void* dst, int dtd, svpc_stream_t stream);
+int svpc_sum(long long n, const float* x, float* out, svpc_stream_t stream);
+
+/* BertLayerNorm (model.py:152-156) on x (+ res), optional + pe[row % pe_period] + tt[tt_ids[row]]
+ * (model.py:561, 890-891).  pre (= x + res) is written only when res != NULL. */
+int svpc_ln_fwd(int rows, int D, const void* x, const void* res, int dt_in, const float* gamma, const float* beta,
+                float eps, const float* pe, int pe_period, const float* tt, const int* tt_ids, void* y, int dt_out,
+                void* pre, float* mean, float* rstd, svpc_stream_t stream);
+int svpc_ln_bwd(int rows, int D, const void* dy, int dt_dy, const void* pre, int dt_pre, const float* mean,
+                const float* rstd, const float* gamma, void* dpre, float* dgamma, float* dbeta, svpc_stream_t stream);
+/* out[bin, :] = sum over rows with ids[row] == bin of dy[row, :]  (token-type embedding gradient, model.py:890) */
+int svpc_index_colsum(int rows, int D, const void* dy, int dt, const int* ids, int nbins, float* out,
+                      svpc_stream_t stream);
+
+/* Embedding gather + LN(W) (model.py:492-494 / 519-521) and its backward (scatter-add into the table). */
+int svpc_embed_ln_fwd(int rows, int W, const float* table, const int* ids, const float* gamma, const float* beta,
+                      float eps, void* y, int dt, float* mean, float* rstd, svpc_stream_t stream);
+int svpc_embed_ln_bwd(int rows, int W, int V, const void* dy, int dt, const float* table, const int* ids,
+                      const float* mean, const float* rstd, const float* gamma, int padding_idx, float* dtable,
+                      float* dgamma, float* dbeta, svpc_stream_t stream);
+
+/* Gathers the first Lv rows of clip (t,b) = (clip_t[n], clip_b[n]) from the S per-step feature tensors
+ * (B, L, F) fp32 and writes (x - mean) * rstd (LN(3072) without affine, model.py:549). */
+int svpc_video_ln_pack(int n_clips, int B, int L, int Lv, int F, const long long* feat_ptrs, const int* clip_t,
+                       const int* clip_b, float eps, void* xhat, int dt, float* mean, float* rstd,
+                       svpc_stream_t stream);
+
+/* BertSelfAttention core (model.py:204-216) over ragged short sequences; one CTA per (sequence, head). */
+int svpc_attn_fwd(int n_seq, int H, int dh, const void* q, long long ldq, const void* k, long long ldk, const void* v,
+                  long long ldv, int dt, const int* q_off, const int* q_len, const int* k_off, const int* k_len,
+                  const float* key_mask, int causal, int max_lq, int max_lk, void* ctx, long long ldo,
+                  svpc_stream_t stream);
+int svpc_attn_bwd(int n_seq, int H, int dh, const void* q, long long ldq, const void* k, long long ldk, const void* v,
+                  long long ldv, int dt, const int* q_off, const int* q_len, const int* k_off, const int* k_len,
+                  const float* key_mask, int causal, int max_lq, int max_lk, const void* dctx, long long lddo, void* dq,
+                  long long lddq, void* dk, long long lddk, void* dv, long long lddv, svpc_stream_t stream);
+
+/* IngredientPositionEncoding (model.py:116-140): segment means between [SEP]s + pe[j]. */
+int svpc_segmean_fwd(int B, int Li, int D, int NI, const void* x, int dt, const int* sep_mask, const int* cu_ingr,
+                     const float* pe, float* E0, int* scratch_row_seg, int* scratch_seg_lohi, svpc_stream_t stream);
+int svpc_segmean_bwd(int B, int Li, int D, int NI, const float* dE0, const int* sep_mask, const int* cu_ingr, void* dx,
+                     int dt, int* scratch_row_seg, int* scratch_seg_lohi, svpc_stream_t stream);
+int svpc_ragged_mean_fwd(int B, int D, const float* x, const int* cu, float* y, svpc_stream_t stream);
+int svpc_ragged_mean_bwd(int B, int D, const float* dy, const int* cu, float* dx, svpc_stream_t stream);
+int svpc_row_normalize_fwd(int rows, int cols, const float* x, float* y, svpc_stream_t stream);
+int svpc_row_normalize_bwd(int rows, int cols, const float* dy, const float* x, float* dx, svpc_stream_t stream);
+
+/* Entity-state recurrence of EntitiyReasoningNetwork.forward (model.py:792-820); one CTA per video. */
+int svpc_reasoner_fwd(int B, int D, int max_ni, const float* E0, const int* cu_ingr, const int* cu_steps,
+                      const int* clip_ent_off, const float* w2v, const float* clog, const float* w4s, float* ent,
+                      float* ebar, float* Es, float* a_saved, svpc_stream_t stream);
+int svpc_reasoner_bwd(int B, int D, int max_ni, const float* E0, const int* cu_ingr, const int* cu_steps,
+                      const int* clip_ent_off, const float* w2v, const float* clog, const float* w4s, const float* ent,
+                      const float* ebar, const float* Es, const float* a_saved, const float* d_ent, const float* d_ebar,
+                      const float* d_Es, float* dE0, float* dw2v, float* dclog, float* dw4s, svpc_stream_t stream);
+
+/* pointer_generator_network + LabelSmoothingLoss (model.py:896-923, 37-55); one CTA per clip. */
+int svpc_pointer_fwd(int n_clips, int Lt, int D, int V, int max_ni, int max_vx, const void* dec, int dt, const float* G,
+                     const float* Esrc, const int* clip_src_off, const int* clip_ni, const int* clip_gi,
+                     const int* clip_vx, const int* clip_P_off, const int* tok_ptr, const int* tok_ids,
+                     const float* wpgen, const float* bpgen, const float* logits, long long ldl, const int* labels,
+                     float smoothing, float* P, float* loss_rows, float* alpha, float* pgen, float* ctx,
+                     svpc_stream_t stream);
+int svpc_pointer_bwd(int n_clips, int Lt, int D, int V, int max_ni, int max_vx, const void* dec, int dt, const float* G,
+                     const float* Esrc, const int* clip_src_off, const int* clip_ni, const int* clip_gi,
+                     const int* clip_vx, const int* clip_P_off, const int* tok_ptr, const int* tok_ids,
+                     const float* wpgen, const float* logits, long long ldl, const int* labels, float smoothing,
+                     const float* P, const float* alpha, const float* pgen, const float* ctx, const float* dP,
+                     const float* dloss, void* ddec, float* dG, float* dE, float* du, float* dwpgen, float* dbpgen,
+                     float* dlogits, svpc_stream_t stream);
+/* 'video' mode: softmax over the vocabulary + LabelSmoothingLoss (model.py:1011-1014). */
+int svpc_softmax_ls_fwd(int rows, int V, const float* logits, long long ldl, const int* labels, float smoothing, float* P,
+                        float* loss_rows, svpc_stream_t stream);
+int svpc_softmax_ls_bwd(int rows, int V, const float* dP, const float* dloss, const float* P, const int* labels,
+                        float smoothing, float* dlogits, long long ldl, svpc_stream_t stream);
+
+/* Textual re-simulator front end (model.py:1018-1021): hard Gumbel-softmax with INJECTED noise g, word-vector
+ * lookup, masked mean over the text positions. */
+int svpc_gumbel_fwd(int n_clips, int Lt, int V, int W, const float* P, const float* g, const int* clip_P_off,
+                    const int* clip_vx, float tau, const float* emb, const float* text_mask, float* xmean, int* idx,
+                    float* yval, svpc_stream_t stream);
+int svpc_gumbel_bwd(int n_clips, int Lt, int V, int W, const float* P, const float* g, const int* clip_P_off,
+                    const int* clip_vx, float tau, const float* emb, const float* text_mask, const int* idx,
+                    const float* yval, const float* dxmean, float* dP, float* demb, svpc_stream_t stream);
+
+/* One time step of nn.LSTM (model.py:865) for all videos: gate order i,f,g,o. rows[b] = sequence row or -1. */
+int svpc_lstm_cell_fwd(int B, int D, const float* xg, const float* hg, const int* rows, float* c, float* h, float* out,
+                       int accumulate_out, float* gates_saved, float* c_saved, float* hprev_saved, float* cprev_saved,
+                       svpc_stream_t stream);
+int svpc_lstm_cell_bwd(int B, int D, const int* rows, const float* dout, const float* dh_rec, float* dc,
+                       const float* gates_saved, const float* c_saved, const float* cprev_saved, float* dgates_all,
+                       float* dgates_step, svpc_stream_t stream);
+
+/* nn.BCELoss(sum) on probabilities (model.py:871) and AsymmetricLoss (libs/ASL/src/loss_functions/losses.py:15-50). */
+int svpc_bce_fwd(long long n, const float* p, const float* y, float* loss, svpc_stream_t stream);
+int svpc_bce_bwd(long long n, const float* p, const float* y, const float* g, float* dp, svpc_stream_t stream);
+int svpc_asl_fwd(int rows, int A, const float* p, const float* y, float* loss, svpc_stream_t stream);
+int svpc_asl_bwd(int rows, int A, const float* p, const float* y, const float* g, float* dp, svpc_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

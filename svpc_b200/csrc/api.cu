@@ -1,0 +1,60 @@
+// Error plumbing, launch counter and small utility kernels of libsvpc_b200.so.
+#include "common.cuh"
+#include <stdarg.h>
+#include <stdio.h>
+#include <atomic>
+
+static thread_local char g_err[512] = "";
+static std::atomic<long long> g_launches{0};
+
+void svpc_set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int svpc_check_launch(const char* what) {
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    svpc_set_error("%s: %s", what, cudaGetErrorString(e));
+    return SVPC_ERR_CUDA;
+  }
+  return SVPC_OK;
+}
+
+extern "C" const char* svpc_last_error(void) { return g_err; }
+extern "C" int svpc_abi_version(void) { return 1; }
+extern "C" long long svpc_launch_count(void) { return g_launches.load(); }
+extern "C" void svpc_reset_launch_count(void) { g_launches.store(0); }
+
+// ------------------------------------------------------------------------------------------------
+template <typename TS, typename TD>
+__global__ void cast_kernel(long long n, const TS* __restrict__ s, TD* __restrict__ d) {
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) stf(d + i, ldf(s + i));
+}
+
+extern "C" int svpc_cast(long long n, const void* src, int dts, void* dst, int dtd, svpc_stream_t stream) {
+  if (n <= 0) return SVPC_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  int blocks = svpc_imin(svpc_cdiv(n, 256), SVPC_NUM_SMS * 16);
+  SVPC_DISPATCH(dts, TS, SVPC_DISPATCH(dtd, TD, (cast_kernel<TS, TD><<<blocks, 256, 0, st>>>(n, (const TS*)src, (TD*)dst))));
+  return svpc_check_launch("cast");
+}
+
+// deterministic single-CTA sum (loss reductions: a few thousand elements)
+__global__ void sum_kernel(long long n, const float* __restrict__ x, float* __restrict__ out) {
+  __shared__ float red[64];
+  float acc = 0.f;
+  for (long long i = threadIdx.x; i < n; i += blockDim.x) acc += x[i];
+  acc = block_sum(acc, red);
+  if (threadIdx.x == 0) *out = acc;
+}
+
+extern "C" int svpc_sum(long long n, const float* x, float* out, svpc_stream_t stream) {
+  sum_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(n, x, out);
+  return svpc_check_launch("sum");
+}

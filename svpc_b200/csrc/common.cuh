@@ -4,17 +4,7 @@
 #include <cuda_bf16.h>
 #include <stdint.h>
 #include <math.h>
-
-#define SVPC_OK 0
-#define SVPC_ERR_ARG (-1)
-#define SVPC_ERR_CUDA (-2)
-#define SVPC_ERR_UNSUPPORTED (-3)
-
-// activation codes shared by the GEMM epilogues (include/svpc_b200.h)
-#define SVPC_ACT_NONE 0
-#define SVPC_ACT_RELU 1
-#define SVPC_ACT_GELU 2
-#define SVPC_ACT_SIGMOID 3
+#include "../../include/svpc_b200.h"
 
 void svpc_set_error(const char* fmt, ...);
 int svpc_check_launch(const char* what);
@@ -28,6 +18,24 @@ int svpc_check_launch(const char* what);
   } while (0)
 
 static inline int svpc_cdiv(long long a, long long b) { return (int)((a + b - 1) / b); }
+static inline int svpc_imin(long long a, long long b) { return (int)(a < b ? a : b); }
+
+#define SVPC_NUM_SMS 148
+
+// ---- typed loads / stores (activations are fp32 or bf16; math is always fp32)
+typedef __nv_bfloat16 bf16;
+__device__ __forceinline__ float ldf(const float* p) { return *p; }
+__device__ __forceinline__ float ldf(const bf16* p) { return __bfloat162float(*p); }
+__device__ __forceinline__ void stf(float* p, float v) { *p = v; }
+__device__ __forceinline__ void stf(bf16* p, float v) { *p = __float2bfloat16_rn(v); }
+
+// dtype dispatch: DT is SVPC_F32 / SVPC_BF16, binds type T
+#define SVPC_DISPATCH(DT, T, ...)                                       \
+  do {                                                                  \
+    if ((DT) == SVPC_F32) { typedef float T; __VA_ARGS__; }             \
+    else if ((DT) == SVPC_BF16) { typedef bf16 T; __VA_ARGS__; }        \
+    else { svpc_set_error("bad dtype code %d", (int)(DT)); return SVPC_ERR_ARG; } \
+  } while (0)
 
 __device__ __forceinline__ float svpc_gelu(float x) {
   // reference src/rtransformer/model.py:64  x * 0.5 * (1 + erf(x / sqrt(2)))
@@ -81,15 +89,14 @@ __device__ __forceinline__ float block_max(float v, float* red) {
   r = warp_max(r);
   return r;
 }
-
-// Counter-based dropout mask: keep iff hash(seed, idx) >= p * 2^32.  Same function in fwd and bwd.
-__device__ __forceinline__ uint32_t svpc_hash32(uint64_t seed, uint64_t idx) {
-  uint64_t z = seed + idx * 0x9E3779B97F4A7C15ull;
-  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
-  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
-  z = z ^ (z >> 31);
-  return (uint32_t)(z >> 32);
-}
-__device__ __forceinline__ float svpc_dropout_scale(uint64_t seed, uint64_t idx, uint32_t thresh, float inv_keep) {
-  return (svpc_hash32(seed, idx) >= thresh) ? inv_keep : 0.f;
+// two sums at once
+__device__ __forceinline__ float2 block_sum2(float a, float b, float* red) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+  a = warp_sum(a); b = warp_sum(b);
+  __syncthreads();
+  if (lane == 0) { red[w] = a; red[32 + w] = b; }
+  __syncthreads();
+  float ra = (lane < nw) ? red[lane] : 0.f;
+  float rb = (lane < nw) ? red[32 + lane] : 0.f;
+  return make_float2(warp_sum(ra), warp_sum(rb));
 }

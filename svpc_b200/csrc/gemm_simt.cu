@@ -1,0 +1,139 @@
+// fp32-accumulate FFMA GEMM with arbitrary element strides: the parity path (fp32 operands, true fp32 products like the
+// reference's sgemm) and the route for shapes the tcgen05 kernel does not take (N of 1 or 3, K = 300, M = 16).
+// D[M,N] = act(A[M,K] . B[N,K]^T + bias) + residual (+ D).
+#include "common.cuh"
+
+#define GS_BM 64
+#define GS_BN 64
+#define GS_BK 16
+#define GS_THREADS 256
+
+struct GemmSimtParams {
+  int M, N, K;
+  const void* A; long long sa_m, sa_k;
+  const void* B; long long sb_n, sb_k;
+  void* D; long long ldd;
+  const float* bias; int act;
+  const void* residual; long long ldr;
+  void* pre; long long ldp;
+  int accumulate;
+};
+
+template <typename TA, typename TB, typename TD>
+__global__ void __launch_bounds__(GS_THREADS) gemm_simt_kernel(const GemmSimtParams p) {
+  __shared__ float As[GS_BK][GS_BM + 4];
+  __shared__ float Bs[GS_BK][GS_BN + 4];
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const int m0 = blockIdx.y * GS_BM, n0 = blockIdx.x * GS_BN;
+  const TA* __restrict__ A = (const TA*)p.A;
+  const TB* __restrict__ B = (const TB*)p.B;
+  const bool a_kfast = p.sa_k == 1, b_kfast = p.sb_k == 1;
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+
+  for (int k0 = 0; k0 < p.K; k0 += GS_BK) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int e = tid + i * GS_THREADS;
+      int mm, kk;
+      if (a_kfast) { kk = e & 15; mm = e >> 4; } else { mm = e & 63; kk = e >> 6; }
+      const int gm = m0 + mm, gk = k0 + kk;
+      As[kk][mm] = (gm < p.M && gk < p.K) ? ldf(A + (long long)gm * p.sa_m + (long long)gk * p.sa_k) : 0.f;
+      int nn, kb;
+      if (b_kfast) { kb = e & 15; nn = e >> 4; } else { nn = e & 63; kb = e >> 6; }
+      const int gn = n0 + nn, gkb = k0 + kb;
+      Bs[kb][nn] = (gn < p.N && gkb < p.K) ? ldf(B + (long long)gn * p.sb_n + (long long)gkb * p.sb_k) : 0.f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < GS_BK; ++kk) {
+      const float4 a = *reinterpret_cast<const float4*>(&As[kk][ty * 4]);
+      const float4 b = *reinterpret_cast<const float4*>(&Bs[kk][tx * 4]);
+      const float av[4] = {a.x, a.y, a.z, a.w};
+      const float bv[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+
+  TD* __restrict__ D = (TD*)p.D;
+  const TD* __restrict__ R = (const TD*)p.residual;
+  TD* __restrict__ Pre = (TD*)p.pre;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int m = m0 + ty * 4 + i;
+    if (m >= p.M) continue;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int n = n0 + tx * 4 + j;
+      if (n >= p.N) continue;
+      float v = acc[i][j];
+      if (p.bias) v += p.bias[n];
+      if (Pre) stf(Pre + (long long)m * p.ldp + n, v);
+      v = svpc_act(v, p.act);
+      if (R) v += ldf(R + (long long)m * p.ldr + n);
+      TD* d = D + (long long)m * p.ldd + n;
+      if (p.accumulate) v += ldf(d);
+      stf(d, v);
+    }
+  }
+}
+
+template <typename TA, typename TB>
+static int launch_td(const GemmSimtParams& p, int dtD, cudaStream_t st) {
+  dim3 grid(svpc_cdiv(p.N, GS_BN), svpc_cdiv(p.M, GS_BM));
+  SVPC_DISPATCH(dtD, TD, (gemm_simt_kernel<TA, TB, TD><<<grid, GS_THREADS, 0, st>>>(p)));
+  return svpc_check_launch("gemm_simt");
+}
+
+int svpc_gemm_simt_launch(int M, int N, int K, const void* A, int dtA, long long sa_m, long long sa_k, const void* B,
+                          int dtB, long long sb_n, long long sb_k, void* D, int dtD, long long ldd, const float* bias,
+                          int act, const void* residual, long long ldr, void* pre, long long ldp, int accumulate,
+                          cudaStream_t st) {
+  GemmSimtParams p{M, N, K, A, sa_m, sa_k, B, sb_n, sb_k, D, ldd, bias, act, residual, ldr, pre, ldp, accumulate};
+  SVPC_DISPATCH(dtA, TA, SVPC_DISPATCH(dtB, TB, return (launch_td<TA, TB>(p, dtD, st))));
+  return SVPC_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// public entry: route to the tcgen05 kernel when the problem is eligible, else to the FFMA kernel
+// ------------------------------------------------------------------------------------------------
+int svpc_gemm_tc_eligible(int M, int N, int K, int dtA, long long sa_m, long long sa_k, int dtB, long long sb_n,
+                          long long sb_k, int dtD, long long ldd);
+int svpc_gemm_tc_launch(int M, int N, int K, const void* A, long long sa_m, long long sa_k, const void* B, long long sb_n,
+                        long long sb_k, void* D, int dtD, long long ldd, const float* bias, int act, const void* residual,
+                        long long ldr, void* pre, long long ldp, int accumulate, cudaStream_t st);
+
+extern "C" int svpc_gemm_route(int M, int N, int K, int dtA, long long sa_m, long long sa_k, int dtB, long long sb_n,
+                               long long sb_k, int dtD, long long ldd) {
+  return svpc_gemm_tc_eligible(M, N, K, dtA, sa_m, sa_k, dtB, sb_n, sb_k, dtD, ldd) ? SVPC_GEMM_TC : SVPC_GEMM_SIMT;
+}
+
+extern "C" int svpc_gemm(int M, int N, int K, const void* A, int dtA, long long sa_m, long long sa_k, const void* B,
+                         int dtB, long long sb_n, long long sb_k, void* D, int dtD, long long ldd, const float* bias,
+                         int act, const void* residual, long long ldr, void* pre, long long ldp, int accumulate,
+                         int route, svpc_stream_t stream) {
+  SVPC_REQUIRE(M >= 0 && N >= 0 && K >= 0, "gemm: negative size");
+  if (M == 0 || N == 0) return SVPC_OK;
+  SVPC_REQUIRE(A && B && D, "gemm: null operand");
+  SVPC_REQUIRE(sa_m == 1 || sa_k == 1, "gemm: A needs a unit stride (sa_m=%lld sa_k=%lld)", sa_m, sa_k);
+  SVPC_REQUIRE(sb_n == 1 || sb_k == 1, "gemm: B needs a unit stride (sb_n=%lld sb_k=%lld)", sb_n, sb_k);
+  SVPC_REQUIRE(!(accumulate && (act != SVPC_ACT_NONE || residual)), "gemm: accumulate excludes act / residual");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int ok = svpc_gemm_tc_eligible(M, N, K, dtA, sa_m, sa_k, dtB, sb_n, sb_k, dtD, ldd);
+  if (route == SVPC_GEMM_TC && !ok) {
+    svpc_set_error("gemm: problem %dx%dx%d not eligible for the tcgen05 route", M, N, K);
+    return SVPC_ERR_UNSUPPORTED;
+  }
+  if (ok && route != SVPC_GEMM_SIMT)
+    return svpc_gemm_tc_launch(M, N, K, A, sa_m, sa_k, B, sb_n, sb_k, D, dtD, ldd, bias, act, residual, ldr, pre, ldp,
+                               accumulate, st);
+  return svpc_gemm_simt_launch(M, N, K, A, dtA, sa_m, sa_k, B, dtB, sb_n, sb_k, D, dtD, ldd, bias, act, residual, ldr,
+                               pre, ldp, accumulate, st);
+}

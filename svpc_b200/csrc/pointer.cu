@@ -1,0 +1,485 @@
+// Output head of the caption decoder and the front end of the textual re-simulator:
+//   * pointer-generator mixing + scatter of the copy mass into the (extended) vocabulary + label-smoothed KL loss on
+//     PROBABILITIES (reference model.py:896-923, 37-55), one CTA per clip, rows of the clip processed in sequence so
+//     the per-ingredient gradients reduce inside the CTA;
+//   * plain softmax + the same loss for the 'video' mode (model.py:1011-1014);
+//   * hard Gumbel-softmax with injected noise -> word-vector lookup -> masked mean (model.py:1018-1021).
+// Quirks kept: softmax over the INGREDIENT axis; copy mass of ingredient i split equally over its token ids, added in
+// dictionary order by one thread (same accumulation order as the reference's Python loop); log(p + 1e-12); smoothing
+// mass s/(Vx-1) with the LAST column zeroed (one_hot[ignore_index=-1] = 0) unless it is the target.
+#include "common.cuh"
+
+#define PG_THREADS 256
+
+__device__ __forceinline__ float ls_q(int v, int label, int vx, float s, float conf) {
+  if (v == label) return conf;
+  if (v == vx - 1) return 0.f;
+  return s;
+}
+__device__ __forceinline__ float ls_const(int label, int vx, float s, float conf) {
+  const int n_s = vx - 1 - (label != vx - 1 ? 1 : 0);
+  float c = conf > 0.f ? conf * logf(conf) : 0.f;
+  if (s > 0.f) c += (float)n_s * s * logf(s);
+  return c;
+}
+
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(PG_THREADS) pointer_fwd_kernel(
+    int Lt, int D, int V, int max_ni, int max_vx, const T* __restrict__ dec, const float* __restrict__ G,
+    const float* __restrict__ Esrc, const int* __restrict__ clip_src_off, const int* __restrict__ clip_ni,
+    const int* __restrict__ clip_gi, const int* __restrict__ clip_vx, const int* __restrict__ clip_P_off,
+    const int* __restrict__ tok_ptr, const int* __restrict__ tok_ids, const float* __restrict__ wpgen,
+    const float* __restrict__ bpgen, const float* __restrict__ logits, long long ldl, const int* __restrict__ labels,
+    float smoothing, float* __restrict__ P, float* __restrict__ loss_rows, float* __restrict__ alpha_out,
+    float* __restrict__ pgen_out, float* __restrict__ ctx_out) {
+  extern __shared__ float sm[];
+  float* sdec = sm;               // D
+  float* sctx = sdec + D;         // D
+  float* prow = sctx + D;         // max_vx
+  float* alpha = prow + max_vx;   // max_ni
+  __shared__ float red[64];
+  const int n = blockIdx.x;
+  const int src = clip_src_off[n], ni = clip_ni[n], gi = clip_gi[n], vx = clip_vx[n];
+  const long long poff = clip_P_off[n];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const float bp = bpgen[0];
+  for (int l = 0; l < Lt; ++l) {
+    const long long r = (long long)n * Lt + l;
+    for (int d = threadIdx.x; d < D; d += PG_THREADS) sdec[d] = ldf(dec + r * D + d);
+    __syncthreads();
+    for (int i = warp; i < ni; i += PG_THREADS / 32) {
+      const float* g = G + (long long)(src + i) * D;
+      float s = 0.f;
+      for (int d = lane; d < D; d += 32) s = fmaf(g[d], sdec[d], s);
+      s = warp_sum(s);
+      if (lane == 0) alpha[i] = s;
+    }
+    __syncthreads();
+    if (warp == 0) {   // softmax over the ingredient axis (model.py:900)
+      float mx = -INFINITY;
+      for (int i = lane; i < ni; i += 32) mx = fmaxf(mx, alpha[i]);
+      mx = warp_max(mx);
+      float sum = 0.f;
+      for (int i = lane; i < ni; i += 32) { const float e = expf(alpha[i] - mx); alpha[i] = e; sum += e; }
+      sum = warp_sum(sum);
+      for (int i = lane; i < ni; i += 32) {
+        const float a = alpha[i] / sum;
+        alpha[i] = a;
+        alpha_out[r * max_ni + i] = a;
+      }
+    }
+    __syncthreads();
+    float pu = 0.f;
+    for (int d = threadIdx.x; d < D; d += PG_THREADS) {
+      float c = 0.f;
+      for (int i = 0; i < ni; ++i) c = fmaf(alpha[i], Esrc[(long long)(src + i) * D + d], c);
+      sctx[d] = c;
+      ctx_out[r * D + d] = c;
+      pu += sdec[d] * wpgen[d] + c * wpgen[D + d];
+    }
+    const float pg = svpc_sigmoid(block_sum(pu, red) + bp);
+    if (threadIdx.x == 0) pgen_out[r] = pg;
+    const float* lrow = logits + r * ldl;
+    float mx = -INFINITY;
+    for (int v = threadIdx.x; v < V; v += PG_THREADS) mx = fmaxf(mx, lrow[v]);
+    mx = block_max(mx, red);
+    float se = 0.f;
+    for (int v = threadIdx.x; v < V; v += PG_THREADS) { const float e = expf(lrow[v] - mx); prow[v] = e; se += e; }
+    se = block_sum(se, red);
+    for (int v = threadIdx.x; v < vx; v += PG_THREADS) prow[v] = v < V ? pg * (prow[v] / se) : 0.f;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      for (int i = 0; i < ni; ++i) {
+        const int lo = tok_ptr[gi + i], hi = tok_ptr[gi + i + 1];
+        const float add = alpha[i] * (1.f - pg) / (float)(hi - lo);
+        for (int t = lo; t < hi; ++t) prow[tok_ids[t]] += add;
+      }
+    }
+    __syncthreads();
+    const int label = labels[r];
+    const float s = smoothing / (float)(vx - 1), conf = 1.f - smoothing;
+    float acc = 0.f;
+    for (int v = threadIdx.x; v < vx; v += PG_THREADS) {
+      const float p = prow[v];
+      P[poff + (long long)l * vx + v] = p;
+      if (label >= 0) acc += ls_q(v, label, vx, s, conf) * logf(p + 1e-12f);
+    }
+    acc = block_sum(acc, red);
+    if (threadIdx.x == 0) loss_rows[r] = label >= 0 ? ls_const(label, vx, s, conf) - acc : 0.f;
+    __syncthreads();
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(PG_THREADS) pointer_bwd_kernel(
+    int Lt, int D, int V, int max_ni, int max_vx, const T* __restrict__ dec, const float* __restrict__ G,
+    const float* __restrict__ Esrc, const int* __restrict__ clip_src_off, const int* __restrict__ clip_ni,
+    const int* __restrict__ clip_gi, const int* __restrict__ clip_vx, const int* __restrict__ clip_P_off,
+    const int* __restrict__ tok_ptr, const int* __restrict__ tok_ids, const float* __restrict__ wpgen,
+    const float* __restrict__ logits, long long ldl, const int* __restrict__ labels, float smoothing,
+    const float* __restrict__ P, const float* __restrict__ alpha_in, const float* __restrict__ pgen_in,
+    const float* __restrict__ dP, const float* __restrict__ dloss, T* __restrict__ ddec, float* __restrict__ dG,
+    float* __restrict__ dE, float* __restrict__ du_out, float* __restrict__ dlogits) {
+  extern __shared__ float sm[];
+  float* gP = sm;                    // max_vx
+  float* dsc = gP + max_vx;          // max_ni * Lt   d score[i][l]
+  float* alpha = dsc + max_ni * Lt;  // max_ni
+  float* ci = alpha + max_ni;        // max_ni
+  float* wE = ci + max_ni;           // max_ni   w2 . E_i
+  float* beta = wE + max_ni;         // max_ni   sum_l alpha_il du_l
+  __shared__ float red[64];
+  __shared__ float s_du;
+  const int n = blockIdx.x;
+  const int src = clip_src_off[n], ni = clip_ni[n], gi = clip_gi[n], vx = clip_vx[n];
+  const long long poff = clip_P_off[n];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const float gl = dloss[0];
+  for (int i = warp; i < ni; i += PG_THREADS / 32) {
+    const float* e = Esrc + (long long)(src + i) * D;
+    float s = 0.f;
+    for (int d = lane; d < D; d += 32) s = fmaf(wpgen[D + d], e[d], s);
+    s = warp_sum(s);
+    if (lane == 0) { wE[i] = s; beta[i] = 0.f; }
+  }
+  __syncthreads();
+  for (int l = 0; l < Lt; ++l) {
+    const long long r = (long long)n * Lt + l;
+    const float pg = pgen_in[r];
+    const int label = labels[r];
+    const float s = smoothing / (float)(vx - 1), conf = 1.f - smoothing;
+    const float* lrow = logits + r * ldl;
+    for (int i = threadIdx.x; i < ni; i += PG_THREADS) alpha[i] = alpha_in[r * max_ni + i];
+    float mx = -INFINITY;
+    for (int v = threadIdx.x; v < V; v += PG_THREADS) mx = fmaxf(mx, lrow[v]);
+    mx = block_max(mx, red);
+    float se = 0.f;
+    for (int v = threadIdx.x; v < V; v += PG_THREADS) se += expf(lrow[v] - mx);
+    se = block_sum(se, red);
+    // gradient w.r.t. the mixed probabilities
+    float pa = 0.f;
+    for (int v = threadIdx.x; v < vx; v += PG_THREADS) {
+      float g = dP ? dP[poff + (long long)l * vx + v] : 0.f;
+      if (label >= 0) g -= gl * ls_q(v, label, vx, s, conf) / (P[poff + (long long)l * vx + v] + 1e-12f);
+      gP[v] = g;
+      if (v < V) pa = fmaf(g, expf(lrow[v] - mx) / se, pa);
+    }
+    const float A = block_sum(pa, red);      // sum_v gP_v sm_v   (syncs: gP visible)
+    for (int i = threadIdx.x; i < ni; i += PG_THREADS) {
+      const int lo = tok_ptr[gi + i], hi = tok_ptr[gi + i + 1];
+      float c = 0.f;
+      for (int t = lo; t < hi; ++t) c += gP[tok_ids[t]];
+      ci[i] = c / (float)(hi - lo);
+    }
+    __syncthreads();
+    if (warp == 0) {
+      float t = 0.f;
+      for (int i = lane; i < ni; i += 32) t = fmaf(alpha[i], ci[i], t);
+      t = warp_sum(t);
+      const float dpg = A - t;
+      const float du = dpg * pg * (1.f - pg);
+      // d alpha_i = (1 - pg) c_i + du * (w2 . E_i);  d score = alpha (d alpha - sum alpha d alpha)
+      float dot = 0.f;
+      for (int i = lane; i < ni; i += 32) dot = fmaf(alpha[i], (1.f - pg) * ci[i] + du * wE[i], dot);
+      dot = warp_sum(dot);
+      for (int i = lane; i < ni; i += 32) {
+        const float dal = (1.f - pg) * ci[i] + du * wE[i];
+        dsc[i * Lt + l] = alpha[i] * (dal - dot);
+        beta[i] += alpha[i] * du;
+      }
+      if (lane == 0) { s_du = du; du_out[r] = du; }
+    }
+    __syncthreads();
+    const float du = s_du;
+    for (int v = threadIdx.x; v < V; v += PG_THREADS)
+      dlogits[r * ldl + v] = (expf(lrow[v] - mx) / se) * pg * (gP[v] - A);
+    for (int d = threadIdx.x; d < D; d += PG_THREADS) {
+      float a = du * wpgen[d];
+      for (int i = 0; i < ni; ++i) a = fmaf(dsc[i * Lt + l], G[(long long)(src + i) * D + d], a);
+      stf(ddec + r * D + d, a);
+    }
+    __syncthreads();
+  }
+  // dG_i[d] += sum_l dscore[i][l] dec[l][d] ;  dE_i[d] += beta_i w2[d]
+  for (int d = threadIdx.x; d < D; d += PG_THREADS) {
+    for (int i = 0; i < ni; ++i) {
+      float a = 0.f;
+      for (int l = 0; l < Lt; ++l) a = fmaf(dsc[i * Lt + l], ldf(dec + ((long long)n * Lt + l) * D + d), a);
+      atomicAdd(dG + (long long)(src + i) * D + d, a);
+      atomicAdd(dE + (long long)(src + i) * D + d, beta[i] * wpgen[D + d]);
+    }
+  }
+}
+
+int svpc_weighted_colsum(int rows, int cols, const void* x, int dt, const float* w, float* out, cudaStream_t st);
+
+extern "C" int svpc_pointer_fwd(int n_clips, int Lt, int D, int V, int max_ni, int max_vx, const void* dec, int dt,
+                                const float* G, const float* Esrc, const int* clip_src_off, const int* clip_ni,
+                                const int* clip_gi, const int* clip_vx, const int* clip_P_off, const int* tok_ptr,
+                                const int* tok_ids, const float* wpgen, const float* bpgen, const float* logits,
+                                long long ldl, const int* labels, float smoothing, float* P, float* loss_rows,
+                                float* alpha, float* pgen, float* ctx, svpc_stream_t stream) {
+  if (n_clips <= 0) return SVPC_OK;
+  const size_t smem = sizeof(float) * (2 * (size_t)D + max_vx + max_ni);
+  SVPC_REQUIRE(smem <= 200 * 1024, "pointer_fwd: shared memory");
+  cudaStream_t st = (cudaStream_t)stream;
+  SVPC_DISPATCH(dt, T, {
+    cudaFuncSetAttribute(pointer_fwd_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    pointer_fwd_kernel<T><<<n_clips, PG_THREADS, smem, st>>>(Lt, D, V, max_ni, max_vx, (const T*)dec, G, Esrc, clip_src_off,
+                                                            clip_ni, clip_gi, clip_vx, clip_P_off, tok_ptr, tok_ids, wpgen,
+                                                            bpgen, logits, ldl, labels, smoothing, P, loss_rows, alpha, pgen, ctx);
+  });
+  return svpc_check_launch("pointer_fwd");
+}
+
+extern "C" int svpc_pointer_bwd(int n_clips, int Lt, int D, int V, int max_ni, int max_vx, const void* dec, int dt,
+                                const float* G, const float* Esrc, const int* clip_src_off, const int* clip_ni,
+                                const int* clip_gi, const int* clip_vx, const int* clip_P_off, const int* tok_ptr,
+                                const int* tok_ids, const float* wpgen, const float* logits, long long ldl,
+                                const int* labels, float smoothing, const float* P, const float* alpha, const float* pgen,
+                                const float* ctx, const float* dP, const float* dloss, void* ddec, float* dG, float* dE,
+                                float* du, float* dwpgen, float* dbpgen, float* dlogits, svpc_stream_t stream) {
+  if (n_clips <= 0) return SVPC_OK;
+  const size_t smem = sizeof(float) * ((size_t)max_vx + (size_t)max_ni * Lt + 4 * (size_t)max_ni);
+  SVPC_REQUIRE(smem <= 200 * 1024, "pointer_bwd: shared memory");
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaMemsetAsync(dwpgen, 0, sizeof(float) * 2 * D, st);
+  SVPC_DISPATCH(dt, T, {
+    cudaFuncSetAttribute(pointer_bwd_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    pointer_bwd_kernel<T><<<n_clips, PG_THREADS, smem, st>>>(Lt, D, V, max_ni, max_vx, (const T*)dec, G, Esrc, clip_src_off,
+                                                            clip_ni, clip_gi, clip_vx, clip_P_off, tok_ptr, tok_ids, wpgen,
+                                                            logits, ldl, labels, smoothing, P, alpha, pgen, dP, dloss,
+                                                            (T*)ddec, dG, dE, du, dlogits);
+  });
+  int rc = svpc_check_launch("pointer_bwd");
+  if (rc) return rc;
+  const int R = n_clips * Lt;
+  rc = svpc_weighted_colsum(R, D, dec, dt, du, dwpgen, st);
+  if (rc) return rc;
+  rc = svpc_weighted_colsum(R, D, ctx, SVPC_F32, du, dwpgen + D, st);
+  if (rc) return rc;
+  return svpc_sum(R, du, dbpgen, stream);
+}
+
+// ------------------------------------------------------------------------------------------------
+// 'video' mode: P = softmax(logits), label-smoothed KL on P
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(PG_THREADS) softmax_ls_fwd_kernel(int V, const float* __restrict__ logits, long long ldl,
+                                                                    const int* __restrict__ labels, float smoothing,
+                                                                    float* __restrict__ P, float* __restrict__ loss_rows) {
+  __shared__ float red[64];
+  const long long r = blockIdx.x;
+  const float* lrow = logits + r * ldl;
+  float mx = -INFINITY;
+  for (int v = threadIdx.x; v < V; v += PG_THREADS) mx = fmaxf(mx, lrow[v]);
+  mx = block_max(mx, red);
+  float se = 0.f;
+  for (int v = threadIdx.x; v < V; v += PG_THREADS) se += expf(lrow[v] - mx);
+  se = block_sum(se, red);
+  const int label = labels[r];
+  const float s = smoothing / (float)(V - 1), conf = 1.f - smoothing;
+  float acc = 0.f;
+  for (int v = threadIdx.x; v < V; v += PG_THREADS) {
+    const float p = expf(lrow[v] - mx) / se;
+    P[r * V + v] = p;
+    if (label >= 0) acc += ls_q(v, label, V, s, conf) * logf(p + 1e-12f);
+  }
+  acc = block_sum(acc, red);
+  if (threadIdx.x == 0) loss_rows[r] = label >= 0 ? ls_const(label, V, s, conf) - acc : 0.f;
+}
+
+__global__ void __launch_bounds__(PG_THREADS) softmax_ls_bwd_kernel(int V, const float* __restrict__ dP,
+                                                                    const float* __restrict__ dloss,
+                                                                    const float* __restrict__ P,
+                                                                    const int* __restrict__ labels, float smoothing,
+                                                                    float* __restrict__ dlogits, long long ldl) {
+  __shared__ float red[64];
+  const long long r = blockIdx.x;
+  const int label = labels[r];
+  const float gl = dloss[0];
+  const float s = smoothing / (float)(V - 1), conf = 1.f - smoothing;
+  float dot = 0.f;
+  for (int v = threadIdx.x; v < V; v += PG_THREADS) {
+    const float p = P[r * V + v];
+    float g = dP ? dP[r * V + v] : 0.f;
+    if (label >= 0) g -= gl * ls_q(v, label, V, s, conf) / (p + 1e-12f);
+    dot = fmaf(g, p, dot);
+  }
+  dot = block_sum(dot, red);
+  for (int v = threadIdx.x; v < V; v += PG_THREADS) {
+    const float p = P[r * V + v];
+    float g = dP ? dP[r * V + v] : 0.f;
+    if (label >= 0) g -= gl * ls_q(v, label, V, s, conf) / (p + 1e-12f);
+    dlogits[r * ldl + v] = p * (g - dot);
+  }
+}
+
+extern "C" int svpc_softmax_ls_fwd(int rows, int V, const float* logits, long long ldl, const int* labels,
+                                   float smoothing, float* P, float* loss_rows, svpc_stream_t stream) {
+  if (rows <= 0) return SVPC_OK;
+  softmax_ls_fwd_kernel<<<rows, PG_THREADS, 0, (cudaStream_t)stream>>>(V, logits, ldl, labels, smoothing, P, loss_rows);
+  return svpc_check_launch("softmax_ls_fwd");
+}
+extern "C" int svpc_softmax_ls_bwd(int rows, int V, const float* dP, const float* dloss, const float* P,
+                                   const int* labels, float smoothing, float* dlogits, long long ldl,
+                                   svpc_stream_t stream) {
+  if (rows <= 0) return SVPC_OK;
+  softmax_ls_bwd_kernel<<<rows, PG_THREADS, 0, (cudaStream_t)stream>>>(V, dP, dloss, P, labels, smoothing, dlogits, ldl);
+  return svpc_check_launch("softmax_ls_bwd");
+}
+
+// ------------------------------------------------------------------------------------------------
+// textual re-simulator front end
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(PG_THREADS) gumbel_fwd_kernel(int Lt, int V, int W, const float* __restrict__ P,
+                                                                const float* __restrict__ g,
+                                                                const int* __restrict__ clip_P_off,
+                                                                const int* __restrict__ clip_vx, float tau,
+                                                                const float* __restrict__ emb,
+                                                                const float* __restrict__ text_mask,
+                                                                float* __restrict__ xmean, int* __restrict__ idx_out,
+                                                                float* __restrict__ yval_out) {
+  __shared__ float red[64];
+  __shared__ float smax[PG_THREADS / 32];
+  __shared__ int sidx[PG_THREADS / 32];
+  __shared__ int s_best;
+  __shared__ float s_mx;
+  const int n = blockIdx.x, vx = clip_vx[n];
+  const long long poff = clip_P_off[n];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};   // W <= 4 * PG_THREADS
+  float cnt = 0.f;
+  for (int l = 0; l < Lt; ++l) {
+    const long long r = (long long)n * Lt + l;
+    const float* prow = P + poff + (long long)l * vx;
+    const float* grow = g + poff + (long long)l * vx;
+    float mx = -INFINITY;
+    int best = 0x7fffffff;
+    for (int v = threadIdx.x; v < vx; v += PG_THREADS) {
+      const float z = (logf(prow[v] + 1e-12f) + grow[v]) / tau;
+      if (z > mx) { mx = z; best = v; }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+      const float om = __shfl_xor_sync(0xffffffffu, mx, o);
+      const int ob = __shfl_xor_sync(0xffffffffu, best, o);
+      if (om > mx || (om == mx && ob < best)) { mx = om; best = ob; }
+    }
+    __syncthreads();
+    if (lane == 0) { smax[warp] = mx; sidx[warp] = best; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      float m = smax[0]; int bi = sidx[0];
+      for (int w = 1; w < PG_THREADS / 32; ++w)
+        if (smax[w] > m || (smax[w] == m && sidx[w] < bi)) { m = smax[w]; bi = sidx[w]; }
+      s_best = bi; s_mx = m;
+    }
+    __syncthreads();
+    mx = s_mx; best = s_best;
+    float se = 0.f;
+    for (int v = threadIdx.x; v < vx; v += PG_THREADS) se += expf((logf(prow[v] + 1e-12f) + grow[v]) / tau - mx);
+    se = block_sum(se, red);
+    const float y = 1.0f / se;                 // y_soft at its argmax
+    const float yv = (1.0f - y) + y;           // y_hard - y_soft.detach() + y_soft
+    if (threadIdx.x == 0) { idx_out[r] = best; yval_out[r] = yv; }
+    const bool m = text_mask[r] == 1.0f;
+    if (m) {
+      cnt += 1.f;
+      if (best < V) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int w = threadIdx.x + i * PG_THREADS;
+          if (w < W) acc[i] = fmaf(yv, emb[(long long)best * W + w], acc[i]);
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int w = threadIdx.x + i * PG_THREADS;
+    if (w < W) xmean[(long long)n * W + w] = acc[i] / cnt;
+  }
+}
+
+__global__ void __launch_bounds__(PG_THREADS) gumbel_bwd_kernel(int Lt, int V, int W, const float* __restrict__ P,
+                                                                const float* __restrict__ g,
+                                                                const int* __restrict__ clip_P_off,
+                                                                const int* __restrict__ clip_vx, float tau,
+                                                                const float* __restrict__ emb,
+                                                                const float* __restrict__ text_mask,
+                                                                const int* __restrict__ idx_in,
+                                                                const float* __restrict__ yval_in,
+                                                                const float* __restrict__ dxmean, float* __restrict__ dP,
+                                                                float* __restrict__ demb) {
+  extern __shared__ float sm[];
+  float* dxm = sm;        // W
+  float* tv = dxm + W;    // V     t_v = emb[v] . dxmean
+  __shared__ float red[64];
+  const int n = blockIdx.x, vx = clip_vx[n];
+  const long long poff = clip_P_off[n];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int w = threadIdx.x; w < W; w += PG_THREADS) dxm[w] = dxmean[(long long)n * W + w];
+  float cnt = 0.f;
+  for (int l = 0; l < Lt; ++l) cnt += (text_mask[(long long)n * Lt + l] == 1.0f) ? 1.f : 0.f;
+  __syncthreads();
+  for (int v = warp; v < V; v += PG_THREADS / 32) {
+    const float* e = emb + (long long)v * W;
+    float s = 0.f;
+    for (int w = lane; w < W; w += 32) s = fmaf(e[w], dxm[w], s);
+    s = warp_sum(s);
+    if (lane == 0) tv[v] = s;
+  }
+  __syncthreads();
+  for (int l = 0; l < Lt; ++l) {
+    const long long r = (long long)n * Lt + l;
+    const float* prow = P + poff + (long long)l * vx;
+    const float* grow = g + poff + (long long)l * vx;
+    float* drow = dP + poff + (long long)l * vx;
+    if (text_mask[r] != 1.0f) {
+      for (int v = threadIdx.x; v < vx; v += PG_THREADS) drow[v] = 0.f;
+      continue;
+    }
+    const int best = idx_in[r];
+    const float mx = (logf(prow[best] + 1e-12f) + grow[best]) / tau;
+    float se = 0.f, sd = 0.f;
+    for (int v = threadIdx.x; v < vx; v += PG_THREADS) {
+      const float e = expf((logf(prow[v] + 1e-12f) + grow[v]) / tau - mx);
+      se += e;
+      if (v < V) sd = fmaf(e, tv[v], sd);
+    }
+    const float2 rr = block_sum2(se, sd, red);
+    const float inv = 1.f / rr.x;
+    const float sdot = rr.y * inv / cnt;              // sum_v y_v dy_v
+    for (int v = threadIdx.x; v < vx; v += PG_THREADS) {
+      const float y = expf((logf(prow[v] + 1e-12f) + grow[v]) / tau - mx) * inv;
+      const float dy = v < V ? tv[v] / cnt : 0.f;
+      drow[v] = y * (dy - sdot) / tau / (prow[v] + 1e-12f);
+    }
+    if (best < V) {
+      const float c = yval_in[r] / cnt;
+      for (int w = threadIdx.x; w < W; w += PG_THREADS) atomicAdd(demb + (long long)best * W + w, c * dxm[w]);
+    }
+  }
+}
+
+extern "C" int svpc_gumbel_fwd(int n_clips, int Lt, int V, int W, const float* P, const float* g, const int* clip_P_off,
+                               const int* clip_vx, float tau, const float* emb, const float* text_mask, float* xmean,
+                               int* idx, float* yval, svpc_stream_t stream) {
+  if (n_clips <= 0) return SVPC_OK;
+  SVPC_REQUIRE(W <= 4 * PG_THREADS, "gumbel_fwd: W=%d too wide", W);
+  gumbel_fwd_kernel<<<n_clips, PG_THREADS, 0, (cudaStream_t)stream>>>(Lt, V, W, P, g, clip_P_off, clip_vx, tau, emb, text_mask,
+                                                                     xmean, idx, yval);
+  return svpc_check_launch("gumbel_fwd");
+}
+
+extern "C" int svpc_gumbel_bwd(int n_clips, int Lt, int V, int W, const float* P, const float* g, const int* clip_P_off,
+                               const int* clip_vx, float tau, const float* emb, const float* text_mask, const int* idx,
+                               const float* yval, const float* dxmean, float* dP, float* demb, svpc_stream_t stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaMemsetAsync(demb, 0, sizeof(float) * (size_t)V * W, st);
+  if (n_clips <= 0) return SVPC_OK;
+  const size_t smem = sizeof(float) * ((size_t)W + V);
+  cudaFuncSetAttribute(gumbel_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  gumbel_bwd_kernel<<<n_clips, PG_THREADS, smem, st>>>(Lt, V, W, P, g, clip_P_off, clip_vx, tau, emb, text_mask, idx, yval,
+                                                      dxmean, dP, demb);
+  return svpc_check_launch("gumbel_bwd");
+}

@@ -1,0 +1,555 @@
+// Bandwidth-bound row-wise kernels: LayerNorm (+residual, +position / token-type rows), activation backward + bias
+// gradient, embedding gather + LN, video-feature LN staging, ingredient segment means.
+// Layout rule: a CTA owns whole rows, threads stride the contiguous column dimension (coalesced), row statistics by
+// warp shuffles; column reductions (dgamma / dbeta / dbias) are kept in registers across a grid-stride loop over rows
+// and flushed with one red.global per column per CTA.
+#include "common.cuh"
+
+#define RW_THREADS 256
+#define RW_MAXPT 16          // columns cached per thread (D <= RW_THREADS * RW_MAXPT = 4096)
+
+static inline int rw_grid(long long rows) { return svpc_imin(rows, (long long)SVPC_NUM_SMS * 8); }
+
+// ------------------------------------------------------------------------------------------------
+// activation backward + column sum
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void act_bwd_kernel(int rows, int cols, const T* __restrict__ dy, const T* __restrict__ ref, int act,
+                               T* __restrict__ dz, float* __restrict__ dbias) {
+  // blockDim = (32, 8); a CTA owns a 32-column strip for a slice of rows
+  const int c = blockIdx.x * 32 + threadIdx.x;
+  __shared__ float red[8][33];
+  float acc = 0.f;
+  if (c < cols) {
+    for (int r = blockIdx.y * 8 + threadIdx.y; r < rows; r += gridDim.y * 8) {
+      const long long o = (long long)r * cols + c;
+      float g = ldf(dy + o);
+      if (act == SVPC_ACT_RELU) g = ldf(ref + o) > 0.f ? g : 0.f;
+      else if (act == SVPC_ACT_GELU) g *= svpc_gelu_grad(ldf(ref + o));
+      else if (act == SVPC_ACT_SIGMOID) { const float y = ldf(ref + o); g *= y * (1.f - y); }
+      if (dz) stf(dz + o, g);
+      acc += g;
+    }
+  }
+  red[threadIdx.y][threadIdx.x] = acc;
+  __syncthreads();
+  if (threadIdx.y == 0 && c < cols && dbias) {
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s += red[i][threadIdx.x];
+    atomicAdd(dbias + c, s);
+  }
+}
+
+extern "C" int svpc_act_bwd(int rows, int cols, const void* dy, const void* ref, int dt, int act, void* dz, float* dbias,
+                            svpc_stream_t stream) {
+  if (rows <= 0 || cols <= 0) return SVPC_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dbias) cudaMemsetAsync(dbias, 0, sizeof(float) * cols, st);
+  dim3 grid(svpc_cdiv(cols, 32), svpc_imin(svpc_cdiv(rows, 8), 64));
+  SVPC_DISPATCH(dt, T, (act_bwd_kernel<T><<<grid, dim3(32, 8), 0, st>>>(rows, cols, (const T*)dy, (const T*)ref, act,
+                                                                      (T*)dz, dbias)));
+  return svpc_check_launch("act_bwd");
+}
+
+extern "C" int svpc_colsum(int rows, int cols, const void* x, int dt, float* out, svpc_stream_t stream) {
+  return svpc_act_bwd(rows, cols, x, nullptr, dt, SVPC_ACT_NONE, nullptr, out, stream);
+}
+
+// out[c] += sum_r w[r] * x[r, c]
+template <typename T>
+__global__ void weighted_colsum_kernel(int rows, int cols, const T* __restrict__ x, const float* __restrict__ w,
+                                       float* __restrict__ out) {
+  const int c = blockIdx.x * 32 + threadIdx.x;
+  __shared__ float red[8][33];
+  float acc = 0.f;
+  if (c < cols)
+    for (int r = blockIdx.y * 8 + threadIdx.y; r < rows; r += gridDim.y * 8) acc += w[r] * ldf(x + (long long)r * cols + c);
+  red[threadIdx.y][threadIdx.x] = acc;
+  __syncthreads();
+  if (threadIdx.y == 0 && c < cols) {
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s += red[i][threadIdx.x];
+    atomicAdd(out + c, s);
+  }
+}
+
+int svpc_weighted_colsum(int rows, int cols, const void* x, int dt, const float* w, float* out, cudaStream_t st) {
+  dim3 grid(svpc_cdiv(cols, 32), svpc_imin(svpc_cdiv(rows, 8), 64));
+  SVPC_DISPATCH(dt, T, (weighted_colsum_kernel<T><<<grid, dim3(32, 8), 0, st>>>(rows, cols, (const T*)x, w, out)));
+  return svpc_check_launch("weighted_colsum");
+}
+
+// ------------------------------------------------------------------------------------------------
+// LayerNorm forward: y = ((x+res) - mean) * rstd * gamma + beta (+ pe[row % period]) (+ tt[tt_ids[row]])
+// ------------------------------------------------------------------------------------------------
+template <typename TI, typename TO>
+__global__ void __launch_bounds__(RW_THREADS) ln_fwd_kernel(int rows, int D, const TI* __restrict__ x,
+                                                            const TI* __restrict__ res, const float* __restrict__ gamma,
+                                                            const float* __restrict__ beta, float eps,
+                                                            const float* __restrict__ pe, int pe_period,
+                                                            const float* __restrict__ tt, const int* __restrict__ tt_ids,
+                                                            TO* __restrict__ y, TI* __restrict__ pre,
+                                                            float* __restrict__ mean, float* __restrict__ rstd) {
+  __shared__ float red[64];
+  for (int r = blockIdx.x; r < rows; r += gridDim.x) {
+    const long long base = (long long)r * D;
+    float v[RW_MAXPT];
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < RW_MAXPT; ++i) {
+      const int c = threadIdx.x + i * RW_THREADS;
+      v[i] = 0.f;
+      if (c < D) {
+        float t = ldf(x + base + c);
+        if (res) {
+          t += ldf(res + base + c);
+          stf(pre + base + c, t);
+          t = ldf(pre + base + c);      // statistics on the stored (possibly bf16-rounded) value the backward will read
+        }
+        v[i] = t;
+        s += t;
+      }
+    }
+    const float mu = block_sum(s, red) / D;
+    float q = 0.f;
+#pragma unroll
+    for (int i = 0; i < RW_MAXPT; ++i) {
+      const int c = threadIdx.x + i * RW_THREADS;
+      if (c < D) { const float d = v[i] - mu; q += d * d; }
+    }
+    const float var = block_sum(q, red) / D;
+    const float rs = 1.0f / sqrtf(var + eps);
+    if (threadIdx.x == 0) { mean[r] = mu; rstd[r] = rs; }
+    const float* per = pe ? pe + (long long)(r % pe_period) * D : nullptr;
+    const float* ttr = tt ? tt + (long long)tt_ids[r] * D : nullptr;
+#pragma unroll
+    for (int i = 0; i < RW_MAXPT; ++i) {
+      const int c = threadIdx.x + i * RW_THREADS;
+      if (c < D) {
+        float o = (v[i] - mu) * rs * gamma[c] + beta[c];
+        if (per) o += per[c];
+        if (ttr) o += ttr[c];
+        stf(y + base + c, o);
+      }
+    }
+  }
+}
+
+extern "C" int svpc_ln_fwd(int rows, int D, const void* x, const void* res, int dt_in, const float* gamma,
+                           const float* beta, float eps, const float* pe, int pe_period, const float* tt,
+                           const int* tt_ids, void* y, int dt_out, void* pre, float* mean, float* rstd,
+                           svpc_stream_t stream) {
+  if (rows <= 0) return SVPC_OK;
+  SVPC_REQUIRE(D <= RW_THREADS * RW_MAXPT, "ln_fwd: D=%d too wide", D);
+  SVPC_REQUIRE(!res || pre, "ln_fwd: residual given without a pre buffer");
+  cudaStream_t st = (cudaStream_t)stream;
+  SVPC_DISPATCH(dt_in, TI, SVPC_DISPATCH(dt_out, TO, (ln_fwd_kernel<TI, TO><<<rw_grid(rows), RW_THREADS, 0, st>>>(
+      rows, D, (const TI*)x, (const TI*)res, gamma, beta, eps, pe, pe_period, tt, tt_ids, (TO*)y, (TI*)pre, mean, rstd))));
+  return svpc_check_launch("ln_fwd");
+}
+
+// ------------------------------------------------------------------------------------------------
+// LayerNorm backward
+// ------------------------------------------------------------------------------------------------
+template <typename TG, typename TP>
+__global__ void __launch_bounds__(RW_THREADS) ln_bwd_kernel(int rows, int D, const TG* __restrict__ dy,
+                                                            const TP* __restrict__ pre, const float* __restrict__ mean,
+                                                            const float* __restrict__ rstd, const float* __restrict__ gamma,
+                                                            TP* __restrict__ dpre, float* __restrict__ dgamma,
+                                                            float* __restrict__ dbeta) {
+  __shared__ float red[64];
+  float ag[RW_MAXPT], ab[RW_MAXPT];
+#pragma unroll
+  for (int i = 0; i < RW_MAXPT; ++i) { ag[i] = 0.f; ab[i] = 0.f; }
+  for (int r = blockIdx.x; r < rows; r += gridDim.x) {
+    const long long base = (long long)r * D;
+    const float mu = mean[r], rs = rstd[r];
+    float g[RW_MAXPT], xh[RW_MAXPT];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < RW_MAXPT; ++i) {
+      const int c = threadIdx.x + i * RW_THREADS;
+      g[i] = 0.f; xh[i] = 0.f;
+      if (c < D) {
+        const float d = ldf(dy + base + c);
+        xh[i] = (ldf(pre + base + c) - mu) * rs;
+        g[i] = d * gamma[c];
+        ag[i] += d * xh[i];
+        ab[i] += d;
+        s1 += g[i];
+        s2 += g[i] * xh[i];
+      }
+    }
+    const float2 ss = block_sum2(s1, s2, red);
+    const float m1 = ss.x / D, m2 = ss.y / D;
+#pragma unroll
+    for (int i = 0; i < RW_MAXPT; ++i) {
+      const int c = threadIdx.x + i * RW_THREADS;
+      if (c < D) stf(dpre + base + c, rs * (g[i] - m1 - xh[i] * m2));
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < RW_MAXPT; ++i) {
+    const int c = threadIdx.x + i * RW_THREADS;
+    if (c < D) { atomicAdd(dgamma + c, ag[i]); atomicAdd(dbeta + c, ab[i]); }
+  }
+}
+
+extern "C" int svpc_ln_bwd(int rows, int D, const void* dy, int dt_dy, const void* pre, int dt_pre, const float* mean,
+                           const float* rstd, const float* gamma, void* dpre, float* dgamma, float* dbeta,
+                           svpc_stream_t stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaMemsetAsync(dgamma, 0, sizeof(float) * D, st);
+  cudaMemsetAsync(dbeta, 0, sizeof(float) * D, st);
+  if (rows <= 0) return SVPC_OK;
+  SVPC_REQUIRE(D <= RW_THREADS * RW_MAXPT, "ln_bwd: D=%d too wide", D);
+  const int grid = svpc_imin(rows, SVPC_NUM_SMS * 4);
+  SVPC_DISPATCH(dt_dy, TG, SVPC_DISPATCH(dt_pre, TP, (ln_bwd_kernel<TG, TP><<<grid, RW_THREADS, 0, st>>>(
+      rows, D, (const TG*)dy, (const TP*)pre, mean, rstd, gamma, (TP*)dpre, dgamma, dbeta))));
+  return svpc_check_launch("ln_bwd");
+}
+
+// out[ids[r], c] += dy[r, c]  (nbins small: token types)
+template <typename T>
+__global__ void index_colsum_kernel(int rows, int D, const T* __restrict__ dy, const int* __restrict__ ids, int nbins,
+                                    float* __restrict__ out) {
+  // blockDim.x threads over columns (grid.x strips), grid.y row slices; up to 8 bins kept in registers
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= D) return;
+  float acc[8];
+#pragma unroll
+  for (int b = 0; b < 8; ++b) acc[b] = 0.f;
+  for (int r = blockIdx.y; r < rows; r += gridDim.y) {
+    const int id = ids[r];
+    const float v = ldf(dy + (long long)r * D + c);
+#pragma unroll
+    for (int b = 0; b < 8; ++b) acc[b] += (id == b) ? v : 0.f;
+  }
+#pragma unroll
+  for (int b = 0; b < 8; ++b)
+    if (b < nbins) atomicAdd(out + (long long)b * D + c, acc[b]);
+}
+
+extern "C" int svpc_index_colsum(int rows, int D, const void* dy, int dt, const int* ids, int nbins, float* out,
+                                 svpc_stream_t stream) {
+  SVPC_REQUIRE(nbins <= 8, "index_colsum: nbins=%d > 8", nbins);
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaMemsetAsync(out, 0, sizeof(float) * nbins * D, st);
+  if (rows <= 0) return SVPC_OK;
+  dim3 grid(svpc_cdiv(D, 128), svpc_imin(rows, 256));
+  SVPC_DISPATCH(dt, T, (index_colsum_kernel<T><<<grid, 128, 0, st>>>(rows, D, (const T*)dy, ids, nbins, out)));
+  return svpc_check_launch("index_colsum");
+}
+
+// ------------------------------------------------------------------------------------------------
+// embedding gather + LN(W)
+// ------------------------------------------------------------------------------------------------
+#define EM_THREADS 128
+#define EM_MAXPT 4      // W <= 512
+template <typename T>
+__global__ void __launch_bounds__(EM_THREADS) embed_ln_fwd_kernel(int rows, int W, const float* __restrict__ table,
+                                                                  const int* __restrict__ ids,
+                                                                  const float* __restrict__ gamma,
+                                                                  const float* __restrict__ beta, float eps,
+                                                                  T* __restrict__ y, float* __restrict__ mean,
+                                                                  float* __restrict__ rstd) {
+  __shared__ float red[64];
+  for (int r = blockIdx.x; r < rows; r += gridDim.x) {
+    const float* src = table + (long long)ids[r] * W;
+    float v[EM_MAXPT];
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < EM_MAXPT; ++i) {
+      const int c = threadIdx.x + i * EM_THREADS;
+      v[i] = c < W ? src[c] : 0.f;
+      s += v[i];
+    }
+    const float mu = block_sum(s, red) / W;
+    float q = 0.f;
+#pragma unroll
+    for (int i = 0; i < EM_MAXPT; ++i) {
+      const int c = threadIdx.x + i * EM_THREADS;
+      if (c < W) { const float d = v[i] - mu; q += d * d; }
+    }
+    const float rs = 1.0f / sqrtf(block_sum(q, red) / W + eps);
+    if (threadIdx.x == 0) { mean[r] = mu; rstd[r] = rs; }
+#pragma unroll
+    for (int i = 0; i < EM_MAXPT; ++i) {
+      const int c = threadIdx.x + i * EM_THREADS;
+      if (c < W) stf(y + (long long)r * W + c, (v[i] - mu) * rs * gamma[c] + beta[c]);
+    }
+  }
+}
+
+extern "C" int svpc_embed_ln_fwd(int rows, int W, const float* table, const int* ids, const float* gamma,
+                                 const float* beta, float eps, void* y, int dt, float* mean, float* rstd,
+                                 svpc_stream_t stream) {
+  if (rows <= 0) return SVPC_OK;
+  SVPC_REQUIRE(W <= EM_THREADS * EM_MAXPT, "embed_ln: W=%d too wide", W);
+  cudaStream_t st = (cudaStream_t)stream;
+  SVPC_DISPATCH(dt, T, (embed_ln_fwd_kernel<T><<<rw_grid(rows), EM_THREADS, 0, st>>>(rows, W, table, ids, gamma, beta, eps,
+                                                                                    (T*)y, mean, rstd)));
+  return svpc_check_launch("embed_ln_fwd");
+}
+
+template <typename T>
+__global__ void __launch_bounds__(EM_THREADS) embed_ln_bwd_kernel(int rows, int W, const T* __restrict__ dy,
+                                                                  const float* __restrict__ table,
+                                                                  const int* __restrict__ ids,
+                                                                  const float* __restrict__ mean,
+                                                                  const float* __restrict__ rstd,
+                                                                  const float* __restrict__ gamma, int padding_idx,
+                                                                  float* __restrict__ dtable, float* __restrict__ dgamma,
+                                                                  float* __restrict__ dbeta) {
+  __shared__ float red[64];
+  float ag[EM_MAXPT], ab[EM_MAXPT];
+#pragma unroll
+  for (int i = 0; i < EM_MAXPT; ++i) { ag[i] = 0.f; ab[i] = 0.f; }
+  for (int r = blockIdx.x; r < rows; r += gridDim.x) {
+    const int id = ids[r];
+    const float* src = table + (long long)id * W;
+    const float mu = mean[r], rs = rstd[r];
+    float g[EM_MAXPT], xh[EM_MAXPT];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < EM_MAXPT; ++i) {
+      const int c = threadIdx.x + i * EM_THREADS;
+      g[i] = 0.f; xh[i] = 0.f;
+      if (c < W) {
+        const float d = ldf(dy + (long long)r * W + c);
+        xh[i] = (src[c] - mu) * rs;
+        g[i] = d * gamma[c];
+        ag[i] += d * xh[i];
+        ab[i] += d;
+        s1 += g[i];
+        s2 += g[i] * xh[i];
+      }
+    }
+    const float2 ss = block_sum2(s1, s2, red);
+    const float m1 = ss.x / W, m2 = ss.y / W;
+    if (id != padding_idx) {
+#pragma unroll
+      for (int i = 0; i < EM_MAXPT; ++i) {
+        const int c = threadIdx.x + i * EM_THREADS;
+        if (c < W) atomicAdd(dtable + (long long)id * W + c, rs * (g[i] - m1 - xh[i] * m2));
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < EM_MAXPT; ++i) {
+    const int c = threadIdx.x + i * EM_THREADS;
+    if (c < W) { atomicAdd(dgamma + c, ag[i]); atomicAdd(dbeta + c, ab[i]); }
+  }
+}
+
+extern "C" int svpc_embed_ln_bwd(int rows, int W, int V, const void* dy, int dt, const float* table, const int* ids,
+                                 const float* mean, const float* rstd, const float* gamma, int padding_idx,
+                                 float* dtable, float* dgamma, float* dbeta, svpc_stream_t stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaMemsetAsync(dtable, 0, sizeof(float) * (size_t)V * W, st);
+  cudaMemsetAsync(dgamma, 0, sizeof(float) * W, st);
+  cudaMemsetAsync(dbeta, 0, sizeof(float) * W, st);
+  if (rows <= 0) return SVPC_OK;
+  SVPC_REQUIRE(W <= EM_THREADS * EM_MAXPT, "embed_ln: W=%d too wide", W);
+  const int grid = svpc_imin(rows, SVPC_NUM_SMS * 4);
+  SVPC_DISPATCH(dt, T, (embed_ln_bwd_kernel<T><<<grid, EM_THREADS, 0, st>>>(rows, W, (const T*)dy, table, ids, mean, rstd,
+                                                                           gamma, padding_idx, dtable, dgamma, dbeta)));
+  return svpc_check_launch("embed_ln_bwd");
+}
+
+// ------------------------------------------------------------------------------------------------
+// video features: gather the first Lv rows of every clip from the per-step (B, L, F) tensors, LN statistics,
+// write the normalised rows in the compute dtype (the only pass over the 1.23 MB/clip of fp32 features)
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(RW_THREADS) video_ln_pack_kernel(int n_rows, int B, int L, int Lv, int F,
+                                                                   const long long* __restrict__ feat_ptrs,
+                                                                   const int* __restrict__ clip_t,
+                                                                   const int* __restrict__ clip_b, float eps,
+                                                                   T* __restrict__ xhat, float* __restrict__ mean,
+                                                                   float* __restrict__ rstd) {
+  __shared__ float red[64];
+  const int F4 = F >> 2;
+  for (int r = blockIdx.x; r < n_rows; r += gridDim.x) {
+    const int n = r / Lv, row = r - n * Lv;
+    const float* src = reinterpret_cast<const float*>(feat_ptrs[clip_t[n]]) + ((long long)clip_b[n] * L + row) * F;
+    const float4* src4 = reinterpret_cast<const float4*>(src);
+    float4 v[RW_MAXPT / 4];
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < RW_MAXPT / 4; ++i) {
+      const int c = threadIdx.x + i * RW_THREADS;
+      v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (c < F4) { v[i] = __ldg(src4 + c); s += v[i].x + v[i].y + v[i].z + v[i].w; }
+    }
+    const float mu = block_sum(s, red) / F;
+    float q = 0.f;
+#pragma unroll
+    for (int i = 0; i < RW_MAXPT / 4; ++i) {
+      const int c = threadIdx.x + i * RW_THREADS;
+      if (c < F4) {
+        const float a = v[i].x - mu, b = v[i].y - mu, cc = v[i].z - mu, d = v[i].w - mu;
+        q += a * a + b * b + cc * cc + d * d;
+      }
+    }
+    const float rs = 1.0f / sqrtf(block_sum(q, red) / F + eps);
+    if (threadIdx.x == 0) { mean[r] = mu; rstd[r] = rs; }
+    T* dst = xhat + (long long)r * F;
+#pragma unroll
+    for (int i = 0; i < RW_MAXPT / 4; ++i) {
+      const int c = threadIdx.x + i * RW_THREADS;
+      if (c < F4) {
+        stf(dst + 4 * c + 0, (v[i].x - mu) * rs);
+        stf(dst + 4 * c + 1, (v[i].y - mu) * rs);
+        stf(dst + 4 * c + 2, (v[i].z - mu) * rs);
+        stf(dst + 4 * c + 3, (v[i].w - mu) * rs);
+      }
+    }
+  }
+}
+
+extern "C" int svpc_video_ln_pack(int n_clips, int B, int L, int Lv, int F, const long long* feat_ptrs,
+                                  const int* clip_t, const int* clip_b, float eps, void* xhat, int dt, float* mean,
+                                  float* rstd, svpc_stream_t stream) {
+  if (n_clips <= 0) return SVPC_OK;
+  SVPC_REQUIRE(F % 4 == 0 && F <= RW_THREADS * RW_MAXPT, "video_ln_pack: F=%d must be a multiple of 4 and <= 4096", F);
+  cudaStream_t st = (cudaStream_t)stream;
+  const int n_rows = n_clips * Lv;
+  SVPC_DISPATCH(dt, T, (video_ln_pack_kernel<T><<<svpc_imin(n_rows, SVPC_NUM_SMS * 16), RW_THREADS, 0, st>>>(
+      n_rows, B, L, Lv, F, feat_ptrs, clip_t, clip_b, eps, (T*)xhat, mean, rstd)));
+  return svpc_check_launch("video_ln_pack");
+}
+
+// ------------------------------------------------------------------------------------------------
+// ingredient vectors: segment means between [SEP]s (+ pe[j])
+// ------------------------------------------------------------------------------------------------
+__global__ void seg_scan_kernel(int B, int Li, const int* __restrict__ sep_mask, const int* __restrict__ cu_ingr,
+                                int* __restrict__ row_seg, int* __restrict__ seg_lohi) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  const int g0 = cu_ingr[b], ni = cu_ingr[b + 1] - g0;
+  int prev = 0, j = 0;
+  for (int r = 0; r < Li; ++r) row_seg[b * Li + r] = -1;
+  for (int r = 0; r < Li && j < ni; ++r) {
+    if (sep_mask[b * Li + r] == 1) {
+      seg_lohi[2 * (g0 + j)] = prev;
+      seg_lohi[2 * (g0 + j) + 1] = r;
+      for (int t = prev; t < r; ++t) row_seg[b * Li + t] = g0 + j;
+      prev = r + 1;
+      ++j;
+    }
+  }
+  for (; j < ni; ++j) { seg_lohi[2 * (g0 + j)] = 0; seg_lohi[2 * (g0 + j) + 1] = 0; }   // fewer [SEP]s than announced
+}
+
+template <typename T>
+__global__ void segmean_fwd_kernel(int B, int Li, int D, const T* __restrict__ x, const int* __restrict__ cu_ingr,
+                                   const int* __restrict__ seg_lohi, const float* __restrict__ pe,
+                                   float* __restrict__ E0) {
+  const int g = blockIdx.x;
+  // video of this ingredient
+  int b = 0;
+  while (b + 1 < B && cu_ingr[b + 1] <= g) ++b;
+  const int j = g - cu_ingr[b];
+  const int lo = seg_lohi[2 * g], hi = seg_lohi[2 * g + 1];
+  const float inv = 1.0f / (float)(hi - lo);      // empty segment -> inf * 0 = NaN, as torch's mean of empty
+  for (int c = threadIdx.x; c < D; c += blockDim.x) {
+    float s = 0.f;
+    for (int r = lo; r < hi; ++r) s += ldf(x + ((long long)b * Li + r) * D + c);
+    E0[(long long)g * D + c] = s * inv + pe[(long long)j * D + c];
+  }
+}
+
+template <typename T>
+__global__ void segmean_bwd_kernel(int rows, int D, const float* __restrict__ dE0, const int* __restrict__ row_seg,
+                                   const int* __restrict__ seg_lohi, T* __restrict__ dx) {
+  const int r = blockIdx.x;
+  const int g = row_seg[r];
+  float inv = 0.f;
+  if (g >= 0) inv = 1.0f / (float)(seg_lohi[2 * g + 1] - seg_lohi[2 * g]);
+  for (int c = threadIdx.x; c < D; c += blockDim.x)
+    stf(dx + (long long)r * D + c, g >= 0 ? dE0[(long long)g * D + c] * inv : 0.f);
+}
+
+extern "C" int svpc_segmean_fwd(int B, int Li, int D, int NI, const void* x, int dt, const int* sep_mask,
+                                const int* cu_ingr, const float* pe, float* E0, int* scratch_row_seg,
+                                int* scratch_seg_lohi, svpc_stream_t stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  if (B <= 0 || NI <= 0) return SVPC_OK;
+  seg_scan_kernel<<<svpc_cdiv(B, 64), 64, 0, st>>>(B, Li, sep_mask, cu_ingr, scratch_row_seg, scratch_seg_lohi);
+  int rc = svpc_check_launch("seg_scan");
+  if (rc) return rc;
+  SVPC_DISPATCH(dt, T, (segmean_fwd_kernel<T><<<NI, 256, 0, st>>>(B, Li, D, (const T*)x, cu_ingr, scratch_seg_lohi, pe, E0)));
+  return svpc_check_launch("segmean_fwd");
+}
+
+extern "C" int svpc_segmean_bwd(int B, int Li, int D, int NI, const float* dE0, const int* sep_mask, const int* cu_ingr,
+                                void* dx, int dt, int* scratch_row_seg, int* scratch_seg_lohi, svpc_stream_t stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  if (B <= 0) return SVPC_OK;
+  seg_scan_kernel<<<svpc_cdiv(B, 64), 64, 0, st>>>(B, Li, sep_mask, cu_ingr, scratch_row_seg, scratch_seg_lohi);
+  int rc = svpc_check_launch("seg_scan");
+  if (rc) return rc;
+  SVPC_DISPATCH(dt, T, (segmean_bwd_kernel<T><<<B * Li, 256, 0, st>>>(B * Li, D, dE0, scratch_row_seg, scratch_seg_lohi, (T*)dx)));
+  return svpc_check_launch("segmean_bwd");
+}
+
+__global__ void ragged_mean_fwd_kernel(int D, const float* __restrict__ x, const int* __restrict__ cu, float* __restrict__ y) {
+  const int b = blockIdx.x, lo = cu[b], hi = cu[b + 1];
+  const float inv = 1.0f / (float)(hi - lo);
+  for (int c = threadIdx.x; c < D; c += blockDim.x) {
+    float s = 0.f;
+    for (int r = lo; r < hi; ++r) s += x[(long long)r * D + c];
+    y[(long long)b * D + c] = s * inv;
+  }
+}
+__global__ void ragged_mean_bwd_kernel(int D, const float* __restrict__ dy, const int* __restrict__ cu, float* __restrict__ dx) {
+  const int b = blockIdx.x, lo = cu[b], hi = cu[b + 1];
+  const float inv = 1.0f / (float)(hi - lo);
+  for (int c = threadIdx.x; c < D; c += blockDim.x) {
+    const float g = dy[(long long)b * D + c] * inv;
+    for (int r = lo; r < hi; ++r) dx[(long long)r * D + c] = g;
+  }
+}
+extern "C" int svpc_ragged_mean_fwd(int B, int D, const float* x, const int* cu, float* y, svpc_stream_t stream) {
+  if (B <= 0) return SVPC_OK;
+  ragged_mean_fwd_kernel<<<B, 256, 0, (cudaStream_t)stream>>>(D, x, cu, y);
+  return svpc_check_launch("ragged_mean_fwd");
+}
+extern "C" int svpc_ragged_mean_bwd(int B, int D, const float* dy, const int* cu, float* dx, svpc_stream_t stream) {
+  if (B <= 0) return SVPC_OK;
+  ragged_mean_bwd_kernel<<<B, 256, 0, (cudaStream_t)stream>>>(D, dy, cu, dx);
+  return svpc_check_launch("ragged_mean_bwd");
+}
+
+// y = x / sum(x)  (model.py:798)
+__global__ void row_normalize_fwd_kernel(int cols, const float* __restrict__ x, float* __restrict__ y) {
+  __shared__ float red[64];
+  const long long base = (long long)blockIdx.x * cols;
+  float s = 0.f;
+  for (int c = threadIdx.x; c < cols; c += blockDim.x) s += x[base + c];
+  s = block_sum(s, red);
+  for (int c = threadIdx.x; c < cols; c += blockDim.x) y[base + c] = x[base + c] / s;
+}
+// dx = (dy - sum(dy * x) / s) / s
+__global__ void row_normalize_bwd_kernel(int cols, const float* __restrict__ dy, const float* __restrict__ x,
+                                         float* __restrict__ dx) {
+  __shared__ float red[64];
+  const long long base = (long long)blockIdx.x * cols;
+  float s = 0.f, t = 0.f;
+  for (int c = threadIdx.x; c < cols; c += blockDim.x) { s += x[base + c]; t += dy[base + c] * x[base + c]; }
+  const float2 r = block_sum2(s, t, red);
+  for (int c = threadIdx.x; c < cols; c += blockDim.x) dx[base + c] = (dy[base + c] - r.y / r.x) / r.x;
+}
+extern "C" int svpc_row_normalize_fwd(int rows, int cols, const float* x, float* y, svpc_stream_t stream) {
+  if (rows <= 0) return SVPC_OK;
+  row_normalize_fwd_kernel<<<rows, 128, 0, (cudaStream_t)stream>>>(cols, x, y);
+  return svpc_check_launch("row_normalize_fwd");
+}
+extern "C" int svpc_row_normalize_bwd(int rows, int cols, const float* dy, const float* x, float* dx, svpc_stream_t stream) {
+  if (rows <= 0) return SVPC_OK;
+  row_normalize_bwd_kernel<<<rows, 128, 0, (cudaStream_t)stream>>>(cols, dy, x, dx);
+  return svpc_check_launch("row_normalize_bwd");
+}

@@ -1,0 +1,531 @@
+"""ctypes binding of ``libsvpc_b200.so`` (C ABI in ``include/svpc_b200.h``): the ONLY operator implementation of the
+product.  torch supplies device memory and the current CUDA stream; every function below checks its tensors are CUDA
+and in the expected layout, allocates outputs with torch and enqueues hand-written sm_100a kernels.  No CPU path:
+a missing library or a non-CUDA tensor raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libsvpc_b200.so")
+
+F32, BF16 = 0, 1
+_DT = {torch.float32: F32, torch.bfloat16: BF16}
+GEMM_AUTO, GEMM_SIMT, GEMM_TC = 0, 1, 2
+
+
+class SvpcError(RuntimeError):
+    pass
+
+
+def load_library(path: str = LIB_PATH):
+    if not os.path.isfile(path):
+        raise SvpcError(f"{path} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                        f"(or `make -C svpc_b200/csrc`); there is no CPU fallback for the SVPC operators")
+    lib = C.CDLL(path)
+    lib.svpc_last_error.restype = C.c_char_p
+    lib.svpc_launch_count.restype = C.c_longlong
+    return lib
+
+
+def _ptr(t):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _ll(x):
+    return C.c_longlong(int(x))
+
+
+def _f(x):
+    return C.c_float(float(x))
+
+
+def _mat_strides(t):
+    """Element strides of a 2-D view with size-1 dimensions normalised so that one of the two is 1."""
+    s0, s1 = t.stride()
+    if t.shape[1] == 1:
+        s1 = 1
+    if t.shape[0] == 1 and s1 != 1:
+        s0 = 1
+    if s0 != 1 and s1 != 1:
+        raise SvpcError(f"gemm operand needs a unit stride, got shape {tuple(t.shape)} strides {t.stride()}")
+    return s0, s1
+
+
+class CudaBackend:
+    name = "cuda-sm100a"
+
+    def __init__(self):
+        self.lib = load_library()
+        self.gemm_route = GEMM_AUTO
+        self._ptr_cache = {}
+
+    # ------------------------------------------------------------------ plumbing
+    def _call(self, fn, *args):
+        rc = getattr(self.lib, fn)(*args, C.c_void_p(torch.cuda.current_stream().cuda_stream))
+        if rc != 0:
+            raise SvpcError(f"{fn} failed ({rc}): {self.lib.svpc_last_error().decode()}")
+
+    @staticmethod
+    def _chk(*ts):
+        for t in ts:
+            if t is not None and not t.is_cuda:
+                raise SvpcError("svpc_b200 operators need CUDA tensors (no CPU path)")
+
+    @staticmethod
+    def _c(t):
+        return t if t.is_contiguous() else t.contiguous()
+
+    def launch_count(self):
+        return int(self.lib.svpc_launch_count())
+
+    def reset_launch_count(self):
+        self.lib.svpc_reset_launch_count()
+
+    # ------------------------------------------------------------------ dense
+    def gemm(self, a, bt, out_dtype, bias=None, act=0, residual=None, out=None, accumulate=False, want_pre=False,
+             route=None):
+        """out[M,N] = act(a[M,K] @ bt[N,K]^T + bias) + residual.  a / bt may be any 2-D views with one unit stride."""
+        self._chk(a, bt, bias, residual, out)
+        M, K = a.shape
+        N = bt.shape[0]
+        assert bt.shape[1] == K, (a.shape, bt.shape)
+        if out is None:
+            out = torch.empty(M, N, dtype=out_dtype, device=a.device)
+        assert out.shape == (M, N) and (N == 1 or out.stride(1) == 1)
+        pre = torch.empty(M, N, dtype=out.dtype, device=a.device) if want_pre else None
+        if residual is not None:
+            assert residual.dtype == out.dtype and residual.shape == (M, N) and (N == 1 or residual.stride(1) == 1)
+        if M > 0 and N > 0:
+            sa, sb = _mat_strides(a), _mat_strides(bt)
+            self._call("svpc_gemm", M, N, K,
+                       _ptr(a), _DT[a.dtype], _ll(sa[0]), _ll(sa[1]),
+                       _ptr(bt), _DT[bt.dtype], _ll(sb[0]), _ll(sb[1]),
+                       _ptr(out), _DT[out.dtype], _ll(out.stride(0)),
+                       _ptr(bias), int(act),
+                       _ptr(residual), _ll(residual.stride(0) if residual is not None else 0),
+                       _ptr(pre), _ll(N),
+                       int(bool(accumulate)), int(self.gemm_route if route is None else route))
+        return (out, pre) if want_pre else out
+
+    def act_bwd(self, dy, ref, act):
+        self._chk(dy, ref)
+        dy = self._c(dy)
+        rows, cols = dy.shape
+        dz = torch.empty_like(dy)
+        dbias = torch.empty(cols, dtype=torch.float32, device=dy.device)
+        self._call("svpc_act_bwd", rows, cols, _ptr(dy), _ptr(None if ref is None else self._c(ref)), _DT[dy.dtype], int(act),
+                   _ptr(dz), _ptr(dbias))
+        return dz, dbias
+
+    def colsum(self, x):
+        self._chk(x)
+        x = self._c(x)
+        out = torch.empty(x.shape[1], dtype=torch.float32, device=x.device)
+        self._call("svpc_colsum", x.shape[0], x.shape[1], _ptr(x), _DT[x.dtype], _ptr(out))
+        return out
+
+    def cast(self, x, dtype):
+        self._chk(x)
+        if x.dtype == dtype:
+            return x
+        x = self._c(x)
+        out = torch.empty(x.shape, dtype=dtype, device=x.device)
+        self._call("svpc_cast", _ll(x.numel()), _ptr(x), _DT[x.dtype], _ptr(out), _DT[dtype])
+        return out
+
+    def sum_all(self, x):
+        self._chk(x)
+        x = self._c(x)
+        out = torch.empty((), dtype=torch.float32, device=x.device)
+        self._call("svpc_sum", _ll(x.numel()), _ptr(x), _ptr(out))
+        return out
+
+    # ------------------------------------------------------------------ layer norm / embeddings
+    def ln_fwd(self, x, res, gamma, beta, eps, out_dtype, pe=None, pe_period=0, tt=None, tt_ids=None):
+        self._chk(x, res, gamma, beta, pe, tt, tt_ids)
+        x = self._c(x)
+        rows, D = x.shape
+        y = torch.empty(rows, D, dtype=out_dtype, device=x.device)
+        mean = torch.empty(rows, dtype=torch.float32, device=x.device)
+        rstd = torch.empty(rows, dtype=torch.float32, device=x.device)
+        pre = x
+        if res is not None:
+            res = self._c(res)
+            assert res.dtype == x.dtype and res.shape == x.shape
+            pre = torch.empty_like(x)
+        self._call("svpc_ln_fwd", rows, D, _ptr(x), _ptr(res), _DT[x.dtype], _ptr(gamma), _ptr(beta), _f(eps),
+                   _ptr(pe), int(pe_period), _ptr(tt), _ptr(tt_ids), _ptr(y), _DT[out_dtype],
+                   _ptr(pre if res is not None else None), _ptr(mean), _ptr(rstd))
+        return y, pre, mean, rstd
+
+    def ln_bwd(self, dy, pre, mean, rstd, gamma):
+        self._chk(dy, pre)
+        dy = self._c(dy)
+        rows, D = dy.shape
+        dpre = torch.empty_like(pre)
+        dgamma = torch.empty(D, dtype=torch.float32, device=dy.device)
+        dbeta = torch.empty(D, dtype=torch.float32, device=dy.device)
+        self._call("svpc_ln_bwd", rows, D, _ptr(dy), _DT[dy.dtype], _ptr(pre), _DT[pre.dtype], _ptr(mean), _ptr(rstd),
+                   _ptr(gamma), _ptr(dpre), _ptr(dgamma), _ptr(dbeta))
+        return dpre, dgamma, dbeta
+
+    def index_colsum(self, dy, ids, nbins):
+        self._chk(dy, ids)
+        dy = self._c(dy)
+        out = torch.empty(nbins, dy.shape[1], dtype=torch.float32, device=dy.device)
+        self._call("svpc_index_colsum", dy.shape[0], dy.shape[1], _ptr(dy), _DT[dy.dtype], _ptr(ids), int(nbins), _ptr(out))
+        return out
+
+    def embed_ln_fwd(self, table, ids, gamma, beta, eps, out_dtype):
+        self._chk(table, ids)
+        rows, W = ids.numel(), table.shape[1]
+        y = torch.empty(rows, W, dtype=out_dtype, device=table.device)
+        mean = torch.empty(rows, dtype=torch.float32, device=table.device)
+        rstd = torch.empty(rows, dtype=torch.float32, device=table.device)
+        self._call("svpc_embed_ln_fwd", rows, W, _ptr(self._c(table)), _ptr(ids), _ptr(gamma), _ptr(beta), _f(eps), _ptr(y),
+                   _DT[out_dtype], _ptr(mean), _ptr(rstd))
+        return y, mean, rstd
+
+    def embed_ln_bwd(self, dy, table, ids, mean, rstd, gamma, eps, padding_idx):
+        self._chk(dy, table, ids)
+        dy = self._c(dy)
+        V, W = table.shape
+        dtable = torch.empty(V, W, dtype=torch.float32, device=dy.device)
+        dgamma = torch.empty(W, dtype=torch.float32, device=dy.device)
+        dbeta = torch.empty(W, dtype=torch.float32, device=dy.device)
+        self._call("svpc_embed_ln_bwd", dy.shape[0], W, V, _ptr(dy), _DT[dy.dtype], _ptr(self._c(table)), _ptr(ids), _ptr(mean),
+                   _ptr(rstd), _ptr(gamma), int(-1 if padding_idx is None else padding_idx), _ptr(dtable), _ptr(dgamma),
+                   _ptr(dbeta))
+        return dtable, dgamma, dbeta
+
+    def video_ln_pack(self, feats_list, clip_t, clip_b, Lv, eps, out_dtype):
+        f0 = feats_list[0]
+        self._chk(f0, clip_t, clip_b)
+        B, L, Fdim = f0.shape
+        for f in feats_list:
+            if not (f.is_cuda and f.dtype == torch.float32 and f.is_contiguous() and f.shape == f0.shape):
+                raise SvpcError("video features must be contiguous fp32 CUDA tensors of one shape (B, L, F)")
+        key = tuple(f.data_ptr() for f in feats_list)
+        ptrs = self._ptr_cache.get(key)
+        if ptrs is None:
+            if len(self._ptr_cache) > 64:
+                self._ptr_cache.clear()
+            ptrs = torch.tensor(list(key), dtype=torch.int64).to(f0.device)
+            self._ptr_cache[key] = ptrs
+        n_clips = clip_t.numel()
+        xhat = torch.empty(n_clips * Lv, Fdim, dtype=out_dtype, device=f0.device)
+        mean = torch.empty(n_clips * Lv, dtype=torch.float32, device=f0.device)
+        rstd = torch.empty(n_clips * Lv, dtype=torch.float32, device=f0.device)
+        self._call("svpc_video_ln_pack", n_clips, B, L, int(Lv), Fdim, _ptr(ptrs), _ptr(clip_t), _ptr(clip_b), _f(eps),
+                   _ptr(xhat), _DT[out_dtype], _ptr(mean), _ptr(rstd))
+        return xhat, mean, rstd
+
+    # ------------------------------------------------------------------ attention
+    @staticmethod
+    def _rowview(t):
+        assert t.dim() == 2 and t.stride(1) == 1, (t.shape, t.stride())
+        return t
+
+    def attn_fwd(self, q, k, v, q_off, q_len, k_off, k_len, key_mask, causal, n_heads, max_lq, max_lk, out_dtype):
+        self._chk(q, k, v, q_off, key_mask)
+        q, k, v = self._rowview(q), self._rowview(k), self._rowview(v)
+        D = q.shape[1]
+        assert out_dtype == q.dtype == k.dtype == v.dtype
+        ctx = torch.empty(q.shape[0], D, dtype=out_dtype, device=q.device)
+        self._call("svpc_attn_fwd", int(q_off.numel()), int(n_heads), D // n_heads, _ptr(q), _ll(q.stride(0)), _ptr(k),
+                   _ll(k.stride(0)), _ptr(v), _ll(v.stride(0)), _DT[q.dtype], _ptr(q_off), _ptr(q_len), _ptr(k_off),
+                   _ptr(k_len), _ptr(key_mask), int(bool(causal)), int(max_lq), int(max_lk), _ptr(ctx), _ll(D))
+        return ctx
+
+    def attn_bwd(self, dctx, q, k, v, q_off, q_len, k_off, k_len, key_mask, causal, n_heads, max_lq, max_lk, dq, dk, dv):
+        self._chk(dctx, q, k, v, dq, dk, dv)
+        dctx = self._c(dctx)
+        D = q.shape[1]
+        for t in (q, k, v, dq, dk, dv):
+            self._rowview(t)
+        assert dctx.dtype == q.dtype == dq.dtype == dk.dtype == dv.dtype
+        self._call("svpc_attn_bwd", int(q_off.numel()), int(n_heads), D // n_heads, _ptr(q), _ll(q.stride(0)), _ptr(k),
+                   _ll(k.stride(0)), _ptr(v), _ll(v.stride(0)), _DT[q.dtype], _ptr(q_off), _ptr(q_len), _ptr(k_off),
+                   _ptr(k_len), _ptr(key_mask), int(bool(causal)), int(max_lq), int(max_lk), _ptr(dctx), _ll(D),
+                   _ptr(dq), _ll(dq.stride(0)), _ptr(dk), _ll(dk.stride(0)), _ptr(dv), _ll(dv.stride(0)))
+
+    # ------------------------------------------------------------------ ingredients
+    def segmean_fwd(self, x, sep_mask, cu_ingr, pe, NI):
+        self._chk(x, sep_mask, cu_ingr, pe)
+        x = self._c(x)
+        B, Li = sep_mask.shape
+        D = x.shape[1]
+        NI = int(NI)
+        E0 = torch.empty(NI, D, dtype=torch.float32, device=x.device)
+        row_seg = torch.empty(B * Li, dtype=torch.int32, device=x.device)
+        lohi = torch.empty(max(NI, 1) * 2, dtype=torch.int32, device=x.device)
+        self._call("svpc_segmean_fwd", B, Li, D, NI, _ptr(x), _DT[x.dtype], _ptr(sep_mask), _ptr(cu_ingr), _ptr(pe), _ptr(E0),
+                   _ptr(row_seg), _ptr(lohi))
+        return E0
+
+    def segmean_bwd(self, dE0, sep_mask, cu_ingr, Li, out_dtype):
+        self._chk(dE0, sep_mask)
+        dE0 = self._c(dE0)
+        B = sep_mask.shape[0]
+        NI, D = dE0.shape
+        dx = torch.empty(B * Li, D, dtype=out_dtype, device=dE0.device)
+        row_seg = torch.empty(B * Li, dtype=torch.int32, device=dE0.device)
+        lohi = torch.empty(max(NI, 1) * 2, dtype=torch.int32, device=dE0.device)
+        self._call("svpc_segmean_bwd", B, Li, D, NI, _ptr(dE0), _ptr(sep_mask), _ptr(cu_ingr), _ptr(dx), _DT[out_dtype],
+                   _ptr(row_seg), _ptr(lohi))
+        return dx
+
+    def ragged_mean_fwd(self, x, cu):
+        self._chk(x, cu)
+        x = self._c(x)
+        B = cu.numel() - 1
+        y = torch.empty(B, x.shape[1], dtype=torch.float32, device=x.device)
+        self._call("svpc_ragged_mean_fwd", B, x.shape[1], _ptr(x), _ptr(cu), _ptr(y))
+        return y
+
+    def ragged_mean_bwd(self, dy, cu, NI):
+        self._chk(dy, cu)
+        dy = self._c(dy)
+        B = cu.numel() - 1
+        dx = torch.empty(int(NI), dy.shape[1], dtype=torch.float32, device=dy.device)
+        self._call("svpc_ragged_mean_bwd", B, dy.shape[1], _ptr(dy), _ptr(cu), _ptr(dx))
+        return dx
+
+    def row_normalize_fwd(self, x):
+        self._chk(x)
+        x = self._c(x)
+        y = torch.empty_like(x)
+        self._call("svpc_row_normalize_fwd", x.shape[0], x.shape[1], _ptr(x), _ptr(y))
+        return y
+
+    def row_normalize_bwd(self, dy, x):
+        self._chk(dy, x)
+        dy, x = self._c(dy), self._c(x)
+        dx = torch.empty_like(x)
+        self._call("svpc_row_normalize_bwd", x.shape[0], x.shape[1], _ptr(dy), _ptr(x), _ptr(dx))
+        return dx
+
+    # ------------------------------------------------------------------ visual simulator recurrence
+    def reasoner_fwd(self, E0, lay, w2v, clog, w4s):
+        cu_ingr, cu_steps, clip_ent_off = lay["cu_ingr"], lay["cu_steps"], lay["clip_ent_off"]
+        self._chk(E0, cu_ingr, cu_steps, clip_ent_off, w2v, clog, w4s)
+        E0, w2v, clog, w4s = self._c(E0), self._c(w2v), self._c(clog), self._c(w4s)
+        B, max_ni, NE = int(lay["B"]), int(lay["max_ni"]), int(lay["NE"])
+        Nc, D = w2v.shape
+        ent = torch.empty(NE, dtype=torch.float32, device=E0.device)
+        a = torch.empty(NE, dtype=torch.float32, device=E0.device)
+        ebar = torch.empty(Nc, D, dtype=torch.float32, device=E0.device)
+        Es = torch.empty(NE, D, dtype=torch.float32, device=E0.device)
+        self._call("svpc_reasoner_fwd", B, D, max_ni, _ptr(E0), _ptr(cu_ingr), _ptr(cu_steps), _ptr(clip_ent_off),
+                   _ptr(w2v), _ptr(clog), _ptr(w4s), _ptr(ent), _ptr(ebar), _ptr(Es), _ptr(a))
+        return ent, ebar, Es, (a,)
+
+    def reasoner_bwd(self, d_ent, d_ebar, d_Es, E0, lay, w2v, clog, w4s, ent, ebar, Es, saved):
+        cu_ingr, cu_steps, clip_ent_off = lay["cu_ingr"], lay["cu_steps"], lay["clip_ent_off"]
+        (a,) = saved
+        B, max_ni = int(lay["B"]), int(lay["max_ni"])
+        Nc, D = w2v.shape
+        E0, w2v, clog, w4s = self._c(E0), self._c(w2v), self._c(clog), self._c(w4s)
+        dE0 = torch.empty_like(E0)
+        dw2v = torch.empty_like(w2v)
+        dclog = torch.empty_like(clog)
+        dw4s = torch.empty_like(w4s)
+        self._call("svpc_reasoner_bwd", B, D, max_ni, _ptr(E0), _ptr(cu_ingr), _ptr(cu_steps), _ptr(clip_ent_off),
+                   _ptr(w2v), _ptr(clog), _ptr(w4s), _ptr(ent), _ptr(ebar), _ptr(Es), _ptr(a),
+                   _ptr(self._c(d_ent)), _ptr(self._c(d_ebar)), _ptr(self._c(d_Es)), _ptr(dE0), _ptr(dw2v), _ptr(dclog),
+                   _ptr(dw4s))
+        return dE0, dw2v, dclog, dw4s
+
+    # ------------------------------------------------------------------ pointer-generator + caption loss
+    def pointer_fwd(self, dec, G, Esrc, wpgen, bpgen, logits, lay):
+        self._chk(dec, G, Esrc, wpgen, bpgen, logits)
+        dec, G, Esrc, wpgen, logits = self._c(dec), self._c(G), self._c(Esrc), self._c(wpgen), self._c(logits)
+        Lt, V = int(lay["Lt"]), int(lay["V"])
+        R, D = dec.shape
+        Nc = R // Lt
+        max_ni, max_vx = max(int(lay["max_ni"]), 1), int(lay["max_vx"])
+        dev = dec.device
+        P = torch.empty(int(lay["P_numel"]), dtype=torch.float32, device=dev)
+        rows = torch.empty(R, dtype=torch.float32, device=dev)
+        alpha = torch.empty(R, max_ni, dtype=torch.float32, device=dev)
+        pgen = torch.empty(R, dtype=torch.float32, device=dev)
+        ctx = torch.empty(R, D, dtype=torch.float32, device=dev)
+        self._call("svpc_pointer_fwd", Nc, Lt, D, V, max_ni, max_vx, _ptr(dec), _DT[dec.dtype], _ptr(G), _ptr(Esrc),
+                   _ptr(lay["clip_src_off"]), _ptr(lay["clip_ni"]), _ptr(lay["clip_gi"]), _ptr(lay["clip_vx"]),
+                   _ptr(lay["clip_P_off"]), _ptr(lay["tok_ptr"]), _ptr(lay["tok_ids"]), _ptr(wpgen), _ptr(bpgen),
+                   _ptr(logits), _ll(logits.stride(0)), _ptr(lay["labels"]), _f(lay["smoothing"]), _ptr(P), _ptr(rows),
+                   _ptr(alpha), _ptr(pgen), _ptr(ctx))
+        return P, rows, (alpha, pgen, ctx)
+
+    def pointer_bwd(self, dP, dloss, dec, G, Esrc, wpgen, bpgen, logits, lay, P, saved):
+        alpha, pgen, ctx = saved
+        dec, G, Esrc, wpgen, logits = self._c(dec), self._c(G), self._c(Esrc), self._c(wpgen), self._c(logits)
+        Lt, V = int(lay["Lt"]), int(lay["V"])
+        R, D = dec.shape
+        Nc = R // Lt
+        max_ni, max_vx = max(int(lay["max_ni"]), 1), int(lay["max_vx"])
+        dev = dec.device
+        ddec = torch.empty_like(dec)
+        dG = torch.zeros_like(G)
+        dE = torch.zeros_like(Esrc)
+        du = torch.empty(R, dtype=torch.float32, device=dev)
+        dw = torch.empty(2 * D, dtype=torch.float32, device=dev)
+        db = torch.empty(1, dtype=torch.float32, device=dev)
+        dlog = torch.empty_like(logits)
+        dloss = dloss.to(torch.float32).reshape(1)
+        self._call("svpc_pointer_bwd", Nc, Lt, D, V, max_ni, max_vx, _ptr(dec), _DT[dec.dtype], _ptr(G), _ptr(Esrc),
+                   _ptr(lay["clip_src_off"]), _ptr(lay["clip_ni"]), _ptr(lay["clip_gi"]), _ptr(lay["clip_vx"]),
+                   _ptr(lay["clip_P_off"]), _ptr(lay["tok_ptr"]), _ptr(lay["tok_ids"]), _ptr(wpgen), _ptr(logits),
+                   _ll(logits.stride(0)), _ptr(lay["labels"]), _f(lay["smoothing"]), _ptr(P), _ptr(alpha), _ptr(pgen),
+                   _ptr(ctx), _ptr(None if dP is None else self._c(dP)), _ptr(dloss), _ptr(ddec), _ptr(dG), _ptr(dE),
+                   _ptr(du), _ptr(dw), _ptr(db), _ptr(dlog))
+        return ddec, dG, dE, dw, db, dlog
+
+    def softmax_ls_fwd(self, logits, labels, V, smoothing):
+        self._chk(logits, labels)
+        logits = self._c(logits)
+        R = logits.shape[0]
+        P = torch.empty(R, V, dtype=torch.float32, device=logits.device)
+        rows = torch.empty(R, dtype=torch.float32, device=logits.device)
+        self._call("svpc_softmax_ls_fwd", R, int(V), _ptr(logits), _ll(logits.stride(0)), _ptr(labels), _f(smoothing), _ptr(P),
+                   _ptr(rows))
+        return P, rows
+
+    def softmax_ls_bwd(self, dP, dloss, logits, labels, V, smoothing, P):
+        R = logits.shape[0]
+        dlog = torch.empty(R, logits.shape[1], dtype=torch.float32, device=logits.device)
+        dloss = dloss.to(torch.float32).reshape(1)
+        self._call("svpc_softmax_ls_bwd", R, int(V), _ptr(None if dP is None else self._c(dP)), _ptr(dloss), _ptr(P),
+                   _ptr(labels), _f(smoothing), _ptr(dlog), _ll(dlog.stride(0)))
+        return dlog
+
+    # ------------------------------------------------------------------ textual re-simulator
+    def gumbel_fwd(self, P, g, emb, lay, text_mask):
+        self._chk(P, g, emb, text_mask)
+        Lt, V = int(lay["Lt"]), int(lay["V"])
+        Nc = lay["clip_P_off"].numel()
+        W = emb.shape[1]
+        dev = P.device
+        assert g.numel() == P.numel()
+        x = torch.empty(Nc, W, dtype=torch.float32, device=dev)
+        idx = torch.empty(Nc * Lt, dtype=torch.int32, device=dev)
+        yval = torch.empty(Nc * Lt, dtype=torch.float32, device=dev)
+        self._call("svpc_gumbel_fwd", Nc, Lt, V, W, _ptr(P), _ptr(self._c(g)), _ptr(lay["clip_P_off"]), _ptr(lay["clip_vx"]),
+                   _f(lay["tau"]), _ptr(self._c(emb)), _ptr(text_mask), _ptr(x), _ptr(idx), _ptr(yval))
+        return x, idx, yval
+
+    def gumbel_bwd(self, dx, P, g, emb, lay, text_mask, idx, yval):
+        Lt, V = int(lay["Lt"]), int(lay["V"])
+        Nc = lay["clip_P_off"].numel()
+        W = emb.shape[1]
+        dP = torch.empty_like(P)
+        demb = torch.empty_like(emb, dtype=torch.float32)
+        self._call("svpc_gumbel_bwd", Nc, Lt, V, W, _ptr(P), _ptr(self._c(g)), _ptr(lay["clip_P_off"]), _ptr(lay["clip_vx"]),
+                   _f(lay["tau"]), _ptr(self._c(emb)), _ptr(text_mask), _ptr(idx), _ptr(yval), _ptr(self._c(dx)), _ptr(dP),
+                   _ptr(demb))
+        return dP, demb
+
+    # ------------------------------------------------------------------ losses
+    def bce_fwd(self, p, y):
+        self._chk(p, y)
+        out = torch.empty((), dtype=torch.float32, device=p.device)
+        self._call("svpc_bce_fwd", _ll(p.numel()), _ptr(self._c(p)), _ptr(self._c(y)), _ptr(out))
+        return out
+
+    def bce_bwd(self, p, y, g):
+        dp = torch.empty_like(p)
+        self._call("svpc_bce_bwd", _ll(p.numel()), _ptr(self._c(p)), _ptr(self._c(y)), _ptr(g.to(torch.float32).reshape(1)), _ptr(dp))
+        return dp
+
+    def asl_fwd(self, p, y):
+        self._chk(p, y)
+        out = torch.empty((), dtype=torch.float32, device=p.device)
+        self._call("svpc_asl_fwd", p.shape[0], p.shape[1], _ptr(self._c(p)), _ptr(self._c(y)), _ptr(out))
+        return out
+
+    def asl_bwd(self, p, y, g):
+        dp = torch.empty_like(p)
+        self._call("svpc_asl_bwd", p.shape[0], p.shape[1], _ptr(self._c(p)), _ptr(self._c(y)), _ptr(g.to(torch.float32).reshape(1)),
+                   _ptr(dp))
+        return dp
+
+    # ------------------------------------------------------------------ recipe encoder (BiLSTM)
+    _lstm_rows = {}
+
+    def _lstm_row_table(self, steps, device):
+        key = (tuple(steps), str(device))
+        t = self._lstm_rows.get(key)
+        if t is None:
+            B, Smax = len(steps), max(steps)
+            cu = [0]
+            for s in steps:
+                cu.append(cu[-1] + s)
+            fwd = [[cu[b] + j if j < steps[b] else -1 for b in range(B)] for j in range(Smax)]
+            rev = [[cu[b] + steps[b] - 1 - j if j < steps[b] else -1 for b in range(B)] for j in range(Smax)]
+            if len(self._lstm_rows) > 64:
+                self._lstm_rows.clear()
+            t = torch.tensor([fwd, rev], dtype=torch.int32).to(device)
+            self._lstm_rows[key] = t
+        return t
+
+    def bilstm_fwd(self, x, cu_steps, steps, params):
+        """x (Nc, W) fp32 -> (Nc, D): both directions of nn.LSTM over every video's clips, summed (model.py:1022-1024).
+        The input projection of all clips is one GEMM per direction; the recurrence is Smax x (GEMM + cell kernel)."""
+        self._chk(x)
+        x = self._c(x)
+        Nc, W = x.shape
+        D = params["weight_hh_l0"].shape[1]
+        B, Smax = len(steps), max(steps)
+        dev = x.device
+        rows = self._lstm_row_table(steps, dev)
+        out = torch.empty(Nc, D, dtype=torch.float32, device=dev)
+        saved = [rows]
+        for di, suf in enumerate(("", "_reverse")):
+            w_ih, w_hh = params["weight_ih_l0" + suf], params["weight_hh_l0" + suf]
+            bias = params["bias_ih_l0" + suf] + params["bias_hh_l0" + suf]
+            xg = self.gemm(x, w_ih, torch.float32, bias)
+            h = torch.zeros(B, D, dtype=torch.float32, device=dev)
+            c = torch.zeros(B, D, dtype=torch.float32, device=dev)
+            gates = torch.empty(Nc, 4 * D, dtype=torch.float32, device=dev)
+            csv = torch.empty(Nc, D, dtype=torch.float32, device=dev)
+            hprev = torch.empty(Nc, D, dtype=torch.float32, device=dev)
+            cprev = torch.empty(Nc, D, dtype=torch.float32, device=dev)
+            for j in range(Smax):
+                hg = self.gemm(h, w_hh, torch.float32)
+                self._call("svpc_lstm_cell_fwd", B, D, _ptr(xg), _ptr(hg), _ptr(rows[di, j]), _ptr(c), _ptr(h), _ptr(out),
+                           int(di == 1), _ptr(gates), _ptr(csv), _ptr(hprev), _ptr(cprev))
+            saved += [gates, csv, hprev, cprev]
+        return out, tuple(saved)
+
+    def bilstm_bwd(self, dout, x, cu_steps, steps, params, saved):
+        dout, x = self._c(dout), self._c(x)
+        Nc, W = x.shape
+        D = params["weight_hh_l0"].shape[1]
+        B, Smax = len(steps), max(steps)
+        dev = x.device
+        rows = saved[0]
+        grads = {}
+        dx = torch.empty(Nc, W, dtype=torch.float32, device=dev)
+        for di, suf in enumerate(("", "_reverse")):
+            gates, csv, hprev, cprev = saved[1 + 4 * di:5 + 4 * di]
+            w_ih, w_hh = params["weight_ih_l0" + suf], params["weight_hh_l0" + suf]
+            dgates = torch.empty(Nc, 4 * D, dtype=torch.float32, device=dev)
+            dgs = torch.empty(B, 4 * D, dtype=torch.float32, device=dev)
+            dh = torch.zeros(B, D, dtype=torch.float32, device=dev)
+            dc = torch.zeros(B, D, dtype=torch.float32, device=dev)
+            for j in range(Smax - 1, -1, -1):
+                self._call("svpc_lstm_cell_bwd", B, D, _ptr(rows[di, j]), _ptr(dout), _ptr(dh), _ptr(dc), _ptr(gates), _ptr(csv),
+                           _ptr(cprev), _ptr(dgates), _ptr(dgs))
+                dh = self.gemm(dgs, w_hh.t(), torch.float32)
+            grads["weight_hh_l0" + suf] = self.gemm(dgates.t(), hprev.t(), torch.float32)
+            grads["weight_ih_l0" + suf] = self.gemm(dgates.t(), x.t(), torch.float32)
+            db = self.colsum(dgates)
+            grads["bias_ih_l0" + suf] = db
+            grads["bias_hh_l0" + suf] = db.clone()
+            self.gemm(dgates, w_ih.t(), torch.float32, out=dx, accumulate=(di == 1))
+        return dx, grads

@@ -251,26 +251,27 @@ class SegMeanFn(Function):
     """Ingredient vectors: mean of the token vectors between [SEP]s, + pe[j]  (reference model.py:116-140)."""
 
     @staticmethod
-    def forward(ctx, x, sep_mask, cu_ingr, pe):
+    def forward(ctx, x, sep_mask, cu_ingr, pe, NI):
         ctx.save_for_backward(sep_mask, cu_ingr)
         ctx.Li, ctx.dt = sep_mask.shape[1], x.dtype
-        return be().segmean_fwd(x, sep_mask, cu_ingr, pe)
+        return be().segmean_fwd(x, sep_mask, cu_ingr, pe, NI)
 
     @staticmethod
     def backward(ctx, dE):
         sep_mask, cu_ingr = ctx.saved_tensors
-        return be().segmean_bwd(dE.contiguous(), sep_mask, cu_ingr, ctx.Li, ctx.dt), None, None, None
+        return be().segmean_bwd(dE.contiguous(), sep_mask, cu_ingr, ctx.Li, ctx.dt), None, None, None, None
 
 
 class RaggedMeanFn(Function):
     @staticmethod
     def forward(ctx, x, cu):
         ctx.save_for_backward(cu)
+        ctx.NI = x.shape[0]
         return be().ragged_mean_fwd(x, cu)
 
     @staticmethod
     def backward(ctx, dy):
-        return be().ragged_mean_bwd(dy.contiguous(), ctx.saved_tensors[0]), None
+        return be().ragged_mean_bwd(dy.contiguous(), ctx.saved_tensors[0], ctx.NI), None
 
 
 class RowNormalizeFn(Function):
@@ -291,7 +292,7 @@ class ReasonerFn(Function):
 
     @staticmethod
     def forward(ctx, E0, w2v, clog, w4s, lay):
-        ent, ebar, Es, saved = be().reasoner_fwd(E0, lay["cu_ingr"], lay["cu_steps"], lay["clip_ent_off"], w2v, clog, w4s)
+        ent, ebar, Es, saved = be().reasoner_fwd(E0, lay, w2v, clog, w4s)
         ctx.lay = lay
         ctx.n_saved = len(saved)
         ctx.save_for_backward(E0, w2v, clog, w4s, ent, ebar, Es, *saved)
@@ -302,9 +303,8 @@ class ReasonerFn(Function):
         E0, w2v, clog, w4s, ent, ebar, Es, *saved = ctx.saved_tensors
         lay = ctx.lay
         z = lambda g, like: torch.zeros_like(like) if g is None else g.contiguous()
-        dE0, dw2v, dclog, dw4s = be().reasoner_bwd(z(d_ent, ent), z(d_ebar, ebar), z(d_Es, Es), E0, lay["cu_ingr"],
-                                                   lay["cu_steps"], lay["clip_ent_off"], w2v, clog, w4s, ent, ebar, Es,
-                                                   tuple(saved))
+        dE0, dw2v, dclog, dw4s = be().reasoner_bwd(z(d_ent, ent), z(d_ebar, ebar), z(d_Es, Es), E0, lay, w2v, clog, w4s,
+                                                   ent, ebar, Es, tuple(saved))
         return dE0, dw2v, dclog, dw4s, None
 
 

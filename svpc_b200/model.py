@@ -268,7 +268,8 @@ class StateAwareRecursiveTransformer(nn.Module):
                         out_dtype=f32)                                                                    # (Nc, D)
         clog = self._lin(hhat, prefix + ".W3", out_dtype=f32)                                            # (Nc, 3)
         w4s = self._lin(fbar, prefix + ".W4", out_dtype=f32).reshape(-1)                                 # (Nc,)
-        lay = dict(cu_ingr=plan.t["cu_ingr"], cu_steps=plan.t["cu_steps"], clip_ent_off=plan.t["clip_ent_off"])
+        lay = dict(cu_ingr=plan.t["cu_ingr"], cu_steps=plan.t["cu_steps"], clip_ent_off=plan.t["clip_ent_off"],
+                   max_ni=plan.max_ni, NE=plan.NE, B=plan.B)
         ent, ebar, Es = Fn.ReasonerFn.apply(E0, w2v, clog, w4s, lay)
         return ent, ac, ebar, Es, fbar
 
@@ -325,7 +326,7 @@ class StateAwareRecursiveTransformer(nn.Module):
         ids = ingr_input_ids.reshape(-1).to(torch.int32)
         x = self._word_fc("ingredient_embeddings", ids)
         return Fn.SegMeanFn.apply(x, ingr_sep_masks.to(torch.int32).contiguous(), plan.t["cu_ingr"],
-                                  self.p("ingredient_embeddings.position_embeddings_ingr.pe"))
+                                  self.p("ingredient_embeddings.position_embeddings_ingr.pe"), plan.NI)
 
     def _context(self, mode, V, E0, ebar, fbar, plan):
         cd = self.compute_dtype

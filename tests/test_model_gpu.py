@@ -1,0 +1,102 @@
+"""GPU parity tests of the whole step through the drop-in model (svpc_b200.model -> ctypes -> libsvpc_b200.so):
+against the committed reference golden fixtures (tiny configuration, all four model modes, ragged + OOV and
+full-length batches) and against the CPU oracle at the real YouCook2 layer sizes."""
+import copy
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from svpc_b200 import backend  # noqa: E402
+from svpc_b200.config import youcook2_config  # noqa: E402
+from svpc_b200 import synth  # noqa: E402
+from svpc_b200.model import StateAwareRecursiveTransformer  # noqa: E402
+from svpc_b200.synth import forward_args  # noqa: E402
+from tests.helpers import CASES, MODES, load_case, check_against_golden  # noqa: E402
+
+DEV = torch.device("cuda")
+
+
+@pytest.fixture(autouse=True)
+def _cuda_backend():
+    backend.set_backend(None)          # product default: the CUDA library
+    yield
+    backend.set_backend(None)
+
+
+def build(cfg, sd, dtype=torch.float32):
+    m = StateAwareRecursiveTransformer(cfg, compute_dtype=dtype)
+    m.load_state_dict(sd, strict=True)
+    return m.to(DEV).eval()
+
+
+def run(m, batch):
+    loss, preds, ents, acts = m(*forward_args(batch, DEV), gumbel_noise=batch["gumbel"])
+    loss.backward()
+    torch.cuda.synchronize()
+    return loss.detach().cpu(), preds, ents, acts, {n: p.grad for n, p in m.named_parameters()}
+
+
+@pytest.mark.parametrize("case", list(CASES))
+@pytest.mark.parametrize("mode", MODES)
+def test_fp32_matches_reference_golden(case, mode):
+    cfg, sd, batch, gold = load_case(case, mode)
+    m = build(cfg, sd)
+    assert backend.get().name == "cuda-sm100a"
+    loss, preds, ents, acts, grads = run(m, batch)
+    # north_star: fp32-accumulate path within 1e-4 relative on loss and prediction scores
+    check_against_golden(gold, loss, preds, ents, acts, grads, loss_tol=1e-5, out_tol=1e-4, grad_tol=1e-3, what=f"{case}/{mode}")
+
+
+@pytest.mark.parametrize("mode", MODES)
+def test_bf16_loss_within_1e2(mode):
+    cfg, sd, batch, gold = load_case("ragged", mode)
+    m = build(cfg, sd, torch.bfloat16)
+    loss, preds, ents, acts, grads = run(m, batch)
+    assert abs(float(loss) - float(gold["loss"])) <= 1e-2 * abs(float(gold["loss"])), (float(loss), float(gold["loss"]))
+    for g in grads.values():
+        assert g is None or torch.isfinite(g).all()
+
+
+@pytest.mark.parametrize("mode", ("video", "full"))
+def test_fp32_matches_oracle_at_youcook2_sizes(mode):
+    from oracle import svpc_oracle as O
+    cfg = youcook2_config(mode)
+    sd = synth.init_state_dict(cfg, seed=3)
+    batch = synth.make_batch(cfg, B=2, S=3, seed=11, ragged=True, n_ingr=6, n_oov=2)
+    ref_loss, parts, ref_grads, ref_preds, ref_ents, ref_acts = O.loss_and_grads(sd, cfg, copy.deepcopy(batch))
+    m = build(cfg, sd)
+    loss, preds, ents, acts, grads = run(m, batch)
+    assert abs(float(loss) - float(ref_loss)) <= 1e-4 * abs(float(ref_loss)), (float(loss), float(ref_loss))
+    for a, b in zip(preds, ref_preds):
+        err = (a.detach().cpu() - b.detach()).abs().max().item()
+        assert err <= 1e-4 * b.abs().max().item(), err
+    gscale = max(float(g.abs().max()) for g in ref_grads.values() if g is not None)
+    for n, rg in ref_grads.items():
+        if rg is None:
+            continue
+        g = grads[n]
+        assert g is not None, n
+        err = (g.cpu() - rg).abs().max().item()
+        assert err <= 2e-3 * max(float(rg.abs().max()), 1e-3 * gscale), (n, err)
+
+
+@pytest.mark.parametrize("mode", ("full",))
+def test_bf16_tcgen05_at_youcook2_sizes(mode):
+    """bf16 operands on the tcgen05 route at real layer sizes: loss within 1e-2 relative of the fp32 oracle."""
+    from oracle import svpc_oracle as O
+    cfg = youcook2_config(mode)
+    sd = synth.init_state_dict(cfg, seed=3)
+    batch = synth.make_batch(cfg, B=2, S=3, seed=11, ragged=True, n_ingr=6, n_oov=2)
+    ref_loss = O.forward(sd, cfg, copy.deepcopy(batch))[0]
+    m = build(cfg, sd, torch.bfloat16)
+    loss, preds, ents, acts, grads = run(m, batch)
+    assert abs(float(loss) - float(ref_loss)) <= 1e-2 * abs(float(ref_loss)), (float(loss), float(ref_loss))
+
+
+def test_no_cpu_path():
+    from svpc_b200.cuda_backend import SvpcError
+    be = backend.get()
+    with pytest.raises(SvpcError):
+        be.colsum(torch.zeros(4, 4))

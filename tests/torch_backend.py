@@ -206,7 +206,7 @@ class TorchBackend:
             out.append(x[b * Li + lo: b * Li + hi].mean(dim=0) + pe[j])
         return torch.stack(out)
 
-    def segmean_fwd(self, x, sep_mask, cu_ingr, pe):
+    def segmean_fwd(self, x, sep_mask, cu_ingr, pe, NI=None):
         return self._segmean(self.f(x), sep_mask, self.f(pe), cu_ingr).float()
 
     def segmean_bwd(self, dE0, sep_mask, cu_ingr, Li, out_dtype):
@@ -220,7 +220,7 @@ class TorchBackend:
         c = cu.tolist()
         return torch.stack([self.f(x)[c[b]:c[b + 1]].mean(0) for b in range(len(c) - 1)]).float()
 
-    def ragged_mean_bwd(self, dy, cu):
+    def ragged_mean_bwd(self, dy, cu, NI=None):
         c = cu.tolist()
         return torch.cat([(self.f(dy)[b] / (c[b + 1] - c[b])).expand(c[b + 1] - c[b], -1) for b in range(len(c) - 1)]).float()
 
@@ -248,11 +248,13 @@ class TorchBackend:
                 ents.append(e); ebars.append(ebar[0]); Es.append(E); As.append(a)
         return torch.cat(ents), torch.stack(ebars), torch.cat(Es), torch.cat(As)
 
-    def reasoner_fwd(self, E0, cu_ingr, cu_steps, clip_ent_off, w2v, clog, w4s):
+    def reasoner_fwd(self, E0, lay, w2v, clog, w4s):
+        cu_ingr, cu_steps = lay["cu_ingr"], lay["cu_steps"]
         ent, ebar, Es, a = self._reasoner(self.f(E0), self.f(w2v), self.f(clog), self.f(w4s), cu_ingr, cu_steps)
         return ent.float(), ebar.float(), Es.float(), (a.float(),)
 
-    def reasoner_bwd(self, d_ent, d_ebar, d_Es, E0, cu_ingr, cu_steps, clip_ent_off, w2v, clog, w4s, ent, ebar, Es, saved):
+    def reasoner_bwd(self, d_ent, d_ebar, d_Es, E0, lay, w2v, clog, w4s, ent, ebar, Es, saved):
+        cu_ingr, cu_steps = lay["cu_ingr"], lay["cu_steps"]
         g = _vjp(lambda a, b, c, d: self._reasoner(a, b, c, d, cu_ingr, cu_steps)[:3],
                  [self.f(E0), self.f(w2v), self.f(clog), self.f(w4s)], [self.f(d_ent), self.f(d_ebar), self.f(d_Es)])
         return tuple(x.float() for x in g)
