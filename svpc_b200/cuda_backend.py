@@ -63,12 +63,34 @@ class CudaBackend:
         self.lib = load_library()
         self.gemm_route = GEMM_AUTO
         self._ptr_cache = {}
+        self.timing = None
 
     # ------------------------------------------------------------------ plumbing
-    def _call(self, fn, *args):
+    def _call(self, fn, *args, tag=None):
+        timing = self.timing
+        if timing is not None:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
         rc = getattr(self.lib, fn)(*args, C.c_void_p(torch.cuda.current_stream().cuda_stream))
+        if timing is not None:
+            e1.record()
+            timing.append((tag or fn, e0, e1))
         if rc != 0:
             raise SvpcError(f"{fn} failed ({rc}): {self.lib.svpc_last_error().decode()}")
+
+    def start_timing(self):
+        """Per-call CUDA-event timing on the launching stream (bench.py roofline pass)."""
+        self.timing = []
+
+    def stop_timing(self):
+        torch.cuda.synchronize()
+        out = {}
+        for tag, e0, e1 in self.timing or []:
+            ms = e0.elapsed_time(e1)
+            n, t = out.get(tag, (0, 0.0))
+            out[tag] = (n + 1, t + ms)
+        self.timing = None
+        return out
 
     @staticmethod
     def _chk(*ts):
@@ -109,8 +131,16 @@ class CudaBackend:
                        _ptr(bias), int(act),
                        _ptr(residual), _ll(residual.stride(0) if residual is not None else 0),
                        _ptr(pre), _ll(N),
-                       int(bool(accumulate)), int(self.gemm_route if route is None else route))
+                       int(bool(accumulate)), int(self.gemm_route if route is None else route),
+                       tag=None if self.timing is None else self._gemm_tag(M, N, K, a, bt, out, sa, sb))
         return (out, pre) if want_pre else out
+
+    def _gemm_tag(self, M, N, K, a, bt, out, sa, sb):
+        r = self.lib.svpc_gemm_route(M, N, K, _DT[a.dtype], _ll(sa[0]), _ll(sa[1]), _DT[bt.dtype], _ll(sb[0]), _ll(sb[1]),
+                                     _DT[out.dtype], _ll(out.stride(0)))
+        if self.gemm_route == GEMM_SIMT:
+            r = GEMM_SIMT
+        return f"gemm_{'tc' if r == GEMM_TC else 'simt'}:{M}x{N}x{K}:{'T' if sa[1] != 1 else 'N'}{'T' if sb[1] != 1 else 'N'}"
 
     def act_bwd(self, dy, ref, act):
         self._chk(dy, ref)
