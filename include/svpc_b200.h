@@ -150,13 +150,16 @@ int svpc_gumbel_bwd(int n_clips, int Lt, int V, int W, const float* P, const flo
                     const int* clip_vx, float tau, const float* emb, const float* text_mask, const int* idx,
                     const float* yval, const float* dxmean, float* dP, float* demb, svpc_stream_t stream);
 
-/* One time step of nn.LSTM (model.py:865) for all videos: gate order i,f,g,o. rows[b] = sequence row or -1. */
-int svpc_lstm_cell_fwd(int B, int D, const float* xg, const float* hg, const int* rows, float* c, float* h, float* out,
-                       int accumulate_out, float* gates_saved, float* c_saved, float* hprev_saved, float* cprev_saved,
-                       svpc_stream_t stream);
-int svpc_lstm_cell_bwd(int B, int D, const int* rows, const float* dout, const float* dh_rec, float* dc,
-                       const float* gates_saved, const float* c_saved, const float* cprev_saved, float* dgates_all,
-                       float* dgates_step, svpc_stream_t stream);
+/* Recurrence of nn.LSTM(bidirectional) (model.py:865, 1022-1024), gate order i,f,g,o: ONE launch per time step j for
+ * both directions and all videos, recurrent product fused with the cell.  rows (2, Smax, B): clip row of video b at
+ * step j of direction dir, or -1.  xg (2, Nc, 4D) = x W_ih^T + b_ih + b_hh; whh (2, 4D, D); hs / cs / hprev (2, Nc, D),
+ * gates (2, Nc, 4D) are saved for the backward; out (Nc, D) must be zero-initialised (both directions are summed into it).
+ * Backward: call with j = Smax-1 .. 0; whh_t (2, D, 4D) = W_hh^T (svpc_transpose_f32); dc (2, B, D) zero-initialised. */
+int svpc_lstm_step_fwd(int B, int D, int Nc, int Smax, int j, const float* xg, const float* whh, const int* rows,
+                       float* hs, float* cs, float* gates, float* out, float* hprev, svpc_stream_t stream);
+int svpc_lstm_step_bwd(int B, int D, int Nc, int Smax, int j, const float* whh_t, const int* rows, const float* cs,
+                       const float* gates, const float* dout, float* dgates, float* dc, svpc_stream_t stream);
+int svpc_transpose_f32(int R, int C, const float* in, float* out, svpc_stream_t stream);
 
 /* nn.BCELoss(sum) on probabilities (model.py:871) and AsymmetricLoss (libs/ASL/src/loss_functions/losses.py:15-50). */
 int svpc_bce_fwd(long long n, const float* p, const float* y, float* loss, svpc_stream_t stream);

@@ -1,12 +1,9 @@
 #!/bin/bash
-# first GPU pass: operator parity, whole-model parity, then the tcgen05 route (separately, so a hang there cannot hide the rest)
+# GPU pass: operator parity, whole-model parity (incl. graph replay), bench, ncu launch list
 mkdir -p gpurun_out
-nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > gpurun_out/smi.txt 2>&1
-timeout 600 python -m pytest tests/test_ops_gpu.py -q -m gpu -k "not gemm_tc" --tb=short --maxfail=30 > gpurun_out/ops.log 2>&1; echo "ops rc=$?"
-tail -25 gpurun_out/ops.log
-timeout 600 python -m pytest tests/test_model_gpu.py -q -m gpu -k "fp32 or no_cpu" --tb=short --maxfail=30 > gpurun_out/model_fp32.log 2>&1; echo "model fp32 rc=$?"
-tail -25 gpurun_out/model_fp32.log
-timeout 300 python -m pytest tests/test_ops_gpu.py -q -m gpu -k "gemm_tc" --tb=line --maxfail=100 > gpurun_out/tc.log 2>&1; echo "tc rc=$?"
-tail -40 gpurun_out/tc.log
-timeout 600 python -m pytest tests/test_model_gpu.py -q -m gpu -k "bf16" --tb=short > gpurun_out/model_bf16.log 2>&1; echo "model bf16 rc=$?"
-tail -15 gpurun_out/model_bf16.log
+timeout 1200 python -m pytest tests -q -m gpu --tb=short --maxfail=20 > gpurun_out/tests.log 2>&1; echo "tests rc=$?"
+tail -30 gpurun_out/tests.log
+CMD="python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-e2e --no-kernel-timing --no-graph"
+timeout 600 $CMD > gpurun_out/plain.log 2>&1 && \
+timeout 1500 ncu --metrics gpu__time_duration.sum --clock-control none -c 6000 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu.log 2>&1
+echo "ncu rc=$?"; tail -2 gpurun_out/ncu.log; wc -l gpurun_out/launches.csv

@@ -84,6 +84,22 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* v) {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+// 4-element row-contiguous loads / stores of the output type
+__device__ __forceinline__ float4 ld4(const float* p) { return *reinterpret_cast<const float4*>(p); }
+__device__ __forceinline__ float4 ld4(const bf16* p) {
+  const uint2 u = *reinterpret_cast<const uint2*>(p);
+  const __nv_bfloat162 a = *reinterpret_cast<const __nv_bfloat162*>(&u.x), b = *reinterpret_cast<const __nv_bfloat162*>(&u.y);
+  return make_float4(__low2float(a), __high2float(a), __low2float(b), __high2float(b));
+}
+__device__ __forceinline__ void st4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
+__device__ __forceinline__ void st4(bf16* p, float4 v) {
+  const __nv_bfloat162 a = __floats2bfloat162_rn(v.x, v.y), b = __floats2bfloat162_rn(v.z, v.w);
+  uint2 u;
+  u.x = *reinterpret_cast<const uint32_t*>(&a);
+  u.y = *reinterpret_cast<const uint32_t*>(&b);
+  *reinterpret_cast<uint2*>(p) = u;
+}
+
 // shared-memory matrix descriptor (cute::UMMA::SmemDescriptor), 128B swizzle, version 1 (Blackwell)
 __device__ __forceinline__ uint64_t make_sdesc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
   uint64_t d = 0;
@@ -107,7 +123,7 @@ struct TcParams {
 };
 
 template <int BN, bool A_MN, bool B_MN, int KSTAGES, typename TD>
-__global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA,
+__global__ void __launch_bounds__(TC_THREADS, 2) gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA,
                                                                 const __grid_constant__ CUtensorMap tmB,
                                                                 const TcParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -194,15 +210,16 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
     }
   } else {
     // ------------------------------------------------------------------ epilogue (warps 2..5)
+    // Phase 1: TMEM -> registers (lane = row) -> shared memory (the ring is free once tmem_full has fired).
+    // Phase 2: each warp re-reads its 32 rows with lanes along the columns, so bias / activation / residual /
+    //          accumulate and the stores are row-contiguous: 512 B (fp32) or 256 B (bf16) per warp instruction.
     const int q = warp & 3;              // TMEM lane quarter this warp may read
-    const int m = m0 + q * 32 + lane;
     if (nkb > 0) {
       mbar_wait(tmem_full, 0);
       tc_fence_after();
     }
-    TD* __restrict__ Dp = (TD*)p.D;
-    const TD* __restrict__ Rp = (const TD*)p.residual;
-    TD* __restrict__ Pp = (TD*)p.pre;
+    constexpr int LDS = BN + 4;          // padded row stride (floats): conflict-free float4 writes by 8-lane phases
+    float* stage = reinterpret_cast<float*>(smem) + (size_t)q * 32 * LDS;
 #pragma unroll 1
     for (int c = 0; c < BN / 32; ++c) {
       uint32_t v[32];
@@ -210,30 +227,64 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
         tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(c * 32), v);
       } else {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] = 0u;
+        for (int jj = 0; jj < 32; ++jj) v[jj] = 0u;
       }
-      if (m < p.M) {
+      float* dst = stage + (size_t)lane * LDS + c * 32;
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          const int n = n0 + c * 32 + j;
-          if (n < p.N) {
-            float x = __uint_as_float(v[j]);
-            if (p.atomic) {
-              atomicAdd(reinterpret_cast<float*>(Dp) + (long long)m * p.ldd + n, x);
-            } else {
-              if (p.bias) x += p.bias[n];
-              if (Pp) stf(Pp + (long long)m * p.ldp + n, x);
-              x = svpc_act(x, p.act);
-              if (Rp) x += ldf(Rp + (long long)m * p.ldr + n);
-              TD* d = Dp + (long long)m * p.ldd + n;
-              if (p.accumulate) x += ldf(d);
-              stf(d, x);
-            }
+      for (int jj = 0; jj < 32; jj += 4)
+        *reinterpret_cast<uint4*>(dst + jj) = make_uint4(v[jj], v[jj + 1], v[jj + 2], v[jj + 3]);
+    }
+    tc_fence_before();
+    __syncwarp();
+    TD* __restrict__ Dp = (TD*)p.D;
+    const TD* __restrict__ Rp = (const TD*)p.residual;
+    TD* __restrict__ Pp = (TD*)p.pre;
+    const int mw = m0 + q * 32;
+    constexpr int VEC_ROWS = 128 / BN;   // rows covered by one warp pass in the vector path (1 for BN=128, 2 for BN=64)
+    const bool vec_ok = !p.atomic && (n0 + BN <= p.N) && (p.ldd % 4 == 0) && (((uintptr_t)Dp & 15) == 0) &&
+                        (!Rp || (p.ldr % 4 == 0 && ((uintptr_t)Rp & 15) == 0)) &&
+                        (!Pp || (p.ldp % 4 == 0 && ((uintptr_t)Pp & 15) == 0)) && (((uintptr_t)p.bias & 15) == 0);
+    if (vec_ok) {
+      const int cl = (lane % (BN / 4)) * 4;            // this lane's 4 columns inside the tile
+      const int rsub = lane / (BN / 4);                // row inside the pass
+      float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (p.bias) bv = *reinterpret_cast<const float4*>(p.bias + n0 + cl);
+#pragma unroll 4
+      for (int r = rsub; r < 32; r += VEC_ROWS) {
+        const int m = mw + r;
+        if (m >= p.M) break;
+        float4 x = *reinterpret_cast<const float4*>(stage + (size_t)r * LDS + cl);
+        x.x += bv.x; x.y += bv.y; x.z += bv.z; x.w += bv.w;
+        if (Pp) st4(Pp + (long long)m * p.ldp + n0 + cl, x);
+        x.x = svpc_act(x.x, p.act); x.y = svpc_act(x.y, p.act); x.z = svpc_act(x.z, p.act); x.w = svpc_act(x.w, p.act);
+        if (Rp) { const float4 rr = ld4(Rp + (long long)m * p.ldr + n0 + cl); x.x += rr.x; x.y += rr.y; x.z += rr.z; x.w += rr.w; }
+        TD* d = Dp + (long long)m * p.ldd + n0 + cl;
+        if (p.accumulate) { const float4 dd = ld4(d); x.x += dd.x; x.y += dd.y; x.z += dd.z; x.w += dd.w; }
+        st4(d, x);
+      }
+    } else {
+      for (int r = 0; r < 32; ++r) {
+        const int m = mw + r;
+        if (m >= p.M) break;
+#pragma unroll
+        for (int cc = 0; cc < BN / 32; ++cc) {
+          const int n = n0 + cc * 32 + lane;
+          if (n >= p.N) continue;
+          float x = stage[(size_t)r * LDS + cc * 32 + lane];
+          if (p.atomic) {
+            atomicAdd(reinterpret_cast<float*>(Dp) + (long long)m * p.ldd + n, x);
+          } else {
+            if (p.bias) x += p.bias[n];
+            if (Pp) stf(Pp + (long long)m * p.ldp + n, x);
+            x = svpc_act(x, p.act);
+            if (Rp) x += ldf(Rp + (long long)m * p.ldr + n);
+            TD* d = Dp + (long long)m * p.ldd + n;
+            if (p.accumulate) x += ldf(d);
+            stf(d, x);
           }
         }
       }
     }
-    tc_fence_before();
   }
   __syncthreads();
   if (warp == 2) {
@@ -292,12 +343,13 @@ int svpc_gemm_tc_eligible(int M, int N, int K, int dtA, long long sa_m, long lon
 
 template <int BN, bool A_MN, bool B_MN, typename TD>
 static int launch_cfg(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, dim3 grid, cudaStream_t st) {
-  constexpr int KSTAGES = BN == 128 ? 6 : (BN == 64 ? 8 : 4);
+  constexpr int KSTAGES = BN == 128 ? 3 : 4;   // 96 KB per CTA: two CTAs per SM, one's epilogue under the other's main loop
   constexpr size_t smem = (size_t)KSTAGES * (TC_BM * TC_BK * 2 + BN * TC_BK * 2) + 1024 + 256;
   auto kern = gemm_tc_kernel<BN, A_MN, B_MN, KSTAGES, TD>;
   static bool attr_set = false;
   if (!attr_set) {
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     attr_set = true;
   }
   kern<<<grid, TC_THREADS, smem, st>>>(ta, tb, p);

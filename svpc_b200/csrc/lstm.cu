@@ -1,0 +1,235 @@
+// Recurrence of the recipe encoder (reference nn.LSTM(300 -> 768, bidirectional), model.py:865, 1022-1024; gate order
+// i, f, g, o).  The input projections x W_ih^T + b of all clips are one batched GEMM per direction (svpc_gemm); what is
+// left is sequential over a video's clips with a batch of only `videos` rows, i.e. a weight-streaming problem:
+// every step reads W_hh (4D x D fp32 = 9.4 MB per direction at D = 768, L2-resident after the first step) once.
+//
+// One launch per time step covers both directions and all videos, and fuses the recurrent product with the cell:
+//   forward   gates = xg[row] + h_prev W_hh^T ; (i, f, g, o) -> c, h ; out[row] += h           (lstm_step_fwd_kernel)
+//   backward  dh = dout[row] + dgates[next row] W_hh ; cell backward -> dgates[row], dc        (lstm_step_bwd_kernel)
+// A warp owns one hidden unit d: it streams the 4 gate rows of W_hh (forward) / row d of W_hh^T (backward) with
+// coalesced float4 loads against the h (or dgates) rows of up to 16 videos staged in shared memory, reduces the
+// 16 x 4 partial sums with a transposing shuffle tree, and lane 2b finishes video b.
+#include "common.cuh"
+
+#define LSTM_BV 16          // videos per CTA (smem rows)
+#define LSTM_WARPS 8        // hidden units per CTA
+
+// Transposing warp reduction: every lane holds N partial sums v[0..N); afterwards lane l holds the full sums of
+// elements 2l*N/64.. (see callers).  N halves per round; static indexing keeps v[] in registers.
+template <int N>
+__device__ __forceinline__ void warp_reduce_transpose(float (&v)[N], int lane) {
+  // rounds: (off, n) = (16, N/2), (8, N/4), ...
+#pragma unroll
+  for (int off = 16, n = N / 2; n >= 1 && off >= 1; off >>= 1, n >>= 1) {
+    const bool up = (lane & off) != 0;
+#pragma unroll
+    for (int i = 0; i < N / 2; ++i) {
+      if (i < n) {
+        const float send = up ? v[i] : v[i + n];
+        const float keep = up ? v[i + n] : v[i];
+        v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+      }
+    }
+  }
+}
+
+struct LstmStepParams {
+  int B, D, Nc, Smax, j;
+  const float* xg;      // (2, Nc, 4D)  x W_ih^T + b_ih + b_hh per direction
+  const float* whh;     // fwd: (2, 4D, D) W_hh ; bwd: (2, D, 4D) W_hh^T
+  const int* rows;      // (2, Smax, B) row of video b's clip at step j of direction dir, -1 when none
+  float* hs;            // (2, Nc, D) h per clip row
+  float* cs;            // (2, Nc, D) c per clip row
+  float* gates;         // (2, Nc, 4D) activated gates per clip row
+  float* out;           // (Nc, D)    sum of both directions' h (zero-initialised, atomically accumulated)
+  float* hprev;         // (2, Nc, D) h entering each clip's step (operand of the W_hh weight gradient)
+  // backward only
+  const float* dout;    // (Nc, D)
+  float* dgates;        // (2, Nc, 4D) gradient w.r.t. the gate pre-activations
+  float* dc;            // (2, B, D)  carried cell gradient
+};
+
+__global__ void __launch_bounds__(LSTM_WARPS * 32) lstm_step_fwd_kernel(const LstmStepParams p) {
+  extern __shared__ __align__(16) float hsm[];          // [LSTM_BV][D]
+  const int dir = blockIdx.y, b0 = blockIdx.z * LSTM_BV;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int D = p.D, j = p.j;
+  const int* rows_j = p.rows + ((long long)dir * p.Smax + j) * p.B;
+  const int* rows_p = rows_j - p.B;                      // step j-1 (valid when j > 0)
+  const float* hs = p.hs + (long long)dir * p.Nc * D;
+  if (j > 0) {
+    for (int e = threadIdx.x * 4; e < LSTM_BV * D; e += blockDim.x * 4) {
+      const int b = e / D, k = e - b * D;
+      int rp = -1;
+      if (b0 + b < p.B && rows_j[b0 + b] >= 0) rp = rows_p[b0 + b];
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (rp >= 0) v = *reinterpret_cast<const float4*>(hs + (long long)rp * D + k);
+      *reinterpret_cast<float4*>(hsm + e) = v;
+    }
+    __syncthreads();
+  }
+  const int d = blockIdx.x * LSTM_WARPS + warp;
+  if (d >= D) return;
+  float acc[LSTM_BV * 4];                                 // [video][gate]
+#pragma unroll
+  for (int i = 0; i < LSTM_BV * 4; ++i) acc[i] = 0.f;
+  if (j > 0) {
+    const float* w = p.whh + (long long)dir * 4 * D * D + (long long)d * D;
+    for (int k = lane * 4; k < D; k += 128) {
+      float4 wv[4];
+#pragma unroll
+      for (int g = 0; g < 4; ++g) wv[g] = __ldg(reinterpret_cast<const float4*>(w + (long long)g * D * D + k));
+#pragma unroll
+      for (int b = 0; b < LSTM_BV; ++b) {
+        const float4 h = *reinterpret_cast<const float4*>(hsm + b * D + k);
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          float a = acc[b * 4 + g];
+          a = fmaf(h.x, wv[g].x, a); a = fmaf(h.y, wv[g].y, a); a = fmaf(h.z, wv[g].z, a); a = fmaf(h.w, wv[g].w, a);
+          acc[b * 4 + g] = a;
+        }
+      }
+    }
+    warp_reduce_transpose<LSTM_BV * 4>(acc, lane);        // lane l: elements 2l, 2l+1 = video l/2, gates 2(l&1), +1
+  }
+  // exchange so that both lanes of a pair hold all four gates of video lane/2
+  const float o0 = __shfl_xor_sync(0xffffffffu, acc[0], 1), o1 = __shfl_xor_sync(0xffffffffu, acc[1], 1);
+  if (lane & 1) return;
+  const int b = b0 + (lane >> 1);
+  if (b >= p.B) return;
+  const int r = rows_j[b];
+  if (r < 0) return;
+  const int rp = j > 0 ? rows_p[b] : -1;
+  const float* x = p.xg + ((long long)dir * p.Nc + r) * 4 * D;
+  const float gi = svpc_sigmoid(x[d] + acc[0]);
+  const float gf = svpc_sigmoid(x[D + d] + acc[1]);
+  const float gg = tanhf(x[2 * D + d] + o0);
+  const float go = svpc_sigmoid(x[3 * D + d] + o1);
+  float* cs = p.cs + (long long)dir * p.Nc * D;
+  const float cp = rp >= 0 ? cs[(long long)rp * D + d] : 0.f;
+  const float cn = gf * cp + gi * gg;
+  const float hn = go * tanhf(cn);
+  cs[(long long)r * D + d] = cn;
+  p.hs[((long long)dir * p.Nc + r) * D + d] = hn;
+  p.hprev[((long long)dir * p.Nc + r) * D + d] = rp >= 0 ? hs[(long long)rp * D + d] : 0.f;
+  float* g = p.gates + ((long long)dir * p.Nc + r) * 4 * D;
+  g[d] = gi; g[D + d] = gf; g[2 * D + d] = gg; g[3 * D + d] = go;
+  atomicAdd(p.out + (long long)r * D + d, hn);
+}
+
+// Step j of the reverse sweep (called with j = Smax-1 ... 0).  rows of step j+1 give the gate gradients already computed.
+__global__ void __launch_bounds__(LSTM_WARPS * 32) lstm_step_bwd_kernel(const LstmStepParams p) {
+  extern __shared__ __align__(16) float gsm[];          // [LSTM_BV][D] chunk of the next step's gate gradients
+  const int dir = blockIdx.y, b0 = blockIdx.z * LSTM_BV;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int D = p.D, j = p.j;
+  const int* rows_j = p.rows + ((long long)dir * p.Smax + j) * p.B;
+  const int* rows_n = rows_j + p.B;                      // step j+1 (valid when j + 1 < Smax)
+  const bool has_next = j + 1 < p.Smax;
+  const int d = blockIdx.x * LSTM_WARPS + warp;          // d >= D warps still help staging
+  float acc[LSTM_BV];
+#pragma unroll
+  for (int i = 0; i < LSTM_BV; ++i) acc[i] = 0.f;
+  if (has_next) {
+    const float* dg = p.dgates + (long long)dir * p.Nc * 4 * D;
+    const float* wt = p.whh + (long long)dir * 4 * D * D + (long long)(d < D ? d : 0) * 4 * D;
+    for (int c = 0; c < 4; ++c) {                        // chunks of D along the 4D reduction
+      __syncthreads();
+      for (int e = threadIdx.x * 4; e < LSTM_BV * D; e += blockDim.x * 4) {
+        const int b = e / D, k = e - b * D;
+        const int rn = (b0 + b < p.B) ? rows_n[b0 + b] : -1;
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (rn >= 0) v = *reinterpret_cast<const float4*>(dg + (long long)rn * 4 * D + c * D + k);
+        *reinterpret_cast<float4*>(gsm + e) = v;
+      }
+      __syncthreads();
+      if (d < D) {
+        for (int k = lane * 4; k < D; k += 128) {
+          const float4 wv = __ldg(reinterpret_cast<const float4*>(wt + c * D + k));
+#pragma unroll
+          for (int b = 0; b < LSTM_BV; ++b) {
+            const float4 g = *reinterpret_cast<const float4*>(gsm + b * D + k);
+            float a = acc[b];
+            a = fmaf(g.x, wv.x, a); a = fmaf(g.y, wv.y, a); a = fmaf(g.z, wv.z, a); a = fmaf(g.w, wv.w, a);
+            acc[b] = a;
+          }
+        }
+      }
+    }
+    warp_reduce_transpose<LSTM_BV>(acc, lane);            // 4 rounds: lane l holds half-sums of video l/2
+    acc[0] += __shfl_xor_sync(0xffffffffu, acc[0], 1);
+  }
+  if (d >= D || (lane & 1)) return;
+  const int b = b0 + (lane >> 1);
+  if (b >= p.B) return;
+  const int r = rows_j[b];
+  if (r < 0) return;
+  const int rp = j > 0 ? rows_j[b - p.B] : -1;            // rows of step j-1
+  const float* g = p.gates + ((long long)dir * p.Nc + r) * 4 * D;
+  const float* cs = p.cs + (long long)dir * p.Nc * D;
+  const float gi = g[d], gf = g[D + d], gg = g[2 * D + d], go = g[3 * D + d];
+  const float tc = tanhf(cs[(long long)r * D + d]);
+  const float cp = rp >= 0 ? cs[(long long)rp * D + d] : 0.f;
+  const float dh = p.dout[(long long)r * D + d] + acc[0];
+  float* dcp = p.dc + ((long long)dir * p.B + b) * D + d;
+  const float dct = *dcp + dh * go * (1.f - tc * tc);
+  *dcp = dct * gf;
+  float* da = p.dgates + ((long long)dir * p.Nc + r) * 4 * D;
+  da[d] = dct * gg * gi * (1.f - gi);
+  da[D + d] = dct * cp * gf * (1.f - gf);
+  da[2 * D + d] = dct * gi * (1.f - gg * gg);
+  da[3 * D + d] = dh * tc * go * (1.f - go);
+}
+
+static int lstm_launch(bool bwd, const LstmStepParams& p, cudaStream_t st) {
+  SVPC_REQUIRE(p.D % 4 == 0, "lstm_step: hidden size %d must be a multiple of 4", p.D);
+  if (p.B <= 0 || p.Nc <= 0) return SVPC_OK;
+  const size_t smem = (size_t)LSTM_BV * p.D * sizeof(float);
+  SVPC_REQUIRE(smem <= 200 * 1024, "lstm_step: hidden size %d too large", p.D);
+  static bool attr = false;
+  if (!attr) {
+    cudaFuncSetAttribute(lstm_step_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    cudaFuncSetAttribute(lstm_step_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    attr = true;
+  }
+  dim3 grid(svpc_cdiv(p.D, LSTM_WARPS), 2, svpc_cdiv(p.B, LSTM_BV));
+  if (bwd) lstm_step_bwd_kernel<<<grid, LSTM_WARPS * 32, smem, st>>>(p);
+  else lstm_step_fwd_kernel<<<grid, LSTM_WARPS * 32, smem, st>>>(p);
+  return svpc_check_launch(bwd ? "lstm_step_bwd" : "lstm_step_fwd");
+}
+
+extern "C" int svpc_lstm_step_fwd(int B, int D, int Nc, int Smax, int j, const float* xg, const float* whh, const int* rows,
+                                  float* hs, float* cs, float* gates, float* out, float* hprev, svpc_stream_t stream) {
+  LstmStepParams p{B, D, Nc, Smax, j, xg, whh, rows, hs, cs, gates, out, hprev, nullptr, nullptr, nullptr};
+  return lstm_launch(false, p, (cudaStream_t)stream);
+}
+
+extern "C" int svpc_lstm_step_bwd(int B, int D, int Nc, int Smax, int j, const float* whh_t, const int* rows,
+                                  const float* cs, const float* gates, const float* dout, float* dgates, float* dc,
+                                  svpc_stream_t stream) {
+  LstmStepParams p{B, D, Nc, Smax, j, nullptr, whh_t, rows, nullptr, const_cast<float*>(cs), const_cast<float*>(gates),
+                   nullptr, nullptr, dout, dgates, dc};
+  return lstm_launch(true, p, (cudaStream_t)stream);
+}
+
+// out[c, r] = in[r, c]  (fp32; W_hh^T for the reverse sweep, once per backward)
+__global__ void transpose_f32_kernel(int R, int Cc, const float* __restrict__ in, float* __restrict__ out) {
+  __shared__ float t[32][33];
+  const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int r = r0 + i, c = c0 + threadIdx.x;
+    if (r < R && c < Cc) t[i][threadIdx.x] = in[(long long)r * Cc + c];
+  }
+  __syncthreads();
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int c = c0 + i, r = r0 + threadIdx.x;
+    if (r < R && c < Cc) out[(long long)c * R + r] = t[threadIdx.x][i];
+  }
+}
+
+extern "C" int svpc_transpose_f32(int R, int Cc, const float* in, float* out, svpc_stream_t stream) {
+  if (R <= 0 || Cc <= 0) return SVPC_OK;
+  dim3 grid(svpc_cdiv(Cc, 32), svpc_cdiv(R, 32));
+  transpose_f32_kernel<<<grid, dim3(32, 8), 0, (cudaStream_t)stream>>>(R, Cc, in, out);
+  return svpc_check_launch("transpose_f32");
+}

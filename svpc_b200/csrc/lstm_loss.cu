@@ -1,88 +1,6 @@
-// LSTM cell of the recipe encoder (reference nn.LSTM, model.py:865, 1022-1024; gate order i, f, g, o) and the two
-// multi-label losses taken on probabilities: nn.BCELoss(sum) (model.py:871) and AsymmetricLoss
+// The two multi-label losses taken on probabilities (the LSTM recurrence lives in lstm.cu): nn.BCELoss(sum) (model.py:871) and AsymmetricLoss
 // (libs/ASL/src/loss_functions/losses.py:15-50).
 #include "common.cuh"
-
-// One time step for all videos.  rows[b] = row of video b's current clip in the (Nc, .) arrays, or -1 when the video
-// has no clip at this step.  xg = x W_ih^T + b_ih + b_hh for every clip (batched GEMM), hg = h W_hh^T for this step.
-__global__ void lstm_cell_fwd_kernel(int B, int D, const float* __restrict__ xg, const float* __restrict__ hg,
-                                     const int* __restrict__ rows, float* __restrict__ c, float* __restrict__ h,
-                                     float* __restrict__ out, int accumulate_out, float* __restrict__ gates_saved,
-                                     float* __restrict__ c_saved, float* __restrict__ hprev_saved,
-                                     float* __restrict__ cprev_saved) {
-  const int b = blockIdx.y;
-  const int d = blockIdx.x * blockDim.x + threadIdx.x;
-  if (d >= D) return;
-  const int r = rows[b];
-  if (r < 0) return;
-  const float* x = xg + (long long)r * 4 * D;
-  const float* hh = hg + (long long)b * 4 * D;
-  const float gi = svpc_sigmoid(x[d] + hh[d]);
-  const float gf = svpc_sigmoid(x[D + d] + hh[D + d]);
-  const float gg = tanhf(x[2 * D + d] + hh[2 * D + d]);
-  const float go = svpc_sigmoid(x[3 * D + d] + hh[3 * D + d]);
-  const float cp = c[(long long)b * D + d], hp = h[(long long)b * D + d];
-  const float cn = gf * cp + gi * gg;
-  const float hn = go * tanhf(cn);
-  c[(long long)b * D + d] = cn;
-  h[(long long)b * D + d] = hn;
-  float* g = gates_saved + (long long)r * 4 * D;
-  g[d] = gi; g[D + d] = gf; g[2 * D + d] = gg; g[3 * D + d] = go;
-  c_saved[(long long)r * D + d] = cn;
-  hprev_saved[(long long)r * D + d] = hp;
-  cprev_saved[(long long)r * D + d] = cp;
-  float* o = out + (long long)r * D + d;
-  *o = accumulate_out ? *o + hn : hn;
-}
-
-// Reverse of one time step.  dh_rec (B, D) = gradient w.r.t. h of this step coming from the later step (through W_hh),
-// dc (B, D) carried cell gradient (in/out).  Writes the pre-activation gate gradients both at the clip's row
-// (dgates_all, for the batched weight / input gradients) and per video (dgates_step, for the recurrent GEMM).
-__global__ void lstm_cell_bwd_kernel(int B, int D, const int* __restrict__ rows, const float* __restrict__ dout,
-                                     const float* __restrict__ dh_rec, float* __restrict__ dc,
-                                     const float* __restrict__ gates_saved, const float* __restrict__ c_saved,
-                                     const float* __restrict__ cprev_saved, float* __restrict__ dgates_all,
-                                     float* __restrict__ dgates_step) {
-  const int b = blockIdx.y;
-  const int d = blockIdx.x * blockDim.x + threadIdx.x;
-  if (d >= D) return;
-  const int r = rows[b];
-  float* ds = dgates_step + (long long)b * 4 * D;
-  if (r < 0) { ds[d] = 0.f; ds[D + d] = 0.f; ds[2 * D + d] = 0.f; ds[3 * D + d] = 0.f; return; }
-  const float* g = gates_saved + (long long)r * 4 * D;
-  const float gi = g[d], gf = g[D + d], gg = g[2 * D + d], go = g[3 * D + d];
-  const float tc = tanhf(c_saved[(long long)r * D + d]);
-  const float dh = dout[(long long)r * D + d] + dh_rec[(long long)b * D + d];
-  const float dct = dc[(long long)b * D + d] + dh * go * (1.f - tc * tc);
-  const float di = dct * gg * gi * (1.f - gi);
-  const float df = dct * cprev_saved[(long long)r * D + d] * gf * (1.f - gf);
-  const float dg = dct * gi * (1.f - gg * gg);
-  const float dO = dh * tc * go * (1.f - go);
-  dc[(long long)b * D + d] = dct * gf;
-  float* da = dgates_all + (long long)r * 4 * D;
-  da[d] = di; da[D + d] = df; da[2 * D + d] = dg; da[3 * D + d] = dO;
-  ds[d] = di; ds[D + d] = df; ds[2 * D + d] = dg; ds[3 * D + d] = dO;
-}
-
-extern "C" int svpc_lstm_cell_fwd(int B, int D, const float* xg, const float* hg, const int* rows, float* c, float* h,
-                                  float* out, int accumulate_out, float* gates_saved, float* c_saved, float* hprev_saved,
-                                  float* cprev_saved, svpc_stream_t stream) {
-  if (B <= 0) return SVPC_OK;
-  dim3 grid(svpc_cdiv(D, 128), B);
-  lstm_cell_fwd_kernel<<<grid, 128, 0, (cudaStream_t)stream>>>(B, D, xg, hg, rows, c, h, out, accumulate_out, gates_saved,
-                                                              c_saved, hprev_saved, cprev_saved);
-  return svpc_check_launch("lstm_cell_fwd");
-}
-
-extern "C" int svpc_lstm_cell_bwd(int B, int D, const int* rows, const float* dout, const float* dh_rec, float* dc,
-                                  const float* gates_saved, const float* c_saved, const float* cprev_saved,
-                                  float* dgates_all, float* dgates_step, svpc_stream_t stream) {
-  if (B <= 0) return SVPC_OK;
-  dim3 grid(svpc_cdiv(D, 128), B);
-  lstm_cell_bwd_kernel<<<grid, 128, 0, (cudaStream_t)stream>>>(B, D, rows, dout, dh_rec, dc, gates_saved, c_saved, cprev_saved,
-                                                              dgates_all, dgates_step);
-  return svpc_check_launch("lstm_cell_bwd");
-}
 
 // ------------------------------------------------------------------------------------------------
 // nn.BCELoss(reduction='sum'): -(y * max(log p, -100) + (1 - y) * max(log(1 - p), -100)); the clamp and the

@@ -63,6 +63,7 @@ class CudaBackend:
         self.lib = load_library()
         self.gemm_route = GEMM_AUTO
         self._ptr_cache = {}
+        self._w_cache = {}
         self.timing = None
 
     # ------------------------------------------------------------------ plumbing
@@ -101,6 +102,9 @@ class CudaBackend:
     @staticmethod
     def _c(t):
         return t if t.is_contiguous() else t.contiguous()
+
+    def clear_weight_caches(self):
+        self._w_cache.clear()
 
     def launch_count(self):
         return int(self.lib.svpc_launch_count())
@@ -503,9 +507,31 @@ class CudaBackend:
             self._lstm_rows[key] = t
         return t
 
+    def _lstm_whh(self, params, transposed):
+        """(2, 4D, D) stack of both directions' W_hh (or (2, D, 4D) of their transposes), rebuilt when the optimiser
+        has touched the parameters."""
+        ws = [params["weight_hh_l0"], params["weight_hh_l0_reverse"]]
+        key = ("whh_t" if transposed else "whh",) + tuple(w.data_ptr() for w in ws)
+        ver = tuple(w._version for w in ws)
+        hit = self._w_cache.get(key)
+        if hit is not None and hit[0] == ver:
+            return hit[1]
+        G, D = ws[0].shape
+        out = torch.empty(2, D, G, dtype=torch.float32, device=ws[0].device) if transposed else \
+            torch.empty(2, G, D, dtype=torch.float32, device=ws[0].device)
+        for di, w in enumerate(ws):
+            w = self._c(w)
+            if transposed:
+                self._call("svpc_transpose_f32", G, D, _ptr(w), _ptr(out[di]))
+            else:
+                self._call("svpc_cast", _ll(w.numel()), _ptr(w), F32, _ptr(out[di]), F32)
+        self._w_cache[key] = (ver, out)
+        return out
+
     def bilstm_fwd(self, x, cu_steps, steps, params):
         """x (Nc, W) fp32 -> (Nc, D): both directions of nn.LSTM over every video's clips, summed (model.py:1022-1024).
-        The input projection of all clips is one GEMM per direction; the recurrence is Smax x (GEMM + cell kernel)."""
+        The input projection of all clips is one GEMM per direction; the recurrence is Smax fused step kernels
+        (both directions, all videos, recurrent product + cell in one launch)."""
         self._chk(x)
         x = self._c(x)
         Nc, W = x.shape
@@ -513,24 +539,21 @@ class CudaBackend:
         B, Smax = len(steps), max(steps)
         dev = x.device
         rows = self._lstm_row_table(steps, dev)
-        out = torch.empty(Nc, D, dtype=torch.float32, device=dev)
-        saved = [rows]
+        f32 = torch.float32
+        xg = torch.empty(2, Nc, 4 * D, dtype=f32, device=dev)
         for di, suf in enumerate(("", "_reverse")):
-            w_ih, w_hh = params["weight_ih_l0" + suf], params["weight_hh_l0" + suf]
             bias = params["bias_ih_l0" + suf] + params["bias_hh_l0" + suf]
-            xg = self.gemm(x, w_ih, torch.float32, bias)
-            h = torch.zeros(B, D, dtype=torch.float32, device=dev)
-            c = torch.zeros(B, D, dtype=torch.float32, device=dev)
-            gates = torch.empty(Nc, 4 * D, dtype=torch.float32, device=dev)
-            csv = torch.empty(Nc, D, dtype=torch.float32, device=dev)
-            hprev = torch.empty(Nc, D, dtype=torch.float32, device=dev)
-            cprev = torch.empty(Nc, D, dtype=torch.float32, device=dev)
-            for j in range(Smax):
-                hg = self.gemm(h, w_hh, torch.float32)
-                self._call("svpc_lstm_cell_fwd", B, D, _ptr(xg), _ptr(hg), _ptr(rows[di, j]), _ptr(c), _ptr(h), _ptr(out),
-                           int(di == 1), _ptr(gates), _ptr(csv), _ptr(hprev), _ptr(cprev))
-            saved += [gates, csv, hprev, cprev]
-        return out, tuple(saved)
+            self.gemm(x, params["weight_ih_l0" + suf], f32, bias, out=xg[di])
+        whh = self._lstm_whh(params, False)
+        out = torch.zeros(Nc, D, dtype=f32, device=dev)
+        hs = torch.empty(2, Nc, D, dtype=f32, device=dev)
+        cs = torch.empty(2, Nc, D, dtype=f32, device=dev)
+        hprev = torch.empty(2, Nc, D, dtype=f32, device=dev)
+        gates = torch.empty(2, Nc, 4 * D, dtype=f32, device=dev)
+        for j in range(Smax):
+            self._call("svpc_lstm_step_fwd", B, D, Nc, Smax, j, _ptr(xg), _ptr(whh), _ptr(rows), _ptr(hs), _ptr(cs),
+                       _ptr(gates), _ptr(out), _ptr(hprev))
+        return out, (rows, cs, gates, hprev)
 
     def bilstm_bwd(self, dout, x, cu_steps, steps, params, saved):
         dout, x = self._c(dout), self._c(x)
@@ -538,24 +561,22 @@ class CudaBackend:
         D = params["weight_hh_l0"].shape[1]
         B, Smax = len(steps), max(steps)
         dev = x.device
-        rows = saved[0]
+        rows, cs, gates, hprev = saved
+        f32 = torch.float32
+        whh_t = self._lstm_whh(params, True)
+        dgates = torch.empty(2, Nc, 4 * D, dtype=f32, device=dev)
+        dc = torch.zeros(2, B, D, dtype=f32, device=dev)
+        for j in range(Smax - 1, -1, -1):
+            self._call("svpc_lstm_step_bwd", B, D, Nc, Smax, j, _ptr(whh_t), _ptr(rows), _ptr(cs), _ptr(gates), _ptr(dout),
+                       _ptr(dgates), _ptr(dc))
         grads = {}
-        dx = torch.empty(Nc, W, dtype=torch.float32, device=dev)
+        dx = torch.empty(Nc, W, dtype=f32, device=dev)
         for di, suf in enumerate(("", "_reverse")):
-            gates, csv, hprev, cprev = saved[1 + 4 * di:5 + 4 * di]
-            w_ih, w_hh = params["weight_ih_l0" + suf], params["weight_hh_l0" + suf]
-            dgates = torch.empty(Nc, 4 * D, dtype=torch.float32, device=dev)
-            dgs = torch.empty(B, 4 * D, dtype=torch.float32, device=dev)
-            dh = torch.zeros(B, D, dtype=torch.float32, device=dev)
-            dc = torch.zeros(B, D, dtype=torch.float32, device=dev)
-            for j in range(Smax - 1, -1, -1):
-                self._call("svpc_lstm_cell_bwd", B, D, _ptr(rows[di, j]), _ptr(dout), _ptr(dh), _ptr(dc), _ptr(gates), _ptr(csv),
-                           _ptr(cprev), _ptr(dgates), _ptr(dgs))
-                dh = self.gemm(dgs, w_hh.t(), torch.float32)
-            grads["weight_hh_l0" + suf] = self.gemm(dgates.t(), hprev.t(), torch.float32)
-            grads["weight_ih_l0" + suf] = self.gemm(dgates.t(), x.t(), torch.float32)
-            db = self.colsum(dgates)
+            dg = dgates[di]
+            grads["weight_hh_l0" + suf] = self.gemm(dg.t(), hprev[di].t(), f32)
+            grads["weight_ih_l0" + suf] = self.gemm(dg.t(), x.t(), f32)
+            db = self.colsum(dg)
             grads["bias_ih_l0" + suf] = db
             grads["bias_hh_l0" + suf] = db.clone()
-            self.gemm(dgates, w_ih.t(), torch.float32, out=dx, accumulate=(di == 1))
+            self.gemm(dg, params["weight_ih_l0" + suf].t(), f32, out=dx, accumulate=(di == 1))
         return dx, grads

@@ -51,7 +51,7 @@ WEIGHTS = WeightCache()
 
 
 class _LinMeta:
-    __slots__ = ("n_x", "n_w", "has_bias", "act", "out_dtype", "cd", "w_is_kn", "has_res")
+    __slots__ = ("n_x", "n_w", "has_bias", "act", "out_dtype", "cd", "w_is_kn", "has_res", "cache")
 
     def __init__(self, **kw):
         for k, v in kw.items():
@@ -71,7 +71,7 @@ class LinearFn(Function):
         ws = args[meta.n_x:meta.n_x + meta.n_w]
         bs = args[meta.n_x + meta.n_w:]
         cd = meta.cd
-        W = WEIGHTS.get(ws, cd)
+        W = WEIGHTS.get(ws, cd) if meta.cache else be().cast(ws[0].detach().contiguous(), cd)
         bias = None
         if meta.has_bias:
             bias = bs[0].detach() if len(bs) == 1 else WEIGHTS.get(bs, torch.float32)
@@ -156,12 +156,12 @@ class LinearFn(Function):
         return (None, d_res, *dxs, *dws, *dbs)
 
 
-def linear(xs, ws, bs, *, act=ACT_NONE, out_dtype=None, cd=torch.float32, residual=None, w_is_kn=False):
+def linear(xs, ws, bs, *, act=ACT_NONE, out_dtype=None, cd=torch.float32, residual=None, w_is_kn=False, cache=True):
     xs = list(xs) if isinstance(xs, (list, tuple)) else [xs]
     ws = list(ws) if isinstance(ws, (list, tuple)) else [ws]
     bs = [] if bs is None else (list(bs) if isinstance(bs, (list, tuple)) else [bs])
     meta = _LinMeta(n_x=len(xs), n_w=len(ws), has_bias=len(bs) > 0, act=act, out_dtype=out_dtype or cd, cd=cd,
-                    w_is_kn=w_is_kn, has_res=residual is not None)
+                    w_is_kn=w_is_kn, has_res=residual is not None, cache=cache or len(ws) > 1)
     return LinearFn.apply(meta, residual, *xs, *ws, *bs)
 
 

@@ -1,0 +1,104 @@
+"""CUDA-graph replay of the SVPC training step.
+
+The reference is launch-bound by construction (~430k library kernels per step).  The batched step of
+``svpc_b200.model`` still enqueues a few hundred kernels from Python; on a B200 those kernels finish faster than the
+interpreter can issue them.  ``GraphedTrainStep`` therefore captures ONE forward + backward (+ the bf16 weight refresh
+and, under data parallelism, the bucketed gradient all-reduces) into a CUDA graph whose shapes are fixed by the batch
+signature (clips per video, ingredients per video, OOV widths), and replays it on static input buffers:
+
+    step = GraphedTrainStep(model, example_args, gumbel_noise=noise)     # warm-up + capture
+    step.load(args, noise)        # copies a new batch into the static buffers (H2D from pinned memory or D2D)
+    loss = step.run()             # graph replay; gradients land in p.grad exactly as after loss.backward()
+
+A batch with a different signature needs a new capture (``step.matches(args)`` tells); the data layer can bucket batches
+by signature, or pad to the configuration maxima.
+"""
+from __future__ import annotations
+
+import gc
+
+import torch
+
+from . import functional as Fn
+
+
+def _is_tensor_list(x):
+    return isinstance(x, (list, tuple)) and len(x) > 0 and isinstance(x[0], torch.Tensor)
+
+
+class GraphedTrainStep:
+    N_POS = 13      # positional arguments of StateAwareRecursiveTransformer.forward (reference model.py:1027-1030)
+
+    def __init__(self, model, example_args, gumbel_noise=None, reducer=None, warmup: int = 3):
+        assert len(example_args) == self.N_POS
+        self.model, self.reducer = model, reducer
+        dev = next(model.parameters()).device
+        assert dev.type == "cuda", "GraphedTrainStep needs a CUDA model"
+        self.device = dev
+        self.static = [self._clone(a) for a in example_args]
+        self.noise = None if gumbel_noise is None else [g.to(dev).clone() for g in gumbel_noise]
+        a = self.static
+        self.plan = model.make_plan(a[8], a[9], a[10], a[11], dev)
+        self.sig = self.plan.signature()
+        # pre-build every cached index array outside the capture
+        for C in (1, 2, 3):
+            self.plan.cross_lay(C, dev, model.config.hidden_size)
+        self.graph = torch.cuda.CUDAGraph()
+        self.loss = None
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            for _ in range(max(1, warmup)):
+                self._eager()
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        self.outputs = None         # drop the warm-up autograd graphs (their AccumulateGrad nodes belong to `side`)
+        gc.collect()
+        Fn.be().clear_weight_caches()
+        Fn.WEIGHTS.clear()          # the refresh of the compute-dtype weight copies becomes part of the graph
+        model.zero_grad(set_to_none=True)
+        with torch.cuda.graph(self.graph):
+            self.loss = self._eager(zero=False)
+        torch.cuda.synchronize(dev)
+
+    def _clone(self, a):
+        if isinstance(a, torch.Tensor):
+            return a.to(self.device).clone()
+        if _is_tensor_list(a):
+            return [t.to(self.device).clone() for t in a]
+        return a
+
+    def _eager(self, zero=True):
+        if zero:
+            self.model.zero_grad(set_to_none=True)
+        out = self.model(*self.static, gumbel_noise=self.noise, plan=self.plan)
+        loss = out[0]
+        loss.backward()
+        if self.reducer is not None:
+            self.reducer.finish()
+        self.outputs = out
+        return loss
+
+    # ------------------------------------------------------------------------------------------
+    def matches(self, args):
+        return self.model.plan_signature(args[8], args[9], args[10]) == self.sig
+
+    def load(self, args, gumbel_noise=None):
+        """Copy a batch (host-pinned or device tensors) into the static buffers; asynchronous on the current stream."""
+        for dst, src in zip(self.static, args):
+            if isinstance(dst, torch.Tensor):
+                dst.copy_(src, non_blocking=True)
+            elif _is_tensor_list(dst):
+                for d, s in zip(dst, src):
+                    d.copy_(s, non_blocking=True)
+        if gumbel_noise is not None and self.noise is not None:
+            for d, s in zip(self.noise, gumbel_noise):
+                d.copy_(s, non_blocking=True)
+        if args[9] is not self.static[9] and self.plan.mode != "video":
+            if not self.plan.update_tokens(args[9]):
+                raise ValueError("ingr_id_dict has a different number of copy tokens than the captured batch: re-capture")
+            self.static[9] = args[9]
+
+    def run(self):
+        self.graph.replay()
+        return self.loss

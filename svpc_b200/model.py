@@ -72,17 +72,8 @@ class StepPlan:
         clip_gi = [cu_ingr[b] for b in clip_b]
         clip_vx = [vx[b] for b in clip_b]
         clip_src_copy = [cu_ingr[b] for b in clip_b]
-        tok_ptr, tok_ids = [0], []
-        if mode != "video":
-            for b in range(B):
-                d = ingr_id_dict[b]
-                for i in range(ni[b]):
-                    ids = list(d.get(i, []))
-                    for t in ids:
-                        if not (0 <= int(t) < vx[b]):
-                            raise ValueError(f"ingr_id_dict[{b}][{i}] holds token id {t} outside [0, {vx[b]})")
-                    tok_ids += [int(t) for t in ids]
-                    tok_ptr.append(len(tok_ids))
+        self.mode = mode
+        tok_ptr, tok_ids = self._tok_csr(ingr_id_dict)
         Nc = self.Nc
         ints = OrderedDict(
             cu_steps=cu_steps, cu_ingr=cu_ingr, clip_t=clip_t, clip_b=clip_b, clip_ent_off=clip_ent_off,
@@ -102,7 +93,7 @@ class StepPlan:
         if device.type == "cuda":
             host = host.pin_memory()
         dev = host.to(device, non_blocking=True)
-        self._host = host
+        self._host, self._dev, self._spans = host, dev, spans
         self.t = {k: dev[o:o + n] for k, (o, n) in spans.items()}
         t = self.t
         self.max_ni = max(ni) if ni else 0
@@ -114,6 +105,39 @@ class StepPlan:
                              max_lq=max(steps), max_lk=max(steps), D=D)
         self.dec_lay = dict(q_off=t["dec_off"], q_len=t["dec_len"], k_off=t["dec_off"], k_len=t["dec_len"],
                             max_lq=Lt, max_lk=Lt, D=D)
+
+    def _tok_csr(self, ingr_id_dict):
+        """CSR ingredient (global index) -> extended token ids (reference ingr_id_dict, model.py:912-914)."""
+        tok_ptr, tok_ids = [0], []
+        if self.mode != "video":
+            for b in range(self.B):
+                d = ingr_id_dict[b]
+                for i in range(self.ni[b]):
+                    ids = list(d.get(i, []))
+                    for t in ids:
+                        if not (0 <= int(t) < self.vx[b]):
+                            raise ValueError(f"ingr_id_dict[{b}][{i}] holds token id {t} outside [0, {self.vx[b]})")
+                    tok_ids += [int(t) for t in ids]
+                    tok_ptr.append(len(tok_ids))
+        return tok_ptr, tok_ids
+
+    def signature(self):
+        """What a captured CUDA graph of the step depends on (shapes of every launch)."""
+        return (tuple(self.steps), tuple(self.ni), tuple(self.vx), self._spans["tok_ids"][1])
+
+    def update_tokens(self, ingr_id_dict):
+        """Refresh the copy CSR in place (same lengths): used when a captured step is replayed on a new batch."""
+        tok_ptr, tok_ids = self._tok_csr(ingr_id_dict)
+        if not tok_ids:
+            tok_ids = [0]
+        o, n = self._spans["tok_ids"]
+        if len(tok_ids) != n:
+            return False
+        self._host[o:o + n] = torch.tensor(tok_ids, dtype=torch.int32)
+        o2, n2 = self._spans["tok_ptr"]
+        self._host[o2:o2 + n2] = torch.tensor(tok_ptr, dtype=torch.int32)
+        self._dev.copy_(self._host, non_blocking=True)
+        return True
 
     def cross_lay(self, C, device, D):
         key = ("cross", C)
@@ -242,7 +266,7 @@ class StateAwareRecursiveTransformer(nn.Module):
         W, g0, b0 = self.p(pfx + ".2.weight"), self.p(pfx + ".0.weight"), self.p(pfx + ".0.bias")
         Wf = W * g0
         bf = self.p(pfx + ".2.bias") + (W * b0).sum(dim=1)
-        z = Fn.linear(xhat, Wf, bf, act=ACT_RELU, cd=self.compute_dtype)
+        z = Fn.linear(xhat, Wf, bf, act=ACT_RELU, cd=self.compute_dtype, cache=False)   # Wf is a per-step temporary
         return self._ln(z, None, pfx + ".4", pe=self.p("video_embeddings.position_embeddings_video.pe"),
                         pe_period=cfg.max_v_len, tt=self.p("token_type_embeddings.weight"), tt_ids=vid_ids)
 
@@ -351,9 +375,19 @@ class StateAwareRecursiveTransformer(nn.Module):
             dct = ingr_id_dict
         return StepPlan(self.config, steps, ni, ez, dct, device, mode)
 
+    def plan_signature(self, batch_step_num, ingr_id_dict, extra_zeros):
+        """Host-only: the StepPlan.signature() a batch would have (what a captured graph of the step depends on)."""
+        V = self.config.vocab_size
+        steps = tuple(int(s) for s in batch_step_num)
+        if self.config.model_mode == "video":
+            return (steps, (0,) * len(steps), (V,) * len(steps), 1)
+        ni = tuple(len(d) for d in ingr_id_dict)
+        ntok = sum(len(d.get(i, [])) for d, n in zip(ingr_id_dict, ni) for i in range(n))
+        return (steps, ni, tuple(V + int(z) for z in extra_zeros), max(ntok, 1))
+
     def forward(self, input_ids_list, video_features_list, input_masks_list, token_type_ids_list, input_labels_list,
                 ingr_input_ids, ingr_masks, ingr_sep_masks, batch_step_num, ingr_id_dict, extra_zeros, alignments, actions,
-                return_memory=False, predict=False, gumbel_noise=None):
+                return_memory=False, predict=False, gumbel_noise=None, plan=None):
         """Reference model.py:1027-1189.  ``token_type_ids_list``, ``ingr_masks`` and ``return_memory`` are accepted and
         unused, as in the reference.  ``gumbel_noise`` (or ``self.gumbel_noise``): list of (S_b, Lt, Vx_b) noise tensors
         for the textual re-simulator; drawn on the device when absent."""
@@ -361,7 +395,8 @@ class StateAwareRecursiveTransformer(nn.Module):
         mode, Lv, Lt, V, D = cfg.model_mode, cfg.max_v_len, cfg.max_t_len, cfg.vocab_size, cfg.hidden_size
         f32 = torch.float32
         dev = video_features_list[0].device
-        plan = self.make_plan(batch_step_num, ingr_id_dict, extra_zeros, alignments, dev)
+        if plan is None:
+            plan = self.make_plan(batch_step_num, ingr_id_dict, extra_zeros, alignments, dev)
         B, Nc = plan.B, plan.Nc
 
         Vst, cls, ids, masks = self._encode_clips(input_ids_list, video_features_list, input_masks_list, plan)

@@ -100,3 +100,41 @@ def test_no_cpu_path():
     be = backend.get()
     with pytest.raises(SvpcError):
         be.colsum(torch.zeros(4, 4))
+
+
+@pytest.mark.parametrize("mode", ("video", "full"))
+@pytest.mark.parametrize("dtype", (torch.float32, torch.bfloat16))
+def test_graph_replay_matches_eager(mode, dtype):
+    """CUDA-graph replay of fwd+bwd gives the eager result, also after new inputs are loaded into the static buffers."""
+    from svpc_b200.graph import GraphedTrainStep
+    cfg, sd, batch, gold = load_case("ragged", mode)
+    m = build(cfg, sd, dtype)
+
+    def eager():                         # no reference to the eager autograd graph may survive into the capture
+        loss, _p, _e, _a, grads = run(m, batch)
+        return float(loss), {n: (None if g is None else g.detach().clone()) for n, g in grads.items()}
+    loss, grads = eager()
+    m.zero_grad(set_to_none=True)
+    import gc
+    gc.collect()
+    # capture on a DIFFERENT batch of the same signature, then load the real one
+    other = synth.make_batch(cfg, **{**CASES["ragged"][1], "seed": 99})
+    if m.plan_signature(other["batch_step_num"], other["ingr_id_dict"], other["extra_zeros"]) != \
+            m.plan_signature(batch["batch_step_num"], batch["ingr_id_dict"], batch["extra_zeros"]):
+        other = batch
+    step = GraphedTrainStep(m, forward_args(other, DEV), gumbel_noise=[g.to(DEV) for g in other["gumbel"]])
+    args = forward_args(batch)           # host tensors
+    assert step.matches(args)
+    step.load(args, batch["gumbel"])
+    for _ in range(2):
+        gl = step.run()
+    torch.cuda.synchronize()
+    tol = 1e-6 if dtype == torch.float32 else 1e-5
+    assert abs(float(gl) - float(loss)) <= tol * abs(float(loss)), (float(gl), float(loss))
+    gscale = max(float(g.abs().max()) for g in grads.values() if g is not None)
+    for n, p in m.named_parameters():
+        if grads[n] is None:
+            assert p.grad is None or float(p.grad.abs().max()) == 0.0, n
+        else:          # atomics (split-K, scatter) reorder fp32 sums: compare against the tensor's / the global scale
+            err = float((p.grad - grads[n]).abs().max())
+            assert err <= 1e-4 * max(float(grads[n].abs().max()), 1e-3 * gscale), (n, err)
