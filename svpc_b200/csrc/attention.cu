@@ -159,11 +159,25 @@ static size_t at_smem_bwd(int max_lq, int max_lk, int dh) {
   return sizeof(float) * ((size_t)(2 * max_lq + 2 * max_lk) * (dh + 1) + 2 * (size_t)max_lq * max_lk + max_lk);
 }
 
+// tensor-core route (attention_tc.cu): bf16, head dim 64, 16 <= L <= 128
+int svpc_attn_tc_eligible(int dh, int dt, int max_lq, int max_lk, long long ldq, long long ldk, long long ldv, long long ldo,
+                          const void* q, const void* k, const void* v, const void* o);
+int svpc_attn_tc_fwd(int n_seq, int H, const void* q, long long ldq, const void* k, long long ldk, const void* v,
+                     long long ldv, const int* q_off, const int* q_len, const int* k_off, const int* k_len,
+                     const float* key_mask, int causal, int max_lq, int max_lk, void* ctx, long long ldo, cudaStream_t st);
+int svpc_attn_tc_bwd(int n_seq, int H, const void* q, long long ldq, const void* k, long long ldk, const void* v,
+                     long long ldv, const int* q_off, const int* q_len, const int* k_off, const int* k_len,
+                     const float* key_mask, int causal, int max_lq, int max_lk, const void* dctx, long long lddo, void* dq,
+                     long long lddq, void* dk, long long lddk, void* dv, long long lddv, cudaStream_t st);
+
 extern "C" int svpc_attn_fwd(int n_seq, int H, int dh, const void* q, long long ldq, const void* k, long long ldk,
                              const void* v, long long ldv, int dt, const int* q_off, const int* q_len, const int* k_off,
                              const int* k_len, const float* key_mask, int causal, int max_lq, int max_lk, void* ctx,
                              long long ldo, svpc_stream_t stream) {
   if (n_seq <= 0) return SVPC_OK;
+  if (svpc_attn_tc_eligible(dh, dt, max_lq, max_lk, ldq, ldk, ldv, ldo, q, k, v, ctx))
+    return svpc_attn_tc_fwd(n_seq, H, q, ldq, k, ldk, v, ldv, q_off, q_len, k_off, k_len, key_mask, causal, max_lq, max_lk,
+                            ctx, ldo, (cudaStream_t)stream);
   const size_t smem = at_smem_fwd(max_lq, max_lk, dh);
   SVPC_REQUIRE(smem <= 227 * 1024, "attn_fwd: sequence too long for the short-sequence kernel (lq=%d lk=%d)", max_lq, max_lk);
   cudaStream_t st = (cudaStream_t)stream;
@@ -181,6 +195,10 @@ extern "C" int svpc_attn_bwd(int n_seq, int H, int dh, const void* q, long long 
                              long long lddo, void* dq, long long lddq, void* dk, long long lddk, void* dv, long long lddv,
                              svpc_stream_t stream) {
   if (n_seq <= 0) return SVPC_OK;
+  if (svpc_attn_tc_eligible(dh, dt, max_lq, max_lk, ldq, ldk, ldv, lddo, q, k, v, dctx) && (lddq | lddk | lddv) % 2 == 0 &&
+      (((uintptr_t)dq | (uintptr_t)dk | (uintptr_t)dv) & 3) == 0 && lddo % 8 == 0 && ((uintptr_t)dctx & 15) == 0)
+    return svpc_attn_tc_bwd(n_seq, H, q, ldq, k, ldk, v, ldv, q_off, q_len, k_off, k_len, key_mask, causal, max_lq, max_lk,
+                            dctx, lddo, dq, lddq, dk, lddk, dv, lddv, (cudaStream_t)stream);
   const size_t smem = at_smem_bwd(max_lq, max_lk, dh);
   SVPC_REQUIRE(smem <= 227 * 1024, "attn_bwd: sequence too long for the short-sequence kernel (lq=%d lk=%d)", max_lq, max_lk);
   cudaStream_t st = (cudaStream_t)stream;

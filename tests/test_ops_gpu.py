@@ -190,6 +190,11 @@ ATT_CASES = {
     "cross": ([8, 8], [3, 3], False, False, True),
     "ragged_steps": ([4, 2, 3], [4, 2, 3], False, False, False),
     "full_len": ([100, 100], [100, 100], False, True, False),
+    # shapes that take the tensor-core kernel on bf16 / head dim 64 (16 <= L <= 128)
+    "tc_ragged": ([100, 37, 64, 16], [100, 37, 64, 16], False, True, False),
+    "tc_causal": ([25, 25, 17], [25, 25, 17], True, True, False),
+    "tc_cross": ([25, 30], [20, 48], False, True, True),
+    "tc_128": ([128], [128], True, False, False),
 }
 
 
@@ -198,8 +203,10 @@ ATT_CASES = {
 @pytest.mark.parametrize("H,dh", [(4, 16), (12, 64)])
 def test_attention(cb, tb, dt, case, H, dh):
     ql, kl, causal, use_mask, cross = ATT_CASES[case]
-    if case == "full_len" and dh == 16:
+    if (case == "full_len" or case.startswith("tc_")) and dh == 16:
         pytest.skip("covered by the other head size")
+    if case == "tc_128" and dt == F32:
+        pytest.skip("the fp32 short-sequence kernel stages Q/K/V/dO/P/dS in one CTA's shared memory: L <= ~110")
     D = H * dh
     nq, nk = sum(ql), sum(kl)
     qo = I32([sum(ql[:i]) for i in range(len(ql))]); ko = I32([sum(kl[:i]) for i in range(len(kl))])
