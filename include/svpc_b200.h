@@ -66,6 +66,8 @@ int svpc_act_bwd(int rows, int cols, const void* dy, const void* ref, int dt, in
                  svpc_stream_t stream);
 int svpc_colsum(int rows, int cols, const void* x, int dt, float* out, svpc_stream_t stream);
 int svpc_cast(long long n, const void* src, int dts, void* dst, int dtd, svpc_stream_t stream);
+int svpc_cast2d(int rows, int cols, const void* src, int dts, long long lds, void* dst, int dtd, long long ldd,
+                svpc_stream_t stream);
 int svpc_sum(long long n, const float* x, float* out, svpc_stream_t stream);
 
 /* BertLayerNorm (model.py:152-156) on x (+ res), optional + pe[row % pe_period] + tt[tt_ids[row]]
@@ -79,9 +81,10 @@ int svpc_ln_bwd(int rows, int D, const void* dy, int dt_dy, const void* pre, int
 int svpc_index_colsum(int rows, int D, const void* dy, int dt, const int* ids, int nbins, float* out,
                       svpc_stream_t stream);
 
-/* Embedding gather + LN(W) (model.py:492-494 / 519-521) and its backward (scatter-add into the table). */
+/* Embedding gather + LN(W) (model.py:492-494 / 519-521) and its backward (scatter-add into the table).  ldy: row
+ * pitch of y in elements (>= W; padded to 16 bytes so that y is a TMA-addressable GEMM operand). */
 int svpc_embed_ln_fwd(int rows, int W, const float* table, const int* ids, const float* gamma, const float* beta,
-                      float eps, void* y, int dt, float* mean, float* rstd, svpc_stream_t stream);
+                      float eps, void* y, long long ldy, int dt, float* mean, float* rstd, svpc_stream_t stream);
 int svpc_embed_ln_bwd(int rows, int W, int V, const void* dy, int dt, const float* table, const int* ids,
                       const float* mean, const float* rstd, const float* gamma, int padding_idx, float* dtable,
                       float* dgamma, float* dbeta, svpc_stream_t stream);

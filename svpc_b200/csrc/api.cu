@@ -45,6 +45,29 @@ extern "C" int svpc_cast(long long n, const void* src, int dts, void* dst, int d
   return svpc_check_launch("cast");
 }
 
+// strided 2-D cast: dst[r, c] = src[r, c] with independent row pitches (padded bf16 GEMM operands: TMA wants row pitches
+// that are multiples of 16 bytes, the model's word-vector size 300 and vocabulary 951 are not multiples of 8)
+template <typename TS, typename TD>
+__global__ void cast2d_kernel(int rows, int cols, const TS* __restrict__ s, long long lds, TD* __restrict__ d, long long ldd) {
+  const long long n = (long long)rows * cols;
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) {
+    const long long r = i / cols, c = i - r * cols;
+    stf(d + r * ldd + c, ldf(s + r * lds + c));
+  }
+}
+
+extern "C" int svpc_cast2d(int rows, int cols, const void* src, int dts, long long lds, void* dst, int dtd, long long ldd,
+                           svpc_stream_t stream) {
+  if (rows <= 0 || cols <= 0) return SVPC_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  int blocks = svpc_imin(svpc_cdiv((long long)rows * cols, 256), SVPC_NUM_SMS * 16);
+  SVPC_DISPATCH(dts, TS, SVPC_DISPATCH(dtd, TD, (cast2d_kernel<TS, TD><<<blocks, 256, 0, st>>>(rows, cols, (const TS*)src, lds,
+                                                                                             (TD*)dst, ldd))));
+  return svpc_check_launch("cast2d");
+}
+
 // deterministic single-CTA sum (loss reductions: a few thousand elements)
 __global__ void sum_kernel(long long n, const float* __restrict__ x, float* __restrict__ out) {
   __shared__ float red[64];

@@ -17,6 +17,8 @@ struct GemmSimtParams {
   const void* residual; long long ldr;
   void* pre; long long ldp;
   int accumulate;
+  int k_per_split;         // grid.z slices of K (split-K: fp32 atomics into a zeroed / accumulated D)
+  int atomic;
 };
 
 template <typename TA, typename TB, typename TD>
@@ -34,18 +36,19 @@ __global__ void __launch_bounds__(GS_THREADS) gemm_simt_kernel(const GemmSimtPar
 #pragma unroll
     for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
 
-  for (int k0 = 0; k0 < p.K; k0 += GS_BK) {
+  const int kbeg = blockIdx.z * p.k_per_split, kend = min(p.K, kbeg + p.k_per_split);
+  for (int k0 = kbeg; k0 < kend; k0 += GS_BK) {
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       const int e = tid + i * GS_THREADS;
       int mm, kk;
       if (a_kfast) { kk = e & 15; mm = e >> 4; } else { mm = e & 63; kk = e >> 6; }
       const int gm = m0 + mm, gk = k0 + kk;
-      As[kk][mm] = (gm < p.M && gk < p.K) ? ldf(A + (long long)gm * p.sa_m + (long long)gk * p.sa_k) : 0.f;
+      As[kk][mm] = (gm < p.M && gk < kend) ? ldf(A + (long long)gm * p.sa_m + (long long)gk * p.sa_k) : 0.f;
       int nn, kb;
       if (b_kfast) { kb = e & 15; nn = e >> 4; } else { nn = e & 63; kb = e >> 6; }
       const int gn = n0 + nn, gkb = k0 + kb;
-      Bs[kb][nn] = (gn < p.N && gkb < p.K) ? ldf(B + (long long)gn * p.sb_n + (long long)gkb * p.sb_k) : 0.f;
+      Bs[kb][nn] = (gn < p.N && gkb < kend) ? ldf(B + (long long)gn * p.sb_n + (long long)gkb * p.sb_k) : 0.f;
     }
     __syncthreads();
 #pragma unroll
@@ -74,6 +77,7 @@ __global__ void __launch_bounds__(GS_THREADS) gemm_simt_kernel(const GemmSimtPar
       const int n = n0 + tx * 4 + j;
       if (n >= p.N) continue;
       float v = acc[i][j];
+      if (p.atomic) { atomicAdd(reinterpret_cast<float*>(D) + (long long)m * p.ldd + n, v); continue; }
       if (p.bias) v += p.bias[n];
       if (Pre) stf(Pre + (long long)m * p.ldp + n, v);
       v = svpc_act(v, p.act);
@@ -86,8 +90,20 @@ __global__ void __launch_bounds__(GS_THREADS) gemm_simt_kernel(const GemmSimtPar
 }
 
 template <typename TA, typename TB>
-static int launch_td(const GemmSimtParams& p, int dtD, cudaStream_t st) {
-  dim3 grid(svpc_cdiv(p.N, GS_BN), svpc_cdiv(p.M, GS_BM));
+static int launch_td(GemmSimtParams p, int dtD, cudaStream_t st) {
+  const int tiles = svpc_cdiv(p.N, GS_BN) * svpc_cdiv(p.M, GS_BM);
+  int split = 1;
+  const bool plain = !p.bias && p.act == SVPC_ACT_NONE && !p.residual && !p.pre && dtD == SVPC_F32;
+  if (plain && tiles < SVPC_NUM_SMS / 2 && p.K >= 512) split = svpc_imin(SVPC_NUM_SMS / tiles, p.K / 128);
+  if (split < 1) split = 1;
+  p.k_per_split = svpc_cdiv(svpc_cdiv(p.K, split), GS_BK) * GS_BK;
+  split = svpc_cdiv(p.K, p.k_per_split);
+  p.atomic = split > 1;
+  if (p.atomic && !p.accumulate) {
+    cudaError_t e = cudaMemset2DAsync(p.D, (size_t)p.ldd * 4, 0, (size_t)p.N * 4, (size_t)p.M, st);
+    if (e != cudaSuccess) { svpc_set_error("gemm_simt: memset2D: %s", cudaGetErrorString(e)); return SVPC_ERR_CUDA; }
+  }
+  dim3 grid(svpc_cdiv(p.N, GS_BN), svpc_cdiv(p.M, GS_BM), split);
   SVPC_DISPATCH(dtD, TD, (gemm_simt_kernel<TA, TB, TD><<<grid, GS_THREADS, 0, st>>>(p)));
   return svpc_check_launch("gemm_simt");
 }
@@ -96,7 +112,7 @@ int svpc_gemm_simt_launch(int M, int N, int K, const void* A, int dtA, long long
                           int dtB, long long sb_n, long long sb_k, void* D, int dtD, long long ldd, const float* bias,
                           int act, const void* residual, long long ldr, void* pre, long long ldp, int accumulate,
                           cudaStream_t st) {
-  GemmSimtParams p{M, N, K, A, sa_m, sa_k, B, sb_n, sb_k, D, ldd, bias, act, residual, ldr, pre, ldp, accumulate};
+  GemmSimtParams p{M, N, K, A, sa_m, sa_k, B, sb_n, sb_k, D, ldd, bias, act, residual, ldr, pre, ldp, accumulate, K, 0};
   SVPC_DISPATCH(dtA, TA, SVPC_DISPATCH(dtB, TB, return (launch_td<TA, TB>(p, dtD, st))));
   return SVPC_OK;
 }
@@ -126,7 +142,8 @@ extern "C" int svpc_gemm(int M, int N, int K, const void* A, int dtA, long long 
   SVPC_REQUIRE(sb_n == 1 || sb_k == 1, "gemm: B needs a unit stride (sb_n=%lld sb_k=%lld)", sb_n, sb_k);
   SVPC_REQUIRE(!(accumulate && (act != SVPC_ACT_NONE || residual)), "gemm: accumulate excludes act / residual");
   cudaStream_t st = (cudaStream_t)stream;
-  const int ok = svpc_gemm_tc_eligible(M, N, K, dtA, sa_m, sa_k, dtB, sb_n, sb_k, dtD, ldd);
+  const int ok = svpc_gemm_tc_eligible(M, N, K, dtA, sa_m, sa_k, dtB, sb_n, sb_k, dtD, ldd) &&
+                 (((uintptr_t)A | (uintptr_t)B) & 15) == 0;   // TMA: 16-byte aligned global base
   if (route == SVPC_GEMM_TC && !ok) {
     svpc_set_error("gemm: problem %dx%dx%d not eligible for the tcgen05 route", M, N, K);
     return SVPC_ERR_UNSUPPORTED;

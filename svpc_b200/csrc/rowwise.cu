@@ -41,11 +41,16 @@ __global__ void act_bwd_kernel(int rows, int cols, const T* __restrict__ dy, con
   }
 }
 
+static int act_bwd_vec_launch(int rows, int cols, const void* dy, const void* ref, int dt, int act, void* dz, float* dbias,
+                              cudaStream_t st);
+
 extern "C" int svpc_act_bwd(int rows, int cols, const void* dy, const void* ref, int dt, int act, void* dz, float* dbias,
                             svpc_stream_t stream) {
   if (rows <= 0 || cols <= 0) return SVPC_OK;
   cudaStream_t st = (cudaStream_t)stream;
   if (dbias) cudaMemsetAsync(dbias, 0, sizeof(float) * cols, st);
+  if (cols % 8 == 0 && (((uintptr_t)dy | (uintptr_t)ref | (uintptr_t)dz) & 15) == 0)
+    return act_bwd_vec_launch(rows, cols, dy, ref, dt, act, dz, dbias, st);
   dim3 grid(svpc_cdiv(cols, 32), svpc_imin(svpc_cdiv(rows, 8), 64));
   SVPC_DISPATCH(dt, T, (act_bwd_kernel<T><<<grid, dim3(32, 8), 0, st>>>(rows, cols, (const T*)dy, (const T*)ref, act,
                                                                       (T*)dz, dbias)));
@@ -79,6 +84,208 @@ int svpc_weighted_colsum(int rows, int cols, const void* x, int dt, const float*
   dim3 grid(svpc_cdiv(cols, 32), svpc_imin(svpc_cdiv(rows, 8), 64));
   SVPC_DISPATCH(dt, T, (weighted_colsum_kernel<T><<<grid, dim3(32, 8), 0, st>>>(rows, cols, (const T*)x, w, out)));
   return svpc_check_launch("weighted_colsum");
+}
+
+// ------------------------------------------------------------------------------------------------
+// Warp-per-row LayerNorm for D = NCH * 256 (the model's hidden size 768 = 3 * 256): every lane owns 8 contiguous
+// columns per 256-column chunk (16-byte loads / stores for bf16, 2 x 16 for fp32), row statistics by warp shuffles only,
+// no block barrier.  Same two-pass statistics (mean, then centred second moment) as the generic kernel.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void ld8(const float* p, float (&v)[8]) {
+  const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
+  v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+}
+__device__ __forceinline__ void ld8(const bf16* p, float (&v)[8]) {
+  const uint4 u = *reinterpret_cast<const uint4*>(p);
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) { v[2 * i] = __low2float(h[i]); v[2 * i + 1] = __high2float(h[i]); }
+}
+__device__ __forceinline__ void st8(float* p, const float (&v)[8]) {
+  *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+  *reinterpret_cast<float4*>(p + 4) = make_float4(v[4], v[5], v[6], v[7]);
+}
+__device__ __forceinline__ void st8(bf16* p, const float (&v)[8]) {
+  uint4 u;
+  __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+  *reinterpret_cast<uint4*>(p) = u;
+}
+__device__ __forceinline__ float rnd_as(float v, const float*) { return v; }
+__device__ __forceinline__ float rnd_as(float v, const bf16*) { return __bfloat162float(__float2bfloat16_rn(v)); }
+
+template <typename TI, typename TO, int NCH>
+__global__ void __launch_bounds__(256) ln_fwd_warp_kernel(int rows, const TI* __restrict__ x, const TI* __restrict__ res,
+                                                          const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                          float eps, const float* __restrict__ pe, int pe_period,
+                                                          const float* __restrict__ tt, const int* __restrict__ tt_ids,
+                                                          TO* __restrict__ y, TI* __restrict__ pre,
+                                                          float* __restrict__ mean, float* __restrict__ rstd) {
+  constexpr int D = NCH * 256;
+  const int lane = threadIdx.x & 31;
+  const int nw = gridDim.x * 8;
+  for (int r = blockIdx.x * 8 + (threadIdx.x >> 5); r < rows; r += nw) {
+    const long long base = (long long)r * D;
+    float v[NCH][8];
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < NCH; ++i) {
+      const int c = i * 256 + lane * 8;
+      ld8(x + base + c, v[i]);
+      if (res) {
+        float t[8];
+        ld8(res + base + c, t);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) v[i][e] = rnd_as(v[i][e] + t[e], x);   // statistics on the stored (rounded) value
+        st8(pre + base + c, v[i]);
+      }
+#pragma unroll
+      for (int e = 0; e < 8; ++e) s += v[i][e];
+    }
+    const float mu = warp_sum(s) * (1.0f / D);
+    float q = 0.f;
+#pragma unroll
+    for (int i = 0; i < NCH; ++i)
+#pragma unroll
+      for (int e = 0; e < 8; ++e) { const float d = v[i][e] - mu; q = fmaf(d, d, q); }
+    const float var = warp_sum(q) * (1.0f / D);
+    const float rs = 1.0f / sqrtf(var + eps);
+    if (lane == 0) { mean[r] = mu; rstd[r] = rs; }
+    const float* per = pe ? pe + (long long)(r % pe_period) * D : nullptr;
+    const float* ttr = tt ? tt + (long long)tt_ids[r] * D : nullptr;
+#pragma unroll
+    for (int i = 0; i < NCH; ++i) {
+      const int c = i * 256 + lane * 8;
+      float g[8], b[8], o[8];
+      ld8(gamma + c, g);
+      ld8(beta + c, b);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) o[e] = (v[i][e] - mu) * rs * g[e] + b[e];
+      if (per) { ld8(per + c, g);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) o[e] += g[e]; }
+      if (ttr) { ld8(ttr + c, g);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) o[e] += g[e]; }
+      st8(y + base + c, o);
+    }
+  }
+}
+
+template <typename TG, typename TP, int NCH>
+__global__ void __launch_bounds__(256, 2) ln_bwd_warp_kernel(int rows, const TG* __restrict__ dy, const TP* __restrict__ pre,
+                                                             const float* __restrict__ mean, const float* __restrict__ rstd,
+                                                             const float* __restrict__ gamma, TP* __restrict__ dpre,
+                                                             float* __restrict__ dgamma, float* __restrict__ dbeta) {
+  constexpr int D = NCH * 256;
+  __shared__ float part[8][D];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int nw = gridDim.x * 8;
+  float ag[NCH][8], ab[NCH][8];
+#pragma unroll
+  for (int i = 0; i < NCH; ++i)
+#pragma unroll
+    for (int e = 0; e < 8; ++e) { ag[i][e] = 0.f; ab[i][e] = 0.f; }
+  for (int r = blockIdx.x * 8 + warp; r < rows; r += nw) {
+    const long long base = (long long)r * D;
+    const float mu = mean[r], rs = rstd[r];
+    float d[NCH][8], xh[NCH][8];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < NCH; ++i) {
+      const int c = i * 256 + lane * 8;
+      float gm[8];
+      ld8(dy + base + c, d[i]);
+      ld8(pre + base + c, xh[i]);
+      ld8(gamma + c, gm);                       // L1-resident
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        xh[i][e] = (xh[i][e] - mu) * rs;
+        ag[i][e] = fmaf(d[i][e], xh[i][e], ag[i][e]);
+        ab[i][e] += d[i][e];
+        d[i][e] *= gm[e];                       // g = dy * gamma
+        s1 += d[i][e];
+        s2 = fmaf(d[i][e], xh[i][e], s2);
+      }
+    }
+    const float m1 = warp_sum(s1) * (1.0f / D), m2 = warp_sum(s2) * (1.0f / D);
+#pragma unroll
+    for (int i = 0; i < NCH; ++i) {
+      float o[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) o[e] = rs * (d[i][e] - m1 - xh[i][e] * m2);
+      st8(dpre + base + i * 256 + lane * 8, o);
+    }
+  }
+  // column sums: across the CTA's warps through shared memory, then one red.global per column per CTA
+#pragma unroll
+  for (int pass = 0; pass < 2; ++pass) {
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < NCH; ++i)
+#pragma unroll
+      for (int e = 0; e < 8; ++e) part[warp][i * 256 + lane * 8 + e] = pass == 0 ? ag[i][e] : ab[i][e];
+    __syncthreads();
+    for (int c = threadIdx.x; c < D; c += 256) {
+      float t = 0.f;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) t += part[w][c];
+      atomicAdd((pass == 0 ? dgamma : dbeta) + c, t);
+    }
+  }
+}
+
+// activation backward + bias gradient, 8 columns (16 B of bf16) per thread: a warp covers 256 contiguous columns of a row
+template <typename T>
+__global__ void __launch_bounds__(256) act_bwd_vec_kernel(int rows, int cols, const T* __restrict__ dy,
+                                                          const T* __restrict__ ref, int act, T* __restrict__ dz,
+                                                          float* __restrict__ dbias) {
+  __shared__ float red[8][256];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int c0 = (blockIdx.x * 32 + tx) * 8;
+  float acc[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+  if (c0 < cols) {
+    for (int r = blockIdx.y * 8 + ty; r < rows; r += gridDim.y * 8) {
+      const long long o = (long long)r * cols + c0;
+      float g[8], y[8];
+      ld8(dy + o, g);
+      if (act != SVPC_ACT_NONE) {
+        ld8(ref + o, y);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          if (act == SVPC_ACT_RELU) g[e] = y[e] > 0.f ? g[e] : 0.f;
+          else if (act == SVPC_ACT_GELU) g[e] *= svpc_gelu_grad(y[e]);
+          else g[e] *= y[e] * (1.f - y[e]);
+        }
+      }
+      if (dz) st8(dz + o, g);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) acc[e] += g[e];
+    }
+  }
+#pragma unroll
+  for (int e = 0; e < 8; ++e) red[ty][tx * 8 + e] = acc[e];
+  __syncthreads();
+  const int c = blockIdx.x * 256 + threadIdx.x;
+  if (dbias && c < cols) {
+    float t = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) t += red[i][threadIdx.x];
+    atomicAdd(dbias + c, t);
+  }
+}
+
+static inline bool rw_al16(const void* p) { return ((uintptr_t)p & 15) == 0; }
+
+static int act_bwd_vec_launch(int rows, int cols, const void* dy, const void* ref, int dt, int act, void* dz, float* dbias,
+                              cudaStream_t st) {
+  const int gx = svpc_cdiv(cols, 256);
+  dim3 grid(gx, svpc_imin(svpc_cdiv(rows, 8), svpc_cdiv(SVPC_NUM_SMS * 4, gx)));
+  SVPC_DISPATCH(dt, T, (act_bwd_vec_kernel<T><<<grid, 256, 0, st>>>(rows, cols, (const T*)dy, (const T*)ref, act, (T*)dz, dbias)));
+  return svpc_check_launch("act_bwd");
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -145,6 +352,13 @@ extern "C" int svpc_ln_fwd(int rows, int D, const void* x, const void* res, int 
   SVPC_REQUIRE(D <= RW_THREADS * RW_MAXPT, "ln_fwd: D=%d too wide", D);
   SVPC_REQUIRE(!res || pre, "ln_fwd: residual given without a pre buffer");
   cudaStream_t st = (cudaStream_t)stream;
+  if (D == 768 && rw_al16(x) && rw_al16(res) && rw_al16(y) && rw_al16(pre) && rw_al16(gamma) && rw_al16(beta) && rw_al16(pe) &&
+      rw_al16(tt)) {
+    const int grid = svpc_imin(svpc_cdiv(rows, 8), SVPC_NUM_SMS * 8);
+    SVPC_DISPATCH(dt_in, TI, SVPC_DISPATCH(dt_out, TO, (ln_fwd_warp_kernel<TI, TO, 3><<<grid, 256, 0, st>>>(
+        rows, (const TI*)x, (const TI*)res, gamma, beta, eps, pe, pe_period, tt, tt_ids, (TO*)y, (TI*)pre, mean, rstd))));
+    return svpc_check_launch("ln_fwd");
+  }
   SVPC_DISPATCH(dt_in, TI, SVPC_DISPATCH(dt_out, TO, (ln_fwd_kernel<TI, TO><<<rw_grid(rows), RW_THREADS, 0, st>>>(
       rows, D, (const TI*)x, (const TI*)res, gamma, beta, eps, pe, pe_period, tt, tt_ids, (TO*)y, (TI*)pre, mean, rstd))));
   return svpc_check_launch("ln_fwd");
@@ -205,6 +419,12 @@ extern "C" int svpc_ln_bwd(int rows, int D, const void* dy, int dt_dy, const voi
   cudaMemsetAsync(dbeta, 0, sizeof(float) * D, st);
   if (rows <= 0) return SVPC_OK;
   SVPC_REQUIRE(D <= RW_THREADS * RW_MAXPT, "ln_bwd: D=%d too wide", D);
+  if (D == 768 && rw_al16(dy) && rw_al16(pre) && rw_al16(dpre) && rw_al16(gamma)) {
+    const int g2 = svpc_imin(svpc_cdiv(rows, 8), SVPC_NUM_SMS * 4);
+    SVPC_DISPATCH(dt_dy, TG, SVPC_DISPATCH(dt_pre, TP, (ln_bwd_warp_kernel<TG, TP, 3><<<g2, 256, 0, st>>>(
+        rows, (const TG*)dy, (const TP*)pre, mean, rstd, gamma, (TP*)dpre, dgamma, dbeta))));
+    return svpc_check_launch("ln_bwd");
+  }
   const int grid = svpc_imin(rows, SVPC_NUM_SMS * 4);
   SVPC_DISPATCH(dt_dy, TG, SVPC_DISPATCH(dt_pre, TP, (ln_bwd_kernel<TG, TP><<<grid, RW_THREADS, 0, st>>>(
       rows, D, (const TG*)dy, (const TP*)pre, mean, rstd, gamma, (TP*)dpre, dgamma, dbeta))));
@@ -253,8 +473,8 @@ __global__ void __launch_bounds__(EM_THREADS) embed_ln_fwd_kernel(int rows, int 
                                                                   const int* __restrict__ ids,
                                                                   const float* __restrict__ gamma,
                                                                   const float* __restrict__ beta, float eps,
-                                                                  T* __restrict__ y, float* __restrict__ mean,
-                                                                  float* __restrict__ rstd) {
+                                                                  T* __restrict__ y, long long ldy,
+                                                                  float* __restrict__ mean, float* __restrict__ rstd) {
   __shared__ float red[64];
   for (int r = blockIdx.x; r < rows; r += gridDim.x) {
     const float* src = table + (long long)ids[r] * W;
@@ -278,19 +498,20 @@ __global__ void __launch_bounds__(EM_THREADS) embed_ln_fwd_kernel(int rows, int 
 #pragma unroll
     for (int i = 0; i < EM_MAXPT; ++i) {
       const int c = threadIdx.x + i * EM_THREADS;
-      if (c < W) stf(y + (long long)r * W + c, (v[i] - mu) * rs * gamma[c] + beta[c]);
+      if (c < W) stf(y + (long long)r * ldy + c, (v[i] - mu) * rs * gamma[c] + beta[c]);
     }
   }
 }
 
 extern "C" int svpc_embed_ln_fwd(int rows, int W, const float* table, const int* ids, const float* gamma,
-                                 const float* beta, float eps, void* y, int dt, float* mean, float* rstd,
+                                 const float* beta, float eps, void* y, long long ldy, int dt, float* mean, float* rstd,
                                  svpc_stream_t stream) {
   if (rows <= 0) return SVPC_OK;
   SVPC_REQUIRE(W <= EM_THREADS * EM_MAXPT, "embed_ln: W=%d too wide", W);
+  SVPC_REQUIRE(ldy >= W, "embed_ln: ldy=%lld < W=%d", ldy, W);
   cudaStream_t st = (cudaStream_t)stream;
   SVPC_DISPATCH(dt, T, (embed_ln_fwd_kernel<T><<<rw_grid(rows), EM_THREADS, 0, st>>>(rows, W, table, ids, gamma, beta, eps,
-                                                                                    (T*)y, mean, rstd)));
+                                                                                    (T*)y, ldy, mean, rstd)));
   return svpc_check_launch("embed_ln_fwd");
 }
 

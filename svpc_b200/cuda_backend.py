@@ -163,10 +163,24 @@ class CudaBackend:
         self._call("svpc_colsum", x.shape[0], x.shape[1], _ptr(x), _DT[x.dtype], _ptr(out))
         return out
 
+    @staticmethod
+    def _padded_empty(rows, cols, dtype, device):
+        """(rows, cols) tensor whose row pitch is a multiple of 16 bytes (a TMA requirement for GEMM operands)."""
+        q = 16 // torch.empty((), dtype=dtype).element_size()
+        ld = (cols + q - 1) // q * q
+        if ld == cols:
+            return torch.empty(rows, cols, dtype=dtype, device=device)
+        return torch.zeros(rows, ld, dtype=dtype, device=device)[:, :cols]
+
     def cast(self, x, dtype):
         self._chk(x)
         if x.dtype == dtype:
             return x
+        if x.dim() == 2 and dtype == torch.bfloat16 and x.shape[1] % 8 != 0 and x.shape[1] > 8 and x.stride(1) == 1:
+            out = self._padded_empty(x.shape[0], x.shape[1], dtype, x.device)
+            self._call("svpc_cast2d", x.shape[0], x.shape[1], _ptr(x), _DT[x.dtype], _ll(x.stride(0)), _ptr(out), _DT[dtype],
+                       _ll(out.stride(0)))
+            return out
         x = self._c(x)
         out = torch.empty(x.shape, dtype=dtype, device=x.device)
         self._call("svpc_cast", _ll(x.numel()), _ptr(x), _DT[x.dtype], _ptr(out), _DT[dtype])
@@ -218,11 +232,12 @@ class CudaBackend:
     def embed_ln_fwd(self, table, ids, gamma, beta, eps, out_dtype):
         self._chk(table, ids)
         rows, W = ids.numel(), table.shape[1]
-        y = torch.empty(rows, W, dtype=out_dtype, device=table.device)
+        y = self._padded_empty(rows, W, out_dtype, table.device) if out_dtype == torch.bfloat16 else \
+            torch.empty(rows, W, dtype=out_dtype, device=table.device)
         mean = torch.empty(rows, dtype=torch.float32, device=table.device)
         rstd = torch.empty(rows, dtype=torch.float32, device=table.device)
         self._call("svpc_embed_ln_fwd", rows, W, _ptr(self._c(table)), _ptr(ids), _ptr(gamma), _ptr(beta), _f(eps), _ptr(y),
-                   _DT[out_dtype], _ptr(mean), _ptr(rstd))
+                   _ll(y.stride(0)), _DT[out_dtype], _ptr(mean), _ptr(rstd))
         return y, mean, rstd
 
     def embed_ln_bwd(self, dy, table, ids, mean, rstd, gamma, eps, padding_idx):
