@@ -164,6 +164,14 @@ int svpc_lstm_step_bwd(int B, int D, int Nc, int Smax, int j, const float* whh_t
                        const float* gates, const float* dout, float* dgates, float* dc, svpc_stream_t stream);
 int svpc_transpose_f32(int R, int C, const float* in, float* out, svpc_stream_t stream);
 
+/* Greedy decoding step (src/translator.py:106-112): per clip argmax of the current position's scores with column `unk`
+ * forced to -1e10; ext_out[r, pos] = argmax (extended id), next_in[r] = argmax, or unk when it is a copied OOV id
+ * (>= width - n_oov).  Row r starts at scores + row_off[r] (or r * ld when row_off is NULL) and is row_width[r] (or
+ * `width`) wide. */
+int svpc_greedy_pick(int rows, const float* scores, const int* row_off, long long ld, const int* row_width, int width,
+                     const int* row_noov, int unk, int* next_in, long long* ext_out, long long ld_ext, int pos,
+                     svpc_stream_t stream);
+
 /* nn.BCELoss(sum) on probabilities (model.py:871) and AsymmetricLoss (libs/ASL/src/loss_functions/losses.py:15-50). */
 int svpc_bce_fwd(long long n, const float* p, const float* y, float* loss, svpc_stream_t stream);
 int svpc_bce_bwd(long long n, const float* p, const float* y, const float* g, float* dp, svpc_stream_t stream);

@@ -479,6 +479,13 @@ class CudaBackend:
                    _ptr(demb))
         return dP, demb
 
+    # ------------------------------------------------------------------ greedy decoding
+    def greedy_pick(self, scores, row_off, ld, row_width, width, row_noov, unk, next_in, ext_out, pos):
+        self._chk(scores, next_in, ext_out)
+        assert ext_out.dtype == torch.int64 and ext_out.stride(1) == 1 and next_in.dtype == torch.int32
+        self._call("svpc_greedy_pick", int(next_in.numel()), _ptr(scores), _ptr(row_off), _ll(ld), _ptr(row_width), int(width),
+                   _ptr(row_noov), int(unk), _ptr(next_in), _ptr(ext_out), _ll(ext_out.stride(0)), int(pos))
+
     # ------------------------------------------------------------------ losses
     def bce_fwd(self, p, y):
         self._chk(p, y)

@@ -23,6 +23,7 @@ from . import functional as Fn
 from .backend import ACT_NONE, ACT_RELU, ACT_GELU, ACT_SIGMOID
 from .config import SvpcConfig, PAD, UNK, IGNORE
 from .synth import state_dict_spec, sinusoid_table
+from .compat import make_node as _make_node
 
 LSTM_KEYS = tuple(f"{k}_l0{s}" for s in ("", "_reverse") for k in ("weight_ih", "weight_hh", "bias_ih", "bias_hh"))
 
@@ -152,19 +153,6 @@ class StepPlan:
 # ------------------------------------------------------------------------------------------------
 # module tree with the reference's attribute names
 # ------------------------------------------------------------------------------------------------
-class _Node(nn.Module):
-    """Plain container: holds parameters / buffers / child nodes under the reference's names."""
-
-    def __init__(self, owner=None):
-        super().__init__()
-        object.__setattr__(self, "_owner", owner)
-
-    def _child(self, name):
-        if name not in self._modules:
-            self.add_module(name, _Node(self._owner))
-        return self._modules[name]
-
-
 class StateAwareRecursiveTransformer(nn.Module):
     """Drop-in for reference model.py:826.  ``compute_dtype``: torch.float32 = parity path (fp32 operands, fp32
     accumulate), torch.bfloat16 = fast path (bf16 operands on tcgen05, fp32 accumulate / statistics / losses)."""
@@ -219,9 +207,22 @@ class StateAwareRecursiveTransformer(nn.Module):
 
     def _apply(self, fn, *a, **k):
         r = super()._apply(fn, *a, **k)
+        self._invalidate()
+        return r
+
+    def _invalidate(self):
+        """Parameters were moved / replaced: drop the name -> tensor cache and the compute-dtype weight copies."""
         self._pcache = {}
         Fn.WEIGHTS.clear()
-        return r
+
+    def _load_from_state_dict(self, state_dict, prefix, *args, **kwargs):
+        # a reference checkpoint saved without set_pretrained_embedding holds `reasoner.action_embeddings.weight`
+        # (nn.Embedding); after it the key is the bare Parameter `reasoner.action_embeddings` (model.py:773-775)
+        for r in ("reasoner", "recipe_reasoner"):
+            old = f"{prefix}{r}.action_embeddings.weight"
+            if old in state_dict:
+                state_dict[f"{prefix}{r}.action_embeddings"] = state_dict.pop(old)
+        return super()._load_from_state_dict(state_dict, prefix, *args, **kwargs)
 
     # ------------------------------------------------------------------------------------------
     # building blocks (all batched over clips)
@@ -375,6 +376,51 @@ class StateAwareRecursiveTransformer(nn.Module):
             dct = ingr_id_dict
         return StepPlan(self.config, steps, ni, ez, dct, device, mode)
 
+    def make_plan_raw(self, steps, ni, extra_zeros, ingr_id_dict, device):
+        """StepPlan from explicit per-video counts (piecewise callers: svpc_b200.compat, svpc_b200.decode)."""
+        return StepPlan(self.config, [int(s) for s in steps], [int(n) for n in ni], [int(z) for z in extra_zeros],
+                        ingr_id_dict, device, "copy")
+
+    # ---- piecewise entry points used by the reference translator (src/translator.py:57-159)
+    def forward_step(self, input_ids, video_features, input_masks):
+        """Reference model.py:887-894: (N, L) ids, (N, L, F) features, (N, L) masks -> (N, max_v_len, D), all rows of
+        the last encoder layer (the batched training step only evaluates its [CLS] row)."""
+        cfg = self.config
+        Lv, N = cfg.max_v_len, input_ids.shape[0]
+        plan = self.make_plan_raw([1] * N, [0] * N, [0] * N, [{} for _ in range(N)], video_features.device)
+        vid_ids = input_ids[:, :Lv].reshape(-1).to(torch.int32)
+        vid_mask = input_masks[:, :Lv].reshape(-1).to(torch.float32).contiguous()
+        x = self._video_embed([video_features.contiguous()], plan, vid_ids)
+        for l in range(cfg.num_hidden_layers):
+            x = self._encoder_layer(x, f"encoder.layer.{l}", plan.enc_lay, vid_mask)
+        return x.reshape(N, Lv, -1)
+
+    def pointer_generator_network(self, decoder_outputs, ingredient_vectors, ingr_id_dict, extra_zero):
+        """Reference model.py:896-923 for ONE video: (S, Lt, D), (S, Ni, D), {ingredient: [token ids]}, n_oov ->
+        (S, Lt, V + n_oov) probabilities."""
+        cfg = self.config
+        S, Lt, D = decoder_outputs.shape
+        Ni = ingredient_vectors.shape[1]
+        plan = self.make_plan_raw([S], [Ni], [extra_zero], [ingr_id_dict], decoder_outputs.device)
+        dec = decoder_outputs.reshape(S * Lt, D).to(self.compute_dtype)
+        Esrc = ingredient_vectors.reshape(S * Ni, D).float().contiguous()
+        P = self._pointer(dec, Esrc, plan, plan.t["clip_ent_off"],
+                          torch.full((S * Lt,), IGNORE, dtype=torch.int32, device=dec.device), Lt)[0]
+        return P.view(S, Lt, plan.vx[0])
+
+    def _pointer(self, dec, Esrc, plan, clip_src_off, labels, Lt, clip_P_off=None, P_numel=None, G=None):
+        cfg = self.config
+        if G is None:
+            G = self._lin(Esrc, "Wing", out_dtype=torch.float32)
+        logits = self._lm_logits(dec)
+        lay = dict(Lt=Lt, V=cfg.vocab_size, smoothing=float(cfg.label_smoothing), max_ni=plan.max_ni,
+                   clip_src_off=clip_src_off, clip_ni=plan.t["clip_ni"], clip_gi=plan.t["clip_gi"],
+                   clip_vx=plan.t["clip_vx"], clip_P_off=plan.t["clip_P_off"] if clip_P_off is None else clip_P_off,
+                   P_numel=plan.P_numel if P_numel is None else P_numel, tok_ptr=plan.t["tok_ptr"],
+                   tok_ids=plan.t["tok_ids"], labels=labels, max_vx=max(plan.vx))
+        return Fn.PointerFn.apply(dec, G, Esrc, self.p("pgen_linear.0.weight").reshape(-1), self.p("pgen_linear.0.bias"),
+                                  logits, lay)
+
     def plan_signature(self, batch_step_num, ingr_id_dict, extra_zeros):
         """Host-only: the StepPlan.signature() a batch would have (what a captured graph of the step depends on)."""
         V = self.config.vocab_size
@@ -481,6 +527,3 @@ class StateAwareRecursiveTransformer(nn.Module):
             return mems, ents, acts
         return total, preds, ents, acts
 
-
-def _make_node(owner, path, name):
-    return _Node(owner)

@@ -1,0 +1,109 @@
+"""Greedy decoding on the CUDA library: (a) the batched KV-cached decoder (svpc_b200.decode) and (b) the reference
+translator's piecewise sub-module calls (a line-for-line restatement of src/translator.py:50-163 lives in this test,
+because /root/reference does not travel to the GPU box) must both reproduce the golden captions of the reference
+Translator token for token on the fp32 path."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from svpc_b200 import backend  # noqa: E402
+from svpc_b200.config import BOS, UNK  # noqa: E402
+from svpc_b200.decode import greedy_decode  # noqa: E402
+from svpc_b200.model import StateAwareRecursiveTransformer  # noqa: E402
+from tests.helpers import MODES, GREEDY_SHARPEN, load_case  # noqa: E402
+from tests.test_decode_host import decode_inputs  # noqa: E402
+
+DEV = torch.device("cuda")
+
+
+@pytest.fixture(autouse=True)
+def _cuda_backend():
+    backend.set_backend(None)
+    yield
+    backend.set_backend(None)
+
+
+def build(mode, dtype=torch.float32):
+    cfg, sd, batch, gold = load_case("ragged", mode)
+    sd = {k: v.clone() for k, v in sd.items()}
+    sd["decoder_classifier.decoder.weight"] *= GREEDY_SHARPEN
+    m = StateAwareRecursiveTransformer(cfg, compute_dtype=dtype)
+    m.load_state_dict(sd)
+    return cfg, m.to(DEV).eval(), batch, gold
+
+
+@pytest.mark.parametrize("mode", MODES)
+def test_batched_greedy_decode_token_identical(mode):
+    cfg, m, batch, gold = build(mode)
+    seqs = greedy_decode(m, decode_inputs(batch, DEV))
+    for b, s in enumerate(seqs):
+        assert torch.equal(s.cpu(), torch.from_numpy(gold[f"greedy.{b}"])), (mode, b)
+
+
+def translator_style_decode(model, mi):
+    """src/translator.py:50-163 and 175-191, restated: one video at a time, full decoder re-run per position."""
+    (ids_l, feats_l, masks_l, _tt, ingr_ids, _im, ingr_sep, dicts, oovs, _al, _ac, steps) = mi
+    cfg = model.config
+    Lv, Lt, mode = cfg.max_v_len, cfg.max_t_len, cfg.model_mode
+    out = []
+    with torch.no_grad():
+        for b, S in enumerate(steps):
+            ids = torch.stack([x[b] for x in ids_l[:S]]).clone()
+            feats = torch.stack([x[b] for x in feats_l[:S]])
+            masks = torch.stack([x[b] for x in masks_l[:S]]).clone()
+            ids[:, Lv:] = 0
+            masks[:, Lv:] = 0
+            iid = torch.tensor(ingr_ids[b], dtype=torch.long, device=DEV)
+            sep = torch.tensor(ingr_sep[b], dtype=torch.long, device=DEV)
+            E0 = model.ingredient_embeddings(iid.unsqueeze(0), sep.unsqueeze(0)).squeeze(0)
+            enc = model.forward_step(ids, feats, masks)
+            enc = model.step_positional_encoding(enc[:, 0, :].unsqueeze(0))
+            step = model.step_wise_encoder(enc, torch.ones(1, S, device=DEV))[-1].squeeze(0)
+            text_ids, ext_ids, text_masks = ids[:, Lv:], ids[:, Lv:].clone(), masks[:, Lv:]
+            nxt = torch.full((S,), BOS, dtype=torch.long, device=DEV)
+            nxt_ext = nxt.clone()
+            if mode in ("full", "reason_copy"):
+                _, _, ent_v, E_stack, act_v = model.reasoner(step.unsqueeze(0), E0)
+                ga = torch.cat([step.unsqueeze(1), model.Went(ent_v).unsqueeze(1), model.Wac(act_v).unsqueeze(1)], dim=1)
+                src = E_stack
+            elif mode == "copy":
+                ga = torch.cat([step.unsqueeze(1), E0.mean(dim=0)[None, None].repeat(S, 1, 1)], dim=1)
+                src = E0.clone().unsqueeze(0).repeat(S, 1, 1)
+            else:
+                ga, src = step.unsqueeze(1), None
+            ga_mask = torch.ones(ga.shape[0], ga.shape[1], device=DEV)
+            for d in range(Lt):
+                text_ids[:, d] = nxt
+                ext_ids[:, d] = nxt_ext
+                text_masks[:, d] = 1
+                dec = model.decoder(model.text_embeddings(text_ids), text_masks, ga, ga_mask, diagonal_mask=True)[-1]
+                if mode == "video":
+                    scores = model.decoder_classifier(dec)
+                else:
+                    scores = model.pointer_generator_network(dec, src, dicts[b], len(oovs[b]))
+                scores[:, :, UNK] = -1e10
+                w = scores[:, d].max(1)[1]
+                nxt_ext = w.detach().clone()
+                if mode != "video":
+                    w[w >= scores.shape[-1] - len(oovs[b])] = UNK
+                nxt = w
+            out.append(ext_ids if mode != "video" else text_ids)
+    return out
+
+
+@pytest.mark.parametrize("mode", MODES)
+def test_translator_submodule_calls_token_identical(mode):
+    cfg, m, batch, gold = build(mode)
+    seqs = translator_style_decode(m, decode_inputs(batch, DEV))
+    for b, s in enumerate(seqs):
+        assert torch.equal(s.cpu(), torch.from_numpy(gold[f"greedy.{b}"])), (mode, b)
+
+
+def test_bf16_decode_runs_and_agrees_mostly():
+    cfg, m, batch, gold = build("full", torch.bfloat16)
+    seqs = greedy_decode(m, decode_inputs(batch, DEV))
+    same = sum(int((s.cpu() == torch.from_numpy(gold[f"greedy.{b}"])).sum()) for b, s in enumerate(seqs))
+    tot = sum(s.numel() for s in seqs)
+    assert all(int(s.min()) >= 0 for s in seqs)
+    assert same >= 0.8 * tot, (same, tot)      # bf16 promises no token identity (north_star), only a sane decode

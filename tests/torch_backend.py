@@ -412,3 +412,17 @@ class TorchBackend:
 
     def sum_all(self, x):
         return self.f(x).sum().float()
+
+    # ---------------------------------------------------------------- greedy decoding
+    def greedy_pick(self, scores, row_off, ld, row_width, width, row_noov, unk, next_in, ext_out, pos):
+        flat = scores.reshape(-1)
+        for r in range(next_in.numel()):
+            o = int(row_off[r]) if row_off is not None else r * int(ld)
+            w = int(row_width[r]) if row_width is not None else int(width)
+            s = flat[o:o + w].clone().float()
+            s[unk] = -1e10
+            bi = int(torch.argmax(s))
+            bi = int((s == s[bi]).nonzero()[0])          # lowest index among ties
+            noov = int(row_noov[r]) if row_noov is not None else 0
+            ext_out[r, pos] = bi
+            next_in[r] = unk if bi >= w - noov else bi
