@@ -30,7 +30,7 @@ def _as_long_tensor(x, device):
 
 
 @torch.no_grad()
-def greedy_decode(model, model_inputs):
+def greedy_decode(model, model_inputs, plan=None):
     """``model_inputs``: the 12-tuple ``Translator.translate_batch`` takes (translate.py:57-70):
     (input_ids_list, video_features_list, input_masks_list, token_type_ids_list, ingr_input_ids, ingr_masks,
     ingr_sep_masks, ingr_id_dict, oov_word_dict, alignments, actions, batch_step_num)."""
@@ -50,7 +50,8 @@ def greedy_decode(model, model_inputs):
         ni = [len(d) for d in ingr_id_dict]
         n_oov = [len(d) for d in oov_word_dict]
         dicts = ingr_id_dict
-    plan = model.make_plan_raw(steps, ni, n_oov, dicts, dev)
+    if plan is None:
+        plan = model.make_plan_raw(steps, ni, n_oov, dicts, dev)
     Nc = plan.Nc
 
     # ---- encode every clip, build the decoder context (same stages as the training step)

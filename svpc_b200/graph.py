@@ -102,3 +102,72 @@ class GraphedTrainStep:
     def run(self):
         self.graph.replay()
         return self.loss
+
+
+class GraphedDecoder:
+    """CUDA-graph replay of ``svpc_b200.decode.greedy_decode`` for one batch signature (clips / ingredients / OOV words
+    per video): the ~700 launches of a 25-position decode become one graph launch.
+
+        dec = GraphedDecoder(model, example_inputs)      # warm-up + capture
+        dec.load(inputs)                                 # copy a batch (pinned host or device tensors) into the static buffers
+        seqs = dec.run()                                 # list of (S_b, max_t_len) int64 extended ids (views of a static buffer)
+    """
+
+    TENSOR_LISTS = (0, 1, 2, 3)      # input_ids_list, video_features_list, input_masks_list, token_type_ids_list
+    TENSORS = (4, 5, 6)              # ingr_input_ids, ingr_masks, ingr_sep_masks (lists of lists in translate.py:57-70)
+
+    def __init__(self, model, example_inputs, warmup: int = 2):
+        from .decode import greedy_decode
+        self._decode = greedy_decode
+        self.model = model
+        dev = next(model.parameters()).device
+        assert dev.type == "cuda", "GraphedDecoder needs a CUDA model"
+        self.device = dev
+        st = list(example_inputs)
+        for i in self.TENSOR_LISTS:
+            st[i] = [t.to(dev).clone() for t in st[i]]
+        for i in self.TENSORS:
+            st[i] = torch.as_tensor(st[i]).to(device=dev, dtype=torch.long).clone()
+        self.static = st
+        mode = model.config.model_mode
+        steps = [int(x) for x in st[11]]
+        B = len(steps)
+        if mode == "video":
+            ni, n_oov, dicts = [0] * B, [0] * B, [{} for _ in range(B)]
+        else:
+            ni, n_oov, dicts = [len(d) for d in st[7]], [len(d) for d in st[8]], st[7]
+        self.plan = model.make_plan_raw(steps, ni, n_oov, dicts, dev)
+        self.sig = (tuple(steps), tuple(ni), tuple(n_oov))
+        self.graph = torch.cuda.CUDAGraph()
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side), torch.no_grad():
+            for _ in range(max(1, warmup)):
+                self._decode(model, tuple(self.static), plan=self.plan)
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        with torch.no_grad(), torch.cuda.graph(self.graph):
+            self.out = self._decode(model, tuple(self.static), plan=self.plan)
+        torch.cuda.synchronize(dev)
+
+    def matches(self, inputs):
+        mode = self.model.config.model_mode
+        steps = tuple(int(x) for x in inputs[11])
+        if mode == "video":
+            return steps == self.sig[0]
+        return (steps, tuple(len(d) for d in inputs[7]), tuple(len(d) for d in inputs[8])) == self.sig
+
+    def load(self, inputs):
+        for i in self.TENSOR_LISTS:
+            for d, s in zip(self.static[i], inputs[i]):
+                d.copy_(s, non_blocking=True)
+        for i in self.TENSORS:
+            self.static[i].copy_(torch.as_tensor(inputs[i]), non_blocking=True)
+        if inputs[7] is not self.static[7] and self.plan.mode != "video" and self.model.config.model_mode != "video":
+            if not self.plan.update_tokens(inputs[7]):
+                raise ValueError("ingr_id_dict has a different number of copy tokens than the captured batch: re-capture")
+            self.static[7] = inputs[7]
+
+    def run(self):
+        self.graph.replay()
+        return self.out

@@ -107,3 +107,18 @@ def test_bf16_decode_runs_and_agrees_mostly():
     tot = sum(s.numel() for s in seqs)
     assert all(int(s.min()) >= 0 for s in seqs)
     assert same >= 0.8 * tot, (same, tot)      # bf16 promises no token identity (north_star), only a sane decode
+
+
+@pytest.mark.parametrize("mode", ("video", "full"))
+def test_graphed_decoder_matches_eager(mode):
+    from svpc_b200.graph import GraphedDecoder
+    cfg, m, batch, gold = build(mode)
+    inputs = decode_inputs(batch, DEV)
+    dec = GraphedDecoder(m, inputs)
+    assert dec.matches(inputs)
+    dec.load(decode_inputs(batch))            # host tensors -> static buffers
+    for _ in range(2):
+        seqs = dec.run()
+    torch.cuda.synchronize()
+    for b, s in enumerate(seqs):
+        assert torch.equal(s.cpu(), torch.from_numpy(gold[f"greedy.{b}"])), (mode, b)
