@@ -48,8 +48,16 @@ int svpc_gemm_route(int M, int N, int K, int dtA, long long sa_m, long long sa_k
 long long svpc_launch_count(void);
 void svpc_reset_launch_count(void);
 
-/* D[M,N] = act(A[M,K] . B[N,K]^T + bias[N]) + residual[M,N]  (+ D when accumulate); optional copy of the
- * pre-activation.  A and B are addressed by element strides (one of each pair must be 1).  Replaces every
+/* Train-mode dropout (nn.Dropout, model.py:214, 231, 287, 495, 522, 550, 757) is a counter-based mask that every kernel
+ * recomputes instead of storing: keep(seed, site, element index), kept elements scaled by 1 / (1 - p).  `drop_seed` is a
+ * DEVICE pointer to the step seed (bumped by the caller once per forward, so a captured CUDA graph draws fresh masks on
+ * every replay); `drop_site` distinguishes the call sites of one step; drop_p == 0 or a NULL seed disables it.
+ * svpc_dropout_mask writes the scale (0 or 1/(1-p)) of elements [0, n) - used by the tests to state the contract. */
+int svpc_dropout_mask(long long n, const unsigned int* drop_seed, unsigned int drop_site, float drop_p, float* out,
+                      svpc_stream_t stream);
+
+/* D[M,N] = drop(act(A[M,K] . B[N,K]^T + bias[N])) + residual[M,N]  (+ D when accumulate); optional copy of the
+ * pre-activation.  Dropout element index = m * N + n.  A and B are addressed by element strides (one of each pair must be 1).  Replaces every
  * nn.Linear / matmul on the path: model.py:195-197,230,263,286,496,551,706-708,738,797-811,899,939-940 and their
  * autograd dgrad / wgrad. */
 int svpc_gemm(int M, int N, int K,
@@ -59,11 +67,13 @@ int svpc_gemm(int M, int N, int K,
               const float* bias, int act,
               const void* residual, long long ldr,
               void* pre, long long ldp,
-              int accumulate, int route, svpc_stream_t stream);
+              int accumulate, int route,
+              const unsigned int* drop_seed, unsigned int drop_site, float drop_p, svpc_stream_t stream);
 
-/* dz = dy * act'(ref), dbias[c] = sum_r dz[r,c].  ref = output for RELU/SIGMOID, pre-activation for GELU. */
+/* dz = dy * dropscale(r * cols + c) * act'(ref), dbias[c] = sum_r dz[r,c].  ref = output for RELU/SIGMOID,
+ * pre-activation for GELU. */
 int svpc_act_bwd(int rows, int cols, const void* dy, const void* ref, int dt, int act, void* dz, float* dbias,
-                 svpc_stream_t stream);
+                 const unsigned int* drop_seed, unsigned int drop_site, float drop_p, svpc_stream_t stream);
 int svpc_colsum(int rows, int cols, const void* x, int dt, float* out, svpc_stream_t stream);
 int svpc_cast(long long n, const void* src, int dts, void* dst, int dtd, svpc_stream_t stream);
 int svpc_cast2d(int rows, int cols, const void* src, int dts, long long lds, void* dst, int dtd, long long ldd,
@@ -84,26 +94,37 @@ int svpc_index_colsum(int rows, int D, const void* dy, int dt, const int* ids, i
 /* Embedding gather + LN(W) (model.py:492-494 / 519-521) and its backward (scatter-add into the table).  ldy: row
  * pitch of y in elements (>= W; padded to 16 bytes so that y is a TMA-addressable GEMM operand). */
 int svpc_embed_ln_fwd(int rows, int W, const float* table, const int* ids, const float* gamma, const float* beta,
-                      float eps, void* y, long long ldy, int dt, float* mean, float* rstd, svpc_stream_t stream);
+                      float eps, void* y, long long ldy, int dt, float* mean, float* rstd,
+                      const unsigned int* drop_seed, unsigned int drop_site, float drop_p, svpc_stream_t stream);
 int svpc_embed_ln_bwd(int rows, int W, int V, const void* dy, int dt, const float* table, const int* ids,
                       const float* mean, const float* rstd, const float* gamma, int padding_idx, float* dtable,
-                      float* dgamma, float* dbeta, svpc_stream_t stream);
+                      float* dgamma, float* dbeta, const unsigned int* drop_seed, unsigned int drop_site, float drop_p,
+                      svpc_stream_t stream);
 
 /* Gathers the first Lv rows of clip (t,b) = (clip_t[n], clip_b[n]) from the S per-step feature tensors
  * (B, L, F) fp32 and writes (x - mean) * rstd (LN(3072) without affine, model.py:549). */
 int svpc_video_ln_pack(int n_clips, int B, int L, int Lv, int F, const long long* feat_ptrs, const int* clip_t,
-                       const int* clip_b, float eps, void* xhat, int dt, float* mean, float* rstd,
+                       const int* clip_b, float eps, void* xhat, int dt, float* mean, float* rstd, const float* gamma,
+                       const float* beta, const unsigned int* drop_seed, unsigned int drop_site, float drop_p,
                        svpc_stream_t stream);
+/* train mode (gamma / beta given): xhat <- drop(xhat * gamma + beta), element index row * F + c (model.py:549-550); its
+ * backward towards gamma / beta (the features are inputs), xhat recomputed from the features and the statistics */
+int svpc_video_ln_affine_bwd(int n_clips, int B, int L, int Lv, int F, const long long* feat_ptrs, const int* clip_t,
+                             const int* clip_b, const float* mean, const float* rstd, const void* dy, int dt,
+                             float* dgamma, float* dbeta, const unsigned int* drop_seed, unsigned int drop_site,
+                             float drop_p, svpc_stream_t stream);
 
-/* BertSelfAttention core (model.py:204-216) over ragged short sequences; one CTA per (sequence, head). */
+/* BertSelfAttention core (model.py:204-216) over ragged short sequences; one CTA per (sequence, head).  Dropout on the
+ * probabilities (model.py:214): element index ((seq * H + head) * max_lq + i) * max_lk + j. */
 int svpc_attn_fwd(int n_seq, int H, int dh, const void* q, long long ldq, const void* k, long long ldk, const void* v,
                   long long ldv, int dt, const int* q_off, const int* q_len, const int* k_off, const int* k_len,
                   const float* key_mask, int causal, int max_lq, int max_lk, void* ctx, long long ldo,
-                  svpc_stream_t stream);
+                  const unsigned int* drop_seed, unsigned int drop_site, float drop_p, svpc_stream_t stream);
 int svpc_attn_bwd(int n_seq, int H, int dh, const void* q, long long ldq, const void* k, long long ldk, const void* v,
                   long long ldv, int dt, const int* q_off, const int* q_len, const int* k_off, const int* k_len,
                   const float* key_mask, int causal, int max_lq, int max_lk, const void* dctx, long long lddo, void* dq,
-                  long long lddq, void* dk, long long lddk, void* dv, long long lddv, svpc_stream_t stream);
+                  long long lddq, void* dk, long long lddk, void* dv, long long lddv, const unsigned int* drop_seed,
+                  unsigned int drop_site, float drop_p, svpc_stream_t stream);
 
 /* IngredientPositionEncoding (model.py:116-140): segment means between [SEP]s + pe[j]. */
 int svpc_segmean_fwd(int B, int Li, int D, int NI, const void* x, int dt, const int* sep_mask, const int* cu_ingr,

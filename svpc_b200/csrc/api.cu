@@ -68,6 +68,23 @@ extern "C" int svpc_cast2d(int rows, int cols, const void* src, int dts, long lo
   return svpc_check_launch("cast2d");
 }
 
+__global__ void dropout_mask_kernel(long long n, const SvpcDrop drop, float* __restrict__ out) {
+  const bool dropping = drop.seed != nullptr && drop.p > 0.f;
+  const uint32_t key = svpc_drop_key(drop);
+  const float inv = dropping ? 1.f / (1.f - drop.p) : 1.f;
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  for (; i < n; i += (long long)gridDim.x * blockDim.x)
+    out[i] = dropping ? svpc_drop_scale(key, drop.p, inv, (unsigned long long)i) : 1.f;
+}
+
+extern "C" int svpc_dropout_mask(long long n, const unsigned int* drop_seed, unsigned int drop_site, float drop_p, float* out,
+                                 svpc_stream_t stream) {
+  if (n <= 0) return SVPC_OK;
+  const SvpcDrop drop{drop_p > 0.f ? drop_seed : nullptr, drop_site, drop_p};
+  dropout_mask_kernel<<<svpc_imin(svpc_cdiv(n, 256), SVPC_NUM_SMS * 16), 256, 0, (cudaStream_t)stream>>>(n, drop, out);
+  return svpc_check_launch("dropout_mask");
+}
+
 // deterministic single-CTA sum (loss reductions: a few thousand elements)
 __global__ void sum_kernel(long long n, const float* __restrict__ x, float* __restrict__ out) {
   __shared__ float red[64];

@@ -52,7 +52,8 @@ __global__ void __launch_bounds__(AT_THREADS) attn_fwd_kernel(int H, int dh, con
                                                               const int* __restrict__ q_off, const int* __restrict__ q_len,
                                                               const int* __restrict__ k_off, const int* __restrict__ k_len,
                                                               const float* __restrict__ key_mask, int causal, int max_lq,
-                                                              int max_lk, T* __restrict__ ctx, long long ldo) {
+                                                              int max_lk, T* __restrict__ ctx, long long ldo,
+                                                              const SvpcDrop drop) {
   extern __shared__ float sm[];
   const int n = blockIdx.x / H, h = blockIdx.x - n * H;
   const int lq = q_len[n], lk = k_len[n], qo = q_off[n], ko = k_off[n];
@@ -69,6 +70,16 @@ __global__ void __launch_bounds__(AT_THREADS) attn_fwd_kernel(int H, int dh, con
     for (int j = threadIdx.x; j < lk; j += AT_THREADS) km[j] = key_mask[ko + j];
   __syncthreads();
   at_scores_softmax(S, Q, K, lq, lk, dh, pitch, rsqrtf((float)dh), key_mask ? km : nullptr, causal);
+  if (drop.seed != nullptr && drop.p > 0.f) {          // dropout on the probabilities (model.py:214)
+    const uint32_t dkey = svpc_drop_key(drop);
+    const float dinv = 1.f / (1.f - drop.p);
+    const unsigned long long base = (unsigned long long)blockIdx.x * max_lq;
+    for (int idx = threadIdx.x; idx < lq * lk; idx += AT_THREADS) {
+      const int i = idx / lk, j = idx - i * lk;
+      S[idx] *= svpc_drop_scale(dkey, drop.p, dinv, (base + i) * max_lk + j);
+    }
+    __syncthreads();
+  }
   for (int idx = threadIdx.x; idx < lq * dh; idx += AT_THREADS) {
     const int i = idx / dh, d = idx - i * dh;
     const float* p = S + i * lk;
@@ -87,8 +98,13 @@ __global__ void __launch_bounds__(AT_THREADS) attn_bwd_kernel(int H, int dh, con
                                                               const float* __restrict__ key_mask, int causal, int max_lq,
                                                               int max_lk, const T* __restrict__ dctx, long long lddo,
                                                               T* __restrict__ dq, long long lddq, T* __restrict__ dk,
-                                                              long long lddk, T* __restrict__ dv, long long lddv) {
+                                                              long long lddk, T* __restrict__ dv, long long lddv,
+                                                              const SvpcDrop drop) {
   extern __shared__ float sm[];
+  const bool dropping = drop.seed != nullptr && drop.p > 0.f;
+  const uint32_t dkey = svpc_drop_key(drop);
+  const float dinv = dropping ? 1.f / (1.f - drop.p) : 1.f;
+  const unsigned long long dbase = (unsigned long long)blockIdx.x * max_lq;
   const int n = blockIdx.x / H, h = blockIdx.x - n * H;
   const int lq = q_len[n], lk = k_len[n], qo = q_off[n], ko = k_off[n];
   const int pitch = dh + 1;
@@ -112,7 +128,11 @@ __global__ void __launch_bounds__(AT_THREADS) attn_bwd_kernel(int H, int dh, con
   for (int idx = threadIdx.x; idx < lk * dh; idx += AT_THREADS) {
     const int j = idx / dh, d = idx - j * dh;
     float a = 0.f;
-    for (int i = 0; i < lq; ++i) a = fmaf(P[i * lk + j], dO[i * pitch + d], a);
+    for (int i = 0; i < lq; ++i) {
+      float pij = P[i * lk + j];
+      if (dropping) pij *= svpc_drop_scale(dkey, drop.p, dinv, (dbase + i) * max_lk + j);
+      a = fmaf(pij, dO[i * pitch + d], a);
+    }
     stf(dv + (long long)(ko + j) * lddv + h * dh + d, a);
   }
   // dP[i][j] = dO_i . V_j
@@ -122,6 +142,7 @@ __global__ void __launch_bounds__(AT_THREADS) attn_bwd_kernel(int H, int dh, con
     const float* b = V + j * pitch;
     float s = 0.f;
     for (int d = 0; d < dh; ++d) s = fmaf(a[d], b[d], s);
+    if (dropping) s *= svpc_drop_scale(dkey, drop.p, dinv, (dbase + i) * max_lk + j);
     dS[idx] = s;
   }
   __syncthreads();
@@ -164,27 +185,30 @@ int svpc_attn_tc_eligible(int dh, int dt, int max_lq, int max_lk, long long ldq,
                           const void* q, const void* k, const void* v, const void* o);
 int svpc_attn_tc_fwd(int n_seq, int H, const void* q, long long ldq, const void* k, long long ldk, const void* v,
                      long long ldv, const int* q_off, const int* q_len, const int* k_off, const int* k_len,
-                     const float* key_mask, int causal, int max_lq, int max_lk, void* ctx, long long ldo, cudaStream_t st);
+                     const float* key_mask, int causal, int max_lq, int max_lk, void* ctx, long long ldo, SvpcDrop drop,
+                     cudaStream_t st);
 int svpc_attn_tc_bwd(int n_seq, int H, const void* q, long long ldq, const void* k, long long ldk, const void* v,
                      long long ldv, const int* q_off, const int* q_len, const int* k_off, const int* k_len,
                      const float* key_mask, int causal, int max_lq, int max_lk, const void* dctx, long long lddo, void* dq,
-                     long long lddq, void* dk, long long lddk, void* dv, long long lddv, cudaStream_t st);
+                     long long lddq, void* dk, long long lddk, void* dv, long long lddv, SvpcDrop drop, cudaStream_t st);
 
 extern "C" int svpc_attn_fwd(int n_seq, int H, int dh, const void* q, long long ldq, const void* k, long long ldk,
                              const void* v, long long ldv, int dt, const int* q_off, const int* q_len, const int* k_off,
                              const int* k_len, const float* key_mask, int causal, int max_lq, int max_lk, void* ctx,
-                             long long ldo, svpc_stream_t stream) {
+                             long long ldo, const unsigned int* drop_seed, unsigned int drop_site, float drop_p,
+                             svpc_stream_t stream) {
   if (n_seq <= 0) return SVPC_OK;
+  const SvpcDrop drop{drop_p > 0.f ? drop_seed : nullptr, drop_site, drop_p};
   if (svpc_attn_tc_eligible(dh, dt, max_lq, max_lk, ldq, ldk, ldv, ldo, q, k, v, ctx))
     return svpc_attn_tc_fwd(n_seq, H, q, ldq, k, ldk, v, ldv, q_off, q_len, k_off, k_len, key_mask, causal, max_lq, max_lk,
-                            ctx, ldo, (cudaStream_t)stream);
+                            ctx, ldo, drop, (cudaStream_t)stream);
   const size_t smem = at_smem_fwd(max_lq, max_lk, dh);
   SVPC_REQUIRE(smem <= 227 * 1024, "attn_fwd: sequence too long for the short-sequence kernel (lq=%d lk=%d)", max_lq, max_lk);
   cudaStream_t st = (cudaStream_t)stream;
   SVPC_DISPATCH(dt, T, {
     cudaFuncSetAttribute(attn_fwd_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     attn_fwd_kernel<T><<<n_seq * H, AT_THREADS, smem, st>>>(H, dh, (const T*)q, ldq, (const T*)k, ldk, (const T*)v, ldv, q_off,
-                                                            q_len, k_off, k_len, key_mask, causal, max_lq, max_lk, (T*)ctx, ldo);
+                                                            q_len, k_off, k_len, key_mask, causal, max_lq, max_lk, (T*)ctx, ldo, drop);
   });
   return svpc_check_launch("attn_fwd");
 }
@@ -193,12 +217,13 @@ extern "C" int svpc_attn_bwd(int n_seq, int H, int dh, const void* q, long long 
                              const void* v, long long ldv, int dt, const int* q_off, const int* q_len, const int* k_off,
                              const int* k_len, const float* key_mask, int causal, int max_lq, int max_lk, const void* dctx,
                              long long lddo, void* dq, long long lddq, void* dk, long long lddk, void* dv, long long lddv,
-                             svpc_stream_t stream) {
+                             const unsigned int* drop_seed, unsigned int drop_site, float drop_p, svpc_stream_t stream) {
   if (n_seq <= 0) return SVPC_OK;
+  const SvpcDrop drop{drop_p > 0.f ? drop_seed : nullptr, drop_site, drop_p};
   if (svpc_attn_tc_eligible(dh, dt, max_lq, max_lk, ldq, ldk, ldv, lddo, q, k, v, dctx) && (lddq | lddk | lddv) % 2 == 0 &&
       (((uintptr_t)dq | (uintptr_t)dk | (uintptr_t)dv) & 3) == 0 && lddo % 8 == 0 && ((uintptr_t)dctx & 15) == 0)
     return svpc_attn_tc_bwd(n_seq, H, q, ldq, k, ldk, v, ldv, q_off, q_len, k_off, k_len, key_mask, causal, max_lq, max_lk,
-                            dctx, lddo, dq, lddq, dk, lddk, dv, lddv, (cudaStream_t)stream);
+                            dctx, lddo, dq, lddq, dk, lddk, dv, lddv, drop, (cudaStream_t)stream);
   const size_t smem = at_smem_bwd(max_lq, max_lk, dh);
   SVPC_REQUIRE(smem <= 227 * 1024, "attn_bwd: sequence too long for the short-sequence kernel (lq=%d lk=%d)", max_lq, max_lk);
   cudaStream_t st = (cudaStream_t)stream;
@@ -206,7 +231,7 @@ extern "C" int svpc_attn_bwd(int n_seq, int H, int dh, const void* q, long long 
     cudaFuncSetAttribute(attn_bwd_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     attn_bwd_kernel<T><<<n_seq * H, AT_THREADS, smem, st>>>(H, dh, (const T*)q, ldq, (const T*)k, ldk, (const T*)v, ldv, q_off,
                                                             q_len, k_off, k_len, key_mask, causal, max_lq, max_lk,
-                                                            (const T*)dctx, lddo, (T*)dq, lddq, (T*)dk, lddk, (T*)dv, lddv);
+                                                            (const T*)dctx, lddo, (T*)dq, lddq, (T*)dk, lddk, (T*)dv, lddv, drop);
   });
   return svpc_check_launch("attn_bwd");
 }

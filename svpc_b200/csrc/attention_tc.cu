@@ -124,6 +124,40 @@ __device__ __forceinline__ void atc_softmax(float (&s)[NT][4], int i0, int lk, i
   }
 }
 
+// dropout scale (0 or 1/(1-p), or 0/1 when inv == 1) of the thread's elements of tile nt: element index
+// ((seq * H + head) * max_lq + i) * max_lk + j, the same in the forward, the backward and the FFMA kernel
+struct AtcDrop {
+  bool on;
+  uint32_t key;
+  float p, inv;
+  unsigned long long base;     // (seq * H + head) * max_lq
+  int max_lk;
+  __device__ __forceinline__ float scale(int i, int j) const {
+    return on ? svpc_drop_scale(key, p, inv, (base + (unsigned long long)i) * max_lk + j) : 1.f;
+  }
+};
+__device__ __forceinline__ AtcDrop atc_make_drop(const SvpcDrop& d, int seq_head, int max_lq, int max_lk) {
+  AtcDrop a;
+  a.on = d.seed != nullptr && d.p > 0.f;
+  a.key = svpc_drop_key(d);
+  a.p = d.p;
+  a.inv = a.on ? 1.f / (1.f - d.p) : 1.f;
+  a.base = (unsigned long long)seq_head * max_lq;
+  a.max_lk = max_lk;
+  return a;
+}
+template <int NT>
+__device__ __forceinline__ void atc_apply_drop(float (&s)[NT][4], const AtcDrop& dr, int i0, int lk_pad, int lane) {
+  if (!dr.on) return;
+  const int t2 = (lane & 3) * 2;
+#pragma unroll
+  for (int nt = 0; nt < NT; ++nt)
+    if (nt * 8 < lk_pad) {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) s[nt][e] *= dr.scale(i0 + (e >> 1) * 8, nt * 8 + t2 + (e & 1));
+    }
+}
+
 // acc[dt] (16 x 8 tile over the head dim) += A(16 x k_pad, bf16 pairs taken from fp32 tiles p[NT][4]) . B, B row-major
 // [k][64] in smem (V in P.V, K in dS.K)
 template <int NT>
@@ -164,7 +198,8 @@ struct AtcParams {
   long long ldq, ldk, ldv;
   const int *q_off, *q_len, *k_off, *k_len;
   const float* key_mask;
-  int causal, lq_pad, lk_pad;
+  int causal, lq_pad, lk_pad, max_lq, max_lk;
+  SvpcDrop drop;                 // dropout on the attention probabilities (model.py:214)
   bf16* ctx; long long ldo;
   const bf16* dctx; long long lddo;
   bf16 *dq, *dk, *dv;
@@ -196,6 +231,8 @@ __global__ void __launch_bounds__(256) attn_tc_fwd_kernel(const AtcParams p) {
   atc_mma_abt<NT>(s, qf, sK, p.lk_pad, lane);
   float inv[2];
   atc_softmax<NT>(s, r0 + (lane >> 2), lk, p.lk_pad, madd, p.causal, 0.125f, lane, false, inv);
+  const AtcDrop dr = atc_make_drop(p.drop, blockIdx.x, p.max_lq, p.max_lk);
+  atc_apply_drop<NT>(s, dr, r0 + (lane >> 2), p.lk_pad, lane);     // scale 1/(1-p) rides on the kept probabilities
   float o[8][4];
 #pragma unroll
   for (int dt = 0; dt < 8; ++dt) o[dt][0] = o[dt][1] = o[dt][2] = o[dt][3] = 0.f;
@@ -225,13 +262,19 @@ __device__ __forceinline__ void atc_mma_xtb(float (&acc)[8][4], const bf16* X, i
 }
 
 template <int NT>
-__device__ __forceinline__ void atc_write_x(bf16* X, int xp, const float (&s)[NT][4], int r0, int lk_pad, int lane) {
+__device__ __forceinline__ void atc_write_x(bf16* X, int xp, const float (&s)[NT][4], int r0, int lk_pad, int lane,
+                                            const AtcDrop* dr) {
   const int g = lane >> 2, t2 = (lane & 3) * 2;
 #pragma unroll
   for (int nt = 0; nt < NT; ++nt) {
     if (nt * 8 < lk_pad) {
-      *reinterpret_cast<uint32_t*>(X + (r0 + g) * xp + nt * 8 + t2) = pack_bf16(s[nt][0], s[nt][1]);
-      *reinterpret_cast<uint32_t*>(X + (r0 + g + 8) * xp + nt * 8 + t2) = pack_bf16(s[nt][2], s[nt][3]);
+      float v[4] = {s[nt][0], s[nt][1], s[nt][2], s[nt][3]};
+      if (dr) {
+#pragma unroll
+        for (int e = 0; e < 4; ++e) v[e] *= dr->scale(r0 + g + (e >> 1) * 8, nt * 8 + t2 + (e & 1));
+      }
+      *reinterpret_cast<uint32_t*>(X + (r0 + g) * xp + nt * 8 + t2) = pack_bf16(v[0], v[1]);
+      *reinterpret_cast<uint32_t*>(X + (r0 + g + 8) * xp + nt * 8 + t2) = pack_bf16(v[2], v[3]);
     }
   }
 }
@@ -259,6 +302,8 @@ __global__ void __launch_bounds__(NT <= 14 ? 224 : 256, NT <= 14 ? 2 : 1) attn_t
   const int r0 = warp * 16;
   const bool active = r0 < p.lq_pad;                       // every warp of the CTA owns one padded row block
   const float scale = 0.125f;
+  const AtcDrop dr = atc_make_drop(p.drop, blockIdx.x, p.max_lq, p.max_lk);
+  const int gi = r0 + (lane >> 2), t2 = (lane & 3) * 2;
   float s[NT][4];
   if (active) {
     uint32_t af[4][4];
@@ -266,7 +311,7 @@ __global__ void __launch_bounds__(NT <= 14 ? 224 : 256, NT <= 14 ? 2 : 1) attn_t
     atc_mma_abt<NT>(s, af, sK, p.lk_pad, lane);
     float inv[2];
     atc_softmax<NT>(s, r0 + (lane >> 2), lk, p.lk_pad, madd, p.causal, scale, lane, true, inv);
-    atc_write_x<NT>(sX, xp, s, r0, p.lk_pad, lane);        // P (bf16) for dV
+    atc_write_x<NT>(sX, xp, s, r0, p.lk_pad, lane, dr.on ? &dr : nullptr);   // dropped P (bf16) for dV
     // D_i = sum_j P_ij dP_ij, dP = dO V^T (recomputed below instead of kept: 4*NT registers saved)
     atc_load_a(af, sdO, r0, lane);
     float dsum[2] = {0.f, 0.f};
@@ -276,7 +321,8 @@ __global__ void __launch_bounds__(NT <= 14 ? 224 : 256, NT <= 14 ? 2 : 1) attn_t
         float dp[4];
         atc_tile_abt(dp, af, sV, nt, lane);
 #pragma unroll
-        for (int e = 0; e < 4; ++e) dsum[e >> 1] = fmaf(s[nt][e], dp[e], dsum[e >> 1]);
+        for (int e = 0; e < 4; ++e)
+          dsum[e >> 1] = fmaf(s[nt][e], dp[e] * dr.scale(gi + (e >> 1) * 8, nt * 8 + t2 + (e & 1)), dsum[e >> 1]);
       }
     }
 #pragma unroll
@@ -291,7 +337,8 @@ __global__ void __launch_bounds__(NT <= 14 ? 224 : 256, NT <= 14 ? 2 : 1) attn_t
         float dp[4];
         atc_tile_abt(dp, af, sV, nt, lane);
 #pragma unroll
-        for (int e = 0; e < 4; ++e) s[nt][e] = s[nt][e] * (dp[e] - dsum[e >> 1]) * scale;
+        for (int e = 0; e < 4; ++e)
+          s[nt][e] = s[nt][e] * (dp[e] * dr.scale(gi + (e >> 1) * 8, nt * 8 + t2 + (e & 1)) - dsum[e >> 1]) * scale;
       }
     }
   }
@@ -311,7 +358,7 @@ __global__ void __launch_bounds__(NT <= 14 ? 224 : 256, NT <= 14 ? 2 : 1) attn_t
     atc_store(p.dq + (long long)qo * p.lddq + h * ATC_DH, p.lddq, acc, r0, lq, lane, 1.f, 1.f);
   }
   __syncthreads();                                          // every warp is done reading P
-  if (active) atc_write_x<NT>(sX, xp, s, r0, p.lk_pad, lane);
+  if (active) atc_write_x<NT>(sX, xp, s, r0, p.lk_pad, lane, nullptr);
   __syncthreads();
   // dK[j] = sum_i dS[i][j] Q[i]
   for (int j0 = warp * 16; j0 < p.lk_pad; j0 += nwarps * 16) {
@@ -337,6 +384,7 @@ int svpc_attn_tc_fwd_launch(int n_seq, const AtcParams& p0, int max_lq, int max_
   AtcParams p = p0;
   p.lq_pad = atc_pad16(max_lq);
   p.lk_pad = atc_pad16(max_lk);
+  p.max_lq = max_lq; p.max_lk = max_lk;
   const size_t smem = (size_t)(p.lq_pad + 2 * p.lk_pad) * ATC_PITCH * 2 + (size_t)p.lk_pad * 4;
   const int threads = 32 * (p.lq_pad / 16);
   static bool attr = false;
@@ -355,6 +403,7 @@ int svpc_attn_tc_bwd_launch(int n_seq, const AtcParams& p0, int max_lq, int max_
   AtcParams p = p0;
   p.lq_pad = atc_pad16(max_lq);
   p.lk_pad = atc_pad16(max_lk);
+  p.max_lq = max_lq; p.max_lk = max_lk;
   const size_t smem = (size_t)(2 * p.lq_pad + 2 * p.lk_pad) * ATC_PITCH * 2 + (size_t)p.lq_pad * (p.lk_pad + 8) * 2 +
                       (size_t)p.lk_pad * 4;
   const int threads = 32 * (p.lq_pad / 16);
@@ -374,8 +423,10 @@ int svpc_attn_tc_bwd_launch(int n_seq, const AtcParams& p0, int max_lq, int max_
 // plain-argument entry points used by the dispatch in attention.cu
 int svpc_attn_tc_fwd(int n_seq, int H, const void* q, long long ldq, const void* k, long long ldk, const void* v,
                      long long ldv, const int* q_off, const int* q_len, const int* k_off, const int* k_len,
-                     const float* key_mask, int causal, int max_lq, int max_lk, void* ctx, long long ldo, cudaStream_t st) {
+                     const float* key_mask, int causal, int max_lq, int max_lk, void* ctx, long long ldo, SvpcDrop drop,
+                     cudaStream_t st) {
   AtcParams p{};
+  p.drop = drop;
   p.H = H; p.q = (const bf16*)q; p.k = (const bf16*)k; p.v = (const bf16*)v;
   p.ldq = ldq; p.ldk = ldk; p.ldv = ldv;
   p.q_off = q_off; p.q_len = q_len; p.k_off = k_off; p.k_len = k_len;
@@ -387,8 +438,9 @@ int svpc_attn_tc_fwd(int n_seq, int H, const void* q, long long ldq, const void*
 int svpc_attn_tc_bwd(int n_seq, int H, const void* q, long long ldq, const void* k, long long ldk, const void* v,
                      long long ldv, const int* q_off, const int* q_len, const int* k_off, const int* k_len,
                      const float* key_mask, int causal, int max_lq, int max_lk, const void* dctx, long long lddo, void* dq,
-                     long long lddq, void* dk, long long lddk, void* dv, long long lddv, cudaStream_t st) {
+                     long long lddq, void* dk, long long lddk, void* dv, long long lddv, SvpcDrop drop, cudaStream_t st) {
   AtcParams p{};
+  p.drop = drop;
   p.H = H; p.q = (const bf16*)q; p.k = (const bf16*)k; p.v = (const bf16*)v;
   p.ldq = ldq; p.ldk = ldk; p.ldv = ldv;
   p.q_off = q_off; p.q_len = q_len; p.k_off = k_off; p.k_len = k_len;

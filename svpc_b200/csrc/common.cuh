@@ -57,6 +57,27 @@ __device__ __forceinline__ float svpc_act(float v, int act) {
   }
 }
 
+// ---- dropout (train mode): counter-based mask, recomputed wherever it is needed (forward, backward) instead of stored.
+// keep(seed, site, idx) is a pure function of the step seed (read from device memory so that a captured CUDA graph sees
+// a fresh seed every replay), the call site and the element index; kept elements are scaled by 1 / (1 - p).
+struct SvpcDrop {
+  const unsigned int* seed;   // device pointer, NULL = no dropout
+  unsigned int site;
+  float p;
+};
+__device__ __forceinline__ uint32_t svpc_mix32(uint32_t h) {
+  h ^= h >> 16; h *= 0x85ebca6bu; h ^= h >> 13; h *= 0xc2b2ae35u; h ^= h >> 16;
+  return h;
+}
+__device__ __forceinline__ uint32_t svpc_drop_key(const SvpcDrop& d) {
+  return d.seed ? svpc_mix32(*d.seed * 0x9e3779b9u + d.site * 0x7f4a7c15u + 0x1234567u) : 0u;
+}
+// 0 for a dropped element, 1 / (1 - p) for a kept one
+__device__ __forceinline__ float svpc_drop_scale(uint32_t key, float p, float inv_keep, unsigned long long idx) {
+  const uint32_t h = svpc_mix32((uint32_t)idx ^ svpc_mix32(key + (uint32_t)(idx >> 32) * 0x85ebca6bu));
+  return ((h >> 8) * (1.0f / 16777216.0f)) >= p ? inv_keep : 0.f;
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

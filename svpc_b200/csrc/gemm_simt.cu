@@ -19,6 +19,7 @@ struct GemmSimtParams {
   int accumulate;
   int k_per_split;         // grid.z slices of K (split-K: fp32 atomics into a zeroed / accumulated D)
   int atomic;
+  SvpcDrop drop;           // dropout after the activation, before the residual
 };
 
 template <typename TA, typename TB, typename TD>
@@ -65,6 +66,9 @@ __global__ void __launch_bounds__(GS_THREADS) gemm_simt_kernel(const GemmSimtPar
     __syncthreads();
   }
 
+  const bool dropping = p.drop.seed != nullptr && p.drop.p > 0.f;
+  const uint32_t dkey = svpc_drop_key(p.drop);
+  const float dinv = dropping ? 1.f / (1.f - p.drop.p) : 1.f;
   TD* __restrict__ D = (TD*)p.D;
   const TD* __restrict__ R = (const TD*)p.residual;
   TD* __restrict__ Pre = (TD*)p.pre;
@@ -81,6 +85,7 @@ __global__ void __launch_bounds__(GS_THREADS) gemm_simt_kernel(const GemmSimtPar
       if (p.bias) v += p.bias[n];
       if (Pre) stf(Pre + (long long)m * p.ldp + n, v);
       v = svpc_act(v, p.act);
+      if (dropping) v *= svpc_drop_scale(dkey, p.drop.p, dinv, (unsigned long long)m * p.N + n);
       if (R) v += ldf(R + (long long)m * p.ldr + n);
       TD* d = D + (long long)m * p.ldd + n;
       if (p.accumulate) v += ldf(d);
@@ -93,7 +98,7 @@ template <typename TA, typename TB>
 static int launch_td(GemmSimtParams p, int dtD, cudaStream_t st) {
   const int tiles = svpc_cdiv(p.N, GS_BN) * svpc_cdiv(p.M, GS_BM);
   int split = 1;
-  const bool plain = !p.bias && p.act == SVPC_ACT_NONE && !p.residual && !p.pre && dtD == SVPC_F32;
+  const bool plain = !p.bias && p.act == SVPC_ACT_NONE && !p.residual && !p.pre && dtD == SVPC_F32 && !p.drop.seed;
   if (plain && tiles < SVPC_NUM_SMS / 2 && p.K >= 512) split = svpc_imin(SVPC_NUM_SMS / tiles, p.K / 128);
   if (split < 1) split = 1;
   p.k_per_split = svpc_cdiv(svpc_cdiv(p.K, split), GS_BK) * GS_BK;
@@ -111,8 +116,8 @@ static int launch_td(GemmSimtParams p, int dtD, cudaStream_t st) {
 int svpc_gemm_simt_launch(int M, int N, int K, const void* A, int dtA, long long sa_m, long long sa_k, const void* B,
                           int dtB, long long sb_n, long long sb_k, void* D, int dtD, long long ldd, const float* bias,
                           int act, const void* residual, long long ldr, void* pre, long long ldp, int accumulate,
-                          cudaStream_t st) {
-  GemmSimtParams p{M, N, K, A, sa_m, sa_k, B, sb_n, sb_k, D, ldd, bias, act, residual, ldr, pre, ldp, accumulate, K, 0};
+                          SvpcDrop drop, cudaStream_t st) {
+  GemmSimtParams p{M, N, K, A, sa_m, sa_k, B, sb_n, sb_k, D, ldd, bias, act, residual, ldr, pre, ldp, accumulate, K, 0, drop};
   SVPC_DISPATCH(dtA, TA, SVPC_DISPATCH(dtB, TB, return (launch_td<TA, TB>(p, dtD, st))));
   return SVPC_OK;
 }
@@ -124,7 +129,7 @@ int svpc_gemm_tc_eligible(int M, int N, int K, int dtA, long long sa_m, long lon
                           long long sb_k, int dtD, long long ldd);
 int svpc_gemm_tc_launch(int M, int N, int K, const void* A, long long sa_m, long long sa_k, const void* B, long long sb_n,
                         long long sb_k, void* D, int dtD, long long ldd, const float* bias, int act, const void* residual,
-                        long long ldr, void* pre, long long ldp, int accumulate, cudaStream_t st);
+                        long long ldr, void* pre, long long ldp, int accumulate, SvpcDrop drop, cudaStream_t st);
 
 extern "C" int svpc_gemm_route(int M, int N, int K, int dtA, long long sa_m, long long sa_k, int dtB, long long sb_n,
                                long long sb_k, int dtD, long long ldd) {
@@ -134,7 +139,8 @@ extern "C" int svpc_gemm_route(int M, int N, int K, int dtA, long long sa_m, lon
 extern "C" int svpc_gemm(int M, int N, int K, const void* A, int dtA, long long sa_m, long long sa_k, const void* B,
                          int dtB, long long sb_n, long long sb_k, void* D, int dtD, long long ldd, const float* bias,
                          int act, const void* residual, long long ldr, void* pre, long long ldp, int accumulate,
-                         int route, svpc_stream_t stream) {
+                         int route, const unsigned int* drop_seed, unsigned int drop_site, float drop_p,
+                         svpc_stream_t stream) {
   SVPC_REQUIRE(M >= 0 && N >= 0 && K >= 0, "gemm: negative size");
   if (M == 0 || N == 0) return SVPC_OK;
   SVPC_REQUIRE(A && B && D, "gemm: null operand");
@@ -142,6 +148,8 @@ extern "C" int svpc_gemm(int M, int N, int K, const void* A, int dtA, long long 
   SVPC_REQUIRE(sb_n == 1 || sb_k == 1, "gemm: B needs a unit stride (sb_n=%lld sb_k=%lld)", sb_n, sb_k);
   SVPC_REQUIRE(!(accumulate && (act != SVPC_ACT_NONE || residual)), "gemm: accumulate excludes act / residual");
   cudaStream_t st = (cudaStream_t)stream;
+  SVPC_REQUIRE(drop_p >= 0.f && drop_p < 1.f, "gemm: dropout p=%f outside [0, 1)", drop_p);
+  const SvpcDrop drop{drop_p > 0.f ? drop_seed : nullptr, drop_site, drop_p};
   const int ok = svpc_gemm_tc_eligible(M, N, K, dtA, sa_m, sa_k, dtB, sb_n, sb_k, dtD, ldd) &&
                  (((uintptr_t)A | (uintptr_t)B) & 15) == 0;   // TMA: 16-byte aligned global base
   if (route == SVPC_GEMM_TC && !ok) {
@@ -150,7 +158,7 @@ extern "C" int svpc_gemm(int M, int N, int K, const void* A, int dtA, long long 
   }
   if (ok && route != SVPC_GEMM_SIMT)
     return svpc_gemm_tc_launch(M, N, K, A, sa_m, sa_k, B, sb_n, sb_k, D, dtD, ldd, bias, act, residual, ldr, pre, ldp,
-                               accumulate, st);
+                               accumulate, drop, st);
   return svpc_gemm_simt_launch(M, N, K, A, dtA, sa_m, sa_k, B, dtB, sb_n, sb_k, D, dtD, ldd, bias, act, residual, ldr,
-                               pre, ldp, accumulate, st);
+                               pre, ldp, accumulate, drop, st);
 }

@@ -120,6 +120,7 @@ struct TcParams {
   void* pre; long long ldp;
   int accumulate;          // D += result
   int atomic;              // split-K: red.global.add.f32
+  SvpcDrop drop;           // dropout after the activation, before the residual (model.py:231, 287, 757)
 };
 
 template <int BN, bool A_MN, bool B_MN, int KSTAGES, typename TD>
@@ -244,6 +245,9 @@ __global__ void __launch_bounds__(TC_THREADS, 2) gemm_tc_kernel(const __grid_con
     const bool vec_ok = !p.atomic && (n0 + BN <= p.N) && (p.ldd % 4 == 0) && (((uintptr_t)Dp & 15) == 0) &&
                         (!Rp || (p.ldr % 4 == 0 && ((uintptr_t)Rp & 15) == 0)) &&
                         (!Pp || (p.ldp % 4 == 0 && ((uintptr_t)Pp & 15) == 0)) && (((uintptr_t)p.bias & 15) == 0);
+    const bool dropping = p.drop.seed != nullptr && p.drop.p > 0.f;
+    const uint32_t dkey = svpc_drop_key(p.drop);
+    const float dinv = dropping ? 1.f / (1.f - p.drop.p) : 1.f;
     if (vec_ok) {
       const int cl = (lane % (BN / 4)) * 4;            // this lane's 4 columns inside the tile
       const int rsub = lane / (BN / 4);                // row inside the pass
@@ -257,6 +261,11 @@ __global__ void __launch_bounds__(TC_THREADS, 2) gemm_tc_kernel(const __grid_con
         x.x += bv.x; x.y += bv.y; x.z += bv.z; x.w += bv.w;
         if (Pp) st4(Pp + (long long)m * p.ldp + n0 + cl, x);
         x.x = svpc_act(x.x, p.act); x.y = svpc_act(x.y, p.act); x.z = svpc_act(x.z, p.act); x.w = svpc_act(x.w, p.act);
+        if (dropping) {
+          const unsigned long long e0 = (unsigned long long)m * p.N + n0 + cl;
+          x.x *= svpc_drop_scale(dkey, p.drop.p, dinv, e0); x.y *= svpc_drop_scale(dkey, p.drop.p, dinv, e0 + 1);
+          x.z *= svpc_drop_scale(dkey, p.drop.p, dinv, e0 + 2); x.w *= svpc_drop_scale(dkey, p.drop.p, dinv, e0 + 3);
+        }
         if (Rp) { const float4 rr = ld4(Rp + (long long)m * p.ldr + n0 + cl); x.x += rr.x; x.y += rr.y; x.z += rr.z; x.w += rr.w; }
         TD* d = Dp + (long long)m * p.ldd + n0 + cl;
         if (p.accumulate) { const float4 dd = ld4(d); x.x += dd.x; x.y += dd.y; x.z += dd.z; x.w += dd.w; }
@@ -277,6 +286,7 @@ __global__ void __launch_bounds__(TC_THREADS, 2) gemm_tc_kernel(const __grid_con
             if (p.bias) x += p.bias[n];
             if (Pp) stf(Pp + (long long)m * p.ldp + n, x);
             x = svpc_act(x, p.act);
+            if (dropping) x *= svpc_drop_scale(dkey, p.drop.p, dinv, (unsigned long long)m * p.N + n);
             if (Rp) x += ldf(Rp + (long long)m * p.ldr + n);
             TD* d = Dp + (long long)m * p.ldd + n;
             if (p.accumulate) x += ldf(d);
@@ -367,7 +377,7 @@ static int launch_major(bool a_mn, bool b_mn, const CUtensorMap& ta, const CUten
 
 int svpc_gemm_tc_launch(int M, int N, int K, const void* A, long long sa_m, long long sa_k, const void* B, long long sb_n,
                         long long sb_k, void* D, int dtD, long long ldd, const float* bias, int act, const void* residual,
-                        long long ldr, void* pre, long long ldp, int accumulate, cudaStream_t st) {
+                        long long ldr, void* pre, long long ldp, int accumulate, SvpcDrop drop, cudaStream_t st) {
   const bool a_mn = sa_k != 1, b_mn = sb_k != 1;
   const int BN = (N <= 64) ? 64 : 128;
   CUtensorMap ta, tb;
@@ -379,14 +389,14 @@ int svpc_gemm_tc_launch(int M, int N, int K, const void* A, long long sa_m, long
   const int tiles_m = svpc_cdiv(M, TC_BM), tiles_n = svpc_cdiv(N, BN);
   const int kb_total = svpc_cdiv(K, TC_BK);
   int split = 1;
-  const bool plain = !bias && act == SVPC_ACT_NONE && !residual && !pre && dtD == SVPC_F32;
+  const bool plain = !bias && act == SVPC_ACT_NONE && !residual && !pre && dtD == SVPC_F32 && !drop.seed;
   if (plain && tiles_m * tiles_n < SVPC_NUM_SMS / 2 && kb_total >= 16) {
     split = svpc_imin(svpc_imin(SVPC_NUM_SMS / (tiles_m * tiles_n), kb_total / 8), 32);
     if (split < 1) split = 1;
   }
   int kb_per = svpc_cdiv(kb_total, split);
   split = svpc_cdiv(kb_total, kb_per);
-  TcParams p{M, N, K, kb_per, D, ldd, bias, act, residual, ldr, pre, ldp, accumulate, split > 1 ? 1 : 0};
+  TcParams p{M, N, K, kb_per, D, ldd, bias, act, residual, ldr, pre, ldp, accumulate, split > 1 ? 1 : 0, drop};
   if (split > 1 && !accumulate) {
     cudaError_t e = cudaMemset2DAsync(D, (size_t)ldd * 4, 0, (size_t)N * 4, (size_t)M, st);
     if (e != cudaSuccess) { svpc_set_error("gemm_tc: memset2D: %s", cudaGetErrorString(e)); return SVPC_ERR_CUDA; }

@@ -15,7 +15,10 @@ static inline int rw_grid(long long rows) { return svpc_imin(rows, (long long)SV
 // ------------------------------------------------------------------------------------------------
 template <typename T>
 __global__ void act_bwd_kernel(int rows, int cols, const T* __restrict__ dy, const T* __restrict__ ref, int act,
-                               T* __restrict__ dz, float* __restrict__ dbias) {
+                               T* __restrict__ dz, float* __restrict__ dbias, const SvpcDrop drop) {
+  const bool dropping = drop.seed != nullptr && drop.p > 0.f;
+  const uint32_t dkey = svpc_drop_key(drop);
+  const float dinv = dropping ? 1.f / (1.f - drop.p) : 1.f;
   // blockDim = (32, 8); a CTA owns a 32-column strip for a slice of rows
   const int c = blockIdx.x * 32 + threadIdx.x;
   __shared__ float red[8][33];
@@ -24,6 +27,7 @@ __global__ void act_bwd_kernel(int rows, int cols, const T* __restrict__ dy, con
     for (int r = blockIdx.y * 8 + threadIdx.y; r < rows; r += gridDim.y * 8) {
       const long long o = (long long)r * cols + c;
       float g = ldf(dy + o);
+      if (dropping) g *= svpc_drop_scale(dkey, drop.p, dinv, (unsigned long long)o);
       if (act == SVPC_ACT_RELU) g = ldf(ref + o) > 0.f ? g : 0.f;
       else if (act == SVPC_ACT_GELU) g *= svpc_gelu_grad(ldf(ref + o));
       else if (act == SVPC_ACT_SIGMOID) { const float y = ldf(ref + o); g *= y * (1.f - y); }
@@ -42,23 +46,24 @@ __global__ void act_bwd_kernel(int rows, int cols, const T* __restrict__ dy, con
 }
 
 static int act_bwd_vec_launch(int rows, int cols, const void* dy, const void* ref, int dt, int act, void* dz, float* dbias,
-                              cudaStream_t st);
+                              SvpcDrop drop, cudaStream_t st);
 
 extern "C" int svpc_act_bwd(int rows, int cols, const void* dy, const void* ref, int dt, int act, void* dz, float* dbias,
-                            svpc_stream_t stream) {
+                            const unsigned int* drop_seed, unsigned int drop_site, float drop_p, svpc_stream_t stream) {
   if (rows <= 0 || cols <= 0) return SVPC_OK;
   cudaStream_t st = (cudaStream_t)stream;
+  const SvpcDrop drop{drop_p > 0.f ? drop_seed : nullptr, drop_site, drop_p};
   if (dbias) cudaMemsetAsync(dbias, 0, sizeof(float) * cols, st);
   if (cols % 8 == 0 && (((uintptr_t)dy | (uintptr_t)ref | (uintptr_t)dz) & 15) == 0)
-    return act_bwd_vec_launch(rows, cols, dy, ref, dt, act, dz, dbias, st);
+    return act_bwd_vec_launch(rows, cols, dy, ref, dt, act, dz, dbias, drop, st);
   dim3 grid(svpc_cdiv(cols, 32), svpc_imin(svpc_cdiv(rows, 8), 64));
   SVPC_DISPATCH(dt, T, (act_bwd_kernel<T><<<grid, dim3(32, 8), 0, st>>>(rows, cols, (const T*)dy, (const T*)ref, act,
-                                                                      (T*)dz, dbias)));
+                                                                      (T*)dz, dbias, drop)));
   return svpc_check_launch("act_bwd");
 }
 
 extern "C" int svpc_colsum(int rows, int cols, const void* x, int dt, float* out, svpc_stream_t stream) {
-  return svpc_act_bwd(rows, cols, x, nullptr, dt, SVPC_ACT_NONE, nullptr, out, stream);
+  return svpc_act_bwd(rows, cols, x, nullptr, dt, SVPC_ACT_NONE, nullptr, out, nullptr, 0, 0.f, stream);
 }
 
 // out[c] += sum_r w[r] * x[r, c]
@@ -240,8 +245,11 @@ __global__ void __launch_bounds__(256, 2) ln_bwd_warp_kernel(int rows, const TG*
 template <typename T>
 __global__ void __launch_bounds__(256) act_bwd_vec_kernel(int rows, int cols, const T* __restrict__ dy,
                                                           const T* __restrict__ ref, int act, T* __restrict__ dz,
-                                                          float* __restrict__ dbias) {
+                                                          float* __restrict__ dbias, const SvpcDrop drop) {
   __shared__ float red[8][256];
+  const bool dropping = drop.seed != nullptr && drop.p > 0.f;
+  const uint32_t dkey = svpc_drop_key(drop);
+  const float dinv = dropping ? 1.f / (1.f - drop.p) : 1.f;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const int c0 = (blockIdx.x * 32 + tx) * 8;
   float acc[8];
@@ -252,6 +260,10 @@ __global__ void __launch_bounds__(256) act_bwd_vec_kernel(int rows, int cols, co
       const long long o = (long long)r * cols + c0;
       float g[8], y[8];
       ld8(dy + o, g);
+      if (dropping) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) g[e] *= svpc_drop_scale(dkey, drop.p, dinv, (unsigned long long)(o + e));
+      }
       if (act != SVPC_ACT_NONE) {
         ld8(ref + o, y);
 #pragma unroll
@@ -281,10 +293,10 @@ __global__ void __launch_bounds__(256) act_bwd_vec_kernel(int rows, int cols, co
 static inline bool rw_al16(const void* p) { return ((uintptr_t)p & 15) == 0; }
 
 static int act_bwd_vec_launch(int rows, int cols, const void* dy, const void* ref, int dt, int act, void* dz, float* dbias,
-                              cudaStream_t st) {
+                              SvpcDrop drop, cudaStream_t st) {
   const int gx = svpc_cdiv(cols, 256);
   dim3 grid(gx, svpc_imin(svpc_cdiv(rows, 8), svpc_cdiv(SVPC_NUM_SMS * 4, gx)));
-  SVPC_DISPATCH(dt, T, (act_bwd_vec_kernel<T><<<grid, 256, 0, st>>>(rows, cols, (const T*)dy, (const T*)ref, act, (T*)dz, dbias)));
+  SVPC_DISPATCH(dt, T, (act_bwd_vec_kernel<T><<<grid, 256, 0, st>>>(rows, cols, (const T*)dy, (const T*)ref, act, (T*)dz, dbias, drop)));
   return svpc_check_launch("act_bwd");
 }
 
@@ -474,8 +486,12 @@ __global__ void __launch_bounds__(EM_THREADS) embed_ln_fwd_kernel(int rows, int 
                                                                   const float* __restrict__ gamma,
                                                                   const float* __restrict__ beta, float eps,
                                                                   T* __restrict__ y, long long ldy,
-                                                                  float* __restrict__ mean, float* __restrict__ rstd) {
+                                                                  float* __restrict__ mean, float* __restrict__ rstd,
+                                                                  const SvpcDrop drop) {
   __shared__ float red[64];
+  const bool dropping = drop.seed != nullptr && drop.p > 0.f;
+  const uint32_t dkey = svpc_drop_key(drop);
+  const float dinv = dropping ? 1.f / (1.f - drop.p) : 1.f;
   for (int r = blockIdx.x; r < rows; r += gridDim.x) {
     const float* src = table + (long long)ids[r] * W;
     float v[EM_MAXPT];
@@ -498,20 +514,26 @@ __global__ void __launch_bounds__(EM_THREADS) embed_ln_fwd_kernel(int rows, int 
 #pragma unroll
     for (int i = 0; i < EM_MAXPT; ++i) {
       const int c = threadIdx.x + i * EM_THREADS;
-      if (c < W) stf(y + (long long)r * ldy + c, (v[i] - mu) * rs * gamma[c] + beta[c]);
+      if (c < W) {
+        float o = (v[i] - mu) * rs * gamma[c] + beta[c];
+        if (dropping) o *= svpc_drop_scale(dkey, drop.p, dinv, (unsigned long long)r * W + c);
+        stf(y + (long long)r * ldy + c, o);
+      }
     }
   }
 }
 
 extern "C" int svpc_embed_ln_fwd(int rows, int W, const float* table, const int* ids, const float* gamma,
                                  const float* beta, float eps, void* y, long long ldy, int dt, float* mean, float* rstd,
+                                 const unsigned int* drop_seed, unsigned int drop_site, float drop_p,
                                  svpc_stream_t stream) {
   if (rows <= 0) return SVPC_OK;
   SVPC_REQUIRE(W <= EM_THREADS * EM_MAXPT, "embed_ln: W=%d too wide", W);
   SVPC_REQUIRE(ldy >= W, "embed_ln: ldy=%lld < W=%d", ldy, W);
+  const SvpcDrop drop{drop_p > 0.f ? drop_seed : nullptr, drop_site, drop_p};
   cudaStream_t st = (cudaStream_t)stream;
   SVPC_DISPATCH(dt, T, (embed_ln_fwd_kernel<T><<<rw_grid(rows), EM_THREADS, 0, st>>>(rows, W, table, ids, gamma, beta, eps,
-                                                                                    (T*)y, ldy, mean, rstd)));
+                                                                                    (T*)y, ldy, mean, rstd, drop)));
   return svpc_check_launch("embed_ln_fwd");
 }
 
@@ -523,8 +545,11 @@ __global__ void __launch_bounds__(EM_THREADS) embed_ln_bwd_kernel(int rows, int 
                                                                   const float* __restrict__ rstd,
                                                                   const float* __restrict__ gamma, int padding_idx,
                                                                   float* __restrict__ dtable, float* __restrict__ dgamma,
-                                                                  float* __restrict__ dbeta) {
+                                                                  float* __restrict__ dbeta, const SvpcDrop drop) {
   __shared__ float red[64];
+  const bool dropping = drop.seed != nullptr && drop.p > 0.f;
+  const uint32_t dkey = svpc_drop_key(drop);
+  const float dinv = dropping ? 1.f / (1.f - drop.p) : 1.f;
   float ag[EM_MAXPT], ab[EM_MAXPT];
 #pragma unroll
   for (int i = 0; i < EM_MAXPT; ++i) { ag[i] = 0.f; ab[i] = 0.f; }
@@ -539,7 +564,8 @@ __global__ void __launch_bounds__(EM_THREADS) embed_ln_bwd_kernel(int rows, int 
       const int c = threadIdx.x + i * EM_THREADS;
       g[i] = 0.f; xh[i] = 0.f;
       if (c < W) {
-        const float d = ldf(dy + (long long)r * W + c);
+        float d = ldf(dy + (long long)r * W + c);
+        if (dropping) d *= svpc_drop_scale(dkey, drop.p, dinv, (unsigned long long)r * W + c);
         xh[i] = (src[c] - mu) * rs;
         g[i] = d * gamma[c];
         ag[i] += d * xh[i];
@@ -567,8 +593,10 @@ __global__ void __launch_bounds__(EM_THREADS) embed_ln_bwd_kernel(int rows, int 
 
 extern "C" int svpc_embed_ln_bwd(int rows, int W, int V, const void* dy, int dt, const float* table, const int* ids,
                                  const float* mean, const float* rstd, const float* gamma, int padding_idx,
-                                 float* dtable, float* dgamma, float* dbeta, svpc_stream_t stream) {
+                                 float* dtable, float* dgamma, float* dbeta, const unsigned int* drop_seed,
+                                 unsigned int drop_site, float drop_p, svpc_stream_t stream) {
   cudaStream_t st = (cudaStream_t)stream;
+  const SvpcDrop drop{drop_p > 0.f ? drop_seed : nullptr, drop_site, drop_p};
   cudaMemsetAsync(dtable, 0, sizeof(float) * (size_t)V * W, st);
   cudaMemsetAsync(dgamma, 0, sizeof(float) * W, st);
   cudaMemsetAsync(dbeta, 0, sizeof(float) * W, st);
@@ -576,7 +604,7 @@ extern "C" int svpc_embed_ln_bwd(int rows, int W, int V, const void* dy, int dt,
   SVPC_REQUIRE(W <= EM_THREADS * EM_MAXPT, "embed_ln: W=%d too wide", W);
   const int grid = svpc_imin(rows, SVPC_NUM_SMS * 4);
   SVPC_DISPATCH(dt, T, (embed_ln_bwd_kernel<T><<<grid, EM_THREADS, 0, st>>>(rows, W, (const T*)dy, table, ids, mean, rstd,
-                                                                           gamma, padding_idx, dtable, dgamma, dbeta)));
+                                                                           gamma, padding_idx, dtable, dgamma, dbeta, drop)));
   return svpc_check_launch("embed_ln_bwd");
 }
 
@@ -590,9 +618,13 @@ __global__ void __launch_bounds__(RW_THREADS) video_ln_pack_kernel(int n_rows, i
                                                                    const int* __restrict__ clip_t,
                                                                    const int* __restrict__ clip_b, float eps,
                                                                    T* __restrict__ xhat, float* __restrict__ mean,
-                                                                   float* __restrict__ rstd) {
+                                                                   float* __restrict__ rstd, const float* __restrict__ gamma,
+                                                                   const float* __restrict__ beta, const SvpcDrop drop) {
   __shared__ float red[64];
   const int F4 = F >> 2;
+  const bool dropping = drop.seed != nullptr && drop.p > 0.f;
+  const uint32_t dkey = svpc_drop_key(drop);
+  const float dinv = dropping ? 1.f / (1.f - drop.p) : 1.f;
   for (int r = blockIdx.x; r < n_rows; r += gridDim.x) {
     const int n = r / Lv, row = r - n * Lv;
     const float* src = reinterpret_cast<const float*>(feat_ptrs[clip_t[n]]) + ((long long)clip_b[n] * L + row) * F;
@@ -622,10 +654,16 @@ __global__ void __launch_bounds__(RW_THREADS) video_ln_pack_kernel(int n_rows, i
     for (int i = 0; i < RW_MAXPT / 4; ++i) {
       const int c = threadIdx.x + i * RW_THREADS;
       if (c < F4) {
-        stf(dst + 4 * c + 0, (v[i].x - mu) * rs);
-        stf(dst + 4 * c + 1, (v[i].y - mu) * rs);
-        stf(dst + 4 * c + 2, (v[i].z - mu) * rs);
-        stf(dst + 4 * c + 3, (v[i].w - mu) * rs);
+        float o[4] = {(v[i].x - mu) * rs, (v[i].y - mu) * rs, (v[i].z - mu) * rs, (v[i].w - mu) * rs};
+        if (gamma) {                       // train mode: LN affine and dropout applied here (model.py:549-550)
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            o[e] = o[e] * gamma[4 * c + e] + beta[4 * c + e];
+            if (dropping) o[e] *= svpc_drop_scale(dkey, drop.p, dinv, (unsigned long long)r * F + 4 * c + e);
+          }
+        }
+#pragma unroll
+        for (int e = 0; e < 4; ++e) stf(dst + 4 * c + e, o[e]);
       }
     }
   }
@@ -633,14 +671,72 @@ __global__ void __launch_bounds__(RW_THREADS) video_ln_pack_kernel(int n_rows, i
 
 extern "C" int svpc_video_ln_pack(int n_clips, int B, int L, int Lv, int F, const long long* feat_ptrs,
                                   const int* clip_t, const int* clip_b, float eps, void* xhat, int dt, float* mean,
-                                  float* rstd, svpc_stream_t stream) {
+                                  float* rstd, const float* gamma, const float* beta, const unsigned int* drop_seed,
+                                  unsigned int drop_site, float drop_p, svpc_stream_t stream) {
   if (n_clips <= 0) return SVPC_OK;
+  SVPC_REQUIRE((gamma == nullptr) == (beta == nullptr), "video_ln_pack: gamma and beta go together");
+  const SvpcDrop drop{(drop_p > 0.f && gamma) ? drop_seed : nullptr, drop_site, drop_p};
   SVPC_REQUIRE(F % 4 == 0 && F <= RW_THREADS * RW_MAXPT, "video_ln_pack: F=%d must be a multiple of 4 and <= 4096", F);
   cudaStream_t st = (cudaStream_t)stream;
   const int n_rows = n_clips * Lv;
   SVPC_DISPATCH(dt, T, (video_ln_pack_kernel<T><<<svpc_imin(n_rows, SVPC_NUM_SMS * 16), RW_THREADS, 0, st>>>(
-      n_rows, B, L, Lv, F, feat_ptrs, clip_t, clip_b, eps, (T*)xhat, mean, rstd)));
+      n_rows, B, L, Lv, F, feat_ptrs, clip_t, clip_b, eps, (T*)xhat, mean, rstd, gamma, beta, drop)));
   return svpc_check_launch("video_ln_pack");
+}
+
+// Backward of the train-mode staging y = drop(xhat * gamma + beta): dgamma[c] = sum_r dy*scale*xhat, dbeta[c] = sum_r dy*scale
+// (the features are inputs: no gradient flows further).  xhat is recomputed from the raw features and the saved statistics.
+template <typename T>
+__global__ void __launch_bounds__(RW_THREADS) video_ln_affine_bwd_kernel(int n_rows, int B, int L, int Lv, int F,
+                                                                         const long long* __restrict__ feat_ptrs,
+                                                                         const int* __restrict__ clip_t,
+                                                                         const int* __restrict__ clip_b,
+                                                                         const float* __restrict__ mean,
+                                                                         const float* __restrict__ rstd,
+                                                                         const T* __restrict__ dy, float* __restrict__ dgamma,
+                                                                         float* __restrict__ dbeta, const SvpcDrop drop) {
+  const bool dropping = drop.seed != nullptr && drop.p > 0.f;
+  const uint32_t dkey = svpc_drop_key(drop);
+  const float dinv = dropping ? 1.f / (1.f - drop.p) : 1.f;
+  float ag[RW_MAXPT], ab[RW_MAXPT];
+#pragma unroll
+  for (int i = 0; i < RW_MAXPT; ++i) { ag[i] = 0.f; ab[i] = 0.f; }
+  for (int r = blockIdx.x; r < n_rows; r += gridDim.x) {
+    const int n = r / Lv, row = r - n * Lv;
+    const float* src = reinterpret_cast<const float*>(feat_ptrs[clip_t[n]]) + ((long long)clip_b[n] * L + row) * F;
+    const float mu = mean[r], rs = rstd[r];
+#pragma unroll
+    for (int i = 0; i < RW_MAXPT; ++i) {
+      const int c = threadIdx.x + i * RW_THREADS;
+      if (c < F) {
+        float d = ldf(dy + (long long)r * F + c);
+        if (dropping) d *= svpc_drop_scale(dkey, drop.p, dinv, (unsigned long long)r * F + c);
+        ag[i] = fmaf(d, (__ldg(src + c) - mu) * rs, ag[i]);
+        ab[i] += d;
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < RW_MAXPT; ++i) {
+    const int c = threadIdx.x + i * RW_THREADS;
+    if (c < F) { atomicAdd(dgamma + c, ag[i]); atomicAdd(dbeta + c, ab[i]); }
+  }
+}
+
+extern "C" int svpc_video_ln_affine_bwd(int n_clips, int B, int L, int Lv, int F, const long long* feat_ptrs,
+                                        const int* clip_t, const int* clip_b, const float* mean, const float* rstd,
+                                        const void* dy, int dt, float* dgamma, float* dbeta, const unsigned int* drop_seed,
+                                        unsigned int drop_site, float drop_p, svpc_stream_t stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaMemsetAsync(dgamma, 0, sizeof(float) * F, st);
+  cudaMemsetAsync(dbeta, 0, sizeof(float) * F, st);
+  if (n_clips <= 0) return SVPC_OK;
+  SVPC_REQUIRE(F <= RW_THREADS * RW_MAXPT, "video_ln_affine_bwd: F=%d too wide", F);
+  const SvpcDrop drop{drop_p > 0.f ? drop_seed : nullptr, drop_site, drop_p};
+  const int n_rows = n_clips * Lv;
+  SVPC_DISPATCH(dt, T, (video_ln_affine_bwd_kernel<T><<<svpc_imin(n_rows, SVPC_NUM_SMS * 2), RW_THREADS, 0, st>>>(
+      n_rows, B, L, Lv, F, feat_ptrs, clip_t, clip_b, mean, rstd, (const T*)dy, dgamma, dbeta, drop)));
+  return svpc_check_launch("video_ln_affine_bwd");
 }
 
 // ------------------------------------------------------------------------------------------------

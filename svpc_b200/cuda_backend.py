@@ -44,6 +44,15 @@ def _f(x):
     return C.c_float(float(x))
 
 
+def _drop(drop):
+    """drop = None or (seed tensor (1,) int32 on the device, site id, p) -> the three C arguments."""
+    if drop is None:
+        return None, C.c_uint(0), C.c_float(0.0)
+    seed, site, p = drop
+    assert seed.is_cuda and seed.dtype == torch.int32 and seed.numel() == 1
+    return C.c_void_p(seed.data_ptr()), C.c_uint(int(site)), C.c_float(float(p))
+
+
 def _mat_strides(t):
     """Element strides of a 2-D view with size-1 dimensions normalised so that one of the two is 1."""
     s0, s1 = t.stride()
@@ -114,7 +123,7 @@ class CudaBackend:
 
     # ------------------------------------------------------------------ dense
     def gemm(self, a, bt, out_dtype, bias=None, act=0, residual=None, out=None, accumulate=False, want_pre=False,
-             route=None):
+             route=None, drop=None):
         """out[M,N] = act(a[M,K] @ bt[N,K]^T + bias) + residual.  a / bt may be any 2-D views with one unit stride."""
         self._chk(a, bt, bias, residual, out)
         M, K = a.shape
@@ -135,7 +144,7 @@ class CudaBackend:
                        _ptr(bias), int(act),
                        _ptr(residual), _ll(residual.stride(0) if residual is not None else 0),
                        _ptr(pre), _ll(N),
-                       int(bool(accumulate)), int(self.gemm_route if route is None else route),
+                       int(bool(accumulate)), int(self.gemm_route if route is None else route), *_drop(drop),
                        tag=None if self.timing is None else self._gemm_tag(M, N, K, a, bt, out, sa, sb))
         return (out, pre) if want_pre else out
 
@@ -146,15 +155,21 @@ class CudaBackend:
             r = GEMM_SIMT
         return f"gemm_{'tc' if r == GEMM_TC else 'simt'}:{M}x{N}x{K}:{'T' if sa[1] != 1 else 'N'}{'T' if sb[1] != 1 else 'N'}"
 
-    def act_bwd(self, dy, ref, act):
+    def act_bwd(self, dy, ref, act, drop=None):
         self._chk(dy, ref)
         dy = self._c(dy)
         rows, cols = dy.shape
         dz = torch.empty_like(dy)
         dbias = torch.empty(cols, dtype=torch.float32, device=dy.device)
         self._call("svpc_act_bwd", rows, cols, _ptr(dy), _ptr(None if ref is None else self._c(ref)), _DT[dy.dtype], int(act),
-                   _ptr(dz), _ptr(dbias))
+                   _ptr(dz), _ptr(dbias), *_drop(drop))
         return dz, dbias
+
+    def dropout_mask(self, n, drop):
+        """Scale (0 or 1/(1-p)) of elements [0, n) of a dropout site: the contract the tests check the kernels against."""
+        out = torch.empty(int(n), dtype=torch.float32, device=drop[0].device)
+        self._call("svpc_dropout_mask", _ll(n), *_drop(drop), _ptr(out))
+        return out
 
     def colsum(self, x):
         self._chk(x)
@@ -229,7 +244,7 @@ class CudaBackend:
         self._call("svpc_index_colsum", dy.shape[0], dy.shape[1], _ptr(dy), _DT[dy.dtype], _ptr(ids), int(nbins), _ptr(out))
         return out
 
-    def embed_ln_fwd(self, table, ids, gamma, beta, eps, out_dtype):
+    def embed_ln_fwd(self, table, ids, gamma, beta, eps, out_dtype, drop=None):
         self._chk(table, ids)
         rows, W = ids.numel(), table.shape[1]
         y = self._padded_empty(rows, W, out_dtype, table.device) if out_dtype == torch.bfloat16 else \
@@ -237,10 +252,10 @@ class CudaBackend:
         mean = torch.empty(rows, dtype=torch.float32, device=table.device)
         rstd = torch.empty(rows, dtype=torch.float32, device=table.device)
         self._call("svpc_embed_ln_fwd", rows, W, _ptr(self._c(table)), _ptr(ids), _ptr(gamma), _ptr(beta), _f(eps), _ptr(y),
-                   _ll(y.stride(0)), _DT[out_dtype], _ptr(mean), _ptr(rstd))
+                   _ll(y.stride(0)), _DT[out_dtype], _ptr(mean), _ptr(rstd), *_drop(drop))
         return y, mean, rstd
 
-    def embed_ln_bwd(self, dy, table, ids, mean, rstd, gamma, eps, padding_idx):
+    def embed_ln_bwd(self, dy, table, ids, mean, rstd, gamma, eps, padding_idx, drop=None):
         self._chk(dy, table, ids)
         dy = self._c(dy)
         V, W = table.shape
@@ -249,12 +264,12 @@ class CudaBackend:
         dbeta = torch.empty(W, dtype=torch.float32, device=dy.device)
         self._call("svpc_embed_ln_bwd", dy.shape[0], W, V, _ptr(dy), _DT[dy.dtype], _ptr(self._c(table)), _ptr(ids), _ptr(mean),
                    _ptr(rstd), _ptr(gamma), int(-1 if padding_idx is None else padding_idx), _ptr(dtable), _ptr(dgamma),
-                   _ptr(dbeta))
+                   _ptr(dbeta), *_drop(drop))
         return dtable, dgamma, dbeta
 
-    def video_ln_pack(self, feats_list, clip_t, clip_b, Lv, eps, out_dtype):
+    def _feat_ptrs(self, feats_list):
         f0 = feats_list[0]
-        self._chk(f0, clip_t, clip_b)
+        self._chk(f0)
         B, L, Fdim = f0.shape
         for f in feats_list:
             if not (f.is_cuda and f.dtype == torch.float32 and f.is_contiguous() and f.shape == f0.shape):
@@ -266,13 +281,29 @@ class CudaBackend:
                 self._ptr_cache.clear()
             ptrs = torch.tensor(list(key), dtype=torch.int64).to(f0.device)
             self._ptr_cache[key] = ptrs
+        return ptrs, B, L, Fdim
+
+    def video_ln_pack(self, feats_list, clip_t, clip_b, Lv, eps, out_dtype, gamma=None, beta=None, drop=None):
+        """(x - mean) * rstd of the first Lv rows of every clip; with gamma / beta (train mode) the LN affine and the
+        dropout between LN and the projection are applied here too (model.py:549-550)."""
+        ptrs, B, L, Fdim = self._feat_ptrs(feats_list)
+        f0 = feats_list[0]
         n_clips = clip_t.numel()
         xhat = torch.empty(n_clips * Lv, Fdim, dtype=out_dtype, device=f0.device)
         mean = torch.empty(n_clips * Lv, dtype=torch.float32, device=f0.device)
         rstd = torch.empty(n_clips * Lv, dtype=torch.float32, device=f0.device)
         self._call("svpc_video_ln_pack", n_clips, B, L, int(Lv), Fdim, _ptr(ptrs), _ptr(clip_t), _ptr(clip_b), _f(eps),
-                   _ptr(xhat), _DT[out_dtype], _ptr(mean), _ptr(rstd))
+                   _ptr(xhat), _DT[out_dtype], _ptr(mean), _ptr(rstd), _ptr(gamma), _ptr(beta), *_drop(drop))
         return xhat, mean, rstd
+
+    def video_ln_affine_bwd(self, dy, feats_list, clip_t, clip_b, Lv, mean, rstd, drop=None):
+        ptrs, B, L, Fdim = self._feat_ptrs(feats_list)
+        dy = self._c(dy)
+        dgamma = torch.empty(Fdim, dtype=torch.float32, device=dy.device)
+        dbeta = torch.empty(Fdim, dtype=torch.float32, device=dy.device)
+        self._call("svpc_video_ln_affine_bwd", int(clip_t.numel()), B, L, int(Lv), Fdim, _ptr(ptrs), _ptr(clip_t), _ptr(clip_b),
+                   _ptr(mean), _ptr(rstd), _ptr(dy), _DT[dy.dtype], _ptr(dgamma), _ptr(dbeta), *_drop(drop))
+        return dgamma, dbeta
 
     # ------------------------------------------------------------------ attention
     @staticmethod
@@ -280,7 +311,7 @@ class CudaBackend:
         assert t.dim() == 2 and t.stride(1) == 1, (t.shape, t.stride())
         return t
 
-    def attn_fwd(self, q, k, v, q_off, q_len, k_off, k_len, key_mask, causal, n_heads, max_lq, max_lk, out_dtype):
+    def attn_fwd(self, q, k, v, q_off, q_len, k_off, k_len, key_mask, causal, n_heads, max_lq, max_lk, out_dtype, drop=None):
         self._chk(q, k, v, q_off, key_mask)
         q, k, v = self._rowview(q), self._rowview(k), self._rowview(v)
         D = q.shape[1]
@@ -288,10 +319,11 @@ class CudaBackend:
         ctx = torch.empty(q.shape[0], D, dtype=out_dtype, device=q.device)
         self._call("svpc_attn_fwd", int(q_off.numel()), int(n_heads), D // n_heads, _ptr(q), _ll(q.stride(0)), _ptr(k),
                    _ll(k.stride(0)), _ptr(v), _ll(v.stride(0)), _DT[q.dtype], _ptr(q_off), _ptr(q_len), _ptr(k_off),
-                   _ptr(k_len), _ptr(key_mask), int(bool(causal)), int(max_lq), int(max_lk), _ptr(ctx), _ll(D))
+                   _ptr(k_len), _ptr(key_mask), int(bool(causal)), int(max_lq), int(max_lk), _ptr(ctx), _ll(D), *_drop(drop))
         return ctx
 
-    def attn_bwd(self, dctx, q, k, v, q_off, q_len, k_off, k_len, key_mask, causal, n_heads, max_lq, max_lk, dq, dk, dv):
+    def attn_bwd(self, dctx, q, k, v, q_off, q_len, k_off, k_len, key_mask, causal, n_heads, max_lq, max_lk, dq, dk, dv,
+                 drop=None):
         self._chk(dctx, q, k, v, dq, dk, dv)
         dctx = self._c(dctx)
         D = q.shape[1]
@@ -301,7 +333,7 @@ class CudaBackend:
         self._call("svpc_attn_bwd", int(q_off.numel()), int(n_heads), D // n_heads, _ptr(q), _ll(q.stride(0)), _ptr(k),
                    _ll(k.stride(0)), _ptr(v), _ll(v.stride(0)), _DT[q.dtype], _ptr(q_off), _ptr(q_len), _ptr(k_off),
                    _ptr(k_len), _ptr(key_mask), int(bool(causal)), int(max_lq), int(max_lk), _ptr(dctx), _ll(D),
-                   _ptr(dq), _ll(dq.stride(0)), _ptr(dk), _ll(dk.stride(0)), _ptr(dv), _ll(dv.stride(0)))
+                   _ptr(dq), _ll(dq.stride(0)), _ptr(dk), _ll(dk.stride(0)), _ptr(dv), _ll(dv.stride(0)), *_drop(drop))
 
     # ------------------------------------------------------------------ ingredients
     def segmean_fwd(self, x, sep_mask, cu_ingr, pe, NI):

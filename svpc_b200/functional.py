@@ -51,7 +51,7 @@ WEIGHTS = WeightCache()
 
 
 class _LinMeta:
-    __slots__ = ("n_x", "n_w", "has_bias", "act", "out_dtype", "cd", "w_is_kn", "has_res", "cache")
+    __slots__ = ("n_x", "n_w", "has_bias", "act", "out_dtype", "cd", "w_is_kn", "has_res", "cache", "drop")
 
     def __init__(self, **kw):
         for k, v in kw.items():
@@ -79,11 +79,11 @@ class LinearFn(Function):
         want_pre = meta.act == ACT_GELU
         if meta.w_is_kn:
             assert meta.n_x == 1 and meta.n_w == 1
-            out = be().gemm(xs_c[0], W.t(), meta.out_dtype, bias, meta.act, residual, want_pre=want_pre)
+            out = be().gemm(xs_c[0], W.t(), meta.out_dtype, bias, meta.act, residual, want_pre=want_pre, drop=meta.drop)
         elif meta.n_x == 1:
-            out = be().gemm(xs_c[0], W, meta.out_dtype, bias, meta.act, residual, want_pre=want_pre)
+            out = be().gemm(xs_c[0], W, meta.out_dtype, bias, meta.act, residual, want_pre=want_pre, drop=meta.drop)
         else:
-            assert meta.act == ACT_NONE and residual is None
+            assert meta.act == ACT_NONE and residual is None and meta.drop is None
             k0 = 0
             out = None
             for j, x in enumerate(xs_c):
@@ -111,8 +111,8 @@ class LinearFn(Function):
         dy = dy.contiguous()
         need = ctx.needs_input_grad
         d_res = dy if (meta.has_res and need[1]) else None
-        if meta.act != ACT_NONE:
-            dz, dbias = be().act_bwd(dy, ref, meta.act)
+        if meta.act != ACT_NONE or meta.drop is not None:
+            dz, dbias = be().act_bwd(dy, ref, meta.act, drop=meta.drop)     # dy * dropout scale * act'
         else:
             dz = dy
             dbias = be().colsum(dy) if meta.has_bias else None
@@ -156,12 +156,14 @@ class LinearFn(Function):
         return (None, d_res, *dxs, *dws, *dbs)
 
 
-def linear(xs, ws, bs, *, act=ACT_NONE, out_dtype=None, cd=torch.float32, residual=None, w_is_kn=False, cache=True):
+def linear(xs, ws, bs, *, act=ACT_NONE, out_dtype=None, cd=torch.float32, residual=None, w_is_kn=False, cache=True,
+           drop=None):
+    """drop = (seed tensor, site, p): nn.Dropout applied after the activation and before the residual add."""
     xs = list(xs) if isinstance(xs, (list, tuple)) else [xs]
     ws = list(ws) if isinstance(ws, (list, tuple)) else [ws]
     bs = [] if bs is None else (list(bs) if isinstance(bs, (list, tuple)) else [bs])
     meta = _LinMeta(n_x=len(xs), n_w=len(ws), has_bias=len(bs) > 0, act=act, out_dtype=out_dtype or cd, cd=cd,
-                    w_is_kn=w_is_kn, has_res=residual is not None, cache=cache or len(ws) > 1)
+                    w_is_kn=w_is_kn, has_res=residual is not None, cache=cache or len(ws) > 1, drop=drop)
     return LinearFn.apply(meta, residual, *xs, *ws, *bs)
 
 
@@ -196,17 +198,18 @@ class EmbedLNFn(Function):
     """LN_W(table[ids])  (reference model.py:492-494 / 519-521); row ``padding_idx`` of the table gets no gradient."""
 
     @staticmethod
-    def forward(ctx, table, ids, gamma, beta, eps, out_dtype, padding_idx):
-        y, mean, rstd = be().embed_ln_fwd(table.detach(), ids, gamma.detach(), beta.detach(), eps, out_dtype)
+    def forward(ctx, table, ids, gamma, beta, eps, out_dtype, padding_idx, drop=None):
+        y, mean, rstd = be().embed_ln_fwd(table.detach(), ids, gamma.detach(), beta.detach(), eps, out_dtype, drop=drop)
         ctx.save_for_backward(table.detach(), ids, mean, rstd, gamma.detach())
-        ctx.eps, ctx.padding_idx = eps, padding_idx
+        ctx.eps, ctx.padding_idx, ctx.drop = eps, padding_idx, drop
         return y
 
     @staticmethod
     def backward(ctx, dy):
         table, ids, mean, rstd, gamma = ctx.saved_tensors
-        dtable, dgamma, dbeta = be().embed_ln_bwd(dy.contiguous(), table, ids, mean, rstd, gamma, ctx.eps, ctx.padding_idx)
-        return dtable, None, dgamma, dbeta, None, None, None
+        dtable, dgamma, dbeta = be().embed_ln_bwd(dy.contiguous(), table, ids, mean, rstd, gamma, ctx.eps, ctx.padding_idx,
+                                                  drop=ctx.drop)
+        return dtable, None, dgamma, dbeta, None, None, None, None
 
 
 class AttentionFn(Function):
@@ -217,16 +220,16 @@ class AttentionFn(Function):
     comes back in the same packing, so the fused projection's backward sees one contiguous tensor."""
 
     @staticmethod
-    def forward(ctx, qsrc, kvsrc, cols, lay, key_mask, causal, n_heads, out_dtype):
+    def forward(ctx, qsrc, kvsrc, cols, lay, key_mask, causal, n_heads, out_dtype, drop=None):
         D = lay["D"]
         src2 = qsrc if kvsrc is None else kvsrc
         q = qsrc[:, cols[0]:cols[0] + D]
         k = src2[:, cols[1]:cols[1] + D]
         v = src2[:, cols[2]:cols[2] + D]
         out = be().attn_fwd(q, k, v, lay["q_off"], lay["q_len"], lay["k_off"], lay["k_len"], key_mask, causal, n_heads,
-                            lay["max_lq"], lay["max_lk"], out_dtype)
+                            lay["max_lq"], lay["max_lk"], out_dtype, drop=drop)
         ctx.save_for_backward(qsrc, kvsrc, key_mask)
-        ctx.lay, ctx.causal, ctx.n_heads, ctx.cols = lay, causal, n_heads, cols
+        ctx.lay, ctx.causal, ctx.n_heads, ctx.cols, ctx.drop = lay, causal, n_heads, cols, drop
         return out
 
     @staticmethod
@@ -239,12 +242,31 @@ class AttentionFn(Function):
         sl = lambda t, c: t[:, c:c + D]
         be().attn_bwd(dctx.contiguous(), sl(qsrc, cols[0]), sl(src2, cols[1]), sl(src2, cols[2]), lay["q_off"], lay["q_len"],
                       lay["k_off"], lay["k_len"], key_mask, ctx.causal, ctx.n_heads, lay["max_lq"], lay["max_lk"],
-                      sl(dqsrc, cols[0]), sl(dkvsrc, cols[1]), sl(dkvsrc, cols[2]))
-        return dqsrc, (None if kvsrc is None else dkvsrc), None, None, None, None, None, None
+                      sl(dqsrc, cols[0]), sl(dkvsrc, cols[1]), sl(dkvsrc, cols[2]), drop=ctx.drop)
+        return dqsrc, (None if kvsrc is None else dkvsrc), None, None, None, None, None, None, None
 
 
-def attention(qsrc, kvsrc, cols, lay, key_mask, causal, n_heads, out_dtype):
-    return AttentionFn.apply(qsrc, kvsrc, cols, lay, key_mask, causal, n_heads, out_dtype)
+def attention(qsrc, kvsrc, cols, lay, key_mask, causal, n_heads, out_dtype, drop=None):
+    return AttentionFn.apply(qsrc, kvsrc, cols, lay, key_mask, causal, n_heads, out_dtype, drop)
+
+
+class VideoLNDropFn(Function):
+    """Train-mode staging of the video features: drop(LN_F(x) * gamma + beta) in the compute dtype (reference
+    model.py:549-550).  The features are inputs, so the backward only produces dgamma / dbeta."""
+
+    @staticmethod
+    def forward(ctx, gamma, beta, feats_list, clip_t, clip_b, Lv, eps, out_dtype, drop):
+        y, mean, rstd = be().video_ln_pack(feats_list, clip_t, clip_b, Lv, eps, out_dtype, gamma=gamma.detach(),
+                                           beta=beta.detach(), drop=drop)
+        ctx.save_for_backward(clip_t, clip_b, mean, rstd)
+        ctx.feats, ctx.Lv, ctx.drop = feats_list, Lv, drop
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        clip_t, clip_b, mean, rstd = ctx.saved_tensors
+        dgamma, dbeta = be().video_ln_affine_bwd(dy.contiguous(), ctx.feats, clip_t, clip_b, ctx.Lv, mean, rstd, drop=ctx.drop)
+        return dgamma, dbeta, None, None, None, None, None, None, None
 
 
 class SegMeanFn(Function):

@@ -194,6 +194,7 @@ class StateAwareRecursiveTransformer(nn.Module):
             node.register_parameter(leaf, nn.Parameter(t))
         self._pcache = {}
         self.last_parts = {}
+        self._seed_t, self._site = None, 0      # train-mode dropout: device step seed (bumped per forward), site counter
 
     # ---- parameter lookup by reference key
     def p(self, name):
@@ -227,6 +228,23 @@ class StateAwareRecursiveTransformer(nn.Module):
     # ------------------------------------------------------------------------------------------
     # building blocks (all batched over clips)
     # ------------------------------------------------------------------------------------------
+    def _begin_step(self, device):
+        """Train mode: new dropout masks for this forward (the seed lives on the device so that a captured graph draws
+        fresh masks on every replay)."""
+        self._site = 0
+        if self.training:
+            if self._seed_t is None or self._seed_t.device != device:
+                self._seed_t = torch.randint(1, 2 ** 30, (1,), dtype=torch.int32, device=device)
+            else:
+                self._seed_t += 1
+
+    def _drop(self, p):
+        """(seed, site, p) for one nn.Dropout site of the reference, or None in eval mode / p == 0."""
+        if not self.training or p <= 0.0 or self._seed_t is None:
+            return None
+        self._site += 1
+        return (self._seed_t, self._site, float(p))
+
     def _lin(self, x, prefix, **kw):
         return Fn.linear(x, self.p(prefix + ".weight"), self.p(prefix + ".bias"), cd=self.compute_dtype, **kw)
 
@@ -245,16 +263,20 @@ class StateAwareRecursiveTransformer(nn.Module):
         ap = prefix + ".attention"
         if cls_lay is None:
             qkv = self._qkv(x, ap + ".self", ("query", "key", "value"))
-            ctx = Fn.attention(qkv, None, (0, D, 2 * D), lay, key_mask, False, Hh, cd)
+            ctx = Fn.attention(qkv, None, (0, D, 2 * D), lay, key_mask, False, Hh, cd,
+                               drop=self._drop(cfg.attention_probs_dropout_prob))
             res = x
         else:
             kv = self._qkv(x, ap + ".self", ("key", "value"))
             res = x[::cls_stride].contiguous()
             q = self._lin(res, ap + ".self.query")
-            ctx = Fn.attention(q, kv, (0, 0, D), cls_lay, key_mask, False, Hh, cd)
-        a = self._ln(self._lin(ctx, ap + ".output.dense", residual=res), None, ap + ".output.LayerNorm")
+            ctx = Fn.attention(q, kv, (0, 0, D), cls_lay, key_mask, False, Hh, cd,
+                               drop=self._drop(cfg.attention_probs_dropout_prob))
+        ph = cfg.hidden_dropout_prob
+        a = self._ln(self._lin(ctx, ap + ".output.dense", residual=res, drop=self._drop(ph)), None, ap + ".output.LayerNorm")
         h = self._lin(a, prefix + ".hidden_intermediate.dense", act=ACT_GELU)
-        return self._ln(self._lin(h, prefix + ".output.dense", residual=a), None, prefix + ".output.LayerNorm")
+        return self._ln(self._lin(h, prefix + ".output.dense", residual=a, drop=self._drop(ph)), None,
+                        prefix + ".output.LayerNorm")
 
     def _video_embed(self, feats_list, plan, vid_ids):
         """BertEmbeddingsVideoUntied + token-type add (reference model.py:548-562, 889-891).  LN(3072)'s affine is
@@ -262,6 +284,15 @@ class StateAwareRecursiveTransformer(nn.Module):
         in the compute dtype, and the 90 GFLOP input-gradient GEMM is not needed for gamma / beta."""
         cfg = self.config
         pfx = "video_embeddings.video_embeddings"
+        drop = self._drop(cfg.hidden_dropout_prob)
+        if drop is not None:
+            # train mode: dropout sits between LN(3072) and the projection (model.py:549-551), so the affine cannot be
+            # folded into the weights; the normalised, scaled and dropped features are staged once in the compute dtype
+            a = Fn.VideoLNDropFn.apply(self.p(pfx + ".0.weight"), self.p(pfx + ".0.bias"), list(feats_list), plan.t["clip_t"],
+                                       plan.t["clip_b"], cfg.max_v_len, cfg.layer_norm_eps, self.compute_dtype, drop)
+            z = self._lin(a, pfx + ".2", act=ACT_RELU)
+            return self._ln(z, None, pfx + ".4", pe=self.p("video_embeddings.position_embeddings_video.pe"),
+                            pe_period=cfg.max_v_len, tt=self.p("token_type_embeddings.weight"), tt_ids=vid_ids)
         xhat, _, _ = Fn.be().video_ln_pack(feats_list, plan.t["clip_t"], plan.t["clip_b"], cfg.max_v_len,
                                           cfg.layer_norm_eps, self.compute_dtype)
         W, g0, b0 = self.p(pfx + ".2.weight"), self.p(pfx + ".0.weight"), self.p(pfx + ".0.bias")
@@ -276,7 +307,8 @@ class StateAwareRecursiveTransformer(nn.Module):
         cfg = self.config
         pfx = which + ".word_fc"
         e = Fn.EmbedLNFn.apply(self.p(which + ".word_embeddings.weight"), ids, self.p(pfx + ".0.weight"),
-                               self.p(pfx + ".0.bias"), cfg.layer_norm_eps, self.compute_dtype, PAD)
+                               self.p(pfx + ".0.bias"), cfg.layer_norm_eps, self.compute_dtype, PAD,
+                               self._drop(cfg.hidden_dropout_prob))
         z = self._lin(e, pfx + ".2", act=ACT_RELU)
         return self._ln(z, None, pfx + ".4", pe=pe, pe_period=pe_period)
 
@@ -284,7 +316,7 @@ class StateAwareRecursiveTransformer(nn.Module):
         """EntitiyReasoningNetwork.forward (reference model.py:777-823): everything that depends only on the step
         vector is batched over all clips; the entity-state recurrence is one sequential kernel per video."""
         f32 = torch.float32
-        h_as = self._lin(V, prefix + ".action_selector.0", act=ACT_RELU)
+        h_as = self._lin(V, prefix + ".action_selector.0", act=ACT_RELU, drop=self._drop(0.4))     # nn.Dropout(p=0.4), model.py:757
         ac = self._lin(h_as, prefix + ".action_selector.3", act=ACT_SIGMOID, out_dtype=f32)            # (Nc, A)
         fbar = Fn.linear(Fn.RowNormalizeFn.apply(ac), self.p(prefix + ".action_embeddings"), None, cd=self.compute_dtype,
                          out_dtype=f32, w_is_kn=True)                                                     # (Nc, W)  Eq. 1
@@ -305,13 +337,15 @@ class StateAwareRecursiveTransformer(nn.Module):
         for l in range(cfg.num_hidden_layers):
             pfx = f"decoder.layer.{l}"
             qkv = self._qkv(x, pfx + ".self_attention", ("query", "key", "value"))
-            sa = Fn.attention(qkv, None, (0, D, 2 * D), plan.dec_lay, text_mask, True, Hh, cd)
+            pa = cfg.attention_probs_dropout_prob
+            sa = Fn.attention(qkv, None, (0, D, 2 * D), plan.dec_lay, text_mask, True, Hh, cd, drop=self._drop(pa))
             h1 = self._ln(sa, x, pfx + ".norm1")
             q2 = self._lin(h1, pfx + ".dec_enc_attention.query")
             kv2 = self._qkv(ctx, pfx + ".dec_enc_attention", ("key", "value"))
-            ca = Fn.attention(q2, kv2, (0, 0, D), cross, None, False, Hh, cd)
+            ca = Fn.attention(q2, kv2, (0, 0, D), cross, None, False, Hh, cd, drop=self._drop(pa))
             h2 = self._ln(ca, h1, pfx + ".norm2")
-            x = self._ln(self._lin(h2, pfx + ".output.dense", residual=h2), None, pfx + ".output.LayerNorm")
+            x = self._ln(self._lin(h2, pfx + ".output.dense", residual=h2, drop=self._drop(cfg.hidden_dropout_prob)), None,
+                         pfx + ".output.LayerNorm")
         return x
 
     def _lm_logits(self, dec):
@@ -441,6 +475,7 @@ class StateAwareRecursiveTransformer(nn.Module):
         mode, Lv, Lt, V, D = cfg.model_mode, cfg.max_v_len, cfg.max_t_len, cfg.vocab_size, cfg.hidden_size
         f32 = torch.float32
         dev = video_features_list[0].device
+        self._begin_step(dev)
         if plan is None:
             plan = self.make_plan(batch_step_num, ingr_id_dict, extra_zeros, alignments, dev)
         B, Nc = plan.B, plan.Nc

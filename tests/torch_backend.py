@@ -60,7 +60,9 @@ class TorchBackend:
         return None if x is None else x.to(self.math_dtype)
 
     # ---------------------------------------------------------------- dense
-    def gemm(self, a, bt, out_dtype, bias=None, act=0, residual=None, out=None, accumulate=False, want_pre=False):
+    def gemm(self, a, bt, out_dtype, bias=None, act=0, residual=None, out=None, accumulate=False, want_pre=False,
+             route=None, drop=None):
+        assert drop is None, "the plain-torch statements are eval-mode (no dropout)"
         pre = self.f(a) @ self.f(bt).t()
         if bias is not None:
             pre = pre + self.f(bias)
@@ -80,7 +82,7 @@ class TorchBackend:
             return y, pre.to(out_dtype)
         return y
 
-    def act_bwd(self, dy, ref, act):
+    def act_bwd(self, dy, ref, act, drop=None):
         dy32 = self.f(dy)
         if act == ACT_RELU:
             dz = dy32 * (self.f(ref) > 0)
@@ -131,11 +133,11 @@ class TorchBackend:
         out.index_add_(0, ids.long(), self.f(dy))
         return out.float()
 
-    def embed_ln_fwd(self, table, ids, gamma, beta, eps, out_dtype):
+    def embed_ln_fwd(self, table, ids, gamma, beta, eps, out_dtype, drop=None):
         y, mean, rstd = self._ln(self.f(table)[ids.long()], self.f(gamma), self.f(beta), eps)
         return y.to(out_dtype), mean.float(), rstd.float()
 
-    def embed_ln_bwd(self, dy, table, ids, mean, rstd, gamma, eps, padding_idx):
+    def embed_ln_bwd(self, dy, table, ids, mean, rstd, gamma, eps, padding_idx, drop=None):
         def fn(t, g):
             return self._ln(t[ids.long()], g, torch.zeros_like(g), eps)[0]
         dtable, dgamma = _vjp(fn, [self.f(table), self.f(gamma)], [self.f(dy)])
@@ -143,7 +145,8 @@ class TorchBackend:
             dtable[padding_idx].zero_()
         return dtable.float(), dgamma.float(), self.f(dy).sum(0).float()
 
-    def video_ln_pack(self, feats_list, clip_t, clip_b, Lv, eps, out_dtype):
+    def video_ln_pack(self, feats_list, clip_t, clip_b, Lv, eps, out_dtype, gamma=None, beta=None, drop=None):
+        assert gamma is None and drop is None
         x = torch.stack([f for f in feats_list])                      # (S, B, L, F)
         x = self.f(x[clip_t.long(), clip_b.long(), :Lv])              # (Nc, Lv, F)
         x = x.reshape(-1, x.shape[-1])
@@ -176,11 +179,12 @@ class TorchBackend:
         ctx = ctx.index_copy(0, idx, torch.cat([c for _, _, c in pieces]))
         return ctx
 
-    def attn_fwd(self, q, k, v, q_off, q_len, k_off, k_len, key_mask, causal, n_heads, max_lq, max_lk, out_dtype):
+    def attn_fwd(self, q, k, v, q_off, q_len, k_off, k_len, key_mask, causal, n_heads, max_lq, max_lk, out_dtype, drop=None):
         return self._attn(self.f(q), self.f(k), self.f(v), q_off.tolist(), q_len.tolist(), k_off.tolist(),
                           k_len.tolist(), key_mask, causal, n_heads).to(out_dtype)
 
-    def attn_bwd(self, dctx, q, k, v, q_off, q_len, k_off, k_len, key_mask, causal, n_heads, max_lq, max_lk, dq, dk, dv):
+    def attn_bwd(self, dctx, q, k, v, q_off, q_len, k_off, k_len, key_mask, causal, n_heads, max_lq, max_lk, dq, dk, dv,
+                 drop=None):
         qo, ql, ko, kl = q_off.tolist(), q_len.tolist(), k_off.tolist(), k_len.tolist()
         g = _vjp(lambda a, b, c: self._attn(a, b, c, qo, ql, ko, kl, key_mask, causal, n_heads),
                  [self.f(q), self.f(k), self.f(v)], [self.f(dctx)])
