@@ -115,7 +115,7 @@ int svpc_video_ln_affine_bwd(int n_clips, int B, int L, int Lv, int F, const lon
                              float drop_p, svpc_stream_t stream);
 
 /* BertSelfAttention core (model.py:204-216) over ragged short sequences; one CTA per (sequence, head).  Dropout on the
- * probabilities (model.py:214): element index ((seq * H + head) * max_lq + i) * max_lk + j. */
+ * probabilities (model.py:214): element index ((seq * H + head) * max_lq + i) * lks + j, lks = max_lk rounded up to even. */
 int svpc_attn_fwd(int n_seq, int H, int dh, const void* q, long long ldq, const void* k, long long ldk, const void* v,
                   long long ldv, int dt, const int* q_off, const int* q_len, const int* k_off, const int* k_len,
                   const float* key_mask, int causal, int max_lq, int max_lk, void* ctx, long long ldo,

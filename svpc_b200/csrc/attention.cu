@@ -76,7 +76,7 @@ __global__ void __launch_bounds__(AT_THREADS) attn_fwd_kernel(int H, int dh, con
     const unsigned long long base = (unsigned long long)blockIdx.x * max_lq;
     for (int idx = threadIdx.x; idx < lq * lk; idx += AT_THREADS) {
       const int i = idx / lk, j = idx - i * lk;
-      S[idx] *= svpc_drop_scale(dkey, drop.p, dinv, (base + i) * max_lk + j);
+      S[idx] *= svpc_drop_scale(dkey, drop.p, dinv, (base + i) * ((max_lk + 1) & ~1) + j);
     }
     __syncthreads();
   }
@@ -130,7 +130,7 @@ __global__ void __launch_bounds__(AT_THREADS) attn_bwd_kernel(int H, int dh, con
     float a = 0.f;
     for (int i = 0; i < lq; ++i) {
       float pij = P[i * lk + j];
-      if (dropping) pij *= svpc_drop_scale(dkey, drop.p, dinv, (dbase + i) * max_lk + j);
+      if (dropping) pij *= svpc_drop_scale(dkey, drop.p, dinv, (dbase + i) * ((max_lk + 1) & ~1) + j);
       a = fmaf(pij, dO[i * pitch + d], a);
     }
     stf(dv + (long long)(ko + j) * lddv + h * dh + d, a);
@@ -142,7 +142,7 @@ __global__ void __launch_bounds__(AT_THREADS) attn_bwd_kernel(int H, int dh, con
     const float* b = V + j * pitch;
     float s = 0.f;
     for (int d = 0; d < dh; ++d) s = fmaf(a[d], b[d], s);
-    if (dropping) s *= svpc_drop_scale(dkey, drop.p, dinv, (dbase + i) * max_lk + j);
+    if (dropping) s *= svpc_drop_scale(dkey, drop.p, dinv, (dbase + i) * ((max_lk + 1) & ~1) + j);
     dS[idx] = s;
   }
   __syncthreads();

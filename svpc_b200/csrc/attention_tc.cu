@@ -125,15 +125,18 @@ __device__ __forceinline__ void atc_softmax(float (&s)[NT][4], int i0, int lk, i
 }
 
 // dropout scale (0 or 1/(1-p), or 0/1 when inv == 1) of the thread's elements of tile nt: element index
-// ((seq * H + head) * max_lq + i) * max_lk + j, the same in the forward, the backward and the FFMA kernel
+// ((seq * H + head) * max_lq + i) * lks + j with lks = max_lk rounded up to even; the same in the forward, the backward
+// and the FFMA kernel
 struct AtcDrop {
   bool on;
   uint32_t key;
   float p, inv;
   unsigned long long base;     // (seq * H + head) * max_lq
-  int max_lk;
-  __device__ __forceinline__ float scale(int i, int j) const {
-    return on ? svpc_drop_scale(key, p, inv, (base + (unsigned long long)i) * max_lk + j) : 1.f;
+  int lks;                     // row stride of the index space: max_lk rounded up to even, so (j, j+1) with j even is one pair
+  // scales of columns j (even) and j + 1 of row i
+  __device__ __forceinline__ void scale2(int i, int j, float& s0, float& s1) const {
+    if (on) svpc_drop_scale2(key, p, inv, (base + (unsigned long long)i) * lks + j, s0, s1);
+    else { s0 = 1.f; s1 = 1.f; }
   }
 };
 __device__ __forceinline__ AtcDrop atc_make_drop(const SvpcDrop& d, int seq_head, int max_lq, int max_lk) {
@@ -143,9 +146,10 @@ __device__ __forceinline__ AtcDrop atc_make_drop(const SvpcDrop& d, int seq_head
   a.p = d.p;
   a.inv = a.on ? 1.f / (1.f - d.p) : 1.f;
   a.base = (unsigned long long)seq_head * max_lq;
-  a.max_lk = max_lk;
+  a.lks = (max_lk + 1) & ~1;
   return a;
 }
+// multiply the thread's elements of every tile by their dropout scale: v[nt][0..1] row i0, v[nt][2..3] row i0 + 8
 template <int NT>
 __device__ __forceinline__ void atc_apply_drop(float (&s)[NT][4], const AtcDrop& dr, int i0, int lk_pad, int lane) {
   if (!dr.on) return;
@@ -153,8 +157,11 @@ __device__ __forceinline__ void atc_apply_drop(float (&s)[NT][4], const AtcDrop&
 #pragma unroll
   for (int nt = 0; nt < NT; ++nt)
     if (nt * 8 < lk_pad) {
-#pragma unroll
-      for (int e = 0; e < 4; ++e) s[nt][e] *= dr.scale(i0 + (e >> 1) * 8, nt * 8 + t2 + (e & 1));
+      float a, b;
+      dr.scale2(i0, nt * 8 + t2, a, b);
+      s[nt][0] *= a; s[nt][1] *= b;
+      dr.scale2(i0 + 8, nt * 8 + t2, a, b);
+      s[nt][2] *= a; s[nt][3] *= b;
     }
 }
 
@@ -270,8 +277,11 @@ __device__ __forceinline__ void atc_write_x(bf16* X, int xp, const float (&s)[NT
     if (nt * 8 < lk_pad) {
       float v[4] = {s[nt][0], s[nt][1], s[nt][2], s[nt][3]};
       if (dr) {
-#pragma unroll
-        for (int e = 0; e < 4; ++e) v[e] *= dr->scale(r0 + g + (e >> 1) * 8, nt * 8 + t2 + (e & 1));
+        float a, b;
+        dr->scale2(r0 + g, nt * 8 + t2, a, b);
+        v[0] *= a; v[1] *= b;
+        dr->scale2(r0 + g + 8, nt * 8 + t2, a, b);
+        v[2] *= a; v[3] *= b;
       }
       *reinterpret_cast<uint32_t*>(X + (r0 + g) * xp + nt * 8 + t2) = pack_bf16(v[0], v[1]);
       *reinterpret_cast<uint32_t*>(X + (r0 + g + 8) * xp + nt * 8 + t2) = pack_bf16(v[2], v[3]);
@@ -320,9 +330,11 @@ __global__ void __launch_bounds__(NT <= 14 ? 224 : 256, NT <= 14 ? 2 : 1) attn_t
       if (nt * 8 < p.lk_pad) {
         float dp[4];
         atc_tile_abt(dp, af, sV, nt, lane);
+        float m[4];
+        dr.scale2(gi, nt * 8 + t2, m[0], m[1]);
+        dr.scale2(gi + 8, nt * 8 + t2, m[2], m[3]);
 #pragma unroll
-        for (int e = 0; e < 4; ++e)
-          dsum[e >> 1] = fmaf(s[nt][e], dp[e] * dr.scale(gi + (e >> 1) * 8, nt * 8 + t2 + (e & 1)), dsum[e >> 1]);
+        for (int e = 0; e < 4; ++e) dsum[e >> 1] = fmaf(s[nt][e], dp[e] * m[e], dsum[e >> 1]);
       }
     }
 #pragma unroll
@@ -336,9 +348,11 @@ __global__ void __launch_bounds__(NT <= 14 ? 224 : 256, NT <= 14 ? 2 : 1) attn_t
       if (nt * 8 < p.lk_pad) {
         float dp[4];
         atc_tile_abt(dp, af, sV, nt, lane);
+        float m[4];
+        dr.scale2(gi, nt * 8 + t2, m[0], m[1]);
+        dr.scale2(gi + 8, nt * 8 + t2, m[2], m[3]);
 #pragma unroll
-        for (int e = 0; e < 4; ++e)
-          s[nt][e] = s[nt][e] * (dp[e] * dr.scale(gi + (e >> 1) * 8, nt * 8 + t2 + (e & 1)) - dsum[e >> 1]) * scale;
+        for (int e = 0; e < 4; ++e) s[nt][e] = s[nt][e] * (dp[e] * m[e] - dsum[e >> 1]) * scale;
       }
     }
   }

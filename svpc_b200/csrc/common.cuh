@@ -72,10 +72,22 @@ __device__ __forceinline__ uint32_t svpc_mix32(uint32_t h) {
 __device__ __forceinline__ uint32_t svpc_drop_key(const SvpcDrop& d) {
   return d.seed ? svpc_mix32(*d.seed * 0x9e3779b9u + d.site * 0x7f4a7c15u + 0x1234567u) : 0u;
 }
+// One 32-bit hash serves the element pair (idx & ~1, idx | 1): 16 bits each (p is resolved to 1/65536).
+__device__ __forceinline__ uint32_t svpc_drop_hash(uint32_t key, unsigned long long pair) {
+  return svpc_mix32((uint32_t)pair * 0x9e3779b1u + (uint32_t)(pair >> 32) * 0x85ebca6bu + key);
+}
+__device__ __forceinline__ uint32_t svpc_drop_thresh(float p) { return (uint32_t)(p * 65536.0f); }
 // 0 for a dropped element, 1 / (1 - p) for a kept one
 __device__ __forceinline__ float svpc_drop_scale(uint32_t key, float p, float inv_keep, unsigned long long idx) {
-  const uint32_t h = svpc_mix32((uint32_t)idx ^ svpc_mix32(key + (uint32_t)(idx >> 32) * 0x85ebca6bu));
-  return ((h >> 8) * (1.0f / 16777216.0f)) >= p ? inv_keep : 0.f;
+  const uint32_t h = svpc_drop_hash(key, idx >> 1);
+  return ((h >> ((idx & 1) * 16)) & 0xffffu) >= svpc_drop_thresh(p) ? inv_keep : 0.f;
+}
+// both elements of an aligned pair (idx even) with one hash
+__device__ __forceinline__ void svpc_drop_scale2(uint32_t key, float p, float inv_keep, unsigned long long idx_even,
+                                                 float& s0, float& s1) {
+  const uint32_t h = svpc_drop_hash(key, idx_even >> 1), t = svpc_drop_thresh(p);
+  s0 = (h & 0xffffu) >= t ? inv_keep : 0.f;
+  s1 = (h >> 16) >= t ? inv_keep : 0.f;
 }
 
 __device__ __forceinline__ float warp_sum(float v) {

@@ -263,8 +263,16 @@ __global__ void __launch_bounds__(TC_THREADS, 2) gemm_tc_kernel(const __grid_con
         x.x = svpc_act(x.x, p.act); x.y = svpc_act(x.y, p.act); x.z = svpc_act(x.z, p.act); x.w = svpc_act(x.w, p.act);
         if (dropping) {
           const unsigned long long e0 = (unsigned long long)m * p.N + n0 + cl;
-          x.x *= svpc_drop_scale(dkey, p.drop.p, dinv, e0); x.y *= svpc_drop_scale(dkey, p.drop.p, dinv, e0 + 1);
-          x.z *= svpc_drop_scale(dkey, p.drop.p, dinv, e0 + 2); x.w *= svpc_drop_scale(dkey, p.drop.p, dinv, e0 + 3);
+          if ((e0 & 1) == 0) {             // aligned pairs: one hash per two elements
+            float s0, s1;
+            svpc_drop_scale2(dkey, p.drop.p, dinv, e0, s0, s1);
+            x.x *= s0; x.y *= s1;
+            svpc_drop_scale2(dkey, p.drop.p, dinv, e0 + 2, s0, s1);
+            x.z *= s0; x.w *= s1;
+          } else {
+            x.x *= svpc_drop_scale(dkey, p.drop.p, dinv, e0); x.y *= svpc_drop_scale(dkey, p.drop.p, dinv, e0 + 1);
+            x.z *= svpc_drop_scale(dkey, p.drop.p, dinv, e0 + 2); x.w *= svpc_drop_scale(dkey, p.drop.p, dinv, e0 + 3);
+          }
         }
         if (Rp) { const float4 rr = ld4(Rp + (long long)m * p.ldr + n0 + cl); x.x += rr.x; x.y += rr.y; x.z += rr.z; x.w += rr.w; }
         TD* d = Dp + (long long)m * p.ldd + n0 + cl;

@@ -260,9 +260,13 @@ __global__ void __launch_bounds__(256) act_bwd_vec_kernel(int rows, int cols, co
       const long long o = (long long)r * cols + c0;
       float g[8], y[8];
       ld8(dy + o, g);
-      if (dropping) {
+      if (dropping) {                    // cols % 8 == 0 and c0 % 8 == 0: o is even, (o + e, o + e + 1) are aligned pairs
 #pragma unroll
-        for (int e = 0; e < 8; ++e) g[e] *= svpc_drop_scale(dkey, drop.p, dinv, (unsigned long long)(o + e));
+        for (int e = 0; e < 8; e += 2) {
+          float s0, s1;
+          svpc_drop_scale2(dkey, drop.p, dinv, (unsigned long long)(o + e), s0, s1);
+          g[e] *= s0; g[e + 1] *= s1;
+        }
       }
       if (act != SVPC_ACT_NONE) {
         ld8(ref + o, y);
@@ -656,10 +660,14 @@ __global__ void __launch_bounds__(RW_THREADS) video_ln_pack_kernel(int n_rows, i
       if (c < F4) {
         float o[4] = {(v[i].x - mu) * rs, (v[i].y - mu) * rs, (v[i].z - mu) * rs, (v[i].w - mu) * rs};
         if (gamma) {                       // train mode: LN affine and dropout applied here (model.py:549-550)
-#pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            o[e] = o[e] * gamma[4 * c + e] + beta[4 * c + e];
-            if (dropping) o[e] *= svpc_drop_scale(dkey, drop.p, dinv, (unsigned long long)r * F + 4 * c + e);
+          const float4 g4 = *reinterpret_cast<const float4*>(gamma + 4 * c), b4 = *reinterpret_cast<const float4*>(beta + 4 * c);
+          o[0] = o[0] * g4.x + b4.x; o[1] = o[1] * g4.y + b4.y; o[2] = o[2] * g4.z + b4.z; o[3] = o[3] * g4.w + b4.w;
+          if (dropping) {                  // F is a multiple of 4: (4c, 4c+1) and (4c+2, 4c+3) are aligned pairs
+            float s0, s1;
+            svpc_drop_scale2(dkey, drop.p, dinv, (unsigned long long)r * F + 4 * c, s0, s1);
+            o[0] *= s0; o[1] *= s1;
+            svpc_drop_scale2(dkey, drop.p, dinv, (unsigned long long)r * F + 4 * c + 2, s0, s1);
+            o[2] *= s0; o[3] *= s1;
           }
         }
 #pragma unroll
@@ -686,40 +694,60 @@ extern "C" int svpc_video_ln_pack(int n_clips, int B, int L, int Lv, int F, cons
 
 // Backward of the train-mode staging y = drop(xhat * gamma + beta): dgamma[c] = sum_r dy*scale*xhat, dbeta[c] = sum_r dy*scale
 // (the features are inputs: no gradient flows further).  xhat is recomputed from the raw features and the saved statistics.
+// Layout: a CTA owns a 256-column slab (lane = 8 contiguous columns: one 16-byte bf16 load of dy, two float4 loads of the
+// features) for a strided set of rows (8 row lanes); column sums over the row lanes through shared memory, one red.global
+// per column per CTA.
 template <typename T>
-__global__ void __launch_bounds__(RW_THREADS) video_ln_affine_bwd_kernel(int n_rows, int B, int L, int Lv, int F,
-                                                                         const long long* __restrict__ feat_ptrs,
-                                                                         const int* __restrict__ clip_t,
-                                                                         const int* __restrict__ clip_b,
-                                                                         const float* __restrict__ mean,
-                                                                         const float* __restrict__ rstd,
-                                                                         const T* __restrict__ dy, float* __restrict__ dgamma,
-                                                                         float* __restrict__ dbeta, const SvpcDrop drop) {
+__global__ void __launch_bounds__(256) video_ln_affine_bwd_kernel(int n_rows, int B, int L, int Lv, int F,
+                                                                  const long long* __restrict__ feat_ptrs,
+                                                                  const int* __restrict__ clip_t,
+                                                                  const int* __restrict__ clip_b,
+                                                                  const float* __restrict__ mean,
+                                                                  const float* __restrict__ rstd,
+                                                                  const T* __restrict__ dy, float* __restrict__ dgamma,
+                                                                  float* __restrict__ dbeta, const SvpcDrop drop) {
+  __shared__ float red[8][256];
   const bool dropping = drop.seed != nullptr && drop.p > 0.f;
   const uint32_t dkey = svpc_drop_key(drop);
   const float dinv = dropping ? 1.f / (1.f - drop.p) : 1.f;
-  float ag[RW_MAXPT], ab[RW_MAXPT];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int c0 = (blockIdx.x * 32 + tx) * 8;
+  float ag[8], ab[8];
 #pragma unroll
-  for (int i = 0; i < RW_MAXPT; ++i) { ag[i] = 0.f; ab[i] = 0.f; }
-  for (int r = blockIdx.x; r < n_rows; r += gridDim.x) {
-    const int n = r / Lv, row = r - n * Lv;
-    const float* src = reinterpret_cast<const float*>(feat_ptrs[clip_t[n]]) + ((long long)clip_b[n] * L + row) * F;
-    const float mu = mean[r], rs = rstd[r];
+  for (int e = 0; e < 8; ++e) { ag[e] = 0.f; ab[e] = 0.f; }
+  if (c0 < F) {
+    for (int r = blockIdx.y * 8 + ty; r < n_rows; r += gridDim.y * 8) {
+      const int n = r / Lv, row = r - n * Lv;
+      const float* src = reinterpret_cast<const float*>(feat_ptrs[clip_t[n]]) + ((long long)clip_b[n] * L + row) * F + c0;
+      const float mu = mean[r], rs = rstd[r];
+      float d[8], x[8];
+      ld8(dy + (long long)r * F + c0, d);
+      ld8(src, x);
+      if (dropping) {
 #pragma unroll
-    for (int i = 0; i < RW_MAXPT; ++i) {
-      const int c = threadIdx.x + i * RW_THREADS;
-      if (c < F) {
-        float d = ldf(dy + (long long)r * F + c);
-        if (dropping) d *= svpc_drop_scale(dkey, drop.p, dinv, (unsigned long long)r * F + c);
-        ag[i] = fmaf(d, (__ldg(src + c) - mu) * rs, ag[i]);
-        ab[i] += d;
+        for (int e = 0; e < 8; e += 2) {
+          float s0, s1;
+          svpc_drop_scale2(dkey, drop.p, dinv, (unsigned long long)r * F + c0 + e, s0, s1);
+          d[e] *= s0; d[e + 1] *= s1;
+        }
       }
+#pragma unroll
+      for (int e = 0; e < 8; ++e) { ag[e] = fmaf(d[e], (x[e] - mu) * rs, ag[e]); ab[e] += d[e]; }
     }
   }
 #pragma unroll
-  for (int i = 0; i < RW_MAXPT; ++i) {
-    const int c = threadIdx.x + i * RW_THREADS;
-    if (c < F) { atomicAdd(dgamma + c, ag[i]); atomicAdd(dbeta + c, ab[i]); }
+  for (int pass = 0; pass < 2; ++pass) {
+    __syncthreads();
+#pragma unroll
+    for (int e = 0; e < 8; ++e) red[ty][tx * 8 + e] = pass == 0 ? ag[e] : ab[e];
+    __syncthreads();
+    const int c = blockIdx.x * 256 + threadIdx.x;
+    if (c < F) {
+      float t = 0.f;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) t += red[w][threadIdx.x];
+      atomicAdd((pass == 0 ? dgamma : dbeta) + c, t);
+    }
   }
 }
 
@@ -731,10 +759,12 @@ extern "C" int svpc_video_ln_affine_bwd(int n_clips, int B, int L, int Lv, int F
   cudaMemsetAsync(dgamma, 0, sizeof(float) * F, st);
   cudaMemsetAsync(dbeta, 0, sizeof(float) * F, st);
   if (n_clips <= 0) return SVPC_OK;
-  SVPC_REQUIRE(F <= RW_THREADS * RW_MAXPT, "video_ln_affine_bwd: F=%d too wide", F);
+  SVPC_REQUIRE(F % 8 == 0 && (((uintptr_t)dy) & 15) == 0, "video_ln_affine_bwd: F=%d must be a multiple of 8, dy 16-byte aligned", F);
   const SvpcDrop drop{drop_p > 0.f ? drop_seed : nullptr, drop_site, drop_p};
   const int n_rows = n_clips * Lv;
-  SVPC_DISPATCH(dt, T, (video_ln_affine_bwd_kernel<T><<<svpc_imin(n_rows, SVPC_NUM_SMS * 2), RW_THREADS, 0, st>>>(
+  const int gx = svpc_cdiv(F, 256);
+  dim3 grid(gx, svpc_imin(svpc_cdiv(n_rows, 8), svpc_cdiv(SVPC_NUM_SMS * 8, gx)));
+  SVPC_DISPATCH(dt, T, (video_ln_affine_bwd_kernel<T><<<grid, 256, 0, st>>>(
       n_rows, B, L, Lv, F, feat_ptrs, clip_t, clip_b, mean, rstd, (const T*)dy, dgamma, dbeta, drop)));
   return svpc_check_launch("video_ln_affine_bwd");
 }

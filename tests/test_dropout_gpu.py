@@ -124,7 +124,8 @@ def test_attention_dropout(cb, dt, ql, kl, causal):
     qo, ko = I32([sum(ql[:i]) for i in range(len(ql))]), I32([sum(kl[:i]) for i in range(len(kl))])
     d = mkdrop(site=11, p=0.1)
     mlq, mlk = max(ql), max(kl)
-    full = cb.dropout_mask(len(ql) * H * mlq * mlk, d).view(len(ql), H, mlq, mlk).double()
+    lks = (mlk + 1) // 2 * 2          # index-space row stride: max_lk rounded up to even
+    full = cb.dropout_mask(len(ql) * H * mlq * lks, d).view(len(ql), H, mlq, lks).double()
     ctx = cb.attn_fwd(q, k, v, qo, I32(ql), ko, I32(kl), km, causal, H, mlq, mlk, dt, drop=d)
     ref, bwd = attn_ref(q, k, v, ql, kl, km, causal, H, lambda n, h, lq, lk: full[n, h, :lq, :lk])
     tol = 3e-2 if dt == BF16 else 3e-5
