@@ -4,22 +4,33 @@
 // (the M / N index contiguous: dgrad uses W as an MN-major B, wgrad uses dY and X as MN-major A and B), so no
 // transposed copies of weights or activations are ever materialised.
 //
-// Structure (one 128 x BN output tile per CTA, 192 threads):
-//   warp 0      TMA producer: cp.async.bulk.tensor 2D boxes, 128B swizzle, into a KSTAGES-deep shared-memory ring,
-//               completion on mbarriers (expect_tx)
-//   warp 1      MMA issuer: one elected lane issues tcgen05.mma.cta_group::1.kind::f16 (UMMA 128 x BN x 16) from
-//               shared-memory descriptors into a TMEM accumulator; tcgen05.commit releases ring slots / signals the
-//               epilogue
-//   warps 2-5   epilogue: tcgen05.ld (32 lanes x 32 columns per warp) -> bias / activation / residual -> global;
+// Structure: PERSISTENT kernel, one CTA of 192 threads per SM, walking a list of work units (128 x BN tiles, BN <= 256;
+// split-K slices for weight gradients; narrower column slices for the tiles of the last partial round):
+//   warp 0      TMA producer: cp.async.bulk.tensor 2D boxes, 128B swizzle, into a 4-deep shared-memory ring
+//               (A 16 KB + B up to 32 KB per stage), completion on mbarriers (expect_tx); runs ahead across units
+//   warp 1      MMA issuer: one elected lane issues tcgen05.mma.cta_group::1.kind::f16 (UMMA 128 x width x 16) from
+//               shared-memory descriptors into one of TWO 256-column TMEM accumulators; tcgen05.commit releases ring
+//               slots / signals the epilogue
+//   warps 2-5   epilogue: tcgen05.ld (32 lanes x 32 columns per warp) -> smem transposition -> bias / activation /
+//               dropout / residual -> row-contiguous global stores, overlapped with the next unit's main loop;
 //               warp 2 also owns the TMEM allocation
-// Split-K (grid.z) with fp32 red.global for weight-gradient shapes whose output has too few tiles to fill 148 SMs.
+// Split-K with fp32 red.global.add.v4 for weight-gradient shapes whose output has too few tiles to fill 148 SMs.
 #include "common.cuh"
 #include <cuda.h>
+#include <stdlib.h>
 
 #define TC_BM 128
 #define TC_BK 64                 // 64 bf16 = 128 B = one swizzle row
-#define TC_THREADS 192
+#define TC_BN_MAX 256
+#define TC_STAGES 4
+#define TC_EPI_WARPS 8                                  // two per TMEM lane quarter
+#define TC_THREADS (64 + 32 * TC_EPI_WARPS)
 #define TC_UMMA_K 16
+#define TC_A_BYTES (TC_BM * TC_BK * 2)                  // 16 KB
+#define TC_B_BYTES (TC_BN_MAX * TC_BK * 2)              // 32 KB
+#define TC_STAGE_BYTES (TC_A_BYTES + TC_B_BYTES)
+#define TC_EPI_BYTES (TC_EPI_WARPS * 32 * 32 * 4)        // one 32 x 32 fp32 transposition buffer (XOR-swizzled) per warp
+#define TC_SMEM_BYTES (TC_STAGES * TC_STAGE_BYTES + TC_EPI_BYTES + 256 + 1024)
 
 // ------------------------------------------------------------------------------------------------ PTX wrappers
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -81,8 +92,10 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* v) {
         "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
       : "r"(taddr)
       : "memory");
-  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
+// the registers written by tmem_ld32 may only be read after this (the first reader must be a memory operation: the
+// "memory" clobber is what keeps the compiler from hoisting it)
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // 4-element row-contiguous loads / stores of the output type
 __device__ __forceinline__ float4 ld4(const float* p) { return *reinterpret_cast<const float4*>(p); }
@@ -100,6 +113,33 @@ __device__ __forceinline__ void st4(bf16* p, float4 v) {
   *reinterpret_cast<uint2*>(p) = u;
 }
 
+// explicit shared-space 16-byte accesses (a pointer derived from the dynamic shared base through integer arithmetic is
+// "generic" to the compiler, which then emits slower generic ST / LD)
+__device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ void red_add_f32x4(float* gptr, float4 v) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(gptr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ void red_add_f32(float* gptr, float v) {
+  asm volatile("red.global.add.f32 [%0], %1;" ::"l"(gptr), "f"(v) : "memory");
+}
+
+// four consecutive elements in their storage type
+template <typename T> struct Raw4;
+template <> struct Raw4<float> { typedef float4 type; };
+template <> struct Raw4<bf16> { typedef uint2 type; };
+__device__ __forceinline__ float4 raw4_to_float4(float4 v) { return v; }
+__device__ __forceinline__ float4 raw4_to_float4(uint2 u) {
+  const __nv_bfloat162 a = *reinterpret_cast<const __nv_bfloat162*>(&u.x), b = *reinterpret_cast<const __nv_bfloat162*>(&u.y);
+  return make_float4(__low2float(a), __high2float(a), __low2float(b), __high2float(b));
+}
+
 // shared-memory matrix descriptor (cute::UMMA::SmemDescriptor), 128B swizzle, version 1 (Blackwell)
 __device__ __forceinline__ uint64_t make_sdesc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
   uint64_t d = 0;
@@ -113,7 +153,6 @@ __device__ __forceinline__ uint64_t make_sdesc(uint32_t saddr, uint32_t lbo_byte
 
 struct TcParams {
   int M, N, K;
-  int kb_per_split;        // K blocks (of TC_BK) per grid.z slice
   void* D; long long ldd;
   const float* bias; int act;
   const void* residual; long long ldr;
@@ -121,39 +160,188 @@ struct TcParams {
   int accumulate;          // D += result
   int atomic;              // split-K: red.global.add.f32
   SvpcDrop drop;           // dropout after the activation, before the residual (model.py:231, 287, 757)
+  // ---- work list (see tc_unit): every role of every CTA walks units blockIdx.x, blockIdx.x + gridDim.x, ...
+  int BN;                  // tile width (64 / 128 / 256)
+  int tiles_n;             // tiles along N
+  int split, kb_per;       // split-K slices per tile, K blocks (of TC_BK) per slice
+  int kb_total;
+  int main_tiles;          // tiles handled whole (x split); the remaining `tiles - main_tiles` are cut along N
+  int tail_s;              // ... into tail_s sub-tiles of width BN / tail_s each, so the last round is short
+  int total_units;
+  int dbg;                 // diagnostics only (SVPC_TC_DBG): bit0 no TMEM load, bit1 no epilogue math/stores, bit2 no staging, bit3 no chunk loop
 };
 
-template <int BN, bool A_MN, bool B_MN, int KSTAGES, typename TD>
-__global__ void __launch_bounds__(TC_THREADS, 2) gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA,
+struct TcUnit { int m0, n0, width, kb0, kb1; };
+
+// unit index -> (row block, column range, K-block range).  Full 128 x BN tiles first (split-K slices adjacent); the
+// tiles of the last, partial round are cut into narrower column slices so that every SM gets a (shorter) piece.
+__device__ __forceinline__ TcUnit tc_unit(const TcParams& p, int u) {
+  TcUnit w;
+  const int main_units = p.main_tiles * p.split;
+  int tile, ks = 0, sub = 0;
+  w.width = p.BN;
+  if (u < main_units) {
+    tile = u / p.split;
+    ks = u - tile * p.split;
+  } else {
+    const int r = u - main_units;
+    tile = p.main_tiles + r / p.tail_s;
+    sub = r % p.tail_s;
+    w.width = p.BN / p.tail_s;
+  }
+  const int tm = tile / p.tiles_n;
+  w.m0 = tm * TC_BM;
+  w.n0 = (tile - tm * p.tiles_n) * p.BN + sub * w.width;
+  w.kb0 = ks * p.kb_per;
+  w.kb1 = min(p.kb_total, w.kb0 + p.kb_per);
+  return w;
+}
+
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+template <int ACT>
+__device__ __forceinline__ float tc_act(float v) {
+  if (ACT == SVPC_ACT_RELU) return v > 0.f ? v : 0.f;
+  if (ACT == SVPC_ACT_GELU) return svpc_gelu(v);
+  if (ACT == SVPC_ACT_SIGMOID) return svpc_sigmoid(v);
+  return v;
+}
+
+// The warp's 32 x 32 fp32 transposition buffer: 16-byte slot (row r, column group g) lives at r * 8 + (g ^ (r & 7)), so
+// both the writes (lane = row, one column group at a time) and the reads (8 lanes per row) are bank-conflict free.
+__device__ __forceinline__ uint32_t epi_slot(int r, int g) { return (uint32_t)(r * 8 + (g ^ (r & 7))) * 16u; }   // byte offset
+
+// Epilogue of one 32 x 32 chunk: this lane owns column group g = lane & 7 (columns n .. n+3) of rows rsub, rsub + 4, ...
+// Vector path: all four columns in range, 16-byte aligned rows.  Loads (residual, accumulate) are issued for all 8 rows
+// before the first store so their latencies overlap.
+template <int ACT, bool DROP, typename TD>
+__device__ __forceinline__ void epi_vec(const TcParams& p, uint32_t stage, int mw, int n, int rsub, int g,
+                                        uint32_t dkey, float dinv) {
+  float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (p.bias) bv = *reinterpret_cast<const float4*>(p.bias + n);
+  const int m_first = mw + rsub;
+  const int rows = min(8, (p.M - m_first + 3) >> 2);       // rows m_first, m_first + 4, ... below M
+  TD* __restrict__ d0 = (TD*)p.D + (long long)m_first * p.ldd + n;
+  const long long dstep = 4 * p.ldd;
+#pragma unroll 1
+  for (int j0 = 0; j0 < 8; j0 += 4) {       // two batches of 4 rows: bounded register use, 4 loads in flight
+    typename Raw4<TD>::type rr[4];         // residual rows, still in the storage type (2 registers each for bf16)
+    if (p.residual) {
+      const TD* r0 = (const TD*)p.residual + (long long)(m_first + 4 * j0) * p.ldr + n;
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (j0 + j < rows) rr[j] = *reinterpret_cast<const typename Raw4<TD>::type*>(r0 + (long long)j * 4 * p.ldr);
+    }
+#pragma unroll
+    for (int jj = 0; jj < 4; ++jj) {
+      const int j = j0 + jj;
+      if (j >= rows) break;
+      const int r = j * 4 + rsub;
+      float4 x = lds128(stage + epi_slot(r, g));
+      x.x += bv.x; x.y += bv.y; x.z += bv.z; x.w += bv.w;
+      if (p.pre) st4((TD*)p.pre + (long long)(mw + r) * p.ldp + n, x);
+      x.x = tc_act<ACT>(x.x); x.y = tc_act<ACT>(x.y); x.z = tc_act<ACT>(x.z); x.w = tc_act<ACT>(x.w);
+      if (DROP) {
+        const unsigned long long e0 = (unsigned long long)(mw + r) * p.N + n;
+        if ((e0 & 1) == 0) {             // aligned pairs: one hash per two elements
+          float s0, s1;
+          svpc_drop_scale2(dkey, p.drop.p, dinv, e0, s0, s1);
+          x.x *= s0; x.y *= s1;
+          svpc_drop_scale2(dkey, p.drop.p, dinv, e0 + 2, s0, s1);
+          x.z *= s0; x.w *= s1;
+        } else {
+          x.x *= svpc_drop_scale(dkey, p.drop.p, dinv, e0); x.y *= svpc_drop_scale(dkey, p.drop.p, dinv, e0 + 1);
+          x.z *= svpc_drop_scale(dkey, p.drop.p, dinv, e0 + 2); x.w *= svpc_drop_scale(dkey, p.drop.p, dinv, e0 + 3);
+        }
+      }
+      if (p.residual) { const float4 r4 = raw4_to_float4(rr[jj]); x.x += r4.x; x.y += r4.y; x.z += r4.z; x.w += r4.w; }
+      if (p.accumulate) { const float4 dd = ld4(d0 + j * dstep); x.x += dd.x; x.y += dd.y; x.z += dd.z; x.w += dd.w; }
+      st4(d0 + j * dstep, x);
+    }
+  }
+}
+
+// Edge / unaligned path (N not a multiple of 4, odd row pitch, last partial columns): rare, kept out of line.
+template <typename TD>
+__device__ __forceinline__ void epi_scalar(const TcParams& p, uint32_t stage, int mw, int n, int rsub, int g, bool dropping,
+                                        uint32_t dkey, float dinv) {
+  TD* __restrict__ Dp = (TD*)p.D;
+  const TD* __restrict__ Rp = (const TD*)p.residual;
+  TD* __restrict__ Pp = (TD*)p.pre;
+#pragma unroll 1
+  for (int j = 0; j < 8; ++j) {
+    const int r = j * 4 + rsub;
+    const int m = mw + r;
+    if (m >= p.M) break;
+    const float4 x = lds128(stage + epi_slot(r, g));
+#pragma unroll 1
+    for (int e = 0; e < 4 && n + e < p.N; ++e) {
+      float y = e == 0 ? x.x : (e == 1 ? x.y : (e == 2 ? x.z : x.w));
+      if (p.bias) y += p.bias[n + e];
+      if (Pp) stf(Pp + (long long)m * p.ldp + n + e, y);
+      y = svpc_act(y, p.act);
+      if (dropping) y *= svpc_drop_scale(dkey, p.drop.p, dinv, (unsigned long long)m * p.N + n + e);
+      if (Rp) y += ldf(Rp + (long long)m * p.ldr + n + e);
+      TD* d = Dp + (long long)m * p.ldd + n + e;
+      if (p.accumulate) y += ldf(d);
+      stf(d, y);
+    }
+  }
+}
+
+// split-K partial sums: fp32 reductions into D (plain epilogue only)
+__device__ __forceinline__ void epi_atomic(const TcParams& p, uint32_t stage, int mw, int n, int rsub, int g, bool vec) {
+  float* Dp = reinterpret_cast<float*>(p.D);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int r = j * 4 + rsub;
+    const int m = mw + r;
+    if (m >= p.M) break;
+    const float4 x = lds128(stage + epi_slot(r, g));
+    float* d = Dp + (long long)m * p.ldd + n;
+    if (vec) {
+      red_add_f32x4(d, x);
+    } else {
+      red_add_f32(d, x.x);
+      if (n + 1 < p.N) red_add_f32(d + 1, x.y);
+      if (n + 2 < p.N) red_add_f32(d + 2, x.z);
+      if (n + 3 < p.N) red_add_f32(d + 3, x.w);
+    }
+  }
+}
+
+// Persistent kernel, one CTA per SM.  Shared memory: TC_STAGES x (A 128x64 + B 256x64) bf16 ring (48 KB per stage),
+// a 4 x 32 x 36 fp32 transposition buffer for the epilogue warps, barriers.  TMEM: 2 accumulators of 256 fp32 columns
+// (all 512 columns), so the epilogue of unit i drains one while the MMAs of unit i+1 fill the other.
+// ACT / DROP: the epilogue is specialised at compile time (a runtime switch over activations inside the row loop made
+// the epilogue, not the MMAs, the bottleneck of the K = 768 GEMMs).
+template <bool A_MN, bool B_MN, typename TD, int ACT, bool DROP>
+__global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA,
                                                                 const __grid_constant__ CUtensorMap tmB,
-                                                                const TcParams p) {
+                                                                const __grid_constant__ TcParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
-  constexpr uint32_t A_BYTES = TC_BM * TC_BK * 2;   // 16 KB
-  constexpr uint32_t B_BYTES = BN * TC_BK * 2;
-  constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-  uint64_t* full_bar = (uint64_t*)(smem + KSTAGES * STAGE_BYTES);
-  uint64_t* empty_bar = full_bar + KSTAGES;
-  uint64_t* tmem_full = empty_bar + KSTAGES;
-  uint32_t* tmem_slot = (uint32_t*)(tmem_full + 1);
+  float* epi_stage = reinterpret_cast<float*>(smem + TC_STAGES * TC_STAGE_BYTES);
+  uint64_t* full_bar = (uint64_t*)(smem + TC_STAGES * TC_STAGE_BYTES + TC_EPI_BYTES);
+  uint64_t* empty_bar = full_bar + TC_STAGES;
+  uint64_t* tmem_full = empty_bar + TC_STAGES;       // [2]
+  uint64_t* tmem_empty = tmem_full + 2;              // [2]
+  uint32_t* tmem_slot = (uint32_t*)(tmem_empty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int m0 = blockIdx.y * TC_BM, n0 = blockIdx.x * BN;
-  const int kb_total = (p.K + TC_BK - 1) / TC_BK;
-  const int kb0 = blockIdx.z * p.kb_per_split;
-  const int kb1 = min(kb_total, kb0 + p.kb_per_split);
-  const int nkb = kb1 - kb0;
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"((uint64_t)&tmA) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"((uint64_t)&tmB) : "memory");
   }
   if (warp == 1 && lane == 0) {
-    for (int s = 0; s < KSTAGES; ++s) { mbar_init(full_bar + s, 1); mbar_init(empty_bar + s, 1); }
-    mbar_init(tmem_full, 1);
+    for (int s = 0; s < TC_STAGES; ++s) { mbar_init(full_bar + s, 1); mbar_init(empty_bar + s, 1); }
+    for (int a = 0; a < 2; ++a) { mbar_init(tmem_full + a, 1); mbar_init(tmem_empty + a, TC_EPI_WARPS); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == 2) tmem_alloc(tmem_slot, BN);
+  if (warp == 2) tmem_alloc(tmem_slot, 512);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -162,152 +350,144 @@ __global__ void __launch_bounds__(TC_THREADS, 2) gemm_tc_kernel(const __grid_con
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
     if (lane == 0) {
-      for (int i = 0; i < nkb; ++i) {
-        const int s = i % KSTAGES, ph = (i / KSTAGES) & 1;
-        mbar_wait(empty_bar + s, ph ^ 1);
-        uint8_t* sa = smem + s * STAGE_BYTES;
-        uint8_t* sb = sa + A_BYTES;
-        mbar_expect_tx(full_bar + s, STAGE_BYTES);
-        const int k = (kb0 + i) * TC_BK;
-        if (A_MN) {
+      uint32_t it = 0;                                   // K blocks issued so far (ring position)
+      for (int u = blockIdx.x; u < p.total_units; u += gridDim.x) {
+        const TcUnit w = tc_unit(p, u);
+        if (w.n0 >= p.N) continue;
+        const uint32_t bytes = TC_A_BYTES + (uint32_t)w.width * (TC_BK * 2);
+        const int nbox = w.width >> 6;
+        for (int kb = w.kb0; kb < w.kb1; ++kb, ++it) {
+          const uint32_t s = it % TC_STAGES, ph = (it / TC_STAGES) & 1;
+          mbar_wait(empty_bar + s, ph ^ 1);
+          uint8_t* sa = smem + s * TC_STAGE_BYTES;
+          uint8_t* sb = sa + TC_A_BYTES;
+          mbar_expect_tx(full_bar + s, bytes);
+          const int k = kb * TC_BK;
+          if (A_MN) {
 #pragma unroll
-          for (int j = 0; j < TC_BM / 64; ++j) tma_load_2d(sa + j * (64 * TC_BK * 2), &tmA, full_bar + s, m0 + j * 64, k);
-        } else {
-          tma_load_2d(sa, &tmA, full_bar + s, k, m0);
-        }
-        if (B_MN) {
-#pragma unroll
-          for (int j = 0; j < BN / 64; ++j) tma_load_2d(sb + j * (64 * TC_BK * 2), &tmB, full_bar + s, n0 + j * 64, k);
-        } else {
-          tma_load_2d(sb, &tmB, full_bar + s, k, n0);
+            for (int j = 0; j < TC_BM / 64; ++j) tma_load_2d(sa + j * (64 * TC_BK * 2), &tmA, full_bar + s, w.m0 + j * 64, k);
+          } else {
+            tma_load_2d(sa, &tmA, full_bar + s, k, w.m0);
+          }
+          // B in 64-column boxes (8 KB each): K-major boxes stack into one [width][64] swizzled tile, MN-major boxes are
+          // the 64-wide N blocks the descriptor strides over
+          for (int j = 0; j < nbox; ++j) {
+            if (B_MN) tma_load_2d(sb + j * (64 * TC_BK * 2), &tmB, full_bar + s, w.n0 + j * 64, k);
+            else tma_load_2d(sb + j * (64 * TC_BK * 2), &tmB, full_bar + s, k, w.n0 + j * 64);
+          }
         }
       }
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
     if (lane == 0) {
-      // instruction descriptor: fp32 accumulate, bf16 x bf16, majors, N>>3, M>>4 (cute::UMMA::InstrDescriptor)
-      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((A_MN ? 1u : 0u) << 15) | ((B_MN ? 1u : 0u) << 16) |
-                             ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
-      for (int i = 0; i < nkb; ++i) {
-        const int s = i % KSTAGES, ph = (i / KSTAGES) & 1;
-        mbar_wait(full_bar + s, ph);
+      uint32_t it = 0, ui = 0;
+      for (int u = blockIdx.x; u < p.total_units; u += gridDim.x) {
+        const TcUnit w = tc_unit(p, u);
+        if (w.n0 >= p.N) continue;
+        const uint32_t acc = ui & 1, aph = (ui >> 1) & 1;
+        ++ui;
+        mbar_wait(tmem_empty + acc, aph ^ 1);            // epilogue has drained this accumulator
         tc_fence_after();
-        const uint32_t sa = smem_u32(smem + s * STAGE_BYTES);
-        const uint32_t sb = sa + A_BYTES;
+        // instruction descriptor: fp32 accumulate, bf16 x bf16, majors, N>>3, M>>4 (cute::UMMA::InstrDescriptor)
+        const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((A_MN ? 1u : 0u) << 15) | ((B_MN ? 1u : 0u) << 16) |
+                               ((uint32_t)(w.width >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
+        const uint32_t tacc = tmem_base + acc * TC_BN_MAX;
+        for (int kb = w.kb0; kb < w.kb1; ++kb, ++it) {
+          const uint32_t s = it % TC_STAGES, ph = (it / TC_STAGES) & 1;
+          mbar_wait(full_bar + s, ph);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + s * TC_STAGE_BYTES);
+          const uint32_t sb = sa + TC_A_BYTES;
 #pragma unroll
-        for (int k = 0; k < TC_BK / TC_UMMA_K; ++k) {
-          // K-major: 8-row groups 1024 B apart, +32 B per K step inside the swizzle row.
-          // MN-major: 64-wide MN blocks (TC_BK * 128 B apart, LBO), 8-k groups 1024 B apart (SBO), +2048 B per K step.
-          const uint64_t ad = A_MN ? make_sdesc(sa + k * (TC_UMMA_K * 128), TC_BK * 128, 1024)
-                                   : make_sdesc(sa + k * (TC_UMMA_K * 2), 16, 1024);
-          const uint64_t bd = B_MN ? make_sdesc(sb + k * (TC_UMMA_K * 128), TC_BK * 128, 1024)
-                                   : make_sdesc(sb + k * (TC_UMMA_K * 2), 16, 1024);
-          umma_f16(tmem_base, ad, bd, idesc, (i > 0 || k > 0) ? 1u : 0u);
+          for (int k = 0; k < TC_BK / TC_UMMA_K; ++k) {
+            // K-major: 8-row groups 1024 B apart, +32 B per K step inside the swizzle row.
+            // MN-major: 64-wide MN blocks (TC_BK * 128 B apart, LBO), 8-k groups 1024 B apart (SBO), +2048 B per K step.
+            const uint64_t ad = A_MN ? make_sdesc(sa + k * (TC_UMMA_K * 128), TC_BK * 128, 1024)
+                                     : make_sdesc(sa + k * (TC_UMMA_K * 2), 16, 1024);
+            const uint64_t bd = B_MN ? make_sdesc(sb + k * (TC_UMMA_K * 128), TC_BK * 128, 1024)
+                                     : make_sdesc(sb + k * (TC_UMMA_K * 2), 16, 1024);
+            umma_f16(tacc, ad, bd, idesc, (kb > w.kb0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit(empty_bar + s);      // ring slot free once these MMAs have read it
         }
-        umma_commit(empty_bar + s);      // ring slot free once these MMAs have read it
+        umma_commit(tmem_full + acc);      // accumulator complete
       }
-      umma_commit(tmem_full);            // accumulator complete
     }
   } else {
-    // ------------------------------------------------------------------ epilogue (warps 2..5)
-    // Phase 1: TMEM -> registers (lane = row) -> shared memory (the ring is free once tmem_full has fired).
-    // Phase 2: each warp re-reads its 32 rows with lanes along the columns, so bias / activation / residual /
-    //          accumulate and the stores are row-contiguous: 512 B (fp32) or 256 B (bf16) per warp instruction.
+    // ------------------------------------------------------------------ epilogue (warps 2 .. 2 + TC_EPI_WARPS)
+    // Two warps per TMEM lane quarter, each taking every other 32-column chunk.  Per chunk: TMEM -> registers
+    // (lane = row) -> swizzled shared memory -> re-read with lanes along the columns, so bias / activation / dropout /
+    // residual / accumulate and the stores are row-contiguous (4 rows x 128 B (fp32) or 64 B (bf16) per warp
+    // instruction); the other warp of the scheduler covers the TMEM / memory latencies.
     const int q = warp & 3;              // TMEM lane quarter this warp may read
-    if (nkb > 0) {
-      mbar_wait(tmem_full, 0);
-      tc_fence_after();
-    }
-    constexpr int LDS = BN + 4;          // padded row stride (floats): conflict-free float4 writes by 8-lane phases
-    float* stage = reinterpret_cast<float*>(smem) + (size_t)q * 32 * LDS;
-#pragma unroll 1
-    for (int c = 0; c < BN / 32; ++c) {
-      uint32_t v[32];
-      if (nkb > 0) {
-        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(c * 32), v);
-      } else {
-#pragma unroll
-        for (int jj = 0; jj < 32; ++jj) v[jj] = 0u;
-      }
-      float* dst = stage + (size_t)lane * LDS + c * 32;
-#pragma unroll
-      for (int jj = 0; jj < 32; jj += 4)
-        *reinterpret_cast<uint4*>(dst + jj) = make_uint4(v[jj], v[jj + 1], v[jj + 2], v[jj + 3]);
-    }
-    tc_fence_before();
-    __syncwarp();
-    TD* __restrict__ Dp = (TD*)p.D;
-    const TD* __restrict__ Rp = (const TD*)p.residual;
-    TD* __restrict__ Pp = (TD*)p.pre;
-    const int mw = m0 + q * 32;
-    constexpr int VEC_ROWS = 128 / BN;   // rows covered by one warp pass in the vector path (1 for BN=128, 2 for BN=64)
-    const bool vec_ok = !p.atomic && (n0 + BN <= p.N) && (p.ldd % 4 == 0) && (((uintptr_t)Dp & 15) == 0) &&
-                        (!Rp || (p.ldr % 4 == 0 && ((uintptr_t)Rp & 15) == 0)) &&
-                        (!Pp || (p.ldp % 4 == 0 && ((uintptr_t)Pp & 15) == 0)) && (((uintptr_t)p.bias & 15) == 0);
-    const bool dropping = p.drop.seed != nullptr && p.drop.p > 0.f;
-    const uint32_t dkey = svpc_drop_key(p.drop);
+    const int ew = warp - 2;             // epilogue warp index
+    const int half = ew >> 2;            // which chunks of the quarter: half, half + 2, ...
+    constexpr int CSTEP = TC_EPI_WARPS / 4;
+    const uint32_t stage = smem_u32(epi_stage) + (uint32_t)ew * (32 * 32 * 4);
+    const bool vec_all = (p.ldd % 4 == 0) && (((uintptr_t)p.D & 15) == 0) &&
+                         (!p.residual || (p.ldr % 4 == 0 && ((uintptr_t)p.residual & 15) == 0)) &&
+                         (!p.pre || (p.ldp % 4 == 0 && ((uintptr_t)p.pre & 15) == 0)) && (((uintptr_t)p.bias & 15) == 0);
+    const bool dropping = DROP;
+    const uint32_t dkey = DROP ? svpc_drop_key(p.drop) : 0u;
     const float dinv = dropping ? 1.f / (1.f - p.drop.p) : 1.f;
-    if (vec_ok) {
-      const int cl = (lane % (BN / 4)) * 4;            // this lane's 4 columns inside the tile
-      const int rsub = lane / (BN / 4);                // row inside the pass
-      float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (p.bias) bv = *reinterpret_cast<const float4*>(p.bias + n0 + cl);
-#pragma unroll 4
-      for (int r = rsub; r < 32; r += VEC_ROWS) {
-        const int m = mw + r;
-        if (m >= p.M) break;
-        float4 x = *reinterpret_cast<const float4*>(stage + (size_t)r * LDS + cl);
-        x.x += bv.x; x.y += bv.y; x.z += bv.z; x.w += bv.w;
-        if (Pp) st4(Pp + (long long)m * p.ldp + n0 + cl, x);
-        x.x = svpc_act(x.x, p.act); x.y = svpc_act(x.y, p.act); x.z = svpc_act(x.z, p.act); x.w = svpc_act(x.w, p.act);
-        if (dropping) {
-          const unsigned long long e0 = (unsigned long long)m * p.N + n0 + cl;
-          if ((e0 & 1) == 0) {             // aligned pairs: one hash per two elements
-            float s0, s1;
-            svpc_drop_scale2(dkey, p.drop.p, dinv, e0, s0, s1);
-            x.x *= s0; x.y *= s1;
-            svpc_drop_scale2(dkey, p.drop.p, dinv, e0 + 2, s0, s1);
-            x.z *= s0; x.w *= s1;
+    const int g = lane & 7;              // this lane's column group (4 columns) inside a chunk
+    const int rsub = lane >> 3;          // row inside a 4-row pass
+    uint32_t ui = 0;
+    for (int u = blockIdx.x; u < p.total_units; u += gridDim.x) {
+      const TcUnit w = tc_unit(p, u);
+      if (w.n0 >= p.N) continue;
+      const uint32_t acc = ui & 1, aph = (ui >> 1) & 1;
+      ++ui;
+      mbar_wait(tmem_full + acc, aph);
+      tc_fence_after();
+      const int mw = w.m0 + q * 32;
+      const int nchunks = w.width >> 5;
+      const uint32_t trow = tmem_base + acc * TC_BN_MAX + ((uint32_t)(q * 32) << 16);
+#pragma unroll 1
+      for (int c = half; c < nchunks; c += CSTEP) {
+        if (p.dbg & 8) break;
+        {
+          uint32_t v[32];
+          if (!(p.dbg & 1)) {
+            tmem_ld32(trow + (uint32_t)(c * 32), v);
+            tmem_ld_wait();
           } else {
-            x.x *= svpc_drop_scale(dkey, p.drop.p, dinv, e0); x.y *= svpc_drop_scale(dkey, p.drop.p, dinv, e0 + 1);
-            x.z *= svpc_drop_scale(dkey, p.drop.p, dinv, e0 + 2); x.w *= svpc_drop_scale(dkey, p.drop.p, dinv, e0 + 3);
-          }
-        }
-        if (Rp) { const float4 rr = ld4(Rp + (long long)m * p.ldr + n0 + cl); x.x += rr.x; x.y += rr.y; x.z += rr.z; x.w += rr.w; }
-        TD* d = Dp + (long long)m * p.ldd + n0 + cl;
-        if (p.accumulate) { const float4 dd = ld4(d); x.x += dd.x; x.y += dd.y; x.z += dd.z; x.w += dd.w; }
-        st4(d, x);
-      }
-    } else {
-      for (int r = 0; r < 32; ++r) {
-        const int m = mw + r;
-        if (m >= p.M) break;
 #pragma unroll
-        for (int cc = 0; cc < BN / 32; ++cc) {
-          const int n = n0 + cc * 32 + lane;
-          if (n >= p.N) continue;
-          float x = stage[(size_t)r * LDS + cc * 32 + lane];
-          if (p.atomic) {
-            atomicAdd(reinterpret_cast<float*>(Dp) + (long long)m * p.ldd + n, x);
-          } else {
-            if (p.bias) x += p.bias[n];
-            if (Pp) stf(Pp + (long long)m * p.ldp + n, x);
-            x = svpc_act(x, p.act);
-            if (dropping) x *= svpc_drop_scale(dkey, p.drop.p, dinv, (unsigned long long)m * p.N + n);
-            if (Rp) x += ldf(Rp + (long long)m * p.ldr + n);
-            TD* d = Dp + (long long)m * p.ldd + n;
-            if (p.accumulate) x += ldf(d);
-            stf(d, x);
+            for (int jj = 0; jj < 32; ++jj) v[jj] = 0u;
+          }
+          if (!(p.dbg & 4)) {
+#pragma unroll
+            for (int jj = 0; jj < 8; ++jj)
+              sts128(stage + epi_slot(lane, jj), v[4 * jj], v[4 * jj + 1], v[4 * jj + 2], v[4 * jj + 3]);
           }
         }
+        __syncwarp();
+        if (p.dbg & 2) continue;
+        const int nb = w.n0 + c * 32;
+        const int n = nb + g * 4;
+        if (n < p.N && mw < p.M) {
+          if (p.atomic) {
+            epi_atomic(p, stage, mw, n, rsub, g, vec_all && (n + 4 <= p.N));
+          } else if (vec_all && (n + 4 <= p.N)) {
+            epi_vec<ACT, DROP, TD>(p, stage, mw, n, rsub, g, dkey, dinv);
+          } else {
+            epi_scalar<TD>(p, stage, mw, n, rsub, g, dropping, dkey, dinv);
+          }
+        }
+        __syncwarp();                      // the transposition buffer is rewritten by the next chunk
       }
+      // every column this warp reads of the accumulator has left TMEM (the last tmem_ld_wait above): hand it back
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tmem_empty + acc);
     }
   }
+  tc_fence_before();
   __syncthreads();
   if (warp == 2) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, BN);
+    tmem_dealloc(tmem_base, 512);
   }
 }
 
@@ -359,62 +539,102 @@ int svpc_gemm_tc_eligible(int M, int N, int K, int dtA, long long sa_m, long lon
   return 1;
 }
 
-template <int BN, bool A_MN, bool B_MN, typename TD>
-static int launch_cfg(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, dim3 grid, cudaStream_t st) {
-  constexpr int KSTAGES = BN == 128 ? 3 : 4;   // 96 KB per CTA: two CTAs per SM, one's epilogue under the other's main loop
-  constexpr size_t smem = (size_t)KSTAGES * (TC_BM * TC_BK * 2 + BN * TC_BK * 2) + 1024 + 256;
-  auto kern = gemm_tc_kernel<BN, A_MN, B_MN, KSTAGES, TD>;
+template <bool A_MN, bool B_MN, typename TD, int ACT, bool DROP>
+static int launch_cfg(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, int grid, cudaStream_t st) {
+  auto kern = gemm_tc_kernel<A_MN, B_MN, TD, ACT, DROP>;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_BYTES);
     attr_set = true;
   }
-  kern<<<grid, TC_THREADS, smem, st>>>(ta, tb, p);
+  kern<<<grid, TC_THREADS, TC_SMEM_BYTES, st>>>(ta, tb, p);
   return svpc_check_launch("gemm_tc");
 }
 
-template <int BN, typename TD>
-static int launch_major(bool a_mn, bool b_mn, const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, dim3 grid,
+template <bool A_MN, bool B_MN, typename TD>
+static int launch_epi(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, int grid, cudaStream_t st) {
+  const bool drop = p.drop.seed != nullptr && p.drop.p > 0.f;
+#define TC_CASE(A) \
+  case A: return drop ? launch_cfg<A_MN, B_MN, TD, A, true>(ta, tb, p, grid, st) : launch_cfg<A_MN, B_MN, TD, A, false>(ta, tb, p, grid, st);
+  switch (p.act) {
+    TC_CASE(SVPC_ACT_RELU)
+    TC_CASE(SVPC_ACT_GELU)
+    TC_CASE(SVPC_ACT_SIGMOID)
+    default: break;
+  }
+  return drop ? launch_cfg<A_MN, B_MN, TD, SVPC_ACT_NONE, true>(ta, tb, p, grid, st)
+              : launch_cfg<A_MN, B_MN, TD, SVPC_ACT_NONE, false>(ta, tb, p, grid, st);
+#undef TC_CASE
+}
+
+template <typename TD>
+static int launch_major(bool a_mn, bool b_mn, const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, int grid,
                         cudaStream_t st) {
-  if (!a_mn && !b_mn) return launch_cfg<BN, false, false, TD>(ta, tb, p, grid, st);
-  if (!a_mn && b_mn) return launch_cfg<BN, false, true, TD>(ta, tb, p, grid, st);
-  if (a_mn && !b_mn) return launch_cfg<BN, true, false, TD>(ta, tb, p, grid, st);
-  return launch_cfg<BN, true, true, TD>(ta, tb, p, grid, st);
+  if (!a_mn && !b_mn) return launch_epi<false, false, TD>(ta, tb, p, grid, st);
+  if (!a_mn && b_mn) return launch_epi<false, true, TD>(ta, tb, p, grid, st);
+  if (a_mn && !b_mn) return launch_epi<true, false, TD>(ta, tb, p, grid, st);
+  return launch_epi<true, true, TD>(ta, tb, p, grid, st);
+}
+
+// tile width: the padded width ceil(N / BN) * BN, weighted by how much worse a narrower UMMA uses the operand bandwidth
+static int choose_bn(int N) {
+  const int cand[3] = {256, 128, 64};
+  const double pen[3] = {1.0, 1.05, 1.25};
+  int best = 256;
+  double best_cost = 1e30;
+  for (int i = 0; i < 3; ++i) {
+    const double c = (double)svpc_cdiv(N, cand[i]) * cand[i] * pen[i];
+    if (c < best_cost) { best_cost = c; best = cand[i]; }
+  }
+  return best;
 }
 
 int svpc_gemm_tc_launch(int M, int N, int K, const void* A, long long sa_m, long long sa_k, const void* B, long long sb_n,
                         long long sb_k, void* D, int dtD, long long ldd, const float* bias, int act, const void* residual,
                         long long ldr, void* pre, long long ldp, int accumulate, SvpcDrop drop, cudaStream_t st) {
   const bool a_mn = sa_k != 1, b_mn = sb_k != 1;
-  const int BN = (N <= 64) ? 64 : 128;
+  const int BN = choose_bn(N);
   CUtensorMap ta, tb;
   int rc;
   if (a_mn) rc = make_map(&ta, A, M, K, sa_k, 64, TC_BK); else rc = make_map(&ta, A, K, M, sa_m, TC_BK, TC_BM);
   if (rc) return rc;
-  if (b_mn) rc = make_map(&tb, B, N, K, sb_k, 64, TC_BK); else rc = make_map(&tb, B, K, N, sb_n, TC_BK, BN);
+  if (b_mn) rc = make_map(&tb, B, N, K, sb_k, 64, TC_BK); else rc = make_map(&tb, B, K, N, sb_n, TC_BK, 64);
   if (rc) return rc;
-  const int tiles_m = svpc_cdiv(M, TC_BM), tiles_n = svpc_cdiv(N, BN);
+  const int G = SVPC_NUM_SMS;
+  const int tiles_m = svpc_cdiv(M, TC_BM), tiles_n = svpc_cdiv(N, BN), tiles = tiles_m * tiles_n;
   const int kb_total = svpc_cdiv(K, TC_BK);
+  SVPC_REQUIRE(kb_total > 0, "gemm_tc: K == 0");
   int split = 1;
   const bool plain = !bias && act == SVPC_ACT_NONE && !residual && !pre && dtD == SVPC_F32 && !drop.seed;
-  if (plain && tiles_m * tiles_n < SVPC_NUM_SMS / 2 && kb_total >= 16) {
-    split = svpc_imin(svpc_imin(SVPC_NUM_SMS / (tiles_m * tiles_n), kb_total / 8), 32);
-    if (split < 1) split = 1;
+  if (plain && tiles * 2 <= G && kb_total >= 16) {
+    // split-K: rounds of G units x K blocks per unit, plus ~4 K-block-times of atomic epilogue per unit
+    long long best = (long long)svpc_cdiv(tiles, G) * (kb_total + 4);
+    for (int sp = 2; sp <= 32 && kb_total / sp >= 8; ++sp) {
+      const long long c = (long long)svpc_cdiv((long long)tiles * sp, G) * (svpc_cdiv(kb_total, sp) + 4);
+      if (c < best) { best = c; split = sp; }
+    }
   }
-  int kb_per = svpc_cdiv(kb_total, split);
+  const int kb_per = svpc_cdiv(kb_total, split);
   split = svpc_cdiv(kb_total, kb_per);
-  TcParams p{M, N, K, kb_per, D, ldd, bias, act, residual, ldr, pre, ldp, accumulate, split > 1 ? 1 : 0, drop};
+  int main_tiles = tiles, tail_s = 1;
+  if (split == 1) {
+    const int rem = tiles % G;
+    if (rem > 0) {
+      while (tail_s * 2 <= BN / 64 && (long long)rem * tail_s * 2 <= G) tail_s *= 2;
+      if (tail_s > 1) main_tiles = tiles - rem;
+    }
+  }
+  const int total_units = main_tiles * split + (tiles - main_tiles) * tail_s;
+  TcParams p{M, N, K, D, ldd, bias, act, residual, ldr, pre, ldp, accumulate, split > 1 ? 1 : 0, drop,
+             BN, tiles_n, split, kb_per, kb_total, main_tiles, tail_s, total_units, 0};
+  if (const char* e = getenv("SVPC_TC_DBG")) p.dbg = atoi(e);
   if (split > 1 && !accumulate) {
     cudaError_t e = cudaMemset2DAsync(D, (size_t)ldd * 4, 0, (size_t)N * 4, (size_t)M, st);
     if (e != cudaSuccess) { svpc_set_error("gemm_tc: memset2D: %s", cudaGetErrorString(e)); return SVPC_ERR_CUDA; }
   }
-  dim3 grid(tiles_n, tiles_m, split);
-  if (dtD == SVPC_F32) {
-    return BN == 64 ? launch_major<64, float>(a_mn, b_mn, ta, tb, p, grid, st) : launch_major<128, float>(a_mn, b_mn, ta, tb, p, grid, st);
-  } else if (dtD == SVPC_BF16) {
-    return BN == 64 ? launch_major<64, bf16>(a_mn, b_mn, ta, tb, p, grid, st) : launch_major<128, bf16>(a_mn, b_mn, ta, tb, p, grid, st);
-  }
+  const int grid = svpc_imin(total_units, G);
+  if (dtD == SVPC_F32) return launch_major<float>(a_mn, b_mn, ta, tb, p, grid, st);
+  if (dtD == SVPC_BF16) return launch_major<bf16>(a_mn, b_mn, ta, tb, p, grid, st);
   svpc_set_error("gemm_tc: bad output dtype %d", dtD);
   return SVPC_ERR_ARG;
 }

@@ -103,6 +103,74 @@ class GraphedTrainStep:
         self.graph.replay()
         return self.loss
 
+    # ------------------------------------------------------------------------------------------
+    # host -> device input pipeline: the upload of batch i+1 overlaps the replay of batch i
+    def prefetch(self, args, gumbel_noise=None):
+        """Start the H2D copy of a batch from pinned host memory into a staging set on a dedicated copy stream.  The
+        next ``run_prefetched()`` moves it into the static buffers (one D2D pass) and replays the step, so the upload of
+        the following batch can already be in flight while this one computes."""
+        self._pf = getattr(self, "_pf", None) or _Prefetcher(self.device)
+        pairs = []
+        for dst, src in zip(self.static, args):
+            if isinstance(dst, torch.Tensor):
+                pairs.append((dst, src))
+            elif _is_tensor_list(dst):
+                pairs += list(zip(dst, src))
+        if gumbel_noise is not None and self.noise is not None:
+            pairs += list(zip(self.noise, gumbel_noise))
+        self._pf.stage(pairs)
+        self._pf_dict = args[9]
+
+    def run_prefetched(self):
+        self._pf.commit()
+        d = self._pf_dict
+        if d is not None and d is not self.static[9] and self.plan.mode != "video":
+            if not self.plan.update_tokens(d):
+                raise ValueError("ingr_id_dict has a different number of copy tokens than the captured batch: re-capture")
+            self.static[9] = d
+        return self.run()
+
+
+class _Prefetcher:
+    """Double buffer between pinned host memory and the static inputs of a captured graph.
+
+    ``stage``  (copy stream): waits until the previous staging contents were consumed, then H2D into the staging set.
+    ``commit`` (compute stream): waits for the staged copy, D2D staging -> static (HBM-speed, ~0.1 ms for 300 MB)."""
+
+    def __init__(self, device):
+        self.device = device
+        self.stream = torch.cuda.Stream(device=device)
+        self.staged = torch.cuda.Event()
+        self.consumed = None
+        self.bufs = {}
+        self.pairs = None
+
+    def stage(self, pairs):
+        cur = torch.cuda.current_stream(self.device)
+        if self.consumed is not None:
+            self.stream.wait_event(self.consumed)
+        else:
+            self.stream.wait_stream(cur)
+        staged = []
+        with torch.cuda.stream(self.stream):
+            for dst, src in pairs:
+                b = self.bufs.get(dst.data_ptr())
+                if b is None:
+                    b = self.bufs[dst.data_ptr()] = torch.empty_like(dst)
+                b.copy_(src, non_blocking=True)
+                staged.append((dst, b))
+            self.staged.record(self.stream)
+        self.pairs = staged
+
+    def commit(self):
+        assert self.pairs is not None, "commit() without a staged batch"
+        cur = torch.cuda.current_stream(self.device)
+        cur.wait_event(self.staged)
+        torch._foreach_copy_([d for d, _ in self.pairs], [b for _, b in self.pairs])
+        self.consumed = torch.cuda.Event()
+        self.consumed.record(cur)
+        self.pairs = None
+
 
 class GraphedDecoder:
     """CUDA-graph replay of ``svpc_b200.decode.greedy_decode`` for one batch signature (clips / ingredients / OOV words
@@ -171,3 +239,23 @@ class GraphedDecoder:
     def run(self):
         self.graph.replay()
         return self.out
+
+    def prefetch(self, inputs):
+        """H2D of a batch on the copy stream into a staging set (see GraphedTrainStep.prefetch)."""
+        self._pf = getattr(self, "_pf", None) or _Prefetcher(self.device)
+        pairs = []
+        for i in self.TENSOR_LISTS:
+            pairs += list(zip(self.static[i], inputs[i]))
+        for i in self.TENSORS:
+            pairs.append((self.static[i], torch.as_tensor(inputs[i])))
+        self._pf.stage(pairs)
+        self._pf_dict = inputs[7]
+
+    def run_prefetched(self):
+        self._pf.commit()
+        d = self._pf_dict
+        if d is not None and d is not self.static[7] and self.plan.mode != "video" and self.model.config.model_mode != "video":
+            if not self.plan.update_tokens(d):
+                raise ValueError("ingr_id_dict has a different number of copy tokens than the captured batch: re-capture")
+            self.static[7] = d
+        return self.run()

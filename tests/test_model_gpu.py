@@ -138,3 +138,32 @@ def test_graph_replay_matches_eager(mode, dtype):
         else:          # atomics (split-K, scatter) reorder fp32 sums: compare against the tensor's / the global scale
             err = float((p.grad - grads[n]).abs().max())
             assert err <= 1e-4 * max(float(grads[n].abs().max()), 1e-3 * gscale), (n, err)
+
+
+def test_prefetch_pipeline_matches_load():
+    """The host->device input pipeline (copy stream + staging set, GraphedTrainStep.prefetch / run_prefetched) feeds the
+    captured step the same inputs as a synchronous load(): alternating two different batches gives each one's own loss."""
+    from svpc_b200.graph import GraphedTrainStep
+    cfg, sd, batch, gold = load_case("ragged", "full")
+    m = build(cfg, sd, torch.float32)
+    other = synth.make_batch(cfg, **{**CASES["ragged"][1], "seed": 99})
+    if m.plan_signature(other["batch_step_num"], other["ingr_id_dict"], other["extra_zeros"]) != \
+            m.plan_signature(batch["batch_step_num"], batch["ingr_id_dict"], batch["extra_zeros"]):
+        pytest.skip("no second batch with the same signature")
+    step = GraphedTrainStep(m, forward_args(other, DEV), gumbel_noise=[g.to(DEV) for g in other["gumbel"]])
+    pin = lambda x: x.pin_memory() if isinstance(x, torch.Tensor) else ([t.pin_memory() for t in x] if isinstance(x, list) and x and isinstance(x[0], torch.Tensor) else x)
+    hosts = [([pin(a) for a in forward_args(b)], [g.pin_memory() for g in b["gumbel"]]) for b in (batch, other)]
+    want = []
+    for a, g in hosts:
+        step.load(a, g)
+        want.append(float(step.run()))
+    assert abs(want[0] - want[1]) > 1e-3 * abs(want[0])          # the two batches are distinguishable
+    got = []
+    step.prefetch(*hosts[0])
+    for i in range(6):
+        loss = step.run_prefetched()
+        if i + 1 < 6:
+            step.prefetch(*hosts[(i + 1) % 2])                   # upload of the next batch overlaps this replay
+        got.append(float(loss))
+    for i, v in enumerate(got):
+        assert abs(v - want[i % 2]) <= 1e-6 * abs(want[i % 2]), (i, v, want)
