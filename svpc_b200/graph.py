@@ -26,6 +26,68 @@ def _is_tensor_list(x):
     return isinstance(x, (list, tuple)) and len(x) > 0 and isinstance(x[0], torch.Tensor)
 
 
+class InputArena:
+    """One contiguous buffer for every tensor input of a step, three times: pinned host memory (the data loader collates
+    straight into ``host_views``), a device staging copy (written by ONE H2D memcpy on the copy stream) and the static
+    device copy a captured graph reads (refreshed by ONE D2D memcpy).  Replaces ~90 per-tensor copies per step
+    (reference train.py:91-112 `prepare_batch_inputs` issues one .cuda() per tensor)."""
+
+    ALIGN = 256
+
+    def __init__(self, tensors, device):
+        self.device = device
+        self.spec, off = [], 0
+        for t in tensors:
+            n = t.numel() * t.element_size()
+            self.spec.append((off, tuple(t.shape), t.dtype))
+            off += (n + self.ALIGN - 1) // self.ALIGN * self.ALIGN
+        self.nbytes = off
+        self.host = torch.empty(off, dtype=torch.uint8).pin_memory()
+        self.stage = torch.empty(off, dtype=torch.uint8, device=device)
+        self.static = torch.empty(off, dtype=torch.uint8, device=device)
+
+    def _views(self, buf):
+        out = []
+        for off, shape, dtype in self.spec:
+            n = 1
+            for d in shape:
+                n *= d
+            nb = n * torch.empty((), dtype=dtype).element_size()
+            out.append(buf[off:off + nb].view(dtype).view(shape))
+        return out
+
+    def host_views(self):
+        return self._views(self.host)
+
+    def static_views(self):
+        return self._views(self.static)
+
+
+def _flatten(args, noise):
+    """(tensors in a fixed order, rebuild(list of tensors) -> (args, noise))."""
+    flat, slots = [], []
+    for i, a in enumerate(args):
+        if isinstance(a, torch.Tensor):
+            slots.append(("t", i, len(flat)))
+            flat.append(a)
+        elif _is_tensor_list(a):
+            slots.append(("l", i, len(flat), len(a)))
+            flat += list(a)
+    n0 = len(flat)
+    if noise is not None:
+        flat += list(noise)
+
+    def rebuild(ts):
+        out = list(args)
+        for sl in slots:
+            if sl[0] == "t":
+                out[sl[1]] = ts[sl[2]]
+            else:
+                out[sl[1]] = list(ts[sl[2]:sl[2] + sl[3]])
+        return out, (None if noise is None else list(ts[n0:]))
+    return flat, rebuild
+
+
 class GraphedTrainStep:
     N_POS = 13      # positional arguments of StateAwareRecursiveTransformer.forward (reference model.py:1027-1030)
 
@@ -35,8 +97,13 @@ class GraphedTrainStep:
         dev = next(model.parameters()).device
         assert dev.type == "cuda", "GraphedTrainStep needs a CUDA model"
         self.device = dev
-        self.static = [self._clone(a) for a in example_args]
-        self.noise = None if gumbel_noise is None else [g.to(dev).clone() for g in gumbel_noise]
+        flat, rebuild = _flatten(list(example_args), gumbel_noise)
+        self.arena = InputArena(flat, dev)
+        sv = self.arena.static_views()
+        for d, t in zip(sv, flat):
+            d.copy_(t)
+        self.static, self.noise = rebuild(sv)
+        self._rebuild = rebuild
         a = self.static
         self.plan = model.make_plan(a[8], a[9], a[10], a[11], dev)
         self.sig = self.plan.signature()
@@ -105,11 +172,25 @@ class GraphedTrainStep:
 
     # ------------------------------------------------------------------------------------------
     # host -> device input pipeline: the upload of batch i+1 overlaps the replay of batch i
+    def host_inputs(self):
+        """(args, noise) whose tensors are views of the arena's pinned host buffer: a loader that collates into them
+        makes ``prefetch`` a single H2D memcpy."""
+        if getattr(self, "_host_args", None) is None:
+            self._host_args = self._rebuild(self.arena.host_views())
+            self._host_args[0][9] = self.static[9]
+        return self._host_args
+
     def prefetch(self, args, gumbel_noise=None):
         """Start the H2D copy of a batch from pinned host memory into a staging set on a dedicated copy stream.  The
         next ``run_prefetched()`` moves it into the static buffers (one D2D pass) and replays the step, so the upload of
         the following batch can already be in flight while this one computes."""
         self._pf = getattr(self, "_pf", None) or _Prefetcher(self.device)
+        ha = getattr(self, "_host_args", None)
+        if ha is not None and args is ha[0] and (gumbel_noise is None or gumbel_noise is ha[1]):
+            # the batch already sits in the pinned arena: one H2D, one D2D
+            self._pf.stage([(self.arena.static, self.arena.host)], bufs=[self.arena.stage])
+            self._pf_dict = args[9]
+            return
         pairs = []
         for dst, src in zip(self.static, args):
             if isinstance(dst, torch.Tensor):
@@ -145,7 +226,7 @@ class _Prefetcher:
         self.bufs = {}
         self.pairs = None
 
-    def stage(self, pairs):
+    def stage(self, pairs, bufs=None):
         cur = torch.cuda.current_stream(self.device)
         if self.consumed is not None:
             self.stream.wait_event(self.consumed)
@@ -153,8 +234,8 @@ class _Prefetcher:
             self.stream.wait_stream(cur)
         staged = []
         with torch.cuda.stream(self.stream):
-            for dst, src in pairs:
-                b = self.bufs.get(dst.data_ptr())
+            for i, (dst, src) in enumerate(pairs):
+                b = bufs[i] if bufs is not None else self.bufs.get(dst.data_ptr())
                 if b is None:
                     b = self.bufs[dst.data_ptr()] = torch.empty_like(dst)
                 b.copy_(src, non_blocking=True)
@@ -166,7 +247,10 @@ class _Prefetcher:
         assert self.pairs is not None, "commit() without a staged batch"
         cur = torch.cuda.current_stream(self.device)
         cur.wait_event(self.staged)
-        torch._foreach_copy_([d for d, _ in self.pairs], [b for _, b in self.pairs])
+        if len(self.pairs) == 1:
+            self.pairs[0][0].copy_(self.pairs[0][1], non_blocking=True)
+        else:
+            torch._foreach_copy_([d for d, _ in self.pairs], [b for _, b in self.pairs])
         self.consumed = torch.cuda.Event()
         self.consumed.record(cur)
         self.pairs = None

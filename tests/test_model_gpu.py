@@ -167,3 +167,19 @@ def test_prefetch_pipeline_matches_load():
         got.append(float(loss))
     for i, v in enumerate(got):
         assert abs(v - want[i % 2]) <= 1e-6 * abs(want[i % 2]), (i, v, want)
+    # arena path: the batch is collated into the pinned host views -> one H2D + one D2D memcpy per step
+    a_args, a_noise = step.host_inputs()
+    for which in (0, 1, 0):
+        src_args, src_noise = hosts[which]
+        for dst, src in zip(a_args, src_args):
+            if isinstance(dst, torch.Tensor):
+                dst.copy_(src)
+            elif isinstance(dst, list) and dst and isinstance(dst[0], torch.Tensor):
+                for d, s in zip(dst, src):
+                    d.copy_(s)
+        for d, s in zip(a_noise, src_noise):
+            d.copy_(s)
+        a_args[9] = src_args[9]
+        step.prefetch(a_args, a_noise)
+        v = float(step.run_prefetched())
+        assert abs(v - want[which]) <= 1e-6 * abs(want[which]), (which, v, want)
