@@ -158,7 +158,7 @@ int svpc_pointer_bwd(int n_clips, int Lt, int D, int V, int max_ni, int max_vx, 
                      const float* wpgen, const float* logits, long long ldl, const int* labels, float smoothing,
                      const float* P, const float* alpha, const float* pgen, const float* ctx, const float* dP,
                      const float* dloss, void* ddec, float* dG, float* dE, float* du, float* dwpgen, float* dbpgen,
-                     float* dlogits, svpc_stream_t stream);
+                     float* dlogits, float* dscore_ws /* scratch: n_clips * Lt * max_ni floats */, svpc_stream_t stream);
 /* 'video' mode: softmax over the vocabulary + LabelSmoothingLoss (model.py:1011-1014). */
 int svpc_softmax_ls_fwd(int rows, int V, const float* logits, long long ldl, const int* labels, float smoothing, float* P,
                         float* loss_rows, svpc_stream_t stream);
@@ -172,7 +172,8 @@ int svpc_gumbel_fwd(int n_clips, int Lt, int V, int W, const float* P, const flo
                     float* yval, svpc_stream_t stream);
 int svpc_gumbel_bwd(int n_clips, int Lt, int V, int W, const float* P, const float* g, const int* clip_P_off,
                     const int* clip_vx, float tau, const float* emb, const float* text_mask, const int* idx,
-                    const float* yval, const float* dxmean, float* dP, float* demb, svpc_stream_t stream);
+                    const float* yval, const float* dxmean, float* dP, float* demb,
+                    float* tv_ws /* scratch: n_clips * V floats */, svpc_stream_t stream);
 
 /* Recurrence of nn.LSTM(bidirectional) (model.py:865, 1022-1024), gate order i,f,g,o: ONE launch per time step j for
  * both directions and all videos, recurrent product fused with the cell.  rows (2, Smax, B): clip row of video b at

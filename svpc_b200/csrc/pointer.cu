@@ -1,7 +1,7 @@
 // Output head of the caption decoder and the front end of the textual re-simulator:
 //   * pointer-generator mixing + scatter of the copy mass into the (extended) vocabulary + label-smoothed KL loss on
-//     PROBABILITIES (reference model.py:896-923, 37-55), one CTA per clip, rows of the clip processed in sequence so
-//     the per-ingredient gradients reduce inside the CTA;
+//     PROBABILITIES (reference model.py:896-923, 37-55), one CTA per (clip, text position); the per-ingredient
+//     gradients are reduced over a clip's positions by a second, per-clip kernel;
 //   * plain softmax + the same loss for the 'video' mode (model.py:1011-1014);
 //   * hard Gumbel-softmax with injected noise -> word-vector lookup -> masked mean (model.py:1018-1021).
 // Quirks kept: softmax over the INGREDIENT axis; copy mass of ingredient i split equally over its token ids, added in
@@ -39,12 +39,12 @@ __global__ void __launch_bounds__(PG_THREADS) pointer_fwd_kernel(
   float* prow = sctx + D;         // max_vx
   float* alpha = prow + max_vx;   // max_ni
   __shared__ float red[64];
-  const int n = blockIdx.x;
+  const int n = blockIdx.y, l = blockIdx.x;     // one CTA per (clip, text position): rows are independent
   const int src = clip_src_off[n], ni = clip_ni[n], gi = clip_gi[n], vx = clip_vx[n];
   const long long poff = clip_P_off[n];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const float bp = bpgen[0];
-  for (int l = 0; l < Lt; ++l) {
+  {
     const long long r = (long long)n * Lt + l;
     for (int d = threadIdx.x; d < D; d += PG_THREADS) sdec[d] = ldf(dec + r * D + d);
     __syncthreads();
@@ -107,10 +107,11 @@ __global__ void __launch_bounds__(PG_THREADS) pointer_fwd_kernel(
     }
     acc = block_sum(acc, red);
     if (threadIdx.x == 0) loss_rows[r] = label >= 0 ? ls_const(label, vx, s, conf) - acc : 0.f;
-    __syncthreads();
   }
 }
 
+// Backward, part 1: one CTA per (clip, text position).  Writes d logits, d dec, du (gradient of the p_gen
+// pre-activation) and the score gradients dsc[r][i]; the per-ingredient sums over the clip's positions are part 2.
 template <typename T>
 __global__ void __launch_bounds__(PG_THREADS) pointer_bwd_kernel(
     int Lt, int D, int V, int max_ni, int max_vx, const T* __restrict__ dec, const float* __restrict__ G,
@@ -119,18 +120,17 @@ __global__ void __launch_bounds__(PG_THREADS) pointer_bwd_kernel(
     const int* __restrict__ tok_ptr, const int* __restrict__ tok_ids, const float* __restrict__ wpgen,
     const float* __restrict__ logits, long long ldl, const int* __restrict__ labels, float smoothing,
     const float* __restrict__ P, const float* __restrict__ alpha_in, const float* __restrict__ pgen_in,
-    const float* __restrict__ dP, const float* __restrict__ dloss, T* __restrict__ ddec, float* __restrict__ dG,
-    float* __restrict__ dE, float* __restrict__ du_out, float* __restrict__ dlogits) {
+    const float* __restrict__ dP, const float* __restrict__ dloss, T* __restrict__ ddec, float* __restrict__ du_out,
+    float* __restrict__ dlogits, float* __restrict__ dsc_out) {
   extern __shared__ float sm[];
   float* gP = sm;                    // max_vx
-  float* dsc = gP + max_vx;          // max_ni * Lt   d score[i][l]
-  float* alpha = dsc + max_ni * Lt;  // max_ni
+  float* dsc = gP + max_vx;          // max_ni   d score[i]
+  float* alpha = dsc + max_ni;       // max_ni
   float* ci = alpha + max_ni;        // max_ni
   float* wE = ci + max_ni;           // max_ni   w2 . E_i
-  float* beta = wE + max_ni;         // max_ni   sum_l alpha_il du_l
   __shared__ float red[64];
   __shared__ float s_du;
-  const int n = blockIdx.x;
+  const int n = blockIdx.y, l = blockIdx.x;
   const int src = clip_src_off[n], ni = clip_ni[n], gi = clip_gi[n], vx = clip_vx[n];
   const long long poff = clip_P_off[n];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -140,73 +140,102 @@ __global__ void __launch_bounds__(PG_THREADS) pointer_bwd_kernel(
     float s = 0.f;
     for (int d = lane; d < D; d += 32) s = fmaf(wpgen[D + d], e[d], s);
     s = warp_sum(s);
-    if (lane == 0) { wE[i] = s; beta[i] = 0.f; }
+    if (lane == 0) wE[i] = s;
+  }
+  const long long r = (long long)n * Lt + l;
+  const float pg = pgen_in[r];
+  const int label = labels[r];
+  const float s = smoothing / (float)(vx - 1), conf = 1.f - smoothing;
+  const float* lrow = logits + r * ldl;
+  for (int i = threadIdx.x; i < ni; i += PG_THREADS) alpha[i] = alpha_in[r * max_ni + i];
+  float mx = -INFINITY;
+  for (int v = threadIdx.x; v < V; v += PG_THREADS) mx = fmaxf(mx, lrow[v]);
+  mx = block_max(mx, red);
+  float se = 0.f;
+  for (int v = threadIdx.x; v < V; v += PG_THREADS) se += expf(lrow[v] - mx);
+  se = block_sum(se, red);
+  // gradient w.r.t. the mixed probabilities
+  float pa = 0.f;
+  for (int v = threadIdx.x; v < vx; v += PG_THREADS) {
+    float g = dP ? dP[poff + (long long)l * vx + v] : 0.f;
+    if (label >= 0) g -= gl * ls_q(v, label, vx, s, conf) / (P[poff + (long long)l * vx + v] + 1e-12f);
+    gP[v] = g;
+    if (v < V) pa = fmaf(g, expf(lrow[v] - mx) / se, pa);
+  }
+  const float A = block_sum(pa, red);      // sum_v gP_v sm_v   (syncs: gP, wE, alpha visible)
+  for (int i = threadIdx.x; i < ni; i += PG_THREADS) {
+    const int lo = tok_ptr[gi + i], hi = tok_ptr[gi + i + 1];
+    float c = 0.f;
+    for (int t = lo; t < hi; ++t) c += gP[tok_ids[t]];
+    ci[i] = c / (float)(hi - lo);
   }
   __syncthreads();
-  for (int l = 0; l < Lt; ++l) {
-    const long long r = (long long)n * Lt + l;
-    const float pg = pgen_in[r];
-    const int label = labels[r];
-    const float s = smoothing / (float)(vx - 1), conf = 1.f - smoothing;
-    const float* lrow = logits + r * ldl;
-    for (int i = threadIdx.x; i < ni; i += PG_THREADS) alpha[i] = alpha_in[r * max_ni + i];
-    float mx = -INFINITY;
-    for (int v = threadIdx.x; v < V; v += PG_THREADS) mx = fmaxf(mx, lrow[v]);
-    mx = block_max(mx, red);
-    float se = 0.f;
-    for (int v = threadIdx.x; v < V; v += PG_THREADS) se += expf(lrow[v] - mx);
-    se = block_sum(se, red);
-    // gradient w.r.t. the mixed probabilities
-    float pa = 0.f;
-    for (int v = threadIdx.x; v < vx; v += PG_THREADS) {
-      float g = dP ? dP[poff + (long long)l * vx + v] : 0.f;
-      if (label >= 0) g -= gl * ls_q(v, label, vx, s, conf) / (P[poff + (long long)l * vx + v] + 1e-12f);
-      gP[v] = g;
-      if (v < V) pa = fmaf(g, expf(lrow[v] - mx) / se, pa);
+  if (warp == 0) {
+    float t = 0.f;
+    for (int i = lane; i < ni; i += 32) t = fmaf(alpha[i], ci[i], t);
+    t = warp_sum(t);
+    const float dpg = A - t;
+    const float du = dpg * pg * (1.f - pg);
+    // d alpha_i = (1 - pg) c_i + du * (w2 . E_i);  d score = alpha (d alpha - sum alpha d alpha)
+    float dot = 0.f;
+    for (int i = lane; i < ni; i += 32) dot = fmaf(alpha[i], (1.f - pg) * ci[i] + du * wE[i], dot);
+    dot = warp_sum(dot);
+    for (int i = lane; i < ni; i += 32) {
+      const float dal = (1.f - pg) * ci[i] + du * wE[i];
+      const float ds = alpha[i] * (dal - dot);
+      dsc[i] = ds;
+      dsc_out[r * max_ni + i] = ds;
     }
-    const float A = block_sum(pa, red);      // sum_v gP_v sm_v   (syncs: gP visible)
-    for (int i = threadIdx.x; i < ni; i += PG_THREADS) {
-      const int lo = tok_ptr[gi + i], hi = tok_ptr[gi + i + 1];
-      float c = 0.f;
-      for (int t = lo; t < hi; ++t) c += gP[tok_ids[t]];
-      ci[i] = c / (float)(hi - lo);
-    }
-    __syncthreads();
-    if (warp == 0) {
-      float t = 0.f;
-      for (int i = lane; i < ni; i += 32) t = fmaf(alpha[i], ci[i], t);
-      t = warp_sum(t);
-      const float dpg = A - t;
-      const float du = dpg * pg * (1.f - pg);
-      // d alpha_i = (1 - pg) c_i + du * (w2 . E_i);  d score = alpha (d alpha - sum alpha d alpha)
-      float dot = 0.f;
-      for (int i = lane; i < ni; i += 32) dot = fmaf(alpha[i], (1.f - pg) * ci[i] + du * wE[i], dot);
-      dot = warp_sum(dot);
-      for (int i = lane; i < ni; i += 32) {
-        const float dal = (1.f - pg) * ci[i] + du * wE[i];
-        dsc[i * Lt + l] = alpha[i] * (dal - dot);
-        beta[i] += alpha[i] * du;
-      }
-      if (lane == 0) { s_du = du; du_out[r] = du; }
-    }
-    __syncthreads();
-    const float du = s_du;
-    for (int v = threadIdx.x; v < V; v += PG_THREADS)
-      dlogits[r * ldl + v] = (expf(lrow[v] - mx) / se) * pg * (gP[v] - A);
-    for (int d = threadIdx.x; d < D; d += PG_THREADS) {
-      float a = du * wpgen[d];
-      for (int i = 0; i < ni; ++i) a = fmaf(dsc[i * Lt + l], G[(long long)(src + i) * D + d], a);
-      stf(ddec + r * D + d, a);
-    }
-    __syncthreads();
+    if (lane == 0) { s_du = du; du_out[r] = du; }
   }
-  // dG_i[d] += sum_l dscore[i][l] dec[l][d] ;  dE_i[d] += beta_i w2[d]
+  __syncthreads();
+  const float du = s_du;
+  for (int v = threadIdx.x; v < V; v += PG_THREADS)
+    dlogits[r * ldl + v] = (expf(lrow[v] - mx) / se) * pg * (gP[v] - A);
   for (int d = threadIdx.x; d < D; d += PG_THREADS) {
-    for (int i = 0; i < ni; ++i) {
-      float a = 0.f;
-      for (int l = 0; l < Lt; ++l) a = fmaf(dsc[i * Lt + l], ldf(dec + ((long long)n * Lt + l) * D + d), a);
-      atomicAdd(dG + (long long)(src + i) * D + d, a);
-      atomicAdd(dE + (long long)(src + i) * D + d, beta[i] * wpgen[D + d]);
+    float a = du * wpgen[d];
+    for (int i = 0; i < ni; ++i) a = fmaf(dsc[i], G[(long long)(src + i) * D + d], a);
+    stf(ddec + r * D + d, a);
+  }
+}
+
+// Backward, part 2: one CTA per clip.  dG_i[d] += sum_l dscore[l][i] dec[l][d] ;  dE_i[d] += (sum_l alpha_il du_l) w2[d]
+template <typename T>
+__global__ void __launch_bounds__(PG_THREADS) pointer_bwd_reduce_kernel(
+    int Lt, int D, int max_ni, const T* __restrict__ dec, const int* __restrict__ clip_src_off,
+    const int* __restrict__ clip_ni, const float* __restrict__ wpgen, const float* __restrict__ alpha_in,
+    const float* __restrict__ du, const float* __restrict__ dsc_in, float* __restrict__ dG, float* __restrict__ dE) {
+  extern __shared__ float sm[];
+  float* dsc = sm;                   // Lt * max_ni
+  float* beta = dsc + Lt * max_ni;   // max_ni
+  const int n = blockIdx.x;
+  const int src = clip_src_off[n], ni = clip_ni[n];
+  for (int e = threadIdx.x; e < Lt * max_ni; e += PG_THREADS) dsc[e] = dsc_in[(long long)n * Lt * max_ni + e];
+  for (int i = threadIdx.x; i < ni; i += PG_THREADS) {
+    float b = 0.f;
+    for (int l = 0; l < Lt; ++l) {
+      const long long r = (long long)n * Lt + l;
+      b = fmaf(alpha_in[r * max_ni + i], du[r], b);
+    }
+    beta[i] = b;
+  }
+  __syncthreads();
+  for (int d = threadIdx.x; d < D; d += PG_THREADS) {
+    const float w2 = wpgen[D + d];
+    for (int i0 = 0; i0 < ni; i0 += 4) {        // 4 ingredients per pass over the clip's decoder rows
+      float a[4] = {0.f, 0.f, 0.f, 0.f};
+      for (int l = 0; l < Lt; ++l) {
+        const float x = ldf(dec + ((long long)n * Lt + l) * D + d);
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          if (i0 + k < ni) a[k] = fmaf(dsc[l * max_ni + i0 + k], x, a[k]);
+      }
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        if (i0 + k < ni) {
+          atomicAdd(dG + (long long)(src + i0 + k) * D + d, a[k]);
+          atomicAdd(dE + (long long)(src + i0 + k) * D + d, beta[i0 + k] * w2);
+        }
     }
   }
 }
@@ -225,7 +254,7 @@ extern "C" int svpc_pointer_fwd(int n_clips, int Lt, int D, int V, int max_ni, i
   cudaStream_t st = (cudaStream_t)stream;
   SVPC_DISPATCH(dt, T, {
     cudaFuncSetAttribute(pointer_fwd_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    pointer_fwd_kernel<T><<<n_clips, PG_THREADS, smem, st>>>(Lt, D, V, max_ni, max_vx, (const T*)dec, G, Esrc, clip_src_off,
+    pointer_fwd_kernel<T><<<dim3(Lt, n_clips), PG_THREADS, smem, st>>>(Lt, D, V, max_ni, max_vx, (const T*)dec, G, Esrc, clip_src_off,
                                                             clip_ni, clip_gi, clip_vx, clip_P_off, tok_ptr, tok_ids, wpgen,
                                                             bpgen, logits, ldl, labels, smoothing, P, loss_rows, alpha, pgen, ctx);
   });
@@ -238,18 +267,23 @@ extern "C" int svpc_pointer_bwd(int n_clips, int Lt, int D, int V, int max_ni, i
                                 const int* tok_ids, const float* wpgen, const float* logits, long long ldl,
                                 const int* labels, float smoothing, const float* P, const float* alpha, const float* pgen,
                                 const float* ctx, const float* dP, const float* dloss, void* ddec, float* dG, float* dE,
-                                float* du, float* dwpgen, float* dbpgen, float* dlogits, svpc_stream_t stream) {
+                                float* du, float* dwpgen, float* dbpgen, float* dlogits, float* dscore_ws,
+                                svpc_stream_t stream) {
   if (n_clips <= 0) return SVPC_OK;
-  const size_t smem = sizeof(float) * ((size_t)max_vx + (size_t)max_ni * Lt + 4 * (size_t)max_ni);
-  SVPC_REQUIRE(smem <= 200 * 1024, "pointer_bwd: shared memory");
+  SVPC_REQUIRE(dscore_ws != nullptr, "pointer_bwd: dscore_ws (n_clips * Lt * max_ni floats) is required");
+  const size_t smem = sizeof(float) * ((size_t)max_vx + 4 * (size_t)max_ni);
+  const size_t smem2 = sizeof(float) * ((size_t)max_ni * Lt + (size_t)max_ni);
+  SVPC_REQUIRE(smem <= 200 * 1024 && smem2 <= 200 * 1024, "pointer_bwd: shared memory");
   cudaStream_t st = (cudaStream_t)stream;
   cudaMemsetAsync(dwpgen, 0, sizeof(float) * 2 * D, st);
   SVPC_DISPATCH(dt, T, {
     cudaFuncSetAttribute(pointer_bwd_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    pointer_bwd_kernel<T><<<n_clips, PG_THREADS, smem, st>>>(Lt, D, V, max_ni, max_vx, (const T*)dec, G, Esrc, clip_src_off,
-                                                            clip_ni, clip_gi, clip_vx, clip_P_off, tok_ptr, tok_ids, wpgen,
-                                                            logits, ldl, labels, smoothing, P, alpha, pgen, dP, dloss,
-                                                            (T*)ddec, dG, dE, du, dlogits);
+    pointer_bwd_kernel<T><<<dim3(Lt, n_clips), PG_THREADS, smem, st>>>(
+        Lt, D, V, max_ni, max_vx, (const T*)dec, G, Esrc, clip_src_off, clip_ni, clip_gi, clip_vx, clip_P_off, tok_ptr,
+        tok_ids, wpgen, logits, ldl, labels, smoothing, P, alpha, pgen, dP, dloss, (T*)ddec, du, dlogits, dscore_ws);
+    cudaFuncSetAttribute(pointer_bwd_reduce_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
+    pointer_bwd_reduce_kernel<T><<<n_clips, PG_THREADS, smem2, st>>>(Lt, D, max_ni, (const T*)dec, clip_src_off, clip_ni,
+                                                                   wpgen, alpha, du, dscore_ws, dG, dE);
   });
   int rc = svpc_check_launch("pointer_bwd");
   if (rc) return rc;
@@ -331,133 +365,181 @@ extern "C" int svpc_softmax_ls_bwd(int rows, int V, const float* dP, const float
 // ------------------------------------------------------------------------------------------------
 // textual re-simulator front end
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(PG_THREADS) gumbel_fwd_kernel(int Lt, int V, int W, const float* __restrict__ P,
+// One CTA per (clip, text position): hard Gumbel-softmax of one row -> argmax index and straight-through value.
+__global__ void __launch_bounds__(PG_THREADS) gumbel_fwd_kernel(int Lt, int V, const float* __restrict__ P,
                                                                 const float* __restrict__ g,
                                                                 const int* __restrict__ clip_P_off,
                                                                 const int* __restrict__ clip_vx, float tau,
-                                                                const float* __restrict__ emb,
-                                                                const float* __restrict__ text_mask,
-                                                                float* __restrict__ xmean, int* __restrict__ idx_out,
-                                                                float* __restrict__ yval_out) {
+                                                                int* __restrict__ idx_out, float* __restrict__ yval_out) {
   __shared__ float red[64];
   __shared__ float smax[PG_THREADS / 32];
   __shared__ int sidx[PG_THREADS / 32];
   __shared__ int s_best;
   __shared__ float s_mx;
-  const int n = blockIdx.x, vx = clip_vx[n];
+  const int n = blockIdx.y, l = blockIdx.x, vx = clip_vx[n];
   const long long poff = clip_P_off[n];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  float acc[4] = {0.f, 0.f, 0.f, 0.f};   // W <= 4 * PG_THREADS
-  float cnt = 0.f;
-  for (int l = 0; l < Lt; ++l) {
-    const long long r = (long long)n * Lt + l;
-    const float* prow = P + poff + (long long)l * vx;
-    const float* grow = g + poff + (long long)l * vx;
-    float mx = -INFINITY;
-    int best = 0x7fffffff;
+  const long long r = (long long)n * Lt + l;
+  const float* prow = P + poff + (long long)l * vx;
+  const float* grow = g + poff + (long long)l * vx;
+  float mx = -INFINITY;
+  int best = 0x7fffffff;
+  float zloc[4];                                  // this thread's z values (vx <= 4 * PG_THREADS on the fast path)
+  const bool cache = vx <= 4 * PG_THREADS;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int v = threadIdx.x + k * PG_THREADS;
+    zloc[k] = -INFINITY;
+    if (cache && v < vx) {
+      const float z = (logf(prow[v] + 1e-12f) + grow[v]) / tau;
+      zloc[k] = z;
+      if (z > mx) { mx = z; best = v; }
+    }
+  }
+  if (!cache)
     for (int v = threadIdx.x; v < vx; v += PG_THREADS) {
       const float z = (logf(prow[v] + 1e-12f) + grow[v]) / tau;
       if (z > mx) { mx = z; best = v; }
     }
-    for (int o = 16; o > 0; o >>= 1) {
-      const float om = __shfl_xor_sync(0xffffffffu, mx, o);
-      const int ob = __shfl_xor_sync(0xffffffffu, best, o);
-      if (om > mx || (om == mx && ob < best)) { mx = om; best = ob; }
-    }
-    __syncthreads();
-    if (lane == 0) { smax[warp] = mx; sidx[warp] = best; }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      float m = smax[0]; int bi = sidx[0];
-      for (int w = 1; w < PG_THREADS / 32; ++w)
-        if (smax[w] > m || (smax[w] == m && sidx[w] < bi)) { m = smax[w]; bi = sidx[w]; }
-      s_best = bi; s_mx = m;
-    }
-    __syncthreads();
-    mx = s_mx; best = s_best;
-    float se = 0.f;
-    for (int v = threadIdx.x; v < vx; v += PG_THREADS) se += expf((logf(prow[v] + 1e-12f) + grow[v]) / tau - mx);
-    se = block_sum(se, red);
-    const float y = 1.0f / se;                 // y_soft at its argmax
-    const float yv = (1.0f - y) + y;           // y_hard - y_soft.detach() + y_soft
-    if (threadIdx.x == 0) { idx_out[r] = best; yval_out[r] = yv; }
-    const bool m = text_mask[r] == 1.0f;
-    if (m) {
-      cnt += 1.f;
-      if (best < V) {
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const int w = threadIdx.x + i * PG_THREADS;
-          if (w < W) acc[i] = fmaf(yv, emb[(long long)best * W + w], acc[i]);
-        }
-      }
-    }
+  for (int o = 16; o > 0; o >>= 1) {
+    const float om = __shfl_xor_sync(0xffffffffu, mx, o);
+    const int ob = __shfl_xor_sync(0xffffffffu, best, o);
+    if (om > mx || (om == mx && ob < best)) { mx = om; best = ob; }
   }
+  if (lane == 0) { smax[warp] = mx; sidx[warp] = best; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float m = smax[0]; int bi = sidx[0];
+    for (int w = 1; w < PG_THREADS / 32; ++w)
+      if (smax[w] > m || (smax[w] == m && sidx[w] < bi)) { m = smax[w]; bi = sidx[w]; }
+    s_best = bi; s_mx = m;
+  }
+  __syncthreads();
+  mx = s_mx; best = s_best;
+  float se = 0.f;
+  if (cache) {
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const int w = threadIdx.x + i * PG_THREADS;
-    if (w < W) xmean[(long long)n * W + w] = acc[i] / cnt;
+    for (int k = 0; k < 4; ++k)
+      if (threadIdx.x + k * PG_THREADS < vx) se += expf(zloc[k] - mx);
+  } else {
+    for (int v = threadIdx.x; v < vx; v += PG_THREADS) se += expf((logf(prow[v] + 1e-12f) + grow[v]) / tau - mx);
+  }
+  se = block_sum(se, red);
+  const float y = 1.0f / se;                 // y_soft at its argmax
+  const float yv = (1.0f - y) + y;           // y_hard - y_soft.detach() + y_soft
+  if (threadIdx.x == 0) { idx_out[r] = best; yval_out[r] = yv; }
+}
+
+// One CTA per clip: masked mean over the text positions of yv * Emb[argmax] (positions in order, as the reference sums)
+__global__ void __launch_bounds__(PG_THREADS) gumbel_mean_kernel(int Lt, int V, int W, const float* __restrict__ emb,
+                                                                 const float* __restrict__ text_mask,
+                                                                 const int* __restrict__ idx, const float* __restrict__ yval,
+                                                                 float* __restrict__ xmean) {
+  const int n = blockIdx.x;
+  float cnt = 0.f;
+  for (int l = 0; l < Lt; ++l) cnt += (text_mask[(long long)n * Lt + l] == 1.0f) ? 1.f : 0.f;
+  for (int w = threadIdx.x; w < W; w += PG_THREADS) {
+    float acc = 0.f;
+    for (int l = 0; l < Lt; ++l) {
+      const long long r = (long long)n * Lt + l;
+      const int best = idx[r];
+      if (text_mask[r] == 1.0f && best < V) acc = fmaf(yval[r], emb[(long long)best * W + w], acc);
+    }
+    xmean[(long long)n * W + w] = acc / cnt;
   }
 }
 
-__global__ void __launch_bounds__(PG_THREADS) gumbel_bwd_kernel(int Lt, int V, int W, const float* __restrict__ P,
-                                                                const float* __restrict__ g,
-                                                                const int* __restrict__ clip_P_off,
-                                                                const int* __restrict__ clip_vx, float tau,
-                                                                const float* __restrict__ emb,
-                                                                const float* __restrict__ text_mask,
-                                                                const int* __restrict__ idx_in,
-                                                                const float* __restrict__ yval_in,
-                                                                const float* __restrict__ dxmean, float* __restrict__ dP,
-                                                                float* __restrict__ demb) {
-  extern __shared__ float sm[];
-  float* dxm = sm;        // W
-  float* tv = dxm + W;    // V     t_v = emb[v] . dxmean
-  __shared__ float red[64];
-  const int n = blockIdx.x, vx = clip_vx[n];
-  const long long poff = clip_P_off[n];
+// tv[n][v] = Emb[v] . dxmean[n]: one warp per 8 vocabulary entries
+__global__ void __launch_bounds__(PG_THREADS) gumbel_tv_kernel(int V, int W, const float* __restrict__ emb,
+                                                               const float* __restrict__ dxmean, float* __restrict__ tv) {
+  extern __shared__ float dxm[];   // W
+  const int n = blockIdx.y;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   for (int w = threadIdx.x; w < W; w += PG_THREADS) dxm[w] = dxmean[(long long)n * W + w];
-  float cnt = 0.f;
-  for (int l = 0; l < Lt; ++l) cnt += (text_mask[(long long)n * Lt + l] == 1.0f) ? 1.f : 0.f;
   __syncthreads();
-  for (int v = warp; v < V; v += PG_THREADS / 32) {
+  const int v0 = blockIdx.x * 64 + warp * 8;
+  for (int k = 0; k < 8; ++k) {
+    const int v = v0 + k;
+    if (v >= V) break;
     const float* e = emb + (long long)v * W;
     float s = 0.f;
     for (int w = lane; w < W; w += 32) s = fmaf(e[w], dxm[w], s);
     s = warp_sum(s);
-    if (lane == 0) tv[v] = s;
+    if (lane == 0) tv[(long long)n * V + v] = s;
   }
-  __syncthreads();
-  for (int l = 0; l < Lt; ++l) {
-    const long long r = (long long)n * Lt + l;
-    const float* prow = P + poff + (long long)l * vx;
-    const float* grow = g + poff + (long long)l * vx;
-    float* drow = dP + poff + (long long)l * vx;
-    if (text_mask[r] != 1.0f) {
-      for (int v = threadIdx.x; v < vx; v += PG_THREADS) drow[v] = 0.f;
-      continue;
+}
+
+// One CTA per (clip, text position)
+__global__ void __launch_bounds__(PG_THREADS) gumbel_bwd_kernel(int Lt, int V, int W, const float* __restrict__ P,
+                                                                const float* __restrict__ g,
+                                                                const int* __restrict__ clip_P_off,
+                                                                const int* __restrict__ clip_vx, float tau,
+                                                                const float* __restrict__ text_mask,
+                                                                const int* __restrict__ idx_in,
+                                                                const float* __restrict__ yval_in,
+                                                                const float* __restrict__ dxmean,
+                                                                const float* __restrict__ tv_all, float* __restrict__ dP,
+                                                                float* __restrict__ demb) {
+  __shared__ float red[64];
+  const int n = blockIdx.y, l = blockIdx.x, vx = clip_vx[n];
+  const long long poff = clip_P_off[n];
+  const long long r = (long long)n * Lt + l;
+  const float* prow = P + poff + (long long)l * vx;
+  const float* grow = g + poff + (long long)l * vx;
+  const float* tv = tv_all + (long long)n * V;
+  float* drow = dP + poff + (long long)l * vx;
+  if (text_mask[r] != 1.0f) {
+    for (int v = threadIdx.x; v < vx; v += PG_THREADS) drow[v] = 0.f;
+    return;
+  }
+  float cnt = 0.f;
+  for (int k = 0; k < Lt; ++k) cnt += (text_mask[(long long)n * Lt + k] == 1.0f) ? 1.f : 0.f;
+  const int best = idx_in[r];
+  const float mx = (logf(prow[best] + 1e-12f) + grow[best]) / tau;
+  float se = 0.f, sd = 0.f;
+  float eloc[4], ploc[4];
+  const bool cache = vx <= 4 * PG_THREADS;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int v = threadIdx.x + k * PG_THREADS;
+    eloc[k] = 0.f; ploc[k] = 0.f;
+    if (cache && v < vx) {
+      const float p = prow[v];
+      const float e = expf((logf(p + 1e-12f) + grow[v]) / tau - mx);
+      eloc[k] = e; ploc[k] = p;
+      se += e;
+      if (v < V) sd = fmaf(e, tv[v], sd);
     }
-    const int best = idx_in[r];
-    const float mx = (logf(prow[best] + 1e-12f) + grow[best]) / tau;
-    float se = 0.f, sd = 0.f;
+  }
+  if (!cache)
     for (int v = threadIdx.x; v < vx; v += PG_THREADS) {
       const float e = expf((logf(prow[v] + 1e-12f) + grow[v]) / tau - mx);
       se += e;
       if (v < V) sd = fmaf(e, tv[v], sd);
     }
-    const float2 rr = block_sum2(se, sd, red);
-    const float inv = 1.f / rr.x;
-    const float sdot = rr.y * inv / cnt;              // sum_v y_v dy_v
+  const float2 rr = block_sum2(se, sd, red);
+  const float inv = 1.f / rr.x;
+  const float sdot = rr.y * inv / cnt;              // sum_v y_v dy_v
+  if (cache) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int v = threadIdx.x + k * PG_THREADS;
+      if (v < vx) {
+        const float y = eloc[k] * inv;
+        const float dy = v < V ? tv[v] / cnt : 0.f;
+        drow[v] = y * (dy - sdot) / tau / (ploc[k] + 1e-12f);
+      }
+    }
+  } else {
     for (int v = threadIdx.x; v < vx; v += PG_THREADS) {
       const float y = expf((logf(prow[v] + 1e-12f) + grow[v]) / tau - mx) * inv;
       const float dy = v < V ? tv[v] / cnt : 0.f;
       drow[v] = y * (dy - sdot) / tau / (prow[v] + 1e-12f);
     }
-    if (best < V) {
-      const float c = yval_in[r] / cnt;
-      for (int w = threadIdx.x; w < W; w += PG_THREADS) atomicAdd(demb + (long long)best * W + w, c * dxm[w]);
-    }
+  }
+  if (best < V) {
+    const float c = yval_in[r] / cnt;
+    for (int w = threadIdx.x; w < W; w += PG_THREADS) atomicAdd(demb + (long long)best * W + w, c * dxmean[(long long)n * W + w]);
   }
 }
 
@@ -465,21 +547,26 @@ extern "C" int svpc_gumbel_fwd(int n_clips, int Lt, int V, int W, const float* P
                                const int* clip_vx, float tau, const float* emb, const float* text_mask, float* xmean,
                                int* idx, float* yval, svpc_stream_t stream) {
   if (n_clips <= 0) return SVPC_OK;
-  SVPC_REQUIRE(W <= 4 * PG_THREADS, "gumbel_fwd: W=%d too wide", W);
-  gumbel_fwd_kernel<<<n_clips, PG_THREADS, 0, (cudaStream_t)stream>>>(Lt, V, W, P, g, clip_P_off, clip_vx, tau, emb, text_mask,
-                                                                     xmean, idx, yval);
-  return svpc_check_launch("gumbel_fwd");
+  cudaStream_t st = (cudaStream_t)stream;
+  gumbel_fwd_kernel<<<dim3(Lt, n_clips), PG_THREADS, 0, st>>>(Lt, V, P, g, clip_P_off, clip_vx, tau, idx, yval);
+  int rc = svpc_check_launch("gumbel_fwd");
+  if (rc) return rc;
+  gumbel_mean_kernel<<<n_clips, PG_THREADS, 0, st>>>(Lt, V, W, emb, text_mask, idx, yval, xmean);
+  return svpc_check_launch("gumbel_mean");
 }
 
 extern "C" int svpc_gumbel_bwd(int n_clips, int Lt, int V, int W, const float* P, const float* g, const int* clip_P_off,
                                const int* clip_vx, float tau, const float* emb, const float* text_mask, const int* idx,
-                               const float* yval, const float* dxmean, float* dP, float* demb, svpc_stream_t stream) {
+                               const float* yval, const float* dxmean, float* dP, float* demb, float* tv_ws,
+                               svpc_stream_t stream) {
   cudaStream_t st = (cudaStream_t)stream;
   cudaMemsetAsync(demb, 0, sizeof(float) * (size_t)V * W, st);
   if (n_clips <= 0) return SVPC_OK;
-  const size_t smem = sizeof(float) * ((size_t)W + V);
-  cudaFuncSetAttribute(gumbel_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  gumbel_bwd_kernel<<<n_clips, PG_THREADS, smem, st>>>(Lt, V, W, P, g, clip_P_off, clip_vx, tau, emb, text_mask, idx, yval,
-                                                      dxmean, dP, demb);
+  SVPC_REQUIRE(tv_ws != nullptr, "gumbel_bwd: tv_ws (n_clips * V floats) is required");
+  gumbel_tv_kernel<<<dim3(svpc_cdiv(V, 64), n_clips), PG_THREADS, sizeof(float) * (size_t)W, st>>>(V, W, emb, dxmean, tv_ws);
+  int rc = svpc_check_launch("gumbel_tv");
+  if (rc) return rc;
+  gumbel_bwd_kernel<<<dim3(Lt, n_clips), PG_THREADS, 0, st>>>(Lt, V, W, P, g, clip_P_off, clip_vx, tau, text_mask, idx, yval,
+                                                             dxmean, tv_ws, dP, demb);
   return svpc_check_launch("gumbel_bwd");
 }

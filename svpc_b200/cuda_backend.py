@@ -458,13 +458,14 @@ class CudaBackend:
         dw = torch.empty(2 * D, dtype=torch.float32, device=dev)
         db = torch.empty(1, dtype=torch.float32, device=dev)
         dlog = torch.empty_like(logits)
+        dsc = torch.empty(R, max_ni, dtype=torch.float32, device=dev)
         dloss = dloss.to(torch.float32).reshape(1)
         self._call("svpc_pointer_bwd", Nc, Lt, D, V, max_ni, max_vx, _ptr(dec), _DT[dec.dtype], _ptr(G), _ptr(Esrc),
                    _ptr(lay["clip_src_off"]), _ptr(lay["clip_ni"]), _ptr(lay["clip_gi"]), _ptr(lay["clip_vx"]),
                    _ptr(lay["clip_P_off"]), _ptr(lay["tok_ptr"]), _ptr(lay["tok_ids"]), _ptr(wpgen), _ptr(logits),
                    _ll(logits.stride(0)), _ptr(lay["labels"]), _f(lay["smoothing"]), _ptr(P), _ptr(alpha), _ptr(pgen),
                    _ptr(ctx), _ptr(None if dP is None else self._c(dP)), _ptr(dloss), _ptr(ddec), _ptr(dG), _ptr(dE),
-                   _ptr(du), _ptr(dw), _ptr(db), _ptr(dlog))
+                   _ptr(du), _ptr(dw), _ptr(db), _ptr(dlog), _ptr(dsc))
         return ddec, dG, dE, dw, db, dlog
 
     def softmax_ls_fwd(self, logits, labels, V, smoothing):
@@ -506,9 +507,10 @@ class CudaBackend:
         W = emb.shape[1]
         dP = torch.empty_like(P)
         demb = torch.empty_like(emb, dtype=torch.float32)
+        tv = torch.empty(Nc, V, dtype=torch.float32, device=P.device)
         self._call("svpc_gumbel_bwd", Nc, Lt, V, W, _ptr(P), _ptr(self._c(g)), _ptr(lay["clip_P_off"]), _ptr(lay["clip_vx"]),
                    _f(lay["tau"]), _ptr(self._c(emb)), _ptr(text_mask), _ptr(idx), _ptr(yval), _ptr(self._c(dx)), _ptr(dP),
-                   _ptr(demb))
+                   _ptr(demb), _ptr(tv))
         return dP, demb
 
     # ------------------------------------------------------------------ greedy decoding
