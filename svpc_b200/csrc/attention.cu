@@ -8,8 +8,28 @@
 
 #define AT_THREADS 256
 
+// 8 consecutive elements of a row -> fp32 shared memory (16-byte global loads when the row slice is aligned)
+__device__ __forceinline__ void at_ld8(float* dst, const bf16* src) {
+  const uint4 u = *reinterpret_cast<const uint4*>(src);
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+  for (int e = 0; e < 4; ++e) { dst[2 * e] = __low2float(h[e]); dst[2 * e + 1] = __high2float(h[e]); }
+}
+__device__ __forceinline__ void at_ld8(float* dst, const float* src) {
+  const float4 a = *reinterpret_cast<const float4*>(src), b = *reinterpret_cast<const float4*>(src + 4);
+  dst[0] = a.x; dst[1] = a.y; dst[2] = a.z; dst[3] = a.w; dst[4] = b.x; dst[5] = b.y; dst[6] = b.z; dst[7] = b.w;
+}
+
 template <typename T>
 __device__ __forceinline__ void at_load_rows(float* dst, int pitch, const T* src, long long ld, int rows, int dh) {
+  if ((dh & 7) == 0 && (ld & 7) == 0 && ((uintptr_t)src & 15) == 0) {
+    const int cpr = dh >> 3;                       // 8-element chunks per row
+    for (int i = threadIdx.x; i < rows * cpr; i += AT_THREADS) {
+      const int r = i / cpr, c = i - r * cpr;
+      at_ld8(dst + r * pitch + c * 8, src + (long long)r * ld + c * 8);
+    }
+    return;
+  }
   for (int i = threadIdx.x; i < rows * dh; i += AT_THREADS) {
     const int r = i / dh, d = i - r * dh;
     dst[r * pitch + d] = ldf(src + (long long)r * ld + d);

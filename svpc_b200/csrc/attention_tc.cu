@@ -33,15 +33,19 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
   return *reinterpret_cast<const uint32_t*>(&v);
 }
 
-// rows [0, len) of one head (64 bf16 = 8 x 16 B per row) -> smem, rows [len, rows_pad) zero-filled
+// rows [0, len) of one head (64 bf16 = 8 x 16 B per row) -> smem, rows [len, rows_pad) zero-filled.  Asynchronous
+// 16-byte copies (cp.async, zero-fill through src-size 0): every load of the CTA's operands is in flight at once instead
+// of one global-load round trip per loop iteration; atc_load_wait() before the barrier that publishes the tiles.
 __device__ __forceinline__ void atc_load(bf16* dst, const bf16* src, long long ld, int len, int rows_pad) {
   for (int i = threadIdx.x; i < rows_pad * 8; i += blockDim.x) {
     const int r = i >> 3, c = i & 7;
-    uint4 v = make_uint4(0u, 0u, 0u, 0u);
-    if (r < len) v = *reinterpret_cast<const uint4*>(src + (long long)r * ld + c * 8);
-    *reinterpret_cast<uint4*>(dst + r * ATC_PITCH + c * 8) = v;
+    const bf16* g = src + (long long)(r < len ? r : 0) * ld + c * 8;
+    const uint32_t nbytes = r < len ? 16u : 0u;
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(atc_smem(dst + r * ATC_PITCH + c * 8)), "l"(g), "r"(nbytes)
+                 : "memory");
   }
 }
+__device__ __forceinline__ void atc_load_wait() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 // A fragments (16 rows x 64) of a row-major smem tile starting at row r0
 __device__ __forceinline__ void atc_load_a(uint32_t (&f)[4][4], const bf16* base, int r0, int lane) {
@@ -228,6 +232,7 @@ __global__ void __launch_bounds__(256) attn_tc_fwd_kernel(const AtcParams p) {
   atc_load(sV, p.v + (long long)ko * p.ldv + h * ATC_DH, p.ldv, lk, p.lk_pad);
   for (int j = threadIdx.x; j < p.lk_pad; j += blockDim.x)
     madd[j] = (j < lk && p.key_mask) ? (1.f - p.key_mask[ko + j]) * -10000.f : 0.f;
+  atc_load_wait();
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int r0 = warp * 16;
@@ -307,6 +312,7 @@ __global__ void __launch_bounds__(NT <= 14 ? 224 : 256, NT <= 14 ? 2 : 1) attn_t
   atc_load(sV, p.v + (long long)ko * p.ldv + h * ATC_DH, p.ldv, lk, p.lk_pad);
   for (int j = threadIdx.x; j < p.lk_pad; j += blockDim.x)
     madd[j] = (j < lk && p.key_mask) ? (1.f - p.key_mask[ko + j]) * -10000.f : 0.f;
+  atc_load_wait();
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
   const int r0 = warp * 16;

@@ -94,8 +94,94 @@ __global__ void __launch_bounds__(GS_THREADS) gemm_simt_kernel(const GemmSimtPar
   }
 }
 
+// shared epilogue of the thin kernels: one output element
+template <typename TD>
+__device__ __forceinline__ void gs_epilogue(const GemmSimtParams& p, int m, int n, float v, bool dropping, uint32_t dkey,
+                                            float dinv) {
+  TD* __restrict__ D = (TD*)p.D;
+  const TD* __restrict__ R = (const TD*)p.residual;
+  TD* __restrict__ Pre = (TD*)p.pre;
+  if (p.bias) v += p.bias[n];
+  if (Pre) stf(Pre + (long long)m * p.ldp + n, v);
+  v = svpc_act(v, p.act);
+  if (dropping) v *= svpc_drop_scale(dkey, p.drop.p, dinv, (unsigned long long)m * p.N + n);
+  if (R) v += ldf(R + (long long)m * p.ldr + n);
+  TD* d = D + (long long)m * p.ldd + n;
+  if (p.accumulate) v += ldf(d);
+  stf(d, v);
+}
+
+// N <= 8 outputs per row, both operands K-major (the reasoner's 768 -> 3 and 300 -> 1 projections, model.py:804, 811):
+// one warp per row of A, lanes along K, N accumulators, shuffle reduction.  The 64 x 64 tile kernel would put such a
+// problem on 3 CTAs.
+#define GS_ROWDOT_MAXN 8
+template <typename TA, typename TB, typename TD>
+__global__ void __launch_bounds__(256) gemm_rowdot_kernel(const GemmSimtParams p) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m = blockIdx.x * 8 + warp;
+  if (m >= p.M) return;
+  const TA* __restrict__ a = (const TA*)p.A + (long long)m * p.sa_m;
+  const TB* __restrict__ B = (const TB*)p.B;
+  float acc[GS_ROWDOT_MAXN];
+#pragma unroll
+  for (int n = 0; n < GS_ROWDOT_MAXN; ++n) acc[n] = 0.f;
+  for (int k = lane; k < p.K; k += 32) {
+    const float x = ldf(a + k);
+#pragma unroll
+    for (int n = 0; n < GS_ROWDOT_MAXN; ++n)
+      if (n < p.N) acc[n] = fmaf(x, ldf(B + (long long)n * p.sb_n + k), acc[n]);
+  }
+  const bool dropping = p.drop.seed != nullptr && p.drop.p > 0.f;
+  const uint32_t dkey = svpc_drop_key(p.drop);
+  const float dinv = dropping ? 1.f / (1.f - p.drop.p) : 1.f;
+#pragma unroll
+  for (int n = 0; n < GS_ROWDOT_MAXN; ++n) {
+    if (n >= p.N) break;
+    const float v = warp_sum(acc[n]);
+    if (lane == 0) gs_epilogue<TD>(p, m, n, v, dropping, dkey, dinv);
+  }
+}
+
+// B MN-major (N contiguous) and a short loop: M <= 8 (weight gradients of those projections: few rows of dz^T against
+// all of x) or K <= 8 (their input gradients).  One thread per output element, n fastest: B reads coalesce, A reads
+// broadcast.
+template <typename TA, typename TB, typename TD>
+__global__ void __launch_bounds__(256) gemm_pointwise_kernel(const GemmSimtParams p) {
+  const long long e = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (e >= (long long)p.M * p.N) return;
+  const int m = (int)(e / p.N), n = (int)(e - (long long)m * p.N);
+  const TA* __restrict__ a = (const TA*)p.A + (long long)m * p.sa_m;
+  const TB* __restrict__ b = (const TB*)p.B + n;
+  // 16 independent load pairs in flight per round trip (the loop is latency-bound: few CTAs, one element per thread)
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  int k = 0;
+  for (; k + 16 <= p.K; k += 16) {
+    float av[16], bv[16];
+#pragma unroll
+    for (int u = 0; u < 16; ++u) {
+      av[u] = ldf(a + (long long)(k + u) * p.sa_k);
+      bv[u] = ldf(b + (long long)(k + u) * p.sb_k);
+    }
+#pragma unroll
+    for (int u = 0; u < 16; ++u) acc[u & 3] = fmaf(av[u], bv[u], acc[u & 3]);
+  }
+  for (; k < p.K; ++k) acc[0] = fmaf(ldf(a + (long long)k * p.sa_k), ldf(b + (long long)k * p.sb_k), acc[0]);
+  const float a0 = acc[0], a1 = acc[1], a2 = acc[2], a3 = acc[3];
+  const bool dropping = p.drop.seed != nullptr && p.drop.p > 0.f;
+  gs_epilogue<TD>(p, m, n, (a0 + a1) + (a2 + a3), dropping, svpc_drop_key(p.drop), dropping ? 1.f / (1.f - p.drop.p) : 1.f);
+}
+
 template <typename TA, typename TB>
 static int launch_td(GemmSimtParams p, int dtD, cudaStream_t st) {
+  cudaStream_t st_ = st;
+  if (p.N <= GS_ROWDOT_MAXN && p.sa_k == 1 && p.sb_k == 1 && p.K >= 64) {
+    SVPC_DISPATCH(dtD, TD, (gemm_rowdot_kernel<TA, TB, TD><<<svpc_cdiv(p.M, 8), 256, 0, st_>>>(p)));
+    return svpc_check_launch("gemm_rowdot");
+  }
+  if (p.sb_n == 1 && (p.M <= 8 || p.K <= 8) && p.K <= 4096) {
+    SVPC_DISPATCH(dtD, TD, (gemm_pointwise_kernel<TA, TB, TD><<<svpc_cdiv((long long)p.M * p.N, 256), 256, 0, st_>>>(p)));
+    return svpc_check_launch("gemm_pointwise");
+  }
   const int tiles = svpc_cdiv(p.N, GS_BN) * svpc_cdiv(p.M, GS_BM);
   int split = 1;
   const bool plain = !p.bias && p.act == SVPC_ACT_NONE && !p.residual && !p.pre && dtD == SVPC_F32 && !p.drop.seed;

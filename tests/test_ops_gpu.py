@@ -44,7 +44,8 @@ I32 = lambda x: torch.tensor(x, dtype=torch.int32, device=DEV)
 
 # ---------------------------------------------------------------------------------------------- GEMM
 @pytest.mark.parametrize("dt", [F32, BF16])
-@pytest.mark.parametrize("M,N,K", [(70, 50, 33), (128, 64, 64), (5, 3, 300), (16, 130, 20), (1, 1, 7)])
+@pytest.mark.parametrize("M,N,K", [(70, 50, 33), (128, 64, 64), (5, 3, 300), (16, 130, 20), (1, 1, 7),
+                                   (192, 3, 768), (192, 1, 300), (3, 768, 192), (192, 768, 3)])   # thin kernels
 def test_gemm_simt(cb, tb, dt, M, N, K):
     from svpc_b200.cuda_backend import GEMM_SIMT
     a, b = rnd(M, K, dtype=dt), rnd(N, K, dtype=dt, seed=2)
