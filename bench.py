@@ -423,11 +423,13 @@ def main():
     gf_need_step = (GF_PER_CLIP_AS_WRITTEN[args.mode] - GF_SAVED_PER_CLIP) * n_clips
     if not args.no_kernel_timing and rank == 0:
         hbm, tf_sus, tf_burst, src = peaks()
+        was_enabled, reducer.enabled = reducer.enabled, False     # rank-0-only pass: no collective may be issued here
         be.start_timing()
         nrep = 2
         for _ in range(nrep):
             step(dev_args, noise_dev)
         per = be.stop_timing()
+        reducer.enabled = was_enabled
         tot = sum(t for _, t in per.values())
         top = sorted(((t / nrep, n // nrep, k) for k, (n, t) in per.items()), reverse=True)[:12]
         tc = [(gemm_flops(k) * n, t, n, k) for k, (n, t) in per.items() if k.startswith("gemm_tc")]

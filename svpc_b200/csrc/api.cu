@@ -32,6 +32,7 @@ extern "C" void svpc_reset_launch_count(void) { g_launches.store(0); }
 // ------------------------------------------------------------------------------------------------
 template <typename TS, typename TD>
 __global__ void cast_kernel(long long n, const TS* __restrict__ s, TD* __restrict__ d) {
+  svpc_pdl_sync();
   long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const long long stride = (long long)gridDim.x * blockDim.x;
   for (; i < n; i += stride) stf(d + i, ldf(s + i));
@@ -41,7 +42,7 @@ extern "C" int svpc_cast(long long n, const void* src, int dts, void* dst, int d
   if (n <= 0) return SVPC_OK;
   cudaStream_t st = (cudaStream_t)stream;
   int blocks = svpc_imin(svpc_cdiv(n, 256), SVPC_NUM_SMS * 16);
-  SVPC_DISPATCH(dts, TS, SVPC_DISPATCH(dtd, TD, (cast_kernel<TS, TD><<<blocks, 256, 0, st>>>(n, (const TS*)src, (TD*)dst))));
+  SVPC_DISPATCH(dts, TS, SVPC_DISPATCH(dtd, TD, (svpc_launch(cast_kernel<TS, TD>, blocks, 256, 0, st, n, (const TS*)src, (TD*)dst))));
   return svpc_check_launch("cast");
 }
 
@@ -49,6 +50,7 @@ extern "C" int svpc_cast(long long n, const void* src, int dts, void* dst, int d
 // that are multiples of 16 bytes, the model's word-vector size 300 and vocabulary 951 are not multiples of 8)
 template <typename TS, typename TD>
 __global__ void cast2d_kernel(int rows, int cols, const TS* __restrict__ s, long long lds, TD* __restrict__ d, long long ldd) {
+  svpc_pdl_sync();
   const long long n = (long long)rows * cols;
   long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const long long stride = (long long)gridDim.x * blockDim.x;
@@ -63,12 +65,13 @@ extern "C" int svpc_cast2d(int rows, int cols, const void* src, int dts, long lo
   if (rows <= 0 || cols <= 0) return SVPC_OK;
   cudaStream_t st = (cudaStream_t)stream;
   int blocks = svpc_imin(svpc_cdiv((long long)rows * cols, 256), SVPC_NUM_SMS * 16);
-  SVPC_DISPATCH(dts, TS, SVPC_DISPATCH(dtd, TD, (cast2d_kernel<TS, TD><<<blocks, 256, 0, st>>>(rows, cols, (const TS*)src, lds,
+  SVPC_DISPATCH(dts, TS, SVPC_DISPATCH(dtd, TD, (svpc_launch(cast2d_kernel<TS, TD>, blocks, 256, 0, st, rows, cols, (const TS*)src, lds,
                                                                                              (TD*)dst, ldd))));
   return svpc_check_launch("cast2d");
 }
 
 __global__ void dropout_mask_kernel(long long n, const SvpcDrop drop, float* __restrict__ out) {
+  svpc_pdl_sync();
   const bool dropping = drop.seed != nullptr && drop.p > 0.f;
   const uint32_t key = svpc_drop_key(drop);
   const float inv = dropping ? 1.f / (1.f - drop.p) : 1.f;
@@ -81,12 +84,13 @@ extern "C" int svpc_dropout_mask(long long n, const unsigned int* drop_seed, uns
                                  svpc_stream_t stream) {
   if (n <= 0) return SVPC_OK;
   const SvpcDrop drop{drop_p > 0.f ? drop_seed : nullptr, drop_site, drop_p};
-  dropout_mask_kernel<<<svpc_imin(svpc_cdiv(n, 256), SVPC_NUM_SMS * 16), 256, 0, (cudaStream_t)stream>>>(n, drop, out);
+  svpc_launch(dropout_mask_kernel, svpc_imin(svpc_cdiv(n, 256), SVPC_NUM_SMS * 16), 256, 0, (cudaStream_t)stream, n, drop, out);
   return svpc_check_launch("dropout_mask");
 }
 
 // deterministic single-CTA sum (loss reductions: a few thousand elements)
 __global__ void sum_kernel(long long n, const float* __restrict__ x, float* __restrict__ out) {
+  svpc_pdl_sync();
   __shared__ float red[64];
   float acc = 0.f;
   for (long long i = threadIdx.x; i < n; i += blockDim.x) acc += x[i];
@@ -95,6 +99,6 @@ __global__ void sum_kernel(long long n, const float* __restrict__ x, float* __re
 }
 
 extern "C" int svpc_sum(long long n, const float* x, float* out, svpc_stream_t stream) {
-  sum_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(n, x, out);
+  svpc_launch(sum_kernel, 1, 1024, 0, (cudaStream_t)stream, n, x, out);
   return svpc_check_launch("sum");
 }

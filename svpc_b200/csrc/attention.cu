@@ -74,6 +74,7 @@ __global__ void __launch_bounds__(AT_THREADS) attn_fwd_kernel(int H, int dh, con
                                                               const float* __restrict__ key_mask, int causal, int max_lq,
                                                               int max_lk, T* __restrict__ ctx, long long ldo,
                                                               const SvpcDrop drop) {
+  svpc_pdl_sync();
   extern __shared__ float sm[];
   const int n = blockIdx.x / H, h = blockIdx.x - n * H;
   const int lq = q_len[n], lk = k_len[n], qo = q_off[n], ko = k_off[n];
@@ -120,6 +121,7 @@ __global__ void __launch_bounds__(AT_THREADS) attn_bwd_kernel(int H, int dh, con
                                                               T* __restrict__ dq, long long lddq, T* __restrict__ dk,
                                                               long long lddk, T* __restrict__ dv, long long lddv,
                                                               const SvpcDrop drop) {
+  svpc_pdl_sync();
   extern __shared__ float sm[];
   const bool dropping = drop.seed != nullptr && drop.p > 0.f;
   const uint32_t dkey = svpc_drop_key(drop);
@@ -227,7 +229,7 @@ extern "C" int svpc_attn_fwd(int n_seq, int H, int dh, const void* q, long long 
   cudaStream_t st = (cudaStream_t)stream;
   SVPC_DISPATCH(dt, T, {
     cudaFuncSetAttribute(attn_fwd_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    attn_fwd_kernel<T><<<n_seq * H, AT_THREADS, smem, st>>>(H, dh, (const T*)q, ldq, (const T*)k, ldk, (const T*)v, ldv, q_off,
+    svpc_launch(attn_fwd_kernel<T>, n_seq * H, AT_THREADS, smem, st, H, dh, (const T*)q, ldq, (const T*)k, ldk, (const T*)v, ldv, q_off,
                                                             q_len, k_off, k_len, key_mask, causal, max_lq, max_lk, (T*)ctx, ldo, drop);
   });
   return svpc_check_launch("attn_fwd");
@@ -249,7 +251,7 @@ extern "C" int svpc_attn_bwd(int n_seq, int H, int dh, const void* q, long long 
   cudaStream_t st = (cudaStream_t)stream;
   SVPC_DISPATCH(dt, T, {
     cudaFuncSetAttribute(attn_bwd_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    attn_bwd_kernel<T><<<n_seq * H, AT_THREADS, smem, st>>>(H, dh, (const T*)q, ldq, (const T*)k, ldk, (const T*)v, ldv, q_off,
+    svpc_launch(attn_bwd_kernel<T>, n_seq * H, AT_THREADS, smem, st, H, dh, (const T*)q, ldq, (const T*)k, ldk, (const T*)v, ldv, q_off,
                                                             q_len, k_off, k_len, key_mask, causal, max_lq, max_lk,
                                                             (const T*)dctx, lddo, (T*)dq, lddq, (T*)dk, lddk, (T*)dv, lddv, drop);
   });

@@ -220,6 +220,7 @@ struct AtcParams {
 // ------------------------------------------------------------------------------------------------ forward
 template <int NT>
 __global__ void __launch_bounds__(256) attn_tc_fwd_kernel(const AtcParams p) {
+  svpc_pdl_sync();
   extern __shared__ __align__(16) uint8_t atc_raw[];
   bf16* sQ = reinterpret_cast<bf16*>(atc_raw);
   bf16* sK = sQ + p.lq_pad * ATC_PITCH;
@@ -296,6 +297,7 @@ __device__ __forceinline__ void atc_write_x(bf16* X, int xp, const float (&s)[NT
 
 template <int NT>
 __global__ void __launch_bounds__(NT <= 14 ? 224 : 256, NT <= 14 ? 2 : 1) attn_tc_bwd_kernel(const AtcParams p) {
+  svpc_pdl_sync();
   extern __shared__ __align__(16) uint8_t atc_raw[];
   bf16* sQ = reinterpret_cast<bf16*>(atc_raw);
   bf16* sdO = sQ + p.lq_pad * ATC_PITCH;
@@ -413,9 +415,9 @@ int svpc_attn_tc_fwd_launch(int n_seq, const AtcParams& p0, int max_lq, int max_
     cudaFuncSetAttribute(attn_tc_fwd_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
     attr = true;
   }
-  if (p.lk_pad <= 32) attn_tc_fwd_kernel<4><<<n_seq * p.H, threads, smem, st>>>(p);
-  else if (p.lk_pad <= 112) attn_tc_fwd_kernel<14><<<n_seq * p.H, threads, smem, st>>>(p);
-  else attn_tc_fwd_kernel<16><<<n_seq * p.H, threads, smem, st>>>(p);
+  if (p.lk_pad <= 32) svpc_launch(attn_tc_fwd_kernel<4>, n_seq * p.H, threads, smem, st, p);
+  else if (p.lk_pad <= 112) svpc_launch(attn_tc_fwd_kernel<14>, n_seq * p.H, threads, smem, st, p);
+  else svpc_launch(attn_tc_fwd_kernel<16>, n_seq * p.H, threads, smem, st, p);
   return svpc_check_launch("attn_tc_fwd");
 }
 
@@ -434,9 +436,9 @@ int svpc_attn_tc_bwd_launch(int n_seq, const AtcParams& p0, int max_lq, int max_
     cudaFuncSetAttribute(attn_tc_bwd_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 120 * 1024);
     attr = true;
   }
-  if (p.lk_pad <= 32) attn_tc_bwd_kernel<4><<<n_seq * p.H, threads, smem, st>>>(p);
-  else if (p.lk_pad <= 112 && p.lq_pad <= 112) attn_tc_bwd_kernel<14><<<n_seq * p.H, threads, smem, st>>>(p);
-  else attn_tc_bwd_kernel<16><<<n_seq * p.H, threads, smem, st>>>(p);
+  if (p.lk_pad <= 32) svpc_launch(attn_tc_bwd_kernel<4>, n_seq * p.H, threads, smem, st, p);
+  else if (p.lk_pad <= 112 && p.lq_pad <= 112) svpc_launch(attn_tc_bwd_kernel<14>, n_seq * p.H, threads, smem, st, p);
+  else svpc_launch(attn_tc_bwd_kernel<16>, n_seq * p.H, threads, smem, st, p);
   return svpc_check_launch("attn_tc_bwd");
 }
 

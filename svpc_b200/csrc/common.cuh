@@ -4,6 +4,8 @@
 #include <cuda_bf16.h>
 #include <stdint.h>
 #include <math.h>
+#include <stdlib.h>
+#include <string.h>
 #include "../../include/svpc_b200.h"
 
 void svpc_set_error(const char* fmt, ...);
@@ -21,6 +23,43 @@ static inline int svpc_cdiv(long long a, long long b) { return (int)((a + b - 1)
 static inline int svpc_imin(long long a, long long b) { return (int)(a < b ? a : b); }
 
 #define SVPC_NUM_SMS 148
+
+// ---- programmatic dependent launch (PDL).  The step is ~450 short kernels replayed from a CUDA graph; between two
+// dependent kernels the GPU otherwise drains, then schedules and launches the next grid.  Every kernel of this library is
+// launched with cudaLaunchAttributeProgrammaticStreamSerialization and starts with svpc_pdl_sync():
+//   griddepcontrol.launch_dependents  the NEXT kernel's CTAs may be made resident as soon as all of this grid's CTAs are
+//   griddepcontrol.wait               block until every prerequisite grid has completed and its memory is visible
+// so nothing is read or written before the producer has finished, but launch latency and the tail of the previous grid
+// overlap.  SVPC_PDL=0 in the environment falls back to plain stream order.
+#if defined(__CUDACC__)
+__device__ __forceinline__ void svpc_pdl_sync() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+#endif
+static inline int svpc_pdl_enabled() {
+  static int on = -1;
+  if (on < 0) {
+    const char* e = getenv("SVPC_PDL");
+    on = e ? (atoi(e) != 0) : 1;
+  }
+  return on;
+}
+template <typename... KArgs, typename... Args>
+static inline cudaError_t svpc_launch(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                                      Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = svpc_pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
 
 // ---- typed loads / stores (activations are fp32 or bf16; math is always fp32)
 typedef __nv_bfloat16 bf16;

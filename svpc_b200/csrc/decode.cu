@@ -7,6 +7,7 @@
 __global__ void greedy_pick_kernel(int rows, const float* __restrict__ scores, const int* __restrict__ row_off, long long ld,
                                    const int* __restrict__ row_width, int width, const int* __restrict__ row_noov, int unk,
                                    int* __restrict__ next_in, long long* __restrict__ ext_out, long long ld_ext, int pos) {
+  svpc_pdl_sync();
   const int r = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
   if (r >= rows) return;
@@ -35,7 +36,7 @@ extern "C" int svpc_greedy_pick(int rows, const float* scores, const int* row_of
                                 int width, const int* row_noov, int unk, int* next_in, long long* ext_out, long long ld_ext,
                                 int pos, svpc_stream_t stream) {
   if (rows <= 0) return SVPC_OK;
-  greedy_pick_kernel<<<svpc_cdiv(rows, 8), 256, 0, (cudaStream_t)stream>>>(rows, scores, row_off, ld, row_width, width,
+  svpc_launch(greedy_pick_kernel, svpc_cdiv(rows, 8), 256, 0, (cudaStream_t)stream, rows, scores, row_off, ld, row_width, width,
                                                                           row_noov, unk, next_in, ext_out, ld_ext, pos);
   return svpc_check_launch("greedy_pick");
 }

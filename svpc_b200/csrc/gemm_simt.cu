@@ -24,6 +24,7 @@ struct GemmSimtParams {
 
 template <typename TA, typename TB, typename TD>
 __global__ void __launch_bounds__(GS_THREADS) gemm_simt_kernel(const GemmSimtParams p) {
+  svpc_pdl_sync();
   __shared__ float As[GS_BK][GS_BM + 4];
   __shared__ float Bs[GS_BK][GS_BN + 4];
   const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
@@ -117,6 +118,7 @@ __device__ __forceinline__ void gs_epilogue(const GemmSimtParams& p, int m, int 
 #define GS_ROWDOT_MAXN 8
 template <typename TA, typename TB, typename TD>
 __global__ void __launch_bounds__(256) gemm_rowdot_kernel(const GemmSimtParams p) {
+  svpc_pdl_sync();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int m = blockIdx.x * 8 + warp;
   if (m >= p.M) return;
@@ -147,6 +149,7 @@ __global__ void __launch_bounds__(256) gemm_rowdot_kernel(const GemmSimtParams p
 // broadcast.
 template <typename TA, typename TB, typename TD>
 __global__ void __launch_bounds__(256) gemm_pointwise_kernel(const GemmSimtParams p) {
+  svpc_pdl_sync();
   const long long e = (long long)blockIdx.x * 256 + threadIdx.x;
   if (e >= (long long)p.M * p.N) return;
   const int m = (int)(e / p.N), n = (int)(e - (long long)m * p.N);
@@ -175,11 +178,11 @@ template <typename TA, typename TB>
 static int launch_td(GemmSimtParams p, int dtD, cudaStream_t st) {
   cudaStream_t st_ = st;
   if (p.N <= GS_ROWDOT_MAXN && p.sa_k == 1 && p.sb_k == 1 && p.K >= 64) {
-    SVPC_DISPATCH(dtD, TD, (gemm_rowdot_kernel<TA, TB, TD><<<svpc_cdiv(p.M, 8), 256, 0, st_>>>(p)));
+    SVPC_DISPATCH(dtD, TD, (svpc_launch(gemm_rowdot_kernel<TA, TB, TD>, svpc_cdiv(p.M, 8), 256, 0, st_, p)));
     return svpc_check_launch("gemm_rowdot");
   }
   if (p.sb_n == 1 && (p.M <= 8 || p.K <= 8) && p.K <= 4096) {
-    SVPC_DISPATCH(dtD, TD, (gemm_pointwise_kernel<TA, TB, TD><<<svpc_cdiv((long long)p.M * p.N, 256), 256, 0, st_>>>(p)));
+    SVPC_DISPATCH(dtD, TD, (svpc_launch(gemm_pointwise_kernel<TA, TB, TD>, svpc_cdiv((long long)p.M * p.N, 256), 256, 0, st_, p)));
     return svpc_check_launch("gemm_pointwise");
   }
   const int tiles = svpc_cdiv(p.N, GS_BN) * svpc_cdiv(p.M, GS_BM);
@@ -195,7 +198,7 @@ static int launch_td(GemmSimtParams p, int dtD, cudaStream_t st) {
     if (e != cudaSuccess) { svpc_set_error("gemm_simt: memset2D: %s", cudaGetErrorString(e)); return SVPC_ERR_CUDA; }
   }
   dim3 grid(svpc_cdiv(p.N, GS_BN), svpc_cdiv(p.M, GS_BM), split);
-  SVPC_DISPATCH(dtD, TD, (gemm_simt_kernel<TA, TB, TD><<<grid, GS_THREADS, 0, st>>>(p)));
+  SVPC_DISPATCH(dtD, TD, (svpc_launch(gemm_simt_kernel<TA, TB, TD>, grid, GS_THREADS, 0, st, p)));
   return svpc_check_launch("gemm_simt");
 }
 

@@ -321,6 +321,7 @@ template <bool A_MN, bool B_MN, typename TD, int ACT, bool DROP>
 __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA,
                                                                 const __grid_constant__ CUtensorMap tmB,
                                                                 const __grid_constant__ TcParams p) {
+  svpc_pdl_sync();
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   float* epi_stage = reinterpret_cast<float*>(smem + TC_STAGES * TC_STAGE_BYTES);
@@ -547,7 +548,7 @@ static int launch_cfg(const CUtensorMap& ta, const CUtensorMap& tb, const TcPara
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_BYTES);
     attr_set = true;
   }
-  kern<<<grid, TC_THREADS, TC_SMEM_BYTES, st>>>(ta, tb, p);
+  svpc_launch(kern, grid, TC_THREADS, TC_SMEM_BYTES, st, ta, tb, p);
   return svpc_check_launch("gemm_tc");
 }
 

@@ -50,6 +50,7 @@ struct LstmStepParams {
 };
 
 __global__ void __launch_bounds__(LSTM_WARPS * 32) lstm_step_fwd_kernel(const LstmStepParams p) {
+  svpc_pdl_sync();
   extern __shared__ __align__(16) float hsm[];          // [LSTM_BV][D]
   const int dir = blockIdx.y, b0 = blockIdx.z * LSTM_BV;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -119,6 +120,7 @@ __global__ void __launch_bounds__(LSTM_WARPS * 32) lstm_step_fwd_kernel(const Ls
 
 // Step j of the reverse sweep (called with j = Smax-1 ... 0).  rows of step j+1 give the gate gradients already computed.
 __global__ void __launch_bounds__(LSTM_WARPS * 32) lstm_step_bwd_kernel(const LstmStepParams p) {
+  svpc_pdl_sync();
   extern __shared__ __align__(16) float gsm[];          // [LSTM_BV][D] chunk of the next step's gate gradients
   const int dir = blockIdx.y, b0 = blockIdx.z * LSTM_BV;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -193,8 +195,8 @@ static int lstm_launch(bool bwd, const LstmStepParams& p, cudaStream_t st) {
     attr = true;
   }
   dim3 grid(svpc_cdiv(p.D, LSTM_WARPS), 2, svpc_cdiv(p.B, LSTM_BV));
-  if (bwd) lstm_step_bwd_kernel<<<grid, LSTM_WARPS * 32, smem, st>>>(p);
-  else lstm_step_fwd_kernel<<<grid, LSTM_WARPS * 32, smem, st>>>(p);
+  if (bwd) svpc_launch(lstm_step_bwd_kernel, grid, LSTM_WARPS * 32, smem, st, p);
+  else svpc_launch(lstm_step_fwd_kernel, grid, LSTM_WARPS * 32, smem, st, p);
   return svpc_check_launch(bwd ? "lstm_step_bwd" : "lstm_step_fwd");
 }
 
@@ -214,6 +216,7 @@ extern "C" int svpc_lstm_step_bwd(int B, int D, int Nc, int Smax, int j, const f
 
 // out[c, r] = in[r, c]  (fp32; W_hh^T for the reverse sweep, once per backward)
 __global__ void transpose_f32_kernel(int R, int Cc, const float* __restrict__ in, float* __restrict__ out) {
+  svpc_pdl_sync();
   __shared__ float t[32][33];
   const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
   for (int i = threadIdx.y; i < 32; i += blockDim.y) {
@@ -230,6 +233,6 @@ __global__ void transpose_f32_kernel(int R, int Cc, const float* __restrict__ in
 extern "C" int svpc_transpose_f32(int R, int Cc, const float* in, float* out, svpc_stream_t stream) {
   if (R <= 0 || Cc <= 0) return SVPC_OK;
   dim3 grid(svpc_cdiv(Cc, 32), svpc_cdiv(R, 32));
-  transpose_f32_kernel<<<grid, dim3(32, 8), 0, (cudaStream_t)stream>>>(R, Cc, in, out);
+  svpc_launch(transpose_f32_kernel, grid, dim3(32, 8), 0, (cudaStream_t)stream, R, Cc, in, out);
   return svpc_check_launch("transpose_f32");
 }

@@ -8,6 +8,7 @@
 // backward as ATen: g * (p - y) / max((1 - p) * p, 1e-12)
 // ------------------------------------------------------------------------------------------------
 __global__ void bce_fwd_kernel(long long n, const float* __restrict__ p, const float* __restrict__ y, float* __restrict__ loss) {
+  svpc_pdl_sync();
   __shared__ float red[64];
   float acc = 0.f;
   for (long long i = threadIdx.x; i < n; i += blockDim.x) {
@@ -19,16 +20,17 @@ __global__ void bce_fwd_kernel(long long n, const float* __restrict__ p, const f
 }
 __global__ void bce_bwd_kernel(long long n, const float* __restrict__ p, const float* __restrict__ y,
                                const float* __restrict__ g, float* __restrict__ dp) {
+  svpc_pdl_sync();
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) dp[i] = g[0] * (p[i] - y[i]) / fmaxf((1.f - p[i]) * p[i], 1e-12f);
 }
 extern "C" int svpc_bce_fwd(long long n, const float* p, const float* y, float* loss, svpc_stream_t stream) {
-  bce_fwd_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(n, p, y, loss);
+  svpc_launch(bce_fwd_kernel, 1, 1024, 0, (cudaStream_t)stream, n, p, y, loss);
   return svpc_check_launch("bce_fwd");
 }
 extern "C" int svpc_bce_bwd(long long n, const float* p, const float* y, const float* g, float* dp, svpc_stream_t stream) {
   if (n <= 0) return SVPC_OK;
-  bce_bwd_kernel<<<svpc_cdiv(n, 256), 256, 0, (cudaStream_t)stream>>>(n, p, y, g, dp);
+  svpc_launch(bce_bwd_kernel, svpc_cdiv(n, 256), 256, 0, (cudaStream_t)stream, n, p, y, g, dp);
   return svpc_check_launch("bce_bwd");
 }
 
@@ -60,6 +62,7 @@ __device__ __forceinline__ float asl_elem(float p, float y, float* dldp) {
 }
 
 __global__ void asl_rows_kernel(int rows, int A, const float* __restrict__ y, int* __restrict__ active) {
+  svpc_pdl_sync();
   const int r = blockIdx.x;
   __shared__ int any;
   if (threadIdx.x == 0) any = 0;
@@ -73,6 +76,7 @@ __global__ void asl_rows_kernel(int rows, int A, const float* __restrict__ y, in
 
 __global__ void asl_fwd_kernel(int rows, int A, const float* __restrict__ p, const float* __restrict__ y,
                                float* __restrict__ loss) {
+  svpc_pdl_sync();
   __shared__ float red[64];
   __shared__ int any_s[32];
   float acc = 0.f;
@@ -91,6 +95,7 @@ __global__ void asl_fwd_kernel(int rows, int A, const float* __restrict__ p, con
 
 __global__ void asl_bwd_kernel(int rows, int A, const float* __restrict__ p, const float* __restrict__ y,
                                const float* __restrict__ g, float* __restrict__ dp) {
+  svpc_pdl_sync();
   const int r = blockIdx.x;
   __shared__ int any;
   if (threadIdx.x == 0) any = 0;
@@ -108,11 +113,11 @@ __global__ void asl_bwd_kernel(int rows, int A, const float* __restrict__ p, con
 }
 
 extern "C" int svpc_asl_fwd(int rows, int A, const float* p, const float* y, float* loss, svpc_stream_t stream) {
-  asl_fwd_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(rows, A, p, y, loss);
+  svpc_launch(asl_fwd_kernel, 1, 1024, 0, (cudaStream_t)stream, rows, A, p, y, loss);
   return svpc_check_launch("asl_fwd");
 }
 extern "C" int svpc_asl_bwd(int rows, int A, const float* p, const float* y, const float* g, float* dp, svpc_stream_t stream) {
   if (rows <= 0) return SVPC_OK;
-  asl_bwd_kernel<<<rows, 128, 0, (cudaStream_t)stream>>>(rows, A, p, y, g, dp);
+  svpc_launch(asl_bwd_kernel, rows, 128, 0, (cudaStream_t)stream, rows, A, p, y, g, dp);
   return svpc_check_launch("asl_bwd");
 }

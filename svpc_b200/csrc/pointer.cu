@@ -33,6 +33,7 @@ __global__ void __launch_bounds__(PG_THREADS) pointer_fwd_kernel(
     const float* __restrict__ bpgen, const float* __restrict__ logits, long long ldl, const int* __restrict__ labels,
     float smoothing, float* __restrict__ P, float* __restrict__ loss_rows, float* __restrict__ alpha_out,
     float* __restrict__ pgen_out, float* __restrict__ ctx_out) {
+  svpc_pdl_sync();
   extern __shared__ float sm[];
   float* sdec = sm;               // D
   float* sctx = sdec + D;         // D
@@ -122,6 +123,7 @@ __global__ void __launch_bounds__(PG_THREADS) pointer_bwd_kernel(
     const float* __restrict__ P, const float* __restrict__ alpha_in, const float* __restrict__ pgen_in,
     const float* __restrict__ dP, const float* __restrict__ dloss, T* __restrict__ ddec, float* __restrict__ du_out,
     float* __restrict__ dlogits, float* __restrict__ dsc_out) {
+  svpc_pdl_sync();
   extern __shared__ float sm[];
   float* gP = sm;                    // max_vx
   float* dsc = gP + max_vx;          // max_ni   d score[i]
@@ -205,6 +207,7 @@ __global__ void __launch_bounds__(PG_THREADS) pointer_bwd_reduce_kernel(
     int Lt, int D, int max_ni, const T* __restrict__ dec, const int* __restrict__ clip_src_off,
     const int* __restrict__ clip_ni, const float* __restrict__ wpgen, const float* __restrict__ alpha_in,
     const float* __restrict__ du, const float* __restrict__ dsc_in, float* __restrict__ dG, float* __restrict__ dE) {
+  svpc_pdl_sync();
   extern __shared__ float sm[];
   float* dsc = sm;                   // Lt * max_ni
   float* beta = dsc + Lt * max_ni;   // max_ni
@@ -254,7 +257,7 @@ extern "C" int svpc_pointer_fwd(int n_clips, int Lt, int D, int V, int max_ni, i
   cudaStream_t st = (cudaStream_t)stream;
   SVPC_DISPATCH(dt, T, {
     cudaFuncSetAttribute(pointer_fwd_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    pointer_fwd_kernel<T><<<dim3(Lt, n_clips), PG_THREADS, smem, st>>>(Lt, D, V, max_ni, max_vx, (const T*)dec, G, Esrc, clip_src_off,
+    svpc_launch(pointer_fwd_kernel<T>, dim3(Lt, n_clips), PG_THREADS, smem, st, Lt, D, V, max_ni, max_vx, (const T*)dec, G, Esrc, clip_src_off,
                                                             clip_ni, clip_gi, clip_vx, clip_P_off, tok_ptr, tok_ids, wpgen,
                                                             bpgen, logits, ldl, labels, smoothing, P, loss_rows, alpha, pgen, ctx);
   });
@@ -278,11 +281,11 @@ extern "C" int svpc_pointer_bwd(int n_clips, int Lt, int D, int V, int max_ni, i
   cudaMemsetAsync(dwpgen, 0, sizeof(float) * 2 * D, st);
   SVPC_DISPATCH(dt, T, {
     cudaFuncSetAttribute(pointer_bwd_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    pointer_bwd_kernel<T><<<dim3(Lt, n_clips), PG_THREADS, smem, st>>>(
+    svpc_launch(pointer_bwd_kernel<T>, dim3(Lt, n_clips), PG_THREADS, smem, st, 
         Lt, D, V, max_ni, max_vx, (const T*)dec, G, Esrc, clip_src_off, clip_ni, clip_gi, clip_vx, clip_P_off, tok_ptr,
         tok_ids, wpgen, logits, ldl, labels, smoothing, P, alpha, pgen, dP, dloss, (T*)ddec, du, dlogits, dscore_ws);
     cudaFuncSetAttribute(pointer_bwd_reduce_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
-    pointer_bwd_reduce_kernel<T><<<n_clips, PG_THREADS, smem2, st>>>(Lt, D, max_ni, (const T*)dec, clip_src_off, clip_ni,
+    svpc_launch(pointer_bwd_reduce_kernel<T>, n_clips, PG_THREADS, smem2, st, Lt, D, max_ni, (const T*)dec, clip_src_off, clip_ni,
                                                                    wpgen, alpha, du, dscore_ws, dG, dE);
   });
   int rc = svpc_check_launch("pointer_bwd");
@@ -301,6 +304,7 @@ extern "C" int svpc_pointer_bwd(int n_clips, int Lt, int D, int V, int max_ni, i
 __global__ void __launch_bounds__(PG_THREADS) softmax_ls_fwd_kernel(int V, const float* __restrict__ logits, long long ldl,
                                                                     const int* __restrict__ labels, float smoothing,
                                                                     float* __restrict__ P, float* __restrict__ loss_rows) {
+  svpc_pdl_sync();
   __shared__ float red[64];
   const long long r = blockIdx.x;
   const float* lrow = logits + r * ldl;
@@ -327,6 +331,7 @@ __global__ void __launch_bounds__(PG_THREADS) softmax_ls_bwd_kernel(int V, const
                                                                     const float* __restrict__ P,
                                                                     const int* __restrict__ labels, float smoothing,
                                                                     float* __restrict__ dlogits, long long ldl) {
+  svpc_pdl_sync();
   __shared__ float red[64];
   const long long r = blockIdx.x;
   const int label = labels[r];
@@ -351,14 +356,14 @@ __global__ void __launch_bounds__(PG_THREADS) softmax_ls_bwd_kernel(int V, const
 extern "C" int svpc_softmax_ls_fwd(int rows, int V, const float* logits, long long ldl, const int* labels,
                                    float smoothing, float* P, float* loss_rows, svpc_stream_t stream) {
   if (rows <= 0) return SVPC_OK;
-  softmax_ls_fwd_kernel<<<rows, PG_THREADS, 0, (cudaStream_t)stream>>>(V, logits, ldl, labels, smoothing, P, loss_rows);
+  svpc_launch(softmax_ls_fwd_kernel, rows, PG_THREADS, 0, (cudaStream_t)stream, V, logits, ldl, labels, smoothing, P, loss_rows);
   return svpc_check_launch("softmax_ls_fwd");
 }
 extern "C" int svpc_softmax_ls_bwd(int rows, int V, const float* dP, const float* dloss, const float* P,
                                    const int* labels, float smoothing, float* dlogits, long long ldl,
                                    svpc_stream_t stream) {
   if (rows <= 0) return SVPC_OK;
-  softmax_ls_bwd_kernel<<<rows, PG_THREADS, 0, (cudaStream_t)stream>>>(V, dP, dloss, P, labels, smoothing, dlogits, ldl);
+  svpc_launch(softmax_ls_bwd_kernel, rows, PG_THREADS, 0, (cudaStream_t)stream, V, dP, dloss, P, labels, smoothing, dlogits, ldl);
   return svpc_check_launch("softmax_ls_bwd");
 }
 
@@ -371,6 +376,7 @@ __global__ void __launch_bounds__(PG_THREADS) gumbel_fwd_kernel(int Lt, int V, c
                                                                 const int* __restrict__ clip_P_off,
                                                                 const int* __restrict__ clip_vx, float tau,
                                                                 int* __restrict__ idx_out, float* __restrict__ yval_out) {
+  svpc_pdl_sync();
   __shared__ float red[64];
   __shared__ float smax[PG_THREADS / 32];
   __shared__ int sidx[PG_THREADS / 32];
@@ -435,6 +441,7 @@ __global__ void __launch_bounds__(PG_THREADS) gumbel_mean_kernel(int Lt, int V, 
                                                                  const float* __restrict__ text_mask,
                                                                  const int* __restrict__ idx, const float* __restrict__ yval,
                                                                  float* __restrict__ xmean) {
+  svpc_pdl_sync();
   const int n = blockIdx.x;
   float cnt = 0.f;
   for (int l = 0; l < Lt; ++l) cnt += (text_mask[(long long)n * Lt + l] == 1.0f) ? 1.f : 0.f;
@@ -452,6 +459,7 @@ __global__ void __launch_bounds__(PG_THREADS) gumbel_mean_kernel(int Lt, int V, 
 // tv[n][v] = Emb[v] . dxmean[n]: one warp per 8 vocabulary entries
 __global__ void __launch_bounds__(PG_THREADS) gumbel_tv_kernel(int V, int W, const float* __restrict__ emb,
                                                                const float* __restrict__ dxmean, float* __restrict__ tv) {
+  svpc_pdl_sync();
   extern __shared__ float dxm[];   // W
   const int n = blockIdx.y;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -480,6 +488,7 @@ __global__ void __launch_bounds__(PG_THREADS) gumbel_bwd_kernel(int Lt, int V, i
                                                                 const float* __restrict__ dxmean,
                                                                 const float* __restrict__ tv_all, float* __restrict__ dP,
                                                                 float* __restrict__ demb) {
+  svpc_pdl_sync();
   __shared__ float red[64];
   const int n = blockIdx.y, l = blockIdx.x, vx = clip_vx[n];
   const long long poff = clip_P_off[n];
@@ -548,10 +557,10 @@ extern "C" int svpc_gumbel_fwd(int n_clips, int Lt, int V, int W, const float* P
                                int* idx, float* yval, svpc_stream_t stream) {
   if (n_clips <= 0) return SVPC_OK;
   cudaStream_t st = (cudaStream_t)stream;
-  gumbel_fwd_kernel<<<dim3(Lt, n_clips), PG_THREADS, 0, st>>>(Lt, V, P, g, clip_P_off, clip_vx, tau, idx, yval);
+  svpc_launch(gumbel_fwd_kernel, dim3(Lt, n_clips), PG_THREADS, 0, st, Lt, V, P, g, clip_P_off, clip_vx, tau, idx, yval);
   int rc = svpc_check_launch("gumbel_fwd");
   if (rc) return rc;
-  gumbel_mean_kernel<<<n_clips, PG_THREADS, 0, st>>>(Lt, V, W, emb, text_mask, idx, yval, xmean);
+  svpc_launch(gumbel_mean_kernel, n_clips, PG_THREADS, 0, st, Lt, V, W, emb, text_mask, idx, yval, xmean);
   return svpc_check_launch("gumbel_mean");
 }
 
@@ -563,10 +572,10 @@ extern "C" int svpc_gumbel_bwd(int n_clips, int Lt, int V, int W, const float* P
   cudaMemsetAsync(demb, 0, sizeof(float) * (size_t)V * W, st);
   if (n_clips <= 0) return SVPC_OK;
   SVPC_REQUIRE(tv_ws != nullptr, "gumbel_bwd: tv_ws (n_clips * V floats) is required");
-  gumbel_tv_kernel<<<dim3(svpc_cdiv(V, 64), n_clips), PG_THREADS, sizeof(float) * (size_t)W, st>>>(V, W, emb, dxmean, tv_ws);
+  svpc_launch(gumbel_tv_kernel, dim3(svpc_cdiv(V, 64), n_clips), PG_THREADS, sizeof(float) * (size_t)W, st, V, W, emb, dxmean, tv_ws);
   int rc = svpc_check_launch("gumbel_tv");
   if (rc) return rc;
-  gumbel_bwd_kernel<<<dim3(Lt, n_clips), PG_THREADS, 0, st>>>(Lt, V, W, P, g, clip_P_off, clip_vx, tau, text_mask, idx, yval,
+  svpc_launch(gumbel_bwd_kernel, dim3(Lt, n_clips), PG_THREADS, 0, st, Lt, V, W, P, g, clip_P_off, clip_vx, tau, text_mask, idx, yval,
                                                              dxmean, tv_ws, dP, demb);
   return svpc_check_launch("gumbel_bwd");
 }

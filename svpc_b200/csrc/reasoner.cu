@@ -21,6 +21,7 @@ __global__ void __launch_bounds__(RS_THREADS) reasoner_fwd_kernel(int D, int max
                                                                   const float* __restrict__ w4s, float* __restrict__ ent,
                                                                   float* __restrict__ ebar_out, float* __restrict__ Es,
                                                                   float* __restrict__ a_saved) {
+  svpc_pdl_sync();
   extern __shared__ float sm[];
   float* E = sm;                       // (max_ni, D)
   float* kv = E + (size_t)max_ni * D;  // (D)
@@ -88,6 +89,7 @@ __global__ void __launch_bounds__(RS_THREADS) reasoner_bwd_kernel(
     const float* __restrict__ Es, const float* __restrict__ a_saved, const float* __restrict__ d_ent,
     const float* __restrict__ d_ebar, const float* __restrict__ d_Es, float* __restrict__ dE0, float* __restrict__ dw2v,
     float* __restrict__ dclog, float* __restrict__ dw4s) {
+  svpc_pdl_sync();
   extern __shared__ float sm[];
   float* dE = sm;                        // (max_ni, D) gradient w.r.t. the current entity matrix
   float* Ep = dE + (size_t)max_ni * D;   // (max_ni, D) entity matrix BEFORE this step
@@ -203,7 +205,7 @@ extern "C" int svpc_reasoner_fwd(int B, int D, int max_ni, const float* E0, cons
   const size_t smem = sizeof(float) * ((size_t)max_ni * D + D + 3 * (size_t)max_ni);
   SVPC_REQUIRE(smem <= 220 * 1024, "reasoner_fwd: %d ingredients x %d do not fit in shared memory", max_ni, D);
   cudaFuncSetAttribute(reasoner_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  reasoner_fwd_kernel<<<B, RS_THREADS, smem, (cudaStream_t)stream>>>(D, max_ni, E0, cu_ingr, cu_steps, clip_ent_off, w2v, clog,
+  svpc_launch(reasoner_fwd_kernel, B, RS_THREADS, smem, (cudaStream_t)stream, D, max_ni, E0, cu_ingr, cu_steps, clip_ent_off, w2v, clog,
                                                                     w4s, ent, ebar, Es, a_saved);
   return svpc_check_launch("reasoner_fwd");
 }
@@ -217,7 +219,7 @@ extern "C" int svpc_reasoner_bwd(int B, int D, int max_ni, const float* E0, cons
   const size_t smem = sizeof(float) * (2 * (size_t)max_ni * D + 3 * (size_t)D + 4 * (size_t)max_ni);
   SVPC_REQUIRE(smem <= 220 * 1024, "reasoner_bwd: %d ingredients x %d do not fit in shared memory", max_ni, D);
   cudaFuncSetAttribute(reasoner_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  reasoner_bwd_kernel<<<B, RS_THREADS, smem, (cudaStream_t)stream>>>(D, max_ni, E0, cu_ingr, cu_steps, clip_ent_off, w2v, clog,
+  svpc_launch(reasoner_bwd_kernel, B, RS_THREADS, smem, (cudaStream_t)stream, D, max_ni, E0, cu_ingr, cu_steps, clip_ent_off, w2v, clog,
                                                                     w4s, ent, ebar, Es, a_saved, d_ent, d_ebar, d_Es, dE0,
                                                                     dw2v, dclog, dw4s);
   return svpc_check_launch("reasoner_bwd");

@@ -16,6 +16,7 @@ static inline int rw_grid(long long rows) { return svpc_imin(rows, (long long)SV
 template <typename T>
 __global__ void act_bwd_kernel(int rows, int cols, const T* __restrict__ dy, const T* __restrict__ ref, int act,
                                T* __restrict__ dz, float* __restrict__ dbias, const SvpcDrop drop) {
+  svpc_pdl_sync();
   const bool dropping = drop.seed != nullptr && drop.p > 0.f;
   const uint32_t dkey = svpc_drop_key(drop);
   const float dinv = dropping ? 1.f / (1.f - drop.p) : 1.f;
@@ -57,7 +58,7 @@ extern "C" int svpc_act_bwd(int rows, int cols, const void* dy, const void* ref,
   if (cols % 8 == 0 && (((uintptr_t)dy | (uintptr_t)ref | (uintptr_t)dz) & 15) == 0)
     return act_bwd_vec_launch(rows, cols, dy, ref, dt, act, dz, dbias, drop, st);
   dim3 grid(svpc_cdiv(cols, 32), svpc_imin(svpc_cdiv(rows, 8), 64));
-  SVPC_DISPATCH(dt, T, (act_bwd_kernel<T><<<grid, dim3(32, 8), 0, st>>>(rows, cols, (const T*)dy, (const T*)ref, act,
+  SVPC_DISPATCH(dt, T, (svpc_launch(act_bwd_kernel<T>, grid, dim3(32, 8), 0, st, rows, cols, (const T*)dy, (const T*)ref, act,
                                                                       (T*)dz, dbias, drop)));
   return svpc_check_launch("act_bwd");
 }
@@ -70,6 +71,7 @@ extern "C" int svpc_colsum(int rows, int cols, const void* x, int dt, float* out
 template <typename T>
 __global__ void weighted_colsum_kernel(int rows, int cols, const T* __restrict__ x, const float* __restrict__ w,
                                        float* __restrict__ out) {
+  svpc_pdl_sync();
   const int c = blockIdx.x * 32 + threadIdx.x;
   __shared__ float red[8][33];
   float acc = 0.f;
@@ -87,7 +89,7 @@ __global__ void weighted_colsum_kernel(int rows, int cols, const T* __restrict__
 
 int svpc_weighted_colsum(int rows, int cols, const void* x, int dt, const float* w, float* out, cudaStream_t st) {
   dim3 grid(svpc_cdiv(cols, 32), svpc_imin(svpc_cdiv(rows, 8), 64));
-  SVPC_DISPATCH(dt, T, (weighted_colsum_kernel<T><<<grid, dim3(32, 8), 0, st>>>(rows, cols, (const T*)x, w, out)));
+  SVPC_DISPATCH(dt, T, (svpc_launch(weighted_colsum_kernel<T>, grid, dim3(32, 8), 0, st, rows, cols, (const T*)x, w, out)));
   return svpc_check_launch("weighted_colsum");
 }
 
@@ -127,6 +129,7 @@ __global__ void __launch_bounds__(256) ln_fwd_warp_kernel(int rows, const TI* __
                                                           const float* __restrict__ tt, const int* __restrict__ tt_ids,
                                                           TO* __restrict__ y, TI* __restrict__ pre,
                                                           float* __restrict__ mean, float* __restrict__ rstd) {
+  svpc_pdl_sync();
   constexpr int D = NCH * 256;
   const int lane = threadIdx.x & 31;
   const int nw = gridDim.x * 8;
@@ -183,6 +186,7 @@ __global__ void __launch_bounds__(256, 2) ln_bwd_warp_kernel(int rows, const TG*
                                                              const float* __restrict__ mean, const float* __restrict__ rstd,
                                                              const float* __restrict__ gamma, TP* __restrict__ dpre,
                                                              float* __restrict__ dgamma, float* __restrict__ dbeta) {
+  svpc_pdl_sync();
   constexpr int D = NCH * 256;
   __shared__ float part[8][D];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -246,6 +250,7 @@ template <typename T>
 __global__ void __launch_bounds__(256) act_bwd_vec_kernel(int rows, int cols, const T* __restrict__ dy,
                                                           const T* __restrict__ ref, int act, T* __restrict__ dz,
                                                           float* __restrict__ dbias, const SvpcDrop drop) {
+  svpc_pdl_sync();
   __shared__ float red[8][256];
   const bool dropping = drop.seed != nullptr && drop.p > 0.f;
   const uint32_t dkey = svpc_drop_key(drop);
@@ -300,7 +305,7 @@ static int act_bwd_vec_launch(int rows, int cols, const void* dy, const void* re
                               SvpcDrop drop, cudaStream_t st) {
   const int gx = svpc_cdiv(cols, 256);
   dim3 grid(gx, svpc_imin(svpc_cdiv(rows, 8), svpc_cdiv(SVPC_NUM_SMS * 4, gx)));
-  SVPC_DISPATCH(dt, T, (act_bwd_vec_kernel<T><<<grid, 256, 0, st>>>(rows, cols, (const T*)dy, (const T*)ref, act, (T*)dz, dbias, drop)));
+  SVPC_DISPATCH(dt, T, (svpc_launch(act_bwd_vec_kernel<T>, grid, 256, 0, st, rows, cols, (const T*)dy, (const T*)ref, act, (T*)dz, dbias, drop)));
   return svpc_check_launch("act_bwd");
 }
 
@@ -315,6 +320,7 @@ __global__ void __launch_bounds__(RW_THREADS) ln_fwd_kernel(int rows, int D, con
                                                             const float* __restrict__ tt, const int* __restrict__ tt_ids,
                                                             TO* __restrict__ y, TI* __restrict__ pre,
                                                             float* __restrict__ mean, float* __restrict__ rstd) {
+  svpc_pdl_sync();
   __shared__ float red[64];
   for (int r = blockIdx.x; r < rows; r += gridDim.x) {
     const long long base = (long long)r * D;
@@ -371,11 +377,11 @@ extern "C" int svpc_ln_fwd(int rows, int D, const void* x, const void* res, int 
   if (D == 768 && rw_al16(x) && rw_al16(res) && rw_al16(y) && rw_al16(pre) && rw_al16(gamma) && rw_al16(beta) && rw_al16(pe) &&
       rw_al16(tt)) {
     const int grid = svpc_imin(svpc_cdiv(rows, 8), SVPC_NUM_SMS * 8);
-    SVPC_DISPATCH(dt_in, TI, SVPC_DISPATCH(dt_out, TO, (ln_fwd_warp_kernel<TI, TO, 3><<<grid, 256, 0, st>>>(
+    SVPC_DISPATCH(dt_in, TI, SVPC_DISPATCH(dt_out, TO, (svpc_launch(ln_fwd_warp_kernel<TI, TO, 3>, grid, 256, 0, st, 
         rows, (const TI*)x, (const TI*)res, gamma, beta, eps, pe, pe_period, tt, tt_ids, (TO*)y, (TI*)pre, mean, rstd))));
     return svpc_check_launch("ln_fwd");
   }
-  SVPC_DISPATCH(dt_in, TI, SVPC_DISPATCH(dt_out, TO, (ln_fwd_kernel<TI, TO><<<rw_grid(rows), RW_THREADS, 0, st>>>(
+  SVPC_DISPATCH(dt_in, TI, SVPC_DISPATCH(dt_out, TO, (svpc_launch(ln_fwd_kernel<TI, TO>, rw_grid(rows), RW_THREADS, 0, st, 
       rows, D, (const TI*)x, (const TI*)res, gamma, beta, eps, pe, pe_period, tt, tt_ids, (TO*)y, (TI*)pre, mean, rstd))));
   return svpc_check_launch("ln_fwd");
 }
@@ -389,6 +395,7 @@ __global__ void __launch_bounds__(RW_THREADS) ln_bwd_kernel(int rows, int D, con
                                                             const float* __restrict__ rstd, const float* __restrict__ gamma,
                                                             TP* __restrict__ dpre, float* __restrict__ dgamma,
                                                             float* __restrict__ dbeta) {
+  svpc_pdl_sync();
   __shared__ float red[64];
   float ag[RW_MAXPT], ab[RW_MAXPT];
 #pragma unroll
@@ -437,12 +444,12 @@ extern "C" int svpc_ln_bwd(int rows, int D, const void* dy, int dt_dy, const voi
   SVPC_REQUIRE(D <= RW_THREADS * RW_MAXPT, "ln_bwd: D=%d too wide", D);
   if (D == 768 && rw_al16(dy) && rw_al16(pre) && rw_al16(dpre) && rw_al16(gamma)) {
     const int g2 = svpc_imin(svpc_cdiv(rows, 8), SVPC_NUM_SMS * 4);
-    SVPC_DISPATCH(dt_dy, TG, SVPC_DISPATCH(dt_pre, TP, (ln_bwd_warp_kernel<TG, TP, 3><<<g2, 256, 0, st>>>(
+    SVPC_DISPATCH(dt_dy, TG, SVPC_DISPATCH(dt_pre, TP, (svpc_launch(ln_bwd_warp_kernel<TG, TP, 3>, g2, 256, 0, st, 
         rows, (const TG*)dy, (const TP*)pre, mean, rstd, gamma, (TP*)dpre, dgamma, dbeta))));
     return svpc_check_launch("ln_bwd");
   }
   const int grid = svpc_imin(rows, SVPC_NUM_SMS * 4);
-  SVPC_DISPATCH(dt_dy, TG, SVPC_DISPATCH(dt_pre, TP, (ln_bwd_kernel<TG, TP><<<grid, RW_THREADS, 0, st>>>(
+  SVPC_DISPATCH(dt_dy, TG, SVPC_DISPATCH(dt_pre, TP, (svpc_launch(ln_bwd_kernel<TG, TP>, grid, RW_THREADS, 0, st, 
       rows, D, (const TG*)dy, (const TP*)pre, mean, rstd, gamma, (TP*)dpre, dgamma, dbeta))));
   return svpc_check_launch("ln_bwd");
 }
@@ -451,6 +458,7 @@ extern "C" int svpc_ln_bwd(int rows, int D, const void* dy, int dt_dy, const voi
 template <typename T>
 __global__ void index_colsum_kernel(int rows, int D, const T* __restrict__ dy, const int* __restrict__ ids, int nbins,
                                     float* __restrict__ out) {
+  svpc_pdl_sync();
   // blockDim.x threads over columns (grid.x strips), grid.y row slices; up to 8 bins kept in registers
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= D) return;
@@ -475,7 +483,7 @@ extern "C" int svpc_index_colsum(int rows, int D, const void* dy, int dt, const 
   cudaMemsetAsync(out, 0, sizeof(float) * nbins * D, st);
   if (rows <= 0) return SVPC_OK;
   dim3 grid(svpc_cdiv(D, 128), svpc_imin(rows, 256));
-  SVPC_DISPATCH(dt, T, (index_colsum_kernel<T><<<grid, 128, 0, st>>>(rows, D, (const T*)dy, ids, nbins, out)));
+  SVPC_DISPATCH(dt, T, (svpc_launch(index_colsum_kernel<T>, grid, 128, 0, st, rows, D, (const T*)dy, ids, nbins, out)));
   return svpc_check_launch("index_colsum");
 }
 
@@ -492,6 +500,7 @@ __global__ void __launch_bounds__(EM_THREADS) embed_ln_fwd_kernel(int rows, int 
                                                                   T* __restrict__ y, long long ldy,
                                                                   float* __restrict__ mean, float* __restrict__ rstd,
                                                                   const SvpcDrop drop) {
+  svpc_pdl_sync();
   __shared__ float red[64];
   const bool dropping = drop.seed != nullptr && drop.p > 0.f;
   const uint32_t dkey = svpc_drop_key(drop);
@@ -536,7 +545,7 @@ extern "C" int svpc_embed_ln_fwd(int rows, int W, const float* table, const int*
   SVPC_REQUIRE(ldy >= W, "embed_ln: ldy=%lld < W=%d", ldy, W);
   const SvpcDrop drop{drop_p > 0.f ? drop_seed : nullptr, drop_site, drop_p};
   cudaStream_t st = (cudaStream_t)stream;
-  SVPC_DISPATCH(dt, T, (embed_ln_fwd_kernel<T><<<rw_grid(rows), EM_THREADS, 0, st>>>(rows, W, table, ids, gamma, beta, eps,
+  SVPC_DISPATCH(dt, T, (svpc_launch(embed_ln_fwd_kernel<T>, rw_grid(rows), EM_THREADS, 0, st, rows, W, table, ids, gamma, beta, eps,
                                                                                     (T*)y, ldy, mean, rstd, drop)));
   return svpc_check_launch("embed_ln_fwd");
 }
@@ -550,6 +559,7 @@ __global__ void __launch_bounds__(EM_THREADS) embed_ln_bwd_kernel(int rows, int 
                                                                   const float* __restrict__ gamma, int padding_idx,
                                                                   float* __restrict__ dtable, float* __restrict__ dgamma,
                                                                   float* __restrict__ dbeta, const SvpcDrop drop) {
+  svpc_pdl_sync();
   __shared__ float red[64];
   const bool dropping = drop.seed != nullptr && drop.p > 0.f;
   const uint32_t dkey = svpc_drop_key(drop);
@@ -607,7 +617,7 @@ extern "C" int svpc_embed_ln_bwd(int rows, int W, int V, const void* dy, int dt,
   if (rows <= 0) return SVPC_OK;
   SVPC_REQUIRE(W <= EM_THREADS * EM_MAXPT, "embed_ln: W=%d too wide", W);
   const int grid = svpc_imin(rows, SVPC_NUM_SMS * 4);
-  SVPC_DISPATCH(dt, T, (embed_ln_bwd_kernel<T><<<grid, EM_THREADS, 0, st>>>(rows, W, (const T*)dy, table, ids, mean, rstd,
+  SVPC_DISPATCH(dt, T, (svpc_launch(embed_ln_bwd_kernel<T>, grid, EM_THREADS, 0, st, rows, W, (const T*)dy, table, ids, mean, rstd,
                                                                            gamma, padding_idx, dtable, dgamma, dbeta, drop)));
   return svpc_check_launch("embed_ln_bwd");
 }
@@ -624,6 +634,7 @@ __global__ void __launch_bounds__(RW_THREADS) video_ln_pack_kernel(int n_rows, i
                                                                    T* __restrict__ xhat, float* __restrict__ mean,
                                                                    float* __restrict__ rstd, const float* __restrict__ gamma,
                                                                    const float* __restrict__ beta, const SvpcDrop drop) {
+  svpc_pdl_sync();
   __shared__ float red[64];
   const int F4 = F >> 2;
   const bool dropping = drop.seed != nullptr && drop.p > 0.f;
@@ -687,7 +698,7 @@ extern "C" int svpc_video_ln_pack(int n_clips, int B, int L, int Lv, int F, cons
   SVPC_REQUIRE(F % 4 == 0 && F <= RW_THREADS * RW_MAXPT, "video_ln_pack: F=%d must be a multiple of 4 and <= 4096", F);
   cudaStream_t st = (cudaStream_t)stream;
   const int n_rows = n_clips * Lv;
-  SVPC_DISPATCH(dt, T, (video_ln_pack_kernel<T><<<svpc_imin(n_rows, SVPC_NUM_SMS * 16), RW_THREADS, 0, st>>>(
+  SVPC_DISPATCH(dt, T, (svpc_launch(video_ln_pack_kernel<T>, svpc_imin(n_rows, SVPC_NUM_SMS * 16), RW_THREADS, 0, st, 
       n_rows, B, L, Lv, F, feat_ptrs, clip_t, clip_b, eps, (T*)xhat, mean, rstd, gamma, beta, drop)));
   return svpc_check_launch("video_ln_pack");
 }
@@ -706,6 +717,7 @@ __global__ void __launch_bounds__(256) video_ln_affine_bwd_kernel(int n_rows, in
                                                                   const float* __restrict__ rstd,
                                                                   const T* __restrict__ dy, float* __restrict__ dgamma,
                                                                   float* __restrict__ dbeta, const SvpcDrop drop) {
+  svpc_pdl_sync();
   __shared__ float red[8][256];
   const bool dropping = drop.seed != nullptr && drop.p > 0.f;
   const uint32_t dkey = svpc_drop_key(drop);
@@ -764,7 +776,7 @@ extern "C" int svpc_video_ln_affine_bwd(int n_clips, int B, int L, int Lv, int F
   const int n_rows = n_clips * Lv;
   const int gx = svpc_cdiv(F, 256);
   dim3 grid(gx, svpc_imin(svpc_cdiv(n_rows, 8), svpc_cdiv(SVPC_NUM_SMS * 8, gx)));
-  SVPC_DISPATCH(dt, T, (video_ln_affine_bwd_kernel<T><<<grid, 256, 0, st>>>(
+  SVPC_DISPATCH(dt, T, (svpc_launch(video_ln_affine_bwd_kernel<T>, grid, 256, 0, st, 
       n_rows, B, L, Lv, F, feat_ptrs, clip_t, clip_b, mean, rstd, (const T*)dy, dgamma, dbeta, drop)));
   return svpc_check_launch("video_ln_affine_bwd");
 }
@@ -774,6 +786,7 @@ extern "C" int svpc_video_ln_affine_bwd(int n_clips, int B, int L, int Lv, int F
 // ------------------------------------------------------------------------------------------------
 __global__ void seg_scan_kernel(int B, int Li, const int* __restrict__ sep_mask, const int* __restrict__ cu_ingr,
                                 int* __restrict__ row_seg, int* __restrict__ seg_lohi) {
+  svpc_pdl_sync();
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= B) return;
   const int g0 = cu_ingr[b], ni = cu_ingr[b + 1] - g0;
@@ -795,6 +808,7 @@ template <typename T>
 __global__ void segmean_fwd_kernel(int B, int Li, int D, const T* __restrict__ x, const int* __restrict__ cu_ingr,
                                    const int* __restrict__ seg_lohi, const float* __restrict__ pe,
                                    float* __restrict__ E0) {
+  svpc_pdl_sync();
   const int g = blockIdx.x;
   // video of this ingredient
   int b = 0;
@@ -812,6 +826,7 @@ __global__ void segmean_fwd_kernel(int B, int Li, int D, const T* __restrict__ x
 template <typename T>
 __global__ void segmean_bwd_kernel(int rows, int D, const float* __restrict__ dE0, const int* __restrict__ row_seg,
                                    const int* __restrict__ seg_lohi, T* __restrict__ dx) {
+  svpc_pdl_sync();
   const int r = blockIdx.x;
   const int g = row_seg[r];
   float inv = 0.f;
@@ -825,10 +840,10 @@ extern "C" int svpc_segmean_fwd(int B, int Li, int D, int NI, const void* x, int
                                 int* scratch_seg_lohi, svpc_stream_t stream) {
   cudaStream_t st = (cudaStream_t)stream;
   if (B <= 0 || NI <= 0) return SVPC_OK;
-  seg_scan_kernel<<<svpc_cdiv(B, 64), 64, 0, st>>>(B, Li, sep_mask, cu_ingr, scratch_row_seg, scratch_seg_lohi);
+  svpc_launch(seg_scan_kernel, svpc_cdiv(B, 64), 64, 0, st, B, Li, sep_mask, cu_ingr, scratch_row_seg, scratch_seg_lohi);
   int rc = svpc_check_launch("seg_scan");
   if (rc) return rc;
-  SVPC_DISPATCH(dt, T, (segmean_fwd_kernel<T><<<NI, 256, 0, st>>>(B, Li, D, (const T*)x, cu_ingr, scratch_seg_lohi, pe, E0)));
+  SVPC_DISPATCH(dt, T, (svpc_launch(segmean_fwd_kernel<T>, NI, 256, 0, st, B, Li, D, (const T*)x, cu_ingr, scratch_seg_lohi, pe, E0)));
   return svpc_check_launch("segmean_fwd");
 }
 
@@ -836,14 +851,15 @@ extern "C" int svpc_segmean_bwd(int B, int Li, int D, int NI, const float* dE0, 
                                 void* dx, int dt, int* scratch_row_seg, int* scratch_seg_lohi, svpc_stream_t stream) {
   cudaStream_t st = (cudaStream_t)stream;
   if (B <= 0) return SVPC_OK;
-  seg_scan_kernel<<<svpc_cdiv(B, 64), 64, 0, st>>>(B, Li, sep_mask, cu_ingr, scratch_row_seg, scratch_seg_lohi);
+  svpc_launch(seg_scan_kernel, svpc_cdiv(B, 64), 64, 0, st, B, Li, sep_mask, cu_ingr, scratch_row_seg, scratch_seg_lohi);
   int rc = svpc_check_launch("seg_scan");
   if (rc) return rc;
-  SVPC_DISPATCH(dt, T, (segmean_bwd_kernel<T><<<B * Li, 256, 0, st>>>(B * Li, D, dE0, scratch_row_seg, scratch_seg_lohi, (T*)dx)));
+  SVPC_DISPATCH(dt, T, (svpc_launch(segmean_bwd_kernel<T>, B * Li, 256, 0, st, B * Li, D, dE0, scratch_row_seg, scratch_seg_lohi, (T*)dx)));
   return svpc_check_launch("segmean_bwd");
 }
 
 __global__ void ragged_mean_fwd_kernel(int D, const float* __restrict__ x, const int* __restrict__ cu, float* __restrict__ y) {
+  svpc_pdl_sync();
   const int b = blockIdx.x, lo = cu[b], hi = cu[b + 1];
   const float inv = 1.0f / (float)(hi - lo);
   for (int c = threadIdx.x; c < D; c += blockDim.x) {
@@ -853,6 +869,7 @@ __global__ void ragged_mean_fwd_kernel(int D, const float* __restrict__ x, const
   }
 }
 __global__ void ragged_mean_bwd_kernel(int D, const float* __restrict__ dy, const int* __restrict__ cu, float* __restrict__ dx) {
+  svpc_pdl_sync();
   const int b = blockIdx.x, lo = cu[b], hi = cu[b + 1];
   const float inv = 1.0f / (float)(hi - lo);
   for (int c = threadIdx.x; c < D; c += blockDim.x) {
@@ -862,17 +879,18 @@ __global__ void ragged_mean_bwd_kernel(int D, const float* __restrict__ dy, cons
 }
 extern "C" int svpc_ragged_mean_fwd(int B, int D, const float* x, const int* cu, float* y, svpc_stream_t stream) {
   if (B <= 0) return SVPC_OK;
-  ragged_mean_fwd_kernel<<<B, 256, 0, (cudaStream_t)stream>>>(D, x, cu, y);
+  svpc_launch(ragged_mean_fwd_kernel, B, 256, 0, (cudaStream_t)stream, D, x, cu, y);
   return svpc_check_launch("ragged_mean_fwd");
 }
 extern "C" int svpc_ragged_mean_bwd(int B, int D, const float* dy, const int* cu, float* dx, svpc_stream_t stream) {
   if (B <= 0) return SVPC_OK;
-  ragged_mean_bwd_kernel<<<B, 256, 0, (cudaStream_t)stream>>>(D, dy, cu, dx);
+  svpc_launch(ragged_mean_bwd_kernel, B, 256, 0, (cudaStream_t)stream, D, dy, cu, dx);
   return svpc_check_launch("ragged_mean_bwd");
 }
 
 // y = x / sum(x)  (model.py:798)
 __global__ void row_normalize_fwd_kernel(int cols, const float* __restrict__ x, float* __restrict__ y) {
+  svpc_pdl_sync();
   __shared__ float red[64];
   const long long base = (long long)blockIdx.x * cols;
   float s = 0.f;
@@ -883,6 +901,7 @@ __global__ void row_normalize_fwd_kernel(int cols, const float* __restrict__ x, 
 // dx = (dy - sum(dy * x) / s) / s
 __global__ void row_normalize_bwd_kernel(int cols, const float* __restrict__ dy, const float* __restrict__ x,
                                          float* __restrict__ dx) {
+  svpc_pdl_sync();
   __shared__ float red[64];
   const long long base = (long long)blockIdx.x * cols;
   float s = 0.f, t = 0.f;
@@ -892,11 +911,11 @@ __global__ void row_normalize_bwd_kernel(int cols, const float* __restrict__ dy,
 }
 extern "C" int svpc_row_normalize_fwd(int rows, int cols, const float* x, float* y, svpc_stream_t stream) {
   if (rows <= 0) return SVPC_OK;
-  row_normalize_fwd_kernel<<<rows, 128, 0, (cudaStream_t)stream>>>(cols, x, y);
+  svpc_launch(row_normalize_fwd_kernel, rows, 128, 0, (cudaStream_t)stream, cols, x, y);
   return svpc_check_launch("row_normalize_fwd");
 }
 extern "C" int svpc_row_normalize_bwd(int rows, int cols, const float* dy, const float* x, float* dx, svpc_stream_t stream) {
   if (rows <= 0) return SVPC_OK;
-  row_normalize_bwd_kernel<<<rows, 128, 0, (cudaStream_t)stream>>>(cols, dy, x, dx);
+  svpc_launch(row_normalize_bwd_kernel, rows, 128, 0, (cudaStream_t)stream, cols, dy, x, dx);
   return svpc_check_launch("row_normalize_bwd");
 }
