@@ -494,7 +494,13 @@ def main():
         }
         print(json.dumps(out))
     if world > 1:
-        dist.destroy_process_group()
+        # a captured graph holds NCCL kernels and autograd hooks: tearing the communicator down under it can block, so the
+        # ranks meet once more, flush, and leave without running destructors
+        dist.barrier()
+        torch.cuda.synchronize()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
 
 
 if __name__ == "__main__":

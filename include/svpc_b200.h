@@ -200,6 +200,30 @@ int svpc_bce_bwd(long long n, const float* p, const float* y, const float* g, fl
 int svpc_asl_fwd(int rows, int A, const float* p, const float* y, float* loss, svpc_stream_t stream);
 int svpc_asl_bwd(int rows, int A, const float* p, const float* y, const float* g, float* dp, svpc_stream_t stream);
 
+/* Training-iteration tail, multi-tensor over separately allocated fp32 tensors.  `grads`, `params`, `m`,
+ * `v`, `shadow` are DEVICE arrays of n_tensors DEVICE pointers; numel (n_tensors); a chunk table gives every CTA up to
+ * chunk_elems consecutive elements of one tensor: chunk_tensor / chunk_start (n_chunks), the chunks of tensor t being
+ * tensor_first[t] .. tensor_first[t+1]-1.
+ *   svpc_optim_sqnorm  chunk_sq[c] = sum of squares of chunk c of the gradients (fixed summation order)
+ *   svpc_optim_coef    coef[t] = c_global * c_param(t): c_global = min(1, global_max_norm / (||g|| + 1e-6)) is
+ *                      nn.utils.clip_grad_norm_ over all parameters (src/train.py:141-142), c_param = min(1, param_max_norm /
+ *                      (c_global ||g_t|| + 1e-6)) is BertAdam's per-parameter clip (optimization.py:307-308); a max <= 0
+ *                      disables that clip; norms[0] = ||g|| before clipping, norms[1] = c_global
+ *   svpc_optim_apply   flags bit0: BertAdam.step (optimization.py:310-328, no bias correction): g' = coef g,
+ *                      m = b1 m + (1-b1) g', v = b2 v + (1-b2) g'^2, p -= lr_t (m / (sqrt v + eps) + wd_t p);
+ *                      bit1: EMA (optimization.py:196-203) shadow = (1-d) p + d shadow with d = ema_decay[0],
+ *                      1-d = ema_decay[1] (device scalars, so a captured graph sees the per-step value);
+ *                      bit2: also write g' back (the reference clips p.grad in place).
+ *                      tensor_lr / tensor_wd (n_tensors): scheduled learning rate and weight decay of each tensor. */
+int svpc_optim_sqnorm(int n_chunks, const int* chunk_tensor, const long long* chunk_start, int chunk_elems,
+                      const void* const* grads, const long long* numel, float* chunk_sq, svpc_stream_t stream);
+int svpc_optim_coef(int n_tensors, const int* tensor_first, const float* chunk_sq, float global_max_norm,
+                    float param_max_norm, float* coef, float* norms, svpc_stream_t stream);
+int svpc_optim_apply(int n_chunks, const int* chunk_tensor, const long long* chunk_start, int chunk_elems,
+                     void* const* grads, void* const* params, void* const* m, void* const* v, void* const* shadow,
+                     const long long* numel, const float* coef, const float* tensor_lr, const float* tensor_wd,
+                     double b1, double b2, double eps, const float* ema_decay, int flags, svpc_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
