@@ -44,6 +44,7 @@ def parse():
     ap.add_argument("--cpu-sample-videos", type=int, default=4)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-optimizer", action="store_true", help="skip the fwd+bwd+optimizer iteration measurement")
     ap.add_argument("--no-kernel-timing", action="store_true")
     ap.add_argument("--task", default="train", choices=["train", "decode"],
                     help="train: fwd+bwd clips/s (headline); decode: greedy-decode captions/s (BASELINE.json configs[4])")
@@ -381,6 +382,33 @@ def main():
     clocks = sampler.stop() if rank == 0 else None
     value = world * n_clips * args.steps / (ms / 1e3)
 
+    # ---- whole training iteration: step + global clip + BertAdam + EMA as three more launches
+    iteration = None
+    if not args.no_optimizer:
+        from svpc_b200 import optim as SO
+        named = [(n, p) for n, p in model.named_parameters() if p.requires_grad]
+        nod = ["bias", "LayerNorm.bias", "LayerNorm.weight"]                      # train.py:339-343
+        groups = [{"params": [p for n, p in named if not any(x in n for x in nod)], "weight_decay": 0.01},
+                  {"params": [p for n, p in named if any(x in n for x in nod)], "weight_decay": 0.0}]
+        opt = SO.BertAdam(groups, lr=1e-4, warmup=0.1, t_total=100000, schedule="warmup_linear")   # train.py:353-357
+        ema = SO.EMA(0.9999)                                                      # train.py:344-348, 529
+        for n, p in named:
+            ema.register(n, p.data)
+        it = [0]
+
+        def full_iteration():
+            loss = run_resident()
+            opt.step(grad_clip=1.0, ema=ema, niter=it[0])                         # train.py:141-147
+            it[0] += 1
+            return loss
+        for _ in range(3):
+            full_iteration()
+        ms_it = timed(full_iteration, args.steps)
+        iteration = {"value": round(world * n_clips * args.steps / (ms_it / 1e3), 2), "unit": "clips/s",
+                     "ms_per_step": round(ms_it / args.steps, 3),
+                     "what": "fwd+bwd replay, then clip_grad_norm_(1.0) + BertAdam(lr 1e-4, warmup_linear) + EMA(0.9999) fused into 3 launches over 181 tensors"}
+        assert torch.isfinite(run_resident()).all()
+
     # ---- end-to-end timing: pinned host inputs -> H2D every step, loss read back
     e2e = None
     if not args.no_e2e:
@@ -395,18 +423,24 @@ def main():
                         d.copy_(s_)
             for d, s_ in zip(arena_noise, noise_host):
                 d.copy_(s_)
-            h2d_bytes = gstep.arena.nbytes
+            h2d_bytes = gstep.arena.h2d_nbytes     # the 25 never-read text rows of each (125, 3072) clip block are not uploaded
 
         def e2e_steps(k):
             """k steps, each with its own H2D of every input from pinned host memory and a D2H read of the loss.  With
             the graph, batch i+1 uploads on the copy stream while batch i computes (GraphedTrainStep.prefetch)."""
             if gstep is not None:
                 gstep.prefetch(arena_args, arena_noise)
+                pending, losses = None, []
                 for i in range(k):
-                    loss = gstep.run_prefetched()           # staged batch -> static buffers, graph replay (async)
+                    gstep.run_prefetched()                  # staged batch -> static buffers, graph replay (async)
+                    h = gstep.loss_to_host()                # async D2H of THIS step's loss into a pinned ring slot
                     if i + 1 < k:
                         gstep.prefetch(arena_args, arena_noise)
-                    float(loss)                             # .item(): D2H read of the step's result
+                    if pending is not None:
+                        losses.append(pending.get())        # host reads step i-1's loss while step i runs
+                    pending = h
+                losses.append(pending.get())
+                assert len(losses) == k and all(v == v for v in losses)
                 return
             for _ in range(k):
                 a = [to_dev(x) for x in host_args]
@@ -416,7 +450,7 @@ def main():
         ms_e2e = timed(lambda: e2e_steps(args.steps), 1)
         e2e = {"value": round(world * n_clips * args.steps / (ms_e2e / 1e3), 2), "unit": "clips/s",
                "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": 4, "ms_per_step": round(ms_e2e / args.steps, 3),
-               "pipeline": "every step uploads all of its inputs from pinned host memory; the upload of step i+1 runs on a copy stream under step i (first upload exposed)" if gstep is not None else "serial"}
+               "pipeline": "every step uploads all of its inputs from pinned host memory; the upload of step i+1 runs on a copy stream under step i (first upload exposed); each step's loss goes to pinned host memory and is read by the host one step later, so the device never idles on the host" if gstep is not None else "serial"}
 
     # ---- per-kernel CUDA-event timing (roofline of the dominant kernel)
     roofline, top = None, None
@@ -489,7 +523,7 @@ def main():
                        "l2": "inputs (295 MB of features per step) exceed the 126 MB L2",
                        "gflop_per_clip_as_written": GF_PER_CLIP_AS_WRITTEN[args.mode], "gflop_per_clip_needed": round(gf_need, 3),
                        "step_tflops_needed": round(gf_need * n_clips * world / (ms / args.steps), 2)},
-            "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
+            "e2e": e2e, "iteration_with_optimizer": iteration, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
             "top_kernels_ms_per_step": [[k, n, round(t, 4)] for t, n, k in (top or [])],
         }
         print(json.dumps(out))

@@ -224,6 +224,13 @@ int svpc_optim_apply(int n_chunks, const int* chunk_tensor, const long long* chu
                      const long long* numel, const float* coef, const float* tensor_lr, const float* tensor_wd,
                      double b1, double b2, double eps, const float* ema_decay, int flags, svpc_stream_t stream);
 
+/* Pitched asynchronous copy of `height` blocks of `width` bytes: the per-step input upload without the 25 text rows of
+ * every (125, 3072) clip tensor that the path never reads (model.py:889).  kind 1: `src` is PINNED HOST
+ * memory (the only host pointer in this ABI); kind 3: device to device.  Replaces the per-tensor `.cuda()` calls of
+ * src/train.py:91-112 (prepare_batch_inputs).  Not counted as a kernel launch. */
+int svpc_memcpy2d_async(void* dst, long long dpitch, const void* src, long long spitch, long long width, long long height,
+                        int kind, svpc_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,6 +1,6 @@
 #!/bin/bash
 mkdir -p gpurun_out
-CMD="python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-e2e --no-kernel-timing --no-graph"
+CMD="python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-e2e --no-kernel-timing --no-optimizer --no-graph"
 timeout 600 $CMD > gpurun_out/plain.log 2>&1 && \
 timeout 1500 ncu --metrics gpu__time_duration.sum --clock-control none -c 6000 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu.log 2>&1
 echo "ncu rc=$?"; wc -l gpurun_out/launches.csv

@@ -102,3 +102,25 @@ extern "C" int svpc_sum(long long n, const float* x, float* out, svpc_stream_t s
   svpc_launch(sum_kernel, 1, 1024, 0, (cudaStream_t)stream, n, x, out);
   return svpc_check_launch("sum");
 }
+
+// Host -> device input upload that skips rows the path never reads: the loader's clip tensors are
+// (B, 125, 3072) but only the first 100 rows of each clip hold video features (model.py:889 `[:, :max_v_len]`), so the
+// upload is a pitched copy of `height` blocks of `width` bytes.  `src` is PINNED HOST memory for kind 1 (the one host
+// pointer of this ABI), device memory for kind 3; nothing is synchronised.
+extern "C" int svpc_memcpy2d_async(void* dst, long long dpitch, const void* src, long long spitch, long long width,
+                                   long long height, int kind, svpc_stream_t stream) {
+  if (width <= 0 || height <= 0) return SVPC_OK;
+  if (kind != 1 && kind != 3) {
+    svpc_set_error("memcpy2d: kind must be 1 (pinned host -> device) or 3 (device -> device)");
+    return SVPC_ERR_ARG;
+  }
+  const cudaMemcpyKind k = kind == 1 ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice;
+  cudaError_t e = height == 1 ? cudaMemcpyAsync(dst, src, (size_t)width, k, (cudaStream_t)stream)
+                              : cudaMemcpy2DAsync(dst, (size_t)dpitch, src, (size_t)spitch, (size_t)width, (size_t)height, k,
+                                                  (cudaStream_t)stream);
+  if (e != cudaSuccess) {
+    svpc_set_error("memcpy2d: %s", cudaGetErrorString(e));
+    return SVPC_ERR_CUDA;
+  }
+  return SVPC_OK;
+}

@@ -112,6 +112,11 @@ class CudaBackend:
     def _c(t):
         return t if t.is_contiguous() else t.contiguous()
 
+    def memcpy2d_h2d(self, dst_ptr, dpitch, src_ptr, spitch, width, height):
+        """Pitched async copy from PINNED host memory to the device on the current stream (raw addresses)."""
+        self._call("svpc_memcpy2d_async", C.c_void_p(dst_ptr), _ll(dpitch), C.c_void_p(src_ptr), _ll(spitch), _ll(width),
+                   _ll(height), 1)
+
     def clear_weight_caches(self):
         self._w_cache.clear()
 

@@ -34,17 +34,52 @@ class InputArena:
 
     ALIGN = 256
 
-    def __init__(self, tensors, device):
+    def __init__(self, tensors, device, used_rows=None):
+        """``used_rows``: {index in ``tensors``: r} - of that (B, L, F) tensor only rows [0, r) of every (L, F) block are
+        read by the step (video features: the first max_v_len of 125 rows, model.py:889); the upload skips the rest."""
         self.device = device
-        self.spec, off = [], 0
-        for t in tensors:
+        self.spec, self.plan, self.nbytes = self.layout(tensors, used_rows)
+        self.h2d_nbytes = sum(w * h for _, _, w, h in self.plan)
+        self.host = torch.empty(self.nbytes, dtype=torch.uint8).pin_memory()
+        self.stage = torch.zeros(self.nbytes, dtype=torch.uint8, device=device)
+        self.static = torch.zeros(self.nbytes, dtype=torch.uint8, device=device)
+
+    @classmethod
+    def layout(cls, tensors, used_rows=None):
+        """(spec, upload plan, arena bytes) - pure host arithmetic."""
+        spec, off = [], 0
+        segs = []            # upload plan: (offset, pitch, width, height) in bytes; 1-D copies have height 1
+        for i, t in enumerate(tensors):
             n = t.numel() * t.element_size()
-            self.spec.append((off, tuple(t.shape), t.dtype))
-            off += (n + self.ALIGN - 1) // self.ALIGN * self.ALIGN
-        self.nbytes = off
-        self.host = torch.empty(off, dtype=torch.uint8).pin_memory()
-        self.stage = torch.empty(off, dtype=torch.uint8, device=device)
-        self.static = torch.empty(off, dtype=torch.uint8, device=device)
+            spec.append((off, tuple(t.shape), t.dtype))
+            r = (used_rows or {}).get(i)
+            if r is not None and t.dim() == 3 and r < t.shape[1]:
+                pitch = t.shape[1] * t.shape[2] * t.element_size()
+                segs.append([off, pitch, r * t.shape[2] * t.element_size(), t.shape[0]])
+            else:
+                segs.append([off, 0, n, 1])
+            off += (n + cls.ALIGN - 1) // cls.ALIGN * cls.ALIGN
+        # merge neighbours: consecutive 1-D pieces into one, consecutive pitched pieces with the same geometry into one
+        plan = []
+        for sg in segs:
+            if plan:
+                o, pitch, w, h = plan[-1]
+                if pitch == 0 and sg[1] == 0:
+                    plan[-1][2] = sg[0] + sg[2] - o
+                    continue
+                if pitch and sg[1] == pitch and sg[2] == w and sg[0] == o + pitch * h:
+                    plan[-1][3] += sg[3]
+                    continue
+            plan.append(list(sg))
+        return spec, [tuple(x) for x in plan], off
+
+    def upload(self):
+        """pinned host arena -> device staging arena on the CURRENT stream: one copy per plan entry (3 at the headline
+        configuration: ids/masks, the pitched feature block, labels/noise)."""
+        be = Fn.be()
+        hp, dp = self.host.data_ptr(), self.stage.data_ptr()
+        for o, pitch, w, h in self.plan:
+            be.memcpy2d_h2d(dp + o, pitch or w, hp + o, pitch or w, w, h)
 
     def _views(self, buf):
         out = []
@@ -98,7 +133,9 @@ class GraphedTrainStep:
         assert dev.type == "cuda", "GraphedTrainStep needs a CUDA model"
         self.device = dev
         flat, rebuild = _flatten(list(example_args), gumbel_noise)
-        self.arena = InputArena(flat, dev)
+        feats = {id(t) for t in example_args[1]} if _is_tensor_list(example_args[1]) else set()
+        Lv = model.config.max_v_len
+        self.arena = InputArena(flat, dev, used_rows={i: Lv for i, t in enumerate(flat) if id(t) in feats})
         sv = self.arena.static_views()
         for d, t in zip(sv, flat):
             d.copy_(t)
@@ -187,8 +224,8 @@ class GraphedTrainStep:
         self._pf = getattr(self, "_pf", None) or _Prefetcher(self.device)
         ha = getattr(self, "_host_args", None)
         if ha is not None and args is ha[0] and (gumbel_noise is None or gumbel_noise is ha[1]):
-            # the batch already sits in the pinned arena: one H2D, one D2D
-            self._pf.stage([(self.arena.static, self.arena.host)], bufs=[self.arena.stage])
+            # the batch already sits in the pinned arena: a few large H2D copies (dead feature rows skipped), one D2D
+            self._pf.stage_arena(self.arena)
             self._pf_dict = args[9]
             return
         pairs = []
@@ -202,6 +239,22 @@ class GraphedTrainStep:
         self._pf.stage(pairs)
         self._pf_dict = args[9]
 
+    def loss_to_host(self):
+        """Asynchronous D2H read of the step that was just enqueued: copies the loss into the next slot of a small pinned
+        ring and returns a handle whose ``get()`` waits for that copy only.  Lets a training loop enqueue step i+1 before
+        it looks at the loss of step i (the static loss buffer is overwritten by the next replay), so the device never
+        waits for the host between steps."""
+        ring = getattr(self, "_loss_ring", None)
+        if ring is None:
+            ring = self._loss_ring = {"buf": torch.zeros(4, dtype=torch.float32).pin_memory(), "i": 0,
+                                      "ev": [torch.cuda.Event() for _ in range(4)]}
+        i = ring["i"]
+        ring["i"] = (i + 1) % 4
+        slot, ev = ring["buf"][i:i + 1], ring["ev"][i]
+        slot.copy_(self.loss.detach().reshape(1), non_blocking=True)
+        ev.record(torch.cuda.current_stream(self.device))
+        return _HostScalar(slot, ev)
+
     def run_prefetched(self):
         self._pf.commit()
         d = self._pf_dict
@@ -210,6 +263,15 @@ class GraphedTrainStep:
                 raise ValueError("ingr_id_dict has a different number of copy tokens than the captured batch: re-capture")
             self.static[9] = d
         return self.run()
+
+
+class _HostScalar:
+    def __init__(self, slot, event):
+        self.slot, self.event = slot, event
+
+    def get(self) -> float:
+        self.event.synchronize()
+        return float(self.slot[0])
 
 
 class _Prefetcher:
@@ -242,6 +304,17 @@ class _Prefetcher:
                 staged.append((dst, b))
             self.staged.record(self.stream)
         self.pairs = staged
+
+    def stage_arena(self, arena):
+        cur = torch.cuda.current_stream(self.device)
+        if self.consumed is not None:
+            self.stream.wait_event(self.consumed)
+        else:
+            self.stream.wait_stream(cur)
+        with torch.cuda.stream(self.stream):
+            arena.upload()
+            self.staged.record(self.stream)
+        self.pairs = [(arena.static, arena.stage)]
 
     def commit(self):
         assert self.pairs is not None, "commit() without a staged batch"
@@ -334,6 +407,22 @@ class GraphedDecoder:
             pairs.append((self.static[i], torch.as_tensor(inputs[i])))
         self._pf.stage(pairs)
         self._pf_dict = inputs[7]
+
+    def loss_to_host(self):
+        """Asynchronous D2H read of the step that was just enqueued: copies the loss into the next slot of a small pinned
+        ring and returns a handle whose ``get()`` waits for that copy only.  Lets a training loop enqueue step i+1 before
+        it looks at the loss of step i (the static loss buffer is overwritten by the next replay), so the device never
+        waits for the host between steps."""
+        ring = getattr(self, "_loss_ring", None)
+        if ring is None:
+            ring = self._loss_ring = {"buf": torch.zeros(4, dtype=torch.float32).pin_memory(), "i": 0,
+                                      "ev": [torch.cuda.Event() for _ in range(4)]}
+        i = ring["i"]
+        ring["i"] = (i + 1) % 4
+        slot, ev = ring["buf"][i:i + 1], ring["ev"][i]
+        slot.copy_(self.loss.detach().reshape(1), non_blocking=True)
+        ev.record(torch.cuda.current_stream(self.device))
+        return _HostScalar(slot, ev)
 
     def run_prefetched(self):
         self._pf.commit()

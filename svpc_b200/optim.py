@@ -310,5 +310,8 @@ class BertAdam(Optimizer):
         be._call("svpc_optim_apply", tab.n_chunks, _p(tab.chunk_tensor), _p(tab.chunk_start), CHUNK, _p(gt), _p(pt), _p(mt),
                  _p(vt), _p(st_tab), _p(tab.numel), _p(tab.coef), _p(T["lr"]), _p(T["wd"]), C.c_double(g0["b1"]),
                  C.c_double(g0["b2"]), C.c_double(g0["e"]), _p(T["decay"]) if ema is not None else None, flags)
+        # the kernels wrote the parameters through raw pointers: bump the version counters so every cache keyed on them
+        # (functional.WeightCache's bf16 GEMM-layout copies) sees the update, exactly as after an in-place torch op
+        torch.autograd.graph.increment_version([p for p, g in zip(ps, grads) if g is not None])
         self._last_norm = tab.norms
         return loss

@@ -67,7 +67,12 @@ def test_fused_iteration_matches_reference_golden():
             close(st["next_m"], gold["m/" + n], n, 1e-12)
             close(st["next_v"], gold["v/" + n], n, 1e-20)
             assert st["step"] == int(gold["step/" + n])
+    # reference quirk kept: get_lr() answers [0] as soon as it meets a parameter without state (optimization.py:264-266)
+    assert opt.get_lr() == [0]
+    live = [p for p in opt.param_groups[1]["params"]]
+    opt.param_groups[0]["params"] = [p for p in opt.param_groups[0]["params"] if len(opt.state[p])]
     assert opt.get_lr()[0] == pytest.approx(OC.HYPER["lr"] * (1.0 / 3.0))     # warmup_linear at step 6 of 8, warm-up 0.25
+    assert len(opt.get_lr()) == len(live) + len(opt.param_groups[0]["params"])
 
 
 def test_separate_calls_match_oracle():
@@ -95,6 +100,16 @@ def test_separate_calls_match_oracle():
     for i, (n, p) in enumerate(zip(names, ps)):
         close(p.data, o.p[i].numpy(), n, 1e-8)
         close(ema.shadow[n], o.shadow[i].numpy(), n, 1e-8)
+
+
+def test_step_bumps_parameter_versions():
+    """The bf16 weight cache of the model is keyed on the parameters' version counters: a fused step must advance them."""
+    names, ps, opt, _ = build(with_ema=False)
+    set_grads(names, ps, 0)
+    before = [p._version for p in ps]
+    opt.step(grad_clip=1.0)
+    for n, p, b in zip(names, ps, before):
+        assert (p._version > b) == (n not in OC.NO_GRAD), n
 
 
 def test_no_clip_no_ema_and_zero_lr_properties():
