@@ -185,6 +185,15 @@ int svpc_lstm_step_fwd(int B, int D, int Nc, int Smax, int j, const float* xg, c
 int svpc_lstm_step_bwd(int B, int D, int Nc, int Smax, int j, const float* whh_t, const int* rows, const float* cs,
                        const float* gates, const float* dout, float* dgates, float* dc, svpc_stream_t stream);
 int svpc_transpose_f32(int R, int C, const float* in, float* out, svpc_stream_t stream);
+/* The same recurrence as ONE persistent launch per sweep (all Smax steps): one CTA per SM, half of them per direction,
+ * each keeping the W_hh rows of its 10-11 hidden units resident in shared memory; the steps are separated by a barrier
+ * among the CTAs of a direction on `sync` (>= 3 uint32, zeroed by the caller; sync[2] is set if a barrier timed out).
+ * Arguments as the per-step functions.  Requires ceil(D / (SMs / 2)) <= 12 and (48 + 16) D floats of shared memory. */
+int svpc_lstm_seq_fwd(int B, int D, int Nc, int Smax, const float* xg, const float* whh, const int* rows, float* hs,
+                      float* cs, float* gates, float* out, float* hprev, unsigned int* sync, svpc_stream_t stream);
+int svpc_lstm_seq_bwd(int B, int D, int Nc, int Smax, const float* whh_t, const int* rows, const float* cs,
+                      const float* gates, const float* dout, float* dgates, float* dc, unsigned int* sync,
+                      svpc_stream_t stream);
 
 /* Greedy decoding step (src/translator.py:106-112): per clip argmax of the current position's scores with column `unk`
  * forced to -1e10; ext_out[r, pos] = argmax (extended id), next_in[r] = argmax, or unk when it is a copied OOV id

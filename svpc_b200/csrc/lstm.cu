@@ -214,6 +214,260 @@ extern "C" int svpc_lstm_step_bwd(int B, int D, int Nc, int Smax, int j, const f
   return lstm_launch(true, p, (cudaStream_t)stream);
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// Persistent recurrence: ONE launch for all Smax steps.  The grid is one CTA per SM, half of the CTAs per direction;
+// CTA c of a direction owns hidden units [c D / CPD, (c+1) D / CPD) (10-11 units at D = 768 on 148 SMs) and keeps their
+// slice of W_hh (forward: 4 gate rows per unit; backward: one row of W_hh^T per unit; 135 KB fp32) resident in shared
+// memory for the whole sweep, so a step costs one barrier among the CTAs of a direction + the h (or gate-gradient) rows of
+// the videos from L2, instead of a kernel launch and 9.4 MB of weights per direction.  The barrier is a monotonic
+// counter per direction in global memory (`sync`, zeroed by the caller); all CTAs are co-resident (grid <= #SMs, 1 CTA/SM).
+#define LSTM_PW 12          // warps per CTA = most hidden units a CTA can own
+
+struct LstmSeqParams {
+  LstmStepParams s;
+  unsigned int* sync;    // [2] arrival counters, one per direction (zeroed by the caller); [2] = error flag
+  int cpd;               // CTAs per direction
+};
+
+__device__ __forceinline__ unsigned int ld_acquire_u32(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void red_release_add(unsigned int* p, unsigned int v) {
+  asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+// wait until `target` arrivals were counted (bounded: a lost arrival must not hang the GPU - it raises the error flag)
+__device__ __forceinline__ void dir_barrier_wait(unsigned int* cnt, unsigned int target, unsigned int* err) {
+  if (threadIdx.x == 0) {
+    unsigned int spins = 0;
+    while (ld_acquire_u32(cnt) < target) {
+      __nanosleep(32);
+      if (++spins > (1u << 23)) {
+        atomicExch(err, 1u);
+        break;
+      }
+    }
+  }
+  __syncthreads();
+}
+__device__ __forceinline__ void dir_barrier_arrive(unsigned int* cnt) {
+  __syncthreads();                                       // every thread's global writes of this step are issued
+  if (threadIdx.x == 0) {
+    __threadfence();
+    red_release_add(cnt, 1u);
+  }
+}
+
+__global__ void __launch_bounds__(LSTM_PW * 32, 1) lstm_seq_fwd_kernel(const LstmSeqParams q) {
+  svpc_pdl_sync();
+  const LstmStepParams& p = q.s;
+  extern __shared__ __align__(16) float smem[];
+  const int D = p.D;
+  const int dir = blockIdx.x / q.cpd, c = blockIdx.x - dir * q.cpd;
+  const int u0 = (int)((long long)c * D / q.cpd), u1 = (int)((long long)(c + 1) * D / q.cpd);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float* wsm = smem;                                     // [LSTM_PW][4][D]
+  float* hsm = smem + (size_t)LSTM_PW * 4 * D;           // [LSTM_BV][D]
+  // resident weights: gate rows g*D + d of W_hh[dir] for the owned units
+  for (int e = threadIdx.x * 4; e < (u1 - u0) * 4 * D; e += blockDim.x * 4) {
+    const int u = e / (4 * D), r = e - u * 4 * D, g = r / D, k = r - g * D;
+    *reinterpret_cast<float4*>(wsm + e) =
+        __ldg(reinterpret_cast<const float4*>(p.whh + ((long long)dir * 4 * D + (long long)g * D + u0 + u) * D + k));
+  }
+  const float* hs = p.hs + (long long)dir * p.Nc * D;
+  float* cs = p.cs + (long long)dir * p.Nc * D;
+  unsigned int* cnt = q.sync + dir;
+  const int d = u0 + warp;
+  const bool own = warp < u1 - u0;
+  for (int j = 0; j < p.Smax; ++j) {
+    const int* rows_j = p.rows + ((long long)dir * p.Smax + j) * p.B;
+    const int* rows_p = rows_j - p.B;
+    if (j > 0) dir_barrier_wait(cnt, (unsigned int)(q.cpd * j), q.sync + 2);     // h of step j-1 is complete
+    else __syncthreads();                                                        // weights staged
+    for (int b0 = 0; b0 < p.B; b0 += LSTM_BV) {
+      if (j > 0) {
+        __syncthreads();
+        for (int e = threadIdx.x * 4; e < LSTM_BV * D; e += blockDim.x * 4) {
+          const int b = e / D, k = e - b * D;
+          int rp = -1;
+          if (b0 + b < p.B && rows_j[b0 + b] >= 0) rp = rows_p[b0 + b];
+          float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (rp >= 0) v = __ldcg(reinterpret_cast<const float4*>(hs + (long long)rp * D + k));   // written by other SMs
+          *reinterpret_cast<float4*>(hsm + e) = v;
+        }
+        __syncthreads();
+      }
+      if (!own) continue;
+      float acc[LSTM_BV * 4];
+#pragma unroll
+      for (int i = 0; i < LSTM_BV * 4; ++i) acc[i] = 0.f;
+      if (j > 0) {
+        const float* w = wsm + (size_t)warp * 4 * D;
+        for (int k = lane * 4; k < D; k += 128) {
+          float4 wv[4];
+#pragma unroll
+          for (int g = 0; g < 4; ++g) wv[g] = *reinterpret_cast<const float4*>(w + g * D + k);
+#pragma unroll
+          for (int b = 0; b < LSTM_BV; ++b) {
+            const float4 h = *reinterpret_cast<const float4*>(hsm + b * D + k);
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {
+              float a = acc[b * 4 + g];
+              a = fmaf(h.x, wv[g].x, a); a = fmaf(h.y, wv[g].y, a); a = fmaf(h.z, wv[g].z, a); a = fmaf(h.w, wv[g].w, a);
+              acc[b * 4 + g] = a;
+            }
+          }
+        }
+        warp_reduce_transpose<LSTM_BV * 4>(acc, lane);
+      }
+      const float o0 = __shfl_xor_sync(0xffffffffu, acc[0], 1), o1 = __shfl_xor_sync(0xffffffffu, acc[1], 1);
+      const int b = b0 + (lane >> 1);
+      if ((lane & 1) || b >= p.B) continue;
+      const int r = rows_j[b];
+      if (r < 0) continue;
+      const int rp = j > 0 ? rows_p[b] : -1;
+      const float* x = p.xg + ((long long)dir * p.Nc + r) * 4 * D;
+      const float gi = svpc_sigmoid(x[d] + acc[0]);
+      const float gf = svpc_sigmoid(x[D + d] + acc[1]);
+      const float gg = tanhf(x[2 * D + d] + o0);
+      const float go = svpc_sigmoid(x[3 * D + d] + o1);
+      const float cp = rp >= 0 ? cs[(long long)rp * D + d] : 0.f;     // written by this very thread one step earlier
+      const float cn = gf * cp + gi * gg;
+      const float hn = go * tanhf(cn);
+      cs[(long long)r * D + d] = cn;
+      p.hs[((long long)dir * p.Nc + r) * D + d] = hn;
+      p.hprev[((long long)dir * p.Nc + r) * D + d] = rp >= 0 ? hsm[(lane >> 1) * D + d] : 0.f;
+      float* g = p.gates + ((long long)dir * p.Nc + r) * 4 * D;
+      g[d] = gi; g[D + d] = gf; g[2 * D + d] = gg; g[3 * D + d] = go;
+      atomicAdd(p.out + (long long)r * D + d, hn);
+    }
+    if (j + 1 < p.Smax) dir_barrier_arrive(cnt);
+  }
+}
+
+__global__ void __launch_bounds__(LSTM_PW * 32, 1) lstm_seq_bwd_kernel(const LstmSeqParams q) {
+  svpc_pdl_sync();
+  const LstmStepParams& p = q.s;
+  extern __shared__ __align__(16) float smem[];
+  const int D = p.D;
+  const int dir = blockIdx.x / q.cpd, c = blockIdx.x - dir * q.cpd;
+  const int u0 = (int)((long long)c * D / q.cpd), u1 = (int)((long long)(c + 1) * D / q.cpd);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float* wsm = smem;                                     // [LSTM_PW][4D]  rows u0.. of W_hh^T[dir]
+  float* gsm = smem + (size_t)LSTM_PW * 4 * D;           // [LSTM_BV][D]
+  for (int e = threadIdx.x * 4; e < (u1 - u0) * 4 * D; e += blockDim.x * 4)
+    *reinterpret_cast<float4*>(wsm + e) =
+        __ldg(reinterpret_cast<const float4*>(p.whh + ((long long)dir * D + u0) * 4 * D + e));
+  const float* dg = p.dgates + (long long)dir * p.Nc * 4 * D;
+  const float* cs = p.cs + (long long)dir * p.Nc * D;
+  unsigned int* cnt = q.sync + dir;
+  const int d = u0 + warp;
+  const bool own = warp < u1 - u0;
+  for (int j = p.Smax - 1, it = 0; j >= 0; --j, ++it) {
+    const int* rows_j = p.rows + ((long long)dir * p.Smax + j) * p.B;
+    const int* rows_n = rows_j + p.B;
+    const bool has_next = j + 1 < p.Smax;
+    if (it > 0) dir_barrier_wait(cnt, (unsigned int)(q.cpd * it), q.sync + 2);   // gate gradients of step j+1 complete
+    else __syncthreads();
+    for (int b0 = 0; b0 < p.B; b0 += LSTM_BV) {
+      float acc[LSTM_BV];
+#pragma unroll
+      for (int i = 0; i < LSTM_BV; ++i) acc[i] = 0.f;
+      if (has_next) {
+        for (int ch = 0; ch < 4; ++ch) {
+          __syncthreads();
+          for (int e = threadIdx.x * 4; e < LSTM_BV * D; e += blockDim.x * 4) {
+            const int b = e / D, k = e - b * D;
+            const int rn = (b0 + b < p.B) ? rows_n[b0 + b] : -1;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (rn >= 0) v = __ldcg(reinterpret_cast<const float4*>(dg + (long long)rn * 4 * D + ch * D + k));
+            *reinterpret_cast<float4*>(gsm + e) = v;
+          }
+          __syncthreads();
+          if (own) {
+            const float* wt = wsm + (size_t)warp * 4 * D + ch * D;
+            for (int k = lane * 4; k < D; k += 128) {
+              const float4 wv = *reinterpret_cast<const float4*>(wt + k);
+#pragma unroll
+              for (int b = 0; b < LSTM_BV; ++b) {
+                const float4 g = *reinterpret_cast<const float4*>(gsm + b * D + k);
+                float a = acc[b];
+                a = fmaf(g.x, wv.x, a); a = fmaf(g.y, wv.y, a); a = fmaf(g.z, wv.z, a); a = fmaf(g.w, wv.w, a);
+                acc[b] = a;
+              }
+            }
+          }
+        }
+        warp_reduce_transpose<LSTM_BV>(acc, lane);
+        acc[0] += __shfl_xor_sync(0xffffffffu, acc[0], 1);
+      }
+      const int b = b0 + (lane >> 1);
+      if (!own || (lane & 1) || b >= p.B) continue;
+      const int r = rows_j[b];
+      if (r < 0) continue;
+      const int rp = j > 0 ? rows_j[b - p.B] : -1;
+      const float* g = p.gates + ((long long)dir * p.Nc + r) * 4 * D;
+      const float gi = g[d], gf = g[D + d], gg = g[2 * D + d], go = g[3 * D + d];
+      const float tc = tanhf(cs[(long long)r * D + d]);
+      const float cp = rp >= 0 ? cs[(long long)rp * D + d] : 0.f;
+      const float dh = p.dout[(long long)r * D + d] + acc[0];
+      float* dcp = p.dc + ((long long)dir * p.B + b) * D + d;           // owned by this thread for the whole sweep
+      const float dct = *dcp + dh * go * (1.f - tc * tc);
+      *dcp = dct * gf;
+      float* da = p.dgates + ((long long)dir * p.Nc + r) * 4 * D;
+      da[d] = dct * gg * gi * (1.f - gi);
+      da[D + d] = dct * cp * gf * (1.f - gf);
+      da[2 * D + d] = dct * gi * (1.f - gg * gg);
+      da[3 * D + d] = dh * tc * go * (1.f - go);
+    }
+    if (j > 0) dir_barrier_arrive(cnt);
+  }
+}
+
+static int lstm_seq_launch(bool bwd, LstmSeqParams& q, cudaStream_t st) {
+  const LstmStepParams& p = q.s;
+  SVPC_REQUIRE(p.D % 4 == 0, "lstm_seq: hidden size %d must be a multiple of 4", p.D);
+  SVPC_REQUIRE(q.sync != nullptr, "lstm_seq: needs the zeroed barrier counters");
+  if (p.B <= 0 || p.Nc <= 0 || p.Smax <= 0) return SVPC_OK;
+  static int sms = 0;
+  if (!sms) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  }
+  q.cpd = sms / 2;
+  SVPC_REQUIRE(q.cpd >= 1 && (p.D + q.cpd - 1) / q.cpd <= LSTM_PW,
+               "lstm_seq: %d hidden units over %d CTAs per direction exceed %d units per CTA", p.D, q.cpd, LSTM_PW);
+  const size_t smem = ((size_t)LSTM_PW * 4 * p.D + (size_t)LSTM_BV * p.D) * sizeof(float);
+  SVPC_REQUIRE(smem <= 227 * 1024, "lstm_seq: hidden size %d needs %zu bytes of shared memory", p.D, smem);
+  static bool attr = false;
+  if (!attr) {
+    cudaFuncSetAttribute(lstm_seq_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaFuncSetAttribute(lstm_seq_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    attr = true;
+  }
+  if (bwd) svpc_launch(lstm_seq_bwd_kernel, 2 * q.cpd, LSTM_PW * 32, smem, st, q);
+  else svpc_launch(lstm_seq_fwd_kernel, 2 * q.cpd, LSTM_PW * 32, smem, st, q);
+  return svpc_check_launch(bwd ? "lstm_seq_bwd" : "lstm_seq_fwd");
+}
+
+extern "C" int svpc_lstm_seq_fwd(int B, int D, int Nc, int Smax, const float* xg, const float* whh, const int* rows, float* hs,
+                                 float* cs, float* gates, float* out, float* hprev, unsigned int* sync,
+                                 svpc_stream_t stream) {
+  LstmSeqParams q{{B, D, Nc, Smax, 0, xg, whh, rows, hs, cs, gates, out, hprev, nullptr, nullptr, nullptr}, sync, 0};
+  return lstm_seq_launch(false, q, (cudaStream_t)stream);
+}
+
+extern "C" int svpc_lstm_seq_bwd(int B, int D, int Nc, int Smax, const float* whh_t, const int* rows, const float* cs,
+                                 const float* gates, const float* dout, float* dgates, float* dc, unsigned int* sync,
+                                 svpc_stream_t stream) {
+  LstmSeqParams q{{B, D, Nc, Smax, 0, nullptr, whh_t, rows, nullptr, const_cast<float*>(cs), const_cast<float*>(gates),
+                   nullptr, nullptr, dout, dgates, dc},
+                  sync, 0};
+  return lstm_seq_launch(true, q, (cudaStream_t)stream);
+}
+
 // out[c, r] = in[r, c]  (fp32; W_hh^T for the reverse sweep, once per backward)
 __global__ void transpose_f32_kernel(int R, int Cc, const float* __restrict__ in, float* __restrict__ out) {
   svpc_pdl_sync();

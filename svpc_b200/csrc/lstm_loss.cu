@@ -74,23 +74,57 @@ __global__ void asl_rows_kernel(int rows, int A, const float* __restrict__ y, in
   if (threadIdx.x == 0) active[r] = any;
 }
 
-__global__ void asl_fwd_kernel(int rows, int A, const float* __restrict__ p, const float* __restrict__ y,
-                               float* __restrict__ loss) {
+// gamma is 1 on positives and 4 on negatives for 0/1 targets (the only targets the path produces); other y take powf
+__device__ __forceinline__ float asl_elem_fwd(float p, float y) {
+  if (y != 0.f && y != 1.f) return asl_elem(p, y, nullptr);
+  const float xs = fminf(1.f - p + ASL_CLIP, 1.f);
+  if (y == 1.f) return -(logf(fmaxf(p, ASL_EPS)) * (1.f - p));
+  const float b = 1.f - xs, b2 = b * b;
+  return -(logf(fmaxf(xs, ASL_EPS)) * (b2 * b2));
+}
+
+// One thread-block cluster of ASL_CTAS CTAs: rows are dealt round-robin to the cluster's warps, every CTA reduces its share,
+// CTA 0 adds the partial sums through distributed shared memory in rank order (deterministic, no scratch buffer, one launch).
+#define ASL_CTAS 8
+#define ASL_THREADS 512
+__global__ void __cluster_dims__(ASL_CTAS, 1, 1) __launch_bounds__(ASL_THREADS)
+    asl_fwd_kernel(int rows, int A, const float* __restrict__ p, const float* __restrict__ y, float* __restrict__ loss) {
   svpc_pdl_sync();
   __shared__ float red[64];
-  __shared__ int any_s[32];
+  __shared__ float part;
+  uint32_t rank;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
   float acc = 0.f;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
-  for (int r = warp; r < rows; r += nw) {
+  const int lane = threadIdx.x & 31, nw = ASL_THREADS >> 5;
+  const int gw = rank * nw + (threadIdx.x >> 5);
+  for (int r = gw; r < rows; r += nw * ASL_CTAS) {
+    const float* yr = y + (long long)r * A;
+    const float* pr = p + (long long)r * A;
+    float rowacc = 0.f;
     int a = 0;
-    for (int c = lane; c < A; c += 32) a |= (y[(long long)r * A + c] == 1.0f);
-    a = __any_sync(0xffffffffu, a);
-    if (!a) continue;
-    for (int c = lane; c < A; c += 32) acc += asl_elem(p[(long long)r * A + c], y[(long long)r * A + c], nullptr);
+    for (int c = lane; c < A; c += 32) {
+      const float yv = yr[c];
+      a |= (yv == 1.0f);
+      rowacc += asl_elem_fwd(pr[c], yv);
+    }
+    if (__any_sync(0xffffffffu, a)) acc += rowacc;       // rows without a positive are dropped (model.py:1103-1104)
   }
-  (void)any_s;
   acc = block_sum(acc, red);
-  if (threadIdx.x == 0) *loss = acc;
+  if (threadIdx.x == 0) part = acc;
+  asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+  if (rank == 0 && threadIdx.x == 0) {
+    float tot = 0.f;
+    const uint32_t local = (uint32_t)__cvta_generic_to_shared(&part);
+    for (uint32_t k = 0; k < ASL_CTAS; ++k) {
+      uint32_t remote;
+      float v;
+      asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local), "r"(k));
+      asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(remote) : "memory");
+      tot += v;
+    }
+    *loss = tot;
+  }
+  asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 
 __global__ void asl_bwd_kernel(int rows, int A, const float* __restrict__ p, const float* __restrict__ y,
@@ -113,7 +147,7 @@ __global__ void asl_bwd_kernel(int rows, int A, const float* __restrict__ p, con
 }
 
 extern "C" int svpc_asl_fwd(int rows, int A, const float* p, const float* y, float* loss, svpc_stream_t stream) {
-  svpc_launch(asl_fwd_kernel, 1, 1024, 0, (cudaStream_t)stream, rows, A, p, y, loss);
+  svpc_launch(asl_fwd_kernel, ASL_CTAS, ASL_THREADS, 0, (cudaStream_t)stream, rows, A, p, y, loss);
   return svpc_check_launch("asl_fwd");
 }
 extern "C" int svpc_asl_bwd(int rows, int A, const float* p, const float* y, const float* g, float* dp, svpc_stream_t stream) {

@@ -5,6 +5,7 @@ a missing library or a non-CUDA tensor raises.
 """
 from __future__ import annotations
 
+import collections
 import ctypes as C
 import os
 
@@ -74,6 +75,9 @@ class CudaBackend:
         self._ptr_cache = {}
         self._w_cache = {}
         self.timing = None
+        # BiLSTM recurrence: one persistent launch per sweep (default) or one launch per time step (SVPC_LSTM_STEPS=1)
+        self.lstm_persistent = os.environ.get("SVPC_LSTM_STEPS", "0") != "1"
+        self.lstm_sync_flags = collections.deque(maxlen=8)       # barrier counters of recent sweeps ([2] = time-out flag)
 
     # ------------------------------------------------------------------ plumbing
     def _call(self, fn, *args, tag=None):
@@ -589,7 +593,20 @@ class CudaBackend:
         self._w_cache[key] = (ver, out)
         return out
 
-    def bilstm_fwd(self, x, cu_steps, steps, params):
+    def _lstm_wih_cd(self, params, suf, cd):
+        """W_ih of one direction in the compute dtype (row pitch padded for TMA), re-cast when the optimiser touched it."""
+        w = params["weight_ih_l0" + suf]
+        if cd == torch.float32:
+            return w
+        key = ("wih", suf, cd, w.data_ptr())
+        hit = self._w_cache.get(key)
+        if hit is not None and hit[0] == w._version:
+            return hit[1]
+        out = self.cast(self._c(w), cd)
+        self._w_cache[key] = (w._version, out)
+        return out
+
+    def bilstm_fwd(self, x, cu_steps, steps, params, cd=torch.float32):
         """x (Nc, W) fp32 -> (Nc, D): both directions of nn.LSTM over every video's clips, summed (model.py:1022-1024).
         The input projection of all clips is one GEMM per direction; the recurrence is Smax fused step kernels
         (both directions, all videos, recurrent product + cell in one launch)."""
@@ -602,21 +619,29 @@ class CudaBackend:
         rows = self._lstm_row_table(steps, dev)
         f32 = torch.float32
         xg = torch.empty(2, Nc, 4 * D, dtype=f32, device=dev)
+        xc = self.cast(x, cd)         # bf16 path: the four batched products of the LSTM run on the tensor cores
         for di, suf in enumerate(("", "_reverse")):
             bias = params["bias_ih_l0" + suf] + params["bias_hh_l0" + suf]
-            self.gemm(x, params["weight_ih_l0" + suf], f32, bias, out=xg[di])
+            self.gemm(xc, self._lstm_wih_cd(params, suf, cd), f32, bias, out=xg[di])
         whh = self._lstm_whh(params, False)
         out = torch.zeros(Nc, D, dtype=f32, device=dev)
         hs = torch.empty(2, Nc, D, dtype=f32, device=dev)
         cs = torch.empty(2, Nc, D, dtype=f32, device=dev)
         hprev = torch.empty(2, Nc, D, dtype=f32, device=dev)
         gates = torch.empty(2, Nc, 4 * D, dtype=f32, device=dev)
-        for j in range(Smax):
-            self._call("svpc_lstm_step_fwd", B, D, Nc, Smax, j, _ptr(xg), _ptr(whh), _ptr(rows), _ptr(hs), _ptr(cs),
-                       _ptr(gates), _ptr(out), _ptr(hprev))
+        if self.lstm_persistent:
+            # one launch for the whole sweep: W_hh slices resident in shared memory, per-direction grid barrier per step
+            sync = torch.zeros(4, dtype=torch.int32, device=dev)
+            self._call("svpc_lstm_seq_fwd", B, D, Nc, Smax, _ptr(xg), _ptr(whh), _ptr(rows), _ptr(hs), _ptr(cs),
+                       _ptr(gates), _ptr(out), _ptr(hprev), _ptr(sync))
+            self.lstm_sync_flags.append(sync)
+        else:
+            for j in range(Smax):
+                self._call("svpc_lstm_step_fwd", B, D, Nc, Smax, j, _ptr(xg), _ptr(whh), _ptr(rows), _ptr(hs), _ptr(cs),
+                           _ptr(gates), _ptr(out), _ptr(hprev))
         return out, (rows, cs, gates, hprev)
 
-    def bilstm_bwd(self, dout, x, cu_steps, steps, params, saved):
+    def bilstm_bwd(self, dout, x, cu_steps, steps, params, saved, cd=torch.float32):
         dout, x = self._c(dout), self._c(x)
         Nc, W = x.shape
         D = params["weight_hh_l0"].shape[1]
@@ -627,17 +652,26 @@ class CudaBackend:
         whh_t = self._lstm_whh(params, True)
         dgates = torch.empty(2, Nc, 4 * D, dtype=f32, device=dev)
         dc = torch.zeros(2, B, D, dtype=f32, device=dev)
-        for j in range(Smax - 1, -1, -1):
-            self._call("svpc_lstm_step_bwd", B, D, Nc, Smax, j, _ptr(whh_t), _ptr(rows), _ptr(cs), _ptr(gates), _ptr(dout),
-                       _ptr(dgates), _ptr(dc))
+        if self.lstm_persistent:
+            sync = torch.zeros(4, dtype=torch.int32, device=dev)
+            self._call("svpc_lstm_seq_bwd", B, D, Nc, Smax, _ptr(whh_t), _ptr(rows), _ptr(cs), _ptr(gates), _ptr(dout),
+                       _ptr(dgates), _ptr(dc), _ptr(sync))
+            self.lstm_sync_flags.append(sync)
+        else:
+            for j in range(Smax - 1, -1, -1):
+                self._call("svpc_lstm_step_bwd", B, D, Nc, Smax, j, _ptr(whh_t), _ptr(rows), _ptr(cs), _ptr(gates),
+                           _ptr(dout), _ptr(dgates), _ptr(dc))
         grads = {}
         dx = torch.empty(Nc, W, dtype=f32, device=dev)
+        xc = self.cast(x, cd)
+        dgc = self.cast(dgates.view(2 * Nc, 4 * D), cd).view(2, Nc, 4 * D)
+        hpc = self.cast(hprev.view(2 * Nc, D), cd).view(2, Nc, D)
         for di, suf in enumerate(("", "_reverse")):
-            dg = dgates[di]
-            grads["weight_hh_l0" + suf] = self.gemm(dg.t(), hprev[di].t(), f32)
-            grads["weight_ih_l0" + suf] = self.gemm(dg.t(), x.t(), f32)
-            db = self.colsum(dg)
+            dg = dgc[di]
+            grads["weight_hh_l0" + suf] = self.gemm(dg.t(), hpc[di].t(), f32)
+            grads["weight_ih_l0" + suf] = self.gemm(dg.t(), xc.t(), f32)
+            db = self.colsum(dgates[di])
             grads["bias_ih_l0" + suf] = db
             grads["bias_hh_l0" + suf] = db.clone()
-            self.gemm(dg, params["weight_ih_l0" + suf].t(), f32, out=dx, accumulate=(di == 1))
+            self.gemm(dg, self._lstm_wih_cd(params, suf, cd).t(), f32, out=dx, accumulate=(di == 1))
         return dx, grads

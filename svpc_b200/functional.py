@@ -392,7 +392,7 @@ class BiLSTMFn(Function):
     @staticmethod
     def forward(ctx, x, lay, keys, *params):
         p = {k: v.detach() for k, v in zip(keys, params)}
-        out, saved = be().bilstm_fwd(x, lay["cu_steps"], lay["steps"], p)
+        out, saved = be().bilstm_fwd(x, lay["cu_steps"], lay["steps"], p, cd=lay.get("cd", torch.float32))
         ctx.lay, ctx.keys, ctx.n_p = lay, keys, len(params)
         ctx.save_for_backward(x, *[v.detach() for v in params], *saved)
         return out
@@ -402,7 +402,8 @@ class BiLSTMFn(Function):
         x, *rest = ctx.saved_tensors
         params, saved = rest[:ctx.n_p], rest[ctx.n_p:]
         p = dict(zip(ctx.keys, params))
-        dx, grads = be().bilstm_bwd(dout.contiguous(), x, ctx.lay["cu_steps"], ctx.lay["steps"], p, tuple(saved))
+        dx, grads = be().bilstm_bwd(dout.contiguous(), x, ctx.lay["cu_steps"], ctx.lay["steps"], p, tuple(saved),
+                                    cd=ctx.lay.get("cd", torch.float32))
         return (dx, None, None, *[grads[k] for k in ctx.keys])
 
 

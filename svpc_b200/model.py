@@ -528,7 +528,7 @@ class StateAwareRecursiveTransformer(nn.Module):
                 glay = dict(Lt=Lt, V=V, tau=float(cfg.temperature), clip_P_off=plan.t["clip_P_off"], clip_vx=plan.t["clip_vx"],
                             max_vx=max(plan.vx))
                 xbow = Fn.GumbelBowFn.apply(P, g, self.p("text_embeddings.word_embeddings.weight"), glay, text_mask)
-                llay = dict(cu_steps=plan.t["cu_steps"], steps=plan.steps)
+                llay = dict(cu_steps=plan.t["cu_steps"], steps=plan.steps, cd=self.compute_dtype)
                 r = Fn.BiLSTMFn.apply(xbow, llay, LSTM_KEYS, *[self.p("recipe_encoder." + k) for k in LSTM_KEYS])
                 re_ent, re_ac, _, re_Es, _ = self._reasoner("recipe_reasoner", r, E0, plan)
                 parts["re_entity"] = Fn.BCEFn.apply(re_ent, y_al)

@@ -1,6 +1,7 @@
 """GPU parity tests, operator by operator: every C-ABI entry point of libsvpc_b200.so (through svpc_b200.cuda_backend)
 against the plain-torch statement of the same contract (tests/torch_backend.py, fp64 math) on identical seeded inputs."""
 import math
+import numpy as np
 
 import pytest
 import torch
@@ -395,6 +396,45 @@ def test_bilstm(cb, tb, D, W):
     close("bilstm dx", dx, rdx, 1e-4)
     for key in TorchBackend.LSTM_KEYS:
         close("bilstm d" + key, grads[key], rgrads[key], 1e-4)
+
+
+@pytest.mark.parametrize("persistent", [True, False])
+@pytest.mark.parametrize("cd", [torch.float32, torch.bfloat16])
+def test_bilstm_many_videos(cb, tb, persistent, cd):
+    """20 ragged videos (two groups of 16 inside the kernels), full hidden size; the persistent sweep (one launch, grid
+    barrier per step) and the per-step launches must both match the torch statement; on the bf16 path only the four
+    batched products run on the tensor cores (2e-2)."""
+    D, W = 768, 300
+    rs = np.random.RandomState(3)
+    steps = [int(v) for v in rs.randint(1, 13, size=20)]
+    steps[3] = 12
+    cu = I32([0] + list(np.cumsum(steps)))
+    Nc = sum(steps)
+    x = rnd(Nc, W)
+    k = 1 / math.sqrt(D)
+    params = {}
+    for i, key in enumerate(TorchBackend.LSTM_KEYS):
+        shape = (4 * D, W) if "weight_ih" in key else (4 * D, D) if "weight_hh" in key else (4 * D,)
+        params[key] = (torch.rand(*shape, generator=torch.Generator().manual_seed(i)) * 2 * k - k).to(DEV)
+    was = cb.lstm_persistent
+    cb.lstm_persistent = persistent
+    cb.lstm_sync_flags.clear()
+    try:
+        out, saved = cb.bilstm_fwd(x, cu, steps, params, cd=cd)
+        dout = rnd(Nc, D, seed=5)
+        dx, grads = cb.bilstm_bwd(dout, x, cu, steps, params, saved, cd=cd)
+    finally:
+        cb.lstm_persistent = was
+    assert len(cb.lstm_sync_flags) == (2 if persistent else 0)
+    for f in cb.lstm_sync_flags:
+        assert int(f[2]) == 0, "a grid barrier of the persistent LSTM timed out"
+    rout, _ = tb.bilstm_fwd(x, cu, steps, params)
+    rdx, rgrads = tb.bilstm_bwd(dout, x, cu, steps, params, ())
+    tol = 1e-4 if cd == torch.float32 else 2e-2
+    close("bilstm out", out, rout, tol)
+    close("bilstm dx", dx, rdx, tol)
+    for key in TorchBackend.LSTM_KEYS:
+        close("bilstm d" + key, grads[key], rgrads[key], tol)
 
 
 def test_losses(cb, tb):

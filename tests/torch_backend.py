@@ -377,11 +377,11 @@ class TorchBackend:
 
     LSTM_KEYS = tuple(f"{k}_l0{s}" for s in ("", "_reverse") for k in ("weight_ih", "weight_hh", "bias_ih", "bias_hh"))
 
-    def bilstm_fwd(self, x, cu_steps, steps, params):
+    def bilstm_fwd(self, x, cu_steps, steps, params, cd=None):
         p = {k: self.f(v) for k, v in params.items()}
         return self._bilstm(self.f(x), cu_steps.tolist(), p).float(), ()
 
-    def bilstm_bwd(self, dout, x, cu_steps, steps, params, saved):
+    def bilstm_bwd(self, dout, x, cu_steps, steps, params, saved, cd=None):
         keys = list(self.LSTM_KEYS)
         g = _vjp(lambda a, *ws: self._bilstm(a, cu_steps.tolist(), dict(zip(keys, ws))),
                  [self.f(x)] + [self.f(params[k]) for k in keys], [self.f(dout)])
