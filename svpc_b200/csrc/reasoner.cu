@@ -10,7 +10,7 @@
 // The backward walks the clips in reverse with dE resident in shared memory.
 #include "common.cuh"
 
-#define RS_THREADS 256
+#define RS_THREADS 1024
 
 __global__ void __launch_bounds__(RS_THREADS) reasoner_fwd_kernel(int D, int max_ni, const float* __restrict__ E0,
                                                                   const int* __restrict__ cu_ingr,
