@@ -8,12 +8,16 @@ on every rank, so the reference BertAdam's skip of such parameters (optimization
 """
 from __future__ import annotations
 
+import os
+
 import torch
 import torch.distributed as dist
 
 
 class GradAllReducer:
-    def __init__(self, model, process_group=None, bucket_bytes: int = 32 << 20):
+    def __init__(self, model, process_group=None, bucket_bytes: int = 0):
+        if bucket_bytes <= 0:
+            bucket_bytes = int(float(os.environ.get("SVPC_DDP_BUCKET_MB", "32")) * (1 << 20))
         self.group = process_group
         self.params = [p for p in model.parameters() if p.requires_grad]
         # gradients become ready roughly in reverse registration order

@@ -113,7 +113,8 @@ def attn_ref(q, k, v, ql, kl, km, causal, H, mask_fn):
 
 
 @pytest.mark.parametrize("dt,ql,kl,causal", [(BF16, [100, 37], [100, 37], False), (BF16, [25, 25], [25, 25], True),
-                                              (F32, [12, 7], [12, 7], False), (BF16, [25, 25], [3, 3], False)])
+                                              (F32, [12, 7], [12, 7], False), (BF16, [25, 25], [3, 3], False),
+                                              (F32, [25, 9], [3, 2], False), (BF16, [1, 1], [100, 70], False)])
 def test_attention_dropout(cb, dt, ql, kl, causal):
     H, dh = 12, 64
     D = H * dh

@@ -199,6 +199,10 @@ ATT_CASES = {
     "tc_causal": ([25, 25, 17], [25, 25, 17], True, True, False),
     "tc_cross": ([25, 30], [20, 48], False, True, True),
     "tc_128": ([128], [128], True, False, False),
+    # warp-per-(sequence, head) kernels: decoder cross attention (25 x <= 3, ragged context) and the [CLS]-only layer (1 x 100)
+    "warp_cross": ([25, 25, 25, 9], [3, 2, 1, 3], False, False, True),
+    "warp_cross_masked": ([25, 25], [3, 3], False, True, True),
+    "warp_cls": ([1, 1, 1, 1], [100, 100, 37, 70], False, True, True),
 }
 
 
