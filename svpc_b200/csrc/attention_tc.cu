@@ -219,7 +219,7 @@ struct AtcParams {
 
 // ------------------------------------------------------------------------------------------------ forward
 template <int NT>
-__global__ void __launch_bounds__(256) attn_tc_fwd_kernel(const AtcParams p) {
+__global__ void __launch_bounds__(NT <= 14 ? 224 : 256, NT <= 4 ? 4 : (NT <= 14 ? 3 : 1)) attn_tc_fwd_kernel(const AtcParams p) {
   svpc_pdl_sync();
   extern __shared__ __align__(16) uint8_t atc_raw[];
   bf16* sQ = reinterpret_cast<bf16*>(atc_raw);
