@@ -240,6 +240,14 @@ int svpc_optim_apply(int n_chunks, const int* chunk_tensor, const long long* chu
 int svpc_memcpy2d_async(void* dst, long long dpitch, const void* src, long long spitch, long long width, long long height,
                         int kind, svpc_stream_t stream);
 
+/* Refresh of the compute-dtype copies of many fp32 weight tensors in one launch (functional.WeightCache; replaces the
+ * per-use `.to(bf16)` / torch.cat of fused QKV weights).  src / dst: DEVICE arrays of DEVICE pointers; tensor t has
+ * numel[t] elements in rows of cols[t], element i is written to dst[t][(i / cols[t]) * dst_ld[t] + i % cols[t]];
+ * chunk table as svpc_optim_*.  dt_dst: SVPC_F32 or SVPC_BF16. */
+int svpc_cast_multi(int n_chunks, const int* chunk_tensor, const long long* chunk_start, int chunk_elems,
+                    const void* const* src, void* const* dst, const long long* numel, const int* cols,
+                    const long long* dst_ld, int dt_dst, svpc_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -124,3 +124,54 @@ extern "C" int svpc_memcpy2d_async(void* dst, long long dpitch, const void* src,
   }
   return SVPC_OK;
 }
+
+// ------------------------------------------------------------------------------------------------
+// Refresh of the compute-dtype weight copies in ONE launch (the step used ~30 separate casts, each a few microseconds of
+// work behind a launch): tensor t has numel[t] fp32 elements in rows of cols[t]; element i goes to
+// dst[t][(i / cols[t]) * dst_ld[t] + i % cols[t]] (dst_ld > cols for row-padded TMA operands, slices of fused QKV
+// buffers are plain offsets).  Chunk table as in optim.cu.
+template <typename TD>
+__global__ void __launch_bounds__(256) cast_multi_kernel(const int* __restrict__ chunk_tensor,
+                                                         const long long* __restrict__ chunk_start, int chunk_elems,
+                                                         const float* const* __restrict__ src, TD* const* __restrict__ dst,
+                                                         const long long* __restrict__ numel, const int* __restrict__ cols,
+                                                         const long long* __restrict__ dst_ld) {
+  svpc_pdl_sync();
+  const int c = blockIdx.x, t = chunk_tensor[c];
+  const long long s0 = chunk_start[c];
+  const long long rem = numel[t] - s0;
+  const int n = (int)(rem < chunk_elems ? rem : chunk_elems);
+  const float* sp = src[t] + s0;
+  TD* dp = dst[t];
+  const int cl = cols[t];
+  const long long ld = dst_ld[t];
+  if (ld == cl && (((uintptr_t)sp | (uintptr_t)(dp + s0)) & 15) == 0) {
+    TD* d = dp + s0;
+    const int n4 = n >> 2;
+    for (int i = threadIdx.x; i < n4; i += 256) {
+      const float4 v = __ldg(reinterpret_cast<const float4*>(sp) + i);
+      stf(d + 4 * i, v.x); stf(d + 4 * i + 1, v.y); stf(d + 4 * i + 2, v.z); stf(d + 4 * i + 3, v.w);
+    }
+    for (int i = (n4 << 2) + threadIdx.x; i < n; i += 256) stf(d + i, sp[i]);
+  } else {
+    for (int i = threadIdx.x; i < n; i += 256) {
+      const long long e = s0 + i;
+      const long long r = e / cl;
+      stf(dp + r * ld + (e - r * cl), sp[i]);
+    }
+  }
+}
+
+extern "C" int svpc_cast_multi(int n_chunks, const int* chunk_tensor, const long long* chunk_start, int chunk_elems,
+                               const void* const* src, void* const* dst, const long long* numel, const int* cols,
+                               const long long* dst_ld, int dt_dst, svpc_stream_t stream) {
+  if (n_chunks <= 0) return SVPC_OK;
+  if (chunk_elems <= 0) {
+    svpc_set_error("cast_multi: chunk_elems must be positive");
+    return SVPC_ERR_ARG;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  SVPC_DISPATCH(dt_dst, TD, (svpc_launch(cast_multi_kernel<TD>, n_chunks, 256, 0, st, chunk_tensor, chunk_start, chunk_elems,
+                                         (const float* const*)src, (TD* const*)dst, numel, cols, dst_ld)));
+  return svpc_check_launch("cast_multi");
+}

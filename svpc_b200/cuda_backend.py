@@ -210,6 +210,22 @@ class CudaBackend:
         self._call("svpc_cast", _ll(x.numel()), _ptr(x), _DT[x.dtype], _ptr(out), _DT[dtype])
         return out
 
+    def cast_multi_tables(self, srcs, dsts, numel, cols, lds, chunk, device):
+        """Device tables of one svpc_cast_multi launch (pointer arrays, element counts, row geometry, chunk table)."""
+        ct, cs = [], []
+        for i, n in enumerate(numel):
+            for s in range(0, max(n, 1), chunk):
+                ct.append(i)
+                cs.append(s)
+        mk = lambda v, dt: torch.tensor(v, dtype=dt, device=device)
+        return {"n_chunks": len(ct), "chunk_tensor": mk(ct, torch.int32), "chunk_start": mk(cs, torch.int64),
+                "src": mk(srcs, torch.int64), "dst": mk(dsts, torch.int64), "numel": mk(numel, torch.int64),
+                "cols": mk(cols, torch.int32), "ld": mk(lds, torch.int64)}
+
+    def cast_multi(self, tab, dtype, chunk):
+        self._call("svpc_cast_multi", tab["n_chunks"], _ptr(tab["chunk_tensor"]), _ptr(tab["chunk_start"]), int(chunk),
+                   _ptr(tab["src"]), _ptr(tab["dst"]), _ptr(tab["numel"]), _ptr(tab["cols"]), _ptr(tab["ld"]), _DT[dtype])
+
     def sum_all(self, x):
         self._chk(x)
         x = self._c(x)

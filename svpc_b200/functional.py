@@ -24,27 +24,80 @@ class WeightCache:
     """Concatenated (along the output dim) copies of weight parameters in the compute dtype.
 
     Keyed by the identity of the parameters, invalidated by their autograd version counters (an in-place optimiser
-    update bumps them), so the cast / concat kernels run once per optimiser step, not once per use."""
+    update bumps them), so the casts run once per optimiser step, not once per use.  ``refresh_all`` brings every stale
+    entry up to date with ONE multi-tensor launch that writes into the entries' existing buffers (stable addresses: a
+    captured CUDA graph keeps reading them); a key seen for the first time is built by ``get`` with single casts."""
+
+    CHUNK = 16384
 
     def __init__(self):
-        self.store = {}
+        self.store = {}          # key -> [version tuple or None, tensor, params, dtype]
+        self._tables = {}        # (dtype, keys of the stale set) -> device tables of the multi-tensor launch
+
+    @staticmethod
+    def _version(ws):
+        return tuple(w._version for w in ws) + tuple(w.data_ptr() for w in ws)
 
     def get(self, ws, dtype):
         if len(ws) == 1 and ws[0].dtype == dtype and ws[0].is_contiguous():
             return ws[0].detach()
         key = tuple(id(w) for w in ws) + (dtype,)
-        ver = tuple(w._version for w in ws) + tuple(w.data_ptr() for w in ws)
+        ver = self._version(ws)
         hit = self.store.get(key)
         if hit is not None and hit[0] == ver:
             return hit[1]
         with torch.no_grad():
             parts = [be().cast(w.detach().contiguous(), dtype) for w in ws]
             t = parts[0] if len(parts) == 1 else torch.cat(parts, dim=0)
-        self.store[key] = (ver, t)
+        self.store[key] = [ver, t, list(ws), dtype]
         return t
+
+    def invalidate(self):
+        """Mark every entry stale but keep its buffer (next ``refresh_all`` rewrites them in place)."""
+        for e in self.store.values():
+            e[0] = None
+
+    def prepare(self):
+        """Build the device tables of the next ``refresh_all`` without launching (a CUDA-graph capture cannot upload them)."""
+        self.refresh_all(launch=False)
+
+    def refresh_all(self, launch=True):
+        """One launch per compute dtype for all entries whose parameters changed since they were cast."""
+        stale = [(k, e) for k, e in self.store.items()
+                 if e[0] != self._version(e[2]) and all(w.is_cuda and w.dtype == torch.float32 and w.dim() <= 2 and
+                                                        w.is_contiguous() for w in e[2])]
+        if not stale or not hasattr(be(), "cast_multi"):
+            return
+        for dtype in {e[3] for _, e in stale}:
+            group = [(k, e) for k, e in stale if e[3] == dtype]
+            tkey = (dtype,) + tuple(k for k, _ in group) + tuple(w.data_ptr() for _, e in group for w in e[2])
+            tab = self._tables.get(tkey)
+            if tab is None:
+                if len(self._tables) > 16:
+                    self._tables.clear()
+                srcs, dsts, numel, cols, lds = [], [], [], [], []
+                for _, e in group:
+                    t, off = e[1], 0                      # off: element offset of the next part inside the entry's buffer
+                    esz = t.element_size()
+                    for w in e[2]:
+                        c = w.shape[1] if (w.dim() == 2 and t.dim() == 2) else w.numel()
+                        ld = t.stride(0) if (w.dim() == 2 and t.dim() == 2) else c
+                        srcs.append(w.data_ptr())
+                        dsts.append(t.data_ptr() + off * esz)
+                        numel.append(w.numel())
+                        cols.append(c)
+                        lds.append(ld)
+                        off += w.shape[0] * t.stride(0) if (w.dim() == 2 and t.dim() == 2) else w.numel()
+                tab = self._tables[tkey] = be().cast_multi_tables(srcs, dsts, numel, cols, lds, self.CHUNK,
+                                                                   group[0][1][2][0].device)
+            if launch:
+                be().cast_multi(tab, dtype, self.CHUNK)
+                for _, e in group:
+                    e[0] = self._version(e[2])
 
     def clear(self):
         self.store.clear()
+        self._tables.clear()
 
 
 WEIGHTS = WeightCache()

@@ -159,7 +159,8 @@ class GraphedTrainStep:
         self.outputs = None         # drop the warm-up autograd graphs (their AccumulateGrad nodes belong to `side`)
         gc.collect()
         Fn.be().clear_weight_caches()
-        Fn.WEIGHTS.clear()          # the refresh of the compute-dtype weight copies becomes part of the graph
+        Fn.WEIGHTS.invalidate()     # the refresh of the compute-dtype weight copies (one multi-tensor cast) is captured too
+        Fn.WEIGHTS.prepare()        # ... its pointer tables are uploaded before the capture starts
         model.zero_grad(set_to_none=True)
         with torch.cuda.graph(self.graph):
             self.loss = self._eager(zero=False)

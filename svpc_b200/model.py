@@ -476,6 +476,7 @@ class StateAwareRecursiveTransformer(nn.Module):
         f32 = torch.float32
         dev = video_features_list[0].device
         self._begin_step(dev)
+        Fn.WEIGHTS.refresh_all()          # compute-dtype weight copies touched by the optimiser: one multi-tensor cast
         if plan is None:
             plan = self.make_plan(batch_step_num, ingr_id_dict, extra_zeros, alignments, dev)
         B, Nc = plan.B, plan.Nc

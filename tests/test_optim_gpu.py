@@ -195,3 +195,45 @@ def test_model_scale_against_torch_ops():
         errs = float((ema.shadow[name] - want_s).abs().max() / (want_s.abs().max() + 1e-30))
         worst = max(worst, errs)
     assert worst < TOL, worst
+
+
+@pytest.mark.parametrize("graph", [False, True])
+def test_weight_cache_follows_the_optimizer(graph):
+    """After a fused optimiser step the compute-dtype weight copies (functional.WeightCache, refreshed by ONE multi-tensor
+    cast at the start of the next forward, inside the captured graph too) must equal a fresh cast of the new parameters:
+    the next loss equals that of a new model loaded from the updated state_dict."""
+    import copy
+    from svpc_b200 import optim as SO, synth, functional as Fn
+    from svpc_b200.config import tiny_config
+    from svpc_b200.model import StateAwareRecursiveTransformer
+    dev = torch.device("cuda:0")
+    cfg = tiny_config("full")
+    sd = synth.init_state_dict(cfg, seed=1)
+    batch = synth.make_batch(cfg, B=3, S=4, seed=5, ragged=True, n_ingr=4, n_oov=2)
+    args = synth.forward_args(batch, dev)
+    noise = [g.to(dev) for g in batch["gumbel"]]
+    model = StateAwareRecursiveTransformer(cfg, compute_dtype=torch.bfloat16)
+    model.load_state_dict(sd)
+    model.to(dev).eval()
+    opt = SO.BertAdam([p for p in model.parameters() if p.requires_grad], lr=5e-3, warmup=-1, t_total=-1, weight_decay=0.0)
+    if graph:
+        from svpc_b200.graph import GraphedTrainStep
+        step = GraphedTrainStep(model, args, gumbel_noise=noise, warmup=1)
+        run = lambda: step.run()
+    else:
+        def run():
+            model.zero_grad(set_to_none=True)
+            loss = model(*args, gumbel_noise=noise)[0]
+            loss.backward()
+            return loss
+    l0 = float(run())
+    opt.step(grad_clip=1.0)
+    l1 = float(run())
+    assert abs(l1 - l0) > 1e-4 * abs(l0)                         # the update is visible in the next step
+    fresh = StateAwareRecursiveTransformer(cfg, compute_dtype=torch.bfloat16)
+    fresh.load_state_dict(copy.deepcopy(model.state_dict()))
+    fresh.to(dev).eval()
+    Fn.WEIGHTS.clear()
+    with torch.no_grad():
+        want = float(fresh(*args, gumbel_noise=noise)[0])
+    assert abs(l1 - want) <= 1e-6 * abs(want), (l0, l1, want)
