@@ -54,6 +54,24 @@ def parse():
 
 
 # ------------------------------------------------------------------------------------------------ helpers
+def bind_to_gpu_numa(local_rank):
+    """Pin this rank's host threads to the CPUs NVML reports as local to its GPU, BEFORE any pinned buffer is allocated:
+    first-touch then places the input arena on the GPU's NUMA node, so 8 ranks do not pull their uploads across the socket
+    link.  Returns (description, previous affinity)."""
+    prev = os.sched_getaffinity(0)
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        pr = torch.cuda.get_device_properties(local_rank)
+        bus = "%08x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+        h = pynvml.nvmlDeviceGetHandleByPciBusId(bus.encode())
+        pynvml.nvmlDeviceSetCpuAffinity(h)
+        now = os.sched_getaffinity(0)
+        return f"gpu-local cpus via nvml ({len(now)} of {len(prev)})", prev
+    except Exception as e:                                   # no NVML / no permission: leave the scheduler alone
+        return f"unchanged ({type(e).__name__})", prev
+
+
 class ClockSampler(threading.Thread):
     """Samples SM clock / throttle reasons with nvidia-smi while the timed region runs."""
     Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
@@ -288,6 +306,7 @@ def main():
     assert torch.cuda.is_available(), "bench.py needs a GPU (the SVPC operators have no CPU path)"
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    affinity, full_affinity = bind_to_gpu_numa(local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     cd = torch.bfloat16 if args.dtype == "bf16" else torch.float32
@@ -501,13 +520,21 @@ def main():
                         "flop_per_launch": fl, "launches_per_step": n // nrep, "avg_ms": round(avg_ms, 4),
                         "share_of_step": round(avg_ms * (n // nrep) / (ms / args.steps), 4),
                         "all_tc_gemm_flop_share": round(sum(x[0] for x in tc) / nrep / (gf_need_step * 1e9), 4),
-                        "how": "20 back-to-back launches of this shape, CUDA events on the launching stream"}
+                        "how": "20 back-to-back launches of this shape, CUDA events on the launching stream",
+                        # every tcgen05 GEMM of the step together (per-launch CUDA events in an eager step: short launches
+                        # are overstated by the event overhead, so this is a lower bound of the aggregate efficiency)
+                        "all_tc_gemms": {"launches_per_step": sum(x[2] for x in tc) // nrep,
+                                         "gflop_per_step": round(sum(x[0] for x in tc) / nrep / 1e9, 1),
+                                         "ms_per_step": round(sum(x[1] for x in tc) / nrep, 3),
+                                         "achieved": round(sum(x[0] for x in tc) / (sum(x[1] for x in tc) / 1e3) / 1e12, 1),
+                                         "frac": round(sum(x[0] for x in tc) / (sum(x[1] for x in tc) / 1e3) / 1e12 / tf_sus, 4)}}
     if world > 1:
         dist.barrier()
 
     # ---- CPU baseline (rank 0, N = 1): the reference algorithm on the host cores, bounded sample
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        os.sched_setaffinity(0, full_affinity)              # the CPU baseline gets every host core back
         v, per_step, cores, n = cpu_reference_run(cfg, sd, args, 2, 1, args.cpu_sample_videos)
         cpu = {"value": round(v, 3), "unit": "clips/s", "cores": cores, "kind": "port",
                "sample": f"oracle fwd+bwd fp32 on {n} clips ({args.cpu_sample_videos} videos x {args.clips}), {cores} torch threads, {per_step:.2f} s/step"}
@@ -518,7 +545,7 @@ def main():
             "metric": "vivt train clips/sec", "value": round(value, 2), "unit": "clips/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": round(ms / args.steps, 3), "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
-            "config": {"workload": workload, "parallelism": f"dp{world}", "launch": "eager" if gstep is None else "cuda-graph replay (fwd+bwd+weight refresh captured once)", "global_videos": world * args.videos,
+            "config": {"workload": workload, "parallelism": f"dp{world}", "host_affinity": affinity, "launch": "eager" if gstep is None else "cuda-graph replay (fwd+bwd+weight refresh captured once)", "global_videos": world * args.videos,
                        "weights": "random-init (init_bert_weights scale), seed 2019", "dropout": "off (model.eval())" if args.eval_mode else "train mode: hidden 0.1, attention 0.1, action selector 0.4 (reference defaults), counter-based masks recomputed in backward",
                        "l2": "inputs (295 MB of features per step) exceed the 126 MB L2",
                        "gflop_per_clip_as_written": GF_PER_CLIP_AS_WRITTEN[args.mode], "gflop_per_clip_needed": round(gf_need, 3),
