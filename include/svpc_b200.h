@@ -248,6 +248,15 @@ int svpc_cast_multi(int n_chunks, const int* chunk_tensor, const long long* chun
                     const void* const* src, void* const* dst, const long long* numel, const int* cols,
                     const long long* dst_ld, int dt_dst, svpc_stream_t stream);
 
+/* Training-loop bookkeeping without host synchronisation.  svpc_caption_accuracy = cal_performance +
+ * n_word of src/train.py:32-38, 153-157 over all videos of a step: scores / gold are DEVICE arrays of DEVICE pointers
+ * (video b: rows[b] rows of width[b] fp32 scores, rows[b] int64 labels), row_start = exclusive prefix sum of rows;
+ * acc[0] += correct, acc[1] += labelled rows (label != ignore).  svpc_f1_counts = calculate_f1 (train.py:40-49):
+ * acc[0] += sum gold[p > 0.5], acc[1] += sum gold, acc[2] += count(p > 0.5).  acc is fp64 (exact for counts). */
+int svpc_caption_accuracy(int n_videos, const void* const* scores, const void* const* gold, const int* rows, const int* width,
+                          const int* row_start, int total_rows, long long ignore, double* acc, svpc_stream_t stream);
+int svpc_f1_counts(long long n, const float* p, const float* y, double* acc, svpc_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
