@@ -257,6 +257,21 @@ int svpc_caption_accuracy(int n_videos, const void* const* scores, const void* c
                           const int* row_start, int total_rows, long long ignore, double* acc, svpc_stream_t stream);
 int svpc_f1_counts(long long n, const float* p, const float* y, double* acc, svpc_stream_t stream);
 
+/* Clip features from the per-video .npy files straight into the pinned input arena.  HOST entry points
+ * (every pointer below is a host pointer; no CUDA call is made).  Together they replace, per training step,
+ * `np.concatenate([np.load(<v>_resnet.npy), np.load(<v>_bn.npy)], axis=1)` (src/rtransformer/recursive_caption_dataset.py
+ * :187-189), the float64 `(max_v_len + max_t_len, D)` scratch of `_load_indexed_video_feature` (:389-416), `.astype(
+ * np.float32)` (:332) and the collate stack: each needed row is read once and written once, as fp32, at its final place.
+ * svpc_npy_info: shape / dtype code (0 '<f4', 1 '<f8', 2 '<f2') / byte offset of the data of a rank-2 C-ordered .npy.
+ * svpc_features_gather: job j copies rows[row_start[j] .. row_start[j+1]) of file paths[j] to rows first_row.. of the clip
+ * block dst[j] (block_rows rows of dst_pitch floats) at columns [col_off[j], col_off[j] + file columns) and zero-fills
+ * the block's other rows in that column range; jobs run on n_threads host threads.  The row lists come from
+ * svpc_b200/features.py `clip_rows` (the host mirror of `_convert_to_feat_index_st_ed` / `_load_indexed_video_feature`). */
+int svpc_npy_info(const char* path, long long* rows, long long* cols, int* dtype, long long* data_offset);
+int svpc_features_gather(int n_jobs, const char* const* paths, const long long* row_start, const long long* rows,
+                         float* const* dst, long long dst_pitch, const long long* col_off, int first_row, int block_rows,
+                         int n_threads);
+
 #ifdef __cplusplus
 }
 #endif

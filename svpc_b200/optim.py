@@ -184,18 +184,36 @@ class EMA(object):
                             None, _p(pt), None, None, _p(st), _p(tab.numel), None, None, None,
                             C.c_double(0.0), C.c_double(0.0), C.c_double(0.0), _p(T["decay"]), EMA_FLAG)
 
+    def _copy_all(self, T, key, srcs, dsts):
+        """dst[i] <- src[i] for all registered tensors in ONE launch (multi-tensor fp32 copy through svpc_cast_multi)."""
+        sig = ([t.data_ptr() for t in srcs], [t.data_ptr() for t in dsts])
+        hit = T.get(key)
+        if hit is None or hit[0] != sig:
+            n = [t.numel() for t in srcs]
+            hit = T[key] = (sig, _be().cast_multi_tables(sig[0], sig[1], n, n, n, CHUNK, T["tab"].device))
+        _be().cast_multi(hit[1], torch.float32, CHUNK)
+
     def assign(self, model):                                          # :205-210
-        for name, param in model.named_parameters():
-            if param.requires_grad:
-                assert name in self.shadow
-                self.original[name] = param.data.clone()
-                param.data = self.shadow[name]
+        """Parameters take the shadow values, the originals are kept for ``resume``.  The reference re-points
+        ``param.data`` at the shadow tensors (after one clone per parameter); here the VALUES move - two multi-tensor
+        launches - and every parameter keeps its address, so captured CUDA graphs, optimiser pointer tables and the
+        registered-pointer map stay valid across the evaluation window (train.py:393-405)."""
+        named, T = self._bind(model)
+        params = [p.data for _, p in named]
+        for (n, _), p in zip(named, params):
+            o = self.original.get(n)
+            if o is None or o.shape != p.shape or o.device != p.device:
+                self.original[n] = torch.empty_like(p)
+        self._copy_all(T, "save", params, [self.original[n] for n, _ in named])
+        self._copy_all(T, "load", [self.shadow[n] for n, _ in named], params)
+        torch.autograd.graph.increment_version([p for _, p in named])
 
     def resume(self, model):                                          # :212-216
-        for name, param in model.named_parameters():
-            if param.requires_grad:
-                assert name in self.shadow
-                param.data = self.original[name]
+        named, T = self._bind(model)
+        for n, _ in named:
+            assert n in self.original, "resume() without assign()"
+        self._copy_all(T, "restore", [self.original[n] for n, _ in named], [p.data for _, p in named])
+        torch.autograd.graph.increment_version([p for _, p in named])
 
 
 # ---------------------------------------------------------------------------------------------------- BertAdam
