@@ -346,76 +346,94 @@ __global__ void __launch_bounds__(LSTM_PW * 32, 1) lstm_seq_fwd_kernel(const Lst
   }
 }
 
+// Backward sweep.  Per step the CTA needs dh[b][u] = sum_e dgates[row_next(b)][e] * W_hh^T[u][e] over ALL e < 4D for its
+// (up to LSTM_PW) hidden units u and the B videos: a (B x 4D) x (4D x LSTM_PW) product whose cost is operand delivery, not
+// flops.  The contraction index e is split over the CTA's threads (thread t owns e = 4t, 4t + 4*blockDim, ...): every
+// gate-gradient element is loaded from L2 exactly once per CTA, straight into registers (no staging, no barriers), every
+// resident weight is read from shared memory once per pass of LSTM_BB videos, and each thread carries an LSTM_PW x LSTM_BB
+// register tile of partial sums, reduced by a transposing warp reduction and one cross-warp pass through shared memory.
+#define LSTM_BB 8           // videos per pass of the backward product (register tile LSTM_PW x LSTM_BB)
 __global__ void __launch_bounds__(LSTM_PW * 32, 1) lstm_seq_bwd_kernel(const LstmSeqParams q) {
   svpc_pdl_sync();
   const LstmStepParams& p = q.s;
   extern __shared__ __align__(16) float smem[];
-  const int D = p.D;
+  constexpr int NACC = LSTM_PW * LSTM_BB;
+  const int D = p.D, E4 = 4 * p.D;
   const int dir = blockIdx.x / q.cpd, c = blockIdx.x - dir * q.cpd;
   const int u0 = (int)((long long)c * D / q.cpd), u1 = (int)((long long)(c + 1) * D / q.cpd);
+  const int nu = u1 - u0;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  float* wsm = smem;                                     // [LSTM_PW][4D]  rows u0.. of W_hh^T[dir]
-  float* gsm = smem + (size_t)LSTM_PW * 4 * D;           // [LSTM_BV][D]
-  for (int e = threadIdx.x * 4; e < (u1 - u0) * 4 * D; e += blockDim.x * 4)
-    *reinterpret_cast<float4*>(wsm + e) =
-        __ldg(reinterpret_cast<const float4*>(p.whh + ((long long)dir * D + u0) * 4 * D + e));
-  const float* dg = p.dgates + (long long)dir * p.Nc * 4 * D;
+  float* wsm = smem;                                     // [LSTM_PW][4D]  rows u0.. of W_hh^T[dir], zero beyond nu
+  float* red = smem + (size_t)LSTM_PW * E4;              // [2][LSTM_PW warps][NACC] partial sums
+  for (int e = threadIdx.x * 4; e < LSTM_PW * E4; e += blockDim.x * 4) {
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (e < nu * E4) v = __ldg(reinterpret_cast<const float4*>(p.whh + ((long long)dir * D + u0) * E4 + e));
+    *reinterpret_cast<float4*>(wsm + e) = v;
+  }
+  const float* dg = p.dgates + (long long)dir * p.Nc * E4;
   const float* cs = p.cs + (long long)dir * p.Nc * D;
   unsigned int* cnt = q.sync + dir;
-  const int d = u0 + warp;
-  const bool own = warp < u1 - u0;
   for (int j = p.Smax - 1, it = 0; j >= 0; --j, ++it) {
     const int* rows_j = p.rows + ((long long)dir * p.Smax + j) * p.B;
     const int* rows_n = rows_j + p.B;
     const bool has_next = j + 1 < p.Smax;
     if (it > 0) dir_barrier_wait(cnt, (unsigned int)(q.cpd * it), q.sync + 2);   // gate gradients of step j+1 complete
     else __syncthreads();
-    for (int b0 = 0; b0 < p.B; b0 += LSTM_BV) {
-      float acc[LSTM_BV];
-#pragma unroll
-      for (int i = 0; i < LSTM_BV; ++i) acc[i] = 0.f;
+    for (int b0 = 0, pass = 0; b0 < p.B; b0 += LSTM_BB, ++pass) {
+      float* rbuf = red + (size_t)(pass & 1) * (LSTM_PW * NACC);
       if (has_next) {
-        for (int ch = 0; ch < 4; ++ch) {
-          __syncthreads();
-          for (int e = threadIdx.x * 4; e < LSTM_BV * D; e += blockDim.x * 4) {
-            const int b = e / D, k = e - b * D;
-            const int rn = (b0 + b < p.B) ? rows_n[b0 + b] : -1;
-            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (rn >= 0) v = __ldcg(reinterpret_cast<const float4*>(dg + (long long)rn * 4 * D + ch * D + k));
-            *reinterpret_cast<float4*>(gsm + e) = v;
-          }
-          __syncthreads();
-          if (own) {
-            const float* wt = wsm + (size_t)warp * 4 * D + ch * D;
-            for (int k = lane * 4; k < D; k += 128) {
-              const float4 wv = *reinterpret_cast<const float4*>(wt + k);
+        float acc[NACC];
 #pragma unroll
-              for (int b = 0; b < LSTM_BV; ++b) {
-                const float4 g = *reinterpret_cast<const float4*>(gsm + b * D + k);
-                float a = acc[b];
-                a = fmaf(g.x, wv.x, a); a = fmaf(g.y, wv.y, a); a = fmaf(g.z, wv.z, a); a = fmaf(g.w, wv.w, a);
-                acc[b] = a;
-              }
+        for (int i = 0; i < NACC; ++i) acc[i] = 0.f;
+        const float* gp[LSTM_BB];
+#pragma unroll
+        for (int b = 0; b < LSTM_BB; ++b) {
+          const int rn = (b0 + b < p.B) ? rows_n[b0 + b] : -1;
+          gp[b] = rn >= 0 ? dg + (long long)rn * E4 : nullptr;
+        }
+        for (int e = threadIdx.x * 4; e < E4; e += blockDim.x * 4) {
+          float4 g[LSTM_BB];
+#pragma unroll
+          for (int b = 0; b < LSTM_BB; ++b)
+            g[b] = gp[b] ? __ldcg(reinterpret_cast<const float4*>(gp[b] + e)) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+          for (int u = 0; u < LSTM_PW; ++u) {
+            const float4 wv = *reinterpret_cast<const float4*>(wsm + (size_t)u * E4 + e);
+#pragma unroll
+            for (int b = 0; b < LSTM_BB; ++b) {
+              float a = acc[u * LSTM_BB + b];
+              a = fmaf(g[b].x, wv.x, a); a = fmaf(g[b].y, wv.y, a); a = fmaf(g[b].z, wv.z, a); a = fmaf(g[b].w, wv.w, a);
+              acc[u * LSTM_BB + b] = a;
             }
           }
         }
-        warp_reduce_transpose<LSTM_BV>(acc, lane);
-        acc[0] += __shfl_xor_sync(0xffffffffu, acc[0], 1);
+        warp_reduce_transpose<NACC>(acc, lane);            // lane l holds the warp's sums of elements 3l, 3l+1, 3l+2
+        static_assert(NACC == 96, "three elements per lane after the transposing reduction");
+        float* rw = rbuf + warp * NACC + 3 * lane;
+        rw[0] = acc[0]; rw[1] = acc[1]; rw[2] = acc[2];
       }
-      const int b = b0 + (lane >> 1);
-      if (!own || (lane & 1) || b >= p.B) continue;
+      __syncthreads();
+      const int t = threadIdx.x;
+      const int u = t / LSTM_BB, b = b0 + (t - u * LSTM_BB);
+      if (t >= NACC || u >= nu || b >= p.B) continue;
       const int r = rows_j[b];
       if (r < 0) continue;
+      float sum = 0.f;
+      if (has_next) {
+#pragma unroll
+        for (int w = 0; w < LSTM_PW; ++w) sum += rbuf[w * NACC + t];
+      }
+      const int d = u0 + u;
       const int rp = j > 0 ? rows_j[b - p.B] : -1;
-      const float* g = p.gates + ((long long)dir * p.Nc + r) * 4 * D;
+      const float* g = p.gates + ((long long)dir * p.Nc + r) * E4;
       const float gi = g[d], gf = g[D + d], gg = g[2 * D + d], go = g[3 * D + d];
       const float tc = tanhf(cs[(long long)r * D + d]);
       const float cp = rp >= 0 ? cs[(long long)rp * D + d] : 0.f;
-      const float dh = p.dout[(long long)r * D + d] + acc[0];
+      const float dh = p.dout[(long long)r * D + d] + sum;
       float* dcp = p.dc + ((long long)dir * p.B + b) * D + d;           // owned by this thread for the whole sweep
       const float dct = *dcp + dh * go * (1.f - tc * tc);
       *dcp = dct * gf;
-      float* da = p.dgates + ((long long)dir * p.Nc + r) * 4 * D;
+      float* da = p.dgates + ((long long)dir * p.Nc + r) * E4;
       da[d] = dct * gg * gi * (1.f - gi);
       da[D + d] = dct * cp * gf * (1.f - gf);
       da[2 * D + d] = dct * gi * (1.f - gg * gg);
@@ -439,7 +457,9 @@ static int lstm_seq_launch(bool bwd, LstmSeqParams& q, cudaStream_t st) {
   q.cpd = sms / 2;
   SVPC_REQUIRE(q.cpd >= 1 && (p.D + q.cpd - 1) / q.cpd <= LSTM_PW,
                "lstm_seq: %d hidden units over %d CTAs per direction exceed %d units per CTA", p.D, q.cpd, LSTM_PW);
-  const size_t smem = ((size_t)LSTM_PW * 4 * p.D + (size_t)LSTM_BV * p.D) * sizeof(float);
+  const size_t tail = (size_t)LSTM_BV * p.D > (size_t)2 * LSTM_PW * LSTM_PW * LSTM_BB ? (size_t)LSTM_BV * p.D
+                                                                                  : (size_t)2 * LSTM_PW * LSTM_PW * LSTM_BB;
+  const size_t smem = ((size_t)LSTM_PW * 4 * p.D + tail) * sizeof(float);   // fwd: h staging; bwd: reduction buffers
   SVPC_REQUIRE(smem <= 227 * 1024, "lstm_seq: hidden size %d needs %zu bytes of shared memory", p.D, smem);
   static bool attr = false;
   if (!attr) {
