@@ -28,6 +28,7 @@ __global__ void __launch_bounds__(RS_THREADS) reasoner_fwd_kernel(int D, int max
   float* e = kv + D;                   // (max_ni)
   float* ep = e + max_ni;              // (max_ni)
   float* a = ep + max_ni;              // (max_ni)
+  float* an = a + max_ni;              // (max_ni) a / sum a
   __shared__ float red[64];
   const int b = blockIdx.x;
   const int g0 = cu_ingr[b], ni = cu_ingr[b + 1] - g0;
@@ -56,22 +57,28 @@ __global__ void __launch_bounds__(RS_THREADS) reasoner_fwd_kernel(int D, int max
       a[i] = ai;
       part += ai;
     }
-    const float asum = block_sum(part, red);   // (syncs: a[] visible)
-    const float w4 = w4s[n];
+    const float w4 = w4s[n];                   // (issued before the reduction: its latency hides behind the barriers)
     const long long eo = clip_ent_off[n];
+    const float asum = block_sum(part, red);   // (syncs: a[] visible)
+    for (int i = threadIdx.x; i < ni; i += RS_THREADS) an[i] = a[i] / asum;   // one division per ingredient, not per element
+    __syncthreads();
     for (int d = threadIdx.x; d < D; d += RS_THREADS) {
       float s = 0.f;
-      for (int i = 0; i < ni; ++i) s = fmaf(a[i] / asum, E[i * D + d], s);
+      for (int i = 0; i < ni; ++i) s = fmaf(an[i], E[i * D + d], s);
       ebar_out[(long long)n * D + d] = s;
       const float kk = w4 * s;
       kv[d] = kk > 0.f ? kk : 0.f;
     }
     __syncthreads();
-    for (int idx = threadIdx.x; idx < ni * D; idx += RS_THREADS) {
-      const int i = idx / D, d = idx - i * D;
-      const float v = a[i] * kv[d] + (1.f - a[i]) * E[idx];
-      E[idx] = v;
-      Es[(eo + i) * D + d] = v;
+    for (int i = warp; i < ni; i += RS_THREADS / 32) {           // one warp per entity row: no index division
+      const float ai = a[i], bi = 1.f - ai;
+      float* Ei = E + i * D;
+      float* Eo = Es + (eo + i) * D;
+      for (int d = lane; d < D; d += 32) {
+        const float v = ai * kv[d] + bi * Ei[d];
+        Ei[d] = v;
+        Eo[d] = v;
+      }
     }
     for (int i = threadIdx.x; i < ni; i += RS_THREADS) {
       ent[eo + i] = e[i];
@@ -100,6 +107,7 @@ __global__ void __launch_bounds__(RS_THREADS) reasoner_bwd_kernel(
   float* dan = da + max_ni;              // (max_ni)
   float* de_next = dan + max_ni;         // (max_ni) gradient flowing into e_t from step t+1 (through e_prev)
   float* dz = de_next + max_ni;          // (max_ni)
+  float* avs = dz + max_ni;              // (max_ni) a of this step
   __shared__ float red[64];
   const int b = blockIdx.x;
   const int g0 = cu_ingr[b], ni = cu_ingr[b + 1] - g0;
@@ -120,8 +128,12 @@ __global__ void __launch_bounds__(RS_THREADS) reasoner_bwd_kernel(
     const float x0 = expf(l0 - mx), x1 = expf(l1 - mx), x2 = expf(l2 - mx);
     const float c0 = x0 / (x0 + x1 + x2), c1 = x1 / (x0 + x1 + x2), c2 = x2 / (x0 + x1 + x2);
     float part = 0.f;
-    for (int i = threadIdx.x; i < ni; i += RS_THREADS) part += av[i];
-    const float asum = block_sum(part, red);
+    for (int i = threadIdx.x; i < ni; i += RS_THREADS) {
+      const float ai = av[i];
+      avs[i] = ai;                             // the per-element loops below read a from shared memory, not from L2
+      part += ai;
+    }
+    const float asum = block_sum(part, red);   // (syncs: avs visible)
     // stage E_{t-1}, k ; dE += dEs[n]
     for (int idx = threadIdx.x; idx < ni * D; idx += RS_THREADS) {
       Ep[idx] = Eprev[idx];
@@ -143,7 +155,7 @@ __global__ void __launch_bounds__(RS_THREADS) reasoner_bwd_kernel(
     float pw4 = 0.f;
     for (int d = threadIdx.x; d < D; d += RS_THREADS) {
       float s = 0.f;
-      for (int i = 0; i < ni; ++i) s = fmaf(av[i], dE[i * D + d], s);
+      for (int i = 0; i < ni; ++i) s = fmaf(avs[i], dE[i * D + d], s);
       const float eb = ebar[(long long)n * D + d];
       const float dpre = (w4 * eb > 0.f) ? s : 0.f;
       pw4 = fmaf(dpre, eb, pw4);
@@ -189,9 +201,10 @@ __global__ void __launch_bounds__(RS_THREADS) reasoner_bwd_kernel(
       for (int i = 0; i < ni; ++i) s = fmaf(dz[i], Ep[i * D + d], s);
       dw2v[(long long)n * D + d] = s;
     }
-    for (int idx = threadIdx.x; idx < ni * D; idx += RS_THREADS) {
-      const int i = idx / D, d = idx - i * D;
-      dE[idx] = (1.f - av[i]) * dE[idx] + (av[i] / asum) * deb[d] + dz[i] * w[d];
+    for (int i = warp; i < ni; i += RS_THREADS / 32) {           // one warp per entity row: no index division
+      const float ai = avs[i], bi = 1.f - ai, ani = ai / asum, dzi = dz[i];
+      float* dEi = dE + i * D;
+      for (int d = lane; d < D; d += 32) dEi[d] = bi * dEi[d] + ani * deb[d] + dzi * w[d];
     }
     __syncthreads();
   }
@@ -202,7 +215,7 @@ extern "C" int svpc_reasoner_fwd(int B, int D, int max_ni, const float* E0, cons
                                  const int* clip_ent_off, const float* w2v, const float* clog, const float* w4s,
                                  float* ent, float* ebar, float* Es, float* a_saved, svpc_stream_t stream) {
   if (B <= 0) return SVPC_OK;
-  const size_t smem = sizeof(float) * ((size_t)max_ni * D + D + 3 * (size_t)max_ni);
+  const size_t smem = sizeof(float) * ((size_t)max_ni * D + D + 4 * (size_t)max_ni);
   SVPC_REQUIRE(smem <= 220 * 1024, "reasoner_fwd: %d ingredients x %d do not fit in shared memory", max_ni, D);
   cudaFuncSetAttribute(reasoner_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   svpc_launch(reasoner_fwd_kernel, B, RS_THREADS, smem, (cudaStream_t)stream, D, max_ni, E0, cu_ingr, cu_steps, clip_ent_off, w2v, clog,
@@ -216,7 +229,7 @@ extern "C" int svpc_reasoner_bwd(int B, int D, int max_ni, const float* E0, cons
                                  const float* d_ent, const float* d_ebar, const float* d_Es, float* dE0, float* dw2v,
                                  float* dclog, float* dw4s, svpc_stream_t stream) {
   if (B <= 0) return SVPC_OK;
-  const size_t smem = sizeof(float) * (2 * (size_t)max_ni * D + 3 * (size_t)D + 4 * (size_t)max_ni);
+  const size_t smem = sizeof(float) * (2 * (size_t)max_ni * D + 3 * (size_t)D + 5 * (size_t)max_ni);
   SVPC_REQUIRE(smem <= 220 * 1024, "reasoner_bwd: %d ingredients x %d do not fit in shared memory", max_ni, D);
   cudaFuncSetAttribute(reasoner_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   svpc_launch(reasoner_bwd_kernel, B, RS_THREADS, smem, (cudaStream_t)stream, D, max_ni, E0, cu_ingr, cu_steps, clip_ent_off, w2v, clog,
