@@ -1,5 +1,5 @@
 #!/bin/bash
 mkdir -p gpurun_out
 N=${1:-8}
-timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29531 bench.py --gpus $N --steps 10 --warmup 3 > gpurun_out/bench_n$N.json 2> gpurun_out/bench_n$N.err; echo "bench N=$N rc=$?"
-grep -v Warning gpurun_out/bench_n$N.err | tail -3 | cut -c1-300; cut -c1-1200 gpurun_out/bench_n$N.json
+timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $N --steps 10 --warmup 3 > gpurun_out/bench_n$N.json 2> gpurun_out/bench_n$N.err; echo "bench N=$N rc=$?"
+tail -2 gpurun_out/bench_n$N.err | cut -c1-300; cut -c1-400 gpurun_out/bench_n$N.json
