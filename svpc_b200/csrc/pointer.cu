@@ -12,9 +12,8 @@
 #define PG_THREADS 256
 // The per-(clip, position) pointer-generator kernels are chains of short dependent phases (a dozen barriers, L2 round
 // trips): their throughput is rows in flight per SM / chain latency, so they run with 128-thread CTAs (16 rows per SM).
-#ifndef PTR_THREADS
-#define PTR_THREADS 128
-#endif
+// With few rows (greedy decoding: one position per launch) the chain latency of a single row is what counts: 256 threads.
+static inline int ptr_threads(int Lt, int n_clips) { return (long long)Lt * n_clips >= 8 * SVPC_NUM_SMS ? 128 : PG_THREADS; }
 
 __device__ __forceinline__ float ls_q(int v, int label, int vx, float s, float conf) {
   if (v == label) return conf;
@@ -30,7 +29,7 @@ __device__ __forceinline__ float ls_const(int label, int vx, float s, float conf
 
 // ------------------------------------------------------------------------------------------------
 template <typename T>
-__global__ void __launch_bounds__(PTR_THREADS) pointer_fwd_kernel(
+__global__ void __launch_bounds__(PG_THREADS) pointer_fwd_kernel(
     int Lt, int D, int V, int max_ni, int max_vx, const T* __restrict__ dec, const float* __restrict__ G,
     const float* __restrict__ Esrc, const int* __restrict__ clip_src_off, const int* __restrict__ clip_ni,
     const int* __restrict__ clip_gi, const int* __restrict__ clip_vx, const int* __restrict__ clip_P_off,
@@ -52,9 +51,9 @@ __global__ void __launch_bounds__(PTR_THREADS) pointer_fwd_kernel(
   const float bp = bpgen[0];
   {
     const long long r = (long long)n * Lt + l;
-    for (int d = threadIdx.x; d < D; d += PTR_THREADS) sdec[d] = ldf(dec + r * D + d);
+    for (int d = threadIdx.x; d < D; d += (int)blockDim.x) sdec[d] = ldf(dec + r * D + d);
     __syncthreads();
-    for (int i = warp; i < ni; i += PTR_THREADS / 32) {
+    for (int i = warp; i < ni; i += ((int)blockDim.x >> 5)) {
       const float* g = G + (long long)(src + i) * D;
       float s = 0.f;
       for (int d = lane; d < D; d += 32) s = fmaf(g[d], sdec[d], s);
@@ -77,7 +76,7 @@ __global__ void __launch_bounds__(PTR_THREADS) pointer_fwd_kernel(
     }
     __syncthreads();
     float pu = 0.f;
-    for (int d = threadIdx.x; d < D; d += PTR_THREADS) {
+    for (int d = threadIdx.x; d < D; d += (int)blockDim.x) {
       float c = 0.f;
       for (int i = 0; i < ni; ++i) c = fmaf(alpha[i], Esrc[(long long)(src + i) * D + d], c);
       sctx[d] = c;
@@ -88,12 +87,12 @@ __global__ void __launch_bounds__(PTR_THREADS) pointer_fwd_kernel(
     if (threadIdx.x == 0) pgen_out[r] = pg;
     const float* lrow = logits + r * ldl;
     float mx = -INFINITY;
-    for (int v = threadIdx.x; v < V; v += PTR_THREADS) mx = fmaxf(mx, lrow[v]);
+    for (int v = threadIdx.x; v < V; v += (int)blockDim.x) mx = fmaxf(mx, lrow[v]);
     mx = block_max(mx, red);
     float se = 0.f;
-    for (int v = threadIdx.x; v < V; v += PTR_THREADS) { const float e = expf(lrow[v] - mx); prow[v] = e; se += e; }
+    for (int v = threadIdx.x; v < V; v += (int)blockDim.x) { const float e = expf(lrow[v] - mx); prow[v] = e; se += e; }
     se = block_sum(se, red);
-    for (int v = threadIdx.x; v < vx; v += PTR_THREADS) prow[v] = v < V ? pg * (prow[v] / se) : 0.f;
+    for (int v = threadIdx.x; v < vx; v += (int)blockDim.x) prow[v] = v < V ? pg * (prow[v] / se) : 0.f;
     __syncthreads();
     if (threadIdx.x == 0) {
       for (int i = 0; i < ni; ++i) {
@@ -106,7 +105,7 @@ __global__ void __launch_bounds__(PTR_THREADS) pointer_fwd_kernel(
     const int label = labels[r];
     const float s = smoothing / (float)(vx - 1), conf = 1.f - smoothing;
     float acc = 0.f;
-    for (int v = threadIdx.x; v < vx; v += PTR_THREADS) {
+    for (int v = threadIdx.x; v < vx; v += (int)blockDim.x) {
       const float p = prow[v];
       P[poff + (long long)l * vx + v] = p;
       if (label >= 0) acc += ls_q(v, label, vx, s, conf) * logf(p + 1e-12f);
@@ -119,7 +118,7 @@ __global__ void __launch_bounds__(PTR_THREADS) pointer_fwd_kernel(
 // Backward, part 1: one CTA per (clip, text position).  Writes d logits, d dec, du (gradient of the p_gen
 // pre-activation) and the score gradients dsc[r][i]; the per-ingredient sums over the clip's positions are part 2.
 template <typename T>
-__global__ void __launch_bounds__(PTR_THREADS) pointer_bwd_kernel(
+__global__ void __launch_bounds__(PG_THREADS) pointer_bwd_kernel(
     int Lt, int D, int V, int max_ni, int max_vx, const T* __restrict__ dec, const float* __restrict__ G,
     const float* __restrict__ Esrc, const int* __restrict__ clip_src_off, const int* __restrict__ clip_ni,
     const int* __restrict__ clip_gi, const int* __restrict__ clip_vx, const int* __restrict__ clip_P_off,
@@ -142,7 +141,7 @@ __global__ void __launch_bounds__(PTR_THREADS) pointer_bwd_kernel(
   const long long poff = clip_P_off[n];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const float gl = dloss[0];
-  for (int i = warp; i < ni; i += PTR_THREADS / 32) {
+  for (int i = warp; i < ni; i += ((int)blockDim.x >> 5)) {
     const float* e = Esrc + (long long)(src + i) * D;
     float s = 0.f;
     for (int d = lane; d < D; d += 32) s = fmaf(wpgen[D + d], e[d], s);
@@ -154,23 +153,23 @@ __global__ void __launch_bounds__(PTR_THREADS) pointer_bwd_kernel(
   const int label = labels[r];
   const float s = smoothing / (float)(vx - 1), conf = 1.f - smoothing;
   const float* lrow = logits + r * ldl;
-  for (int i = threadIdx.x; i < ni; i += PTR_THREADS) alpha[i] = alpha_in[r * max_ni + i];
+  for (int i = threadIdx.x; i < ni; i += (int)blockDim.x) alpha[i] = alpha_in[r * max_ni + i];
   float mx = -INFINITY;
-  for (int v = threadIdx.x; v < V; v += PTR_THREADS) mx = fmaxf(mx, lrow[v]);
+  for (int v = threadIdx.x; v < V; v += (int)blockDim.x) mx = fmaxf(mx, lrow[v]);
   mx = block_max(mx, red);
   float se = 0.f;
-  for (int v = threadIdx.x; v < V; v += PTR_THREADS) se += expf(lrow[v] - mx);
+  for (int v = threadIdx.x; v < V; v += (int)blockDim.x) se += expf(lrow[v] - mx);
   se = block_sum(se, red);
   // gradient w.r.t. the mixed probabilities
   float pa = 0.f;
-  for (int v = threadIdx.x; v < vx; v += PTR_THREADS) {
+  for (int v = threadIdx.x; v < vx; v += (int)blockDim.x) {
     float g = dP ? dP[poff + (long long)l * vx + v] : 0.f;
     if (label >= 0) g -= gl * ls_q(v, label, vx, s, conf) / (P[poff + (long long)l * vx + v] + 1e-12f);
     gP[v] = g;
     if (v < V) pa = fmaf(g, expf(lrow[v] - mx) / se, pa);
   }
   const float A = block_sum(pa, red);      // sum_v gP_v sm_v   (syncs: gP, wE, alpha visible)
-  for (int i = threadIdx.x; i < ni; i += PTR_THREADS) {
+  for (int i = threadIdx.x; i < ni; i += (int)blockDim.x) {
     const int lo = tok_ptr[gi + i], hi = tok_ptr[gi + i + 1];
     float c = 0.f;
     for (int t = lo; t < hi; ++t) c += gP[tok_ids[t]];
@@ -197,9 +196,9 @@ __global__ void __launch_bounds__(PTR_THREADS) pointer_bwd_kernel(
   }
   __syncthreads();
   const float du = s_du;
-  for (int v = threadIdx.x; v < V; v += PTR_THREADS)
+  for (int v = threadIdx.x; v < V; v += (int)blockDim.x)
     dlogits[r * ldl + v] = (expf(lrow[v] - mx) / se) * pg * (gP[v] - A);
-  for (int d = threadIdx.x; d < D; d += PTR_THREADS) {
+  for (int d = threadIdx.x; d < D; d += (int)blockDim.x) {
     float a = du * wpgen[d];
     for (int i = 0; i < ni; ++i) a = fmaf(dsc[i], G[(long long)(src + i) * D + d], a);
     stf(ddec + r * D + d, a);
@@ -262,7 +261,7 @@ extern "C" int svpc_pointer_fwd(int n_clips, int Lt, int D, int V, int max_ni, i
   cudaStream_t st = (cudaStream_t)stream;
   SVPC_DISPATCH(dt, T, {
     cudaFuncSetAttribute(pointer_fwd_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    svpc_launch(pointer_fwd_kernel<T>, dim3(Lt, n_clips), PTR_THREADS, smem, st, Lt, D, V, max_ni, max_vx, (const T*)dec, G, Esrc, clip_src_off,
+    svpc_launch(pointer_fwd_kernel<T>, dim3(Lt, n_clips), ptr_threads(Lt, n_clips), smem, st, Lt, D, V, max_ni, max_vx, (const T*)dec, G, Esrc, clip_src_off,
                                                             clip_ni, clip_gi, clip_vx, clip_P_off, tok_ptr, tok_ids, wpgen,
                                                             bpgen, logits, ldl, labels, smoothing, P, loss_rows, alpha, pgen, ctx);
   });
@@ -286,7 +285,7 @@ extern "C" int svpc_pointer_bwd(int n_clips, int Lt, int D, int V, int max_ni, i
   cudaMemsetAsync(dwpgen, 0, sizeof(float) * 2 * D, st);
   SVPC_DISPATCH(dt, T, {
     cudaFuncSetAttribute(pointer_bwd_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    svpc_launch(pointer_bwd_kernel<T>, dim3(Lt, n_clips), PTR_THREADS, smem, st, 
+    svpc_launch(pointer_bwd_kernel<T>, dim3(Lt, n_clips), ptr_threads(Lt, n_clips), smem, st, 
         Lt, D, V, max_ni, max_vx, (const T*)dec, G, Esrc, clip_src_off, clip_ni, clip_gi, clip_vx, clip_P_off, tok_ptr,
         tok_ids, wpgen, logits, ldl, labels, smoothing, P, alpha, pgen, dP, dloss, (T*)ddec, du, dlogits, dscore_ws);
     cudaFuncSetAttribute(pointer_bwd_reduce_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);

@@ -119,6 +119,16 @@ __device__ __forceinline__ void st8(bf16* p, const float (&v)[8]) {
   for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
   *reinterpret_cast<uint4*>(p) = u;
 }
+__device__ __forceinline__ void st4v(float* p, const float (&v)[4]) {
+  *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+}
+__device__ __forceinline__ void st4v(bf16* p, const float (&v)[4]) {
+  uint2 u;
+  __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
+  h[0] = __floats2bfloat162_rn(v[0], v[1]);
+  h[1] = __floats2bfloat162_rn(v[2], v[3]);
+  *reinterpret_cast<uint2*>(p) = u;
+}
 __device__ __forceinline__ float rnd_as(float v, const float*) { return v; }
 __device__ __forceinline__ float rnd_as(float v, const bf16*) { return __bfloat162float(__float2bfloat16_rn(v)); }
 
@@ -681,8 +691,7 @@ __global__ void __launch_bounds__(RW_THREADS) video_ln_pack_kernel(int n_rows, i
             o[2] *= s0; o[3] *= s1;
           }
         }
-#pragma unroll
-        for (int e = 0; e < 4; ++e) stf(dst + 4 * c + e, o[e]);
+        st4v(dst + 4 * c, o);                // one 8-byte (bf16) / 16-byte (fp32) store per thread (F % 4 == 0)
       }
     }
   }

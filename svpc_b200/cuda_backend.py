@@ -121,6 +121,11 @@ class CudaBackend:
         self._call("svpc_memcpy2d_async", C.c_void_p(dst_ptr), _ll(dpitch), C.c_void_p(src_ptr), _ll(spitch), _ll(width),
                    _ll(height), 1)
 
+    def memcpy2d_d2d(self, dst_ptr, dpitch, src_ptr, spitch, width, height):
+        """Pitched async device -> device copy on the current stream (raw addresses)."""
+        self._call("svpc_memcpy2d_async", C.c_void_p(dst_ptr), _ll(dpitch), C.c_void_p(src_ptr), _ll(spitch), _ll(width),
+                   _ll(height), 3)
+
     def clear_weight_caches(self):
         self._w_cache.clear()
 

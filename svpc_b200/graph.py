@@ -81,6 +81,14 @@ class InputArena:
         for o, pitch, w, h in self.plan:
             be.memcpy2d_h2d(dp + o, pitch or w, hp + o, pitch or w, w, h)
 
+    def commit(self):
+        """device staging arena -> static arena on the CURRENT stream, along the same plan as ``upload``: the rows that are
+        never uploaded are not moved either (40 MB of the 295 MB at the headline configuration)."""
+        be = Fn.be()
+        sp, dp = self.stage.data_ptr(), self.static.data_ptr()
+        for o, pitch, w, h in self.plan:
+            be.memcpy2d_d2d(dp + o, pitch or w, sp + o, pitch or w, w, h)
+
     def _views(self, buf):
         out = []
         for off, shape, dtype in self.spec:
@@ -315,13 +323,15 @@ class _Prefetcher:
         with torch.cuda.stream(self.stream):
             arena.upload()
             self.staged.record(self.stream)
-        self.pairs = [(arena.static, arena.stage)]
+        self.pairs = arena
 
     def commit(self):
         assert self.pairs is not None, "commit() without a staged batch"
         cur = torch.cuda.current_stream(self.device)
         cur.wait_event(self.staged)
-        if len(self.pairs) == 1:
+        if isinstance(self.pairs, InputArena):
+            self.pairs.commit()
+        elif len(self.pairs) == 1:
             self.pairs[0][0].copy_(self.pairs[0][1], non_blocking=True)
         else:
             torch._foreach_copy_([d for d, _ in self.pairs], [b for _, b in self.pairs])
