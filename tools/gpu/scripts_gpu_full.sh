@@ -8,4 +8,4 @@ timeout 900 python bench.py --steps 10 --warmup 3 > gpurun_out/bench.json 2> gpu
 cut -c1-3000 gpurun_out/bench.json
 timeout 600 python bench.py --task decode --steps 5 --warmup 3 > gpurun_out/bench_decode.json 2> gpurun_out/bench_decode.err; echo "decode rc=$?"
 cut -c1-1500 gpurun_out/bench_decode.json
-./scripts_gpu_ncu_list.sh
+./tools/gpu/scripts_gpu_ncu_list.sh

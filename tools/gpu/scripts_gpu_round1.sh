@@ -4,4 +4,4 @@ timeout 1500 python -m pytest tests/test_dropout_gpu.py tests/test_model_gpu.py 
 tail -15 gpurun_out/tests.log
 timeout 600 python bench.py --steps 10 --warmup 3 > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"
 cut -c1-1200 gpurun_out/bench.json
-./scripts_gpu_ncu_list.sh
+./tools/gpu/scripts_gpu_ncu_list.sh
