@@ -53,9 +53,16 @@ class GradAllReducer:
         self._launched[bi] = True
         if not params:
             return
-        flat = torch.cat([p.grad.reshape(-1) for p in params])
+        # one flat bucket, every tensor's slot padded to 16 bytes so that the views handed back as .grad keep the alignment
+        # the vectorised optimiser kernels want; the pad elements are never read
+        offs, total = [], 0
+        for p in params:
+            offs.append(total)
+            total += (p.numel() + 3) // 4 * 4
+        flat = torch.empty(total, dtype=params[0].grad.dtype, device=params[0].grad.device)
+        torch._foreach_copy_([flat[o:o + p.numel()].view_as(p) for o, p in zip(offs, params)], [p.grad for p in params])
         h = dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
-        self._work.append((h, flat, params))
+        self._work.append((h, flat, params, offs))
 
     def finish(self):
         """Call after ``loss.backward()``: reduces the buckets whose parameters did not all get a gradient (same set on
@@ -65,14 +72,12 @@ class GradAllReducer:
         for bi, b in enumerate(self.buckets):
             if not self._launched[bi]:
                 self._launch(bi, [p for p in b if p in self._ready[bi]])
-        for h, flat, params in self._work:
+        for h, flat, params, offs in self._work:
             h.wait()
-            off = 0
-            views = []
-            for p in params:
-                views.append(flat[off:off + p.numel()].view_as(p))
-                off += p.numel()
-            torch._foreach_copy_([p.grad for p in params], views)
+            # the summed gradients stay where the collective left them: every .grad becomes a view of its bucket (no
+            # copy-back pass over the 170 MB; inside a captured step the bucket is a static buffer of the graph's pool)
+            for off, p in zip(offs, params):
+                p.grad = flat[off:off + p.numel()].view_as(p)
         self._work = []
         self._ready = [set() for _ in self.buckets]
         self._launched = [False] * len(self.buckets)
