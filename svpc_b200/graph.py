@@ -16,6 +16,7 @@ by signature, or pad to the configuration maxima.
 from __future__ import annotations
 
 import gc
+import os
 
 import torch
 
@@ -38,6 +39,8 @@ class InputArena:
         """``used_rows``: {index in ``tensors``: r} - of that (B, L, F) tensor only rows [0, r) of every (L, F) block are
         read by the step (video features: the first max_v_len of 125 rows, model.py:889); the upload skips the rest."""
         self.device = device
+        if os.environ.get("SVPC_ARENA_PITCHED", "1") == "0":     # diagnostic: upload whole blocks with 1-D copies
+            used_rows = None
         self.spec, self.plan, self.nbytes = self.layout(tensors, used_rows)
         self.h2d_nbytes = sum(w * h for _, _, w, h in self.plan)
         self.host = torch.empty(self.nbytes, dtype=torch.uint8).pin_memory()

@@ -144,9 +144,10 @@ def test_prefetch_pipeline_matches_load():
     """The host->device input pipeline (copy stream + staging set, GraphedTrainStep.prefetch / run_prefetched) feeds the
     captured step the same inputs as a synchronous load(): alternating two different batches gives each one's own loss."""
     from svpc_b200.graph import GraphedTrainStep
-    cfg, sd, batch, gold = load_case("ragged", "full")
+    # (the full-length case: two ragged batches of different seeds never share a plan signature, and the test would skip)
+    cfg, sd, batch, gold = load_case("full_len", "full")
     m = build(cfg, sd, torch.float32)
-    other = synth.make_batch(cfg, **{**CASES["ragged"][1], "seed": 99})
+    other = synth.make_batch(cfg, **{**CASES["full_len"][1], "seed": 99})
     if m.plan_signature(other["batch_step_num"], other["ingr_id_dict"], other["extra_zeros"]) != \
             m.plan_signature(batch["batch_step_num"], batch["ingr_id_dict"], batch["extra_zeros"]):
         pytest.skip("no second batch with the same signature")
