@@ -187,8 +187,12 @@ int svpc_lstm_step_bwd(int B, int D, int Nc, int Smax, int j, const float* whh_t
 int svpc_transpose_f32(int R, int C, const float* in, float* out, svpc_stream_t stream);
 /* The same recurrence as ONE persistent launch per sweep (all Smax steps): one CTA per SM, half of them per direction,
  * each keeping the W_hh rows of its 10-11 hidden units resident in shared memory; the steps are separated by a barrier
- * among the CTAs of a direction on `sync` (>= 3 uint32, zeroed by the caller; sync[2] is set if a barrier timed out).
- * Arguments as the per-step functions.  Requires ceil(D / (SMs / 2)) <= 12 and (48 + 16) D floats of shared memory. */
+ * among the CTAs of a direction on `sync` (>= 3 uint32: the two arrival counters sync[0..1] are reset by the call itself
+ * (a memset node ahead of the kernel); sync[2] is set if a barrier timed out and is STICKY - only the host clears it, so
+ * one buffer can be polled once per epoch).  Arguments as the per-step functions.  Requires ceil(D / (SMs / 2)) <= 12 and
+ * (48 + 16) D floats of shared memory; svpc_lstm_seq_supported(D) says whether the current device can hold the whole
+ * grid co-resident (occupancy calculator) - when it returns 0 use the per-step functions. */
+int svpc_lstm_seq_supported(int D);
 int svpc_lstm_seq_fwd(int B, int D, int Nc, int Smax, const float* xg, const float* whh, const int* rows, float* hs,
                       float* cs, float* gates, float* out, float* hprev, unsigned int* sync, svpc_stream_t stream);
 int svpc_lstm_seq_bwd(int B, int D, int Nc, int Smax, const float* whh_t, const int* rows, const float* cs,

@@ -131,3 +131,82 @@ def load_translator():
     ds.RecursiveCaptionDataset = RecursiveCaptionDataset
     sys.modules.setdefault("src.rtransformer.recursive_caption_dataset", ds)
     return importlib.import_module("src.translator")
+
+
+# ------------------------------------------------------------------------------------------------
+# train mode with explicit dropout masks
+# ------------------------------------------------------------------------------------------------
+_DROP_SITES = (
+    # (regex on the nn.Dropout module's qualified name, oracle tag template, how successive calls map onto the masks)
+    (r"^ingredient_embeddings\.word_fc\.1$", "ingredient_embeddings", "batch"),
+    (r"^video_embeddings\.video_embeddings\.1$", "video_embeddings", "clip_index"),
+    (r"^encoder\.layer\.(\d+)\.attention\.self\.dropout$", "encoder.layer.{}.attn", "clip_index"),
+    (r"^encoder\.layer\.(\d+)\.attention\.output\.dropout$", "encoder.layer.{}.attn_out", "clip_index"),
+    (r"^encoder\.layer\.(\d+)\.output\.dropout$", "encoder.layer.{}.out", "clip_index"),
+    (r"^step_wise_encoder\.layer\.(\d+)\.attention\.self\.dropout$", "step_wise_encoder.layer.{}.attn", "video"),
+    (r"^step_wise_encoder\.layer\.(\d+)\.attention\.output\.dropout$", "step_wise_encoder.layer.{}.attn_out", "video_rows"),
+    (r"^step_wise_encoder\.layer\.(\d+)\.output\.dropout$", "step_wise_encoder.layer.{}.out", "video_rows"),
+    (r"^text_embeddings\.word_fc\.1$", "text_embeddings", "video_clips"),
+    (r"^decoder\.layer\.(\d+)\.self_attention\.dropout$", "decoder.layer.{}.self_attn", "video_clips"),
+    (r"^decoder\.layer\.(\d+)\.dec_enc_attention\.dropout$", "decoder.layer.{}.cross_attn", "video_clips"),
+    (r"^decoder\.layer\.(\d+)\.output\.dropout$", "decoder.layer.{}.out", "video_clips"),
+    (r"^reasoner\.action_selector\.2$", "reasoner.action_selector", "clip"),
+    (r"^recipe_reasoner\.action_selector\.2$", "recipe_reasoner.action_selector", "clip"),
+)
+
+
+def install_dropout_masks(model, drop, steps):
+    """Replace the forward of every nn.Dropout INSTANCE of the (unmodified) reference model by a multiplication with
+    the matching slice of ``drop`` (an ``oracle.svpc_oracle.DropMasks``).  The reference calls its dropout modules
+    per clip index t over the whole batch (forward_step, model.py:1038-1042), per video (step encoder, decoder,
+    model.py:1059-) or per (video, step) (action selector, model.py:797); ``how`` says which, the call counter of the
+    module says where in that sequence the call is, and the shape of the argument is asserted against the slice.
+    Must be re-installed (fresh counters) before every forward."""
+    import re
+    import torch.nn as nn
+    cu = drop.cu
+    B = len(steps)
+    unused = []
+    for name, mod in model.named_modules():
+        if not isinstance(mod, nn.Dropout):
+            continue
+        hit = None
+        for rx, tag, how in _DROP_SITES:
+            m = re.match(rx, name)
+            if m:
+                hit = (tag.format(*m.groups()), how)
+                break
+        if hit is None:
+            def dead(x, _n=name):
+                raise AssertionError(f"unexpected dropout call at {_n}")
+            mod.forward = dead
+            unused.append(name)
+            continue
+        tag, how = hit
+        state = {"i": 0}
+
+        def fwd(x, tag=tag, how=how, state=state, name=name):
+            i = state["i"]
+            state["i"] += 1
+            t = drop.m.get(tag)
+            if t is None:
+                return x
+            if how == "batch":
+                m = t
+            elif how == "clip_index":          # call i = clip index t, rows = videos; videos with S_b <= t are padding
+                m = torch.ones_like(x)
+                for b in range(B):
+                    if i < steps[b]:
+                        m[b] = t[cu[b] + i]
+            elif how == "video":
+                m = t[i].unsqueeze(0)
+            elif how == "video_rows":
+                m = t[cu[i]:cu[i + 1]].unsqueeze(0)
+            elif how == "video_clips":
+                m = t[cu[i]:cu[i + 1]]
+            else:                               # "clip": one call per (video, step) in video-major order
+                m = t[i]
+            assert tuple(m.shape) == tuple(x.shape), (name, i, tuple(m.shape), tuple(x.shape))
+            return x * m.to(x.dtype)
+        mod.forward = fwd
+    return unused

@@ -45,8 +45,38 @@ def linear(x, sd, prefix):
     return F.linear(x, sd[prefix + ".weight"], sd.get(prefix + ".bias"))
 
 
-def attention(xq, xkv, mask, sd, prefix, n_heads):
-    """BertSelfAttention.forward (model.py:181-220). mask: (N, Lq or 1, Lk) of 0/1. No output projection."""
+class DropMasks:
+    """Train mode with EXPLICIT dropout masks: one scale tensor (0 or 1/(1-p)) per reference nn.Dropout site
+    (model.py:214, 231, 287, 495, 522, 550, 757), in a per-clip / per-video canonical layout, so that a test can hand the
+    oracle exactly the masks the CUDA kernels draw (``svpc_dropout_mask``) - or any other masks.  Keys (Nc = clips in
+    video-major order, n = cu_steps[b] + t):
+      video_embeddings                       (Nc, Lv, F)      model.py:550
+      encoder.layer.l.attn                   (Nc, H, Lv, Lv)  :214      .attn_out / .out  (Nc, Lv, D)  :231 / :287
+      step_wise_encoder.layer.l.attn         list of (H, S_b, S_b)      .attn_out / .out  (Nc, D)
+      ingredient_embeddings                  (B, Li, W)       :522      text_embeddings   (Nc, Lt, W)  :495
+      reasoner.action_selector / recipe_reasoner.action_selector        (Nc, D)           :757
+      decoder.layer.l.self_attn (Nc, H, Lt, Lt)   .cross_attn (Nc, H, Lt, C)   .out (Nc, Lt, D)
+    A missing key means "no dropout at that site"."""
+
+    def __init__(self, masks, cu_steps):
+        self.m, self.cu = masks, list(cu_steps)
+
+    def clips(self, tag, b):
+        t = self.m.get(tag)
+        return None if t is None else t[self.cu[b]:self.cu[b + 1]]
+
+    def video(self, tag, b):
+        t = self.m.get(tag)
+        return None if t is None else t[b]
+
+
+def _dm(x, m):
+    return x if m is None else x * m.to(x.dtype)
+
+
+def attention(xq, xkv, mask, sd, prefix, n_heads, pdrop=None):
+    """BertSelfAttention.forward (model.py:181-220). mask: (N, Lq or 1, Lk) of 0/1. No output projection.
+    ``pdrop``: (N, H, Lq, Lk) dropout scales of the attention probabilities (:214)."""
     N, Lq, D = xq.shape
     Lk = xkv.shape[1]
     dh = D // n_heads
@@ -55,71 +85,75 @@ def attention(xq, xkv, mask, sd, prefix, n_heads):
     k = linear(xkv, sd, prefix + ".key").view(N, Lk, n_heads, dh).permute(0, 2, 1, 3)
     v = linear(xkv, sd, prefix + ".value").view(N, Lk, n_heads, dh).permute(0, 2, 1, 3)
     s = torch.matmul(q, k.transpose(-1, -2)) / math.sqrt(dh) + add
-    p = torch.softmax(s, dim=-1)
+    p = _dm(torch.softmax(s, dim=-1), pdrop)
     ctx = torch.matmul(p, v).permute(0, 2, 1, 3).reshape(N, Lq, D)
     return ctx
 
 
-def encoder_layer(x, key_mask, sd, prefix, n_heads, eps):
-    """BertLayerNoMemoryUntied.forward with diagonal_mask=False (model.py:574-591, 242-253, 262-265, 285-289)."""
-    ctx = attention(x, x, key_mask.unsqueeze(1), sd, prefix + ".attention.self", n_heads)
-    a = layer_norm(linear(ctx, sd, prefix + ".attention.output.dense") + x,
+def encoder_layer(x, key_mask, sd, prefix, n_heads, eps, dm=(None, None, None)):
+    """BertLayerNoMemoryUntied.forward with diagonal_mask=False (model.py:574-591, 242-253, 262-265, 285-289).
+    ``dm``: dropout scales of (attention probabilities, BertSelfOutput.dense output, BertOutput.dense output)."""
+    ctx = attention(x, x, key_mask.unsqueeze(1), sd, prefix + ".attention.self", n_heads, dm[0])
+    a = layer_norm(_dm(linear(ctx, sd, prefix + ".attention.output.dense"), dm[1]) + x,
                    sd[prefix + ".attention.output.LayerNorm.weight"], sd[prefix + ".attention.output.LayerNorm.bias"], eps)
     h = gelu(linear(a, sd, prefix + ".hidden_intermediate.dense"))
-    return layer_norm(linear(h, sd, prefix + ".output.dense") + a,
+    return layer_norm(_dm(linear(h, sd, prefix + ".output.dense"), dm[2]) + a,
                       sd[prefix + ".output.LayerNorm.weight"], sd[prefix + ".output.LayerNorm.bias"], eps)
 
 
-def encoder(x, key_mask, sd, prefix, cfg):
+def encoder(x, key_mask, sd, prefix, cfg, dms=None):
     for l in range(cfg["num_hidden_layers"]):
-        x = encoder_layer(x, key_mask, sd, f"{prefix}.layer.{l}", cfg["num_attention_heads"], cfg["layer_norm_eps"])
+        x = encoder_layer(x, key_mask, sd, f"{prefix}.layer.{l}", cfg["num_attention_heads"], cfg["layer_norm_eps"],
+                          (None, None, None) if dms is None else dms[l])
     return x
 
 
-def decoder_layer(x, dec_mask, ctx, sd, prefix, n_heads, eps):
+def decoder_layer(x, dec_mask, ctx, sd, prefix, n_heads, eps, dm=(None, None, None)):
     """BertDecoderLayerNoMemoryUntied.forward (model.py:630-663): causal+pad self-attention, cross-attention to
-    the context tokens with an all-ones mask (model.py:947), BertOutput with itself as residual."""
+    the context tokens with an all-ones mask (model.py:947), BertOutput with itself as residual.
+    ``dm``: dropout scales of (self-attention probabilities, cross-attention probabilities, BertOutput.dense output)."""
     Lt = x.shape[1]
     m = dec_mask.unsqueeze(1) * torch.tril(dec_mask.new_ones(Lt, Lt))
-    h1 = layer_norm(attention(x, x, m, sd, prefix + ".self_attention", n_heads) + x,
+    h1 = layer_norm(attention(x, x, m, sd, prefix + ".self_attention", n_heads, dm[0]) + x,
                     sd[prefix + ".norm1.weight"], sd[prefix + ".norm1.bias"], eps)
     ones = ctx.new_ones(ctx.shape[0], 1, ctx.shape[1])
-    h2 = layer_norm(h1 + attention(h1, ctx, ones, sd, prefix + ".dec_enc_attention", n_heads),
+    h2 = layer_norm(h1 + attention(h1, ctx, ones, sd, prefix + ".dec_enc_attention", n_heads, dm[1]),
                     sd[prefix + ".norm2.weight"], sd[prefix + ".norm2.bias"], eps)
-    return layer_norm(linear(h2, sd, prefix + ".output.dense") + h2,
+    return layer_norm(_dm(linear(h2, sd, prefix + ".output.dense"), dm[2]) + h2,
                       sd[prefix + ".output.LayerNorm.weight"], sd[prefix + ".output.LayerNorm.bias"], eps)
 
 
-def decoder(x, dec_mask, ctx, sd, cfg):
+def decoder(x, dec_mask, ctx, sd, cfg, dms=None):
     for l in range(cfg["num_hidden_layers"]):
-        x = decoder_layer(x, dec_mask, ctx, sd, f"decoder.layer.{l}", cfg["num_attention_heads"], cfg["layer_norm_eps"])
+        x = decoder_layer(x, dec_mask, ctx, sd, f"decoder.layer.{l}", cfg["num_attention_heads"], cfg["layer_norm_eps"],
+                          (None, None, None) if dms is None else dms[l])
     return x
 
 
 # ------------------------------------------------------------------------------------------------
 # embeddings
 # ------------------------------------------------------------------------------------------------
-def word_fc(ids, sd, prefix, eps):
+def word_fc(ids, sd, prefix, eps, dm=None):
     """Embedding -> LN(W) -> (dropout) -> Linear(W->D) -> ReLU -> LN(D) (model.py:492-499 / 519-526)."""
     e = sd[prefix + ".word_embeddings.weight"][ids]
-    e = layer_norm(e, sd[prefix + ".word_fc.0.weight"], sd[prefix + ".word_fc.0.bias"], eps)
+    e = _dm(layer_norm(e, sd[prefix + ".word_fc.0.weight"], sd[prefix + ".word_fc.0.bias"], eps), dm)
     e = torch.relu(linear(e, sd, prefix + ".word_fc.2"))
     return layer_norm(e, sd[prefix + ".word_fc.4.weight"], sd[prefix + ".word_fc.4.bias"], eps)
 
 
-def text_embed(ids, sd, cfg):
+def text_embed(ids, sd, cfg, dm=None):
     """BertEmbeddingsTextUntied.forward (model.py:509-513): ids (N, Lt)."""
-    x = word_fc(ids, sd, "text_embeddings", cfg["layer_norm_eps"])
+    x = word_fc(ids, sd, "text_embeddings", cfg["layer_norm_eps"], dm)
     return x + sd["text_embeddings.position_embeddings_text.pe"][: ids.shape[1]]
 
 
-def ingredient_vectors(ingr_ids, ingr_sep, sd, cfg):
+def ingredient_vectors(ingr_ids, ingr_sep, sd, cfg, dm=None):
     """BertEmbeddingsIngredientsUntied + IngredientPositionEncoding (model.py:534-537, 116-140) for ONE video.
 
     ingr_ids, ingr_sep: (Li,). Returns (Ni, D): ingredient j = mean of the token vectors strictly between the
     previous [SEP] and its own [SEP] (the SEP itself excluded, model.py:131-133) plus pe[j].
     """
-    x = word_fc(ingr_ids, sd, "ingredient_embeddings", cfg["layer_norm_eps"])
+    x = word_fc(ingr_ids, sd, "ingredient_embeddings", cfg["layer_norm_eps"], dm)
     seps = (ingr_sep == 1).nonzero().view(-1).tolist()
     out, prev = [], 0
     for s in seps:
@@ -129,29 +163,30 @@ def ingredient_vectors(ingr_ids, ingr_sep, sd, cfg):
     return out + sd["ingredient_embeddings.position_embeddings_ingr.pe"][: len(seps)]
 
 
-def video_embed(feats, ids, sd, cfg):
+def video_embed(feats, ids, sd, cfg, dm=None):
     """BertEmbeddingsVideoUntied.forward + token-type add (model.py:558-562, 889-891). feats (N, Lv, F)."""
     eps = cfg["layer_norm_eps"]
     p = "video_embeddings.video_embeddings"
-    x = layer_norm(feats, sd[p + ".0.weight"], sd[p + ".0.bias"], eps)
+    x = _dm(layer_norm(feats, sd[p + ".0.weight"], sd[p + ".0.bias"], eps), dm)
     x = torch.relu(linear(x, sd, p + ".2"))
     x = layer_norm(x, sd[p + ".4.weight"], sd[p + ".4.bias"], eps)
     x = x + sd["video_embeddings.position_embeddings_video.pe"][: feats.shape[1]]
     return x + sd["token_type_embeddings.weight"][ids]
 
 
-def forward_step(ids, feats, masks, sd, cfg):
+def forward_step(ids, feats, masks, sd, cfg, dm=None, dms=None):
     """forward_step (model.py:887-894) for a stack of clips: ids/masks (N, L), feats (N, L, F) -> (N, Lv, D)."""
     Lv = cfg["max_v_len"]
-    x = video_embed(feats[:, :Lv], ids[:, :Lv], sd, cfg)
-    return encoder(x, masks[:, :Lv], sd, "encoder", cfg)
+    x = video_embed(feats[:, :Lv], ids[:, :Lv], sd, cfg, dm)
+    return encoder(x, masks[:, :Lv], sd, "encoder", cfg, dms)
 
 
 # ------------------------------------------------------------------------------------------------
 # visual simulator / textual re-simulator
 # ------------------------------------------------------------------------------------------------
-def reasoner(step_vecs, E0, sd, prefix):
-    """EntitiyReasoningNetwork.forward (model.py:777-823), eval mode. step_vecs (S, D), E0 (Ni, D).
+def reasoner(step_vecs, E0, sd, prefix, dm=None):
+    """EntitiyReasoningNetwork.forward (model.py:777-823). step_vecs (S, D), E0 (Ni, D); ``dm`` (S, D): scales of the
+    nn.Dropout(0.4) inside action_selector (:757), absent = eval mode.
 
     Returns (ent_probs (S,Ni), ac_probs (S,A), ebar (S,D), E_stack (S,Ni,D), fbar (S,W)) - the reference's
     return order (model.py:823)."""
@@ -162,7 +197,8 @@ def reasoner(step_vecs, E0, sd, prefix):
     ent, acs, ebars, Es, fbars = [], [], [], [], []
     for t in range(S):
         v = step_vecs[t]
-        ac = torch.sigmoid(linear(torch.relu(linear(v, sd, prefix + ".action_selector.0")), sd, prefix + ".action_selector.3"))
+        h_as = torch.relu(linear(v, sd, prefix + ".action_selector.0"))
+        ac = torch.sigmoid(linear(_dm(h_as, None if dm is None else dm[t]), sd, prefix + ".action_selector.3"))
         fbar = (ac / ac.sum()).unsqueeze(0) @ A_emb                                   # Eq. 1  (1, W)
         hhat = torch.relu(linear(v, sd, prefix + ".W1.0"))                            # Eq. 2
         e = torch.sigmoid(E @ linear(torch.cat([hhat, ac]), sd, prefix + ".W2"))      # (Ni,)
@@ -243,14 +279,14 @@ def bilstm_sum(x, sd):
     return run("", range(S)) + run("_reverse", range(S - 1, -1, -1))
 
 
-def reconstruct(P, text_mask, E0, g, sd, cfg):
+def reconstruct(P, text_mask, E0, g, sd, cfg, dm=None):
     """reconstruct (model.py:1017-1025): Gumbel-ST word samples -> bag of words per step -> BiLSTM -> recipe_reasoner."""
     V = cfg["vocab_size"]
     y = gumbel_hard(torch.log(P + 1e-12), g, cfg["temperature"])[:, :, :V]
     bow = y @ sd["text_embeddings.word_embeddings.weight"]               # (S,Lt,W)
     m = (text_mask == 1).to(bow.dtype)
     x = (bow * m.unsqueeze(-1)).sum(1) / m.sum(1, keepdim=True)          # masked mean (model.py:1020-1021)
-    return reasoner(bilstm_sum(x, sd), E0, sd, "recipe_reasoner")
+    return reasoner(bilstm_sum(x, sd), E0, sd, "recipe_reasoner", dm)
 
 
 def bce_sum(p, y):
@@ -285,8 +321,9 @@ def _context(mode, step_vecs, E0, ebar, fbar, sd):
     return step_vecs.unsqueeze(1)
 
 
-def forward(sd, cfg, batch, dtype=torch.float32, return_parts=False):
-    """StateAwareRecursiveTransformer.forward (model.py:1027-1189), eval mode (dropout off).
+def forward(sd, cfg, batch, dtype=torch.float32, return_parts=False, drop=None):
+    """StateAwareRecursiveTransformer.forward (model.py:1027-1189); eval mode (dropout off) unless ``drop`` (a
+    ``DropMasks``) supplies the scale tensor of every nn.Dropout site.
 
     ``batch`` is the dict of ``svpc_b200.synth.make_batch`` (the 13 positionals under their reference names plus
     ``gumbel``).  Returns (total_loss, prediction_scores_list, entity_prob_list, action_prob_list) and, with
@@ -299,29 +336,37 @@ def forward(sd, cfg, batch, dtype=torch.float32, return_parts=False):
     parts = dict(caption=0., entity=0., action=0., re_entity=0., re_action=0., cls=[], step_vecs=[], ingr=[],
                  dec=[], re_ent=[], re_ac=[], E_stack=[])
     preds, ents, acts = [], [], []
+    nl = cfg["num_hidden_layers"]
+    dc = (lambda tag, b: None) if drop is None else drop.clips
+    dv = (lambda tag, b: None) if drop is None else drop.video
     for b in range(B):
         S = steps[b]
         ids = _stack_video(batch, b, "input_ids_list", S)
         feats = _stack_video(batch, b, "video_features_list", S).to(dtype)
         masks = _stack_video(batch, b, "input_masks_list", S).to(dtype)
         labels = _stack_video(batch, b, "input_labels_list", S)[:, Lv:].clone()
-        enc = forward_step(ids, feats, masks, sd, cfg)                                   # (S, Lv, D)
+        enc = forward_step(ids, feats, masks, sd, cfg, dc("video_embeddings", b),
+                           [tuple(dc(f"encoder.layer.{l}.{k}", b) for k in ("attn", "attn_out", "out")) for l in range(nl)])
         cls = enc[:, 0, :]                                                               # model.py:1064
         x = (cls + sd["step_positional_encoding.pe"][:S]).unsqueeze(0)
-        step_vecs = encoder(x, x.new_ones(1, S), sd, "step_wise_encoder", cfg)[0]        # (S, D)
+        un = lambda t: None if t is None else t.unsqueeze(0)
+        step_vecs = encoder(x, x.new_ones(1, S), sd, "step_wise_encoder", cfg,
+                            [(un(dv(f"step_wise_encoder.layer.{l}.attn", b)), un(dc(f"step_wise_encoder.layer.{l}.attn_out", b)),
+                              un(dc(f"step_wise_encoder.layer.{l}.out", b))) for l in range(nl)])[0]        # (S, D)
         parts["cls"].append(cls); parts["step_vecs"].append(step_vecs)
         E0 = None
         if mode != "video":
-            E0 = ingredient_vectors(batch["ingr_input_ids"][b], batch["ingr_sep_masks"][b], sd, cfg)
+            E0 = ingredient_vectors(batch["ingr_input_ids"][b], batch["ingr_sep_masks"][b], sd, cfg, dv("ingredient_embeddings", b))
             parts["ingr"].append(E0)
         ebar = fbar = E_stack = None
         if mode in ("full", "reason_copy"):
-            ent_p, ac_p, ebar, E_stack, fbar = reasoner(step_vecs, E0, sd, "reasoner")
+            ent_p, ac_p, ebar, E_stack, fbar = reasoner(step_vecs, E0, sd, "reasoner", dc("reasoner.action_selector", b))
             parts["E_stack"].append(E_stack)
         ctx = _context(mode, step_vecs, E0, ebar, fbar, sd)
         text_ids, text_mask = ids[:, Lv:], masks[:, Lv:]
-        dec = decoder(text_embed(text_ids, sd, cfg), text_mask, ctx, sd, cfg)            # (S, Lt, D)
-        parts["dec"].append(dec)
+        dec = decoder(text_embed(text_ids, sd, cfg, dc("text_embeddings", b)), text_mask, ctx, sd, cfg,
+                      [tuple(dc(f"decoder.layer.{l}.{k}", b) for k in ("self_attn", "cross_attn", "out")) for l in range(nl)])
+        parts["dec"].append(dec)                                                         # (S, Lt, D)
         if mode == "video":
             P = torch.softmax(lm_head(dec, sd, cfg["layer_norm_eps"]), dim=-1)
             labels[labels >= cfg["vocab_size"]] = cfg["unk_id"]                          # model.py:1013
@@ -338,7 +383,8 @@ def forward(sd, cfg, batch, dtype=torch.float32, return_parts=False):
             parts["action"] = parts["action"] + asymmetric_loss(ac_p[rows], y_ac[rows])
             ents.append(ent_p); acts.append(ac_p)
             if mode == "full":
-                re_ent, re_ac, _, _, _ = reconstruct(P, text_mask, E0, batch["gumbel"][b].to(dtype), sd, cfg)
+                re_ent, re_ac, _, _, _ = reconstruct(P, text_mask, E0, batch["gumbel"][b].to(dtype), sd, cfg,
+                                                     dc("recipe_reasoner.action_selector", b))
                 parts["re_entity"] = parts["re_entity"] + bce_sum(re_ent, y_al)
                 parts["re_action"] = parts["re_action"] + asymmetric_loss(re_ac[rows], y_ac[rows])
                 parts["re_ent"].append(re_ent); parts["re_ac"].append(re_ac)
@@ -348,11 +394,11 @@ def forward(sd, cfg, batch, dtype=torch.float32, return_parts=False):
     return total, preds, ents, acts
 
 
-def loss_and_grads(sd, cfg, batch, dtype=torch.float32):
+def loss_and_grads(sd, cfg, batch, dtype=torch.float32, drop=None):
     """fwd+bwd: returns (loss, parts, {param name: grad or None})."""
     leaf = {k: (v.to(dtype).clone().requires_grad_(True) if v.is_floating_point() and not k.endswith(".pe") else v)
             for k, v in sd.items()}
-    total, preds, ents, acts, parts = forward(leaf, cfg, batch, dtype=dtype, return_parts=True)
+    total, preds, ents, acts, parts = forward(leaf, cfg, batch, dtype=dtype, return_parts=True, drop=drop)
     total.backward()
     grads = {k: v.grad for k, v in leaf.items() if v.is_floating_point() and not k.endswith(".pe")}
     # padding_idx=0 rows of both word-embedding tables receive no gradient (model.py:492,519)

@@ -116,8 +116,9 @@ class StepPositionalEncoding(Node):
 class Encoder(Node):
     """BertEncoderNoMemoryUntied (reference model.py:594-617): ``encoder`` (clips) and ``step_wise_encoder``."""
 
-    def forward(self, hidden_states, attention_mask, output_all_encoded_layers=True):
+    def forward(self, hidden_states, attention_mask, diagonal_mask=False, output_all_encoded_layers=True):
         m = self.owner
+        assert not diagonal_mask, "the clip / step encoders are never causal (reference model.py:893, 1065)"
         N, L, D = hidden_states.shape
         prefix = "step_wise_encoder" if self is getattr(m, "step_wise_encoder", None) else "encoder"
         dev = hidden_states.device

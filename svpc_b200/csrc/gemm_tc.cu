@@ -4,20 +4,22 @@
 // (the M / N index contiguous: dgrad uses W as an MN-major B, wgrad uses dY and X as MN-major A and B), so no
 // transposed copies of weights or activations are ever materialised.
 //
-// Structure: PERSISTENT kernel, one CTA of 192 threads per SM, walking a list of work units (128 x BN tiles, BN <= 256;
+// Structure: PERSISTENT kernel, one CTA of 320 threads (10 warps) per SM, walking a list of work units (128 x BN tiles, BN <= 256;
 // split-K slices for weight gradients; narrower column slices for the tiles of the last partial round):
 //   warp 0      TMA producer: cp.async.bulk.tensor 2D boxes, 128B swizzle, into a 4-deep shared-memory ring
 //               (A 16 KB + B up to 32 KB per stage), completion on mbarriers (expect_tx); runs ahead across units
 //   warp 1      MMA issuer: one elected lane issues tcgen05.mma.cta_group::1.kind::f16 (UMMA 128 x width x 16) from
 //               shared-memory descriptors into one of TWO 256-column TMEM accumulators; tcgen05.commit releases ring
 //               slots / signals the epilogue
-//   warps 2-5   epilogue: tcgen05.ld (32 lanes x 32 columns per warp) -> smem transposition -> bias / activation /
-//               dropout / residual -> row-contiguous global stores, overlapped with the next unit's main loop;
-//               warp 2 also owns the TMEM allocation
+//   warps 2-9   epilogue (two warps per TMEM lane quarter, alternating 32-column chunks): tcgen05.ld (32 lanes x 32
+//               columns) -> per-warp 32 x 32 fp32 XOR-swizzled smem transposition buffer -> bias / activation / dropout /
+//               residual -> row-contiguous global stores, overlapped with the next unit's main loop; warp 2 also owns
+//               the TMEM allocation
 // Split-K with fp32 red.global.add.v4 for weight-gradient shapes whose output has too few tiles to fill 148 SMs.
 #include "common.cuh"
 #include <cuda.h>
 #include <stdlib.h>
+#include <mutex>
 
 #define TC_BM 128
 #define TC_BK 64                 // 64 bf16 = 128 B = one swizzle row
@@ -168,7 +170,6 @@ struct TcParams {
   int main_tiles;          // tiles handled whole (x split); the remaining `tiles - main_tiles` are cut along N
   int tail_s;              // ... into tail_s sub-tiles of width BN / tail_s each, so the last round is short
   int total_units;
-  int dbg;                 // diagnostics only (SVPC_TC_DBG): bit0 no TMEM load, bit1 no epilogue math/stores, bit2 no staging, bit3 no chunk loop
 };
 
 struct TcUnit { int m0, n0, width, kb0, kb1; };
@@ -312,8 +313,8 @@ __device__ __forceinline__ void epi_atomic(const TcParams& p, uint32_t stage, in
   }
 }
 
-// Persistent kernel, one CTA per SM.  Shared memory: TC_STAGES x (A 128x64 + B 256x64) bf16 ring (48 KB per stage),
-// a 4 x 32 x 36 fp32 transposition buffer for the epilogue warps, barriers.  TMEM: 2 accumulators of 256 fp32 columns
+// Persistent kernel, one CTA per SM.  Shared memory: TC_STAGES (4) x (A 128x64 + B 256x64) bf16 ring (48 KB per stage),
+// one 32 x 32 fp32 transposition buffer per epilogue warp (8 x 4 KB), barriers.  TMEM: 2 accumulators of 256 fp32 columns
 // (all 512 columns), so the epilogue of unit i drains one while the MMAs of unit i+1 fill the other.
 // ACT / DROP: the epilogue is specialised at compile time (a runtime switch over activations inside the row loop made
 // the epilogue, not the MMAs, the bottleneck of the K = 768 GEMMs).
@@ -447,24 +448,15 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
       const uint32_t trow = tmem_base + acc * TC_BN_MAX + ((uint32_t)(q * 32) << 16);
 #pragma unroll 1
       for (int c = half; c < nchunks; c += CSTEP) {
-        if (p.dbg & 8) break;
         {
           uint32_t v[32];
-          if (!(p.dbg & 1)) {
-            tmem_ld32(trow + (uint32_t)(c * 32), v);
-            tmem_ld_wait();
-          } else {
+          tmem_ld32(trow + (uint32_t)(c * 32), v);
+          tmem_ld_wait();
 #pragma unroll
-            for (int jj = 0; jj < 32; ++jj) v[jj] = 0u;
-          }
-          if (!(p.dbg & 4)) {
-#pragma unroll
-            for (int jj = 0; jj < 8; ++jj)
-              sts128(stage + epi_slot(lane, jj), v[4 * jj], v[4 * jj + 1], v[4 * jj + 2], v[4 * jj + 3]);
-          }
+          for (int jj = 0; jj < 8; ++jj)
+            sts128(stage + epi_slot(lane, jj), v[4 * jj], v[4 * jj + 1], v[4 * jj + 2], v[4 * jj + 3]);
         }
         __syncwarp();
-        if (p.dbg & 2) continue;
         const int nb = w.n0 + c * 32;
         const int n = nb + g * 4;
         if (n < p.N && mw < p.M) {
@@ -508,9 +500,29 @@ static PFN_encodeTiled get_encode() {
   return fn;
 }
 
+// Encoded tensor maps are cached (direct-mapped, keyed on every argument of the encoding): on the eager / ragged path the
+// same few hundred operand geometries recur every step and cuTensorMapEncodeTiled costs ~1 us of host time per call.
+struct MapKey { const void* base; long long inner, outer, ld; int bi, bo; };
+struct MapSlot { MapKey k; CUtensorMap m; bool used; };
+#define TC_MAP_SLOTS 2048
+static MapSlot* map_cache() {
+  static MapSlot* c = (MapSlot*)calloc(TC_MAP_SLOTS, sizeof(MapSlot));
+  return c;
+}
+
 // 2-D bf16 tensor map: inner (contiguous) extent `inner`, outer extent `outer`, outer stride `ld` elements
 static int make_map(CUtensorMap* m, const void* base, long long inner, long long outer, long long ld, int box_inner,
                     int box_outer) {
+  MapKey key;
+  memset(&key, 0, sizeof(key));
+  key.base = base; key.inner = inner; key.outer = outer; key.ld = ld; key.bi = box_inner; key.bo = box_outer;
+  unsigned long long h = (unsigned long long)(uintptr_t)base * 0x9E3779B97F4A7C15ull ^ (unsigned long long)inner * 0xC2B2AE3D27D4EB4Full ^
+                         (unsigned long long)outer * 0x165667B19E3779F9ull ^ (unsigned long long)ld * 0x27D4EB2F165667C5ull ^
+                         (unsigned long long)(box_inner * 131 + box_outer);
+  static std::mutex mu;
+  std::lock_guard<std::mutex> lock(mu);
+  MapSlot* slot = map_cache() ? map_cache() + ((h >> 20) % TC_MAP_SLOTS) : nullptr;
+  if (slot && slot->used && memcmp(&slot->k, &key, sizeof(key)) == 0) { *m = slot->m; return SVPC_OK; }
   PFN_encodeTiled enc = get_encode();
   if (!enc) { svpc_set_error("cuTensorMapEncodeTiled not available"); return SVPC_ERR_CUDA; }
   cuuint64_t dims[2] = {(cuuint64_t)inner, (cuuint64_t)outer};
@@ -521,6 +533,7 @@ static int make_map(CUtensorMap* m, const void* base, long long inner, long long
                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) { svpc_set_error("cuTensorMapEncodeTiled failed (%d)", (int)r); return SVPC_ERR_CUDA; }
+  if (slot) { slot->k = key; slot->m = *m; slot->used = true; }
   return SVPC_OK;
 }
 
@@ -627,8 +640,7 @@ int svpc_gemm_tc_launch(int M, int N, int K, const void* A, long long sa_m, long
   }
   const int total_units = main_tiles * split + (tiles - main_tiles) * tail_s;
   TcParams p{M, N, K, D, ldd, bias, act, residual, ldr, pre, ldp, accumulate, split > 1 ? 1 : 0, drop,
-             BN, tiles_n, split, kb_per, kb_total, main_tiles, tail_s, total_units, 0};
-  if (const char* e = getenv("SVPC_TC_DBG")) p.dbg = atoi(e);
+             BN, tiles_n, split, kb_per, kb_total, main_tiles, tail_s, total_units};
   if (split > 1 && !accumulate) {
     cudaError_t e = cudaMemset2DAsync(D, (size_t)ldd * 4, 0, (size_t)N * 4, (size_t)M, st);
     if (e != cudaSuccess) { svpc_set_error("gemm_tc: memset2D: %s", cudaGetErrorString(e)); return SVPC_ERR_CUDA; }

@@ -443,30 +443,64 @@ __global__ void __launch_bounds__(LSTM_PW * 32, 1) lstm_seq_bwd_kernel(const Lst
   }
 }
 
-static int lstm_seq_launch(bool bwd, LstmSeqParams& q, cudaStream_t st) {
-  const LstmStepParams& p = q.s;
-  SVPC_REQUIRE(p.D % 4 == 0, "lstm_seq: hidden size %d must be a multiple of 4", p.D);
-  SVPC_REQUIRE(q.sync != nullptr, "lstm_seq: needs the zeroed barrier counters");
-  if (p.B <= 0 || p.Nc <= 0 || p.Smax <= 0) return SVPC_OK;
-  static int sms = 0;
-  if (!sms) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  }
-  q.cpd = sms / 2;
-  SVPC_REQUIRE(q.cpd >= 1 && (p.D + q.cpd - 1) / q.cpd <= LSTM_PW,
-               "lstm_seq: %d hidden units over %d CTAs per direction exceed %d units per CTA", p.D, q.cpd, LSTM_PW);
-  const size_t tail = (size_t)LSTM_BV * p.D > (size_t)2 * LSTM_PW * LSTM_PW * LSTM_BB ? (size_t)LSTM_BV * p.D
-                                                                                  : (size_t)2 * LSTM_PW * LSTM_PW * LSTM_BB;
-  const size_t smem = ((size_t)LSTM_PW * 4 * p.D + tail) * sizeof(float);   // fwd: h staging; bwd: reduction buffers
-  SVPC_REQUIRE(smem <= 227 * 1024, "lstm_seq: hidden size %d needs %zu bytes of shared memory", p.D, smem);
+// SM count of the CURRENT device (cached per device ordinal)
+static int lstm_device_sms() {
+  static int sms[64] = {0};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64) dev = 0;
+  if (!sms[dev]) cudaDeviceGetAttribute(&sms[dev], cudaDevAttrMultiProcessorCount, dev);
+  return sms[dev];
+}
+
+static size_t lstm_seq_smem(int D) {
+  const size_t tail = (size_t)LSTM_BV * D > (size_t)2 * LSTM_PW * LSTM_PW * LSTM_BB ? (size_t)LSTM_BV * D
+                                                                                : (size_t)2 * LSTM_PW * LSTM_PW * LSTM_BB;
+  return ((size_t)LSTM_PW * 4 * D + tail) * sizeof(float);   // fwd: h staging; bwd: reduction buffers
+}
+
+static void lstm_seq_attrs() {
   static bool attr = false;
   if (!attr) {
     cudaFuncSetAttribute(lstm_seq_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     cudaFuncSetAttribute(lstm_seq_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     attr = true;
   }
+}
+
+// The persistent sweep synchronises its CTAs through global counters, so the whole grid (2 x sms/2 CTAs of one per SM)
+// must be co-resident: 1 when the hidden size fits the per-CTA slice, the shared memory fits, and the occupancy
+// calculator gives both kernels at least one CTA per SM on this device; 0 -> the caller uses the per-step kernels.
+extern "C" int svpc_lstm_seq_supported(int D) {
+  const int sms = lstm_device_sms();
+  const int cpd = sms / 2;
+  if (D <= 0 || D % 4 != 0 || cpd < 1 || (D + cpd - 1) / cpd > LSTM_PW) return 0;
+  const size_t smem = lstm_seq_smem(D);
+  if (smem > 227 * 1024) return 0;
+  lstm_seq_attrs();
+  int nf = 0, nb = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nf, lstm_seq_fwd_kernel, LSTM_PW * 32, smem) != cudaSuccess ||
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, lstm_seq_bwd_kernel, LSTM_PW * 32, smem) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return (nf >= 1 && nb >= 1) ? 1 : 0;
+}
+
+static int lstm_seq_launch(bool bwd, LstmSeqParams& q, cudaStream_t st) {
+  const LstmStepParams& p = q.s;
+  SVPC_REQUIRE(p.D % 4 == 0, "lstm_seq: hidden size %d must be a multiple of 4", p.D);
+  SVPC_REQUIRE(q.sync != nullptr, "lstm_seq: needs the barrier counters");
+  if (p.B <= 0 || p.Nc <= 0 || p.Smax <= 0) return SVPC_OK;
+  q.cpd = lstm_device_sms() / 2;
+  SVPC_REQUIRE(q.cpd >= 1 && (p.D + q.cpd - 1) / q.cpd <= LSTM_PW,
+               "lstm_seq: %d hidden units over %d CTAs per direction exceed %d units per CTA", p.D, q.cpd, LSTM_PW);
+  const size_t smem = lstm_seq_smem(p.D);
+  SVPC_REQUIRE(smem <= 227 * 1024, "lstm_seq: hidden size %d needs %zu bytes of shared memory", p.D, smem);
+  lstm_seq_attrs();
+  // the two arrival counters start at zero for every sweep; sync[2] (barrier time-out) is STICKY: only the host clears it
+  cudaError_t e = cudaMemsetAsync(q.sync, 0, 2 * sizeof(unsigned int), st);
+  if (e != cudaSuccess) { svpc_set_error("lstm_seq: memset: %s", cudaGetErrorString(e)); return SVPC_ERR_CUDA; }
   if (bwd) svpc_launch(lstm_seq_bwd_kernel, 2 * q.cpd, LSTM_PW * 32, smem, st, q);
   else svpc_launch(lstm_seq_fwd_kernel, 2 * q.cpd, LSTM_PW * 32, smem, st, q);
   return svpc_check_launch(bwd ? "lstm_seq_bwd" : "lstm_seq_fwd");

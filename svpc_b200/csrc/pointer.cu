@@ -116,117 +116,6 @@ __global__ void __launch_bounds__(PG_THREADS) pointer_fwd_kernel(
   }
 }
 
-// Warp-per-row form of pointer_fwd_kernel (SVPC_PTR_WARP=1, D <= 32 * PW_DK): a CTA takes PW_ROWS consecutive text positions
-// of ONE clip, stages that clip's W_ing E and E once in shared memory (the row-per-CTA kernel re-reads both from L2 for
-// every row: 61 KB x 4800 rows per step) and every warp walks one row with its decoder vector and context in registers
-// and warp-level reductions only - no block barrier after the staging.
-#define PW_ROWS 8
-#define PW_DK 24
-template <typename T>
-__global__ void __launch_bounds__(PW_ROWS * 32) pointer_fwd_warp_kernel(
-    int Lt, int D, int V, int max_ni, int max_vx, const T* __restrict__ dec, const float* __restrict__ G,
-    const float* __restrict__ Esrc, const int* __restrict__ clip_src_off, const int* __restrict__ clip_ni,
-    const int* __restrict__ clip_gi, const int* __restrict__ clip_vx, const int* __restrict__ clip_P_off,
-    const int* __restrict__ tok_ptr, const int* __restrict__ tok_ids, const float* __restrict__ wpgen,
-    const float* __restrict__ bpgen, const float* __restrict__ logits, long long ldl, const int* __restrict__ labels,
-    float smoothing, float* __restrict__ P, float* __restrict__ loss_rows, float* __restrict__ alpha_out,
-    float* __restrict__ pgen_out, float* __restrict__ ctx_out) {
-  svpc_pdl_sync();
-  extern __shared__ float sm[];
-  float* sG = sm;                                   // max_ni x D
-  float* sE = sG + (size_t)max_ni * D;              // max_ni x D
-  float* wbase = sE + (size_t)max_ni * D;           // per warp: prow[max_vx], alpha[max_ni]
-  const int n = blockIdx.y;
-  const int src = clip_src_off[n], ni = clip_ni[n], gi = clip_gi[n], vx = clip_vx[n];
-  const long long poff = clip_P_off[n];
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  for (int e = threadIdx.x * 4; e < ni * D; e += PW_ROWS * 32 * 4) {
-    *reinterpret_cast<float4*>(sG + e) = __ldg(reinterpret_cast<const float4*>(G + (long long)src * D + e));
-    *reinterpret_cast<float4*>(sE + e) = __ldg(reinterpret_cast<const float4*>(Esrc + (long long)src * D + e));
-  }
-  __syncthreads();
-  const int l = blockIdx.x * PW_ROWS + warp;
-  if (l >= Lt) return;
-  float* prow = wbase + (size_t)warp * (max_vx + max_ni);
-  float* alpha = prow + max_vx;
-  const long long r = (long long)n * Lt + l;
-  float dv[PW_DK];
-#pragma unroll
-  for (int k = 0; k < PW_DK; ++k) dv[k] = (lane + 32 * k < D) ? ldf(dec + r * D + lane + 32 * k) : 0.f;
-  // scores over the ingredients, softmax over the INGREDIENT axis (model.py:899-900)
-  float mx = -INFINITY;
-  for (int i = 0; i < ni; ++i) {
-    const float* g = sG + (size_t)i * D;
-    float sc = 0.f;
-#pragma unroll
-    for (int k = 0; k < PW_DK; ++k)
-      if (lane + 32 * k < D) sc = fmaf(g[lane + 32 * k], dv[k], sc);
-    sc = warp_sum(sc);
-    if (lane == 0) alpha[i] = sc;
-    mx = fmaxf(mx, sc);
-  }
-  __syncwarp();
-  float sum = 0.f;
-  for (int i = lane; i < ni; i += 32) { const float e = expf(alpha[i] - mx); alpha[i] = e; sum += e; }
-  sum = warp_sum(sum);
-  for (int i = lane; i < ni; i += 32) {
-    const float a = alpha[i] / sum;
-    alpha[i] = a;
-    alpha_out[r * max_ni + i] = a;
-  }
-  __syncwarp();
-  // context and p_gen (model.py:901-904)
-  float cv[PW_DK];
-#pragma unroll
-  for (int k = 0; k < PW_DK; ++k) cv[k] = 0.f;
-  for (int i = 0; i < ni; ++i) {
-    const float a = alpha[i];
-    const float* e = sE + (size_t)i * D;
-#pragma unroll
-    for (int k = 0; k < PW_DK; ++k)
-      if (lane + 32 * k < D) cv[k] = fmaf(a, e[lane + 32 * k], cv[k]);
-  }
-  float pu = 0.f;
-#pragma unroll
-  for (int k = 0; k < PW_DK; ++k) {
-    const int d = lane + 32 * k;
-    if (d < D) {
-      ctx_out[r * D + d] = cv[k];
-      pu += dv[k] * wpgen[d] + cv[k] * wpgen[D + d];
-    }
-  }
-  const float pg = svpc_sigmoid(warp_sum(pu) + bpgen[0]);
-  if (lane == 0) pgen_out[r] = pg;
-  // vocabulary softmax, p_gen mixing, copy mass (model.py:906-922)
-  const float* lrow = logits + r * ldl;
-  float lm = -INFINITY;
-  for (int v = lane; v < V; v += 32) lm = fmaxf(lm, lrow[v]);
-  lm = warp_max(lm);
-  float se = 0.f;
-  for (int v = lane; v < V; v += 32) { const float e = expf(lrow[v] - lm); prow[v] = e; se += e; }
-  se = warp_sum(se);
-  for (int v = lane; v < vx; v += 32) prow[v] = v < V ? pg * (prow[v] / se) : 0.f;
-  __syncwarp();
-  if (lane == 0) {
-    for (int i = 0; i < ni; ++i) {
-      const int lo = tok_ptr[gi + i], hi = tok_ptr[gi + i + 1];
-      const float add = alpha[i] * (1.f - pg) / (float)(hi - lo);
-      for (int t = lo; t < hi; ++t) prow[tok_ids[t]] += add;
-    }
-  }
-  __syncwarp();
-  const int label = labels[r];
-  const float s = smoothing / (float)(vx - 1), conf = 1.f - smoothing;
-  float acc = 0.f;
-  for (int v = lane; v < vx; v += 32) {
-    const float pv = prow[v];
-    P[poff + (long long)l * vx + v] = pv;
-    if (label >= 0) acc += ls_q(v, label, vx, s, conf) * logf(pv + 1e-12f);
-  }
-  acc = warp_sum(acc);
-  if (lane == 0) loss_rows[r] = label >= 0 ? ls_const(label, vx, s, conf) - acc : 0.f;
-}
-
 // Backward, part 1: one CTA per (clip, text position).  Writes d logits, d dec, du (gradient of the p_gen
 // pre-activation) and the score gradients dsc[r][i]; the per-ingredient sums over the clip's positions are part 2.
 template <typename T>
@@ -371,22 +260,6 @@ extern "C" int svpc_pointer_fwd(int n_clips, int Lt, int D, int V, int max_ni, i
   const size_t smem = sizeof(float) * (2 * (size_t)D + max_vx + max_ni);
   SVPC_REQUIRE(smem <= 200 * 1024, "pointer_fwd: shared memory");
   cudaStream_t st = (cudaStream_t)stream;
-  static int warp_rows = -1;
-  if (warp_rows < 0) {
-    const char* ev = getenv("SVPC_PTR_WARP");
-    warp_rows = ev ? atoi(ev) : 0;                  // 1: when there are enough rows to fill the GPU; 2: always (tests)
-  }
-  const size_t smem_w = sizeof(float) * (2 * (size_t)max_ni * D + (size_t)PW_ROWS * (max_vx + max_ni));
-  if (warp_rows && D % 4 == 0 && D <= 32 * PW_DK && smem_w <= 200 * 1024 &&
-      (warp_rows >= 2 || (long long)Lt * n_clips >= 8 * SVPC_NUM_SMS)) {
-    SVPC_DISPATCH(dt, T, {
-      cudaFuncSetAttribute(pointer_fwd_warp_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_w);
-      svpc_launch(pointer_fwd_warp_kernel<T>, dim3(svpc_cdiv(Lt, PW_ROWS), n_clips), PW_ROWS * 32, smem_w, st, Lt, D, V, max_ni, max_vx,
-                  (const T*)dec, G, Esrc, clip_src_off, clip_ni, clip_gi, clip_vx, clip_P_off, tok_ptr, tok_ids, wpgen, bpgen,
-                  logits, ldl, labels, smoothing, P, loss_rows, alpha, pgen, ctx);
-    });
-    return svpc_check_launch("pointer_fwd");
-  }
   SVPC_DISPATCH(dt, T, {
     cudaFuncSetAttribute(pointer_fwd_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     svpc_launch(pointer_fwd_kernel<T>, dim3(Lt, n_clips), ptr_threads(Lt, n_clips), smem, st, Lt, D, V, max_ni, max_vx, (const T*)dec, G, Esrc, clip_src_off,

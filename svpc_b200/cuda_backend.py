@@ -5,7 +5,6 @@ a missing library or a non-CUDA tensor raises.
 """
 from __future__ import annotations
 
-import collections
 import ctypes as C
 import os
 
@@ -77,7 +76,8 @@ class CudaBackend:
         self.timing = None
         # BiLSTM recurrence: one persistent launch per sweep (default) or one launch per time step (SVPC_LSTM_STEPS=1)
         self.lstm_persistent = os.environ.get("SVPC_LSTM_STEPS", "0") != "1"
-        self.lstm_sync_flags = collections.deque(maxlen=8)       # barrier counters of recent sweeps ([2] = time-out flag)
+        self._lstm_sync = {}          # device -> (2, 4) int32: barrier counters of the fwd / bwd sweep, [:, 2] = sticky time-out flag
+        self._lstm_ok = {}            # (device, D) -> the persistent sweep fits co-resident on that device
 
     # ------------------------------------------------------------------ plumbing
     def _call(self, fn, *args, tag=None):
@@ -577,6 +577,38 @@ class CudaBackend:
     # ------------------------------------------------------------------ recipe encoder (BiLSTM)
     _lstm_rows = {}
 
+    def lstm_sync(self, device):
+        """Barrier counters of the persistent BiLSTM sweeps on ``device`` (row 0 forward, row 1 backward).  Column 2 is the
+        time-out flag: set by a sweep whose grid barrier gave up (results of that step are wrong), never cleared by the
+        kernels.  ``check_lstm_timeout`` reads it."""
+        t = self._lstm_sync.get(device)
+        if t is None:
+            t = self._lstm_sync[device] = torch.zeros(2, 4, dtype=torch.int32, device=device)
+        return t
+
+    def check_lstm_timeout(self, flags=None):
+        """Raise if a persistent BiLSTM sweep timed out at a grid barrier since the last check (synchronises unless
+        ``flags``, a host copy of ``lstm_sync(device)``, is given)."""
+        for dev, t in list(self._lstm_sync.items()):
+            f = t if flags is None else flags
+            if int(f[:, 2].sum()) != 0:
+                t[:, 2].zero_()
+                raise SvpcError("persistent BiLSTM sweep: a grid barrier timed out (the CTAs of a direction were not "
+                                "co-resident - MPS / MIG SM limits or a concurrent kernel); the recurrent states of that step "
+                                "are invalid.  Set SVPC_LSTM_STEPS=1 to use the per-step kernels.")
+            if flags is not None:
+                break
+
+    def _lstm_use_seq(self, device, D):
+        if not self.lstm_persistent:
+            return False
+        key = (device, int(D))
+        ok = self._lstm_ok.get(key)
+        if ok is None:
+            with torch.cuda.device(device):
+                ok = self._lstm_ok[key] = bool(self.lib.svpc_lstm_seq_supported(int(D)))
+        return ok
+
     def _lstm_row_table(self, steps, device):
         key = (tuple(steps), str(device))
         t = self._lstm_rows.get(key)
@@ -650,12 +682,10 @@ class CudaBackend:
         cs = torch.empty(2, Nc, D, dtype=f32, device=dev)
         hprev = torch.empty(2, Nc, D, dtype=f32, device=dev)
         gates = torch.empty(2, Nc, 4 * D, dtype=f32, device=dev)
-        if self.lstm_persistent:
+        if self._lstm_use_seq(dev, D):
             # one launch for the whole sweep: W_hh slices resident in shared memory, per-direction grid barrier per step
-            sync = torch.zeros(4, dtype=torch.int32, device=dev)
             self._call("svpc_lstm_seq_fwd", B, D, Nc, Smax, _ptr(xg), _ptr(whh), _ptr(rows), _ptr(hs), _ptr(cs),
-                       _ptr(gates), _ptr(out), _ptr(hprev), _ptr(sync))
-            self.lstm_sync_flags.append(sync)
+                       _ptr(gates), _ptr(out), _ptr(hprev), _ptr(self.lstm_sync(dev)[0]))
         else:
             for j in range(Smax):
                 self._call("svpc_lstm_step_fwd", B, D, Nc, Smax, j, _ptr(xg), _ptr(whh), _ptr(rows), _ptr(hs), _ptr(cs),
@@ -673,11 +703,9 @@ class CudaBackend:
         whh_t = self._lstm_whh(params, True)
         dgates = torch.empty(2, Nc, 4 * D, dtype=f32, device=dev)
         dc = torch.zeros(2, B, D, dtype=f32, device=dev)
-        if self.lstm_persistent:
-            sync = torch.zeros(4, dtype=torch.int32, device=dev)
+        if self._lstm_use_seq(dev, D):
             self._call("svpc_lstm_seq_bwd", B, D, Nc, Smax, _ptr(whh_t), _ptr(rows), _ptr(cs), _ptr(gates), _ptr(dout),
-                       _ptr(dgates), _ptr(dc), _ptr(sync))
-            self.lstm_sync_flags.append(sync)
+                       _ptr(dgates), _ptr(dc), _ptr(self.lstm_sync(dev)[1]))
         else:
             for j in range(Smax - 1, -1, -1):
                 self._call("svpc_lstm_step_bwd", B, D, Nc, Smax, j, _ptr(whh_t), _ptr(rows), _ptr(cs), _ptr(gates),

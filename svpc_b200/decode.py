@@ -41,13 +41,14 @@ def greedy_decode(model, model_inputs, plan=None):
     H, nl = cfg.num_attention_heads, cfg.num_hidden_layers
     dev = video_features_list[0].device
     be = Fn.be()
+    Fn.WEIGHTS.refresh_all()      # weight copies touched by an optimiser step / EMA swap: rewritten in place, one launch
     f32, i32 = torch.float32, torch.int32
     steps = [int(s) for s in batch_step_num]
     B = len(steps)
     if mode == "video":
         ni, n_oov, dicts = [0] * B, [0] * B, [{} for _ in range(B)]
     else:
-        ni = [len(d) for d in ingr_id_dict]
+        ni = model.ingredient_counts(ingr_sep_masks, ingr_id_dict)
         n_oov = [len(d) for d in oov_word_dict]
         dicts = ingr_id_dict
     if plan is None:

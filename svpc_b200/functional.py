@@ -6,6 +6,8 @@ host: every tensor operation on activations is a backend (CUDA) call.
 """
 from __future__ import annotations
 
+import weakref
+
 import torch
 from torch.autograd import Function
 
@@ -31,12 +33,25 @@ class WeightCache:
     CHUNK = 16384
 
     def __init__(self):
-        self.store = {}          # key -> [version tuple or None, tensor, params, dtype]
+        self.store = {}          # key -> [version tuple or None, tensor, weak refs to the params, dtype]
         self._tables = {}        # (dtype, keys of the stale set) -> device tables of the multi-tensor launch
 
     @staticmethod
     def _version(ws):
         return tuple(w._version for w in ws) + tuple(w.data_ptr() for w in ws)
+
+    @staticmethod
+    def _params(e):
+        """The entry's parameters, or None when one of them no longer exists."""
+        ws = [r() for r in e[2]]
+        return None if any(w is None for w in ws) else ws
+
+    def _purge(self):
+        dead = [k for k, e in self.store.items() if self._params(e) is None]
+        for k in dead:
+            del self.store[k]
+        if dead:
+            self._tables.clear()
 
     def get(self, ws, dtype):
         if len(ws) == 1 and ws[0].dtype == dtype and ws[0].is_contiguous():
@@ -44,12 +59,21 @@ class WeightCache:
         key = tuple(id(w) for w in ws) + (dtype,)
         ver = self._version(ws)
         hit = self.store.get(key)
-        if hit is not None and hit[0] == ver:
+        if hit is not None and hit[0] == ver and self._params(hit) is not None:
             return hit[1]
         with torch.no_grad():
             parts = [be().cast(w.detach().contiguous(), dtype) for w in ws]
             t = parts[0] if len(parts) == 1 else torch.cat(parts, dim=0)
-        self.store[key] = [ver, t, list(ws), dtype]
+        if hit is not None and self._params(hit) is not None and hit[1].shape == t.shape and hit[1].device == t.device \
+                and hit[1].stride() == t.stride():
+            # stale entry of the same parameters (optimiser step, EMA swap, a decode between two replays): rewrite the
+            # EXISTING buffer - a captured CUDA graph holds its address (cast_multi of refresh_all, every GEMM operand)
+            with torch.no_grad():
+                hit[1].copy_(t)
+            hit[0] = ver
+            return hit[1]
+        self._purge()            # a first sight / reshaped / moved key: also forget entries of parameters that are gone
+        self.store[key] = [ver, t, [weakref.ref(w) for w in ws], dtype]
         return t
 
     def invalidate(self):
@@ -63,23 +87,28 @@ class WeightCache:
 
     def refresh_all(self, launch=True):
         """One launch per compute dtype for all entries whose parameters changed since they were cast."""
-        stale = [(k, e) for k, e in self.store.items()
-                 if e[0] != self._version(e[2]) and all(w.is_cuda and w.dtype == torch.float32 and w.dim() <= 2 and
-                                                        w.is_contiguous() for w in e[2])]
+        stale = []
+        for k, e in self.store.items():
+            ws = self._params(e)
+            if ws is None or e[0] == self._version(ws):
+                continue
+            if all(w.is_cuda and w.dtype == torch.float32 and w.dim() <= 2 and w.is_contiguous() for w in ws) and \
+                    e[1].device == ws[0].device:
+                stale.append((k, e, ws))
         if not stale or not hasattr(be(), "cast_multi"):
             return
-        for dtype in {e[3] for _, e in stale}:
-            group = [(k, e) for k, e in stale if e[3] == dtype]
-            tkey = (dtype,) + tuple(k for k, _ in group) + tuple(w.data_ptr() for _, e in group for w in e[2])
+        for dtype in {e[3] for _, e, _ in stale}:
+            group = [(k, e, ws) for k, e, ws in stale if e[3] == dtype]
+            tkey = (dtype,) + tuple(k for k, _, _ in group) + tuple(w.data_ptr() for _, _, ws in group for w in ws)
             tab = self._tables.get(tkey)
             if tab is None:
                 if len(self._tables) > 16:
                     self._tables.clear()
                 srcs, dsts, numel, cols, lds = [], [], [], [], []
-                for _, e in group:
+                for _, e, ws in group:
                     t, off = e[1], 0                      # off: element offset of the next part inside the entry's buffer
                     esz = t.element_size()
-                    for w in e[2]:
+                    for w in ws:
                         c = w.shape[1] if (w.dim() == 2 and t.dim() == 2) else w.numel()
                         ld = t.stride(0) if (w.dim() == 2 and t.dim() == 2) else c
                         srcs.append(w.data_ptr())
@@ -89,11 +118,15 @@ class WeightCache:
                         lds.append(ld)
                         off += w.shape[0] * t.stride(0) if (w.dim() == 2 and t.dim() == 2) else w.numel()
                 tab = self._tables[tkey] = be().cast_multi_tables(srcs, dsts, numel, cols, lds, self.CHUNK,
-                                                                   group[0][1][2][0].device)
+                                                                   group[0][2][0].device)
             if launch:
                 be().cast_multi(tab, dtype, self.CHUNK)
-                for _, e in group:
-                    e[0] = self._version(e[2])
+                for _, e, ws in group:
+                    e[0] = self._version(ws)
+
+    def buffers(self):
+        """Every cached tensor (a captured graph keeps them alive: it reads and rewrites their addresses)."""
+        return [e[1] for e in self.store.values()]
 
     def clear(self):
         self.store.clear()

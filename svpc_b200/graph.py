@@ -176,6 +176,8 @@ class GraphedTrainStep:
         with torch.cuda.graph(self.graph):
             self.loss = self._eager(zero=False)
         torch.cuda.synchronize(dev)
+        # the graph reads (GEMM operands) and rewrites (the captured weight refresh) the cached weight copies by address
+        self._weight_buffers = Fn.WEIGHTS.buffers() + list(Fn.be()._w_cache.values())
 
     def _clone(self, a):
         if isinstance(a, torch.Tensor):
@@ -259,13 +261,19 @@ class GraphedTrainStep:
         ring = getattr(self, "_loss_ring", None)
         if ring is None:
             ring = self._loss_ring = {"buf": torch.zeros(4, dtype=torch.float32).pin_memory(), "i": 0,
-                                      "ev": [torch.cuda.Event() for _ in range(4)]}
+                                      "ev": [torch.cuda.Event() for _ in range(4)],
+                                      "flags": torch.zeros(4, 2, 4, dtype=torch.int32).pin_memory()}
         i = ring["i"]
         ring["i"] = (i + 1) % 4
         slot, ev = ring["buf"][i:i + 1], ring["ev"][i]
         slot.copy_(self.loss.detach().reshape(1), non_blocking=True)
+        flags = None
+        if self.model.config.model_mode == "full":
+            # the persistent BiLSTM sweeps' barrier time-out flag travels with the loss: a time-out means wrong states
+            flags = ring["flags"][i]
+            flags.copy_(Fn.be().lstm_sync(self.device), non_blocking=True)
         ev.record(torch.cuda.current_stream(self.device))
-        return _HostScalar(slot, ev)
+        return _HostScalar(slot, ev, flags)
 
     def run_prefetched(self):
         self._pf.commit()
@@ -278,11 +286,13 @@ class GraphedTrainStep:
 
 
 class _HostScalar:
-    def __init__(self, slot, event):
-        self.slot, self.event = slot, event
+    def __init__(self, slot, event, lstm_flags=None):
+        self.slot, self.event, self.lstm_flags = slot, event, lstm_flags
 
     def get(self) -> float:
         self.event.synchronize()
+        if self.lstm_flags is not None and int(self.lstm_flags[:, 2].sum()) != 0:
+            Fn.be().check_lstm_timeout(self.lstm_flags)
         return float(self.slot[0])
 
 
@@ -374,7 +384,7 @@ class GraphedDecoder:
         if mode == "video":
             ni, n_oov, dicts = [0] * B, [0] * B, [{} for _ in range(B)]
         else:
-            ni, n_oov, dicts = [len(d) for d in st[7]], [len(d) for d in st[8]], st[7]
+            ni, n_oov, dicts = model.ingredient_counts(example_inputs[6], st[7]), [len(d) for d in st[8]], st[7]
         self.plan = model.make_plan_raw(steps, ni, n_oov, dicts, dev)
         self.sig = (tuple(steps), tuple(ni), tuple(n_oov))
         self.graph = torch.cuda.CUDAGraph()
@@ -421,22 +431,6 @@ class GraphedDecoder:
             pairs.append((self.static[i], torch.as_tensor(inputs[i])))
         self._pf.stage(pairs)
         self._pf_dict = inputs[7]
-
-    def loss_to_host(self):
-        """Asynchronous D2H read of the step that was just enqueued: copies the loss into the next slot of a small pinned
-        ring and returns a handle whose ``get()`` waits for that copy only.  Lets a training loop enqueue step i+1 before
-        it looks at the loss of step i (the static loss buffer is overwritten by the next replay), so the device never
-        waits for the host between steps."""
-        ring = getattr(self, "_loss_ring", None)
-        if ring is None:
-            ring = self._loss_ring = {"buf": torch.zeros(4, dtype=torch.float32).pin_memory(), "i": 0,
-                                      "ev": [torch.cuda.Event() for _ in range(4)]}
-        i = ring["i"]
-        ring["i"] = (i + 1) % 4
-        slot, ev = ring["buf"][i:i + 1], ring["ev"][i]
-        slot.copy_(self.loss.detach().reshape(1), non_blocking=True)
-        ev.record(torch.cuda.current_stream(self.device))
-        return _HostScalar(slot, ev)
 
     def run_prefetched(self):
         self._pf.commit()

@@ -95,6 +95,7 @@ class StepPlan:
             host = host.pin_memory()
         dev = host.to(device, non_blocking=True)
         self._host, self._dev, self._spans = host, dev, spans
+        self._ring, self._ring_i = None, 0       # update_tokens: pinned copies of `host`, each guarded by a CUDA event
         self.t = {k: dev[o:o + n] for k, (o, n) in spans.items()}
         t = self.t
         self.max_ni = max(ni) if ni else 0
@@ -113,6 +114,10 @@ class StepPlan:
         if self.mode != "video":
             for b in range(self.B):
                 d = ingr_id_dict[b]
+                bad = [k for k in d if not (0 <= int(k) < self.ni[b])]
+                if bad:
+                    raise ValueError(f"ingr_id_dict[{b}] has ingredient indices {sorted(bad)} but the video has "
+                                     f"{self.ni[b]} [SEP]-terminated ingredients (reference model.py:1067)")
                 for i in range(self.ni[b]):
                     ids = list(d.get(i, []))
                     for t in ids:
@@ -127,17 +132,29 @@ class StepPlan:
         return (tuple(self.steps), tuple(self.ni), tuple(self.vx), self._spans["tok_ids"][1])
 
     def update_tokens(self, ingr_id_dict):
-        """Refresh the copy CSR in place (same lengths): used when a captured step is replayed on a new batch."""
+        """Refresh the copy CSR in place (same lengths): used when a captured step is replayed on a new batch.  The
+        upload is asynchronous and the host may run several steps ahead (prefetch / run_prefetched / loss_to_host), so
+        every call writes its own pinned slot of a small ring and waits only for the copy that last used that slot."""
         tok_ptr, tok_ids = self._tok_csr(ingr_id_dict)
         if not tok_ids:
             tok_ids = [0]
         o, n = self._spans["tok_ids"]
         if len(tok_ids) != n:
             return False
-        self._host[o:o + n] = torch.tensor(tok_ids, dtype=torch.int32)
+        if self._dev.device.type != "cuda":
+            src = self._host
+        else:
+            if self._ring is None:
+                self._ring = [(self._host.clone().pin_memory(), torch.cuda.Event()) for _ in range(4)]
+            src, ev = self._ring[self._ring_i]
+            self._ring_i = (self._ring_i + 1) % len(self._ring)
+            ev.synchronize()                       # no-op unless the copy issued 4 updates ago is still pending
+        src[o:o + n] = torch.tensor(tok_ids, dtype=torch.int32)
         o2, n2 = self._spans["tok_ptr"]
-        self._host[o2:o2 + n2] = torch.tensor(tok_ptr, dtype=torch.int32)
-        self._dev.copy_(self._host, non_blocking=True)
+        src[o2:o2 + n2] = torch.tensor(tok_ptr, dtype=torch.int32)
+        self._dev.copy_(src, non_blocking=True)
+        if self._dev.device.type == "cuda":
+            ev.record(torch.cuda.current_stream(self._dev.device))
         return True
 
     def cross_lay(self, C, device, D):
@@ -194,6 +211,7 @@ class StateAwareRecursiveTransformer(nn.Module):
             node.register_parameter(leaf, nn.Parameter(t))
         self._pcache = {}
         self.last_parts = {}
+        self.drop_sites = []
         self._seed_t, self._site = None, 0      # train-mode dropout: device step seed (bumped per forward), site counter
 
     # ---- parameter lookup by reference key
@@ -212,9 +230,12 @@ class StateAwareRecursiveTransformer(nn.Module):
         return r
 
     def _invalidate(self):
-        """Parameters were moved / replaced: drop the name -> tensor cache and the compute-dtype weight copies."""
+        """Parameters were moved / replaced: drop the name -> tensor cache and mark the compute-dtype weight copies stale.
+        Their buffers are NOT freed here: another model's captured graph may be reading them (the cache is keyed by
+        parameter identity and version + address, so a moved parameter misses by itself; entries of parameters that no
+        longer exist are purged on the next miss)."""
         self._pcache = {}
-        Fn.WEIGHTS.clear()
+        Fn.WEIGHTS.invalidate()
 
     def _load_from_state_dict(self, state_dict, prefix, *args, **kwargs):
         # a reference checkpoint saved without set_pretrained_embedding holds `reasoner.action_embeddings.weight`
@@ -232,17 +253,21 @@ class StateAwareRecursiveTransformer(nn.Module):
         """Train mode: new dropout masks for this forward (the seed lives on the device so that a captured graph draws
         fresh masks on every replay)."""
         self._site = 0
+        self.drop_sites = []
         if self.training:
             if self._seed_t is None or self._seed_t.device != device:
                 self._seed_t = torch.randint(1, 2 ** 30, (1,), dtype=torch.int32, device=device)
             else:
                 self._seed_t += 1
 
-    def _drop(self, p):
-        """(seed, site, p) for one nn.Dropout site of the reference, or None in eval mode / p == 0."""
+    def _drop(self, p, tag=None):
+        """(seed, site, p) for one nn.Dropout site of the reference, or None in eval mode / p == 0.  ``tag`` names the
+        reference module the site belongs to; (site, tag, p) of the current forward are kept in ``self.drop_sites`` so that
+        a test can rebuild every mask with ``svpc_dropout_mask`` and hand it to the oracle."""
         if not self.training or p <= 0.0 or self._seed_t is None:
             return None
         self._site += 1
+        self.drop_sites.append((self._site, tag, float(p)))
         return (self._seed_t, self._site, float(p))
 
     def _lin(self, x, prefix, **kw):
@@ -264,18 +289,19 @@ class StateAwareRecursiveTransformer(nn.Module):
         if cls_lay is None:
             qkv = self._qkv(x, ap + ".self", ("query", "key", "value"))
             ctx = Fn.attention(qkv, None, (0, D, 2 * D), lay, key_mask, False, Hh, cd,
-                               drop=self._drop(cfg.attention_probs_dropout_prob))
+                               drop=self._drop(cfg.attention_probs_dropout_prob, prefix + ".attn"))
             res = x
         else:
             kv = self._qkv(x, ap + ".self", ("key", "value"))
             res = x[::cls_stride].contiguous()
             q = self._lin(res, ap + ".self.query")
             ctx = Fn.attention(q, kv, (0, 0, D), cls_lay, key_mask, False, Hh, cd,
-                               drop=self._drop(cfg.attention_probs_dropout_prob))
+                               drop=self._drop(cfg.attention_probs_dropout_prob, prefix + ".attn"))
         ph = cfg.hidden_dropout_prob
-        a = self._ln(self._lin(ctx, ap + ".output.dense", residual=res, drop=self._drop(ph)), None, ap + ".output.LayerNorm")
+        a = self._ln(self._lin(ctx, ap + ".output.dense", residual=res, drop=self._drop(ph, prefix + ".attn_out")), None,
+                     ap + ".output.LayerNorm")
         h = self._lin(a, prefix + ".hidden_intermediate.dense", act=ACT_GELU)
-        return self._ln(self._lin(h, prefix + ".output.dense", residual=a, drop=self._drop(ph)), None,
+        return self._ln(self._lin(h, prefix + ".output.dense", residual=a, drop=self._drop(ph, prefix + ".out")), None,
                         prefix + ".output.LayerNorm")
 
     def _video_embed(self, feats_list, plan, vid_ids):
@@ -284,7 +310,7 @@ class StateAwareRecursiveTransformer(nn.Module):
         in the compute dtype, and the 90 GFLOP input-gradient GEMM is not needed for gamma / beta."""
         cfg = self.config
         pfx = "video_embeddings.video_embeddings"
-        drop = self._drop(cfg.hidden_dropout_prob)
+        drop = self._drop(cfg.hidden_dropout_prob, "video_embeddings")
         if drop is not None:
             # train mode: dropout sits between LN(3072) and the projection (model.py:549-551), so the affine cannot be
             # folded into the weights; the normalised, scaled and dropped features are staged once in the compute dtype
@@ -308,7 +334,7 @@ class StateAwareRecursiveTransformer(nn.Module):
         pfx = which + ".word_fc"
         e = Fn.EmbedLNFn.apply(self.p(which + ".word_embeddings.weight"), ids, self.p(pfx + ".0.weight"),
                                self.p(pfx + ".0.bias"), cfg.layer_norm_eps, self.compute_dtype, PAD,
-                               self._drop(cfg.hidden_dropout_prob))
+                               self._drop(cfg.hidden_dropout_prob, which))
         z = self._lin(e, pfx + ".2", act=ACT_RELU)
         return self._ln(z, None, pfx + ".4", pe=pe, pe_period=pe_period)
 
@@ -316,7 +342,8 @@ class StateAwareRecursiveTransformer(nn.Module):
         """EntitiyReasoningNetwork.forward (reference model.py:777-823): everything that depends only on the step
         vector is batched over all clips; the entity-state recurrence is one sequential kernel per video."""
         f32 = torch.float32
-        h_as = self._lin(V, prefix + ".action_selector.0", act=ACT_RELU, drop=self._drop(0.4))     # nn.Dropout(p=0.4), model.py:757
+        h_as = self._lin(V, prefix + ".action_selector.0", act=ACT_RELU,
+                       drop=self._drop(0.4, prefix + ".action_selector"))                                # nn.Dropout(p=0.4), model.py:757
         ac = self._lin(h_as, prefix + ".action_selector.3", act=ACT_SIGMOID, out_dtype=f32)            # (Nc, A)
         fbar = Fn.linear(Fn.RowNormalizeFn.apply(ac), self.p(prefix + ".action_embeddings"), None, cd=self.compute_dtype,
                          out_dtype=f32, w_is_kn=True)                                                     # (Nc, W)  Eq. 1
@@ -338,14 +365,15 @@ class StateAwareRecursiveTransformer(nn.Module):
             pfx = f"decoder.layer.{l}"
             qkv = self._qkv(x, pfx + ".self_attention", ("query", "key", "value"))
             pa = cfg.attention_probs_dropout_prob
-            sa = Fn.attention(qkv, None, (0, D, 2 * D), plan.dec_lay, text_mask, True, Hh, cd, drop=self._drop(pa))
+            sa = Fn.attention(qkv, None, (0, D, 2 * D), plan.dec_lay, text_mask, True, Hh, cd,
+                              drop=self._drop(pa, pfx + ".self_attn"))
             h1 = self._ln(sa, x, pfx + ".norm1")
             q2 = self._lin(h1, pfx + ".dec_enc_attention.query")
             kv2 = self._qkv(ctx, pfx + ".dec_enc_attention", ("key", "value"))
-            ca = Fn.attention(q2, kv2, (0, 0, D), cross, None, False, Hh, cd, drop=self._drop(pa))
+            ca = Fn.attention(q2, kv2, (0, 0, D), cross, None, False, Hh, cd, drop=self._drop(pa, pfx + ".cross_attn"))
             h2 = self._ln(ca, h1, pfx + ".norm2")
-            x = self._ln(self._lin(h2, pfx + ".output.dense", residual=h2, drop=self._drop(cfg.hidden_dropout_prob)), None,
-                         pfx + ".output.LayerNorm")
+            x = self._ln(self._lin(h2, pfx + ".output.dense", residual=h2,
+                                   drop=self._drop(cfg.hidden_dropout_prob, pfx + ".out")), None, pfx + ".output.LayerNorm")
         return x
 
     def _lm_logits(self, dec):
@@ -405,10 +433,22 @@ class StateAwareRecursiveTransformer(nn.Module):
         if mode == "video":
             ni, ez, dct = [0] * B, [0] * B, None
         else:
-            ni = [len(ingr_id_dict[b]) for b in range(B)]
+            ni = self.ingredient_counts(getattr(self, "_sep_counts", None), ingr_id_dict)
             ez = [int(z) for z in extra_zeros]
             dct = ingr_id_dict
         return StepPlan(self.config, steps, ni, ez, dct, device, mode)
+
+    @staticmethod
+    def ingredient_counts(ingr_sep_masks, ingr_id_dict):
+        """Ingredients per video.  The reference counts the [SEP]s of the ingredient row, (ingr_sep_masks[b] == 1).sum()
+        (model.py:1067); with a host-resident mask (lists, CPU tensors - what the loader and the translator hold) that
+        count is used, so an ingredient that tokenises to nothing (a key missing from ingr_id_dict) still has its row.
+        With a device tensor the count would need a device->host sync per step: the dictionary length is used, and
+        StepPlan checks that every key fits."""
+        if ingr_sep_masks is not None and not (isinstance(ingr_sep_masks, torch.Tensor) and ingr_sep_masks.is_cuda):
+            t = torch.as_tensor(ingr_sep_masks)
+            return [int(x) for x in (t == 1).sum(dim=-1).tolist()]
+        return [len(d) for d in ingr_id_dict]
 
     def make_plan_raw(self, steps, ni, extra_zeros, ingr_id_dict, device):
         """StepPlan from explicit per-video counts (piecewise callers: svpc_b200.compat, svpc_b200.decode)."""
@@ -478,7 +518,9 @@ class StateAwareRecursiveTransformer(nn.Module):
         self._begin_step(dev)
         Fn.WEIGHTS.refresh_all()          # compute-dtype weight copies touched by the optimiser: one multi-tensor cast
         if plan is None:
+            self._sep_counts = ingr_sep_masks if mode != "video" else None
             plan = self.make_plan(batch_step_num, ingr_id_dict, extra_zeros, alignments, dev)
+            self._sep_counts = None
         B, Nc = plan.B, plan.Nc
 
         Vst, cls, ids, masks = self._encode_clips(input_ids_list, video_features_list, input_masks_list, plan)

@@ -37,3 +37,34 @@ def test_no_torch_types_in_the_abi():
     src = open(os.path.join(ROOT, "include", "svpc_b200.h")).read()
     assert "at::" not in src and "torch" not in re.sub(r"/\*.*?\*/", "", src, flags=re.S)
     assert ctypes.sizeof(ctypes.c_void_p) == 8
+
+
+def test_integration_stub_matches_header():
+    """The ctypes stub INTEGRATION.md shows for svpc_gemm passes exactly as many arguments as the header declares (a
+    maintainer pasting a stale stub would hand the stream where the dropout seed pointer belongs)."""
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    hdr = open(os.path.join(root, "include", "svpc_b200.h")).read()
+    decl = re.search(r"int svpc_gemm\((.*?)\);", hdr, re.S).group(1)
+    n_decl = len([a for a in decl.split(",") if a.strip()])
+    doc = open(os.path.join(root, "INTEGRATION.md")).read()
+    call = doc[doc.index("lib.svpc_gemm(") + len("lib.svpc_gemm("):]
+    depth, end = 1, 0
+    for end, ch in enumerate(call):
+        depth += ch == "("
+        depth -= ch == ")"
+        if depth == 0:
+            break
+    body = re.sub(r"#[^\n]*", "", call[:end])
+    args, depth, cur = [], 0, ""
+    for ch in body:
+        if ch == "," and depth == 0:
+            args.append(cur)
+            cur = ""
+            continue
+        depth += ch in "(["
+        depth -= ch in ")]"
+        cur += ch
+    args.append(cur)
+    n_stub = len([a for a in args if a.strip()])
+    assert n_stub == n_decl, (n_stub, n_decl)

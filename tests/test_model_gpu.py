@@ -187,3 +187,73 @@ def test_prefetch_pipeline_matches_load():
         step.prefetch(a_args, a_noise)
         v = float(step.run_prefetched())
         assert abs(v - want[which]) <= 1e-6 * abs(want[which]), (which, v, want)
+
+
+def test_graph_survives_optimizer_step_and_decode():
+    """replay -> optimiser step -> greedy decode -> replay: the decode sees stale cached weight copies (the optimiser
+    bumped the parameter versions); they must be refreshed IN PLACE, because the captured graph reads and rewrites them by
+    address.  The second replay must equal an eager step on the updated weights."""
+    from svpc_b200.graph import GraphedTrainStep
+    from svpc_b200.decode import greedy_decode
+    from svpc_b200 import optim as SO
+    from svpc_b200 import functional as Fn
+    from tests.test_decode_host import decode_inputs
+    cfg, sd, batch, gold = load_case("ragged", "full")
+    m = build(cfg, sd, torch.bfloat16)
+    noise = [g.to(DEV) for g in batch["gumbel"]]
+    step = GraphedTrainStep(m, forward_args(batch, DEV), gumbel_noise=noise)
+    l0 = float(step.run())
+    ptrs0 = sorted(t.data_ptr() for t in Fn.WEIGHTS.buffers())
+    opt = SO.BertAdam([p for p in m.parameters() if p.requires_grad], lr=5e-3, warmup=-1, t_total=-1, schedule="warmup_constant")
+    opt.step()
+    with torch.no_grad():
+        greedy_decode(m, decode_inputs(batch, DEV))            # stale hits on the decoder / LM-head weights
+    assert sorted(t.data_ptr() for t in Fn.WEIGHTS.buffers()) == ptrs0, "a cached weight copy was re-allocated"
+    # a second model moved to the device must not free the first model's cached copies either
+    m2 = build(cfg, sd, torch.bfloat16)
+    float(m2(*forward_args(batch, DEV), gumbel_noise=noise)[0])
+    l1 = float(step.run())
+    torch.cuda.synchronize()
+    g1 = {n: p.grad.detach().clone() for n, p in m.named_parameters() if p.grad is not None}
+    assert abs(l1 - l0) > 1e-4 * abs(l0), "the optimiser step did not change the loss"
+    m.zero_grad(set_to_none=True)
+    le = m(*forward_args(batch, DEV), gumbel_noise=noise)[0]
+    le.backward()
+    torch.cuda.synchronize()
+    assert abs(l1 - float(le)) <= 1e-5 * abs(float(le)), (l1, float(le))
+    gscale = max(float(g.abs().max()) for g in g1.values())
+    for n, p in m.named_parameters():
+        if n in g1:
+            err = float((p.grad - g1[n]).abs().max())
+            assert err <= 1e-4 * max(float(g1[n].abs().max()), 1e-3 * gscale), (n, err)
+
+
+def test_token_csr_updates_do_not_race_the_upload():
+    """Several different ingr_id_dicts in flight without any host synchronisation: every replay must scatter the copy mass
+    with ITS batch's token ids (StepPlan.update_tokens writes a ring of pinned buffers guarded by events)."""
+    from svpc_b200.graph import GraphedTrainStep
+    cfg, sd, batch, gold = load_case("full_len", "full")
+    m = build(cfg, sd, torch.float32)
+    step = GraphedTrainStep(m, forward_args(batch, DEV), gumbel_noise=[g.to(DEV) for g in batch["gumbel"]])
+    V = cfg.vocab_size
+    dicts = []
+    for k in range(6):                        # same lengths, different token ids
+        dicts.append([{i: [7 + (t + 3 * k + i) % (V - 7) for t in ids] for i, ids in d.items()} for d in batch["ingr_id_dict"]])
+    args = forward_args(batch, DEV)
+    want = []
+    for d in dicts:                           # synchronous statement
+        a = list(args)
+        a[9] = d
+        step.load(a, batch["gumbel"])
+        want.append(float(step.run()))
+        torch.cuda.synchronize()
+    assert len({round(w, 3) for w in want}) > 1
+    losses = []
+    for d in dicts:                           # asynchronous: the host runs ahead of the device
+        a = list(args)
+        a[9] = d
+        step.load(a, batch["gumbel"])
+        losses.append(step.run().detach().clone())
+    torch.cuda.synchronize()
+    for w, l in zip(want, losses):
+        assert abs(float(l) - w) <= 1e-6 * abs(w), (float(l), w)

@@ -422,16 +422,16 @@ def test_bilstm_many_videos(cb, tb, persistent, cd):
         params[key] = (torch.rand(*shape, generator=torch.Generator().manual_seed(i)) * 2 * k - k).to(DEV)
     was = cb.lstm_persistent
     cb.lstm_persistent = persistent
-    cb.lstm_sync_flags.clear()
+    cb.check_lstm_timeout()
     try:
         out, saved = cb.bilstm_fwd(x, cu, steps, params, cd=cd)
         dout = rnd(Nc, D, seed=5)
         dx, grads = cb.bilstm_bwd(dout, x, cu, steps, params, saved, cd=cd)
     finally:
         cb.lstm_persistent = was
-    assert len(cb.lstm_sync_flags) == (2 if persistent else 0)
-    for f in cb.lstm_sync_flags:
-        assert int(f[2]) == 0, "a grid barrier of the persistent LSTM timed out"
+    if persistent:
+        assert cb._lstm_use_seq(x.device, D), "the persistent sweep must fit co-resident on a whole B200"
+    cb.check_lstm_timeout()          # raises if a grid barrier of the persistent sweep timed out
     rout, _ = tb.bilstm_fwd(x, cu, steps, params)
     rdx, rgrads = tb.bilstm_bwd(dout, x, cu, steps, params, ())
     tol = 1e-4 if cd == torch.float32 else 2e-2
@@ -439,6 +439,16 @@ def test_bilstm_many_videos(cb, tb, persistent, cd):
     close("bilstm dx", dx, rdx, tol)
     for key in TorchBackend.LSTM_KEYS:
         close("bilstm d" + key, grads[key], rgrads[key], tol)
+
+
+def test_lstm_timeout_flag_is_reported(cb):
+    """A barrier time-out of the persistent sweep (sticky flag, column 2 of the barrier buffer) raises at the next check."""
+    from svpc_b200.cuda_backend import SvpcError
+    cb.check_lstm_timeout()
+    cb.lstm_sync(DEV)[1, 2] = 1
+    with pytest.raises(SvpcError):
+        cb.check_lstm_timeout()
+    cb.check_lstm_timeout()          # cleared by the failed check
 
 
 def test_losses(cb, tb):
