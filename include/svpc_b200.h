@@ -59,7 +59,9 @@ int svpc_dropout_mask(long long n, const unsigned int* drop_seed, unsigned int d
 /* D[M,N] = drop(act(A[M,K] . B[N,K]^T + bias[N])) + residual[M,N]  (+ D when accumulate); optional copy of the
  * pre-activation.  Dropout element index = m * N + n.  A and B are addressed by element strides (one of each pair must be 1).  Replaces every
  * nn.Linear / matmul on the path: model.py:195-197,230,263,286,496,551,706-708,738,797-811,899,939-940 and their
- * autograd dgrad / wgrad. */
+ * autograd dgrad / wgrad.  gref != NULL (dtype of D, row pitch ldg): the result is finally multiplied by gact'(gref[m,n])
+ * - an input-gradient GEMM then writes the gradient of the PREVIOUS Linear's pre-activation directly (gref = that
+ * pre-activation for GELU, its output for RELU / SIGMOID), residual = the gradient arriving over a skip connection. */
 int svpc_gemm(int M, int N, int K,
               const void* A, int dtA, long long sa_m, long long sa_k,
               const void* B, int dtB, long long sb_n, long long sb_k,
@@ -68,7 +70,27 @@ int svpc_gemm(int M, int N, int K,
               const void* residual, long long ldr,
               void* pre, long long ldp,
               int accumulate, int route,
-              const unsigned int* drop_seed, unsigned int drop_site, float drop_p, svpc_stream_t stream);
+              const unsigned int* drop_seed, unsigned int drop_site, float drop_p,
+              const void* gref, long long ldg, int gact, svpc_stream_t stream);
+
+/* The same contraction for fp32 operands on the tensor cores (the 1e-4 parity path of model.py:195-197, 230, 263, 286, 551,
+ * 706-708, 738): every fp32 operand is split into two bf16 planes, x = hi + lo with hi = bf16(x), lo = bf16(x - hi)
+ * (svpc_split_bf16, row pitch `ldd` elements, a multiple of 8), and
+ *     D = A_hi.B_hi^T + A_lo.B_hi^T + A_hi.B_lo^T        (fp32 accumulation in one TMEM accumulator; A_lo.B_lo^T ~ 2^-18 dropped)
+ * Epilogue arguments as svpc_gemm.  svpc_gemm_split_eligible: 1 when the tcgen05 kernel can take the problem (M >= 64, N >= 16,
+ * K >= 32, one unit stride per operand and the other a multiple of 8 elements); otherwise run svpc_gemm on the fp32 data. */
+int svpc_split_bf16(int rows, int cols, const float* src, long long lds, void* hi, void* lo, long long ldd, svpc_stream_t stream);
+int svpc_gemm_split_eligible(int M, int N, int K, long long sa_m, long long sa_k, long long sb_n, long long sb_k);
+int svpc_gemm_split(int M, int N, int K,
+                    const void* A_hi, const void* A_lo, long long sa_m, long long sa_k,
+                    const void* B_hi, const void* B_lo, long long sb_n, long long sb_k,
+                    void* D, int dtD, long long ldd,
+                    const float* bias, int act,
+                    const void* residual, long long ldr,
+                    void* pre, long long ldp,
+                    int accumulate,
+                    const unsigned int* drop_seed, unsigned int drop_site, float drop_p,
+                    const void* gref, long long ldg, int gact, svpc_stream_t stream);
 
 /* dz = dy * dropscale(r * cols + c) * act'(ref), dbias[c] = sum_r dz[r,c].  ref = output for RELU/SIGMOID,
  * pre-activation for GELU. */
@@ -85,8 +107,15 @@ int svpc_sum(long long n, const float* x, float* out, svpc_stream_t stream);
 int svpc_ln_fwd(int rows, int D, const void* x, const void* res, int dt_in, const float* gamma, const float* beta,
                 float eps, const float* pe, int pe_period, const float* tt, const int* tt_ids, void* y, int dt_out,
                 void* pre, float* mean, float* rstd, svpc_stream_t stream);
+/* dz != NULL fuses the activation / dropout backward of the Linear whose output (after act and dropout, plus an optional
+ * residual) is the LayerNorm's input (model.py:229-233, 285-289, 496-499, 551-553, 704-709):
+ *   dz[r, c] = dpre[r, c] * dropscale(r * D + c) * act'(ref[r, c]),  dbias[c] = sum_r dz[r, c]   (dbias optional)
+ * dz / ref have the dtype and layout of dpre / pre; ref NULL with SVPC_ACT_RELU uses the LayerNorm input itself (valid when
+ * no residual was added); the drop_* arguments are that Linear's dropout site. */
 int svpc_ln_bwd(int rows, int D, const void* dy, int dt_dy, const void* pre, int dt_pre, const float* mean,
-                const float* rstd, const float* gamma, void* dpre, float* dgamma, float* dbeta, svpc_stream_t stream);
+                const float* rstd, const float* gamma, void* dpre, float* dgamma, float* dbeta,
+                void* dz, int act, const void* ref, float* dbias,
+                const unsigned int* drop_seed, unsigned int drop_site, float drop_p, svpc_stream_t stream);
 /* out[bin, :] = sum over rows with ids[row] == bin of dy[row, :]  (token-type embedding gradient, model.py:890) */
 int svpc_index_colsum(int rows, int D, const void* dy, int dt, const int* ids, int nbins, float* out,
                       svpc_stream_t stream);
@@ -136,8 +165,9 @@ int svpc_ragged_mean_bwd(int B, int D, const float* dy, const int* cu, float* dx
 int svpc_row_normalize_fwd(int rows, int cols, const float* x, float* y, svpc_stream_t stream);
 int svpc_row_normalize_bwd(int rows, int cols, const float* dy, const float* x, float* dx, svpc_stream_t stream);
 
-/* Entity-state recurrence of EntitiyReasoningNetwork.forward (model.py:792-820); one CTA per video. */
-int svpc_reasoner_fwd(int B, int D, int max_ni, const float* E0, const int* cu_ingr, const int* cu_steps,
+/* Entity-state recurrence of EntitiyReasoningNetwork.forward (model.py:792-820); one CTA per video.  max_steps: the largest
+ * number of clips of any video (sizes the shared-memory staging of the per-step rows; 0 = unknown, un-pipelined kernel). */
+int svpc_reasoner_fwd(int B, int D, int max_ni, int max_steps, const float* E0, const int* cu_ingr, const int* cu_steps,
                       const int* clip_ent_off, const float* w2v, const float* clog, const float* w4s, float* ent,
                       float* ebar, float* Es, float* a_saved, svpc_stream_t stream);
 int svpc_reasoner_bwd(int B, int D, int max_ni, const float* E0, const int* cu_ingr, const int* cu_steps,

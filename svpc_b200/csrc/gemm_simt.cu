@@ -20,7 +20,15 @@ struct GemmSimtParams {
   int k_per_split;         // grid.z slices of K (split-K: fp32 atomics into a zeroed / accumulated D)
   int atomic;
   SvpcDrop drop;           // dropout after the activation, before the residual
+  const void* gref; long long ldg; int gact;   // last: D = (...) * gact'(gref[m, n])  (fused activation backward of a dgrad)
 };
+
+__device__ __forceinline__ float gs_act_grad(int act, float ref) {
+  if (act == SVPC_ACT_RELU) return ref > 0.f ? 1.f : 0.f;
+  if (act == SVPC_ACT_GELU) return svpc_gelu_grad(ref);
+  if (act == SVPC_ACT_SIGMOID) return ref * (1.f - ref);
+  return 1.f;
+}
 
 template <typename TA, typename TB, typename TD>
 __global__ void __launch_bounds__(GS_THREADS) gemm_simt_kernel(const GemmSimtParams p) {
@@ -90,6 +98,7 @@ __global__ void __launch_bounds__(GS_THREADS) gemm_simt_kernel(const GemmSimtPar
       if (R) v += ldf(R + (long long)m * p.ldr + n);
       TD* d = D + (long long)m * p.ldd + n;
       if (p.accumulate) v += ldf(d);
+      if (p.gref) v *= gs_act_grad(p.gact, ldf((const TD*)p.gref + (long long)m * p.ldg + n));
       stf(d, v);
     }
   }
@@ -109,6 +118,7 @@ __device__ __forceinline__ void gs_epilogue(const GemmSimtParams& p, int m, int 
   if (R) v += ldf(R + (long long)m * p.ldr + n);
   TD* d = D + (long long)m * p.ldd + n;
   if (p.accumulate) v += ldf(d);
+  if (p.gref) v *= gs_act_grad(p.gact, ldf((const TD*)p.gref + (long long)m * p.ldg + n));
   stf(d, v);
 }
 
@@ -187,7 +197,7 @@ static int launch_td(GemmSimtParams p, int dtD, cudaStream_t st) {
   }
   const int tiles = svpc_cdiv(p.N, GS_BN) * svpc_cdiv(p.M, GS_BM);
   int split = 1;
-  const bool plain = !p.bias && p.act == SVPC_ACT_NONE && !p.residual && !p.pre && dtD == SVPC_F32 && !p.drop.seed;
+  const bool plain = !p.bias && p.act == SVPC_ACT_NONE && !p.residual && !p.pre && dtD == SVPC_F32 && !p.drop.seed && !p.gref;
   if (plain && tiles < SVPC_NUM_SMS / 2 && p.K >= 512) split = svpc_imin(SVPC_NUM_SMS / tiles, p.K / 128);
   if (split < 1) split = 1;
   p.k_per_split = svpc_cdiv(svpc_cdiv(p.K, split), GS_BK) * GS_BK;
@@ -205,8 +215,9 @@ static int launch_td(GemmSimtParams p, int dtD, cudaStream_t st) {
 int svpc_gemm_simt_launch(int M, int N, int K, const void* A, int dtA, long long sa_m, long long sa_k, const void* B,
                           int dtB, long long sb_n, long long sb_k, void* D, int dtD, long long ldd, const float* bias,
                           int act, const void* residual, long long ldr, void* pre, long long ldp, int accumulate,
-                          SvpcDrop drop, cudaStream_t st) {
-  GemmSimtParams p{M, N, K, A, sa_m, sa_k, B, sb_n, sb_k, D, ldd, bias, act, residual, ldr, pre, ldp, accumulate, K, 0, drop};
+                          SvpcDrop drop, cudaStream_t st, const void* gref, long long ldg, int gact) {
+  GemmSimtParams p{M, N, K, A, sa_m, sa_k, B, sb_n, sb_k, D, ldd, bias, act, residual, ldr, pre, ldp, accumulate, K, 0, drop,
+                   gref, ldg, gact};
   SVPC_DISPATCH(dtA, TA, SVPC_DISPATCH(dtB, TB, return (launch_td<TA, TB>(p, dtD, st))));
   return SVPC_OK;
 }
@@ -218,7 +229,8 @@ int svpc_gemm_tc_eligible(int M, int N, int K, int dtA, long long sa_m, long lon
                           long long sb_k, int dtD, long long ldd);
 int svpc_gemm_tc_launch(int M, int N, int K, const void* A, long long sa_m, long long sa_k, const void* B, long long sb_n,
                         long long sb_k, void* D, int dtD, long long ldd, const float* bias, int act, const void* residual,
-                        long long ldr, void* pre, long long ldp, int accumulate, SvpcDrop drop, cudaStream_t st);
+                        long long ldr, void* pre, long long ldp, int accumulate, SvpcDrop drop, cudaStream_t st,
+                        const void* A_lo, const void* B_lo, const void* gref, long long ldg, int gact);
 
 extern "C" int svpc_gemm_route(int M, int N, int K, int dtA, long long sa_m, long long sa_k, int dtB, long long sb_n,
                                long long sb_k, int dtD, long long ldd) {
@@ -229,7 +241,7 @@ extern "C" int svpc_gemm(int M, int N, int K, const void* A, int dtA, long long 
                          int dtB, long long sb_n, long long sb_k, void* D, int dtD, long long ldd, const float* bias,
                          int act, const void* residual, long long ldr, void* pre, long long ldp, int accumulate,
                          int route, const unsigned int* drop_seed, unsigned int drop_site, float drop_p,
-                         svpc_stream_t stream) {
+                         const void* gref, long long ldg, int gact, svpc_stream_t stream) {
   SVPC_REQUIRE(M >= 0 && N >= 0 && K >= 0, "gemm: negative size");
   if (M == 0 || N == 0) return SVPC_OK;
   SVPC_REQUIRE(A && B && D, "gemm: null operand");
@@ -247,7 +259,85 @@ extern "C" int svpc_gemm(int M, int N, int K, const void* A, int dtA, long long 
   }
   if (ok && route != SVPC_GEMM_SIMT)
     return svpc_gemm_tc_launch(M, N, K, A, sa_m, sa_k, B, sb_n, sb_k, D, dtD, ldd, bias, act, residual, ldr, pre, ldp,
-                               accumulate, drop, st);
+                               accumulate, drop, st, nullptr, nullptr, gref, ldg, gact);
   return svpc_gemm_simt_launch(M, N, K, A, dtA, sa_m, sa_k, B, dtB, sb_n, sb_k, D, dtD, ldd, bias, act, residual, ldr,
-                               pre, ldp, accumulate, drop, st);
+                               pre, ldp, accumulate, drop, st, gref, ldg, gact);
+}
+
+// ------------------------------------------------------------------------------------------------
+// fp32 operands on the tensor cores ("bf16 x 3"): x = hi + lo with hi = bf16(x), lo = bf16(x - hi) (|x - hi - lo| <= 2^-18 |x|);
+//   D = A_hi.B_hi^T + A_lo.B_hi^T + A_hi.B_lo^T   accumulated in ONE fp32 TMEM accumulator by gemm_tc_kernel (nseg = 3);
+// the dropped A_lo.B_lo^T term is O(2^-18) relative.  This is the parity (1e-4) path's route for every contraction that is
+// eligible for the tcgen05 kernel; everything else of that path stays fp32 FFMA (gemm_simt_kernel).
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) split_bf16_kernel(int rows, int cols, const float* __restrict__ src, long long lds,
+                                                         bf16* __restrict__ hi, bf16* __restrict__ lo, long long ldd) {
+  svpc_pdl_sync();
+  const int c4 = cols >> 2;                       // groups of 4 columns (vector path needs lds % 4 == 0, ldd % 4 == 0)
+  const bool vec = (lds % 4 == 0) && (ldd % 4 == 0) && (((uintptr_t)src | (uintptr_t)hi | (uintptr_t)lo) & 15) == 0;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  if (vec) {
+    const long long n = (long long)rows * c4;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+      const long long r = i / c4;
+      const int c = (int)(i - r * c4) * 4;
+      const float4 v = *reinterpret_cast<const float4*>(src + r * lds + c);
+      const float x[4] = {v.x, v.y, v.z, v.w};
+      __align__(8) bf16 h[4], l[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        h[e] = __float2bfloat16_rn(x[e]);
+        l[e] = __float2bfloat16_rn(x[e] - __bfloat162float(h[e]));
+      }
+      *reinterpret_cast<uint2*>(hi + r * ldd + c) = *reinterpret_cast<const uint2*>(h);
+      *reinterpret_cast<uint2*>(lo + r * ldd + c) = *reinterpret_cast<const uint2*>(l);
+    }
+  }
+  const int c0 = vec ? c4 * 4 : 0;                // tail columns (or everything on the unaligned path)
+  const int ct = cols - c0;
+  if (ct > 0) {
+    const long long n = (long long)rows * ct;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+      const long long r = i / ct;
+      const int c = c0 + (int)(i - r * ct);
+      const float x = src[r * lds + c];
+      const bf16 h = __float2bfloat16_rn(x);
+      hi[r * ldd + c] = h;
+      lo[r * ldd + c] = __float2bfloat16_rn(x - __bfloat162float(h));
+    }
+  }
+}
+
+extern "C" int svpc_split_bf16(int rows, int cols, const float* src, long long lds, void* hi, void* lo, long long ldd,
+                               svpc_stream_t stream) {
+  if (rows <= 0 || cols <= 0) return SVPC_OK;
+  SVPC_REQUIRE(src && hi && lo && lds >= cols && ldd >= cols, "split_bf16: bad arguments");
+  const int blocks = svpc_imin(svpc_cdiv((long long)rows * cols, 1024), SVPC_NUM_SMS * 16);
+  svpc_launch(split_bf16_kernel, blocks, 256, 0, (cudaStream_t)stream, rows, cols, src, lds, (bf16*)hi, (bf16*)lo, ldd);
+  return svpc_check_launch("split_bf16");
+}
+
+extern "C" int svpc_gemm_split_eligible(int M, int N, int K, long long sa_m, long long sa_k, long long sb_n, long long sb_k) {
+  return svpc_gemm_tc_eligible(M, N, K, SVPC_BF16, sa_m, sa_k, SVPC_BF16, sb_n, sb_k, SVPC_F32, 0);
+}
+
+extern "C" int svpc_gemm_split(int M, int N, int K, const void* A_hi, const void* A_lo, long long sa_m, long long sa_k,
+                               const void* B_hi, const void* B_lo, long long sb_n, long long sb_k, void* D, int dtD,
+                               long long ldd, const float* bias, int act, const void* residual, long long ldr, void* pre,
+                               long long ldp, int accumulate, const unsigned int* drop_seed, unsigned int drop_site,
+                               float drop_p, const void* gref, long long ldg, int gact, svpc_stream_t stream) {
+  SVPC_REQUIRE(M >= 0 && N >= 0 && K >= 0, "gemm_split: negative size");
+  if (M == 0 || N == 0) return SVPC_OK;
+  SVPC_REQUIRE(A_hi && A_lo && B_hi && B_lo && D, "gemm_split: null operand");
+  SVPC_REQUIRE(!(accumulate && (act != SVPC_ACT_NONE || residual)), "gemm_split: accumulate excludes act / residual");
+  SVPC_REQUIRE(drop_p >= 0.f && drop_p < 1.f, "gemm_split: dropout p=%f outside [0, 1)", drop_p);
+  const SvpcDrop drop{drop_p > 0.f ? drop_seed : nullptr, drop_site, drop_p};
+  const bool ok = svpc_gemm_split_eligible(M, N, K, sa_m, sa_k, sb_n, sb_k) &&
+                  (((uintptr_t)A_hi | (uintptr_t)A_lo | (uintptr_t)B_hi | (uintptr_t)B_lo) & 15) == 0;
+  if (!ok) {
+    svpc_set_error("gemm_split: problem %dx%dx%d / strides not eligible for the tcgen05 route", M, N, K);
+    return SVPC_ERR_UNSUPPORTED;
+  }
+  return svpc_gemm_tc_launch(M, N, K, A_hi, sa_m, sa_k, B_hi, sb_n, sb_k, D, dtD, ldd, bias, act, residual, ldr, pre, ldp,
+                             accumulate, drop, (cudaStream_t)stream, A_lo, B_lo, gref, ldg, gact);
 }

@@ -24,7 +24,8 @@
 #define TC_BM 128
 #define TC_BK 64                 // 64 bf16 = 128 B = one swizzle row
 #define TC_BN_MAX 256
-#define TC_STAGES 4
+#define TC_STAGES 4              // ring depth at the full tile width (256 columns); narrower launches cut the same 192 KB into more stages
+#define TC_MAX_STAGES 8
 #define TC_EPI_WARPS 8                                  // two per TMEM lane quarter
 #define TC_THREADS (64 + 32 * TC_EPI_WARPS)
 #define TC_UMMA_K 16
@@ -162,6 +163,7 @@ struct TcParams {
   int accumulate;          // D += result
   int atomic;              // split-K: red.global.add.f32
   SvpcDrop drop;           // dropout after the activation, before the residual (model.py:231, 287, 757)
+  const void* gref; long long ldg; int gact;   // last step of the epilogue: D = (...) * gact'(gref[m, n])  (fused activation backward)
   // ---- work list (see tc_unit): every role of every CTA walks units blockIdx.x, blockIdx.x + gridDim.x, ...
   int BN;                  // tile width (64 / 128 / 256)
   int tiles_n;             // tiles along N
@@ -170,6 +172,8 @@ struct TcParams {
   int main_tiles;          // tiles handled whole (x split); the remaining `tiles - main_tiles` are cut along N
   int tail_s;              // ... into tail_s sub-tiles of width BN / tail_s each, so the last round is short
   int total_units;
+  int nseg;                // 1: D = A.B^T;  3: split-fp32 operands, D = A.B^T + Alo.B^T + A.Blo^T (same accumulator)
+  int nstages, stage_bytes;   // shared-memory ring: nstages slots of A (16 KB) + the launch's widest B tile
 };
 
 struct TcUnit { int m0, n0, width, kb0, kb1; };
@@ -210,6 +214,13 @@ __device__ __forceinline__ float tc_act(float v) {
   return v;
 }
 
+__device__ __forceinline__ float tc_act_grad(int act, float ref) {
+  if (act == SVPC_ACT_RELU) return ref > 0.f ? 1.f : 0.f;
+  if (act == SVPC_ACT_GELU) return svpc_gelu_grad(ref);
+  if (act == SVPC_ACT_SIGMOID) return ref * (1.f - ref);
+  return 1.f;
+}
+
 // The warp's 32 x 32 fp32 transposition buffer: 16-byte slot (row r, column group g) lives at r * 8 + (g ^ (r & 7)), so
 // both the writes (lane = row, one column group at a time) and the reads (8 lanes per row) are bank-conflict free.
 __device__ __forceinline__ uint32_t epi_slot(int r, int g) { return (uint32_t)(r * 8 + (g ^ (r & 7))) * 16u; }   // byte offset
@@ -229,11 +240,18 @@ __device__ __forceinline__ void epi_vec(const TcParams& p, uint32_t stage, int m
 #pragma unroll 1
   for (int j0 = 0; j0 < 8; j0 += 4) {       // two batches of 4 rows: bounded register use, 4 loads in flight
     typename Raw4<TD>::type rr[4];         // residual rows, still in the storage type (2 registers each for bf16)
+    typename Raw4<TD>::type gg[4];         // activation-gradient reference rows
     if (p.residual) {
       const TD* r0 = (const TD*)p.residual + (long long)(m_first + 4 * j0) * p.ldr + n;
 #pragma unroll
       for (int j = 0; j < 4; ++j)
         if (j0 + j < rows) rr[j] = *reinterpret_cast<const typename Raw4<TD>::type*>(r0 + (long long)j * 4 * p.ldr);
+    }
+    if (p.gref) {
+      const TD* g0 = (const TD*)p.gref + (long long)(m_first + 4 * j0) * p.ldg + n;
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (j0 + j < rows) gg[j] = *reinterpret_cast<const typename Raw4<TD>::type*>(g0 + (long long)j * 4 * p.ldg);
     }
 #pragma unroll
     for (int jj = 0; jj < 4; ++jj) {
@@ -259,6 +277,11 @@ __device__ __forceinline__ void epi_vec(const TcParams& p, uint32_t stage, int m
       }
       if (p.residual) { const float4 r4 = raw4_to_float4(rr[jj]); x.x += r4.x; x.y += r4.y; x.z += r4.z; x.w += r4.w; }
       if (p.accumulate) { const float4 dd = ld4(d0 + j * dstep); x.x += dd.x; x.y += dd.y; x.z += dd.z; x.w += dd.w; }
+      if (p.gref) {
+        const float4 g4 = raw4_to_float4(gg[jj]);
+        x.x *= tc_act_grad(p.gact, g4.x); x.y *= tc_act_grad(p.gact, g4.y);
+        x.z *= tc_act_grad(p.gact, g4.z); x.w *= tc_act_grad(p.gact, g4.w);
+      }
       st4(d0 + j * dstep, x);
     }
   }
@@ -287,6 +310,7 @@ __device__ __forceinline__ void epi_scalar(const TcParams& p, uint32_t stage, in
       if (Rp) y += ldf(Rp + (long long)m * p.ldr + n + e);
       TD* d = Dp + (long long)m * p.ldd + n + e;
       if (p.accumulate) y += ldf(d);
+      if (p.gref) y *= tc_act_grad(p.gact, ldf((const TD*)p.gref + (long long)m * p.ldg + n + e));
       stf(d, y);
     }
   }
@@ -321,14 +345,16 @@ __device__ __forceinline__ void epi_atomic(const TcParams& p, uint32_t stage, in
 template <bool A_MN, bool B_MN, typename TD, int ACT, bool DROP>
 __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA,
                                                                 const __grid_constant__ CUtensorMap tmB,
+                                                                const __grid_constant__ CUtensorMap tmAlo,
+                                                                const __grid_constant__ CUtensorMap tmBlo,
                                                                 const __grid_constant__ TcParams p) {
   svpc_pdl_sync();
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   float* epi_stage = reinterpret_cast<float*>(smem + TC_STAGES * TC_STAGE_BYTES);
   uint64_t* full_bar = (uint64_t*)(smem + TC_STAGES * TC_STAGE_BYTES + TC_EPI_BYTES);
-  uint64_t* empty_bar = full_bar + TC_STAGES;
-  uint64_t* tmem_full = empty_bar + TC_STAGES;       // [2]
+  uint64_t* empty_bar = full_bar + TC_MAX_STAGES;
+  uint64_t* tmem_full = empty_bar + TC_MAX_STAGES;   // [2]
   uint64_t* tmem_empty = tmem_full + 2;              // [2]
   uint32_t* tmem_slot = (uint32_t*)(tmem_empty + 2);
 
@@ -337,9 +363,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"((uint64_t)&tmA) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"((uint64_t)&tmB) : "memory");
+    if (p.nseg > 1) {
+      asm volatile("prefetch.tensormap [%0];" ::"l"((uint64_t)&tmAlo) : "memory");
+      asm volatile("prefetch.tensormap [%0];" ::"l"((uint64_t)&tmBlo) : "memory");
+    }
   }
   if (warp == 1 && lane == 0) {
-    for (int s = 0; s < TC_STAGES; ++s) { mbar_init(full_bar + s, 1); mbar_init(empty_bar + s, 1); }
+    for (int s = 0; s < p.nstages; ++s) { mbar_init(full_bar + s, 1); mbar_init(empty_bar + s, 1); }
     for (int a = 0; a < 2; ++a) { mbar_init(tmem_full + a, 1); mbar_init(tmem_empty + a, TC_EPI_WARPS); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -352,30 +382,35 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
     if (lane == 0) {
-      uint32_t it = 0;                                   // K blocks issued so far (ring position)
+      uint32_t s = 0, ph = 0;                            // ring slot and its phase
       for (int u = blockIdx.x; u < p.total_units; u += gridDim.x) {
         const TcUnit w = tc_unit(p, u);
         if (w.n0 >= p.N) continue;
         const uint32_t bytes = TC_A_BYTES + (uint32_t)w.width * (TC_BK * 2);
         const int nbox = w.width >> 6;
-        for (int kb = w.kb0; kb < w.kb1; ++kb, ++it) {
-          const uint32_t s = it % TC_STAGES, ph = (it / TC_STAGES) & 1;
-          mbar_wait(empty_bar + s, ph ^ 1);
-          uint8_t* sa = smem + s * TC_STAGE_BYTES;
-          uint8_t* sb = sa + TC_A_BYTES;
-          mbar_expect_tx(full_bar + s, bytes);
-          const int k = kb * TC_BK;
-          if (A_MN) {
+        // split-fp32 operands: the K loop runs three times over the same accumulator - (A_hi, B_hi), (A_lo, B_hi), (A_hi, B_lo)
+        for (int seg = 0; seg < p.nseg; ++seg) {
+          const CUtensorMap* ma = seg == 1 ? &tmAlo : &tmA;
+          const CUtensorMap* mb = seg == 2 ? &tmBlo : &tmB;
+          for (int kb = w.kb0; kb < w.kb1; ++kb) {
+            mbar_wait(empty_bar + s, ph ^ 1);
+            uint8_t* sa = smem + s * p.stage_bytes;
+            uint8_t* sb = sa + TC_A_BYTES;
+            mbar_expect_tx(full_bar + s, bytes);
+            const int k = kb * TC_BK;
+            if (A_MN) {
 #pragma unroll
-            for (int j = 0; j < TC_BM / 64; ++j) tma_load_2d(sa + j * (64 * TC_BK * 2), &tmA, full_bar + s, w.m0 + j * 64, k);
-          } else {
-            tma_load_2d(sa, &tmA, full_bar + s, k, w.m0);
-          }
-          // B in 64-column boxes (8 KB each): K-major boxes stack into one [width][64] swizzled tile, MN-major boxes are
-          // the 64-wide N blocks the descriptor strides over
-          for (int j = 0; j < nbox; ++j) {
-            if (B_MN) tma_load_2d(sb + j * (64 * TC_BK * 2), &tmB, full_bar + s, w.n0 + j * 64, k);
-            else tma_load_2d(sb + j * (64 * TC_BK * 2), &tmB, full_bar + s, k, w.n0 + j * 64);
+              for (int j = 0; j < TC_BM / 64; ++j) tma_load_2d(sa + j * (64 * TC_BK * 2), ma, full_bar + s, w.m0 + j * 64, k);
+            } else {
+              tma_load_2d(sa, ma, full_bar + s, k, w.m0);
+            }
+            // B in 64-column boxes (8 KB each): K-major boxes stack into one [width][64] swizzled tile, MN-major boxes are
+            // the 64-wide N blocks the descriptor strides over
+            for (int j = 0; j < nbox; ++j) {
+              if (B_MN) tma_load_2d(sb + j * (64 * TC_BK * 2), mb, full_bar + s, w.n0 + j * 64, k);
+              else tma_load_2d(sb + j * (64 * TC_BK * 2), mb, full_bar + s, k, w.n0 + j * 64);
+            }
+            if (++s == (uint32_t)p.nstages) { s = 0; ph ^= 1; }
           }
         }
       }
@@ -383,7 +418,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
     if (lane == 0) {
-      uint32_t it = 0, ui = 0;
+      uint32_t s = 0, ph = 0, ui = 0;
       for (int u = blockIdx.x; u < p.total_units; u += gridDim.x) {
         const TcUnit w = tc_unit(p, u);
         if (w.n0 >= p.N) continue;
@@ -395,11 +430,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
         const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((A_MN ? 1u : 0u) << 15) | ((B_MN ? 1u : 0u) << 16) |
                                ((uint32_t)(w.width >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
         const uint32_t tacc = tmem_base + acc * TC_BN_MAX;
-        for (int kb = w.kb0; kb < w.kb1; ++kb, ++it) {
-          const uint32_t s = it % TC_STAGES, ph = (it / TC_STAGES) & 1;
+        const int nkb = (w.kb1 - w.kb0) * p.nseg;
+        for (int kq = 0; kq < nkb; ++kq) {
           mbar_wait(full_bar + s, ph);
           tc_fence_after();
-          const uint32_t sa = smem_u32(smem + s * TC_STAGE_BYTES);
+          const uint32_t sa = smem_u32(smem + s * p.stage_bytes);
           const uint32_t sb = sa + TC_A_BYTES;
 #pragma unroll
           for (int k = 0; k < TC_BK / TC_UMMA_K; ++k) {
@@ -409,9 +444,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
                                      : make_sdesc(sa + k * (TC_UMMA_K * 2), 16, 1024);
             const uint64_t bd = B_MN ? make_sdesc(sb + k * (TC_UMMA_K * 128), TC_BK * 128, 1024)
                                      : make_sdesc(sb + k * (TC_UMMA_K * 2), 16, 1024);
-            umma_f16(tacc, ad, bd, idesc, (kb > w.kb0 || k > 0) ? 1u : 0u);
+            umma_f16(tacc, ad, bd, idesc, (kq > 0 || k > 0) ? 1u : 0u);
           }
           umma_commit(empty_bar + s);      // ring slot free once these MMAs have read it
+          if (++s == (uint32_t)p.nstages) { s = 0; ph ^= 1; }
         }
         umma_commit(tmem_full + acc);      // accumulator complete
       }
@@ -429,6 +465,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
     const uint32_t stage = smem_u32(epi_stage) + (uint32_t)ew * (32 * 32 * 4);
     const bool vec_all = (p.ldd % 4 == 0) && (((uintptr_t)p.D & 15) == 0) &&
                          (!p.residual || (p.ldr % 4 == 0 && ((uintptr_t)p.residual & 15) == 0)) &&
+                         (!p.gref || (p.ldg % 4 == 0 && ((uintptr_t)p.gref & 15) == 0)) &&
                          (!p.pre || (p.ldp % 4 == 0 && ((uintptr_t)p.pre & 15) == 0)) && (((uintptr_t)p.bias & 15) == 0);
     const bool dropping = DROP;
     const uint32_t dkey = DROP ? svpc_drop_key(p.drop) : 0u;
@@ -554,40 +591,39 @@ int svpc_gemm_tc_eligible(int M, int N, int K, int dtA, long long sa_m, long lon
 }
 
 template <bool A_MN, bool B_MN, typename TD, int ACT, bool DROP>
-static int launch_cfg(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, int grid, cudaStream_t st) {
+static int launch_cfg(const CUtensorMap* tm, const TcParams& p, int grid, cudaStream_t st) {
   auto kern = gemm_tc_kernel<A_MN, B_MN, TD, ACT, DROP>;
   static bool attr_set = false;
   if (!attr_set) {
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_BYTES);
     attr_set = true;
   }
-  svpc_launch(kern, grid, TC_THREADS, TC_SMEM_BYTES, st, ta, tb, p);
+  svpc_launch(kern, grid, TC_THREADS, TC_SMEM_BYTES, st, tm[0], tm[1], tm[2], tm[3], p);
   return svpc_check_launch("gemm_tc");
 }
 
 template <bool A_MN, bool B_MN, typename TD>
-static int launch_epi(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, int grid, cudaStream_t st) {
+static int launch_epi(const CUtensorMap* tm, const TcParams& p, int grid, cudaStream_t st) {
   const bool drop = p.drop.seed != nullptr && p.drop.p > 0.f;
 #define TC_CASE(A) \
-  case A: return drop ? launch_cfg<A_MN, B_MN, TD, A, true>(ta, tb, p, grid, st) : launch_cfg<A_MN, B_MN, TD, A, false>(ta, tb, p, grid, st);
+  case A: return drop ? launch_cfg<A_MN, B_MN, TD, A, true>(tm, p, grid, st) : launch_cfg<A_MN, B_MN, TD, A, false>(tm, p, grid, st);
   switch (p.act) {
     TC_CASE(SVPC_ACT_RELU)
     TC_CASE(SVPC_ACT_GELU)
     TC_CASE(SVPC_ACT_SIGMOID)
     default: break;
   }
-  return drop ? launch_cfg<A_MN, B_MN, TD, SVPC_ACT_NONE, true>(ta, tb, p, grid, st)
-              : launch_cfg<A_MN, B_MN, TD, SVPC_ACT_NONE, false>(ta, tb, p, grid, st);
+  return drop ? launch_cfg<A_MN, B_MN, TD, SVPC_ACT_NONE, true>(tm, p, grid, st)
+              : launch_cfg<A_MN, B_MN, TD, SVPC_ACT_NONE, false>(tm, p, grid, st);
 #undef TC_CASE
 }
 
 template <typename TD>
-static int launch_major(bool a_mn, bool b_mn, const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, int grid,
-                        cudaStream_t st) {
-  if (!a_mn && !b_mn) return launch_epi<false, false, TD>(ta, tb, p, grid, st);
-  if (!a_mn && b_mn) return launch_epi<false, true, TD>(ta, tb, p, grid, st);
-  if (a_mn && !b_mn) return launch_epi<true, false, TD>(ta, tb, p, grid, st);
-  return launch_epi<true, true, TD>(ta, tb, p, grid, st);
+static int launch_major(bool a_mn, bool b_mn, const CUtensorMap* tm, const TcParams& p, int grid, cudaStream_t st) {
+  if (!a_mn && !b_mn) return launch_epi<false, false, TD>(tm, p, grid, st);
+  if (!a_mn && b_mn) return launch_epi<false, true, TD>(tm, p, grid, st);
+  if (a_mn && !b_mn) return launch_epi<true, false, TD>(tm, p, grid, st);
+  return launch_epi<true, true, TD>(tm, p, grid, st);
 }
 
 // tile width: the padded width ceil(N / BN) * BN, weighted by how much worse a narrower UMMA uses the operand bandwidth
@@ -603,23 +639,30 @@ static int choose_bn(int N) {
   return best;
 }
 
+// A_lo / B_lo: the low-order bf16 planes of split-fp32 operands (same strides as A / B), or NULL for a plain bf16 GEMM.
 int svpc_gemm_tc_launch(int M, int N, int K, const void* A, long long sa_m, long long sa_k, const void* B, long long sb_n,
                         long long sb_k, void* D, int dtD, long long ldd, const float* bias, int act, const void* residual,
-                        long long ldr, void* pre, long long ldp, int accumulate, SvpcDrop drop, cudaStream_t st) {
+                        long long ldr, void* pre, long long ldp, int accumulate, SvpcDrop drop, cudaStream_t st,
+                        const void* A_lo, const void* B_lo, const void* gref, long long ldg, int gact) {
   const bool a_mn = sa_k != 1, b_mn = sb_k != 1;
   const int BN = choose_bn(N);
-  CUtensorMap ta, tb;
+  const int nseg = (A_lo && B_lo) ? 3 : 1;
+  CUtensorMap tm[4];
   int rc;
-  if (a_mn) rc = make_map(&ta, A, M, K, sa_k, 64, TC_BK); else rc = make_map(&ta, A, K, M, sa_m, TC_BK, TC_BM);
-  if (rc) return rc;
-  if (b_mn) rc = make_map(&tb, B, N, K, sb_k, 64, TC_BK); else rc = make_map(&tb, B, K, N, sb_n, TC_BK, 64);
-  if (rc) return rc;
+  const void* ops[4] = {A, B, nseg == 3 ? A_lo : A, nseg == 3 ? B_lo : B};
+  for (int i = 0; i < 4; i += 2) {
+    if (a_mn) rc = make_map(&tm[i], ops[i], M, K, sa_k, 64, TC_BK); else rc = make_map(&tm[i], ops[i], K, M, sa_m, TC_BK, TC_BM);
+    if (rc) return rc;
+    if (b_mn) rc = make_map(&tm[i + 1], ops[i + 1], N, K, sb_k, 64, TC_BK); else rc = make_map(&tm[i + 1], ops[i + 1], K, N, sb_n, TC_BK, 64);
+    if (rc) return rc;
+    if (nseg == 1) { tm[2] = tm[0]; tm[3] = tm[1]; break; }
+  }
   const int G = SVPC_NUM_SMS;
   const int tiles_m = svpc_cdiv(M, TC_BM), tiles_n = svpc_cdiv(N, BN), tiles = tiles_m * tiles_n;
   const int kb_total = svpc_cdiv(K, TC_BK);
   SVPC_REQUIRE(kb_total > 0, "gemm_tc: K == 0");
   int split = 1;
-  const bool plain = !bias && act == SVPC_ACT_NONE && !residual && !pre && dtD == SVPC_F32 && !drop.seed;
+  const bool plain = !bias && act == SVPC_ACT_NONE && !residual && !pre && dtD == SVPC_F32 && !drop.seed && !gref;
   if (plain && tiles * 2 <= G && kb_total >= 16) {
     // split-K: rounds of G units x K blocks per unit, plus ~4 K-block-times of atomic epilogue per unit
     long long best = (long long)svpc_cdiv(tiles, G) * (kb_total + 4);
@@ -639,15 +682,22 @@ int svpc_gemm_tc_launch(int M, int N, int K, const void* A, long long sa_m, long
     }
   }
   const int total_units = main_tiles * split + (tiles - main_tiles) * tail_s;
-  TcParams p{M, N, K, D, ldd, bias, act, residual, ldr, pre, ldp, accumulate, split > 1 ? 1 : 0, drop,
-             BN, tiles_n, split, kb_per, kb_total, main_tiles, tail_s, total_units};
+  TcParams p{M, N, K, D, ldd, bias, act, residual, ldr, pre, ldp, accumulate, split > 1 ? 1 : 0, drop, gref, ldg, gact,
+             BN, tiles_n, split, kb_per, kb_total, main_tiles, tail_s, total_units, nseg, 0, 0};
+  {
+    // the 192 KB ring holds 4 stages of a 256-wide tile, 6 of a 128-wide, 8 of a 64-wide one: a launch of narrow tiles
+    // (the 192-row step-level modules, K = 768 = 12 blocks) then has most of its K loop in flight at once
+    const int stage_w = main_tiles > 0 ? BN : BN / tail_s;
+    p.stage_bytes = TC_A_BYTES + stage_w * (TC_BK * 2);
+    p.nstages = svpc_imin(TC_MAX_STAGES, (TC_STAGES * TC_STAGE_BYTES) / p.stage_bytes);
+  }
   if (split > 1 && !accumulate) {
     cudaError_t e = cudaMemset2DAsync(D, (size_t)ldd * 4, 0, (size_t)N * 4, (size_t)M, st);
     if (e != cudaSuccess) { svpc_set_error("gemm_tc: memset2D: %s", cudaGetErrorString(e)); return SVPC_ERR_CUDA; }
   }
   const int grid = svpc_imin(total_units, G);
-  if (dtD == SVPC_F32) return launch_major<float>(a_mn, b_mn, ta, tb, p, grid, st);
-  if (dtD == SVPC_BF16) return launch_major<bf16>(a_mn, b_mn, ta, tb, p, grid, st);
+  if (dtD == SVPC_F32) return launch_major<float>(a_mn, b_mn, tm, p, grid, st);
+  if (dtD == SVPC_BF16) return launch_major<bf16>(a_mn, b_mn, tm, p, grid, st);
   svpc_set_error("gemm_tc: bad output dtype %d", dtD);
   return SVPC_ERR_ARG;
 }

@@ -211,10 +211,283 @@ __global__ void __launch_bounds__(RS_THREADS) reasoner_bwd_kernel(
   for (int i = threadIdx.x; i < ni * D; i += RS_THREADS) dE0[(long long)g0 * D + i] = dE[i];
 }
 
-extern "C" int svpc_reasoner_fwd(int B, int D, int max_ni, const float* E0, const int* cu_ingr, const int* cu_steps,
+
+// ------------------------------------------------------------------------------------------------
+// Pipelined variants (used whenever their shared memory fits): the kernels above spend most of every step waiting -
+// a dozen block barriers and a chain of L2 round trips (w2v row, choice logits, the (Ni, D) matrices of the backward).
+// Here every global read of step t+1 is in flight (cp.async into a second buffer) while step t computes, the small
+// per-ingredient quantities (mixture, normalisation, their gradients) are recomputed redundantly by every thread from
+// shared memory instead of being block-reduced, and a thread OWNS a column d of the entity matrix through the
+// column-wise phases, so a step needs two block barriers.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+// n floats (n % 4 == 0, both sides 16-byte aligned) global -> shared, spread over the CTA
+__device__ __forceinline__ void stage_async(float* dst, const float* src, int n) {
+  for (int i = threadIdx.x * 4; i < n; i += RS_THREADS * 4) cp_async16(dst + i, src + i);
+}
+
+__global__ void __launch_bounds__(RS_THREADS) reasoner_fwd_pipe_kernel(int D, int max_ni, int max_steps, const float* __restrict__ E0,
+                                                                       const int* __restrict__ cu_ingr,
+                                                                       const int* __restrict__ cu_steps,
+                                                                       const int* __restrict__ clip_ent_off,
+                                                                       const float* __restrict__ w2v,
+                                                                       const float* __restrict__ clog,
+                                                                       const float* __restrict__ w4s, float* __restrict__ ent,
+                                                                       float* __restrict__ ebar_out, float* __restrict__ Es,
+                                                                       float* __restrict__ a_saved) {
+  svpc_pdl_sync();
+  extern __shared__ __align__(16) float sm[];
+  float* E = sm;                              // (max_ni, D)
+  float* wb = E + (size_t)max_ni * D;         // (steps, D): the w2v rows of ALL steps of this video, staged up front
+  float* eb = wb + (size_t)max_steps * D;     // 2 x (max_ni): e of this / the previous step
+  const int b = blockIdx.x;
+  const int g0 = cu_ingr[b], ni = cu_ingr[b + 1] - g0;
+  const int n0 = cu_steps[b], n1 = cu_steps[b + 1];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (n1 <= n0) return;
+  stage_async(E, E0 + (long long)g0 * D, ni * D);
+  stage_async(wb, w2v + (long long)n0 * D, (n1 - n0) * D);
+  cp_async_commit();
+  for (int i = threadIdx.x; i < 2 * max_ni; i += RS_THREADS) eb[i] = 0.f;
+  cp_async_wait_all();
+  __syncthreads();
+  for (int n = n0; n < n1; ++n) {
+    const int cur = (n - n0) & 1;
+    const float* w = wb + (size_t)(n - n0) * D;
+    float* e = eb + cur * max_ni;
+    const float* ep = eb + (cur ^ 1) * max_ni;
+    // scalars of this step: issued now, consumed after the barrier
+    const float l0 = clog[3 * n], l1 = clog[3 * n + 1], l2 = clog[3 * n + 2];
+    const float w4 = w4s[n];
+    const long long eo = clip_ent_off[n];
+    // (1) e_i = sigmoid(E_i . w): one warp per entity row
+    for (int i = warp; i < ni; i += RS_THREADS / 32) {
+      float s = 0.f;
+      for (int d = lane; d < D; d += 32) s = fmaf(E[i * D + d], w[d], s);
+      s = warp_sum(s);
+      if (lane == 0) e[i] = svpc_sigmoid(s);
+    }
+    __syncthreads();
+    // (2) mixture a = c0 e + c1 e_prev and its sum, recomputed by every thread (ni broadcast reads)
+    const float mx = fmaxf(l0, fmaxf(l1, l2));
+    const float x0 = expf(l0 - mx), x1 = expf(l1 - mx), x2 = expf(l2 - mx);
+    const float c0 = x0 / (x0 + x1 + x2), c1 = x1 / (x0 + x1 + x2);
+    float asum = 0.f;
+    for (int i = 0; i < ni; ++i) asum += c0 * e[i] + c1 * ep[i];
+    if (threadIdx.x < ni) {
+      const int i = threadIdx.x;
+      ent[eo + i] = e[i];
+      a_saved[eo + i] = c0 * e[i] + c1 * ep[i];
+    }
+    // (3) the thread that owns column d: ebar_d, k_d, and the update of E[:, d]
+    for (int d = threadIdx.x; d < D; d += RS_THREADS) {
+      float s = 0.f;
+      for (int i = 0; i < ni; ++i) s = fmaf((c0 * e[i] + c1 * ep[i]) / asum, E[i * D + d], s);
+      ebar_out[(long long)n * D + d] = s;
+      const float kk = w4 * s;
+      const float kd = kk > 0.f ? kk : 0.f;
+      for (int i = 0; i < ni; ++i) {
+        const float ai = c0 * e[i] + c1 * ep[i];
+        const float v = ai * kd + (1.f - ai) * E[i * D + d];
+        E[i * D + d] = v;
+        Es[(eo + i) * D + d] = v;
+      }
+    }
+    __syncthreads();
+  }
+}
+
+__global__ void __launch_bounds__(RS_THREADS) reasoner_bwd_pipe_kernel(
+    int D, int max_ni, const float* __restrict__ E0, const int* __restrict__ cu_ingr, const int* __restrict__ cu_steps,
+    const int* __restrict__ clip_ent_off, const float* __restrict__ w2v, const float* __restrict__ clog,
+    const float* __restrict__ w4s, const float* __restrict__ ent, const float* __restrict__ ebar,
+    const float* __restrict__ Es, const float* __restrict__ a_saved, const float* __restrict__ d_ent,
+    const float* __restrict__ d_ebar, const float* __restrict__ d_Es, float* __restrict__ dE0, float* __restrict__ dw2v,
+    float* __restrict__ dclog, float* __restrict__ dw4s) {
+  svpc_pdl_sync();
+  extern __shared__ __align__(16) float sm[];
+  const size_t ND = (size_t)max_ni * D;
+  float* dE = sm;                        // (max_ni, D) gradient w.r.t. the current entity matrix
+  float* Epb = dE + ND;                  // 2 x (max_ni, D): entity matrix BEFORE this step / before the next (earlier) one
+  float* dEsb = Epb + 2 * ND;            // 2 x (max_ni, D): d_Es of this / the next step
+  float* vecb = dEsb + 2 * ND;           // 2 x (3 D): ebar row, d_ebar row, w2v row
+  float* deb = vecb + 6 * D;             // (D) d ebar
+  float* kvs = deb + D;                  // (D) k
+  float* da = kvs + D;                   // (max_ni)
+  float* dan = da + max_ni;              // (max_ni)
+  float* de_next = dan + max_ni;         // 2 x (max_ni): gradient flowing into e_t from step t+1, this / next
+  float* svb = de_next + 2 * max_ni;     // 2 x (4 max_ni): a, e, e_prev, d_ent of this / the next step
+  float* pw4 = svb + 8 * max_ni;         // (32) per-warp partial sums of d w4
+  const int b = blockIdx.x;
+  const int g0 = cu_ingr[b], ni = cu_ingr[b + 1] - g0;
+  const int n0 = cu_steps[b], n1 = cu_steps[b + 1];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (n1 <= n0) {
+    for (int i = threadIdx.x; i < ni * D; i += RS_THREADS) dE0[(long long)g0 * D + i] = 0.f;
+    return;
+  }
+  auto stage_step = [&](int n, int buf) {
+    const float* Eprev = (n == n0) ? E0 + (long long)g0 * D : Es + (long long)clip_ent_off[n - 1] * D;
+    stage_async(Epb + buf * ND, Eprev, ni * D);
+    stage_async(dEsb + buf * ND, d_Es + (long long)clip_ent_off[n] * D, ni * D);
+    stage_async(vecb + buf * 3 * D, ebar + (long long)n * D, D);
+    stage_async(vecb + buf * 3 * D + D, d_ebar + (long long)n * D, D);
+    stage_async(vecb + buf * 3 * D + 2 * D, w2v + (long long)n * D, D);
+  };
+  // per-ingredient vectors of a step (a, e, e_prev, d_ent): thread i < ni loads them a step ahead into registers
+  float r_a = 0.f, r_e = 0.f, r_ep = 0.f, r_de = 0.f;
+  auto load_small = [&](int n) {
+    if ((int)threadIdx.x < ni) {
+      const long long eo = clip_ent_off[n];
+      r_a = a_saved[eo + threadIdx.x];
+      r_e = ent[eo + threadIdx.x];
+      r_ep = (n == n0) ? 0.f : ent[clip_ent_off[n - 1] + threadIdx.x];
+      r_de = d_ent[eo + threadIdx.x];
+    }
+  };
+  auto store_small = [&](int buf) {
+    if ((int)threadIdx.x < ni) {
+      float* v = svb + buf * 4 * max_ni;
+      v[threadIdx.x] = r_a; v[max_ni + threadIdx.x] = r_e; v[2 * max_ni + threadIdx.x] = r_ep; v[3 * max_ni + threadIdx.x] = r_de;
+    }
+  };
+  stage_step(n1 - 1, 0);
+  cp_async_commit();
+  load_small(n1 - 1);
+  // scalars of a step, carried one step ahead in registers
+  float w4 = w4s[n1 - 1], l0 = clog[3 * (n1 - 1)], l1 = clog[3 * (n1 - 1) + 1], l2 = clog[3 * (n1 - 1) + 2];
+  for (int i = threadIdx.x; i < ni * D; i += RS_THREADS) dE[i] = 0.f;
+  for (int i = threadIdx.x; i < 2 * max_ni; i += RS_THREADS) de_next[i] = 0.f;
+  store_small(0);
+  cp_async_wait_all();
+  __syncthreads();
+  for (int n = n1 - 1; n >= n0; --n) {
+    const int cur = (n1 - 1 - n) & 1;
+    const float* Ep = Epb + cur * ND;
+    const float* dEs = dEsb + cur * ND;
+    const float* ebr = vecb + cur * 3 * D;
+    const float* debo = ebr + D;
+    const float* w = ebr + 2 * D;
+    const float* av = svb + cur * 4 * max_ni;          // a, e, e_prev, d_ent of this step
+    const float* ev = av + max_ni;
+    const float* epv = ev + max_ni;
+    const float* dev_ = epv + max_ni;
+    float* den_in = de_next + cur * max_ni;            // written by the previous iteration (step n + 1)
+    float* den_out = de_next + (cur ^ 1) * max_ni;
+    float w4n = 0.f, l0n = 0.f, l1n = 0.f, l2n = 0.f;
+    if (n > n0) {                                      // everything step n - 1 reads from global: in flight during this step
+      stage_step(n - 1, cur ^ 1);
+      load_small(n - 1);
+      w4n = w4s[n - 1]; l0n = clog[3 * (n - 1)]; l1n = clog[3 * (n - 1) + 1]; l2n = clog[3 * (n - 1) + 2];
+    }
+    cp_async_commit();
+    // (A) column owner: dE[:, d] += dEs[:, d]; k_d; dk_d = sum_i a_i dE[i][d]; d ebar_d
+    float p4 = 0.f;
+    for (int d = threadIdx.x; d < D; d += RS_THREADS) {
+      const float ebd = ebr[d];
+      const float kk = w4 * ebd;
+      kvs[d] = kk > 0.f ? kk : 0.f;
+      float s = 0.f;
+      for (int i = 0; i < ni; ++i) {
+        const float g = dE[i * D + d] + dEs[i * D + d];
+        dE[i * D + d] = g;
+        s = fmaf(av[i], g, s);
+      }
+      const float dpre = kk > 0.f ? s : 0.f;
+      p4 = fmaf(dpre, ebd, p4);
+      deb[d] = dpre * w4 + debo[d];
+    }
+    p4 = warp_sum(p4);
+    if (lane == 0) pw4[warp] = p4;
+    __syncthreads();
+    // (B) one warp per entity row: da_i = dE_i . (k - Ep_i), dan_i = d ebar . Ep_i
+    for (int i = warp; i < ni; i += RS_THREADS / 32) {
+      float s = 0.f, t = 0.f;
+      for (int d = lane; d < D; d += 32) {
+        const float epd = Ep[i * D + d];
+        s = fmaf(dE[i * D + d], kvs[d] - epd, s);
+        t = fmaf(deb[d], epd, t);
+      }
+      s = warp_sum(s);
+      t = warp_sum(t);
+      if (lane == 0) { da[i] = s; dan[i] = t; }
+    }
+    __syncthreads();
+    // (C) the small per-ingredient chain, recomputed by every thread: asum, tdot, then dz_i on the fly
+    const float mx = fmaxf(l0, fmaxf(l1, l2));
+    const float x0 = expf(l0 - mx), x1 = expf(l1 - mx), x2 = expf(l2 - mx);
+    const float c0 = x0 / (x0 + x1 + x2), c1 = x1 / (x0 + x1 + x2), c2 = x2 / (x0 + x1 + x2);
+    float asum = 0.f;
+    for (int i = 0; i < ni; ++i) asum += av[i];
+    float tdot = 0.f;
+    for (int i = 0; i < ni; ++i) tdot = fmaf(dan[i], av[i] / asum, tdot);
+    if (threadIdx.x == 0) {
+      float p0 = 0.f, p1 = 0.f, t4 = 0.f;
+      for (int i = 0; i < ni; ++i) {
+        const float dai = da[i] + (dan[i] - tdot) / asum;
+        p0 = fmaf(dai, ev[i], p0);
+        p1 = fmaf(dai, epv[i], p1);
+      }
+      const float dot = c0 * p0 + c1 * p1;       // dc2 = 0
+      dclog[3 * n + 0] = c0 * (p0 - dot);
+      dclog[3 * n + 1] = c1 * (p1 - dot);
+      dclog[3 * n + 2] = c2 * (0.f - dot);
+      for (int k = 0; k < RS_THREADS / 32; ++k) t4 += pw4[k];
+      dw4s[n] = t4;
+    }
+    if ((int)threadIdx.x < ni) {
+      const int i = threadIdx.x;
+      den_out[i] = c1 * (da[i] + (dan[i] - tdot) / asum);      // read by step n - 1 (other buffer: no hazard with den_in)
+    }
+    // (D) column owner: dw2v_d = sum_i dz_i Ep[i][d]; dE_prev[:, d] = (1 - a_i) dE + an_i d ebar_d + dz_i w_d
+    for (int d = threadIdx.x; d < D; d += RS_THREADS) {
+      const float debd = deb[d], wd = w[d];
+      float s = 0.f;
+      for (int i = 0; i < ni; ++i) {
+        const float ai = av[i], ei = ev[i];
+        const float dai = da[i] + (dan[i] - tdot) / asum;
+        const float dei = c0 * dai + dev_[i] + den_in[i];
+        const float dzi = dei * ei * (1.f - ei);
+        s = fmaf(dzi, Ep[i * D + d], s);
+        dE[i * D + d] = (1.f - ai) * dE[i * D + d] + (ai / asum) * debd + dzi * wd;
+      }
+      dw2v[(long long)n * D + d] = s;
+    }
+    store_small(cur ^ 1);
+    w4 = w4n; l0 = l0n; l1 = l1n; l2 = l2n;
+    cp_async_wait_all();
+    __syncthreads();
+  }
+  for (int i = threadIdx.x; i < ni * D; i += RS_THREADS) dE0[(long long)g0 * D + i] = dE[i];
+}
+
+// SVPC_REASONER_PIPE=0 keeps the un-pipelined kernels (also the fallback when the double buffers do not fit)
+static bool reasoner_pipelined() {
+  static int on = -1;
+  if (on < 0) {
+    const char* e = getenv("SVPC_REASONER_PIPE");
+    on = e ? (atoi(e) != 0) : 1;
+  }
+  return on != 0;
+}
+
+extern "C" int svpc_reasoner_fwd(int B, int D, int max_ni, int max_steps_hint, const float* E0, const int* cu_ingr, const int* cu_steps,
                                  const int* clip_ent_off, const float* w2v, const float* clog, const float* w4s,
                                  float* ent, float* ebar, float* Es, float* a_saved, svpc_stream_t stream) {
   if (B <= 0) return SVPC_OK;
+  // (ebar has one row per clip: its row count bounds the clips of any one video)
+  const int max_steps = max_steps_hint > 0 ? max_steps_hint : 0;
+  const size_t smem_p = sizeof(float) * ((size_t)max_ni * D + (size_t)max_steps * D + 2 * (size_t)max_ni);
+  if (reasoner_pipelined() && D % 4 == 0 && max_steps > 0 && smem_p <= 220 * 1024) {
+    cudaFuncSetAttribute(reasoner_fwd_pipe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_p);
+    svpc_launch(reasoner_fwd_pipe_kernel, B, RS_THREADS, smem_p, (cudaStream_t)stream, D, max_ni, max_steps, E0, cu_ingr, cu_steps,
+                clip_ent_off, w2v, clog, w4s, ent, ebar, Es, a_saved);
+    return svpc_check_launch("reasoner_fwd");
+  }
   const size_t smem = sizeof(float) * ((size_t)max_ni * D + D + 4 * (size_t)max_ni);
   SVPC_REQUIRE(smem <= 220 * 1024, "reasoner_fwd: %d ingredients x %d do not fit in shared memory", max_ni, D);
   cudaFuncSetAttribute(reasoner_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -229,6 +502,13 @@ extern "C" int svpc_reasoner_bwd(int B, int D, int max_ni, const float* E0, cons
                                  const float* d_ent, const float* d_ebar, const float* d_Es, float* dE0, float* dw2v,
                                  float* dclog, float* dw4s, svpc_stream_t stream) {
   if (B <= 0) return SVPC_OK;
+  const size_t smem_p = sizeof(float) * (5 * (size_t)max_ni * D + 8 * (size_t)D + 12 * (size_t)max_ni + 32);
+  if (reasoner_pipelined() && D % 4 == 0 && smem_p <= 220 * 1024) {
+    cudaFuncSetAttribute(reasoner_bwd_pipe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_p);
+    svpc_launch(reasoner_bwd_pipe_kernel, B, RS_THREADS, smem_p, (cudaStream_t)stream, D, max_ni, E0, cu_ingr, cu_steps,
+                clip_ent_off, w2v, clog, w4s, ent, ebar, Es, a_saved, d_ent, d_ebar, d_Es, dE0, dw2v, dclog, dw4s);
+    return svpc_check_launch("reasoner_bwd");
+  }
   const size_t smem = sizeof(float) * (2 * (size_t)max_ni * D + 3 * (size_t)D + 5 * (size_t)max_ni);
   SVPC_REQUIRE(smem <= 220 * 1024, "reasoner_bwd: %d ingredients x %d do not fit in shared memory", max_ni, D);
   cudaFuncSetAttribute(reasoner_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

@@ -191,25 +191,45 @@ __global__ void __launch_bounds__(256) ln_fwd_warp_kernel(int rows, const TI* __
   }
 }
 
-template <typename TG, typename TP, int NCH>
+// FUSED: the LayerNorm input is y = drop(act(z)) (+ residual) with z the pre-activation of the Linear in front of it; the
+// kernel then also writes dz = dpre * dropscale(r * D + c) * act'(ref) (what that Linear's dgrad / wgrad GEMMs consume) and
+// accumulates dbias[c] = sum_r dz[r, c], so no separate activation-backward pass runs over the tensor.  ref: the Linear's
+// pre-activation (GELU) or output (sigmoid); for ReLU without a residual the LN input itself is the activation output.
+template <typename TG, typename TP, int NCH, bool FUSED>
 __global__ void __launch_bounds__(256, 2) ln_bwd_warp_kernel(int rows, const TG* __restrict__ dy, const TP* __restrict__ pre,
                                                              const float* __restrict__ mean, const float* __restrict__ rstd,
                                                              const float* __restrict__ gamma, TP* __restrict__ dpre,
-                                                             float* __restrict__ dgamma, float* __restrict__ dbeta) {
+                                                             float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                                             TP* __restrict__ dz, int act, const TP* __restrict__ ref,
+                                                             float* __restrict__ dbias, const SvpcDrop drop) {
   svpc_pdl_sync();
   constexpr int D = NCH * 256;
-  __shared__ float part[8][D];
+  extern __shared__ float ln_sm[];
+  float (*part)[D] = reinterpret_cast<float (*)[D]>(ln_sm);              // [8][D] cross-warp reduction of the column sums
+  // FUSED: the column sums of dy (dbeta) and dz (dbias) are accumulated in shared memory, lane-interleaved so that the
+  // read-modify-writes are conflict-free (slot (i * 8 + e) * 32 + lane holds column i * 256 + lane * 8 + e): the register
+  // file then holds one accumulator set (dgamma) instead of three and nothing spills
+  float* bsum = ln_sm + 8 * D + (threadIdx.x >> 5) * D;                  // this warp's [D]
+  float* zsum = ln_sm + 16 * D + (threadIdx.x >> 5) * D;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int nw = gridDim.x * 8;
-  float ag[NCH][8], ab[NCH][8];
+  const bool dropping = FUSED && drop.seed != nullptr && drop.p > 0.f;
+  const uint32_t dkey = FUSED ? svpc_drop_key(drop) : 0u;
+  const float dinv = dropping ? 1.f / (1.f - drop.p) : 1.f;
+  float ag[NCH][8], ab[FUSED ? 1 : NCH][8];
 #pragma unroll
   for (int i = 0; i < NCH; ++i)
 #pragma unroll
-    for (int e = 0; e < 8; ++e) { ag[i][e] = 0.f; ab[i][e] = 0.f; }
+    for (int e = 0; e < 8; ++e) {
+      ag[i][e] = 0.f;
+      if (!FUSED) ab[i][e] = 0.f;
+      else { bsum[(i * 8 + e) * 32 + lane] = 0.f; zsum[(i * 8 + e) * 32 + lane] = 0.f; }     // own slots only: no barrier
+    }
   for (int r = blockIdx.x * 8 + warp; r < rows; r += nw) {
     const long long base = (long long)r * D;
     const float mu = mean[r], rs = rstd[r];
     float d[NCH][8], xh[NCH][8];
+    uint32_t pos = 0;                             // FUSED + ReLU: bit (i * 8 + e) = LN input > 0
     float s1 = 0.f, s2 = 0.f;
 #pragma unroll
     for (int i = 0; i < NCH; ++i) {
@@ -220,9 +240,11 @@ __global__ void __launch_bounds__(256, 2) ln_bwd_warp_kernel(int rows, const TG*
       ld8(gamma + c, gm);                       // L1-resident
 #pragma unroll
       for (int e = 0; e < 8; ++e) {
+        if (FUSED) pos |= (xh[i][e] > 0.f ? 1u : 0u) << (i * 8 + e);
         xh[i][e] = (xh[i][e] - mu) * rs;
         ag[i][e] = fmaf(d[i][e], xh[i][e], ag[i][e]);
-        ab[i][e] += d[i][e];
+        if (FUSED) bsum[(i * 8 + e) * 32 + lane] += d[i][e];
+        else ab[i][e] += d[i][e];
         d[i][e] *= gm[e];                       // g = dy * gamma
         s1 += d[i][e];
         s2 = fmaf(d[i][e], xh[i][e], s2);
@@ -231,26 +253,75 @@ __global__ void __launch_bounds__(256, 2) ln_bwd_warp_kernel(int rows, const TG*
     const float m1 = warp_sum(s1) * (1.0f / D), m2 = warp_sum(s2) * (1.0f / D);
 #pragma unroll
     for (int i = 0; i < NCH; ++i) {
+      const int c = i * 256 + lane * 8;
       float o[8];
 #pragma unroll
       for (int e = 0; e < 8; ++e) o[e] = rs * (d[i][e] - m1 - xh[i][e] * m2);
-      st8(dpre + base + i * 256 + lane * 8, o);
+      st8(dpre + base + c, o);
+      if (FUSED) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) o[e] = rnd_as(o[e], dpre);          // the stored gradient is what the un-fused pass would read
+        if (dropping) {
+#pragma unroll
+          for (int e = 0; e < 8; e += 2) {
+            float s0, s1_;
+            svpc_drop_scale2(dkey, drop.p, dinv, (unsigned long long)(base + c + e), s0, s1_);
+            o[e] *= s0; o[e + 1] *= s1_;
+          }
+        }
+        if (act == SVPC_ACT_RELU && !ref) {
+#pragma unroll
+          for (int e = 0; e < 8; ++e) o[e] = ((pos >> (i * 8 + e)) & 1u) ? o[e] : 0.f;
+        } else if (act != SVPC_ACT_NONE) {
+          float y[8];
+          ld8(ref + base + c, y);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            if (act == SVPC_ACT_RELU) o[e] = y[e] > 0.f ? o[e] : 0.f;
+            else if (act == SVPC_ACT_GELU) o[e] *= svpc_gelu_grad(y[e]);
+            else o[e] *= y[e] * (1.f - y[e]);
+          }
+        }
+        st8(dz + base + c, o);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) zsum[(i * 8 + e) * 32 + lane] += rnd_as(o[e], dz);
+      }
     }
   }
   // column sums: across the CTA's warps through shared memory, then one red.global per column per CTA
+  __syncthreads();
 #pragma unroll
-  for (int pass = 0; pass < 2; ++pass) {
+  for (int i = 0; i < NCH; ++i)
+#pragma unroll
+    for (int e = 0; e < 8; ++e) part[warp][i * 256 + lane * 8 + e] = ag[i][e];
+  __syncthreads();
+  for (int c = threadIdx.x; c < D; c += 256) {
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) t += part[w][c];
+    atomicAdd(dgamma + c, t);
+  }
+  if (!FUSED) {
     __syncthreads();
 #pragma unroll
     for (int i = 0; i < NCH; ++i)
 #pragma unroll
-      for (int e = 0; e < 8; ++e) part[warp][i * 256 + lane * 8 + e] = pass == 0 ? ag[i][e] : ab[i][e];
+      for (int e = 0; e < 8; ++e) part[warp][i * 256 + lane * 8 + e] = ab[i][e];
     __syncthreads();
     for (int c = threadIdx.x; c < D; c += 256) {
       float t = 0.f;
 #pragma unroll
       for (int w = 0; w < 8; ++w) t += part[w][c];
-      atomicAdd((pass == 0 ? dgamma : dbeta) + c, t);
+      atomicAdd(dbeta + c, t);
+    }
+  } else {
+    for (int c = threadIdx.x; c < D; c += 256) {       // (bsum / zsum were complete before the barriers above)
+      const int slot = ((c >> 8) * 8 + (c & 7)) * 32 + ((c & 255) >> 3);      // column c = i * 256 + lane * 8 + e
+      float tb = 0.f, tz = 0.f;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) { tb += ln_sm[8 * D + w * D + slot]; tz += ln_sm[16 * D + w * D + slot]; }
+      atomicAdd(dbeta + c, tb);
+      if (dbias) atomicAdd(dbias + c, tz);
     }
   }
 }
@@ -271,30 +342,44 @@ __global__ void __launch_bounds__(256) act_bwd_vec_kernel(int rows, int cols, co
 #pragma unroll
   for (int e = 0; e < 8; ++e) acc[e] = 0.f;
   if (c0 < cols) {
-    for (int r = blockIdx.y * 8 + ty; r < rows; r += gridDim.y * 8) {
-      const long long o = (long long)r * cols + c0;
-      float g[8], y[8];
-      ld8(dy + o, g);
-      if (dropping) {                    // cols % 8 == 0 and c0 % 8 == 0: o is even, (o + e, o + e + 1) are aligned pairs
+    // four rows per iteration: eight independent 16-byte loads in flight per thread (the kernel is a pure stream)
+    const int rstep = gridDim.y * 8;
+    for (int r0 = blockIdx.y * 8 + ty; r0 < rows; r0 += 4 * rstep) {
+      float g[4][8], y[4][8];
 #pragma unroll
-        for (int e = 0; e < 8; e += 2) {
-          float s0, s1;
-          svpc_drop_scale2(dkey, drop.p, dinv, (unsigned long long)(o + e), s0, s1);
-          g[e] *= s0; g[e + 1] *= s1;
+      for (int u = 0; u < 4; ++u) {
+        const int r = r0 + u * rstep;
+        if (r < rows) {
+          const long long o = (long long)r * cols + c0;
+          ld8(dy + o, g[u]);
+          if (act != SVPC_ACT_NONE) ld8(ref + o, y[u]);
         }
       }
-      if (act != SVPC_ACT_NONE) {
-        ld8(ref + o, y);
 #pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          if (act == SVPC_ACT_RELU) g[e] = y[e] > 0.f ? g[e] : 0.f;
-          else if (act == SVPC_ACT_GELU) g[e] *= svpc_gelu_grad(y[e]);
-          else g[e] *= y[e] * (1.f - y[e]);
+      for (int u = 0; u < 4; ++u) {
+        const int r = r0 + u * rstep;
+        if (r >= rows) break;
+        const long long o = (long long)r * cols + c0;
+        if (dropping) {                    // cols % 8 == 0 and c0 % 8 == 0: o is even, (o + e, o + e + 1) are aligned pairs
+#pragma unroll
+          for (int e = 0; e < 8; e += 2) {
+            float s0, s1;
+            svpc_drop_scale2(dkey, drop.p, dinv, (unsigned long long)(o + e), s0, s1);
+            g[u][e] *= s0; g[u][e + 1] *= s1;
+          }
         }
-      }
-      if (dz) st8(dz + o, g);
+        if (act != SVPC_ACT_NONE) {
 #pragma unroll
-      for (int e = 0; e < 8; ++e) acc[e] += g[e];
+          for (int e = 0; e < 8; ++e) {
+            if (act == SVPC_ACT_RELU) g[u][e] = y[u][e] > 0.f ? g[u][e] : 0.f;
+            else if (act == SVPC_ACT_GELU) g[u][e] *= svpc_gelu_grad(y[u][e]);
+            else g[u][e] *= y[u][e] * (1.f - y[u][e]);
+          }
+        }
+        if (dz) st8(dz + o, g[u]);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) acc[e] += g[u][e];
+      }
     }
   }
 #pragma unroll
@@ -314,7 +399,7 @@ static inline bool rw_al16(const void* p) { return ((uintptr_t)p & 15) == 0; }
 static int act_bwd_vec_launch(int rows, int cols, const void* dy, const void* ref, int dt, int act, void* dz, float* dbias,
                               SvpcDrop drop, cudaStream_t st) {
   const int gx = svpc_cdiv(cols, 256);
-  dim3 grid(gx, svpc_imin(svpc_cdiv(rows, 8), svpc_cdiv(SVPC_NUM_SMS * 4, gx)));
+  dim3 grid(gx, svpc_imin(svpc_cdiv(rows, 32), svpc_cdiv(SVPC_NUM_SMS * 8, gx)));
   SVPC_DISPATCH(dt, T, (svpc_launch(act_bwd_vec_kernel<T>, grid, 256, 0, st, rows, cols, (const T*)dy, (const T*)ref, act, (T*)dz, dbias, drop)));
   return svpc_check_launch("act_bwd");
 }
@@ -404,24 +489,30 @@ __global__ void __launch_bounds__(RW_THREADS) ln_bwd_kernel(int rows, int D, con
                                                             const TP* __restrict__ pre, const float* __restrict__ mean,
                                                             const float* __restrict__ rstd, const float* __restrict__ gamma,
                                                             TP* __restrict__ dpre, float* __restrict__ dgamma,
-                                                            float* __restrict__ dbeta) {
+                                                            float* __restrict__ dbeta, TP* __restrict__ dz, int act,
+                                                            const TP* __restrict__ ref, float* __restrict__ dbias,
+                                                            const SvpcDrop drop) {
   svpc_pdl_sync();
   __shared__ float red[64];
-  float ag[RW_MAXPT], ab[RW_MAXPT];
+  const bool dropping = dz != nullptr && drop.seed != nullptr && drop.p > 0.f;
+  const uint32_t dkey = dz ? svpc_drop_key(drop) : 0u;
+  const float dinv = dropping ? 1.f / (1.f - drop.p) : 1.f;
+  float ag[RW_MAXPT], ab[RW_MAXPT], az[RW_MAXPT];
 #pragma unroll
-  for (int i = 0; i < RW_MAXPT; ++i) { ag[i] = 0.f; ab[i] = 0.f; }
+  for (int i = 0; i < RW_MAXPT; ++i) { ag[i] = 0.f; ab[i] = 0.f; az[i] = 0.f; }
   for (int r = blockIdx.x; r < rows; r += gridDim.x) {
     const long long base = (long long)r * D;
     const float mu = mean[r], rs = rstd[r];
-    float g[RW_MAXPT], xh[RW_MAXPT];
+    float g[RW_MAXPT], xh[RW_MAXPT], raw[RW_MAXPT];
     float s1 = 0.f, s2 = 0.f;
 #pragma unroll
     for (int i = 0; i < RW_MAXPT; ++i) {
       const int c = threadIdx.x + i * RW_THREADS;
-      g[i] = 0.f; xh[i] = 0.f;
+      g[i] = 0.f; xh[i] = 0.f; raw[i] = 0.f;
       if (c < D) {
         const float d = ldf(dy + base + c);
-        xh[i] = (ldf(pre + base + c) - mu) * rs;
+        raw[i] = ldf(pre + base + c);
+        xh[i] = (raw[i] - mu) * rs;
         g[i] = d * gamma[c];
         ag[i] += d * xh[i];
         ab[i] += d;
@@ -434,33 +525,70 @@ __global__ void __launch_bounds__(RW_THREADS) ln_bwd_kernel(int rows, int D, con
 #pragma unroll
     for (int i = 0; i < RW_MAXPT; ++i) {
       const int c = threadIdx.x + i * RW_THREADS;
-      if (c < D) stf(dpre + base + c, rs * (g[i] - m1 - xh[i] * m2));
+      if (c < D) {
+        float o = rs * (g[i] - m1 - xh[i] * m2);
+        stf(dpre + base + c, o);
+        if (dz) {
+          o = rnd_as(o, dpre);
+          if (dropping) o *= svpc_drop_scale(dkey, drop.p, dinv, (unsigned long long)(base + c));
+          if (act != SVPC_ACT_NONE) {
+            const float y = ref ? ldf(ref + base + c) : raw[i];
+            if (act == SVPC_ACT_RELU) o = y > 0.f ? o : 0.f;
+            else if (act == SVPC_ACT_GELU) o *= svpc_gelu_grad(y);
+            else o *= y * (1.f - y);
+          }
+          stf(dz + base + c, o);
+          az[i] += rnd_as(o, dz);
+        }
+      }
     }
   }
 #pragma unroll
   for (int i = 0; i < RW_MAXPT; ++i) {
     const int c = threadIdx.x + i * RW_THREADS;
-    if (c < D) { atomicAdd(dgamma + c, ag[i]); atomicAdd(dbeta + c, ab[i]); }
+    if (c < D) {
+      atomicAdd(dgamma + c, ag[i]);
+      atomicAdd(dbeta + c, ab[i]);
+      if (dz && dbias) atomicAdd(dbias + c, az[i]);
+    }
   }
 }
 
+// dz != NULL: fused activation / dropout backward of the Linear in front of the LayerNorm (see ln_bwd_warp_kernel): dz has
+// the layout and dtype of dpre, ref (optional) of pre; dbias (optional, D floats) receives the column sums of dz.
 extern "C" int svpc_ln_bwd(int rows, int D, const void* dy, int dt_dy, const void* pre, int dt_pre, const float* mean,
                            const float* rstd, const float* gamma, void* dpre, float* dgamma, float* dbeta,
-                           svpc_stream_t stream) {
+                           void* dz, int act, const void* ref, float* dbias, const unsigned int* drop_seed,
+                           unsigned int drop_site, float drop_p, svpc_stream_t stream) {
   cudaStream_t st = (cudaStream_t)stream;
   cudaMemsetAsync(dgamma, 0, sizeof(float) * D, st);
   cudaMemsetAsync(dbeta, 0, sizeof(float) * D, st);
+  if (dz && dbias) cudaMemsetAsync(dbias, 0, sizeof(float) * D, st);
   if (rows <= 0) return SVPC_OK;
   SVPC_REQUIRE(D <= RW_THREADS * RW_MAXPT, "ln_bwd: D=%d too wide", D);
-  if (D == 768 && rw_al16(dy) && rw_al16(pre) && rw_al16(dpre) && rw_al16(gamma)) {
+  SVPC_REQUIRE(dz || (act == SVPC_ACT_NONE && !ref), "ln_bwd: act / ref need the dz output");
+  SVPC_REQUIRE(drop_p >= 0.f && drop_p < 1.f, "ln_bwd: dropout p=%f outside [0, 1)", drop_p);
+  const SvpcDrop drop{(dz && drop_p > 0.f) ? drop_seed : nullptr, drop_site, drop_p};
+  if (D == 768 && rw_al16(dy) && rw_al16(pre) && rw_al16(dpre) && rw_al16(gamma) && rw_al16(dz) && rw_al16(ref)) {
     const int g2 = svpc_imin(svpc_cdiv(rows, 8), SVPC_NUM_SMS * 4);
-    SVPC_DISPATCH(dt_dy, TG, SVPC_DISPATCH(dt_pre, TP, (svpc_launch(ln_bwd_warp_kernel<TG, TP, 3>, g2, 256, 0, st, 
-        rows, (const TG*)dy, (const TP*)pre, mean, rstd, gamma, (TP*)dpre, dgamma, dbeta))));
+    if (dz) {
+      const size_t smem = sizeof(float) * 24 * 768;
+      SVPC_DISPATCH(dt_dy, TG, SVPC_DISPATCH(dt_pre, TP, {
+        static bool attr = false;
+        if (!attr) { cudaFuncSetAttribute(ln_bwd_warp_kernel<TG, TP, 3, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); attr = true; }
+        svpc_launch(ln_bwd_warp_kernel<TG, TP, 3, true>, g2, 256, smem, st, rows, (const TG*)dy, (const TP*)pre, mean, rstd, gamma,
+                    (TP*)dpre, dgamma, dbeta, (TP*)dz, act, (const TP*)ref, dbias, drop);
+      }));
+    } else {
+      SVPC_DISPATCH(dt_dy, TG, SVPC_DISPATCH(dt_pre, TP, (svpc_launch(ln_bwd_warp_kernel<TG, TP, 3, false>, g2, 256, sizeof(float) * 8 * 768, st,
+          rows, (const TG*)dy, (const TP*)pre, mean, rstd, gamma, (TP*)dpre, dgamma, dbeta, (TP*)nullptr, 0, (const TP*)nullptr,
+          (float*)nullptr, drop))));
+    }
     return svpc_check_launch("ln_bwd");
   }
   const int grid = svpc_imin(rows, SVPC_NUM_SMS * 4);
-  SVPC_DISPATCH(dt_dy, TG, SVPC_DISPATCH(dt_pre, TP, (svpc_launch(ln_bwd_kernel<TG, TP>, grid, RW_THREADS, 0, st, 
-      rows, D, (const TG*)dy, (const TP*)pre, mean, rstd, gamma, (TP*)dpre, dgamma, dbeta))));
+  SVPC_DISPATCH(dt_dy, TG, SVPC_DISPATCH(dt_pre, TP, (svpc_launch(ln_bwd_kernel<TG, TP>, grid, RW_THREADS, 0, st,
+      rows, D, (const TG*)dy, (const TP*)pre, mean, rstd, gamma, (TP*)dpre, dgamma, dbeta, (TP*)dz, act, (const TP*)ref, dbias, drop))));
   return svpc_check_launch("ln_bwd");
 }
 

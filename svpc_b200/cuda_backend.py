@@ -65,12 +65,43 @@ def _mat_strides(t):
     return s0, s1
 
 
+class Split2:
+    """An fp32 matrix as two bf16 planes, x = hi + lo (hi = bf16(x), lo = bf16(x - hi)): the operand format of the fp32
+    path's tensor-core route (``svpc_gemm_split``).  ``src`` is the fp32 matrix itself (the FFMA kernel's operand when a
+    problem is not eligible for the tcgen05 kernel).  Views (.t(), slices) apply to all three."""
+    __slots__ = ("hi", "lo", "src")
+    dtype = torch.float32
+    is_cuda = True
+
+    def __init__(self, hi, lo, src):
+        self.hi, self.lo, self.src = hi, lo, src
+
+    @property
+    def shape(self):
+        return self.src.shape
+
+    @property
+    def device(self):
+        return self.src.device
+
+    def t(self):
+        return Split2(self.hi.t(), self.lo.t(), self.src.t())
+
+    def __getitem__(self, idx):
+        return Split2(self.hi[idx], self.lo[idx], self.src[idx])
+
+
 class CudaBackend:
     name = "cuda-sm100a"
 
     def __init__(self):
         self.lib = load_library()
         self.gemm_route = GEMM_AUTO
+        # fp32 (parity) path: contractions that fit the tcgen05 kernel run there on split-bf16 operands (3 passes, fp32
+        # accumulation); SVPC_FP32_TC=0 keeps every fp32 GEMM on the FFMA kernel
+        self.tc3 = os.environ.get("SVPC_FP32_TC", "1") != "0"
+        # ... unless they are tiny (M*N*K below this): the step-level modules (192 rows) gain nothing from the tensor cores
+        self.tc3_min_work = float(os.environ.get("SVPC_FP32_TC_MIN_WORK", "0"))
         self._ptr_cache = {}
         self._w_cache = {}
         self.timing = None
@@ -136,19 +167,71 @@ class CudaBackend:
         self.lib.svpc_reset_launch_count()
 
     # ------------------------------------------------------------------ dense
+    # ---- split-fp32 operands (the parity path on the tensor cores)
+    def _split_shape_ok(self, M, N, K):
+        return M >= 64 and N >= 16 and K >= 32 and float(M) * N * K >= self.tc3_min_work
+
+    def split2(self, x):
+        """fp32 2-D view with one unit stride -> Split2 (planes in the same orientation, row pitch padded to 16 bytes)."""
+        if isinstance(x, Split2):
+            return x
+        self._chk(x)
+        assert x.dtype == torch.float32 and x.dim() == 2
+        if x.shape[1] != 1 and x.stride(1) != 1 and x.stride(0) == 1:
+            return self.split2(x.t()).t()
+        if x.shape[1] > 1 and x.stride(1) != 1:
+            x = x.contiguous()
+        R, Cc = x.shape
+        ld = (Cc + 7) // 8 * 8
+        planes = torch.empty(2, R, ld, dtype=torch.bfloat16, device=x.device) if ld == Cc else \
+            torch.zeros(2, R, ld, dtype=torch.bfloat16, device=x.device)
+        self.split2_into(x, planes)
+        return Split2(planes[0, :, :Cc], planes[1, :, :Cc], x)
+
+    def split2_into(self, x, planes):
+        """planes (2, R, ld) bf16 <- hi / lo of x (R, C) fp32 (row pitch x.stride(0))."""
+        R, Cc = x.shape
+        self._call("svpc_split_bf16", R, Cc, _ptr(x), _ll(x.stride(0) if R > 1 else Cc), _ptr(planes[0]), _ptr(planes[1]),
+                   _ll(planes.stride(1)))
+
+    def maybe_split(self, x):
+        """Split an fp32 activation that is going to be a tensor-core GEMM operand (rows >= 64, columns >= 32); anything
+        else is returned unchanged."""
+        if self.tc3 and self.gemm_route != GEMM_SIMT and isinstance(x, torch.Tensor) and x.dtype == torch.float32 and \
+                x.dim() == 2 and x.shape[0] >= 64 and x.shape[1] >= 32:
+            return self.split2(x)
+        return x
+
     def gemm(self, a, bt, out_dtype, bias=None, act=0, residual=None, out=None, accumulate=False, want_pre=False,
-             route=None, drop=None):
-        """out[M,N] = act(a[M,K] @ bt[N,K]^T + bias) + residual.  a / bt may be any 2-D views with one unit stride."""
-        self._chk(a, bt, bias, residual, out)
+             route=None, drop=None, grad_act=None):
+        """out[M,N] = act(a[M,K] @ bt[N,K]^T + bias) + residual.  a / bt may be any 2-D views with one unit stride, or
+        Split2 operands (fp32 on the tensor cores).  ``grad_act`` = (act code, ref (M, N) of the output dtype): the result
+        is finally multiplied by act'(ref) (an input-gradient GEMM that writes the previous Linear's dz)."""
+        route = self.gemm_route if route is None else route
+        a_s, b_s = isinstance(a, Split2), isinstance(bt, Split2)
         M, K = a.shape
         N = bt.shape[0]
         assert bt.shape[1] == K, (a.shape, bt.shape)
+        both_f32 = a.dtype == torch.float32 and bt.dtype == torch.float32
+        if (a_s or b_s or (self.tc3 and both_f32)) and route != GEMM_SIMT and self._split_shape_ok(M, N, K) and M > 0 and N > 0 \
+                and both_f32:
+            sa_, sb_ = self.split2(a), self.split2(bt)
+            sa, sb = _mat_strides(sa_.hi), _mat_strides(sb_.hi)
+            if self.lib.svpc_gemm_split_eligible(M, N, K, _ll(sa[0]), _ll(sa[1]), _ll(sb[0]), _ll(sb[1])):
+                return self._gemm_split(sa_, sb_, M, N, K, sa, sb, out_dtype, bias, act, residual, out, accumulate, want_pre, drop,
+                                        grad_act)
+        if a_s:
+            a = a.src
+        if b_s:
+            bt = bt.src
+        self._chk(a, bt, bias, residual, out)
         if out is None:
             out = torch.empty(M, N, dtype=out_dtype, device=a.device)
         assert out.shape == (M, N) and (N == 1 or out.stride(1) == 1)
         pre = torch.empty(M, N, dtype=out.dtype, device=a.device) if want_pre else None
         if residual is not None:
             assert residual.dtype == out.dtype and residual.shape == (M, N) and (N == 1 or residual.stride(1) == 1)
+        gref, gact = self._grad_act(grad_act, out, M, N)
         if M > 0 and N > 0:
             sa, sb = _mat_strides(a), _mat_strides(bt)
             self._call("svpc_gemm", M, N, K,
@@ -158,8 +241,35 @@ class CudaBackend:
                        _ptr(bias), int(act),
                        _ptr(residual), _ll(residual.stride(0) if residual is not None else 0),
                        _ptr(pre), _ll(N),
-                       int(bool(accumulate)), int(self.gemm_route if route is None else route), *_drop(drop),
+                       int(bool(accumulate)), int(route), *_drop(drop),
+                       _ptr(gref), _ll(gref.stride(0) if gref is not None else 0), int(gact),
                        tag=None if self.timing is None else self._gemm_tag(M, N, K, a, bt, out, sa, sb))
+        return (out, pre) if want_pre else out
+
+    @staticmethod
+    def _grad_act(grad_act, out, M, N):
+        if grad_act is None:
+            return None, 0
+        gact, gref = grad_act
+        assert gref.dtype == out.dtype and gref.shape == (M, N) and (N == 1 or gref.stride(1) == 1), (gref.dtype, out.dtype)
+        return gref, gact
+
+    def _gemm_split(self, a, bt, M, N, K, sa, sb, out_dtype, bias, act, residual, out, accumulate, want_pre, drop,
+                    grad_act=None):
+        self._chk(a.hi, bt.hi, bias, residual, out)
+        if out is None:
+            out = torch.empty(M, N, dtype=out_dtype, device=a.device)
+        assert out.shape == (M, N) and (N == 1 or out.stride(1) == 1)
+        pre = torch.empty(M, N, dtype=out.dtype, device=a.device) if want_pre else None
+        if residual is not None:
+            assert residual.dtype == out.dtype and residual.shape == (M, N) and (N == 1 or residual.stride(1) == 1)
+        gref, gact = self._grad_act(grad_act, out, M, N)
+        self._call("svpc_gemm_split", M, N, K, _ptr(a.hi), _ptr(a.lo), _ll(sa[0]), _ll(sa[1]),
+                   _ptr(bt.hi), _ptr(bt.lo), _ll(sb[0]), _ll(sb[1]),
+                   _ptr(out), _DT[out.dtype], _ll(out.stride(0)), _ptr(bias), int(act),
+                   _ptr(residual), _ll(residual.stride(0) if residual is not None else 0), _ptr(pre), _ll(N),
+                   int(bool(accumulate)), *_drop(drop), _ptr(gref), _ll(gref.stride(0) if gref is not None else 0), int(gact),
+                   tag=None if self.timing is None else f"gemm_tc3:{M}x{N}x{K}:{'T' if sa[1] != 1 else 'N'}{'T' if sb[1] != 1 else 'N'}")
         return (out, pre) if want_pre else out
 
     def _gemm_tag(self, M, N, K, a, bt, out, sa, sb):
@@ -256,15 +366,28 @@ class CudaBackend:
                    _ptr(pre if res is not None else None), _ptr(mean), _ptr(rstd))
         return y, pre, mean, rstd
 
-    def ln_bwd(self, dy, pre, mean, rstd, gamma):
+    def ln_bwd(self, dy, pre, mean, rstd, gamma, fuse=None):
+        """``fuse`` = (act, ref or None, drop or None, want_dbias): also produce dz = dpre * dropscale * act'(ref) and its
+        column sums - the activation / dropout backward of the Linear in front of the LayerNorm, in the same pass."""
         self._chk(dy, pre)
         dy = self._c(dy)
         rows, D = dy.shape
         dpre = torch.empty_like(pre)
         dgamma = torch.empty(D, dtype=torch.float32, device=dy.device)
         dbeta = torch.empty(D, dtype=torch.float32, device=dy.device)
+        dz = dbias = ref = None
+        act, drop = 0, None
+        if fuse is not None:
+            act, ref, drop, want_dbias = fuse
+            dz = torch.empty_like(pre)
+            dbias = torch.empty(D, dtype=torch.float32, device=dy.device) if want_dbias else None
+            if ref is not None:
+                ref = self._c(ref)
+                assert ref.dtype == pre.dtype and ref.shape == pre.shape
         self._call("svpc_ln_bwd", rows, D, _ptr(dy), _DT[dy.dtype], _ptr(pre), _DT[pre.dtype], _ptr(mean), _ptr(rstd),
-                   _ptr(gamma), _ptr(dpre), _ptr(dgamma), _ptr(dbeta))
+                   _ptr(gamma), _ptr(dpre), _ptr(dgamma), _ptr(dbeta), _ptr(dz), int(act), _ptr(ref), _ptr(dbias), *_drop(drop))
+        if fuse is not None:
+            return dpre, dgamma, dbeta, dz, dbias
         return dpre, dgamma, dbeta
 
     def index_colsum(self, dy, ids, nbins):
@@ -432,7 +555,8 @@ class CudaBackend:
         a = torch.empty(NE, dtype=torch.float32, device=E0.device)
         ebar = torch.empty(Nc, D, dtype=torch.float32, device=E0.device)
         Es = torch.empty(NE, D, dtype=torch.float32, device=E0.device)
-        self._call("svpc_reasoner_fwd", B, D, max_ni, _ptr(E0), _ptr(cu_ingr), _ptr(cu_steps), _ptr(clip_ent_off),
+        self._call("svpc_reasoner_fwd", B, D, max_ni, int(lay.get("max_steps", 0)), _ptr(E0), _ptr(cu_ingr), _ptr(cu_steps),
+                   _ptr(clip_ent_off),
                    _ptr(w2v), _ptr(clog), _ptr(w4s), _ptr(ent), _ptr(ebar), _ptr(Es), _ptr(a))
         return ent, ebar, Es, (a,)
 

@@ -53,6 +53,8 @@ class GradAllReducer:
         self._launched[bi] = True
         if not params:
             return
+        from . import functional as Fn
+        Fn.WGRAD.join()          # weight gradients are produced on a side stream: the flatten below reads them on this one
         # one flat bucket, every tensor's slot padded to 16 bytes so that the views handed back as .grad keep the alignment
         # the vectorised optimiser kernels want; the pad elements are never read
         offs, total = [], 0

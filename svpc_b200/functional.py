@@ -7,6 +7,7 @@ host: every tensor operation on activations is a backend (CUDA) call.
 from __future__ import annotations
 
 import weakref
+from contextlib import nullcontext as _nullcontext
 
 import torch
 from torch.autograd import Function
@@ -76,6 +77,26 @@ class WeightCache:
         self.store[key] = [ver, t, [weakref.ref(w) for w in ws], dtype]
         return t
 
+    def get_split(self, ws):
+        """The (concatenated) fp32 weight as split-bf16 planes (``Split2``): operand of the fp32 path's tensor-core route.
+        Cached and refreshed in place like the compute-dtype copies."""
+        from .cuda_backend import Split2
+        src = self.get(ws, torch.float32)
+        key = tuple(id(w) for w in ws) + ("split2",)
+        ver = self._version(ws)
+        hit = self.store.get(key)
+        N, K = src.shape
+        ld = (K + 7) // 8 * 8
+        if hit is None or self._params(hit) is None or hit[1].shape != (2, N, ld) or hit[1].device != src.device:
+            self._purge()
+            hit = self.store[key] = [None, torch.zeros(2, N, ld, dtype=torch.bfloat16, device=src.device),
+                                     [weakref.ref(w) for w in ws], "split2"]
+        if hit[0] != ver:
+            with torch.no_grad():
+                be().split2_into(src, hit[1])
+            hit[0] = ver
+        return Split2(hit[1][0, :, :K], hit[1][1, :, :K], src)
+
     def invalidate(self):
         """Mark every entry stale but keep its buffer (next ``refresh_all`` rewrites them in place)."""
         for e in self.store.values():
@@ -87,15 +108,18 @@ class WeightCache:
 
     def refresh_all(self, launch=True):
         """One launch per compute dtype for all entries whose parameters changed since they were cast."""
-        stale = []
+        stale, splits = [], []
         for k, e in self.store.items():
             ws = self._params(e)
             if ws is None or e[0] == self._version(ws):
                 continue
+            if e[3] == "split2":
+                splits.append((e, ws))
+                continue
             if all(w.is_cuda and w.dtype == torch.float32 and w.dim() <= 2 and w.is_contiguous() for w in ws) and \
                     e[1].device == ws[0].device:
                 stale.append((k, e, ws))
-        if not stale or not hasattr(be(), "cast_multi"):
+        if not hasattr(be(), "cast_multi"):
             return
         for dtype in {e[3] for _, e, _ in stale}:
             group = [(k, e, ws) for k, e, ws in stale if e[3] == dtype]
@@ -123,10 +147,21 @@ class WeightCache:
                 be().cast_multi(tab, dtype, self.CHUNK)
                 for _, e, ws in group:
                     e[0] = self._version(ws)
+        if launch:
+            # split-bf16 planes of the fp32 path: one split launch per entry, from the (just refreshed) fp32 source
+            for e, ws in splits:
+                if all(w.is_cuda for w in ws):
+                    with torch.no_grad():
+                        be().split2_into(self.get(ws, torch.float32), e[1])
+                    e[0] = self._version(ws)
 
     def buffers(self):
-        """Every cached tensor (a captured graph keeps them alive: it reads and rewrites their addresses)."""
-        return [e[1] for e in self.store.values()]
+        """Every cached tensor and every device table of the multi-tensor refresh (a captured graph keeps them alive: it
+        reads and rewrites their addresses, and its captured refresh launch reads the pointer tables)."""
+        out = [e[1] for e in self.store.values()]
+        for tab in self._tables.values():
+            out += [v for v in tab.values() if isinstance(v, torch.Tensor)]
+        return out
 
     def clear(self):
         self.store.clear()
@@ -134,10 +169,86 @@ class WeightCache:
 
 
 WEIGHTS = WeightCache()
+# fused backward hand-offs (``Link``); SVPC_LINKS=0 falls back to one element-wise pass per activation / fan-out
+import os as _os
+LINKS = _os.environ.get("SVPC_LINKS", "1") != "0"
+# fusing the activation / dropout backward into ln_bwd (grad_link=) saves one read of the gradient but makes the LayerNorm
+# backward kernel carry a third accumulator set: measured slower (34 us against 11.5 + 14 us at 19200 x 768), so off by default
+LN_FUSE = _os.environ.get("SVPC_LN_FUSE", "0") != "0"
+
+
+class _WgradStream:
+    """Weight-gradient GEMMs on a second CUDA stream.
+
+    In the backward pass of a Linear the input gradient is on the critical path (the next node needs it), the weight
+    gradient is a leaf: nothing consumes it before the optimiser / the gradient all-reduce.  ``LinearFn.backward`` therefore
+    enqueues it on a side stream that waits for the operands (``fork``); the main stream goes on with the dgrad chain, so the
+    two overlap - which matters where the chain is made of kernels that leave most SMs idle (the 192-row step-level modules:
+    24-72 CTAs per GEMM, the entity-state recurrence: 16 CTAs).  The main stream re-joins once, when the backward pass ends
+    (an autograd engine callback), and before every gradient bucket is flattened for its all-reduce (``join``).  Operands are
+    kept referenced until the join so that the caching allocator cannot hand their memory to a main-stream kernel while the
+    side stream still reads it.  Works unchanged under CUDA-graph capture (the fork / join become graph edges).
+    SVPC_WGRAD_STREAM=0 keeps everything on one stream."""
+
+    def __init__(self):
+        self.enabled = _os.environ.get("SVPC_WGRAD_STREAM", "1") != "0"
+        self.streams = {}
+        self.keep = []
+        self.active = set()
+        self.cb_queued = False
+
+    def fork(self, device):
+        main = torch.cuda.current_stream(device)
+        side = self.streams.get(device)
+        if side is None:
+            side = self.streams[device] = torch.cuda.Stream(device=device)
+        if side == main:
+            return None
+        side.wait_stream(main)
+        self.active.add(device)
+        if not self.cb_queued:
+            torch.autograd.Variable._execution_engine.queue_callback(self.join)
+            self.cb_queued = True
+        return side
+
+    def join(self):
+        """The current stream of every device with outstanding side-stream work waits for it."""
+        for device in list(self.active):
+            torch.cuda.current_stream(device).wait_stream(self.streams[device])
+        self.active.clear()
+        self.keep.clear()
+        self.cb_queued = False
+
+
+class Link:
+    """Hand-off between two nodes that are neighbours in the BACKWARD pass, so that a gradient is produced in its final form
+    by the kernel that computes it instead of by extra element-wise passes (autograd's fan-out adds, activation backward):
+
+    * skip connections.  x feeds a Linear and, further on, is added back as a residual (reference model.py:232, 288, 645,
+      653).  The node that owns the residual add (``res_link=``: LinearFn with ``residual=x``, LayerNormFn with ``res=x``)
+      leaves the residual's gradient in ``res_grad`` and returns None for it; the Linear that consumes x (``in_link=``) adds
+      it in the epilogue of its input-gradient GEMM.  The producer always runs first: it is downstream of the consumer.
+    * activation / dropout backward.  A Linear with ``out_link=`` records its activation, reference tensor and dropout site;
+      whoever computes the gradient of its output - the LayerNorm behind it (``grad_link=``, fused into ``ln_bwd``) or the
+      next Linear (``in_link=``, fused into that GEMM's epilogue) - writes dz = dy * dropscale * act'(ref) and the bias
+      gradient here, and LinearFn.backward skips its own ``act_bwd`` pass."""
+    __slots__ = ("act", "ref", "drop", "has_bias", "dz", "dbias", "res_grad")
+
+    def __init__(self):
+        self.act, self.ref, self.drop, self.has_bias = ACT_NONE, None, None, False
+        self.dz = self.dbias = self.res_grad = None
+
+    def take_res_grad(self):
+        g, self.res_grad = self.res_grad, None
+        return g
+
+
+WGRAD = _WgradStream()
 
 
 class _LinMeta:
-    __slots__ = ("n_x", "n_w", "has_bias", "act", "out_dtype", "cd", "w_is_kn", "has_res", "cache", "drop")
+    __slots__ = ("n_x", "n_w", "has_bias", "act", "out_dtype", "cd", "w_is_kn", "has_res", "cache", "drop", "in_link",
+                 "out_link", "res_link")
 
     def __init__(self, **kw):
         for k, v in kw.items():
@@ -157,11 +268,17 @@ class LinearFn(Function):
         ws = args[meta.n_x:meta.n_x + meta.n_w]
         bs = args[meta.n_x + meta.n_w:]
         cd = meta.cd
-        W = WEIGHTS.get(ws, cd) if meta.cache else be().cast(ws[0].detach().contiguous(), cd)
+        split = cd == torch.float32 and getattr(be(), "tc3", False) and not meta.w_is_kn
+        if split and meta.cache:
+            W = WEIGHTS.get_split(ws)                 # fp32 path on the tensor cores: hi / lo bf16 planes, cached per version
+        else:
+            W = WEIGHTS.get(ws, cd) if meta.cache else be().cast(ws[0].detach().contiguous(), cd)
         bias = None
         if meta.has_bias:
             bias = bs[0].detach() if len(bs) == 1 else WEIGHTS.get(bs, torch.float32)
         xs_c = [x if x.dtype == cd else be().cast(x, cd) for x in xs]
+        if split:
+            xs_c = [be().maybe_split(x) for x in xs_c]   # split once, reused by the weight-gradient GEMM of the backward
         want_pre = meta.act == ACT_GELU
         if meta.w_is_kn:
             assert meta.n_x == 1 and meta.n_w == 1
@@ -186,53 +303,100 @@ class LinearFn(Function):
         ctx.shapes = [tuple(w.shape) for w in ws]
         ctx.x_dtypes = [x.dtype for x in xs]
         ref = pre if meta.act == ACT_GELU else (out if meta.act in (ACT_RELU, ACT_SIGMOID) else None)
-        ctx.save_for_backward(W, ref, *xs_c)
+        ctx.save_for_backward(ref)
+        ctx.ops = (W, xs_c)          # tensors or Split2 operands (not autograd leaves: plain references)
+        ctx.split = split
+        ctx.w_leaf = all(w.is_leaf for w in ws)
+        ctx.w_params = list(ws) if ctx.w_leaf else []
+        if meta.out_link is not None:
+            L = meta.out_link
+            L.act, L.ref, L.drop, L.has_bias = meta.act, ref, meta.drop, meta.has_bias
         return out
 
     @staticmethod
     def backward(ctx, dy):
         meta = ctx.meta
-        W, ref, *xs_c = ctx.saved_tensors
+        (ref,) = ctx.saved_tensors
+        W, xs_c = ctx.ops
         cd = meta.cd
         dy = dy.contiguous()
         need = ctx.needs_input_grad
         d_res = dy if (meta.has_res and need[1]) else None
-        if meta.act != ACT_NONE or meta.drop is not None:
+        L = meta.out_link
+        if L is not None and L.dz is not None:
+            dz, dbias = L.dz, L.dbias                                         # produced by ln_bwd / the next Linear's dgrad
+            L.dz = L.dbias = L.ref = None
+        elif meta.act != ACT_NONE or meta.drop is not None:
             dz, dbias = be().act_bwd(dy, ref, meta.act, drop=meta.drop)     # dy * dropout scale * act'
         else:
             dz = dy
             dbias = be().colsum(dy) if meta.has_bias else None
         dzc = dz if dz.dtype == cd else be().cast(dz, cd)
+        if ctx.split:
+            dzc = be().maybe_split(dzc)              # one split serves the input- and the weight-gradient GEMM
         n_x, n_w = meta.n_x, meta.n_w
+        # ---- skip-connection gradient of x: added in the epilogue of the input-gradient GEMM instead of by autograd
+        extra = None
+        if meta.res_link is not None and d_res is not None:
+            if meta.res_link is meta.in_link:
+                extra = d_res                        # residual = this Linear's own input (decoder output block, model.py:662)
+            else:
+                assert meta.res_link.res_grad is None
+                meta.res_link.res_grad = d_res
+            d_res = None
+        Lin = meta.in_link
+        grad_act = None
+        if Lin is not None:
+            if extra is None:
+                extra = Lin.take_res_grad()
+            if Lin.act != ACT_NONE and Lin.drop is None and Lin.ref is not None and n_x == 1 and need[2] and \
+                    Lin.ref.dtype == ctx.x_dtypes[0]:
+                grad_act = (Lin.act, Lin.ref)        # x = act(pre): write d(pre) directly
         # ---- input gradients
         dxs = [None] * n_x
         k0 = 0
         for j, x in enumerate(xs_c):
             k1 = k0 + x.shape[1]
             if need[2 + j]:
+                res_j = extra if j == 0 else None
+                if res_j is not None and res_j.dtype != ctx.x_dtypes[j]:
+                    res_j = res_j.to(ctx.x_dtypes[j])
                 if meta.w_is_kn:
-                    dxs[j] = be().gemm(dzc, W, ctx.x_dtypes[j])                     # dz (M,N) @ W(K,N)^T
+                    dxs[j] = be().gemm(dzc, W, ctx.x_dtypes[j], residual=res_j, grad_act=grad_act)                  # dz (M,N) @ W(K,N)^T
                 else:
-                    dxs[j] = be().gemm(dzc, W[:, k0:k1].t(), ctx.x_dtypes[j])      # dz (M,N) @ W(N,K)
+                    dxs[j] = be().gemm(dzc, W[:, k0:k1].t(), ctx.x_dtypes[j], residual=res_j, grad_act=grad_act)   # dz (M,N) @ W(N,K)
             k0 = k1
-        # ---- weight gradients (fp32, written straight into one buffer in the parameters' layout)
+        if grad_act is not None:
+            Lin.dz = dxs[0]
+            Lin.dbias = be().colsum(dxs[0]) if Lin.has_bias else None
+        # ---- weight gradients (fp32, written straight into one buffer in the parameters' layout) - on the side stream
         dws = [None] * n_w
         if any(need[2 + n_x:2 + n_x + n_w]):
             if meta.w_is_kn:
-                dws[0] = be().gemm(xs_c[0].t(), dzc.t(), torch.float32)            # (K,N) = x^T dz
+                dW = torch.empty(xs_c[0].shape[1], dzc.shape[1], dtype=torch.float32, device=dy.device)
             else:
-                Ntot = W.shape[0]
-                Ktot = W.shape[1]
-                dW = torch.empty(Ntot, Ktot, dtype=torch.float32, device=dy.device)
-                k0 = 0
-                for x in xs_c:
-                    k1 = k0 + x.shape[1]
-                    be().gemm(dzc.t(), x.t(), torch.float32, out=dW[:, k0:k1])
-                    k0 = k1
-                n0 = 0
-                for i, shp in enumerate(ctx.shapes):
-                    dws[i] = dW[n0:n0 + shp[0]]
-                    n0 += shp[0]
+                dW = torch.empty(W.shape[0], W.shape[1], dtype=torch.float32, device=dy.device)
+            # side stream only when nothing can read dW before the join: the weights are autograd leaves without an
+            # accumulated .grad (AccumulateGrad then just adopts the tensor; a non-leaf weight - the LN-folded video
+            # projection in eval mode - hands dW to further autograd nodes at once)
+            side = WGRAD.fork(dy.device) if (WGRAD.enabled and dy.is_cuda and ctx.w_leaf and
+                                             all(w.grad is None for w in ctx.w_params)) else None
+            with (torch.cuda.stream(side) if side is not None else _nullcontext()):
+                if meta.w_is_kn:
+                    be().gemm(xs_c[0].t(), dzc.t(), torch.float32, out=dW)             # (K,N) = x^T dz
+                    dws[0] = dW
+                else:
+                    k0 = 0
+                    for x in xs_c:
+                        k1 = k0 + x.shape[1]
+                        be().gemm(dzc.t(), x.t(), torch.float32, out=dW[:, k0:k1])
+                        k0 = k1
+                    n0 = 0
+                    for i, shp in enumerate(ctx.shapes):
+                        dws[i] = dW[n0:n0 + shp[0]]
+                        n0 += shp[0]
+            if side is not None:
+                WGRAD.keep.append((dzc, xs_c))       # (not dW: an extra reference would make AccumulateGrad clone it)
         dbs = []
         if meta.has_bias:
             n0 = 0
@@ -243,41 +407,66 @@ class LinearFn(Function):
 
 
 def linear(xs, ws, bs, *, act=ACT_NONE, out_dtype=None, cd=torch.float32, residual=None, w_is_kn=False, cache=True,
-           drop=None):
-    """drop = (seed tensor, site, p): nn.Dropout applied after the activation and before the residual add."""
+           drop=None, in_link=None, out_link=None, res_link=None):
+    """drop = (seed tensor, site, p): nn.Dropout applied after the activation and before the residual add.
+    in_link / out_link / res_link: see ``Link``."""
     xs = list(xs) if isinstance(xs, (list, tuple)) else [xs]
     ws = list(ws) if isinstance(ws, (list, tuple)) else [ws]
     bs = [] if bs is None else (list(bs) if isinstance(bs, (list, tuple)) else [bs])
+    if not LINKS:
+        in_link = out_link = res_link = None
     meta = _LinMeta(n_x=len(xs), n_w=len(ws), has_bias=len(bs) > 0, act=act, out_dtype=out_dtype or cd, cd=cd,
-                    w_is_kn=w_is_kn, has_res=residual is not None, cache=cache or len(ws) > 1, drop=drop)
+                    w_is_kn=w_is_kn, has_res=residual is not None, cache=cache or len(ws) > 1, drop=drop,
+                    in_link=in_link, out_link=out_link, res_link=res_link if residual is not None else None)
     return LinearFn.apply(meta, residual, *xs, *ws, *bs)
 
 
 # ------------------------------------------------------------------------------------------------
 class LayerNormFn(Function):
-    """y = LN(x (+ res)) * gamma + beta (+ pe[row % period]) (+ tt[tt_ids[row]])  (reference model.py:152-156)."""
+    """y = LN(x (+ res)) * gamma + beta (+ pe[row % period]) (+ tt[tt_ids[row]])  (reference model.py:152-156).
+    grad_link: ``Link`` of the Linear that produced x (its activation / dropout backward is fused into ln_bwd);
+    res_link: ``Link`` that takes the gradient of ``res`` (see ``Link``)."""
 
     @staticmethod
-    def forward(ctx, x, res, gamma, beta, eps, out_dtype, pe, pe_period, tt, tt_ids):
+    def forward(ctx, x, res, gamma, beta, eps, out_dtype, pe, pe_period, tt, tt_ids, grad_link=None, res_link=None):
         y, pre, mean, rstd = be().ln_fwd(x, res, gamma.detach(), beta.detach(), eps, out_dtype, pe, pe_period,
                                          None if tt is None else tt.detach(), tt_ids)
         ctx.save_for_backward(pre, mean, rstd, gamma.detach(), tt_ids)
         ctx.has_res = res is not None
         ctx.has_tt = tt is not None
         ctx.n_tt = 0 if tt is None else tt.shape[0]
+        ctx.grad_link, ctx.res_link = grad_link, (res_link if res is not None else None)
+        ctx.x_plain = res is None          # the LN input is the Linear's output itself
         return y
 
     @staticmethod
     def backward(ctx, dy):
         pre, mean, rstd, gamma, tt_ids = ctx.saved_tensors
         dy = dy.contiguous()
-        dpre, dgamma, dbeta = be().ln_bwd(dy, pre, mean, rstd, gamma)
+        L = ctx.grad_link
+        if L is not None and (L.act != ACT_NONE or L.drop is not None) and (L.ref is None or L.ref.dtype == pre.dtype):
+            ref = L.ref if not (L.act == ACT_RELU and ctx.x_plain) else None
+            if L.act == ACT_NONE:
+                ref = None
+            dpre, dgamma, dbeta, L.dz, L.dbias = be().ln_bwd(dy, pre, mean, rstd, gamma, fuse=(L.act, ref, L.drop, L.has_bias))
+        else:
+            dpre, dgamma, dbeta = be().ln_bwd(dy, pre, mean, rstd, gamma)
         dtt = be().index_colsum(dy, tt_ids, ctx.n_tt) if ctx.has_tt else None
-        return dpre, (dpre if ctx.has_res else None), dgamma, dbeta, None, None, None, None, dtt, None
+        dres = dpre if ctx.has_res else None
+        if ctx.res_link is not None and ctx.needs_input_grad[1]:
+            assert ctx.res_link.res_grad is None
+            ctx.res_link.res_grad = dpre
+            dres = None
+        return dpre, dres, dgamma, dbeta, None, None, None, None, dtt, None, None, None
 
 
-def layer_norm(x, res, gamma, beta, eps, out_dtype=None, pe=None, pe_period=0, tt=None, tt_ids=None):
-    return LayerNormFn.apply(x, res, gamma, beta, eps, out_dtype or x.dtype, pe, pe_period, tt, tt_ids)
+def layer_norm(x, res, gamma, beta, eps, out_dtype=None, pe=None, pe_period=0, tt=None, tt_ids=None, grad_link=None,
+               res_link=None):
+    if not LINKS:
+        grad_link = res_link = None
+    if not LN_FUSE:
+        grad_link = None
+    return LayerNormFn.apply(x, res, gamma, beta, eps, out_dtype or x.dtype, pe, pe_period, tt, tt_ids, grad_link, res_link)
 
 
 class EmbedLNFn(Function):
@@ -420,9 +609,10 @@ class PointerFn(Function):
     """pointer_generator_network + LabelSmoothingLoss (reference model.py:896-923, 37-55) -> (P flat, caption loss)."""
 
     @staticmethod
-    def forward(ctx, dec, G, Esrc, wpgen, bpgen, logits, lay):
+    def forward(ctx, dec, G, Esrc, wpgen, bpgen, logits, lay, dec_link=None):
         P, rows, saved = be().pointer_fwd(dec, G, Esrc, wpgen.detach(), bpgen.detach(), logits, lay)
         ctx.lay = lay
+        ctx.dec_link = dec_link if LINKS else None
         ctx.save_for_backward(dec, G, Esrc, wpgen.detach(), bpgen.detach(), logits, P, *saved)
         return P, be().sum_all(rows)
 
@@ -433,7 +623,12 @@ class PointerFn(Function):
             dloss = torch.zeros((), dtype=torch.float32, device=P.device)
         ddec, dG, dE, dw, db, dlog = be().pointer_bwd(None if dP is None else dP.contiguous(), dloss, dec, G, Esrc,
                                                       wpgen, bpgen, logits, ctx.lay, P, tuple(saved))
-        return ddec, dG, dE, dw, db, dlog, None
+        if ctx.dec_link is not None and ctx.needs_input_grad[0]:
+            # dec also feeds the LM head: its transform Linear adds this piece in the epilogue of its input-gradient GEMM
+            assert ctx.dec_link.res_grad is None
+            ctx.dec_link.res_grad = ddec
+            ddec = None
+        return ddec, dG, dE, dw, db, dlog, None, None
 
 
 class SoftmaxLSFn(Function):

@@ -276,9 +276,9 @@ class StateAwareRecursiveTransformer(nn.Module):
     def _ln(self, x, res, prefix, **kw):
         return Fn.layer_norm(x, res, self.p(prefix + ".weight"), self.p(prefix + ".bias"), self.config.layer_norm_eps, **kw)
 
-    def _qkv(self, x, prefix, names):
+    def _qkv(self, x, prefix, names, **kw):
         return Fn.linear(x, [self.p(f"{prefix}.{n}.weight") for n in names], [self.p(f"{prefix}.{n}.bias") for n in names],
-                         cd=self.compute_dtype)
+                         cd=self.compute_dtype, **kw)
 
     def _encoder_layer(self, x, prefix, lay, key_mask, cls_lay=None, cls_stride=0):
         """BertLayerNoMemoryUntied (reference model.py:574-591).  With ``cls_lay`` only the first row of every
@@ -286,8 +286,11 @@ class StateAwareRecursiveTransformer(nn.Module):
         model.py:1064): keys / values still come from all rows."""
         cfg, cd, D, Hh = self.config, self.compute_dtype, self.config.hidden_size, self.config.num_attention_heads
         ap = prefix + ".attention"
+        # backward hand-offs (Fn.Link): Lx / La carry the skip-connection gradients of x / a into the input-gradient GEMMs of
+        # the QKV / intermediate projections; Lo, Lh, L2 fuse the dropout / GELU backward into ln_bwd and the dgrad epilogue
+        Lx, Lo, La, Lh, L2 = Fn.Link(), Fn.Link(), Fn.Link(), Fn.Link(), Fn.Link()
         if cls_lay is None:
-            qkv = self._qkv(x, ap + ".self", ("query", "key", "value"))
+            qkv = self._qkv(x, ap + ".self", ("query", "key", "value"), in_link=Lx)
             ctx = Fn.attention(qkv, None, (0, D, 2 * D), lay, key_mask, False, Hh, cd,
                                drop=self._drop(cfg.attention_probs_dropout_prob, prefix + ".attn"))
             res = x
@@ -297,12 +300,13 @@ class StateAwareRecursiveTransformer(nn.Module):
             q = self._lin(res, ap + ".self.query")
             ctx = Fn.attention(q, kv, (0, 0, D), cls_lay, key_mask, False, Hh, cd,
                                drop=self._drop(cfg.attention_probs_dropout_prob, prefix + ".attn"))
+            Lx = None
         ph = cfg.hidden_dropout_prob
-        a = self._ln(self._lin(ctx, ap + ".output.dense", residual=res, drop=self._drop(ph, prefix + ".attn_out")), None,
-                     ap + ".output.LayerNorm")
-        h = self._lin(a, prefix + ".hidden_intermediate.dense", act=ACT_GELU)
-        return self._ln(self._lin(h, prefix + ".output.dense", residual=a, drop=self._drop(ph, prefix + ".out")), None,
-                        prefix + ".output.LayerNorm")
+        a = self._ln(self._lin(ctx, ap + ".output.dense", residual=res, drop=self._drop(ph, prefix + ".attn_out"), res_link=Lx,
+                               out_link=Lo), None, ap + ".output.LayerNorm", grad_link=Lo)
+        h = self._lin(a, prefix + ".hidden_intermediate.dense", act=ACT_GELU, in_link=La, out_link=Lh)
+        return self._ln(self._lin(h, prefix + ".output.dense", residual=a, drop=self._drop(ph, prefix + ".out"), in_link=Lh,
+                                  res_link=La, out_link=L2), None, prefix + ".output.LayerNorm", grad_link=L2)
 
     def _video_embed(self, feats_list, plan, vid_ids):
         """BertEmbeddingsVideoUntied + token-type add (reference model.py:548-562, 889-891).  LN(3072)'s affine is
@@ -316,17 +320,19 @@ class StateAwareRecursiveTransformer(nn.Module):
             # folded into the weights; the normalised, scaled and dropped features are staged once in the compute dtype
             a = Fn.VideoLNDropFn.apply(self.p(pfx + ".0.weight"), self.p(pfx + ".0.bias"), list(feats_list), plan.t["clip_t"],
                                        plan.t["clip_b"], cfg.max_v_len, cfg.layer_norm_eps, self.compute_dtype, drop)
-            z = self._lin(a, pfx + ".2", act=ACT_RELU)
+            Lz = Fn.Link()
+            z = self._lin(a, pfx + ".2", act=ACT_RELU, out_link=Lz)
             return self._ln(z, None, pfx + ".4", pe=self.p("video_embeddings.position_embeddings_video.pe"),
-                            pe_period=cfg.max_v_len, tt=self.p("token_type_embeddings.weight"), tt_ids=vid_ids)
+                            pe_period=cfg.max_v_len, tt=self.p("token_type_embeddings.weight"), tt_ids=vid_ids, grad_link=Lz)
         xhat, _, _ = Fn.be().video_ln_pack(feats_list, plan.t["clip_t"], plan.t["clip_b"], cfg.max_v_len,
                                           cfg.layer_norm_eps, self.compute_dtype)
         W, g0, b0 = self.p(pfx + ".2.weight"), self.p(pfx + ".0.weight"), self.p(pfx + ".0.bias")
         Wf = W * g0
         bf = self.p(pfx + ".2.bias") + (W * b0).sum(dim=1)
-        z = Fn.linear(xhat, Wf, bf, act=ACT_RELU, cd=self.compute_dtype, cache=False)   # Wf is a per-step temporary
+        Lz = Fn.Link()
+        z = Fn.linear(xhat, Wf, bf, act=ACT_RELU, cd=self.compute_dtype, cache=False, out_link=Lz)   # Wf is a per-step temporary
         return self._ln(z, None, pfx + ".4", pe=self.p("video_embeddings.position_embeddings_video.pe"),
-                        pe_period=cfg.max_v_len, tt=self.p("token_type_embeddings.weight"), tt_ids=vid_ids)
+                        pe_period=cfg.max_v_len, tt=self.p("token_type_embeddings.weight"), tt_ids=vid_ids, grad_link=Lz)
 
     def _word_fc(self, which, ids, pe=None, pe_period=0):
         """Embedding -> LN(W) -> Linear -> ReLU -> LN(D) (+pe)  (reference model.py:492-499 / 519-526)."""
@@ -335,8 +341,9 @@ class StateAwareRecursiveTransformer(nn.Module):
         e = Fn.EmbedLNFn.apply(self.p(which + ".word_embeddings.weight"), ids, self.p(pfx + ".0.weight"),
                                self.p(pfx + ".0.bias"), cfg.layer_norm_eps, self.compute_dtype, PAD,
                                self._drop(cfg.hidden_dropout_prob, which))
-        z = self._lin(e, pfx + ".2", act=ACT_RELU)
-        return self._ln(z, None, pfx + ".4", pe=pe, pe_period=pe_period)
+        Lz = Fn.Link()
+        z = self._lin(e, pfx + ".2", act=ACT_RELU, out_link=Lz)
+        return self._ln(z, None, pfx + ".4", pe=pe, pe_period=pe_period, grad_link=Lz)
 
     def _reasoner(self, prefix, V, E0, plan):
         """EntitiyReasoningNetwork.forward (reference model.py:777-823): everything that depends only on the step
@@ -353,7 +360,7 @@ class StateAwareRecursiveTransformer(nn.Module):
         clog = self._lin(hhat, prefix + ".W3", out_dtype=f32)                                            # (Nc, 3)
         w4s = self._lin(fbar, prefix + ".W4", out_dtype=f32).reshape(-1)                                 # (Nc,)
         lay = dict(cu_ingr=plan.t["cu_ingr"], cu_steps=plan.t["cu_steps"], clip_ent_off=plan.t["clip_ent_off"],
-                   max_ni=plan.max_ni, NE=plan.NE, B=plan.B)
+                   max_ni=plan.max_ni, NE=plan.NE, B=plan.B, max_steps=max(plan.steps) if plan.steps else 0)
         ent, ebar, Es = Fn.ReasonerFn.apply(E0, w2v, clog, w4s, lay)
         return ent, ac, ebar, Es, fbar
 
@@ -363,23 +370,26 @@ class StateAwareRecursiveTransformer(nn.Module):
         cross = plan.cross_lay(C, x.device, D)
         for l in range(cfg.num_hidden_layers):
             pfx = f"decoder.layer.{l}"
-            qkv = self._qkv(x, pfx + ".self_attention", ("query", "key", "value"))
+            Lx, L1, L2, Lo = Fn.Link(), Fn.Link(), Fn.Link(), Fn.Link()      # skip-connection / dropout hand-offs (Fn.Link)
+            qkv = self._qkv(x, pfx + ".self_attention", ("query", "key", "value"), in_link=Lx)
             pa = cfg.attention_probs_dropout_prob
             sa = Fn.attention(qkv, None, (0, D, 2 * D), plan.dec_lay, text_mask, True, Hh, cd,
                               drop=self._drop(pa, pfx + ".self_attn"))
-            h1 = self._ln(sa, x, pfx + ".norm1")
-            q2 = self._lin(h1, pfx + ".dec_enc_attention.query")
+            h1 = self._ln(sa, x, pfx + ".norm1", res_link=Lx)
+            q2 = self._lin(h1, pfx + ".dec_enc_attention.query", in_link=L1)
             kv2 = self._qkv(ctx, pfx + ".dec_enc_attention", ("key", "value"))
             ca = Fn.attention(q2, kv2, (0, 0, D), cross, None, False, Hh, cd, drop=self._drop(pa, pfx + ".cross_attn"))
-            h2 = self._ln(ca, h1, pfx + ".norm2")
-            x = self._ln(self._lin(h2, pfx + ".output.dense", residual=h2,
-                                   drop=self._drop(cfg.hidden_dropout_prob, pfx + ".out")), None, pfx + ".output.LayerNorm")
+            h2 = self._ln(ca, h1, pfx + ".norm2", res_link=L1)
+            x = self._ln(self._lin(h2, pfx + ".output.dense", residual=h2, drop=self._drop(cfg.hidden_dropout_prob, pfx + ".out"),
+                                   in_link=L2, res_link=L2, out_link=Lo), None, pfx + ".output.LayerNorm", grad_link=Lo)
         return x
 
-    def _lm_logits(self, dec):
-        """BertLMPredictionHead (reference model.py:704-709, 735-739) -> fp32 logits (R, V)."""
-        t = self._lin(dec, "decoder_classifier.transform.dense", act=ACT_GELU)
-        t = self._ln(t, None, "decoder_classifier.transform.LayerNorm")
+    def _lm_logits(self, dec, dec_link=None):
+        """BertLMPredictionHead (reference model.py:704-709, 735-739) -> fp32 logits (R, V).  dec_link: where the pointer
+        generator leaves its share of d(dec) (added in this Linear's input-gradient GEMM)."""
+        Lt = Fn.Link()
+        t = self._lin(dec, "decoder_classifier.transform.dense", act=ACT_GELU, in_link=dec_link, out_link=Lt)
+        t = self._ln(t, None, "decoder_classifier.transform.LayerNorm", grad_link=Lt)
         return Fn.linear(t, self.p("decoder_classifier.decoder.weight"), self.p("decoder_classifier.bias"),
                          cd=self.compute_dtype, out_dtype=torch.float32)
 
@@ -536,7 +546,8 @@ class StateAwareRecursiveTransformer(nn.Module):
         ctx, C = self._context(mode, Vst, E0, ebar, fbar, plan)
         x = self._word_fc("text_embeddings", text_ids, pe=self.p("text_embeddings.position_embeddings_text.pe"), pe_period=Lt)
         dec = self._decoder(x, text_mask, ctx, plan, C)
-        logits = self._lm_logits(dec)
+        Ld = Fn.Link() if mode != "video" else None
+        logits = self._lm_logits(dec, dec_link=Ld)
 
         if mode == "video":
             lab = torch.where(labels >= V, torch.full_like(labels, cfg.unk_id), labels)          # model.py:1013
@@ -550,7 +561,7 @@ class StateAwareRecursiveTransformer(nn.Module):
                        clip_P_off=plan.t["clip_P_off"], P_numel=plan.P_numel, tok_ptr=plan.t["tok_ptr"],
                        tok_ids=plan.t["tok_ids"], labels=labels.reshape(-1).to(torch.int32), max_vx=max(plan.vx))
             P, caption = Fn.PointerFn.apply(dec, G, Esrc, self.p("pgen_linear.0.weight").reshape(-1),
-                                            self.p("pgen_linear.0.bias"), logits, lay)
+                                            self.p("pgen_linear.0.bias"), logits, lay, Ld)
 
         parts = dict(caption=caption)
         total = caption

@@ -115,6 +115,45 @@ def test_gemm_tc_splitk(cb):
     assert float(buf[:, N:].abs().max()) == 0
 
 
+@pytest.mark.parametrize("a_mn", [False, True])
+@pytest.mark.parametrize("b_mn", [False, True])
+@pytest.mark.parametrize("M,N,K", [(128, 128, 64), (200, 951, 768), (1000, 768, 3072), (130, 72, 40), (4800, 768, 300),
+                                   (768, 768, 19200), (192, 768, 768)])
+def test_gemm_split_fp32(cb, a_mn, b_mn, M, N, K):
+    """fp32 operands on the tcgen05 route (split into hi / lo bf16 planes, three passes into one fp32 accumulator): within
+    3e-5 of the fp64 product relative to its scale (plain bf16 operands: ~4e-3), all four operand majors, epilogue included."""
+    from svpc_b200.cuda_backend import Split2
+    A = rnd(K, M).t() if a_mn else rnd(M, K)
+    Bm = rnd(K, N, seed=2).t() if b_mn else rnd(N, K, seed=2)
+    ref = A.double() @ Bm.double().t()
+    assert cb.tc3
+    # the tensor core adds every K = 16 slice into the fp32 accumulator with truncation, so the error of ONE accumulator
+    # grows linearly with K: forward shapes (K <= 3072) stay below 3e-5; the weight-gradient shape (K = 19200) is only
+    # launched without an epilogue, where split-K keeps the chains short (plain case below) - with an epilogue it is 2e-4
+    tol = 3e-5
+    cb.reset_launch_count()
+    got = cb.gemm(A, Bm, F32)
+    assert cb.launch_count() == 3, "two split passes + one tensor-core GEMM expected"
+    close(f"split plain a_mn={a_mn} b_mn={b_mn}", got, ref, tol)
+    if K > 4096:
+        tol = 2e-4
+    sA, sB = cb.split2(A), cb.split2(Bm)
+    assert isinstance(sA, Split2)
+    close("hi + lo", sA.hi.double() + sA.lo.double(), A.double(), 2e-5)
+    bias, res = rnd(N, seed=3), rnd(M, N, seed=4)
+    got, pre = cb.gemm(sA, sB, F32, bias, 2, res, want_pre=True)
+    rpre = ref + bias.double()
+    rr = rpre * 0.5 * (1 + torch.erf(rpre / math.sqrt(2))) + res.double()
+    close("split gelu+res", got, rr, tol)
+    close("split pre", pre, rpre, tol)
+    acc = torch.ones(M, N, dtype=F32, device=DEV)
+    cb.gemm(sA, sB, F32, out=acc, accumulate=True)
+    close("split accumulate", acc, ref + 1, tol)
+    # a problem that is too small for the tcgen05 kernel falls back to the fp32 FFMA kernel on the fp32 data
+    small = cb.gemm(sA[:8], sB, F32)
+    close("split -> simt fallback", small, ref[:8], 1e-5)
+
+
 # ---------------------------------------------------------------------------------------------- row-wise
 @pytest.mark.parametrize("dt", [F32, BF16])
 @pytest.mark.parametrize("rows,D", [(37, 64), (200, 768), (9, 3072)])
@@ -281,8 +320,10 @@ def _reasoner_case(D):
 
 
 @pytest.mark.parametrize("D", [64, 768])
-def test_reasoner(cb, tb, D):
+@pytest.mark.parametrize("max_steps", [0, 4])      # 0: un-pipelined forward kernel; 4: per-step rows staged up front
+def test_reasoner(cb, tb, D, max_steps):
     lay, E0, w2v, clog, w4s, NE, Nc = _reasoner_case(D)
+    lay = dict(lay, max_steps=max_steps)
     ent, ebar, Es, saved = cb.reasoner_fwd(E0, lay, w2v, clog, w4s)
     rent, rebar, rEs, _ = tb.reasoner_fwd(E0, lay, w2v, clog, w4s)
     close("reasoner ent", ent, rent, 1e-5); close("reasoner ebar", ebar, rebar, 1e-5); close("reasoner Es", Es, rEs, 1e-5)

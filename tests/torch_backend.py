@@ -61,7 +61,7 @@ class TorchBackend:
 
     # ---------------------------------------------------------------- dense
     def gemm(self, a, bt, out_dtype, bias=None, act=0, residual=None, out=None, accumulate=False, want_pre=False,
-             route=None, drop=None):
+             route=None, drop=None, grad_act=None):
         assert drop is None, "the plain-torch statements are eval-mode (no dropout)"
         pre = self.f(a) @ self.f(bt).t()
         if bias is not None:
@@ -69,6 +69,9 @@ class TorchBackend:
         y = _act(pre, act)
         if residual is not None:
             y = y + self.f(residual)
+        if grad_act is not None:
+            assert out is None and not accumulate
+            y = self.f(self.act_bwd(y.to(out_dtype), grad_act[1], grad_act[0])[0])
         if out is not None:
             if accumulate:
                 out.add_(y.to(out.dtype))
@@ -122,11 +125,17 @@ class TorchBackend:
         pre_out = x if res is None else pre.to(x.dtype)
         return y.to(out_dtype), pre_out, mean.float(), rstd.float()
 
-    def ln_bwd(self, dy, pre, mean, rstd, gamma):
+    def ln_bwd(self, dy, pre, mean, rstd, gamma, fuse=None):
         g = self.f(dy) * self.f(gamma)
         xhat = (self.f(pre) - self.f(mean)[:, None]) * self.f(rstd)[:, None]
         dpre = self.f(rstd)[:, None] * (g - g.mean(-1, keepdim=True) - xhat * (g * xhat).mean(-1, keepdim=True))
-        return dpre.to(dy.dtype), (self.f(dy) * xhat).sum(0).float(), self.f(dy).sum(0).float()
+        out = (dpre.to(pre.dtype), (self.f(dy) * xhat).sum(0).float(), self.f(dy).sum(0).float())
+        if fuse is None:
+            return out
+        act, ref, drop, want_dbias = fuse
+        assert drop is None, "the plain-torch statements are eval-mode (no dropout)"
+        dz, dbias = self.act_bwd(out[0], pre if ref is None else ref, act)
+        return out + (dz, dbias if want_dbias else None)
 
     def index_colsum(self, dy, ids, nbins):
         out = torch.zeros(nbins, dy.shape[1], dtype=self.math_dtype, device=dy.device)
