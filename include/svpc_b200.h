@@ -131,14 +131,15 @@ int svpc_embed_ln_bwd(int rows, int W, int V, const void* dy, int dt, const floa
                       svpc_stream_t stream);
 
 /* Gathers the first Lv rows of clip (t,b) = (clip_t[n], clip_b[n]) from the S per-step feature tensors
- * (B, L, F) fp32 and writes (x - mean) * rstd (LN(3072) without affine, model.py:549). */
-int svpc_video_ln_pack(int n_clips, int B, int L, int Lv, int F, const long long* feat_ptrs, const int* clip_t,
+ * (B, L, F) (dt_feat: SVPC_F32 as the reference's loader delivers them, or SVPC_BF16 - the half-size upload of the bf16
+ * path) and writes (x - mean) * rstd (LN(3072) without affine, model.py:549). */
+int svpc_video_ln_pack(int n_clips, int B, int L, int Lv, int F, const long long* feat_ptrs, int dt_feat, const int* clip_t,
                        const int* clip_b, float eps, void* xhat, int dt, float* mean, float* rstd, const float* gamma,
                        const float* beta, const unsigned int* drop_seed, unsigned int drop_site, float drop_p,
                        svpc_stream_t stream);
 /* train mode (gamma / beta given): xhat <- drop(xhat * gamma + beta), element index row * F + c (model.py:549-550); its
  * backward towards gamma / beta (the features are inputs), xhat recomputed from the features and the statistics */
-int svpc_video_ln_affine_bwd(int n_clips, int B, int L, int Lv, int F, const long long* feat_ptrs, const int* clip_t,
+int svpc_video_ln_affine_bwd(int n_clips, int B, int L, int Lv, int F, const long long* feat_ptrs, int dt_feat, const int* clip_t,
                              const int* clip_b, const float* mean, const float* rstd, const void* dy, int dt,
                              float* dgamma, float* dbeta, const unsigned int* drop_seed, unsigned int drop_site,
                              float drop_p, svpc_stream_t stream);

@@ -287,6 +287,68 @@ __device__ __forceinline__ void epi_vec(const TcParams& p, uint32_t stage, int m
   }
 }
 
+// bf16 outputs: the residual / activation-gradient reference rows of the whole chunk (8 rows x 8 bytes per lane) are loaded
+// BEFORE the accumulator chunk is fetched from TMEM, so their L2 latency hides behind tcgen05.ld + the transposition instead
+// of stalling the row loop twice per chunk (the residual epilogues ran at 0.36 of peak against 0.60 plain).
+struct EpiPre { uint2 rr[8]; uint2 gg[8]; };
+__device__ __forceinline__ void epi_prefetch_bf16(const TcParams& p, int mw, int n, int rsub, EpiPre& o) {
+  const int m_first = mw + rsub;
+  const int rows = min(8, (p.M - m_first + 3) >> 2);
+  if (p.residual) {
+    const bf16* r0 = (const bf16*)p.residual + (long long)m_first * p.ldr + n;
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+      if (j < rows) o.rr[j] = *reinterpret_cast<const uint2*>(r0 + (long long)j * 4 * p.ldr);
+  }
+  if (p.gref) {
+    const bf16* g0 = (const bf16*)p.gref + (long long)m_first * p.ldg + n;
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+      if (j < rows) o.gg[j] = *reinterpret_cast<const uint2*>(g0 + (long long)j * 4 * p.ldg);
+  }
+}
+
+template <int ACT, bool DROP>
+__device__ __forceinline__ void epi_vec_bf16(const TcParams& p, uint32_t stage, int mw, int n, int rsub, int g,
+                                             uint32_t dkey, float dinv, const EpiPre& o) {
+  float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (p.bias) bv = *reinterpret_cast<const float4*>(p.bias + n);
+  const int m_first = mw + rsub;
+  const int rows = min(8, (p.M - m_first + 3) >> 2);
+  bf16* __restrict__ d0 = (bf16*)p.D + (long long)m_first * p.ldd + n;
+  const long long dstep = 4 * p.ldd;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    if (j >= rows) break;
+    const int r = j * 4 + rsub;
+    float4 x = lds128(stage + epi_slot(r, g));
+    x.x += bv.x; x.y += bv.y; x.z += bv.z; x.w += bv.w;
+    if (p.pre) st4((bf16*)p.pre + (long long)(mw + r) * p.ldp + n, x);
+    x.x = tc_act<ACT>(x.x); x.y = tc_act<ACT>(x.y); x.z = tc_act<ACT>(x.z); x.w = tc_act<ACT>(x.w);
+    if (DROP) {
+      const unsigned long long e0 = (unsigned long long)(mw + r) * p.N + n;
+      if ((e0 & 1) == 0) {             // aligned pairs: one hash per two elements
+        float s0, s1;
+        svpc_drop_scale2(dkey, p.drop.p, dinv, e0, s0, s1);
+        x.x *= s0; x.y *= s1;
+        svpc_drop_scale2(dkey, p.drop.p, dinv, e0 + 2, s0, s1);
+        x.z *= s0; x.w *= s1;
+      } else {
+        x.x *= svpc_drop_scale(dkey, p.drop.p, dinv, e0); x.y *= svpc_drop_scale(dkey, p.drop.p, dinv, e0 + 1);
+        x.z *= svpc_drop_scale(dkey, p.drop.p, dinv, e0 + 2); x.w *= svpc_drop_scale(dkey, p.drop.p, dinv, e0 + 3);
+      }
+    }
+    if (p.residual) { const float4 r4 = raw4_to_float4(o.rr[j]); x.x += r4.x; x.y += r4.y; x.z += r4.z; x.w += r4.w; }
+    if (p.accumulate) { const float4 dd = ld4(d0 + j * dstep); x.x += dd.x; x.y += dd.y; x.z += dd.z; x.w += dd.w; }
+    if (p.gref) {
+      const float4 g4 = raw4_to_float4(o.gg[j]);
+      x.x *= tc_act_grad(p.gact, g4.x); x.y *= tc_act_grad(p.gact, g4.y);
+      x.z *= tc_act_grad(p.gact, g4.z); x.w *= tc_act_grad(p.gact, g4.w);
+    }
+    st4(d0 + j * dstep, x);
+  }
+}
+
 // Edge / unaligned path (N not a multiple of 4, odd row pitch, last partial columns): rare, kept out of line.
 template <typename TD>
 __device__ __forceinline__ void epi_scalar(const TcParams& p, uint32_t stage, int mw, int n, int rsub, int g, bool dropping,
@@ -348,7 +410,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
                                                                 const __grid_constant__ CUtensorMap tmAlo,
                                                                 const __grid_constant__ CUtensorMap tmBlo,
                                                                 const __grid_constant__ TcParams p) {
-  svpc_pdl_sync();
+  // Programmatic dependent launch: the NEXT grid may become resident right away, and this CTA's prologue (barrier
+  // initialisation, the TMEM allocation, the tensor-map prefetch - ~2 us that touch no global data) runs while the grid in
+  // front of it is still draining; griddepcontrol.wait below is the point after which its results may be read.
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   float* epi_stage = reinterpret_cast<float*>(smem + TC_STAGES * TC_STAGE_BYTES);
@@ -378,6 +443,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  asm volatile("griddepcontrol.wait;" ::: "memory");
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
@@ -485,6 +551,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
       const uint32_t trow = tmem_base + acc * TC_BN_MAX + ((uint32_t)(q * 32) << 16);
 #pragma unroll 1
       for (int c = half; c < nchunks; c += CSTEP) {
+        const int nb = w.n0 + c * 32;
+        const int n = nb + g * 4;
+        const bool in_range = n < p.N && mw < p.M;
+        const bool vec = vec_all && (n + 4 <= p.N);
+        EpiPre opnd;
+        if (sizeof(TD) == 2 && in_range && vec && !p.atomic) epi_prefetch_bf16(p, mw, n, rsub, opnd);
         {
           uint32_t v[32];
           tmem_ld32(trow + (uint32_t)(c * 32), v);
@@ -494,13 +566,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
             sts128(stage + epi_slot(lane, jj), v[4 * jj], v[4 * jj + 1], v[4 * jj + 2], v[4 * jj + 3]);
         }
         __syncwarp();
-        const int nb = w.n0 + c * 32;
-        const int n = nb + g * 4;
-        if (n < p.N && mw < p.M) {
+        if (in_range) {
           if (p.atomic) {
-            epi_atomic(p, stage, mw, n, rsub, g, vec_all && (n + 4 <= p.N));
-          } else if (vec_all && (n + 4 <= p.N)) {
-            epi_vec<ACT, DROP, TD>(p, stage, mw, n, rsub, g, dkey, dinv);
+            epi_atomic(p, stage, mw, n, rsub, g, vec);
+          } else if (vec) {
+            if (sizeof(TD) == 2) epi_vec_bf16<ACT, DROP>(p, stage, mw, n, rsub, g, dkey, dinv, opnd);
+            else epi_vec<ACT, DROP, TD>(p, stage, mw, n, rsub, g, dkey, dinv);
           } else {
             epi_scalar<TD>(p, stage, mw, n, rsub, g, dropping, dkey, dinv);
           }

@@ -764,7 +764,15 @@ extern "C" int svpc_embed_ln_bwd(int rows, int W, int V, const void* dy, int dt,
 // video features: gather the first Lv rows of every clip from the per-step (B, L, F) tensors, LN statistics,
 // write the normalised rows in the compute dtype (the only pass over the 1.23 MB/clip of fp32 features)
 // ------------------------------------------------------------------------------------------------
-template <typename T>
+// four consecutive feature values (features arrive as fp32 or, on the bf16 upload path, as bf16)
+__device__ __forceinline__ float4 ldfeat4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
+__device__ __forceinline__ float4 ldfeat4(const bf16* p) {
+  const uint2 u = __ldg(reinterpret_cast<const uint2*>(p));
+  const __nv_bfloat162 a = *reinterpret_cast<const __nv_bfloat162*>(&u.x), b = *reinterpret_cast<const __nv_bfloat162*>(&u.y);
+  return make_float4(__low2float(a), __high2float(a), __low2float(b), __high2float(b));
+}
+
+template <typename T, typename TF>
 __global__ void __launch_bounds__(RW_THREADS) video_ln_pack_kernel(int n_rows, int B, int L, int Lv, int F,
                                                                    const long long* __restrict__ feat_ptrs,
                                                                    const int* __restrict__ clip_t,
@@ -780,15 +788,14 @@ __global__ void __launch_bounds__(RW_THREADS) video_ln_pack_kernel(int n_rows, i
   const float dinv = dropping ? 1.f / (1.f - drop.p) : 1.f;
   for (int r = blockIdx.x; r < n_rows; r += gridDim.x) {
     const int n = r / Lv, row = r - n * Lv;
-    const float* src = reinterpret_cast<const float*>(feat_ptrs[clip_t[n]]) + ((long long)clip_b[n] * L + row) * F;
-    const float4* src4 = reinterpret_cast<const float4*>(src);
+    const TF* src = reinterpret_cast<const TF*>(feat_ptrs[clip_t[n]]) + ((long long)clip_b[n] * L + row) * F;
     float4 v[RW_MAXPT / 4];
     float s = 0.f;
 #pragma unroll
     for (int i = 0; i < RW_MAXPT / 4; ++i) {
       const int c = threadIdx.x + i * RW_THREADS;
       v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (c < F4) { v[i] = __ldg(src4 + c); s += v[i].x + v[i].y + v[i].z + v[i].w; }
+      if (c < F4) { v[i] = ldfeat4(src + 4 * c); s += v[i].x + v[i].y + v[i].z + v[i].w; }
     }
     const float mu = block_sum(s, red) / F;
     float q = 0.f;
@@ -825,7 +832,7 @@ __global__ void __launch_bounds__(RW_THREADS) video_ln_pack_kernel(int n_rows, i
   }
 }
 
-extern "C" int svpc_video_ln_pack(int n_clips, int B, int L, int Lv, int F, const long long* feat_ptrs,
+extern "C" int svpc_video_ln_pack(int n_clips, int B, int L, int Lv, int F, const long long* feat_ptrs, int dt_feat,
                                   const int* clip_t, const int* clip_b, float eps, void* xhat, int dt, float* mean,
                                   float* rstd, const float* gamma, const float* beta, const unsigned int* drop_seed,
                                   unsigned int drop_site, float drop_p, svpc_stream_t stream) {
@@ -835,8 +842,8 @@ extern "C" int svpc_video_ln_pack(int n_clips, int B, int L, int Lv, int F, cons
   SVPC_REQUIRE(F % 4 == 0 && F <= RW_THREADS * RW_MAXPT, "video_ln_pack: F=%d must be a multiple of 4 and <= 4096", F);
   cudaStream_t st = (cudaStream_t)stream;
   const int n_rows = n_clips * Lv;
-  SVPC_DISPATCH(dt, T, (svpc_launch(video_ln_pack_kernel<T>, svpc_imin(n_rows, SVPC_NUM_SMS * 16), RW_THREADS, 0, st, 
-      n_rows, B, L, Lv, F, feat_ptrs, clip_t, clip_b, eps, (T*)xhat, mean, rstd, gamma, beta, drop)));
+  SVPC_DISPATCH(dt, T, SVPC_DISPATCH(dt_feat, TF, (svpc_launch(video_ln_pack_kernel<T, TF>, svpc_imin(n_rows, SVPC_NUM_SMS * 16),
+      RW_THREADS, 0, st, n_rows, B, L, Lv, F, feat_ptrs, clip_t, clip_b, eps, (T*)xhat, mean, rstd, gamma, beta, drop))));
   return svpc_check_launch("video_ln_pack");
 }
 
@@ -845,7 +852,7 @@ extern "C" int svpc_video_ln_pack(int n_clips, int B, int L, int Lv, int F, cons
 // Layout: a CTA owns a 256-column slab (lane = 8 contiguous columns: one 16-byte bf16 load of dy, two float4 loads of the
 // features) for a strided set of rows (8 row lanes); column sums over the row lanes through shared memory, one red.global
 // per column per CTA.
-template <typename T>
+template <typename T, typename TF>
 __global__ void __launch_bounds__(256) video_ln_affine_bwd_kernel(int n_rows, int B, int L, int Lv, int F,
                                                                   const long long* __restrict__ feat_ptrs,
                                                                   const int* __restrict__ clip_t,
@@ -867,7 +874,7 @@ __global__ void __launch_bounds__(256) video_ln_affine_bwd_kernel(int n_rows, in
   if (c0 < F) {
     for (int r = blockIdx.y * 8 + ty; r < n_rows; r += gridDim.y * 8) {
       const int n = r / Lv, row = r - n * Lv;
-      const float* src = reinterpret_cast<const float*>(feat_ptrs[clip_t[n]]) + ((long long)clip_b[n] * L + row) * F + c0;
+      const TF* src = reinterpret_cast<const TF*>(feat_ptrs[clip_t[n]]) + ((long long)clip_b[n] * L + row) * F + c0;
       const float mu = mean[r], rs = rstd[r];
       float d[8], x[8];
       ld8(dy + (long long)r * F + c0, d);
@@ -900,7 +907,7 @@ __global__ void __launch_bounds__(256) video_ln_affine_bwd_kernel(int n_rows, in
   }
 }
 
-extern "C" int svpc_video_ln_affine_bwd(int n_clips, int B, int L, int Lv, int F, const long long* feat_ptrs,
+extern "C" int svpc_video_ln_affine_bwd(int n_clips, int B, int L, int Lv, int F, const long long* feat_ptrs, int dt_feat,
                                         const int* clip_t, const int* clip_b, const float* mean, const float* rstd,
                                         const void* dy, int dt, float* dgamma, float* dbeta, const unsigned int* drop_seed,
                                         unsigned int drop_site, float drop_p, svpc_stream_t stream) {
@@ -913,8 +920,8 @@ extern "C" int svpc_video_ln_affine_bwd(int n_clips, int B, int L, int Lv, int F
   const int n_rows = n_clips * Lv;
   const int gx = svpc_cdiv(F, 256);
   dim3 grid(gx, svpc_imin(svpc_cdiv(n_rows, 8), svpc_cdiv(SVPC_NUM_SMS * 8, gx)));
-  SVPC_DISPATCH(dt, T, (svpc_launch(video_ln_affine_bwd_kernel<T>, grid, 256, 0, st, 
-      n_rows, B, L, Lv, F, feat_ptrs, clip_t, clip_b, mean, rstd, (const T*)dy, dgamma, dbeta, drop)));
+  SVPC_DISPATCH(dt, T, SVPC_DISPATCH(dt_feat, TF, (svpc_launch(video_ln_affine_bwd_kernel<T, TF>, grid, 256, 0, st,
+      n_rows, B, L, Lv, F, feat_ptrs, clip_t, clip_b, mean, rstd, (const T*)dy, dgamma, dbeta, drop))));
   return svpc_check_launch("video_ln_affine_bwd");
 }
 

@@ -226,7 +226,7 @@ class CudaBackend:
             bt = bt.src
         self._chk(a, bt, bias, residual, out)
         if out is None:
-            out = torch.empty(M, N, dtype=out_dtype, device=a.device)
+            out = self._out_empty(M, N, out_dtype, a.device)
         assert out.shape == (M, N) and (N == 1 or out.stride(1) == 1)
         pre = torch.empty(M, N, dtype=out.dtype, device=a.device) if want_pre else None
         if residual is not None:
@@ -258,7 +258,7 @@ class CudaBackend:
                     grad_act=None):
         self._chk(a.hi, bt.hi, bias, residual, out)
         if out is None:
-            out = torch.empty(M, N, dtype=out_dtype, device=a.device)
+            out = self._out_empty(M, N, out_dtype, a.device)
         assert out.shape == (M, N) and (N == 1 or out.stride(1) == 1)
         pre = torch.empty(M, N, dtype=out.dtype, device=a.device) if want_pre else None
         if residual is not None:
@@ -297,10 +297,24 @@ class CudaBackend:
 
     def colsum(self, x):
         self._chk(x)
+        if x.dim() == 2 and not x.is_contiguous() and x.stride(1) == 1 and x.stride(0) > x.shape[1] and x.shape[0] > 0:
+            # row-pitched view: sum the pitched rows as they lie (the pad columns are summed into slots nobody reads)
+            ld = x.stride(0)
+            return self.colsum(x.as_strided((x.shape[0], ld), (ld, 1)))[:x.shape[1]]
         x = self._c(x)
         out = torch.empty(x.shape[1], dtype=torch.float32, device=x.device)
         self._call("svpc_colsum", x.shape[0], x.shape[1], _ptr(x), _DT[x.dtype], _ptr(out))
         return out
+
+    @staticmethod
+    def _out_empty(M, N, dtype, device):
+        """GEMM output: rows pitched to 16 bytes (the epilogue's vector stores need aligned rows; with the 951-word LM head
+        an un-pitched fp32 output drops the whole launch onto the element-wise store path, 47 us against 12)."""
+        q = 16 // torch.empty((), dtype=dtype).element_size()
+        if N <= 8 or N % q == 0:
+            return torch.empty(M, N, dtype=dtype, device=device)
+        ld = (N + q - 1) // q * q
+        return torch.empty(M, ld, dtype=dtype, device=device)[:, :N]
 
     @staticmethod
     def _padded_empty(rows, cols, dtype, device):
@@ -425,8 +439,8 @@ class CudaBackend:
         self._chk(f0)
         B, L, Fdim = f0.shape
         for f in feats_list:
-            if not (f.is_cuda and f.dtype == torch.float32 and f.is_contiguous() and f.shape == f0.shape):
-                raise SvpcError("video features must be contiguous fp32 CUDA tensors of one shape (B, L, F)")
+            if not (f.is_cuda and f.dtype == f0.dtype and f.dtype in _DT and f.is_contiguous() and f.shape == f0.shape):
+                raise SvpcError("video features must be contiguous fp32 (or bf16) CUDA tensors of one shape (B, L, F)")
         key = tuple(f.data_ptr() for f in feats_list)
         ptrs = self._ptr_cache.get(key)
         if ptrs is None:
@@ -445,7 +459,7 @@ class CudaBackend:
         xhat = torch.empty(n_clips * Lv, Fdim, dtype=out_dtype, device=f0.device)
         mean = torch.empty(n_clips * Lv, dtype=torch.float32, device=f0.device)
         rstd = torch.empty(n_clips * Lv, dtype=torch.float32, device=f0.device)
-        self._call("svpc_video_ln_pack", n_clips, B, L, int(Lv), Fdim, _ptr(ptrs), _ptr(clip_t), _ptr(clip_b), _f(eps),
+        self._call("svpc_video_ln_pack", n_clips, B, L, int(Lv), Fdim, _ptr(ptrs), _DT[f0.dtype], _ptr(clip_t), _ptr(clip_b), _f(eps),
                    _ptr(xhat), _DT[out_dtype], _ptr(mean), _ptr(rstd), _ptr(gamma), _ptr(beta), *_drop(drop))
         return xhat, mean, rstd
 
@@ -454,7 +468,8 @@ class CudaBackend:
         dy = self._c(dy)
         dgamma = torch.empty(Fdim, dtype=torch.float32, device=dy.device)
         dbeta = torch.empty(Fdim, dtype=torch.float32, device=dy.device)
-        self._call("svpc_video_ln_affine_bwd", int(clip_t.numel()), B, L, int(Lv), Fdim, _ptr(ptrs), _ptr(clip_t), _ptr(clip_b),
+        self._call("svpc_video_ln_affine_bwd", int(clip_t.numel()), B, L, int(Lv), Fdim, _ptr(ptrs), _DT[feats_list[0].dtype],
+                   _ptr(clip_t), _ptr(clip_b),
                    _ptr(mean), _ptr(rstd), _ptr(dy), _DT[dy.dtype], _ptr(dgamma), _ptr(dbeta), *_drop(drop))
         return dgamma, dbeta
 
@@ -579,7 +594,8 @@ class CudaBackend:
     # ------------------------------------------------------------------ pointer-generator + caption loss
     def pointer_fwd(self, dec, G, Esrc, wpgen, bpgen, logits, lay):
         self._chk(dec, G, Esrc, wpgen, bpgen, logits)
-        dec, G, Esrc, wpgen, logits = self._c(dec), self._c(G), self._c(Esrc), self._c(wpgen), self._c(logits)
+        dec, G, Esrc, wpgen = self._c(dec), self._c(G), self._c(Esrc), self._c(wpgen)
+        logits = self._rowview(logits)                  # (R, V) fp32, rows may be pitched
         Lt, V = int(lay["Lt"]), int(lay["V"])
         R, D = dec.shape
         Nc = R // Lt
@@ -599,7 +615,8 @@ class CudaBackend:
 
     def pointer_bwd(self, dP, dloss, dec, G, Esrc, wpgen, bpgen, logits, lay, P, saved):
         alpha, pgen, ctx = saved
-        dec, G, Esrc, wpgen, logits = self._c(dec), self._c(G), self._c(Esrc), self._c(wpgen), self._c(logits)
+        dec, G, Esrc, wpgen = self._c(dec), self._c(G), self._c(Esrc), self._c(wpgen)
+        logits = self._rowview(logits)
         Lt, V = int(lay["Lt"]), int(lay["V"])
         R, D = dec.shape
         Nc = R // Lt
@@ -611,7 +628,8 @@ class CudaBackend:
         du = torch.empty(R, dtype=torch.float32, device=dev)
         dw = torch.empty(2 * D, dtype=torch.float32, device=dev)
         db = torch.empty(1, dtype=torch.float32, device=dev)
-        dlog = torch.empty_like(logits)
+        # d logits shares the row pitch of the logits (one ldl argument in the C ABI)
+        dlog = torch.empty(R, logits.stride(0), dtype=torch.float32, device=dev)[:, :logits.shape[1]]
         dsc = torch.empty(R, max_ni, dtype=torch.float32, device=dev)
         dloss = dloss.to(torch.float32).reshape(1)
         self._call("svpc_pointer_bwd", Nc, Lt, D, V, max_ni, max_vx, _ptr(dec), _DT[dec.dtype], _ptr(G), _ptr(Esrc),
@@ -624,7 +642,7 @@ class CudaBackend:
 
     def softmax_ls_fwd(self, logits, labels, V, smoothing):
         self._chk(logits, labels)
-        logits = self._c(logits)
+        logits = self._rowview(logits)
         R = logits.shape[0]
         P = torch.empty(R, V, dtype=torch.float32, device=logits.device)
         rows = torch.empty(R, dtype=torch.float32, device=logits.device)

@@ -319,7 +319,8 @@ class LinearFn(Function):
         (ref,) = ctx.saved_tensors
         W, xs_c = ctx.ops
         cd = meta.cd
-        dy = dy.contiguous()
+        if not (dy.dim() == 2 and dy.stride(1) == 1 and meta.act == ACT_NONE and meta.drop is None):
+            dy = dy.contiguous()                      # (a row-pitched gradient - the LM head's - is consumed as it lies)
         need = ctx.needs_input_grad
         d_res = dy if (meta.has_res and need[1]) else None
         L = meta.out_link
