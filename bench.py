@@ -66,6 +66,8 @@ def parse():
     ap.add_argument("--eval-mode", action="store_true", help="run the training step with dropout off (model.eval())")
     ap.add_argument("--no-graph", action="store_true", help="enqueue every kernel from Python instead of replaying a CUDA graph")
     ap.add_argument("--ragged", action="store_true", help="headline step on the ragged batch of SURVEY 8d (train task)")
+    ap.add_argument("--fp32-features", action="store_true",
+                    help="bf16 path: keep the clip features fp32 in the input arena (default: the loader hands them over as bf16)")
     ap.add_argument("--verify-ddp", action="store_true",
                     help="N >= 2: the NCCL data-parallel step on N shards against a 1-rank step on the concatenated batch")
     return ap.parse_args()
@@ -282,7 +284,12 @@ class TrainBench:
         else:
             self.batch = synth.make_batch(self.cfg, B=args.videos, S=args.clips, seed=2019 + rank, ragged=False, n_ingr=10, n_oov=0)
         self.n_clips = self.batch["n_clips"]
-        self.host_args = [tree(lambda t: t.pin_memory(), a) for a in synth.forward_args(self.batch)]
+        # bf16 path: the clip features are handed over as bf16 (what svpc_b200.features.FeatureReader writes into bf16 arena
+        # views): half the upload; LN(3072), the first kernel to read them, computes its statistics in fp32 either way
+        self.feature_dtype = torch.bfloat16 if (cd == torch.bfloat16 and not args.fp32_features) else torch.float32
+        fa = synth.forward_args(self.batch)
+        fa[1] = [t.to(self.feature_dtype) for t in fa[1]]
+        self.host_args = [tree(lambda t: t.pin_memory(), a) for a in fa]
         self.noise_host = [g.pin_memory() for g in self.batch["gumbel"]]
         self.dev_args = [tree(lambda t: t.to(dev, non_blocking=True), a) for a in self.host_args]
         self.noise_dev = [g.to(dev, non_blocking=True) for g in self.noise_host]
@@ -549,6 +556,7 @@ def main():
     # ---------------------------------------------------------------- headline: training step
     tb = TrainBench(args.mode, cd, args, dev, rank, world, train=not args.eval_mode, ragged=args.ragged, graph=not args.no_graph)
     n_clips = tb.n_clips
+    feat_name = "bf16 (rounded once by the loader)" if tb.feature_dtype == torch.bfloat16 else "fp32"
     for _ in range(max(args.warmup, 3)):
         loss = tb.run()
     torch.cuda.synchronize()
@@ -730,7 +738,8 @@ def main():
                        "launch": "eager" if args.no_graph else "cuda-graph replay (fwd+bwd+weight refresh captured once)",
                        "global_videos": world * args.videos, "weights": "random-init (init_bert_weights scale), seed 2019",
                        "dropout": "off (model.eval())" if args.eval_mode else "train mode: hidden 0.1, attention 0.1, action selector 0.4 (reference defaults), counter-based masks recomputed in backward",
-                       "l2": "inputs (295 MB of features per step) exceed the 126 MB L2",
+                       "l2": "inputs (features: 236 MB fp32 / 118 MB bf16 per step) exceed / fill the 126 MB L2; activations (~1 GB per step) evict them between steps",
+                       "features": feat_name,
                        "gflop_per_clip_as_written": GF_PER_CLIP_AS_WRITTEN[args.mode], "gflop_per_clip_needed": round(gf_need, 3),
                        "step_tflops_needed": round(step_tf, 2)},
             "e2e": e2e, "iteration_with_optimizer": iteration, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline,

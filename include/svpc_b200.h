@@ -299,12 +299,13 @@ int svpc_f1_counts(long long n, const float* p, const float* y, double* acc, svp
  * np.float32)` (:332) and the collate stack: each needed row is read once and written once, as fp32, at its final place.
  * svpc_npy_info: shape / dtype code (0 '<f4', 1 '<f8', 2 '<f2') / byte offset of the data of a rank-2 C-ordered .npy.
  * svpc_features_gather: job j copies rows[row_start[j] .. row_start[j+1]) of file paths[j] to rows first_row.. of the clip
- * block dst[j] (block_rows rows of dst_pitch floats) at columns [col_off[j], col_off[j] + file columns) and zero-fills
+ * block dst[j] (block_rows rows of dst_pitch elements) at columns [col_off[j], col_off[j] + file columns) and zero-fills
  * the block's other rows in that column range; jobs run on n_threads host threads.  The row lists come from
  * svpc_b200/features.py `clip_rows` (the host mirror of `_convert_to_feat_index_st_ed` / `_load_indexed_video_feature`). */
 int svpc_npy_info(const char* path, long long* rows, long long* cols, int* dtype, long long* data_offset);
 int svpc_features_gather(int n_jobs, const char* const* paths, const long long* row_start, const long long* rows,
-                         float* const* dst, long long dst_pitch, const long long* col_off, int first_row, int block_rows,
+                         void* const* dst, int dst_dtype /* SVPC_F32, or SVPC_BF16 (round to nearest even) for the half-size upload */,
+                         long long dst_pitch /* elements */, const long long* col_off, int first_row, int block_rows,
                          int n_threads);
 
 #ifdef __cplusplus

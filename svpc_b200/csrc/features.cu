@@ -150,6 +150,28 @@ bool map_file(const char* path, Mapped* m) {
   return true;
 }
 
+// fp32 -> bf16, round to nearest even (what a device-side cast of the reference's fp32 block gives)
+inline unsigned short f32_to_bf16(float f) {
+  unsigned int u;
+  memcpy(&u, &f, 4);
+  if ((u & 0x7fffffffu) > 0x7f800000u) return (unsigned short)((u >> 16) | 0x40);     // NaN stays NaN
+  u += 0x7fffu + ((u >> 16) & 1u);
+  return (unsigned short)(u >> 16);
+}
+
+inline void convert_row_bf16(const unsigned char* src, int dtype, long long cols, unsigned short* dst) {
+  if (dtype == 0) {
+    const float* s = (const float*)src;
+    for (long long c = 0; c < cols; ++c) dst[c] = f32_to_bf16(s[c]);
+  } else if (dtype == 1) {
+    const double* s = (const double*)src;
+    for (long long c = 0; c < cols; ++c) dst[c] = f32_to_bf16((float)s[c]);
+  } else {
+    const __half* s = (const __half*)src;
+    for (long long c = 0; c < cols; ++c) dst[c] = f32_to_bf16(__half2float(s[c]));
+  }
+}
+
 inline void convert_row(const unsigned char* src, int dtype, long long cols, float* dst) {
   if (dtype == 0) {
     memcpy(dst, src, (size_t)cols * 4);
@@ -180,10 +202,11 @@ extern "C" int svpc_npy_info(const char* path, long long* rows, long long* cols,
 // that column range in the block is zero-filled.  Jobs are spread over n_threads host threads; files named by several
 // jobs (the clips of one video) are mapped once.
 extern "C" int svpc_features_gather(int n_jobs, const char* const* paths, const long long* row_start, const long long* rows,
-                                    float* const* dst, long long dst_pitch, const long long* col_off, int first_row,
-                                    int block_rows, int n_threads) {
+                                    void* const* dst, int dst_dtype, long long dst_pitch, const long long* col_off,
+                                    int first_row, int block_rows, int n_threads) {
   if (n_jobs <= 0) return SVPC_OK;
-  if (!paths || !row_start || !rows || !dst || !col_off || dst_pitch <= 0 || first_row < 0 || block_rows <= 0) {
+  if (!paths || !row_start || !rows || !dst || !col_off || dst_pitch <= 0 || first_row < 0 || block_rows <= 0 ||
+      (dst_dtype != SVPC_F32 && dst_dtype != SVPC_BF16)) {
     svpc_set_error("features_gather: bad argument");
     return SVPC_ERR_ARG;
   }
@@ -229,11 +252,19 @@ extern "C" int svpc_features_gather(int n_jobs, const char* const* paths, const 
         const long long cols = m.info.cols, n = row_start[j + 1] - row_start[j];
         const size_t row_bytes = (size_t)cols * esz[m.info.dtype];
         const unsigned char* data = m.base + m.info.data_offset;
-        float* blk = dst[j] + col_off[j];
-        for (int r = 0; r < first_row; ++r) memset(blk + (long long)r * dst_pitch, 0, (size_t)cols * 4);
-        for (long long i = 0; i < n; ++i)
-          convert_row(data + (size_t)rows[row_start[j] + i] * row_bytes, m.info.dtype, cols, blk + (first_row + i) * dst_pitch);
-        for (long long r = first_row + n; r < block_rows; ++r) memset(blk + r * dst_pitch, 0, (size_t)cols * 4);
+        if (dst_dtype == SVPC_F32) {
+          float* blk = (float*)dst[j] + col_off[j];
+          for (int r = 0; r < first_row; ++r) memset(blk + (long long)r * dst_pitch, 0, (size_t)cols * 4);
+          for (long long i = 0; i < n; ++i)
+            convert_row(data + (size_t)rows[row_start[j] + i] * row_bytes, m.info.dtype, cols, blk + (first_row + i) * dst_pitch);
+          for (long long r = first_row + n; r < block_rows; ++r) memset(blk + r * dst_pitch, 0, (size_t)cols * 4);
+        } else {
+          unsigned short* blk = (unsigned short*)dst[j] + col_off[j];
+          for (int r = 0; r < first_row; ++r) memset(blk + (long long)r * dst_pitch, 0, (size_t)cols * 2);
+          for (long long i = 0; i < n; ++i)
+            convert_row_bf16(data + (size_t)rows[row_start[j] + i] * row_bytes, m.info.dtype, cols, blk + (first_row + i) * dst_pitch);
+          for (long long r = first_row + n; r < block_rows; ++r) memset(blk + r * dst_pitch, 0, (size_t)cols * 2);
+        }
       }
     };
     const int nt = n_threads < 1 ? 1 : (n_threads > n_jobs ? n_jobs : n_threads);

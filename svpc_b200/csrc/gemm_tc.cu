@@ -290,29 +290,32 @@ __device__ __forceinline__ void epi_vec(const TcParams& p, uint32_t stage, int m
 // bf16 outputs: the residual / activation-gradient reference rows of the whole chunk (8 rows x 8 bytes per lane) are loaded
 // BEFORE the accumulator chunk is fetched from TMEM, so their L2 latency hides behind tcgen05.ld + the transposition instead
 // of stalling the row loop twice per chunk (the residual epilogues ran at 0.36 of peak against 0.60 plain).
-struct EpiPre { uint2 rr[8]; uint2 gg[8]; };
+struct EpiPre { uint2 rr[8]; uint2 gg[8]; float4 bias; };
 __device__ __forceinline__ void epi_prefetch_bf16(const TcParams& p, int mw, int n, int rsub, EpiPre& o) {
   const int m_first = mw + rsub;
-  const int rows = min(8, (p.M - m_first + 3) >> 2);
+  const int rows = min(8, (p.M - m_first + 3) >> 2);        // >= 1 (the caller checked mw < M ... for rsub = 0; clamped below)
+  // unconditional loads (rows past M re-read the last valid one): a predicated load would be merged into its register with
+  // a PRMT right here, and that PRMT is where the warp would then wait for the data instead of after the TMEM fetch
+  const int last = max(rows - 1, 0);
+  const int m0c = min(m_first, p.M - 1);
+  o.bias = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (p.bias) o.bias = __ldg(reinterpret_cast<const float4*>(p.bias + n));
   if (p.residual) {
-    const bf16* r0 = (const bf16*)p.residual + (long long)m_first * p.ldr + n;
+    const bf16* r0 = (const bf16*)p.residual + (long long)m0c * p.ldr + n;
 #pragma unroll
-    for (int j = 0; j < 8; ++j)
-      if (j < rows) o.rr[j] = *reinterpret_cast<const uint2*>(r0 + (long long)j * 4 * p.ldr);
+    for (int j = 0; j < 8; ++j) o.rr[j] = __ldg(reinterpret_cast<const uint2*>(r0 + (long long)min(j, last) * 4 * p.ldr));
   }
   if (p.gref) {
-    const bf16* g0 = (const bf16*)p.gref + (long long)m_first * p.ldg + n;
+    const bf16* g0 = (const bf16*)p.gref + (long long)m0c * p.ldg + n;
 #pragma unroll
-    for (int j = 0; j < 8; ++j)
-      if (j < rows) o.gg[j] = *reinterpret_cast<const uint2*>(g0 + (long long)j * 4 * p.ldg);
+    for (int j = 0; j < 8; ++j) o.gg[j] = __ldg(reinterpret_cast<const uint2*>(g0 + (long long)min(j, last) * 4 * p.ldg));
   }
 }
 
 template <int ACT, bool DROP>
 __device__ __forceinline__ void epi_vec_bf16(const TcParams& p, uint32_t stage, int mw, int n, int rsub, int g,
                                              uint32_t dkey, float dinv, const EpiPre& o) {
-  float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
-  if (p.bias) bv = *reinterpret_cast<const float4*>(p.bias + n);
+  const float4 bv = o.bias;
   const int m_first = mw + rsub;
   const int rows = min(8, (p.M - m_first + 3) >> 2);
   bf16* __restrict__ d0 = (bf16*)p.D + (long long)m_first * p.ldd + n;

@@ -108,21 +108,25 @@ class FeatureReader:
         return self.max_v_len + self.max_t_len
 
     def load_clips(self, clips, dsts):
-        """``clips``: list of ``(video_name, timestamp, frm2sec)``; ``dsts``: one fp32 CPU tensor ``(max_v_len + max_t_len, D)``
-        per clip with unit column stride and a common row pitch (views of a ``(B, L, D)`` arena tensor qualify).  Returns
-        ``[(video_tokens, mask)]``.  One library call for all clips."""
+        """``clips``: list of ``(video_name, timestamp, frm2sec)``; ``dsts``: one fp32 (or bf16: the half-size upload of
+        the bf16 path, values rounded to nearest even) CPU tensor ``(max_v_len + max_t_len, D)`` per clip with unit column
+        stride and a common row pitch (views of a ``(B, L, D)`` arena tensor qualify).  Returns ``[(video_tokens, mask)]``.
+        One library call for all clips."""
         assert len(clips) == len(dsts)
         if not clips:
             return []
         out, paths, row_start, rows, ptrs, col_off = [], [], [0], [], [], []
         pitch = dsts[0].stride(0)
+        dt0 = dsts[0].dtype
+        if dt0 not in (torch.float32, torch.bfloat16):
+            raise ValueError("clip blocks must be fp32 or bf16, got {}".format(dt0))
         for (name, timestamp, frm2sec), d in zip(clips, dsts):
             feat_len, cols = self.info(name)
             r, tokens, mask = clip_rows(feat_len, timestamp, frm2sec, self.max_v_len)
             out.append((tokens, mask))
-            if (d.dtype != torch.float32 or d.is_cuda or d.dim() != 2 or d.shape[0] != self.block_rows or
+            if (d.dtype != dt0 or d.is_cuda or d.dim() != 2 or d.shape[0] != self.block_rows or
                     d.shape[1] != sum(cols) or d.stride(1) != 1 or d.stride(0) != pitch):
-                raise ValueError("clip block must be a CPU fp32 ({}, {}) tensor with unit column stride and row pitch {}, got "
+                raise ValueError("clip block must be a CPU fp32 / bf16 ({}, {}) tensor with unit column stride and row pitch {}, got "
                                  "{} {} strides {}".format(self.block_rows, sum(cols), pitch, d.dtype, tuple(d.shape), d.stride()))
             c0 = 0
             for p, c in zip(self.paths(name), cols):
@@ -135,7 +139,7 @@ class FeatureReader:
         n = len(paths)
         rc = self.lib.svpc_features_gather(
             n, (C.c_char_p * n)(*paths), (C.c_longlong * (n + 1))(*row_start), (C.c_longlong * max(len(rows), 1))(*rows),
-            (C.c_void_p * n)(*ptrs), C.c_longlong(pitch), (C.c_longlong * n)(*col_off), 1,
+            (C.c_void_p * n)(*ptrs), 1 if dt0 == torch.bfloat16 else 0, C.c_longlong(pitch), (C.c_longlong * n)(*col_off), 1,
             int(self.fill_rows or self.block_rows), int(self.n_threads))
         if rc != 0:
             raise cuda_backend.SvpcError("svpc_features_gather failed ({}): {}".format(rc, self.lib.svpc_last_error().decode()))

@@ -246,6 +246,31 @@ class Link:
 WGRAD = _WgradStream()
 
 
+class _GradSlots:
+    """Where weight-gradient GEMMs write: a data-parallel reducer (svpc_b200.ddp.GradAllReducer) registers itself here and
+    hands out slots of its flat all-reduce buckets, so the summed gradients never need a flatten copy."""
+
+    def __init__(self):
+        self.reducers = []
+
+    def register(self, r):
+        if r not in self.reducers:
+            self.reducers.append(r)
+
+    def unregister(self, r):
+        if r in self.reducers:
+            self.reducers.remove(r)
+
+    def get(self, params):
+        for r in self.reducers:
+            if r.enabled and params and params[0] in r.bucket_of:
+                return r.grad_slot(params)
+        return None
+
+
+GRAD_SLOTS = _GradSlots()
+
+
 class _LinMeta:
     __slots__ = ("n_x", "n_w", "has_bias", "act", "out_dtype", "cd", "w_is_kn", "has_res", "cache", "drop", "in_link",
                  "out_link", "res_link")
@@ -373,10 +398,14 @@ class LinearFn(Function):
         # ---- weight gradients (fp32, written straight into one buffer in the parameters' layout) - on the side stream
         dws = [None] * n_w
         if any(need[2 + n_x:2 + n_x + n_w]):
-            if meta.w_is_kn:
-                dW = torch.empty(xs_c[0].shape[1], dzc.shape[1], dtype=torch.float32, device=dy.device)
-            else:
-                dW = torch.empty(W.shape[0], W.shape[1], dtype=torch.float32, device=dy.device)
+            dW = GRAD_SLOTS.get(ctx.w_params) if (GRAD_SLOTS.reducers and ctx.w_leaf) else None   # a reducer's bucket slot
+            if dW is not None and meta.w_is_kn and tuple(dW.shape) != (xs_c[0].shape[1], dzc.shape[1]):
+                dW = None
+            if dW is None:
+                if meta.w_is_kn:
+                    dW = torch.empty(xs_c[0].shape[1], dzc.shape[1], dtype=torch.float32, device=dy.device)
+                else:
+                    dW = torch.empty(W.shape[0], W.shape[1], dtype=torch.float32, device=dy.device)
             # side stream only when nothing can read dW before the join: the weights are autograd leaves without an
             # accumulated .grad (AccumulateGrad then just adopts the tensor; a non-leaf weight - the LN-folded video
             # projection in eval mode - hands dW to further autograd nodes at once)

@@ -137,7 +137,10 @@ def _flatten(args, noise):
 class GraphedTrainStep:
     N_POS = 13      # positional arguments of StateAwareRecursiveTransformer.forward (reference model.py:1027-1030)
 
-    def __init__(self, model, example_args, gumbel_noise=None, reducer=None, warmup: int = 3):
+    def __init__(self, model, example_args, gumbel_noise=None, reducer=None, warmup: int = 3, feature_dtype=None):
+        """``feature_dtype=torch.bfloat16``: the video features live in the input arena (pinned host, staging, static) as
+        bf16 - half the bytes of every upload.  The first kernel that touches them (LN(3072), statistics in fp32) reads
+        either type; the loader writes bf16 directly (``FeatureReader`` takes bf16 views), ``load()`` converts."""
         assert len(example_args) == self.N_POS
         self.model, self.reducer = model, reducer
         dev = next(model.parameters()).device
@@ -146,7 +149,10 @@ class GraphedTrainStep:
         flat, rebuild = _flatten(list(example_args), gumbel_noise)
         feats = {id(t) for t in example_args[1]} if _is_tensor_list(example_args[1]) else set()
         Lv = model.config.max_v_len
-        self.arena = InputArena(flat, dev, used_rows={i: Lv for i, t in enumerate(flat) if id(t) in feats})
+        self.feature_dtype = feature_dtype or (example_args[1][0].dtype if feats else torch.float32)
+        spec = [torch.empty(t.shape, dtype=self.feature_dtype, device="meta") if id(t) in feats else t for t in flat]
+        self.arena = InputArena(spec, dev, used_rows={i: Lv for i, t in enumerate(flat) if id(t) in feats})
+        self.arena.feature_dtype = {torch.float32: "fp32", torch.bfloat16: "bf16"}.get(self.feature_dtype, str(self.feature_dtype))
         sv = self.arena.static_views()
         for d, t in zip(sv, flat):
             d.copy_(t)

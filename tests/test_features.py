@@ -99,6 +99,21 @@ def test_step_batch_into_a_strided_arena(feat_dir, gold):
                 assert np.array_equal(views[t][b].numpy(), first), (b, t)
 
 
+def test_bf16_blocks_are_the_rounded_fp32_blocks(feat_dir, gold):
+    """bf16 destination (the half-size upload of the bf16 path): every value is the reference's fp32 value rounded to nearest
+    even, the zero rows stay zero, in the same one-call gather into a strided arena."""
+    rd = FeatureReader(feat_dir, FC.MAX_V_LEN, FC.MAX_T_LEN, n_threads=2)
+    L, D = FC.MAX_V_LEN + FC.MAX_T_LEN, sum(FC.COLS)
+    arena = torch.full((len(FC.CLIPS), L, D), float("nan"), dtype=torch.bfloat16)
+    clips = [(name, ts, FC.VIDEOS[name][2]) for name, ts in FC.CLIPS]
+    rd.load_clips(clips, [arena[i] for i in range(len(clips))])
+    for i in range(len(clips)):
+        want = torch.from_numpy(gold["feat_%d" % i]).to(torch.bfloat16)
+        assert torch.equal(arena[i], want), i
+    with pytest.raises(ValueError):
+        rd.load_clips(clips[:1], [torch.zeros(L, D, dtype=torch.float16)])
+
+
 def test_full_width_rows_and_downsampling_match_oracle(tmp_path):
     """YouCook2 widths (2048 + 1024), 100 video slots: long clips are down-sampled to 98 rows (:403-404)."""
     rng = np.random.default_rng(7)

@@ -260,3 +260,27 @@ def test_token_csr_updates_do_not_race_the_upload():
     torch.cuda.synchronize()
     for w, l in zip(want, losses):
         assert abs(float(l) - w) <= 1e-6 * abs(w), (float(l), w)
+
+
+def test_bf16_features_in_the_arena():
+    """The bf16 path takes the clip features as bf16 (half the upload): same loss as with fp32 features within 2e-3, through
+    the eager call and through a captured step whose arena holds bf16 feature blocks; `load()` converts fp32 host features."""
+    from svpc_b200.graph import GraphedTrainStep
+    cfg = youcook2_config("full")
+    sd = synth.init_state_dict(cfg, seed=3)
+    batch = synth.make_batch(cfg, B=2, S=3, seed=11, ragged=True, n_ingr=6, n_oov=2)
+    m = build(cfg, sd, torch.bfloat16)
+    noise = [g.to(DEV) for g in batch["gumbel"]]
+    args32 = forward_args(batch, DEV)
+    l32 = float(m(*args32, gumbel_noise=noise)[0])
+    args16 = list(args32)
+    args16[1] = [t.to(torch.bfloat16) for t in args32[1]]
+    l16 = float(m(*args16, gumbel_noise=noise)[0])
+    assert abs(l16 - l32) <= 2e-3 * abs(l32), (l16, l32)
+    step = GraphedTrainStep(m, args16, gumbel_noise=noise)
+    assert step.feature_dtype == torch.bfloat16
+    lg = float(step.run())
+    assert abs(lg - l16) <= 1e-5 * abs(l16), (lg, l16)
+    step.load(forward_args(batch), batch["gumbel"])          # fp32 host features: converted on the way in
+    lg2 = float(step.run())
+    assert abs(lg2 - l16) <= 1e-5 * abs(l16), (lg2, l16)

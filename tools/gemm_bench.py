@@ -34,6 +34,7 @@ SHAPES = [
 
 def main():
     reps = int(sys.argv[1]) if len(sys.argv) > 1 else 20
+    only = [int(x) for x in sys.argv[2].split(",")] if len(sys.argv) > 2 else None      # indices into SHAPES
     dev = torch.device("cuda")
     be = backend.get()
     peak = 1400.0
@@ -41,7 +42,9 @@ def main():
     if os.path.isfile(p):
         peak = json.load(open(p)).get("bf16_tflops_sustained", peak)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
-    for M, N, K, lay, epi in SHAPES:
+    for si, (M, N, K, lay, epi) in enumerate(SHAPES):
+        if only is not None and si not in only:
+            continue
         a = torch.randn((K, M) if lay[0] == "T" else (M, K), device=dev).to(torch.bfloat16)
         b = torch.randn((K, N) if lay[1] == "T" else (N, K), device=dev).to(torch.bfloat16)
         a = a.t() if lay[0] == "T" else a
