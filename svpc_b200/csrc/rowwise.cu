@@ -342,44 +342,30 @@ __global__ void __launch_bounds__(256) act_bwd_vec_kernel(int rows, int cols, co
 #pragma unroll
   for (int e = 0; e < 8; ++e) acc[e] = 0.f;
   if (c0 < cols) {
-    // four rows per iteration: eight independent 16-byte loads in flight per thread (the kernel is a pure stream)
-    const int rstep = gridDim.y * 8;
-    for (int r0 = blockIdx.y * 8 + ty; r0 < rows; r0 += 4 * rstep) {
-      float g[4][8], y[4][8];
+    for (int r = blockIdx.y * 8 + ty; r < rows; r += gridDim.y * 8) {
+      const long long o = (long long)r * cols + c0;
+      float g[8], y[8];
+      ld8(dy + o, g);
+      if (dropping) {                    // cols % 8 == 0 and c0 % 8 == 0: o is even, (o + e, o + e + 1) are aligned pairs
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int r = r0 + u * rstep;
-        if (r < rows) {
-          const long long o = (long long)r * cols + c0;
-          ld8(dy + o, g[u]);
-          if (act != SVPC_ACT_NONE) ld8(ref + o, y[u]);
+        for (int e = 0; e < 8; e += 2) {
+          float s0, s1;
+          svpc_drop_scale2(dkey, drop.p, dinv, (unsigned long long)(o + e), s0, s1);
+          g[e] *= s0; g[e + 1] *= s1;
         }
       }
+      if (act != SVPC_ACT_NONE) {
+        ld8(ref + o, y);
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int r = r0 + u * rstep;
-        if (r >= rows) break;
-        const long long o = (long long)r * cols + c0;
-        if (dropping) {                    // cols % 8 == 0 and c0 % 8 == 0: o is even, (o + e, o + e + 1) are aligned pairs
-#pragma unroll
-          for (int e = 0; e < 8; e += 2) {
-            float s0, s1;
-            svpc_drop_scale2(dkey, drop.p, dinv, (unsigned long long)(o + e), s0, s1);
-            g[u][e] *= s0; g[u][e + 1] *= s1;
-          }
+        for (int e = 0; e < 8; ++e) {
+          if (act == SVPC_ACT_RELU) g[e] = y[e] > 0.f ? g[e] : 0.f;
+          else if (act == SVPC_ACT_GELU) g[e] *= svpc_gelu_grad(y[e]);
+          else g[e] *= y[e] * (1.f - y[e]);
         }
-        if (act != SVPC_ACT_NONE) {
-#pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            if (act == SVPC_ACT_RELU) g[u][e] = y[u][e] > 0.f ? g[u][e] : 0.f;
-            else if (act == SVPC_ACT_GELU) g[u][e] *= svpc_gelu_grad(y[u][e]);
-            else g[u][e] *= y[u][e] * (1.f - y[u][e]);
-          }
-        }
-        if (dz) st8(dz + o, g[u]);
-#pragma unroll
-        for (int e = 0; e < 8; ++e) acc[e] += g[u][e];
       }
+      if (dz) st8(dz + o, g);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) acc[e] += g[e];
     }
   }
 #pragma unroll
@@ -399,7 +385,7 @@ static inline bool rw_al16(const void* p) { return ((uintptr_t)p & 15) == 0; }
 static int act_bwd_vec_launch(int rows, int cols, const void* dy, const void* ref, int dt, int act, void* dz, float* dbias,
                               SvpcDrop drop, cudaStream_t st) {
   const int gx = svpc_cdiv(cols, 256);
-  dim3 grid(gx, svpc_imin(svpc_cdiv(rows, 32), svpc_cdiv(SVPC_NUM_SMS * 8, gx)));
+  dim3 grid(gx, svpc_imin(svpc_cdiv(rows, 8), svpc_cdiv(SVPC_NUM_SMS * 4, gx)));
   SVPC_DISPATCH(dt, T, (svpc_launch(act_bwd_vec_kernel<T>, grid, 256, 0, st, rows, cols, (const T*)dy, (const T*)ref, act, (T*)dz, dbias, drop)));
   return svpc_check_launch("act_bwd");
 }
@@ -614,12 +600,68 @@ __global__ void index_colsum_kernel(int rows, int D, const T* __restrict__ dy, c
     if (b < nbins) atomicAdd(out + (long long)b * D + c, acc[b]);
 }
 
+// 8 columns (one 16-byte load of bf16) per thread, 8 row lanes per CTA, up to NB bins in registers: the token-type gradient
+// reads the (19200, 768) gradient once at streaming speed instead of two bytes per thread per row
+template <typename T, int NB>
+__global__ void __launch_bounds__(256) index_colsum_vec_kernel(int rows, int D, const T* __restrict__ dy,
+                                                               const int* __restrict__ ids, int nbins,
+                                                               float* __restrict__ out) {
+  svpc_pdl_sync();
+  __shared__ float red[8][256];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int c0 = (blockIdx.x * 32 + tx) * 8;
+  float acc[NB][8];
+#pragma unroll
+  for (int b = 0; b < NB; ++b)
+#pragma unroll
+    for (int e = 0; e < 8; ++e) acc[b][e] = 0.f;
+  if (c0 < D) {
+    const int rstep = gridDim.y * 8;
+    for (int r0 = blockIdx.y * 8 + ty; r0 < rows; r0 += 2 * rstep) {
+      float g0[8], g1[8];
+      const int r1 = r0 + rstep;
+      const bool has1 = r1 < rows;
+      ld8(dy + (long long)r0 * D + c0, g0);
+      if (has1) ld8(dy + (long long)r1 * D + c0, g1);
+      const int id0 = ids[r0], id1 = has1 ? ids[r1] : -1;
+#pragma unroll
+      for (int b = 0; b < NB; ++b)
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          acc[b][e] += (id0 == b) ? g0[e] : 0.f;
+          if (has1) acc[b][e] += (id1 == b) ? g1[e] : 0.f;
+        }
+    }
+  }
+#pragma unroll
+  for (int b = 0; b < NB; ++b) {
+    if (b >= nbins) break;
+    __syncthreads();
+#pragma unroll
+    for (int e = 0; e < 8; ++e) red[ty][tx * 8 + e] = acc[b][e];
+    __syncthreads();
+    const int c = blockIdx.x * 256 + threadIdx.x;
+    if (c < D) {
+      float t = 0.f;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) t += red[w][threadIdx.x];
+      atomicAdd(out + (long long)b * D + c, t);
+    }
+  }
+}
+
 extern "C" int svpc_index_colsum(int rows, int D, const void* dy, int dt, const int* ids, int nbins, float* out,
                                  svpc_stream_t stream) {
   SVPC_REQUIRE(nbins <= 8, "index_colsum: nbins=%d > 8", nbins);
   cudaStream_t st = (cudaStream_t)stream;
   cudaMemsetAsync(out, 0, sizeof(float) * nbins * D, st);
   if (rows <= 0) return SVPC_OK;
+  if (D % 8 == 0 && nbins <= 4 && rw_al16(dy)) {
+    const int gx = svpc_cdiv(D, 256);
+    dim3 grid(gx, svpc_imin(svpc_cdiv(rows, 16), svpc_cdiv(SVPC_NUM_SMS * 4, gx)));
+    SVPC_DISPATCH(dt, T, (svpc_launch(index_colsum_vec_kernel<T, 4>, grid, 256, 0, st, rows, D, (const T*)dy, ids, nbins, out)));
+    return svpc_check_launch("index_colsum");
+  }
   dim3 grid(svpc_cdiv(D, 128), svpc_imin(rows, 256));
   SVPC_DISPATCH(dt, T, (svpc_launch(index_colsum_kernel<T>, grid, 128, 0, st, rows, D, (const T*)dy, ids, nbins, out)));
   return svpc_check_launch("index_colsum");
@@ -832,6 +874,77 @@ __global__ void __launch_bounds__(RW_THREADS) video_ln_pack_kernel(int n_rows, i
   }
 }
 
+// bf16 features -> bf16 rows, one WARP per row (F = 3072: 12 x 16 bytes per lane kept packed in 48 registers): no block
+// barriers, 8 independent rows per CTA in flight.  Two-pass statistics (mean, then centred second moment) as above.
+template <int NCH>
+__global__ void __launch_bounds__(256) video_ln_pack_warp_kernel(int n_rows, int B, int L, int Lv,
+                                                                 const long long* __restrict__ feat_ptrs,
+                                                                 const int* __restrict__ clip_t, const int* __restrict__ clip_b,
+                                                                 float eps, bf16* __restrict__ xhat, float* __restrict__ mean,
+                                                                 float* __restrict__ rstd, const float* __restrict__ gamma,
+                                                                 const float* __restrict__ beta, const SvpcDrop drop) {
+  svpc_pdl_sync();
+  constexpr int F = NCH * 256;
+  const bool dropping = drop.seed != nullptr && drop.p > 0.f;
+  const uint32_t dkey = svpc_drop_key(drop);
+  const float dinv = dropping ? 1.f / (1.f - drop.p) : 1.f;
+  const int lane = threadIdx.x & 31;
+  const int nw = gridDim.x * 8;
+  for (int r = blockIdx.x * 8 + (threadIdx.x >> 5); r < n_rows; r += nw) {
+    const int n = r / Lv, row = r - n * Lv;
+    const bf16* src = reinterpret_cast<const bf16*>(feat_ptrs[clip_t[n]]) + ((long long)clip_b[n] * L + row) * F;
+    uint4 raw[NCH];
+#pragma unroll
+    for (int i = 0; i < NCH; ++i) raw[i] = __ldg(reinterpret_cast<const uint4*>(src + i * 256 + lane * 8));
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < NCH; ++i) {
+      const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw[i]);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) s += __low2float(h[e]) + __high2float(h[e]);
+    }
+    const float mu = warp_sum(s) * (1.0f / F);
+    float q = 0.f;
+#pragma unroll
+    for (int i = 0; i < NCH; ++i) {
+      const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw[i]);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float a = __low2float(h[e]) - mu, b = __high2float(h[e]) - mu;
+        q = fmaf(a, a, q);
+        q = fmaf(b, b, q);
+      }
+    }
+    const float rs = 1.0f / sqrtf(warp_sum(q) * (1.0f / F) + eps);
+    if (lane == 0) { mean[r] = mu; rstd[r] = rs; }
+    bf16* dst = xhat + (long long)r * F;
+#pragma unroll
+    for (int i = 0; i < NCH; ++i) {
+      const int c = i * 256 + lane * 8;
+      const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw[i]);
+      float o[8];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) { o[2 * e] = (__low2float(h[e]) - mu) * rs; o[2 * e + 1] = (__high2float(h[e]) - mu) * rs; }
+      if (gamma) {                       // train mode: LN affine and dropout applied here (model.py:549-550)
+        float g[8], bb[8];
+        ld8(gamma + c, g);
+        ld8(beta + c, bb);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) o[e] = o[e] * g[e] + bb[e];
+        if (dropping) {
+#pragma unroll
+          for (int e = 0; e < 8; e += 2) {
+            float s0, s1;
+            svpc_drop_scale2(dkey, drop.p, dinv, (unsigned long long)r * F + c + e, s0, s1);
+            o[e] *= s0; o[e + 1] *= s1;
+          }
+        }
+      }
+      st8(dst + c, o);
+    }
+  }
+}
+
 extern "C" int svpc_video_ln_pack(int n_clips, int B, int L, int Lv, int F, const long long* feat_ptrs, int dt_feat,
                                   const int* clip_t, const int* clip_b, float eps, void* xhat, int dt, float* mean,
                                   float* rstd, const float* gamma, const float* beta, const unsigned int* drop_seed,
@@ -842,6 +955,11 @@ extern "C" int svpc_video_ln_pack(int n_clips, int B, int L, int Lv, int F, cons
   SVPC_REQUIRE(F % 4 == 0 && F <= RW_THREADS * RW_MAXPT, "video_ln_pack: F=%d must be a multiple of 4 and <= 4096", F);
   cudaStream_t st = (cudaStream_t)stream;
   const int n_rows = n_clips * Lv;
+  if (dt == SVPC_BF16 && dt_feat == SVPC_BF16 && F == 3072 && rw_al16(xhat) && rw_al16(gamma) && rw_al16(beta)) {
+    svpc_launch(video_ln_pack_warp_kernel<12>, svpc_imin(svpc_cdiv(n_rows, 8), SVPC_NUM_SMS * 8), 256, 0, st, n_rows, B, L, Lv,
+                feat_ptrs, clip_t, clip_b, eps, (bf16*)xhat, mean, rstd, gamma, beta, drop);
+    return svpc_check_launch("video_ln_pack");
+  }
   SVPC_DISPATCH(dt, T, SVPC_DISPATCH(dt_feat, TF, (svpc_launch(video_ln_pack_kernel<T, TF>, svpc_imin(n_rows, SVPC_NUM_SMS * 16),
       RW_THREADS, 0, st, n_rows, B, L, Lv, F, feat_ptrs, clip_t, clip_b, eps, (T*)xhat, mean, rstd, gamma, beta, drop))));
   return svpc_check_launch("video_ln_pack");
@@ -872,23 +990,37 @@ __global__ void __launch_bounds__(256) video_ln_affine_bwd_kernel(int n_rows, in
 #pragma unroll
   for (int e = 0; e < 8; ++e) { ag[e] = 0.f; ab[e] = 0.f; }
   if (c0 < F) {
-    for (int r = blockIdx.y * 8 + ty; r < n_rows; r += gridDim.y * 8) {
-      const int n = r / Lv, row = r - n * Lv;
-      const TF* src = reinterpret_cast<const TF*>(feat_ptrs[clip_t[n]]) + ((long long)clip_b[n] * L + row) * F + c0;
-      const float mu = mean[r], rs = rstd[r];
-      float d[8], x[8];
-      ld8(dy + (long long)r * F + c0, d);
-      ld8(src, x);
-      if (dropping) {
+    const int rstep = gridDim.y * 8;
+    for (int r0 = blockIdx.y * 8 + ty; r0 < n_rows; r0 += 2 * rstep) {      // two rows per iteration: four loads in flight
+      float d[2][8], x[2][8], mu[2], rs[2];
+      bool has[2];
 #pragma unroll
-        for (int e = 0; e < 8; e += 2) {
-          float s0, s1;
-          svpc_drop_scale2(dkey, drop.p, dinv, (unsigned long long)r * F + c0 + e, s0, s1);
-          d[e] *= s0; d[e + 1] *= s1;
+      for (int u = 0; u < 2; ++u) {
+        const int r = r0 + u * rstep;
+        has[u] = r < n_rows;
+        if (has[u]) {
+          const int n = r / Lv, row = r - n * Lv;
+          const TF* src = reinterpret_cast<const TF*>(feat_ptrs[clip_t[n]]) + ((long long)clip_b[n] * L + row) * F + c0;
+          mu[u] = mean[r]; rs[u] = rstd[r];
+          ld8(dy + (long long)r * F + c0, d[u]);
+          ld8(src, x[u]);
         }
       }
 #pragma unroll
-      for (int e = 0; e < 8; ++e) { ag[e] = fmaf(d[e], (x[e] - mu) * rs, ag[e]); ab[e] += d[e]; }
+      for (int u = 0; u < 2; ++u) {
+        if (!has[u]) break;
+        const int r = r0 + u * rstep;
+        if (dropping) {
+#pragma unroll
+          for (int e = 0; e < 8; e += 2) {
+            float s0, s1;
+            svpc_drop_scale2(dkey, drop.p, dinv, (unsigned long long)r * F + c0 + e, s0, s1);
+            d[u][e] *= s0; d[u][e + 1] *= s1;
+          }
+        }
+#pragma unroll
+        for (int e = 0; e < 8; ++e) { ag[e] = fmaf(d[u][e], (x[u][e] - mu[u]) * rs[u], ag[e]); ab[e] += d[u][e]; }
+      }
     }
   }
 #pragma unroll

@@ -224,6 +224,66 @@ def test_video_ln_pack(cb, tb, dt):
     assert float(x[0].abs().max()) == 0
 
 
+def test_video_ln_pack_bf16_features(cb, tb):
+    """The bf16 upload path: bf16 feature blocks at the real width (3072) through the warp-per-row kernel, eval (plain
+    normalisation) and train mode (affine + dropout mask at element index row * F + c), and the affine backward."""
+    S, B, L, Lv, Fd = 2, 2, 12, 9, 3072
+    feats32 = [rnd(B, L, Fd, seed=20 + s) for s in range(S)]
+    feats = [f.to(BF16) for f in feats32]
+    ct, cbb = I32([0, 1, 0, 1]), I32([0, 0, 1, 1])
+    x, mean, rstd = cb.video_ln_pack(feats, ct, cbb, Lv, 1e-12, BF16)
+    rx, rmean, rrstd = tb.video_ln_pack([f.float() for f in feats], ct, cbb, Lv, 1e-12, torch.float64)
+    close("video xhat (bf16 in)", x, rx, 1e-2)
+    close("video mean (bf16 in)", mean, rmean, 1e-5)
+    close("video rstd (bf16 in)", rstd, rrstd, 1e-5)
+    gamma, beta = 1 + 0.1 * rnd(Fd, seed=7), 0.1 * rnd(Fd, seed=8)
+    drop = (torch.tensor([11], dtype=torch.int32, device=DEV), 5, 0.1)
+    rows = 4 * Lv
+    mask = cb.dropout_mask(rows * Fd, drop).view(rows, Fd)
+    y, _, _ = cb.video_ln_pack(feats, ct, cbb, Lv, 1e-12, BF16, gamma=gamma, beta=beta, drop=drop)
+    close("video affine+drop (bf16 in)", y, (rx * gamma.double() + beta.double()) * mask.double(), 1e-2)
+    dy = rnd(rows, Fd, dtype=BF16, seed=9)
+    dg, db = cb.video_ln_affine_bwd(dy, feats, ct, cbb, Lv, mean, rstd, drop=drop)
+    close("video dgamma (bf16 in)", dg, (dy.double() * mask.double() * rx).sum(0), 2e-3)
+    close("video dbeta (bf16 in)", db, (dy.double() * mask.double()).sum(0), 2e-3)
+
+
+@pytest.mark.parametrize("dt", [F32, BF16])
+@pytest.mark.parametrize("rows,D", [(200, 768), (37, 64)])
+def test_ln_bwd_fused_activation_backward(cb, tb, dt, rows, D):
+    """ln_bwd with the dz output: dz = dpre * dropscale * act'(ref) and its column sums, against ln_bwd followed by act_bwd."""
+    dy, pre, ref = rnd(rows, D, dtype=dt, seed=1), rnd(rows, D, dtype=dt, seed=2), rnd(rows, D, dtype=dt, seed=3)
+    mean, rstd = pre.float().mean(1), 1.0 / (pre.float().var(1, unbiased=False) + 1e-12).sqrt()
+    g = 1 + 0.1 * rnd(D, seed=4)
+    drop = (torch.tensor([5], dtype=torch.int32, device=DEV), 9, 0.1)
+    tol = 1e-5 if dt == F32 else 2e-2
+    for act, r, d in ((0, None, drop), (2, ref, None), (1, None, None), (1, ref, drop), (3, torch.sigmoid(ref.float()).to(dt), None)):
+        dpre, dg, db, dz, dbias = cb.ln_bwd(dy, pre, mean, rstd, g, fuse=(act, r, d, True))
+        dpre0, dg0, db0 = cb.ln_bwd(dy, pre, mean, rstd, g)
+        dz0, dbias0 = cb.act_bwd(dpre0, pre if (r is None and act == 1) else r, act, drop=d)
+        assert torch.equal(dpre, dpre0)
+        close(f"fused dgamma act{act}", dg, dg0, 1e-4); close(f"fused dbeta act{act}", db, db0, 1e-4)
+        close(f"fused dz act{act}", dz, dz0, tol)
+        close(f"fused dbias act{act}", dbias, dbias0, 2e-3 if dt == BF16 else 1e-4)
+
+
+@pytest.mark.parametrize("dt,M,N,K", [(BF16, 256, 192, 128), (F32, 70, 50, 33), (BF16, 4800, 768, 768), (F32, 200, 768, 768)])
+def test_gemm_fused_activation_gradient(cb, tb, dt, M, N, K):
+    """Input-gradient GEMM whose epilogue adds the skip-connection gradient and multiplies by act'(ref): the previous
+    Linear's dz written by the GEMM itself."""
+    a, w = rnd(M, K, dtype=dt, scale=0.3), rnd(N, K, dtype=dt, seed=1, scale=0.3)
+    res, ref = rnd(M, N, dtype=dt, seed=3), rnd(M, N, dtype=dt, seed=4)
+    base = a.double() @ w.double().t()
+    tol = 2e-2 if dt == BF16 else 1e-4
+    for act in (1, 2, 3):
+        r = torch.sigmoid(ref.float()).to(dt) if act == 3 else ref
+        got = cb.gemm(a, w, dt, residual=res, grad_act=(act, r))
+        want = tb.act_bwd((base + res.double()), r.double(), act)[0]
+        close(f"gemm grad_act {act}", got, want, tol)
+    got = cb.gemm(a, w, dt, grad_act=(2, ref))
+    close("gemm grad_act no residual", got, tb.act_bwd(base, ref.double(), 2)[0], tol)
+
+
 # ---------------------------------------------------------------------------------------------- attention
 ATT_CASES = {
     # name: (q_len list, k_len list, causal, use mask, cross)
