@@ -365,9 +365,10 @@ def measure_decode(model, batch, n_videos, args, dev, world, timer, be, e2e=True
     from svpc_b200.graph import GraphedDecoder
     host = tile_decode_inputs(batch, n_videos)
     n_caps = int(sum(host[11]))
+    fdt = torch.bfloat16 if model.compute_dtype == torch.bfloat16 and not args.fp32_features else torch.float32
     resident = tuple(tree(lambda t: t.to(dev), x) for x in host)
     be.reset_launch_count()
-    gdec = GraphedDecoder(model, resident, warmup=1)
+    gdec = GraphedDecoder(model, resident, warmup=1, feature_dtype=fdt)
     per_replay = be.launch_count() // 2
     steps = max(2, min(args.steps, 10))
     with torch.no_grad():
@@ -378,8 +379,14 @@ def measure_decode(model, batch, n_videos, args, dev, world, timer, be, e2e=True
            "value": round(world * n_caps * steps / (ms / 1e3), 1), "unit": "captions/s", "ms_per_step": round(ms / steps, 3),
            "gpu_launches_per_step": per_replay}
     if e2e:
-        hp = tuple(tree(lambda t: t.pin_memory(), x) for x in host)
-        h2d = sum(nbytes(x) for x in hp[:7])
+        # the loader's collate target: the pinned host twin of the decoder's input arena (features as `fdt`)
+        hp = gdec.host_inputs()
+        for i in GraphedDecoder.TENSOR_LISTS:
+            for d_, s_ in zip(hp[i], host[i]):
+                d_.copy_(s_)
+        for i in GraphedDecoder.TENSORS:
+            hp[i].copy_(torch.as_tensor(host[i]))
+        h2d = gdec.arena.h2d_nbytes
         d2h = sum(s.numel() * 8 for s in seqs)
 
         def e2e_steps(k):
@@ -394,7 +401,8 @@ def measure_decode(model, batch, n_videos, args, dev, world, timer, be, e2e=True
             e2e_steps(2)
             ms_e = timer(lambda: e2e_steps(steps), 1)
         out["e2e"] = {"value": round(world * n_caps * steps / (ms_e / 1e3), 1), "unit": "captions/s",
-                      "ms_per_step": round(ms_e / steps, 3), "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)}
+                      "ms_per_step": round(ms_e / steps, 3), "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                      "upload_dtype": gdec.arena.feature_dtype}
         del hp
     del gdec, resident, host
     free_cuda()

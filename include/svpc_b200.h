@@ -171,7 +171,7 @@ int svpc_row_normalize_bwd(int rows, int cols, const float* dy, const float* x, 
 int svpc_reasoner_fwd(int B, int D, int max_ni, int max_steps, const float* E0, const int* cu_ingr, const int* cu_steps,
                       const int* clip_ent_off, const float* w2v, const float* clog, const float* w4s, float* ent,
                       float* ebar, float* Es, float* a_saved, svpc_stream_t stream);
-int svpc_reasoner_bwd(int B, int D, int max_ni, const float* E0, const int* cu_ingr, const int* cu_steps,
+int svpc_reasoner_bwd(int B, int D, int max_ni, int max_steps, const float* E0, const int* cu_ingr, const int* cu_steps,
                       const int* clip_ent_off, const float* w2v, const float* clog, const float* w4s, const float* ent,
                       const float* ebar, const float* Es, const float* a_saved, const float* d_ent, const float* d_ebar,
                       const float* d_Es, float* dE0, float* dw2v, float* dclog, float* dw4s, svpc_stream_t stream);

@@ -585,7 +585,8 @@ class CudaBackend:
         dw2v = torch.empty_like(w2v)
         dclog = torch.empty_like(clog)
         dw4s = torch.empty_like(w4s)
-        self._call("svpc_reasoner_bwd", B, D, max_ni, _ptr(E0), _ptr(cu_ingr), _ptr(cu_steps), _ptr(clip_ent_off),
+        self._call("svpc_reasoner_bwd", B, D, max_ni, int(lay.get("max_steps", 0)), _ptr(E0), _ptr(cu_ingr), _ptr(cu_steps),
+                   _ptr(clip_ent_off),
                    _ptr(w2v), _ptr(clog), _ptr(w4s), _ptr(ent), _ptr(ebar), _ptr(Es), _ptr(a),
                    _ptr(self._c(d_ent)), _ptr(self._c(d_ebar)), _ptr(self._c(d_Es)), _ptr(dE0), _ptr(dw2v), _ptr(dclog),
                    _ptr(dw4s))

@@ -229,6 +229,13 @@ class StateAwareRecursiveTransformer(nn.Module):
         self._invalidate()
         return r
 
+    def train(self, mode: bool = True):
+        """Switching between train and eval marks the cached compute-dtype weight copies stale: an optimiser that updates
+        ``param.data`` in place (the reference's BertAdam, optimization.py:327) does not bump the autograd version counters
+        the cache is keyed on."""
+        Fn.WEIGHTS.invalidate()
+        return super().train(mode)
+
     def _invalidate(self):
         """Parameters were moved / replaced: drop the name -> tensor cache and mark the compute-dtype weight copies stale.
         Their buffers are NOT freed here: another model's captured graph may be reading them (the cache is keyed by
@@ -526,6 +533,8 @@ class StateAwareRecursiveTransformer(nn.Module):
         f32 = torch.float32
         dev = video_features_list[0].device
         self._begin_step(dev)
+        if self.training:
+            Fn.WEIGHTS.invalidate()       # a training step follows an optimiser step: `.data` updates are invisible to versions
         Fn.WEIGHTS.refresh_all()          # compute-dtype weight copies touched by the optimiser: one multi-tensor cast
         if plan is None:
             self._sep_counts = ingr_sep_masks if mode != "video" else None

@@ -122,3 +122,28 @@ def test_graphed_decoder_matches_eager(mode):
     torch.cuda.synchronize()
     for b, s in enumerate(seqs):
         assert torch.equal(s.cpu(), torch.from_numpy(gold[f"greedy.{b}"])), (mode, b)
+
+
+def test_graphed_decoder_arena_pipeline():
+    """The decoder's inputs through the pinned host arena (what a loader fills) and the copy-stream prefetch: same captions as
+    a synchronous load, with the never-read text rows of the feature blocks poisoned on the host (they are not uploaded)."""
+    from svpc_b200.graph import GraphedDecoder
+    cfg, m, batch, gold = build("full")
+    inputs = decode_inputs(batch, DEV)
+    dec = GraphedDecoder(m, inputs)
+    hp = dec.host_inputs()
+    src = decode_inputs(batch)
+    for i in GraphedDecoder.TENSOR_LISTS:
+        for d, s in zip(hp[i], src[i]):
+            d.copy_(s)
+    for i in GraphedDecoder.TENSORS:
+        hp[i].copy_(torch.as_tensor(src[i]))
+    for f in hp[1]:
+        f[:, cfg.max_v_len:] = float("nan")
+    assert dec.arena.h2d_nbytes < dec.arena.nbytes
+    for _ in range(2):
+        dec.prefetch(hp)
+        seqs = dec.run_prefetched()
+    torch.cuda.synchronize()
+    for b, s in enumerate(seqs):
+        assert torch.equal(s.cpu(), torch.from_numpy(gold[f"greedy.{b}"])), b

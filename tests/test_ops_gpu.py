@@ -264,7 +264,7 @@ def test_ln_bwd_fused_activation_backward(cb, tb, dt, rows, D):
         assert torch.equal(dpre, dpre0)
         close(f"fused dgamma act{act}", dg, dg0, 1e-4); close(f"fused dbeta act{act}", db, db0, 1e-4)
         close(f"fused dz act{act}", dz, dz0, tol)
-        close(f"fused dbias act{act}", dbias, dbias0, 2e-3 if dt == BF16 else 1e-4)
+        close(f"fused dbias act{act}", dbias, dbias0, 2e-2 if dt == BF16 else 1e-4)      # (sums of bf16-rounded vs fp32 terms)
 
 
 @pytest.mark.parametrize("dt,M,N,K", [(BF16, 256, 192, 128), (F32, 70, 50, 33), (BF16, 4800, 768, 768), (F32, 200, 768, 768)])
