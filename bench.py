@@ -572,7 +572,7 @@ def main():
 
     # ---- parity of the timed model: eval-mode loss on the timed batch against the CPU oracle (rank 0)
     parity = None
-    if rank == 0 and not args.no_parity:
+    if rank == 0 and world == 1 and not args.no_parity:      # (N > 1: the other ranks would spin at a barrier on the cores the oracle needs)
         from oracle import svpc_oracle as O
         torch.set_num_threads(physical_cores())
         t0 = time.perf_counter()

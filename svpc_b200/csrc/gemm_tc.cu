@@ -658,7 +658,7 @@ static bool operand_ok(long long s_mn, long long s_k, int mn, int K) {
 int svpc_gemm_tc_eligible(int M, int N, int K, int dtA, long long sa_m, long long sa_k, int dtB, long long sb_n,
                           long long sb_k, int dtD, long long ldd) {
   if (dtA != SVPC_BF16 || dtB != SVPC_BF16) return 0;
-  if (M < 64 || N < 16 || K < 32) return 0;
+  if (M < 16 || N < 16 || K < 32) return 0;        // (rows past M are zero-filled by TMA and never stored)
   if (!operand_ok(sa_m, sa_k, M, K) || !operand_ok(sb_n, sb_k, N, K)) return 0;
   (void)dtD; (void)ldd;
   return 1;

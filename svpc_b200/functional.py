@@ -192,12 +192,17 @@ class _WgradStream:
 
     def __init__(self):
         self.enabled = _os.environ.get("SVPC_WGRAD_STREAM", "1") != "0"
+        self.eager_too = _os.environ.get("SVPC_WGRAD_STREAM", "1") == "2"
         self.streams = {}
         self.keep = []
         self.active = set()
         self.cb_queued = False
 
     def fork(self, device):
+        # outside a CUDA-graph capture the step is bound by the interpreter issuing launches, not by the GPU: the stream
+        # switches would only add host time there (SVPC_WGRAD_STREAM=2 forces the side stream in eager mode too)
+        if self.eager_too is False and not torch.cuda.is_current_stream_capturing():
+            return None
         main = torch.cuda.current_stream(device)
         side = self.streams.get(device)
         if side is None:

@@ -70,7 +70,9 @@ def test_gemm_simt(cb, tb, dt, M, N, K):
 TC_SHAPES = [(128, 128, 64), (256, 128, 128), (200, 951, 768), (1000, 768, 3072), (384, 64, 96), (130, 72, 40),
              (4800, 768, 768),
              # persistent schedule: several rounds per SM + a last round cut into narrower column slices
-             (19200, 768, 192), (4800, 2304, 128), (19000, 700, 72), (192, 768, 768), (20000, 300, 64)]
+             (19200, 768, 192), (4800, 2304, 128), (19000, 700, 72), (192, 768, 768), (20000, 300, 64),
+             # fewer rows than half a tile (greedy decode of a few clips per GPU)
+             (24, 768, 768), (16, 64, 32)]
 
 
 @pytest.mark.parametrize("a_mn", [False, True])

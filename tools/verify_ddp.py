@@ -74,6 +74,8 @@ def run(args, dev, rank, world):
             torch.cuda.synchronize()
             gscale = max(float(p.grad.abs().max()) for p in m1.parameters() if p.grad is not None)
             worst, worst_n, missing = 0.0, None, []
+            worst_l2, worst_l2_n = 0.0, None
+            nscale = max(float(p.grad.norm()) for p in m1.parameters() if p.grad is not None)
             for n, p in m1.named_parameters():
                 g = grads_n[n]
                 if p.grad is None:
@@ -86,12 +88,20 @@ def run(args, dev, rank, world):
                 err = float((g - p.grad).abs().max()) / max(float(p.grad.abs().max()), 1e-3 * gscale)
                 if err > worst:
                     worst, worst_n = err, n
-            tol_l, tol_g = (1e-5, 1e-3) if dtype == torch.float32 else (2e-3, 5e-2)
+                l2 = float((g.double() - p.grad.double()).norm()) / max(float(p.grad.norm()), 1e-3 * nscale)
+                if l2 > worst_l2:
+                    worst_l2, worst_l2_n = l2, n
+            # fp32: element-wise (max-norm) bound.  bf16: the two runs take different kernel routes (8 rows per rank fall below
+            # the tensor-core tile, 64 rows do not), so activations are rounded differently: the bound is the bf16 path's own
+            # noise level, relative L2 per tensor (tests/test_headline_gpu.py: 6e-2 against the fp32 path)
+            tol_l, tol_g = (1e-5, 1e-3) if dtype == torch.float32 else (2e-3, 6e-2)
             lerr = abs(float(tot) - float(l1)) / abs(float(l1))
-            results[name] = {"loss_n_ranks": float(tot), "loss_1_rank": float(l1), "loss_rel_err": lerr, "worst_grad_rel_err": worst,
-                             "worst_grad": worst_n, "params_with_mismatched_presence": missing, "ranks_identical": same,
-                             "tol_loss": tol_l, "tol_grad": tol_g,
-                             "ok": bool(lerr <= tol_l and worst <= tol_g and not missing and same)}
+            gerr = worst if dtype == torch.float32 else worst_l2
+            results[name] = {"loss_n_ranks": float(tot), "loss_1_rank": float(l1), "loss_rel_err": lerr, "worst_grad_max_err": worst,
+                             "worst_grad": worst_n, "worst_grad_rel_l2": worst_l2, "worst_grad_l2": worst_l2_n,
+                             "params_with_mismatched_presence": missing, "ranks_identical": same,
+                             "tol_loss": tol_l, "tol_grad": tol_g, "grad_criterion": "max-norm" if dtype == torch.float32 else "relative L2",
+                             "ok": bool(lerr <= tol_l and gerr <= tol_g and not missing and same)}
         dist.barrier()
         red.remove()
     if rank == 0:
