@@ -79,6 +79,7 @@ class GradAllReducer:
         self._launched = [False] * len(self.buckets)
         self._work = []
         self._handed = set()                             # slots given to a weight-gradient GEMM in the current backward pass
+        self._comm = {}                                  # device -> communication stream
         self._hooks = [p.register_post_accumulate_grad_hook(self._on_grad) for p in self.params]
         self.enabled = dist.is_available() and dist.is_initialized() and dist.get_world_size(self.group) > 1
         if self.enabled:
@@ -127,16 +128,33 @@ class GradAllReducer:
         if not params:
             return
         from . import functional as Fn
-        Fn.WGRAD.join()          # weight gradients are produced on a side stream: this stream reads them from here on
         flat = self._flat(bi, params[0])
-        # gradients that were not written into their slot by the GEMM (biases, LayerNorm, embeddings, ...) are copied in
-        stray = [p for p in params if p.grad.data_ptr() != flat.data_ptr() + 4 * self.offset_of[p]]
-        if stray:
-            torch._foreach_copy_([self.slot(p) for p in stray], [p.grad for p in stray])
-        missing = [p for p in self.buckets[bi] if p not in self._ready[bi]]
-        if missing:                                       # parameters without a gradient in this mode: their slots carry zeros
-            torch._foreach_zero_([self.slot(p) for p in missing])
-        h = dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+        ctx = None
+        if flat.is_cuda:
+            # the flatten pass and the collective run on a communication stream that waits for the compute stream AND for
+            # the weight-gradient stream; the compute stream itself does not wait for either (it goes on with the input-
+            # gradient chain) until finish()
+            dev = flat.device
+            cs = self._comm.get(dev)
+            if cs is None:
+                cs = self._comm[dev] = torch.cuda.Stream(device=dev)
+            cs.wait_stream(torch.cuda.current_stream(dev))
+            if dev in Fn.WGRAD.active:
+                cs.wait_stream(Fn.WGRAD.streams[dev])
+            ctx = torch.cuda.stream(cs)
+            ctx.__enter__()
+        try:
+            # gradients that were not written into their slot by the GEMM (biases, LayerNorm, embeddings, ...) are copied in
+            stray = [p for p in params if p.grad.data_ptr() != flat.data_ptr() + 4 * self.offset_of[p]]
+            if stray:
+                torch._foreach_copy_([self.slot(p) for p in stray], [p.grad for p in stray])
+            missing = [p for p in self.buckets[bi] if p not in self._ready[bi]]
+            if missing:                                   # parameters without a gradient in this mode: their slots carry zeros
+                torch._foreach_zero_([self.slot(p) for p in missing])
+            h = dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+        finally:
+            if ctx is not None:
+                ctx.__exit__(None, None, None)
         self._work.append((h, params))
 
     def finish(self):
@@ -147,6 +165,8 @@ class GradAllReducer:
         for bi, b in enumerate(self.buckets):
             if not self._launched[bi]:
                 self._launch(bi, [p for p in b if p in self._ready[bi]])
+        for dev, cs in self._comm.items():
+            torch.cuda.current_stream(dev).wait_stream(cs)
         for h, params in self._work:
             h.wait()
             for p in params:
