@@ -282,12 +282,9 @@ __device__ __forceinline__ void atc_write_x(bf16* X, int xp, const float (&s)[NT
   for (int nt = 0; nt < NT; ++nt) {
     if (nt * 8 < lk_pad) {
       float v[4] = {s[nt][0], s[nt][1], s[nt][2], s[nt][3]};
-      if (dr) {
-        float a, b;
-        dr->scale2(r0 + g, nt * 8 + t2, a, b);
-        v[0] *= a; v[1] *= b;
-        dr->scale2(r0 + g + 8, nt * 8 + t2, a, b);
-        v[2] *= a; v[3] *= b;
+      if (dr) {                          // P with the dropout decision in its sign (see attn_tc_bwd_kernel): dropped -> 0
+#pragma unroll
+        for (int e = 0; e < 4; ++e) v[e] = v[e] < 0.f ? 0.f : v[e] * dr->inv;
       }
       *reinterpret_cast<uint32_t*>(X + (r0 + g) * xp + nt * 8 + t2) = pack_bf16(v[0], v[1]);
       *reinterpret_cast<uint32_t*>(X + (r0 + g + 8) * xp + nt * 8 + t2) = pack_bf16(v[2], v[3]);
@@ -329,6 +326,20 @@ __global__ void __launch_bounds__(NT <= 14 ? 224 : 256, NT <= 14 ? 2 : 1) attn_t
     atc_mma_abt<NT>(s, af, sK, p.lk_pad, lane);
     float inv[2];
     atc_softmax<NT>(s, r0 + (lane >> 2), lk, p.lk_pad, madd, p.causal, scale, lane, true, inv);
+    // dropout: the keep / drop decision of every probability is computed ONCE and kept in the sign of P (P >= 0; a dropped
+    // P is stored negated), instead of re-hashing the element index in each of the three places that need the mask
+    if (dr.on) {
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt) {
+        if (nt * 8 < p.lk_pad) {
+          float m[4];
+          dr.scale2(gi, nt * 8 + t2, m[0], m[1]);
+          dr.scale2(gi + 8, nt * 8 + t2, m[2], m[3]);
+#pragma unroll
+          for (int e = 0; e < 4; ++e) s[nt][e] = m[e] == 0.f ? -s[nt][e] : s[nt][e];
+        }
+      }
+    }
     atc_write_x<NT>(sX, xp, s, r0, p.lk_pad, lane, dr.on ? &dr : nullptr);   // dropped P (bf16) for dV
     // D_i = sum_j P_ij dP_ij, dP = dO V^T (recomputed below instead of kept: 4*NT registers saved)
     atc_load_a(af, sdO, r0, lane);
@@ -338,11 +349,11 @@ __global__ void __launch_bounds__(NT <= 14 ? 224 : 256, NT <= 14 ? 2 : 1) attn_t
       if (nt * 8 < p.lk_pad) {
         float dp[4];
         atc_tile_abt(dp, af, sV, nt, lane);
-        float m[4];
-        dr.scale2(gi, nt * 8 + t2, m[0], m[1]);
-        dr.scale2(gi + 8, nt * 8 + t2, m[2], m[3]);
 #pragma unroll
-        for (int e = 0; e < 4; ++e) dsum[e >> 1] = fmaf(s[nt][e], dp[e] * m[e], dsum[e >> 1]);
+        for (int e = 0; e < 4; ++e) {
+          const float m = (dr.on && s[nt][e] < 0.f) ? 0.f : dr.inv;          // (a dropped probability carries a minus sign)
+          dsum[e >> 1] = fmaf(fabsf(s[nt][e]), dp[e] * m, dsum[e >> 1]);
+        }
       }
     }
 #pragma unroll
@@ -356,11 +367,11 @@ __global__ void __launch_bounds__(NT <= 14 ? 224 : 256, NT <= 14 ? 2 : 1) attn_t
       if (nt * 8 < p.lk_pad) {
         float dp[4];
         atc_tile_abt(dp, af, sV, nt, lane);
-        float m[4];
-        dr.scale2(gi, nt * 8 + t2, m[0], m[1]);
-        dr.scale2(gi + 8, nt * 8 + t2, m[2], m[3]);
 #pragma unroll
-        for (int e = 0; e < 4; ++e) s[nt][e] = s[nt][e] * (dp[e] * m[e] - dsum[e >> 1]) * scale;
+        for (int e = 0; e < 4; ++e) {
+          const float m = (dr.on && s[nt][e] < 0.f) ? 0.f : dr.inv;
+          s[nt][e] = fabsf(s[nt][e]) * (dp[e] * m - dsum[e >> 1]) * scale;
+        }
       }
     }
   }

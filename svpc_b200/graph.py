@@ -484,3 +484,60 @@ class GraphedDecoder:
                 raise ValueError("ingr_id_dict has a different number of copy tokens than the captured batch: re-capture")
             self.static[7] = d
         return self.run()
+
+
+class GraphedStepCache:
+    """Captured training steps for RAGGED data: a small LRU of ``GraphedTrainStep`` keyed by the batch signature (clips,
+    ingredients, OOV width and copy tokens per video - everything the launch shapes depend on).
+
+    A collate function that draws batches from length buckets produces a handful of signatures; each of them is captured
+    the ``capture_after``-th time it is seen and replayed from then on, every other batch runs the eager step (same
+    kernels, launched from Python).  ``stats()`` gives the hit rate.
+
+        cache = GraphedStepCache(model)
+        loss = cache.step(args, gumbel_noise)     # gradients in p.grad exactly as after loss.backward()
+    """
+
+    def __init__(self, model, max_graphs: int = 8, capture_after: int = 2, reducer=None, feature_dtype=None):
+        self.model, self.reducer, self.feature_dtype = model, reducer, feature_dtype
+        self.max_graphs, self.capture_after = int(max_graphs), int(capture_after)
+        self.graphs = {}            # signature -> GraphedTrainStep (insertion order = LRU order)
+        self.seen = {}
+        self.hits = self.misses = self.captures = 0
+
+    def _eager(self, args, gumbel_noise):
+        self.model.zero_grad(set_to_none=True)
+        loss = self.model(*args, gumbel_noise=gumbel_noise)[0]
+        loss.backward()
+        if self.reducer is not None:
+            self.reducer.finish()
+        # detached: a caller holding the loss must not keep this step's autograd graph (and its AccumulateGrad nodes, which
+        # are tied to this stream) alive into a later capture
+        return loss.detach()
+
+    def step(self, args, gumbel_noise=None):
+        sig = self.model.plan_signature(args[8], args[9], args[10])
+        g = self.graphs.get(sig)
+        if g is not None:
+            self.graphs[sig] = self.graphs.pop(sig)           # most recently used last
+            g.load(args, gumbel_noise)
+            self.hits += 1
+            return g.run()
+        self.misses += 1
+        n = self.seen[sig] = self.seen.get(sig, 0) + 1
+        if n >= self.capture_after:
+            if len(self.graphs) >= self.max_graphs:
+                self.graphs.pop(next(iter(self.graphs)))      # least recently used
+            dev = next(self.model.parameters()).device
+            to = lambda x: x.to(dev) if isinstance(x, torch.Tensor) else ([t.to(dev) for t in x] if _is_tensor_list(x) else x)
+            g = GraphedTrainStep(self.model, [to(a) for a in args], gumbel_noise=None if gumbel_noise is None else [t.to(dev) for t in gumbel_noise],
+                                 reducer=self.reducer, warmup=1, feature_dtype=self.feature_dtype)
+            self.graphs[sig] = g
+            self.captures += 1
+            return g.run()
+        return self._eager(args, gumbel_noise)
+
+    def stats(self):
+        tot = self.hits + self.misses
+        return {"steps": tot, "graph_hits": self.hits, "hit_rate": round(self.hits / tot, 4) if tot else 0.0,
+                "captures": self.captures, "signatures_seen": len(self.seen), "graphs_resident": len(self.graphs)}

@@ -284,3 +284,32 @@ def test_bf16_features_in_the_arena():
     step.load(forward_args(batch), batch["gumbel"])          # fp32 host features: converted on the way in
     lg2 = float(step.run())
     assert abs(lg2 - l16) <= 1e-5 * abs(l16), (lg2, l16)
+
+
+def test_graph_cache_for_ragged_batches():
+    """A stream of ragged batches with three signatures: each is captured the second time it appears and replayed from
+    then on; every step - eager, capturing, replayed - gives the eager loss of its batch."""
+    from svpc_b200.graph import GraphedStepCache
+    cfg, sd, _, _ = load_case("ragged", "full")
+    m = build(cfg, sd, torch.float32)
+    batches = [synth.make_batch(cfg, B=3, S=4, seed=40 + i, ragged=True, n_ingr=4, n_oov=2) for i in range(3)]
+    want = []
+    for b in batches:
+        want.append(float(m(*forward_args(b, DEV), gumbel_noise=[g.to(DEV) for g in b["gumbel"]])[0]))
+    sigs = {m.plan_signature(b["batch_step_num"], b["ingr_id_dict"], b["extra_zeros"]) for b in batches}
+    cache = GraphedStepCache(m, max_graphs=3, capture_after=2)
+    order = [0, 1, 2, 0, 1, 2, 0, 1, 2, 2, 0]
+    for i in order:
+        b = batches[i]
+        loss = cache.step(forward_args(b, DEV), [g.to(DEV) for g in b["gumbel"]])
+        assert abs(float(loss) - want[i]) <= 1e-5 * abs(want[i]), (i, float(loss), want[i])
+    st = cache.stats()
+    assert st["steps"] == len(order) and st["signatures_seen"] == len(sigs)
+    if len(sigs) == 3:
+        assert st["captures"] == 3 and st["graph_hits"] == len(order) - 6 and st["graphs_resident"] == 3, st
+    small = GraphedStepCache(m, max_graphs=1, capture_after=1)          # least-recently-used eviction
+    for i in (0, 1, 1, 0):
+        b = batches[i]
+        loss = small.step(forward_args(b, DEV), [g.to(DEV) for g in b["gumbel"]])
+        assert abs(float(loss) - want[i]) <= 1e-5 * abs(want[i]), (i, float(loss), want[i])
+    assert small.stats()["graphs_resident"] == 1
