@@ -719,7 +719,15 @@ int svpc_gemm_tc_launch(int M, int N, int K, const void* A, long long sa_m, long
                         long long ldr, void* pre, long long ldp, int accumulate, SvpcDrop drop, cudaStream_t st,
                         const void* A_lo, const void* B_lo, const void* gref, long long ldg, int gact) {
   const bool a_mn = sa_k != 1, b_mn = sb_k != 1;
-  const int BN = choose_bn(N);
+  // tuning switches (read once): SVPC_TC_BN forces the tile width, SVPC_TC_SPLIT_MAX caps the split-K factor
+  static int env_bn = -1, env_split_max = -1;
+  if (env_bn < 0) {
+    const char* e = getenv("SVPC_TC_BN");
+    env_bn = e ? atoi(e) : 0;
+    e = getenv("SVPC_TC_SPLIT_MAX");
+    env_split_max = e ? atoi(e) : 32;
+  }
+  const int BN = (env_bn == 64 || env_bn == 128 || env_bn == 256) ? env_bn : choose_bn(N);
   const int nseg = (A_lo && B_lo) ? 3 : 1;
   CUtensorMap tm[4];
   int rc;
@@ -740,7 +748,7 @@ int svpc_gemm_tc_launch(int M, int N, int K, const void* A, long long sa_m, long
   if (plain && tiles * 2 <= G && kb_total >= 16) {
     // split-K: rounds of G units x K blocks per unit, plus ~4 K-block-times of atomic epilogue per unit
     long long best = (long long)svpc_cdiv(tiles, G) * (kb_total + 4);
-    for (int sp = 2; sp <= 32 && kb_total / sp >= 8; ++sp) {
+    for (int sp = 2; sp <= env_split_max && kb_total / sp >= 8; ++sp) {
       const long long c = (long long)svpc_cdiv((long long)tiles * sp, G) * (svpc_cdiv(kb_total, sp) + 4);
       if (c < best) { best = c; split = sp; }
     }

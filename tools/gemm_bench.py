@@ -29,6 +29,8 @@ SHAPES = [
     (4800, 951, 768, "NN", "bias-f32"),         # LM head
     (192, 768, 768, "NN", "bias"),              # step encoder / reasoner
     (192, 768, 768, "NT", "plain"),
+    (768, 768, 4800, "TT", "plain-f32"),        # decoder wgrad (split-K)
+    (768, 768, 192, "TT", "plain-f32"),         # step-level wgrad
 ]
 
 
