@@ -16,6 +16,13 @@
 // With few rows (greedy decoding: one position per launch) the chain latency of a single row is what counts: 256 threads.
 static inline int ptr_threads(int Lt, int n_clips) { return (long long)Lt * n_clips >= 8 * SVPC_NUM_SMS ? 128 : PG_THREADS; }
 
+// multi-row kernels (training shapes) unless SVPC_POINTER_ROWS=0
+static inline bool ptr_rows_route(int Lt, int n_clips, int V) {
+  static int on = -1;
+  if (on < 0) { const char* e = getenv("SVPC_POINTER_ROWS"); on = e ? atoi(e) : 1; }
+  return on && Lt > 1 && V <= 1024 && (long long)Lt * n_clips >= 8 * SVPC_NUM_SMS;
+}
+
 __device__ __forceinline__ float ls_q(int v, int label, int vx, float s, float conf) {
   if (v == label) return conf;
   if (v == vx - 1) return 0.f;
@@ -116,6 +123,170 @@ __global__ void __launch_bounds__(PG_THREADS) pointer_fwd_kernel(
   }
 }
 
+// Training shapes (thousands of rows): one CTA per (clip, group of up to PR_ROWS text positions).  The per-row kernel above
+// is a chain of dependent L2 loads (every row re-reads the clip's ni rows of G and of Esrc: 60 KB per row, 295 MB per launch
+// at the benchmark shape, all of it latency: ncu shows half of the warp samples on stall_long_sb at the FFMAs that consume
+// them).  Here the CTA reads G / Esrc once for its rows (loads batched eight deep), and the vocabulary phase runs one WARP
+// per row (warp shuffles only, no block barrier).
+#define PR_ROWS 8
+#define PR_THREADS 256
+#define PR_NV 32            // logits per lane held in registers by the backward's one-warp-per-row vocabulary phase (V <= 1024)
+template <typename T>
+__global__ void __launch_bounds__(PR_THREADS) pointer_fwd_rows_kernel(
+    int Lt, int R, int D, int V, int max_ni, int max_vx, const T* __restrict__ dec, const float* __restrict__ G,
+    const float* __restrict__ Esrc, const int* __restrict__ clip_src_off, const int* __restrict__ clip_ni,
+    const int* __restrict__ clip_gi, const int* __restrict__ clip_vx, const int* __restrict__ clip_P_off,
+    const int* __restrict__ tok_ptr, const int* __restrict__ tok_ids, const float* __restrict__ wpgen,
+    const float* __restrict__ bpgen, const float* __restrict__ logits, long long ldl, const int* __restrict__ labels,
+    float smoothing, float* __restrict__ P, float* __restrict__ loss_rows, float* __restrict__ alpha_out,
+    float* __restrict__ pgen_out, float* __restrict__ ctx_out) {
+  svpc_pdl_sync();
+  extern __shared__ float sm[];
+  float* sdec = sm;                                   // PR_ROWS x D   (rows >= nr are zero)
+  float* prow = sdec + (size_t)PR_ROWS * D;           // PR_ROWS x max_vx
+  float* alpha = prow + (size_t)PR_ROWS * max_vx;     // PR_ROWS x max_ni
+  __shared__ float spu[PR_ROWS][PR_THREADS / 32];
+  __shared__ float spg[PR_ROWS];
+  const int n = blockIdx.y, l0 = blockIdx.x * R;
+  const int nr = min(R, Lt - l0);
+  const int src = clip_src_off[n], ni = clip_ni[n], gi = clip_gi[n], vx = clip_vx[n];
+  const long long poff = clip_P_off[n];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long r0 = (long long)n * Lt + l0;
+  for (int e = threadIdx.x; e < PR_ROWS * D; e += PR_THREADS) sdec[e] = e < nr * D ? ldf(dec + r0 * D + e) : 0.f;
+  __syncthreads();
+  // scores[r][i] = dec_r . G_i : one warp per ingredient, the G row read once for all rows
+  for (int i = warp; i < ni; i += PR_THREADS / 32) {
+    const float* g = G + (long long)(src + i) * D;
+    float acc[PR_ROWS];
+#pragma unroll
+    for (int r = 0; r < PR_ROWS; ++r) acc[r] = 0.f;
+    for (int d0 = lane; d0 < D; d0 += 256) {
+      float gv[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) gv[u] = d0 + 32 * u < D ? g[d0 + 32 * u] : 0.f;
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int dd = min(d0 + 32 * u, D - 1);
+#pragma unroll
+        for (int r = 0; r < PR_ROWS; ++r) acc[r] = fmaf(gv[u], sdec[r * D + dd], acc[r]);
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < PR_ROWS; ++r) {
+      const float s = warp_sum(acc[r]);
+      if (lane == 0) alpha[r * max_ni + i] = s;
+    }
+  }
+  __syncthreads();
+  if (warp < nr) {   // softmax over the ingredient axis (model.py:900), one warp per row
+    float* a = alpha + warp * max_ni;
+    float mx = -INFINITY;
+    for (int i = lane; i < ni; i += 32) mx = fmaxf(mx, a[i]);
+    mx = warp_max(mx);
+    float sum = 0.f;
+    for (int i = lane; i < ni; i += 32) { const float e = expf(a[i] - mx); a[i] = e; sum += e; }
+    sum = warp_sum(sum);
+    for (int i = lane; i < ni; i += 32) {
+      const float v = a[i] / sum;
+      a[i] = v;
+      alpha_out[(r0 + warp) * max_ni + i] = v;
+    }
+  } else {
+    for (int i = lane; i < ni; i += 32) alpha[warp * max_ni + i] = 0.f;
+  }
+  __syncthreads();
+  // context rows and the p_gen pre-activation: each Esrc element read once per CTA, four rows of Esrc in flight
+  float pu[PR_ROWS];
+#pragma unroll
+  for (int r = 0; r < PR_ROWS; ++r) pu[r] = 0.f;
+  for (int d = threadIdx.x; d < D; d += PR_THREADS) {
+    float c[PR_ROWS];
+#pragma unroll
+    for (int r = 0; r < PR_ROWS; ++r) c[r] = 0.f;
+    for (int i0 = 0; i0 < ni; i0 += 4) {
+      float ev[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) ev[u] = i0 + u < ni ? Esrc[(long long)(src + i0 + u) * D + d] : 0.f;
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int ii = min(i0 + u, ni - 1);
+#pragma unroll
+        for (int r = 0; r < PR_ROWS; ++r) c[r] = fmaf(alpha[r * max_ni + ii], ev[u], c[r]);
+      }
+    }
+    const float w1 = wpgen[d], w2 = wpgen[D + d];
+#pragma unroll
+    for (int r = 0; r < PR_ROWS; ++r) {
+      if (r < nr) ctx_out[(r0 + r) * D + d] = c[r];
+      pu[r] += sdec[r * D + d] * w1 + c[r] * w2;
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < PR_ROWS; ++r) {
+    const float s = warp_sum(pu[r]);
+    if (lane == 0) spu[r][warp] = s;
+  }
+  __syncthreads();
+  if (threadIdx.x < nr) {
+    float s = 0.f;
+#pragma unroll
+    for (int w = 0; w < PR_THREADS / 32; ++w) s += spu[threadIdx.x][w];
+    const float pg = svpc_sigmoid(s + bpgen[0]);
+    spg[threadIdx.x] = pg;
+    pgen_out[r0 + threadIdx.x] = pg;
+  }
+  __syncthreads();
+  if (warp >= nr) return;
+  // vocabulary phase: one warp per row
+  const long long r = r0 + warp;
+  const int l = l0 + warp;
+  const float pg = spg[warp];
+  const float* a = alpha + warp * max_ni;
+  float* pr = prow + (size_t)warp * max_vx;
+  const float* lrow = logits + r * ldl;
+  // stage the row's logits in shared memory eight loads deep, then max / exp / normalise out of shared memory
+  float mx = -INFINITY;
+  for (int v0 = lane; v0 < V; v0 += 256) {
+    float t[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) t[u] = v0 + 32 * u < V ? lrow[v0 + 32 * u] : -INFINITY;
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      if (v0 + 32 * u < V) pr[v0 + 32 * u] = t[u];
+      mx = fmaxf(mx, t[u]);
+    }
+  }
+  mx = warp_max(mx);
+  float se = 0.f;
+#pragma unroll 4
+  for (int v = lane; v < V; v += 32) { const float e = expf(pr[v] - mx); pr[v] = e; se += e; }
+  se = warp_sum(se);
+#pragma unroll 4
+  for (int v = lane; v < V; v += 32) pr[v] = pg * (pr[v] / se);
+  for (int v = V + lane; v < vx; v += 32) pr[v] = 0.f;
+  __syncwarp();
+  if (lane == 0) {     // copy mass in dictionary order (the reference's accumulation order)
+    for (int i = 0; i < ni; ++i) {
+      const int lo = tok_ptr[gi + i], hi = tok_ptr[gi + i + 1];
+      const float add = a[i] * (1.f - pg) / (float)(hi - lo);
+      for (int t = lo; t < hi; ++t) pr[tok_ids[t]] += add;
+    }
+  }
+  __syncwarp();
+  const int label = labels[r];
+  const float s = smoothing / (float)(vx - 1), conf = 1.f - smoothing;
+  float acc = 0.f;
+#pragma unroll 4
+  for (int v = lane; v < vx; v += 32) {
+    const float p = pr[v];
+    P[poff + (long long)l * vx + v] = p;
+    if (label >= 0) acc += ls_q(v, label, vx, s, conf) * logf(p + 1e-12f);
+  }
+  acc = warp_sum(acc);
+  if (lane == 0) loss_rows[r] = label >= 0 ? ls_const(label, vx, s, conf) - acc : 0.f;
+}
+
 // Backward, part 1: one CTA per (clip, text position).  Writes d logits, d dec, du (gradient of the p_gen
 // pre-activation) and the score gradients dsc[r][i]; the per-ingredient sums over the clip's positions are part 2.
 template <typename T>
@@ -206,6 +377,152 @@ __global__ void __launch_bounds__(PG_THREADS) pointer_bwd_kernel(
   }
 }
 
+// Backward, part 1 for training shapes: one CTA per (clip, group of up to PR_ROWS positions), same outputs as
+// pointer_bwd_kernel.  w2 . E_i is computed once per CTA, the vocabulary phase runs one warp per row with the row's
+// softmax in registers, and the d dec rows read each G element once per CTA.
+template <typename T>
+__global__ void __launch_bounds__(PR_THREADS) pointer_bwd_rows_kernel(
+    int Lt, int R, int D, int V, int max_ni, int max_vx, const float* __restrict__ G,
+    const float* __restrict__ Esrc, const int* __restrict__ clip_src_off, const int* __restrict__ clip_ni,
+    const int* __restrict__ clip_gi, const int* __restrict__ clip_vx, const int* __restrict__ clip_P_off,
+    const int* __restrict__ tok_ptr, const int* __restrict__ tok_ids, const float* __restrict__ wpgen,
+    const float* __restrict__ logits, long long ldl, const int* __restrict__ labels, float smoothing,
+    const float* __restrict__ P, const float* __restrict__ alpha_in, const float* __restrict__ pgen_in,
+    const float* __restrict__ dP, const float* __restrict__ dloss, T* __restrict__ ddec, float* __restrict__ du_out,
+    float* __restrict__ dlogits, float* __restrict__ dsc_out) {
+  svpc_pdl_sync();
+  extern __shared__ float sm[];
+  float* gPs = sm;                                   // PR_ROWS x max_vx
+  float* dscs = gPs + (size_t)PR_ROWS * max_vx;      // PR_ROWS x max_ni   d score (zero for rows >= nr)
+  float* cis = dscs + PR_ROWS * max_ni;              // PR_ROWS x max_ni
+  float* wE = cis + PR_ROWS * max_ni;                // max_ni   w2 . E_i
+  __shared__ float sdu[PR_ROWS];
+  const int n = blockIdx.y, l0 = blockIdx.x * R;
+  const int nr = min(R, Lt - l0);
+  const int src = clip_src_off[n], ni = clip_ni[n], gi = clip_gi[n], vx = clip_vx[n];
+  const long long poff = clip_P_off[n];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long r0 = (long long)n * Lt + l0;
+  const float gl = dloss[0];
+  for (int i = warp; i < ni; i += PR_THREADS / 32) {
+    const float* e = Esrc + (long long)(src + i) * D;
+    float acc = 0.f;
+    for (int d0 = lane; d0 < D; d0 += 256) {
+      float ev[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) ev[u] = d0 + 32 * u < D ? e[d0 + 32 * u] : 0.f;
+#pragma unroll
+      for (int u = 0; u < 8; ++u) acc = fmaf(wpgen[D + min(d0 + 32 * u, D - 1)], ev[u], acc);
+    }
+    acc = warp_sum(acc);
+    if (lane == 0) wE[i] = acc;
+  }
+  if (threadIdx.x < PR_ROWS) sdu[threadIdx.x] = 0.f;
+  for (int e = threadIdx.x; e < PR_ROWS * max_ni; e += PR_THREADS) dscs[e] = 0.f;
+  __syncthreads();
+  if (warp < nr) {
+    const long long r = r0 + warp;
+    const int l = l0 + warp;
+    const float pg = pgen_in[r];
+    const int label = labels[r];
+    const float s = smoothing / (float)(vx - 1), conf = 1.f - smoothing;
+    const float* lrow = logits + r * ldl;
+    const float* al = alpha_in + r * max_ni;
+    float* gP = gPs + (size_t)warp * max_vx;
+    float* ci = cis + warp * max_ni;
+    float lv[PR_NV];            // logits, then softmax probabilities, of this lane's columns
+#pragma unroll
+    for (int k = 0; k < PR_NV; ++k) lv[k] = lane + 32 * k < V ? lrow[lane + 32 * k] : -INFINITY;
+    float mx = -INFINITY;
+#pragma unroll
+    for (int k = 0; k < PR_NV; ++k) mx = fmaxf(mx, lv[k]);
+    mx = warp_max(mx);
+    float se = 0.f;
+#pragma unroll
+    for (int k = 0; k < PR_NV; ++k) { lv[k] = expf(lv[k] - mx); se += lv[k]; }
+    se = warp_sum(se);
+    const float* Prow = P + poff + (long long)l * vx;
+    const float* dProw = dP ? dP + poff + (long long)l * vx : nullptr;
+    float pa = 0.f;
+#pragma unroll
+    for (int k0 = 0; k0 < PR_NV; k0 += 8) {     // gradient w.r.t. the mixed probabilities, eight columns per lane in flight
+      float pv[8], gv[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int v = lane + 32 * (k0 + u);
+        pv[u] = v < vx ? Prow[v] : 1.f;
+        gv[u] = (dProw && v < vx) ? dProw[v] : 0.f;
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int v = lane + 32 * (k0 + u);
+        lv[k0 + u] /= se;
+        if (v < vx) {
+          float g = gv[u];
+          if (label >= 0) g -= gl * ls_q(v, label, vx, s, conf) / (pv[u] + 1e-12f);
+          gP[v] = g;
+          if (v < V) pa = fmaf(g, lv[k0 + u], pa);
+        }
+      }
+    }
+    for (int v = 32 * PR_NV + lane; v < vx; v += 32) {      // OOV columns beyond the register window (never vocabulary columns)
+      float g = dProw ? dProw[v] : 0.f;
+      if (label >= 0) g -= gl * ls_q(v, label, vx, s, conf) / (Prow[v] + 1e-12f);
+      gP[v] = g;
+    }
+    const float A = warp_sum(pa);
+    __syncwarp();
+    float t = 0.f;
+    for (int i = lane; i < ni; i += 32) {
+      const int lo = tok_ptr[gi + i], hi = tok_ptr[gi + i + 1];
+      float c = 0.f;
+      for (int k = lo; k < hi; ++k) c += gP[tok_ids[k]];
+      c /= (float)(hi - lo);
+      ci[i] = c;
+      t = fmaf(al[i], c, t);
+    }
+    t = warp_sum(t);
+    const float dpg = A - t;
+    const float du = dpg * pg * (1.f - pg);
+    float dot = 0.f;
+    for (int i = lane; i < ni; i += 32) dot = fmaf(al[i], (1.f - pg) * ci[i] + du * wE[i], dot);
+    dot = warp_sum(dot);
+    for (int i = lane; i < ni; i += 32) {
+      const float dal = (1.f - pg) * ci[i] + du * wE[i];
+      const float ds = al[i] * (dal - dot);
+      dscs[warp * max_ni + i] = ds;
+      dsc_out[r * max_ni + i] = ds;
+    }
+    if (lane == 0) { sdu[warp] = du; du_out[r] = du; }
+#pragma unroll
+    for (int k = 0; k < PR_NV; ++k) {
+      const int v = lane + 32 * k;
+      if (v < V) dlogits[r * ldl + v] = lv[k] * pg * (gP[v] - A);
+    }
+  }
+  __syncthreads();
+  for (int d = threadIdx.x; d < D; d += PR_THREADS) {
+    const float w1 = wpgen[d];
+    float acc[PR_ROWS];
+#pragma unroll
+    for (int r = 0; r < PR_ROWS; ++r) acc[r] = sdu[r] * w1;
+    for (int i0 = 0; i0 < ni; i0 += 4) {
+      float gv[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) gv[u] = i0 + u < ni ? G[(long long)(src + i0 + u) * D + d] : 0.f;
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int ii = min(i0 + u, ni - 1);
+#pragma unroll
+        for (int r = 0; r < PR_ROWS; ++r) acc[r] = fmaf(dscs[r * max_ni + ii], gv[u], acc[r]);
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < PR_ROWS; ++r)
+      if (r < nr) stf(ddec + (r0 + r) * D + d, acc[r]);
+  }
+}
+
 // Backward, part 2: one CTA per clip.  dG_i[d] += sum_l dscore[l][i] dec[l][d] ;  dE_i[d] += (sum_l alpha_il du_l) w2[d]
 template <typename T>
 __global__ void __launch_bounds__(PG_THREADS) pointer_bwd_reduce_kernel(
@@ -260,6 +577,17 @@ extern "C" int svpc_pointer_fwd(int n_clips, int Lt, int D, int V, int max_ni, i
   const size_t smem = sizeof(float) * (2 * (size_t)D + max_vx + max_ni);
   SVPC_REQUIRE(smem <= 200 * 1024, "pointer_fwd: shared memory");
   cudaStream_t st = (cudaStream_t)stream;
+  const size_t smem_rows = sizeof(float) * PR_ROWS * ((size_t)D + max_vx + max_ni);
+  if (ptr_rows_route(Lt, n_clips, V) && smem_rows <= 100 * 1024) {
+    const int groups = (Lt + PR_ROWS - 1) / PR_ROWS, R = (Lt + groups - 1) / groups;
+    SVPC_DISPATCH(dt, T, {
+      cudaFuncSetAttribute(pointer_fwd_rows_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_rows);
+      svpc_launch(pointer_fwd_rows_kernel<T>, dim3((Lt + R - 1) / R, n_clips), PR_THREADS, smem_rows, st, Lt, R, D, V, max_ni,
+                  max_vx, (const T*)dec, G, Esrc, clip_src_off, clip_ni, clip_gi, clip_vx, clip_P_off, tok_ptr, tok_ids, wpgen,
+                  bpgen, logits, ldl, labels, smoothing, P, loss_rows, alpha, pgen, ctx);
+    });
+    return svpc_check_launch("pointer_fwd_rows");
+  }
   SVPC_DISPATCH(dt, T, {
     cudaFuncSetAttribute(pointer_fwd_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     svpc_launch(pointer_fwd_kernel<T>, dim3(Lt, n_clips), ptr_threads(Lt, n_clips), smem, st, Lt, D, V, max_ni, max_vx, (const T*)dec, G, Esrc, clip_src_off,
@@ -284,11 +612,21 @@ extern "C" int svpc_pointer_bwd(int n_clips, int Lt, int D, int V, int max_ni, i
   SVPC_REQUIRE(smem <= 200 * 1024 && smem2 <= 200 * 1024, "pointer_bwd: shared memory");
   cudaStream_t st = (cudaStream_t)stream;
   cudaMemsetAsync(dwpgen, 0, sizeof(float) * 2 * D, st);
+  const size_t smem_rows = sizeof(float) * (PR_ROWS * ((size_t)max_vx + 2 * (size_t)max_ni) + max_ni);
+  const bool rows_route = ptr_rows_route(Lt, n_clips, V) && smem_rows <= 100 * 1024;
+  const int groups = (Lt + PR_ROWS - 1) / PR_ROWS, RG = (Lt + groups - 1) / groups;
   SVPC_DISPATCH(dt, T, {
-    cudaFuncSetAttribute(pointer_bwd_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    svpc_launch(pointer_bwd_kernel<T>, dim3(Lt, n_clips), ptr_threads(Lt, n_clips), smem, st, 
-        Lt, D, V, max_ni, max_vx, (const T*)dec, G, Esrc, clip_src_off, clip_ni, clip_gi, clip_vx, clip_P_off, tok_ptr,
-        tok_ids, wpgen, logits, ldl, labels, smoothing, P, alpha, pgen, dP, dloss, (T*)ddec, du, dlogits, dscore_ws);
+    if (rows_route) {
+      cudaFuncSetAttribute(pointer_bwd_rows_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_rows);
+      svpc_launch(pointer_bwd_rows_kernel<T>, dim3((Lt + RG - 1) / RG, n_clips), PR_THREADS, smem_rows, st, Lt, RG, D, V, max_ni,
+          max_vx, G, Esrc, clip_src_off, clip_ni, clip_gi, clip_vx, clip_P_off, tok_ptr, tok_ids, wpgen, logits, ldl, labels,
+          smoothing, P, alpha, pgen, dP, dloss, (T*)ddec, du, dlogits, dscore_ws);
+    } else {
+      cudaFuncSetAttribute(pointer_bwd_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      svpc_launch(pointer_bwd_kernel<T>, dim3(Lt, n_clips), ptr_threads(Lt, n_clips), smem, st,
+          Lt, D, V, max_ni, max_vx, (const T*)dec, G, Esrc, clip_src_off, clip_ni, clip_gi, clip_vx, clip_P_off, tok_ptr,
+          tok_ids, wpgen, logits, ldl, labels, smoothing, P, alpha, pgen, dP, dloss, (T*)ddec, du, dlogits, dscore_ws);
+    }
     cudaFuncSetAttribute(pointer_bwd_reduce_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
     svpc_launch(pointer_bwd_reduce_kernel<T>, n_clips, PG_THREADS, smem2, st, Lt, D, max_ni, (const T*)dec, clip_src_off, clip_ni,
                                                                    wpgen, alpha, du, dscore_ws, dG, dE);

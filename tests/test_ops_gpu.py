@@ -397,9 +397,10 @@ def test_reasoner(cb, tb, D, max_steps):
 
 
 # ---------------------------------------------------------------------------------------------- output head
-def _pointer_case(dt, copy_mode):
-    Lt, D, V = 8, 64, 60
-    steps, ni, ez = [2, 3], [3, 2], [2, 0]
+def _pointer_case(dt, copy_mode, big=False):
+    # big: enough rows (1250 >= 8 x #SMs) for the multi-row kernels, Lt = 25 -> position groups of 7, 7, 7, 4
+    Lt, D, V = (25, 64, 60) if big else (8, 64, 60)
+    steps, ni, ez = ([20, 30] if big else [2, 3]), [3, 2], [2, 0]
     B = 2
     vx = [V + z for z in ez]
     clip_b = [b for b in range(B) for _ in range(steps[b])]
@@ -433,8 +434,9 @@ def _pointer_case(dt, copy_mode):
 
 @pytest.mark.parametrize("dt", [F32, BF16])
 @pytest.mark.parametrize("copy_mode", [False, True])
-def test_pointer(cb, tb, dt, copy_mode):
-    lay, dec, G, E, w, bb, logits, P_numel, Nc, Lt, V = _pointer_case(dt, copy_mode)
+@pytest.mark.parametrize("big", [False, True])
+def test_pointer(cb, tb, dt, copy_mode, big):
+    lay, dec, G, E, w, bb, logits, P_numel, Nc, Lt, V = _pointer_case(dt, copy_mode, big)
     tol = 2e-5 if dt == F32 else 2e-2
     P, rows, saved = cb.pointer_fwd(dec, G, E, w, bb, logits, lay)
     rP, rrows, _ = tb.pointer_fwd(dec, G, E, w, bb, logits, lay)
