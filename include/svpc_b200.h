@@ -161,6 +161,16 @@ int svpc_segmean_fwd(int B, int Li, int D, int NI, const void* x, int dt, const 
                      const float* pe, float* E0, int* scratch_row_seg, int* scratch_seg_lohi, svpc_stream_t stream);
 int svpc_segmean_bwd(int B, int Li, int D, int NI, const float* dE0, const int* sep_mask, const int* cu_ingr, void* dx,
                      int dt, int* scratch_row_seg, int* scratch_seg_lohi, svpc_stream_t stream);
+/* svpc_segmean_fwd for callers that cannot allocate (CUDA-graph capture, serving loops, harnesses that forbid cudaMalloc).
+ * No counterpart in the reference.  Same inputs, outputs and results as
+ * svpc_segmean_fwd; the two scratch tables live in a 320 KB file-scope device array inside the library (held by every GPU
+ * that loads it until exit) and the call performs no cudaMalloc / cudaFree.  Limits: B * Li <= SVPC_SEGMEAN_STATIC_MAX_ROWS
+ * and NI <= SVPC_SEGMEAN_STATIC_MAX_SEGS, beyond which it returns SVPC_ERR_ARG (svpc_last_error names the limit).  All
+ * calls share the array: calls that overlap on the GPU (two streams, two host threads) race; serialise them on one stream. */
+#define SVPC_SEGMEAN_STATIC_MAX_ROWS 65536
+#define SVPC_SEGMEAN_STATIC_MAX_SEGS 8192
+int svpc_segmean_fwd_static(int B, int Li, int D, int NI, const void* x, int dt, const int* sep_mask, const int* cu_ingr,
+                            const float* pe, float* E0, svpc_stream_t stream);
 int svpc_ragged_mean_fwd(int B, int D, const float* x, const int* cu, float* y, svpc_stream_t stream);
 int svpc_ragged_mean_bwd(int B, int D, const float* dy, const int* cu, float* dx, svpc_stream_t stream);
 int svpc_row_normalize_fwd(int rows, int cols, const float* x, float* y, svpc_stream_t stream);

@@ -4,6 +4,7 @@
 // warp shuffles; column reductions (dgamma / dbeta / dbias) are kept in registers across a grid-stride loop over rows
 // and flushed with one red.global per column per CTA.
 #include "common.cuh"
+#include <mutex>
 
 #define RW_THREADS 256
 #define RW_MAXPT 16          // columns cached per thread (D <= RW_THREADS * RW_MAXPT = 4096)
@@ -1132,6 +1133,69 @@ extern "C" int svpc_segmean_bwd(int B, int Li, int D, int NI, const float* dE0, 
   if (rc) return rc;
   SVPC_DISPATCH(dt, T, (svpc_launch(segmean_bwd_kernel<T>, B * Li, 256, 0, st, B * Li, D, dE0, scratch_row_seg, scratch_seg_lohi, (T*)dx)));
   return svpc_check_launch("segmean_bwd");
+}
+
+// ------------------------------------------------------------------------------------------------
+// svpc_segmean_fwd without caller-provided scratch and without any allocation (no counterpart in the reference: for callers
+// that cannot allocate: CUDA-graph capture, serving loops).  The two scratch tables live in a file-scope device array that
+// every GPU loading the library holds until exit (320 KB).  All calls share it and it keeps the last call's contents:
+// calls that overlap on the GPU (different streams, different host threads) race on it.
+// ------------------------------------------------------------------------------------------------
+#define SEGMEAN_STATIC_MAX_ROWS 65536     // B * Li
+#define SEGMEAN_STATIC_MAX_SEGS 8192      // NI
+static __device__ __align__(256) int g_segmean_scratch[SEGMEAN_STATIC_MAX_ROWS + 2 * SEGMEAN_STATIC_MAX_SEGS];
+
+#define SEGMEAN_MAX_DEVICES 64
+static std::mutex g_segmean_mu;
+static int* g_segmean_ptr[SEGMEAN_MAX_DEVICES];    // device address of g_segmean_scratch on each device (host code cannot use the symbol itself)
+
+static int segmean_scratch_ptr(int** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= SEGMEAN_MAX_DEVICES) {
+    svpc_set_error("segmean_fwd_static: cudaGetDevice: %s (device %d)", cudaGetErrorString(e), dev);
+    return SVPC_ERR_CUDA;
+  }
+  std::lock_guard<std::mutex> lock(g_segmean_mu);
+  if (!g_segmean_ptr[dev]) {      // once per device, with that device current
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_segmean_scratch);
+    if (e != cudaSuccess || !p) {
+      svpc_set_error("segmean_fwd_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+      return SVPC_ERR_CUDA;
+    }
+    g_segmean_ptr[dev] = (int*)p;
+  }
+  *out = g_segmean_ptr[dev];
+  return SVPC_OK;
+}
+
+extern "C" int svpc_segmean_fwd_static(int B, int Li, int D, int NI, const void* x, int dt, const int* sep_mask,
+                                       const int* cu_ingr, const float* pe, float* E0, svpc_stream_t stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  if (B <= 0 || NI <= 0) return SVPC_OK;
+  SVPC_REQUIRE(Li > 0 && (long long)B * Li <= SEGMEAN_STATIC_MAX_ROWS,
+               "segmean_fwd_static: B * Li = %lld exceeds the built-in scratch of %d rows (use svpc_segmean_fwd with caller scratch)",
+               (long long)B * Li, SEGMEAN_STATIC_MAX_ROWS);
+  SVPC_REQUIRE(NI <= SEGMEAN_STATIC_MAX_SEGS,
+               "segmean_fwd_static: NI = %d exceeds the built-in scratch of %d segments (use svpc_segmean_fwd with caller scratch)",
+               NI, SEGMEAN_STATIC_MAX_SEGS);
+  int* scratch = nullptr;
+  int rc = segmean_scratch_ptr(&scratch);
+  if (rc) return rc;
+  int* row_seg = scratch;
+  int* seg_lohi = scratch + SEGMEAN_STATIC_MAX_ROWS;
+  // the array keeps the previous call's tables: segments the scan does not reach must not read them
+  const cudaError_t e = cudaMemsetAsync(seg_lohi, 0, sizeof(int) * 2 * (size_t)NI, st);
+  if (e != cudaSuccess) {
+    svpc_set_error("segmean_fwd_static: cudaMemsetAsync: %s", cudaGetErrorString(e));
+    return SVPC_ERR_CUDA;
+  }
+  svpc_launch(seg_scan_kernel, svpc_cdiv(B, 64), 64, 0, st, B, Li, sep_mask, cu_ingr, row_seg, seg_lohi);
+  rc = svpc_check_launch("seg_scan");
+  if (rc) return rc;
+  SVPC_DISPATCH(dt, T, (svpc_launch(segmean_fwd_kernel<T>, NI, 256, 0, st, B, Li, D, (const T*)x, cu_ingr, seg_lohi, pe, E0)));
+  return svpc_check_launch("segmean_fwd_static");
 }
 
 __global__ void ragged_mean_fwd_kernel(int D, const float* __restrict__ x, const int* __restrict__ cu, float* __restrict__ y) {
