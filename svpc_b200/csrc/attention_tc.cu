@@ -218,20 +218,23 @@ struct AtcParams {
 };
 
 // ------------------------------------------------------------------------------------------------ forward
-template <int NT>
+// FULL: both padded lengths equal NT * 8 (the usual case: L = 100 -> 112, L = 25 -> 32), so that every column-block bound
+// check of the unrolled loops folds at compile time
+template <int NT, bool FULL>
 __global__ void __launch_bounds__(NT <= 14 ? 224 : 256, NT <= 4 ? 4 : (NT <= 14 ? 3 : 1)) attn_tc_fwd_kernel(const AtcParams p) {
   svpc_pdl_sync();
+  const int lq_pad = FULL ? NT * 8 : p.lq_pad, lk_pad = FULL ? NT * 8 : p.lk_pad;
   extern __shared__ __align__(16) uint8_t atc_raw[];
   bf16* sQ = reinterpret_cast<bf16*>(atc_raw);
-  bf16* sK = sQ + p.lq_pad * ATC_PITCH;
-  bf16* sV = sK + p.lk_pad * ATC_PITCH;
-  float* madd = reinterpret_cast<float*>(sV + p.lk_pad * ATC_PITCH);
+  bf16* sK = sQ + lq_pad * ATC_PITCH;
+  bf16* sV = sK + lk_pad * ATC_PITCH;
+  float* madd = reinterpret_cast<float*>(sV + lk_pad * ATC_PITCH);
   const int n = blockIdx.x / p.H, h = blockIdx.x - n * p.H;
   const int lq = p.q_len[n], lk = p.k_len[n], qo = p.q_off[n], ko = p.k_off[n];
-  atc_load(sQ, p.q + (long long)qo * p.ldq + h * ATC_DH, p.ldq, lq, p.lq_pad);
-  atc_load(sK, p.k + (long long)ko * p.ldk + h * ATC_DH, p.ldk, lk, p.lk_pad);
-  atc_load(sV, p.v + (long long)ko * p.ldv + h * ATC_DH, p.ldv, lk, p.lk_pad);
-  for (int j = threadIdx.x; j < p.lk_pad; j += blockDim.x)
+  atc_load(sQ, p.q + (long long)qo * p.ldq + h * ATC_DH, p.ldq, lq, lq_pad);
+  atc_load(sK, p.k + (long long)ko * p.ldk + h * ATC_DH, p.ldk, lk, lk_pad);
+  atc_load(sV, p.v + (long long)ko * p.ldv + h * ATC_DH, p.ldv, lk, lk_pad);
+  for (int j = threadIdx.x; j < lk_pad; j += blockDim.x)
     madd[j] = (j < lk && p.key_mask) ? (1.f - p.key_mask[ko + j]) * -10000.f : 0.f;
   atc_load_wait();
   __syncthreads();
@@ -241,15 +244,15 @@ __global__ void __launch_bounds__(NT <= 14 ? 224 : 256, NT <= 4 ? 4 : (NT <= 14 
   uint32_t qf[4][4];
   atc_load_a(qf, sQ, r0, lane);
   float s[NT][4];
-  atc_mma_abt<NT>(s, qf, sK, p.lk_pad, lane);
+  atc_mma_abt<NT>(s, qf, sK, lk_pad, lane);
   float inv[2];
-  atc_softmax<NT>(s, r0 + (lane >> 2), lk, p.lk_pad, madd, p.causal, 0.125f, lane, false, inv);
+  atc_softmax<NT>(s, r0 + (lane >> 2), lk, lk_pad, madd, p.causal, 0.125f, lane, false, inv);
   const AtcDrop dr = atc_make_drop(p.drop, blockIdx.x, p.max_lq, p.max_lk);
-  atc_apply_drop<NT>(s, dr, r0 + (lane >> 2), p.lk_pad, lane);     // scale 1/(1-p) rides on the kept probabilities
+  atc_apply_drop<NT>(s, dr, r0 + (lane >> 2), lk_pad, lane);     // scale 1/(1-p) rides on the kept probabilities
   float o[8][4];
 #pragma unroll
   for (int dt = 0; dt < 8; ++dt) o[dt][0] = o[dt][1] = o[dt][2] = o[dt][3] = 0.f;
-  atc_mma_pb<NT>(o, s, sV, p.lk_pad, lane);
+  atc_mma_pb<NT>(o, s, sV, lk_pad, lane);
   atc_store(p.ctx + (long long)qo * p.ldo + h * ATC_DH, p.ldo, o, r0, lq, lane, inv[0], inv[1]);
 }
 
@@ -284,7 +287,7 @@ __device__ __forceinline__ void atc_write_x(bf16* X, int xp, const float (&s)[NT
       float v[4] = {s[nt][0], s[nt][1], s[nt][2], s[nt][3]};
       if (dr) {                          // P with the dropout decision in its sign (see attn_tc_bwd_kernel): dropped -> 0
 #pragma unroll
-        for (int e = 0; e < 4; ++e) v[e] = v[e] < 0.f ? 0.f : v[e] * dr->inv;
+        for (int e = 0; e < 4; ++e) v[e] = fmaxf(v[e], 0.f) * dr->inv;
       }
       *reinterpret_cast<uint32_t*>(X + (r0 + g) * xp + nt * 8 + t2) = pack_bf16(v[0], v[1]);
       *reinterpret_cast<uint32_t*>(X + (r0 + g + 8) * xp + nt * 8 + t2) = pack_bf16(v[2], v[3]);
@@ -292,30 +295,31 @@ __device__ __forceinline__ void atc_write_x(bf16* X, int xp, const float (&s)[NT
   }
 }
 
-template <int NT>
+template <int NT, bool FULL>
 __global__ void __launch_bounds__(NT <= 14 ? 224 : 256, NT <= 14 ? 2 : 1) attn_tc_bwd_kernel(const AtcParams p) {
   svpc_pdl_sync();
+  const int lq_pad = FULL ? NT * 8 : p.lq_pad, lk_pad = FULL ? NT * 8 : p.lk_pad;
   extern __shared__ __align__(16) uint8_t atc_raw[];
   bf16* sQ = reinterpret_cast<bf16*>(atc_raw);
-  bf16* sdO = sQ + p.lq_pad * ATC_PITCH;
-  bf16* sK = sdO + p.lq_pad * ATC_PITCH;
-  bf16* sV = sK + p.lk_pad * ATC_PITCH;
-  const int xp = p.lk_pad + 8;
-  bf16* sX = sV + p.lk_pad * ATC_PITCH;                  // [lq_pad][xp]: P, then dS
-  float* madd = reinterpret_cast<float*>(sX + p.lq_pad * xp);
+  bf16* sdO = sQ + lq_pad * ATC_PITCH;
+  bf16* sK = sdO + lq_pad * ATC_PITCH;
+  bf16* sV = sK + lk_pad * ATC_PITCH;
+  const int xp = lk_pad + 8;
+  bf16* sX = sV + lk_pad * ATC_PITCH;                  // [lq_pad][xp]: P, then dS
+  float* madd = reinterpret_cast<float*>(sX + lq_pad * xp);
   const int n = blockIdx.x / p.H, h = blockIdx.x - n * p.H;
   const int lq = p.q_len[n], lk = p.k_len[n], qo = p.q_off[n], ko = p.k_off[n];
-  atc_load(sQ, p.q + (long long)qo * p.ldq + h * ATC_DH, p.ldq, lq, p.lq_pad);
-  atc_load(sdO, p.dctx + (long long)qo * p.lddo + h * ATC_DH, p.lddo, lq, p.lq_pad);
-  atc_load(sK, p.k + (long long)ko * p.ldk + h * ATC_DH, p.ldk, lk, p.lk_pad);
-  atc_load(sV, p.v + (long long)ko * p.ldv + h * ATC_DH, p.ldv, lk, p.lk_pad);
-  for (int j = threadIdx.x; j < p.lk_pad; j += blockDim.x)
+  atc_load(sQ, p.q + (long long)qo * p.ldq + h * ATC_DH, p.ldq, lq, lq_pad);
+  atc_load(sdO, p.dctx + (long long)qo * p.lddo + h * ATC_DH, p.lddo, lq, lq_pad);
+  atc_load(sK, p.k + (long long)ko * p.ldk + h * ATC_DH, p.ldk, lk, lk_pad);
+  atc_load(sV, p.v + (long long)ko * p.ldv + h * ATC_DH, p.ldv, lk, lk_pad);
+  for (int j = threadIdx.x; j < lk_pad; j += blockDim.x)
     madd[j] = (j < lk && p.key_mask) ? (1.f - p.key_mask[ko + j]) * -10000.f : 0.f;
   atc_load_wait();
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
   const int r0 = warp * 16;
-  const bool active = r0 < p.lq_pad;                       // every warp of the CTA owns one padded row block
+  const bool active = r0 < lq_pad;                       // every warp of the CTA owns one padded row block
   const float scale = 0.125f;
   const AtcDrop dr = atc_make_drop(p.drop, blockIdx.x, p.max_lq, p.max_lk);
   const int gi = r0 + (lane >> 2), t2 = (lane & 3) * 2;
@@ -323,15 +327,15 @@ __global__ void __launch_bounds__(NT <= 14 ? 224 : 256, NT <= 14 ? 2 : 1) attn_t
   if (active) {
     uint32_t af[4][4];
     atc_load_a(af, sQ, r0, lane);
-    atc_mma_abt<NT>(s, af, sK, p.lk_pad, lane);
+    atc_mma_abt<NT>(s, af, sK, lk_pad, lane);
     float inv[2];
-    atc_softmax<NT>(s, r0 + (lane >> 2), lk, p.lk_pad, madd, p.causal, scale, lane, true, inv);
+    atc_softmax<NT>(s, r0 + (lane >> 2), lk, lk_pad, madd, p.causal, scale, lane, true, inv);
     // dropout: the keep / drop decision of every probability is computed ONCE and kept in the sign of P (P >= 0; a dropped
     // P is stored negated), instead of re-hashing the element index in each of the three places that need the mask
     if (dr.on) {
 #pragma unroll
       for (int nt = 0; nt < NT; ++nt) {
-        if (nt * 8 < p.lk_pad) {
+        if (nt * 8 < lk_pad) {
           float m[4];
           dr.scale2(gi, nt * 8 + t2, m[0], m[1]);
           dr.scale2(gi + 8, nt * 8 + t2, m[2], m[3]);
@@ -340,46 +344,44 @@ __global__ void __launch_bounds__(NT <= 14 ? 224 : 256, NT <= 14 ? 2 : 1) attn_t
         }
       }
     }
-    atc_write_x<NT>(sX, xp, s, r0, p.lk_pad, lane, dr.on ? &dr : nullptr);   // dropped P (bf16) for dV
+    atc_write_x<NT>(sX, xp, s, r0, lk_pad, lane, dr.on ? &dr : nullptr);   // dropped P (bf16) for dV
     // D_i = sum_j P_ij dP_ij, dP = dO V^T (recomputed below instead of kept: 4*NT registers saved)
     atc_load_a(af, sdO, r0, lane);
     float dsum[2] = {0.f, 0.f};
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt) {
-      if (nt * 8 < p.lk_pad) {
+      if (nt * 8 < lk_pad) {
         float dp[4];
         atc_tile_abt(dp, af, sV, nt, lane);
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          const float m = (dr.on && s[nt][e] < 0.f) ? 0.f : dr.inv;          // (a dropped probability carries a minus sign)
-          dsum[e >> 1] = fmaf(fabsf(s[nt][e]), dp[e] * m, dsum[e >> 1]);
-        }
+        for (int e = 0; e < 4; ++e)                                          // (a dropped probability carries a minus sign)
+          dsum[e >> 1] = fmaf(fmaxf(s[nt][e], 0.f), dp[e], dsum[e >> 1]);
       }
     }
 #pragma unroll
     for (int r = 0; r < 2; ++r) {
       dsum[r] += __shfl_xor_sync(0xffffffffu, dsum[r], 1);
       dsum[r] += __shfl_xor_sync(0xffffffffu, dsum[r], 2);
+      dsum[r] *= dr.inv * scale;                            // D_i * scale (the kept probabilities carry 1 / (1 - p))
     }
+    const float c1 = dr.inv * scale;
     // dS = P * (dP - D) * scale, in place of P (dP tile recomputed: two MMAs cost less than 4*NT live registers)
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt) {
-      if (nt * 8 < p.lk_pad) {
+      if (nt * 8 < lk_pad) {
         float dp[4];
         atc_tile_abt(dp, af, sV, nt, lane);
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          const float m = (dr.on && s[nt][e] < 0.f) ? 0.f : dr.inv;
-          s[nt][e] = fabsf(s[nt][e]) * (dp[e] * m - dsum[e >> 1]) * scale;
-        }
+        for (int e = 0; e < 4; ++e)     // P (m dP - D) scale = relu(s) dP (inv scale) - |s| (D scale)
+          s[nt][e] = fmaf(fmaxf(s[nt][e], 0.f) * dp[e], c1, -fabsf(s[nt][e]) * dsum[e >> 1]);
       }
     }
   }
   __syncthreads();                                          // P complete in sX; sV no longer needed as an operand
   // dV[j] = sum_i P[i][j] dO[i]
-  for (int j0 = warp * 16; j0 < p.lk_pad; j0 += nwarps * 16) {
+  for (int j0 = warp * 16; j0 < lk_pad; j0 += nwarps * 16) {
     float acc[8][4];
-    atc_mma_xtb(acc, sX, xp, sdO, j0, p.lq_pad, lane);
+    atc_mma_xtb(acc, sX, xp, sdO, j0, lq_pad, lane);
     atc_store(p.dv + (long long)ko * p.lddv + h * ATC_DH, p.lddv, acc, j0, lk, lane, 1.f, 1.f);
   }
   // dQ[i] = sum_j dS[i][j] K[j]   (dS still in registers)
@@ -387,16 +389,16 @@ __global__ void __launch_bounds__(NT <= 14 ? 224 : 256, NT <= 14 ? 2 : 1) attn_t
     float acc[8][4];
 #pragma unroll
     for (int dt = 0; dt < 8; ++dt) acc[dt][0] = acc[dt][1] = acc[dt][2] = acc[dt][3] = 0.f;
-    atc_mma_pb<NT>(acc, s, sK, p.lk_pad, lane);
+    atc_mma_pb<NT>(acc, s, sK, lk_pad, lane);
     atc_store(p.dq + (long long)qo * p.lddq + h * ATC_DH, p.lddq, acc, r0, lq, lane, 1.f, 1.f);
   }
   __syncthreads();                                          // every warp is done reading P
-  if (active) atc_write_x<NT>(sX, xp, s, r0, p.lk_pad, lane, nullptr);
+  if (active) atc_write_x<NT>(sX, xp, s, r0, lk_pad, lane, nullptr);
   __syncthreads();
   // dK[j] = sum_i dS[i][j] Q[i]
-  for (int j0 = warp * 16; j0 < p.lk_pad; j0 += nwarps * 16) {
+  for (int j0 = warp * 16; j0 < lk_pad; j0 += nwarps * 16) {
     float acc[8][4];
-    atc_mma_xtb(acc, sX, xp, sQ, j0, p.lq_pad, lane);
+    atc_mma_xtb(acc, sX, xp, sQ, j0, lq_pad, lane);
     atc_store(p.dk + (long long)ko * p.lddk + h * ATC_DH, p.lddk, acc, j0, lk, lane, 1.f, 1.f);
   }
 }
@@ -422,13 +424,24 @@ int svpc_attn_tc_fwd_launch(int n_seq, const AtcParams& p0, int max_lq, int max_
   const int threads = 32 * (p.lq_pad / 16);
   static bool attr = false;
   if (!attr) {
-    cudaFuncSetAttribute(attn_tc_fwd_kernel<14>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
-    cudaFuncSetAttribute(attn_tc_fwd_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+    cudaFuncSetAttribute(attn_tc_fwd_kernel<14, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+    cudaFuncSetAttribute(attn_tc_fwd_kernel<14, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+    cudaFuncSetAttribute(attn_tc_fwd_kernel<16, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+    cudaFuncSetAttribute(attn_tc_fwd_kernel<16, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
     attr = true;
   }
-  if (p.lk_pad <= 32) svpc_launch(attn_tc_fwd_kernel<4>, n_seq * p.H, threads, smem, st, p);
-  else if (p.lk_pad <= 112) svpc_launch(attn_tc_fwd_kernel<14>, n_seq * p.H, threads, smem, st, p);
-  else svpc_launch(attn_tc_fwd_kernel<16>, n_seq * p.H, threads, smem, st, p);
+  const int grid = n_seq * p.H;
+  const bool sq = p.lq_pad == p.lk_pad;
+  if (p.lk_pad <= 32) {
+    if (sq && p.lk_pad == 32) svpc_launch(attn_tc_fwd_kernel<4, true>, grid, threads, smem, st, p);
+    else svpc_launch(attn_tc_fwd_kernel<4, false>, grid, threads, smem, st, p);
+  } else if (p.lk_pad <= 112) {
+    if (sq && p.lk_pad == 112) svpc_launch(attn_tc_fwd_kernel<14, true>, grid, threads, smem, st, p);
+    else svpc_launch(attn_tc_fwd_kernel<14, false>, grid, threads, smem, st, p);
+  } else {
+    if (sq && p.lk_pad == 128) svpc_launch(attn_tc_fwd_kernel<16, true>, grid, threads, smem, st, p);
+    else svpc_launch(attn_tc_fwd_kernel<16, false>, grid, threads, smem, st, p);
+  }
   return svpc_check_launch("attn_tc_fwd");
 }
 
@@ -442,14 +455,26 @@ int svpc_attn_tc_bwd_launch(int n_seq, const AtcParams& p0, int max_lq, int max_
   const int threads = 32 * (p.lq_pad / 16);
   static bool attr = false;
   if (!attr) {
-    cudaFuncSetAttribute(attn_tc_bwd_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 120 * 1024);
-    cudaFuncSetAttribute(attn_tc_bwd_kernel<14>, cudaFuncAttributeMaxDynamicSharedMemorySize, 120 * 1024);
-    cudaFuncSetAttribute(attn_tc_bwd_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 120 * 1024);
+    cudaFuncSetAttribute(attn_tc_bwd_kernel<4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 120 * 1024);
+    cudaFuncSetAttribute(attn_tc_bwd_kernel<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 120 * 1024);
+    cudaFuncSetAttribute(attn_tc_bwd_kernel<14, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 120 * 1024);
+    cudaFuncSetAttribute(attn_tc_bwd_kernel<14, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 120 * 1024);
+    cudaFuncSetAttribute(attn_tc_bwd_kernel<16, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 120 * 1024);
+    cudaFuncSetAttribute(attn_tc_bwd_kernel<16, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 120 * 1024);
     attr = true;
   }
-  if (p.lk_pad <= 32) svpc_launch(attn_tc_bwd_kernel<4>, n_seq * p.H, threads, smem, st, p);
-  else if (p.lk_pad <= 112 && p.lq_pad <= 112) svpc_launch(attn_tc_bwd_kernel<14>, n_seq * p.H, threads, smem, st, p);
-  else svpc_launch(attn_tc_bwd_kernel<16>, n_seq * p.H, threads, smem, st, p);
+  const int grid = n_seq * p.H;
+  const bool sq = p.lq_pad == p.lk_pad;
+  if (p.lk_pad <= 32) {
+    if (sq && p.lk_pad == 32) svpc_launch(attn_tc_bwd_kernel<4, true>, grid, threads, smem, st, p);
+    else svpc_launch(attn_tc_bwd_kernel<4, false>, grid, threads, smem, st, p);
+  } else if (p.lk_pad <= 112 && p.lq_pad <= 112) {
+    if (sq && p.lk_pad == 112) svpc_launch(attn_tc_bwd_kernel<14, true>, grid, threads, smem, st, p);
+    else svpc_launch(attn_tc_bwd_kernel<14, false>, grid, threads, smem, st, p);
+  } else {
+    if (sq && p.lk_pad == 128) svpc_launch(attn_tc_bwd_kernel<16, true>, grid, threads, smem, st, p);
+    else svpc_launch(attn_tc_bwd_kernel<16, false>, grid, threads, smem, st, p);
+  }
   return svpc_check_launch("attn_tc_bwd");
 }
 

@@ -222,6 +222,14 @@ extern "C" int svpc_lstm_step_bwd(int B, int D, int Nc, int Smax, int j, const f
 // the videos from L2, instead of a kernel launch and 9.4 MB of weights per direction.  The barrier is a monotonic
 // counter per direction in global memory (`sync`, zeroed by the caller); all CTAs are co-resident (grid <= #SMs, 1 CTA/SM).
 #define LSTM_PW 12          // warps per CTA = most hidden units a CTA can own
+#define LSTM_BB 8           // videos per pass of the backward product (register tile LSTM_PW x LSTM_BB)
+#define LSTM_SRN 64         // videos whose next-step rows the backward stages ahead of the barrier
+#define LSTM_SEQ_EXTRA 2048 // floats of shared memory behind the staging area for small per-step tables (dynamic: the kernels use all of it)
+// offset (floats) of the small tables: behind the resident weights and the larger of the forward / backward staging areas
+__host__ __device__ __forceinline__ size_t lstm_seq_tail_off(int D) {
+  const size_t fwd = (size_t)LSTM_BV * D, bwd = (size_t)2 * LSTM_PW * LSTM_PW * LSTM_BB;
+  return (size_t)LSTM_PW * 4 * D + (fwd > bwd ? fwd : bwd);
+}
 
 struct LstmSeqParams {
   LstmStepParams s;
@@ -280,21 +288,56 @@ __global__ void __launch_bounds__(LSTM_PW * 32, 1) lstm_seq_fwd_kernel(const Lst
   unsigned int* cnt = q.sync + dir;
   const int d = u0 + warp;
   const bool own = warp < u1 - u0;
+  int* srp = reinterpret_cast<int*>(smem + lstm_seq_tail_off(D));   // row of the previous step per video of the current pass (-1: none)
+  const int eb = lane >> 1;                               // video (within a pass) whose state this lane finishes
+  const bool epi = own && !(lane & 1);
+  const int n4 = LSTM_BV * D / 4;
   for (int j = 0; j < p.Smax; ++j) {
     const int* rows_j = p.rows + ((long long)dir * p.Smax + j) * p.B;
     const int* rows_p = rows_j - p.B;
+    // everything that does not depend on the other CTAs is fetched BEFORE the barrier wait: the row indices of the first
+    // pass and this lane's input-gate pre-activations and previous cell state
+    if (threadIdx.x < LSTM_BV)
+      srp[threadIdx.x] = (j > 0 && threadIdx.x < p.B && rows_j[threadIdx.x] >= 0) ? rows_p[threadIdx.x] : -1;
+    int pr = -1, prp = -1;
+    float px0 = 0.f, px1 = 0.f, px2 = 0.f, px3 = 0.f, pcp = 0.f;
+    if (epi && eb < p.B) {
+      pr = rows_j[eb];
+      if (pr >= 0) {
+        prp = j > 0 ? rows_p[eb] : -1;
+        const float* x = p.xg + ((long long)dir * p.Nc + pr) * 4 * D;
+        px0 = x[d]; px1 = x[D + d]; px2 = x[2 * D + d]; px3 = x[3 * D + d];
+        if (prp >= 0) pcp = cs[(long long)prp * D + d];              // written by this very thread one step earlier
+      }
+    }
     if (j > 0) dir_barrier_wait(cnt, (unsigned int)(q.cpd * j), q.sync + 2);     // h of step j-1 is complete
     else __syncthreads();                                                        // weights staged
     for (int b0 = 0; b0 < p.B; b0 += LSTM_BV) {
       if (j > 0) {
-        __syncthreads();
-        for (int e = threadIdx.x * 4; e < LSTM_BV * D; e += blockDim.x * 4) {
-          const int b = e / D, k = e - b * D;
-          int rp = -1;
-          if (b0 + b < p.B && rows_j[b0 + b] >= 0) rp = rows_p[b0 + b];
-          float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (rp >= 0) v = __ldcg(reinterpret_cast<const float4*>(hs + (long long)rp * D + k));   // written by other SMs
-          *reinterpret_cast<float4*>(hsm + e) = v;
+        if (b0 > 0) {
+          __syncthreads();
+          if (threadIdx.x < LSTM_BV)
+            srp[threadIdx.x] = (b0 + threadIdx.x < p.B && rows_j[b0 + threadIdx.x] >= 0) ? rows_p[b0 + threadIdx.x] : -1;
+          __syncthreads();
+        }
+        // h rows of the pass: eight 16-byte loads per thread in flight (written by other SMs: L2 loads)
+        for (int base = threadIdx.x; base < n4; base += 8 * (int)blockDim.x) {
+          float4 v[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const int i = base + u * (int)blockDim.x;
+            v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (i < n4) {
+              const int e = i * 4, b = e / D, k = e - b * D;
+              const int rp = srp[b];
+              if (rp >= 0) v[u] = __ldcg(reinterpret_cast<const float4*>(hs + (long long)rp * D + k));
+            }
+          }
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const int i = base + u * (int)blockDim.x;
+            if (i < n4) *reinterpret_cast<float4*>(hsm + (size_t)i * 4) = v[u];
+          }
         }
         __syncthreads();
       }
@@ -322,22 +365,30 @@ __global__ void __launch_bounds__(LSTM_PW * 32, 1) lstm_seq_fwd_kernel(const Lst
         warp_reduce_transpose<LSTM_BV * 4>(acc, lane);
       }
       const float o0 = __shfl_xor_sync(0xffffffffu, acc[0], 1), o1 = __shfl_xor_sync(0xffffffffu, acc[1], 1);
-      const int b = b0 + (lane >> 1);
+      const int b = b0 + eb;
       if ((lane & 1) || b >= p.B) continue;
-      const int r = rows_j[b];
-      if (r < 0) continue;
-      const int rp = j > 0 ? rows_p[b] : -1;
-      const float* x = p.xg + ((long long)dir * p.Nc + r) * 4 * D;
-      const float gi = svpc_sigmoid(x[d] + acc[0]);
-      const float gf = svpc_sigmoid(x[D + d] + acc[1]);
-      const float gg = tanhf(x[2 * D + d] + o0);
-      const float go = svpc_sigmoid(x[3 * D + d] + o1);
-      const float cp = rp >= 0 ? cs[(long long)rp * D + d] : 0.f;     // written by this very thread one step earlier
+      int r, rp;
+      float x0, x1, x2, x3, cp;
+      if (b0 == 0) {
+        r = pr; rp = prp; x0 = px0; x1 = px1; x2 = px2; x3 = px3; cp = pcp;
+        if (r < 0) continue;
+      } else {
+        r = rows_j[b];
+        if (r < 0) continue;
+        rp = j > 0 ? rows_p[b] : -1;
+        const float* x = p.xg + ((long long)dir * p.Nc + r) * 4 * D;
+        x0 = x[d]; x1 = x[D + d]; x2 = x[2 * D + d]; x3 = x[3 * D + d];
+        cp = rp >= 0 ? cs[(long long)rp * D + d] : 0.f;
+      }
+      const float gi = svpc_sigmoid(x0 + acc[0]);
+      const float gf = svpc_sigmoid(x1 + acc[1]);
+      const float gg = tanhf(x2 + o0);
+      const float go = svpc_sigmoid(x3 + o1);
       const float cn = gf * cp + gi * gg;
       const float hn = go * tanhf(cn);
       cs[(long long)r * D + d] = cn;
       p.hs[((long long)dir * p.Nc + r) * D + d] = hn;
-      p.hprev[((long long)dir * p.Nc + r) * D + d] = rp >= 0 ? hsm[(lane >> 1) * D + d] : 0.f;
+      p.hprev[((long long)dir * p.Nc + r) * D + d] = rp >= 0 ? hsm[eb * D + d] : 0.f;
       float* g = p.gates + ((long long)dir * p.Nc + r) * 4 * D;
       g[d] = gi; g[D + d] = gf; g[2 * D + d] = gg; g[3 * D + d] = go;
       atomicAdd(p.out + (long long)r * D + d, hn);
@@ -352,7 +403,6 @@ __global__ void __launch_bounds__(LSTM_PW * 32, 1) lstm_seq_fwd_kernel(const Lst
 // gate-gradient element is loaded from L2 exactly once per CTA, straight into registers (no staging, no barriers), every
 // resident weight is read from shared memory once per pass of LSTM_BB videos, and each thread carries an LSTM_PW x LSTM_BB
 // register tile of partial sums, reduced by a transposing warp reduction and one cross-warp pass through shared memory.
-#define LSTM_BB 8           // videos per pass of the backward product (register tile LSTM_PW x LSTM_BB)
 __global__ void __launch_bounds__(LSTM_PW * 32, 1) lstm_seq_bwd_kernel(const LstmSeqParams q) {
   svpc_pdl_sync();
   const LstmStepParams& p = q.s;
@@ -365,6 +415,9 @@ __global__ void __launch_bounds__(LSTM_PW * 32, 1) lstm_seq_bwd_kernel(const Lst
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   float* wsm = smem;                                     // [LSTM_PW][4D]  rows u0.. of W_hh^T[dir], zero beyond nu
   float* red = smem + (size_t)LSTM_PW * E4;              // [2][LSTM_PW warps][NACC] partial sums
+  int* srn = reinterpret_cast<int*>(smem + lstm_seq_tail_off(D));   // [LSTM_SRN] rows of step j+1
+  float* sepi = smem + lstm_seq_tail_off(D) + LSTM_SRN;             // [2 passes][8 operands][NACC] epilogue operands
+  static_assert(LSTM_SRN + 2 * 8 * NACC <= LSTM_SEQ_EXTRA, "small tables exceed their shared-memory window");
   for (int e = threadIdx.x * 4; e < LSTM_PW * E4; e += blockDim.x * 4) {
     float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
     if (e < nu * E4) v = __ldg(reinterpret_cast<const float4*>(p.whh + ((long long)dir * D + u0) * E4 + e));
@@ -377,6 +430,31 @@ __global__ void __launch_bounds__(LSTM_PW * 32, 1) lstm_seq_bwd_kernel(const Lst
     const int* rows_j = p.rows + ((long long)dir * p.Smax + j) * p.B;
     const int* rows_n = rows_j + p.B;
     const bool has_next = j + 1 < p.Smax;
+    // operands that do not depend on the other CTAs are staged in shared memory BEFORE the barrier wait, by warps that do not
+    // poll: the next-step rows of the first LSTM_SRN videos and the epilogue operands of the first two passes
+    if (has_next && threadIdx.x >= 256 && threadIdx.x < 256 + LSTM_SRN) {
+      const int b = threadIdx.x - 256;
+      srn[b] = b < p.B ? rows_n[b] : -1;
+    }
+    if (threadIdx.x >= 128 && threadIdx.x < 128 + NACC) {
+      const int t = threadIdx.x - 128, u = t / LSTM_BB, d = u0 + u;
+#pragma unroll
+      for (int pass = 0; pass < 2; ++pass) {
+        const int b = pass * LSTM_BB + (t - u * LSTM_BB);
+        float* e = sepi + (size_t)pass * 8 * NACC + t;
+        int r = -1;
+        if (u < nu && b < p.B) r = rows_j[b];
+        e[0] = __int_as_float(r);
+        if (r >= 0) {
+          const int rp = j > 0 ? rows_j[b - p.B] : -1;
+          const float* g = p.gates + ((long long)dir * p.Nc + r) * E4;
+          e[1 * NACC] = g[d]; e[2 * NACC] = g[D + d]; e[3 * NACC] = g[2 * D + d]; e[4 * NACC] = g[3 * D + d];
+          e[5 * NACC] = cs[(long long)r * D + d];
+          e[6 * NACC] = rp >= 0 ? cs[(long long)rp * D + d] : 0.f;
+          e[7 * NACC] = p.dout[(long long)r * D + d];
+        }
+      }
+    }
     if (it > 0) dir_barrier_wait(cnt, (unsigned int)(q.cpd * it), q.sync + 2);   // gate gradients of step j+1 complete
     else __syncthreads();
     for (int b0 = 0, pass = 0; b0 < p.B; b0 += LSTM_BB, ++pass) {
@@ -388,7 +466,7 @@ __global__ void __launch_bounds__(LSTM_PW * 32, 1) lstm_seq_bwd_kernel(const Lst
         const float* gp[LSTM_BB];
 #pragma unroll
         for (int b = 0; b < LSTM_BB; ++b) {
-          const int rn = (b0 + b < p.B) ? rows_n[b0 + b] : -1;
+          const int rn = (b0 + b < LSTM_SRN) ? srn[b0 + b] : (b0 + b < p.B) ? rows_n[b0 + b] : -1;
           gp[b] = rn >= 0 ? dg + (long long)rn * E4 : nullptr;
         }
         for (int e = threadIdx.x * 4; e < E4; e += blockDim.x * 4) {
@@ -416,20 +494,31 @@ __global__ void __launch_bounds__(LSTM_PW * 32, 1) lstm_seq_bwd_kernel(const Lst
       const int t = threadIdx.x;
       const int u = t / LSTM_BB, b = b0 + (t - u * LSTM_BB);
       if (t >= NACC || u >= nu || b >= p.B) continue;
-      const int r = rows_j[b];
-      if (r < 0) continue;
+      const int d = u0 + u;
+      int r;
+      float gi, gf, gg, go, cr, cp, dob;
+      if (pass < 2) {
+        const float* e = sepi + (size_t)pass * 8 * NACC + t;
+        r = __float_as_int(e[0]);
+        if (r < 0) continue;
+        gi = e[1 * NACC]; gf = e[2 * NACC]; gg = e[3 * NACC]; go = e[4 * NACC]; cr = e[5 * NACC]; cp = e[6 * NACC]; dob = e[7 * NACC];
+      } else {
+        r = rows_j[b];
+        if (r < 0) continue;
+        const int rp = j > 0 ? rows_j[b - p.B] : -1;
+        const float* g = p.gates + ((long long)dir * p.Nc + r) * E4;
+        gi = g[d]; gf = g[D + d]; gg = g[2 * D + d]; go = g[3 * D + d];
+        cr = cs[(long long)r * D + d];
+        cp = rp >= 0 ? cs[(long long)rp * D + d] : 0.f;
+        dob = p.dout[(long long)r * D + d];
+      }
       float sum = 0.f;
       if (has_next) {
 #pragma unroll
         for (int w = 0; w < LSTM_PW; ++w) sum += rbuf[w * NACC + t];
       }
-      const int d = u0 + u;
-      const int rp = j > 0 ? rows_j[b - p.B] : -1;
-      const float* g = p.gates + ((long long)dir * p.Nc + r) * E4;
-      const float gi = g[d], gf = g[D + d], gg = g[2 * D + d], go = g[3 * D + d];
-      const float tc = tanhf(cs[(long long)r * D + d]);
-      const float cp = rp >= 0 ? cs[(long long)rp * D + d] : 0.f;
-      const float dh = p.dout[(long long)r * D + d] + sum;
+      const float tc = tanhf(cr);
+      const float dh = dob + sum;
       float* dcp = p.dc + ((long long)dir * p.B + b) * D + d;           // owned by this thread for the whole sweep
       const float dct = *dcp + dh * go * (1.f - tc * tc);
       *dcp = dct * gf;
@@ -454,9 +543,7 @@ static int lstm_device_sms() {
 }
 
 static size_t lstm_seq_smem(int D) {
-  const size_t tail = (size_t)LSTM_BV * D > (size_t)2 * LSTM_PW * LSTM_PW * LSTM_BB ? (size_t)LSTM_BV * D
-                                                                                : (size_t)2 * LSTM_PW * LSTM_PW * LSTM_BB;
-  return ((size_t)LSTM_PW * 4 * D + tail) * sizeof(float);   // fwd: h staging; bwd: reduction buffers
+  return (lstm_seq_tail_off(D) + LSTM_SEQ_EXTRA) * sizeof(float);   // resident weights; fwd: h staging, bwd: reduction buffers; small tables
 }
 
 static void lstm_seq_attrs() {
