@@ -68,6 +68,8 @@ def parse():
     ap.add_argument("--ragged", action="store_true", help="headline step on the ragged batch of SURVEY 8d (train task)")
     ap.add_argument("--fp32-features", action="store_true",
                     help="bf16 path: keep the clip features fp32 in the input arena (default: the loader hands them over as bf16)")
+    ap.add_argument("--inject-noise", action="store_true",
+                    help="upload the Gumbel noise of the re-simulator with the batch instead of drawing it on the device")
     ap.add_argument("--verify-ddp", action="store_true",
                     help="N >= 2: the NCCL data-parallel step on N shards against a 1-rank step on the concatenated batch")
     return ap.parse_args()
@@ -290,9 +292,14 @@ class TrainBench:
         fa = synth.forward_args(self.batch)
         fa[1] = [t.to(self.feature_dtype) for t in fa[1]]
         self.host_args = [tree(lambda t: t.pin_memory(), a) for a in fa]
-        self.noise_host = [g.pin_memory() for g in self.batch["gumbel"]]
+        # Gumbel noise: the reference draws it on the GPU inside the step (F.gumbel_softmax, model.py:1018) and so does the timed
+        # step (svpc_gumbel_noise, seeded per step); --inject-noise uploads the batch's noise instead.  The parity forward always
+        # gets the batch's noise: the oracle needs the same numbers.
+        inject = getattr(args, "inject_noise", False)
+        self.noise_host = [g.pin_memory() for g in self.batch["gumbel"]] if inject else None
         self.dev_args = [tree(lambda t: t.to(dev, non_blocking=True), a) for a in self.host_args]
-        self.noise_dev = [g.to(dev, non_blocking=True) for g in self.noise_host]
+        self.noise_dev = [g.to(dev, non_blocking=True) for g in self.noise_host] if inject else None
+        self.parity_noise = [g.to(dev) for g in self.batch["gumbel"]]
         torch.cuda.synchronize()
         self.gstep, self.per_replay = None, 0
         if graph:
@@ -316,7 +323,7 @@ class TrainBench:
         was = self.model.training
         self.model.eval()
         with torch.no_grad():
-            loss = float(self.model(*self.dev_args, gumbel_noise=self.noise_dev)[0])
+            loss = float(self.model(*self.dev_args, gumbel_noise=self.parity_noise)[0])
         self.model.train(was)
         return loss
 
@@ -671,7 +678,7 @@ def main():
     # ---- end-to-end timing: pinned host inputs -> H2D every step, loss read back
     e2e = None
     if not args.no_e2e:
-        h2d_bytes = sum(nbytes(a) for a in tb.host_args) + sum(nbytes(g) for g in tb.noise_host)
+        h2d_bytes = sum(nbytes(a) for a in tb.host_args) + sum(nbytes(g) for g in (tb.noise_host or []))
         gstep = tb.gstep
         if gstep is not None:
             # the loader's collate target: pinned host views of the step's input arena
@@ -682,7 +689,7 @@ def main():
                 elif is_tlist(dst):
                     for d_, s_ in zip(dst, src):
                         d_.copy_(s_)
-            for d_, s_ in zip(arena_noise, tb.noise_host):
+            for d_, s_ in zip(arena_noise or [], tb.noise_host or []):
                 d_.copy_(s_)
             h2d_bytes = gstep.arena.h2d_nbytes     # the 25 never-read text rows of each (125, 3072) clip block are not uploaded
 
@@ -705,7 +712,7 @@ def main():
                 return
             for _ in range(k):
                 a = [tree(lambda t: t.to(dev, non_blocking=True), x) for x in tb.host_args]
-                nz = [g.to(dev, non_blocking=True) for g in tb.noise_host]
+                nz = [g.to(dev, non_blocking=True) for g in tb.noise_host] if tb.noise_host is not None else None
                 tb.model.zero_grad(set_to_none=True)
                 l_ = tb.model(*a, gumbel_noise=nz)[0]
                 l_.backward()
@@ -719,6 +726,8 @@ def main():
                "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": 4, "ms_per_step": round(ms_e2e / args.steps, 3),
                "h2d_ceiling_gbs": round(ceil, 1), "h2d_ms_at_ceiling": round(h2d_bytes / ceil / 1e6, 3),
                "upload_dtype": getattr(gstep.arena, "feature_dtype", "fp32") if gstep is not None else "fp32",
+               "gumbel_noise": "uploaded with the batch (--inject-noise)" if tb.noise_host is not None else
+                               "drawn on the device inside the step (svpc_gumbel_noise; the reference's F.gumbel_softmax draws it on the GPU too)",
                "pipeline": "every step uploads all of its inputs from pinned host memory; the upload of step i+1 runs on a copy stream under step i (first upload exposed); each step's loss goes to pinned host memory and is read by the host one step later" if gstep is not None else "serial"}
 
     # ---- roofline: the whole step against the tensor peak + the dominant tcgen05 GEMM alone

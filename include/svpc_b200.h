@@ -55,6 +55,10 @@ void svpc_reset_launch_count(void);
  * svpc_dropout_mask writes the scale (0 or 1/(1-p)) of elements [0, n) - used by the tests to state the contract. */
 int svpc_dropout_mask(long long n, const unsigned int* drop_seed, unsigned int drop_site, float drop_p, float* out,
                       svpc_stream_t stream);
+/* Gumbel(0,1) noise of F.gumbel_softmax (model.py:1018; torch draws -log(Exp(1)) on the device inside the step): element i is
+ * -log(-log(u_i)), u_i from the counter hash of (*seed, site, i), so that a replayed CUDA graph draws new noise when the
+ * device seed is bumped.  The model uses it when no noise is injected (tests inject the oracle's noise instead). */
+int svpc_gumbel_noise(long long n, const unsigned int* seed, unsigned int site, float* out, svpc_stream_t stream);
 
 /* D[M,N] = drop(act(A[M,K] . B[N,K]^T + bias[N])) + residual[M,N]  (+ D when accumulate); optional copy of the
  * pre-activation.  Dropout element index = m * N + n.  A and B are addressed by element strides (one of each pair must be 1).  Replaces every

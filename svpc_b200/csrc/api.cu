@@ -89,6 +89,31 @@ extern "C" int svpc_dropout_mask(long long n, const unsigned int* drop_seed, uns
   return svpc_check_launch("dropout_mask");
 }
 
+// Gumbel(0, 1) noise for the hard Gumbel-softmax of the textual re-simulator (reference model.py:1018, F.gumbel_softmax:
+// -log(Exp(1)) drawn on the GPU inside the step).  Counter-based like the dropout masks: element i of the step with device
+// seed *seed is -log(-log(u)), u = (23 bits of hash(seed, site, i) + 0.5) / 2^23, so a captured graph draws fresh noise on
+// every replay (the seed lives on the device) and nothing has to be uploaded.
+__global__ void gumbel_noise_kernel(long long n, const SvpcDrop key_src, float* __restrict__ out) {
+  svpc_pdl_sync();
+  const uint32_t key = svpc_drop_key(key_src);
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  for (; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const uint32_t h = svpc_mix32((uint32_t)i * 0x9e3779b1u + (uint32_t)((unsigned long long)i >> 32) * 0x85ebca6bu + key);
+    // 23 bits + 0.5: every value is exact in fp32 and strictly inside (0, 1) (with 24 bits the largest one rounds to 1.0 and
+    // -log(-log(1)) is +inf: one element in 2^24, i.e. every few steps at 4.6 M elements per step)
+    const float u = ((float)(h >> 9) + 0.5f) * (1.0f / 8388608.0f);
+    out[i] = -logf(-logf(u));
+  }
+}
+
+extern "C" int svpc_gumbel_noise(long long n, const unsigned int* seed, unsigned int site, float* out, svpc_stream_t stream) {
+  if (n <= 0) return SVPC_OK;
+  SVPC_REQUIRE(seed != nullptr && out != nullptr, "gumbel_noise: needs the device seed and the output");
+  const SvpcDrop key_src{seed, site, 1.f};
+  svpc_launch(gumbel_noise_kernel, svpc_imin(svpc_cdiv(n, 256), SVPC_NUM_SMS * 16), 256, 0, (cudaStream_t)stream, n, key_src, out);
+  return svpc_check_launch("gumbel_noise");
+}
+
 // deterministic single-CTA sum (loss reductions: a few thousand elements)
 __global__ void sum_kernel(long long n, const float* __restrict__ x, float* __restrict__ out) {
   svpc_pdl_sync();

@@ -11,6 +11,9 @@
 #include "common.cuh"
 
 #define ATC_DH 64
+#ifndef ATC_FWD_BLOCKS
+#define ATC_FWD_BLOCKS 4   // CTAs per SM the L <= 112 forward is compiled for (measured at L = 100: 2 -> 83 us without spills, 3 -> 75 us, 4 -> 73 us: occupancy wins over the spills)
+#endif
 #define ATC_PITCH 72   // bf16 elements per smem row (64 + 8 pad)
 
 __device__ __forceinline__ uint32_t atc_smem(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -221,7 +224,7 @@ struct AtcParams {
 // FULL: both padded lengths equal NT * 8 (the usual case: L = 100 -> 112, L = 25 -> 32), so that every column-block bound
 // check of the unrolled loops folds at compile time
 template <int NT, bool FULL>
-__global__ void __launch_bounds__(NT <= 14 ? 224 : 256, NT <= 4 ? 4 : (NT <= 14 ? 3 : 1)) attn_tc_fwd_kernel(const AtcParams p) {
+__global__ void __launch_bounds__(NT <= 14 ? 224 : 256, NT <= 4 ? 4 : (NT <= 14 ? ATC_FWD_BLOCKS : 1)) attn_tc_fwd_kernel(const AtcParams p) {
   svpc_pdl_sync();
   const int lq_pad = FULL ? NT * 8 : p.lq_pad, lk_pad = FULL ? NT * 8 : p.lk_pad;
   extern __shared__ __align__(16) uint8_t atc_raw[];

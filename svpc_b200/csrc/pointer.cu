@@ -761,6 +761,7 @@ __global__ void __launch_bounds__(PG_THREADS) gumbel_fwd_kernel(int Lt, int V, c
     float m = smax[0]; int bi = sidx[0];
     for (int w = 1; w < PG_THREADS / 32; ++w)
       if (smax[w] > m || (smax[w] == m && sidx[w] < bi)) { m = smax[w]; bi = sidx[w]; }
+    if (bi >= vx) bi = 0;          // a row of NaNs compares false everywhere: never hand out an index outside the row
     s_best = bi; s_mx = m;
   }
   __syncthreads();

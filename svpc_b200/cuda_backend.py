@@ -295,6 +295,12 @@ class CudaBackend:
         self._call("svpc_dropout_mask", _ll(n), *_drop(drop), _ptr(out))
         return out
 
+    def gumbel_noise(self, n, seed, site):
+        """Gumbel(0,1) noise of one step (reference: F.gumbel_softmax draws it on the device, model.py:1018)."""
+        out = torch.empty(int(n), dtype=torch.float32, device=seed.device)
+        self._call("svpc_gumbel_noise", _ll(n), _ptr(seed), C.c_uint(int(site)), _ptr(out))
+        return out
+
     def colsum(self, x):
         self._chk(x)
         if x.dim() == 2 and not x.is_contiguous() and x.stride(1) == 1 and x.stride(0) > x.shape[1] and x.shape[0] > 0:

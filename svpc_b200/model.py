@@ -25,6 +25,7 @@ from .config import SvpcConfig, PAD, UNK, IGNORE
 from .synth import state_dict_spec, sinusoid_table
 from .compat import make_node as _make_node
 
+GUMBEL_SITE = 0x6b6d     # hash site of the Gumbel noise (dropout sites count from 1)
 LSTM_KEYS = tuple(f"{k}_l0{s}" for s in ("", "_reverse") for k in ("weight_ih", "weight_hh", "bias_ih", "bias_hh"))
 
 
@@ -584,7 +585,9 @@ class StateAwareRecursiveTransformer(nn.Module):
             if mode == "full":
                 noise = gumbel_noise if gumbel_noise is not None else self.gumbel_noise
                 self.gumbel_noise = None
-                if noise is None:
+                if noise is None and self.training and self._seed_t is not None:
+                    g = Fn.be().gumbel_noise(plan.P_numel, self._seed_t, GUMBEL_SITE)     # drawn on the device, per step seed
+                elif noise is None:
                     g = -torch.empty(plan.P_numel, dtype=f32, device=dev).exponential_().log()
                 else:
                     g = torch.cat([n.reshape(-1) for n in noise]).to(device=dev, dtype=f32)

@@ -485,6 +485,23 @@ def test_gumbel(cb, tb):
     close("gumbel dP", dP, rdP, 1e-4); close("gumbel demb", demb, rdemb, 1e-4)
 
 
+def test_gumbel_noise_kernel(cb):
+    """Device-drawn Gumbel(0,1) noise (what F.gumbel_softmax draws, model.py:1018): moments, reproducibility per seed."""
+    n = 1 << 20
+    seed = torch.tensor([77], dtype=torch.int32, device=DEV)
+    g = cb.gumbel_noise(n, seed, 5)
+    assert torch.isfinite(g).all()
+    assert abs(float(g.mean()) - 0.5772) < 5e-3 and abs(float(g.var()) - math.pi ** 2 / 6) < 2e-2
+    # P(g < x) = exp(-exp(-x))
+    for x in (-1.0, 0.0, 1.0, 3.0):
+        assert abs(float((g < x).float().mean()) - math.exp(-math.exp(-x))) < 3e-3
+    assert torch.equal(g, cb.gumbel_noise(n, seed, 5))
+    assert not torch.equal(g, cb.gumbel_noise(n, seed, 6))
+    assert not torch.equal(g, cb.gumbel_noise(n, seed + 1, 5))
+    big = cb.gumbel_noise(1 << 26, seed, 9)       # 64 M draws: the extreme hash values occur (u must never round to 0 or 1)
+    assert torch.isfinite(big).all() and float(big.max()) < 17.0 and float(big.min()) > -3.0
+
+
 # ---------------------------------------------------------------------------------------------- BiLSTM + losses
 @pytest.mark.parametrize("D,W", [(64, 24), (768, 300)])
 def test_bilstm(cb, tb, D, W):

@@ -355,6 +355,9 @@ class TorchBackend:
             yvals.append(y.gather(1, index).view(-1))
         return torch.stack(xs), torch.cat(idxs).int(), torch.cat(yvals)
 
+    def gumbel_noise(self, n, seed, site):
+        return -torch.empty(int(n), dtype=torch.float32, device=seed.device).exponential_().log()
+
     def gumbel_fwd(self, P, g, emb, lay, text_mask):
         x, idx, yv = self._gumbel(self.f(P), self.f(g), self.f(emb), lay, text_mask)
         return x.float(), idx, yv.detach().float()
