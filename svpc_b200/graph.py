@@ -46,6 +46,12 @@ class InputArena:
         self.host = torch.empty(self.nbytes, dtype=torch.uint8).pin_memory()
         self.stage = torch.zeros(self.nbytes, dtype=torch.uint8, device=device)
         self.static = torch.zeros(self.nbytes, dtype=torch.uint8, device=device)
+        # zero-copy feature blocks (enable_zero_copy): the step reads the clip features through a device table of
+        # pointers, so the pitched blocks are uploaded alternately into `static` and `stage` and the commit only rewrites
+        # the table (128 bytes) instead of moving ~120 MB device to device
+        self.zc_table, self.zc_tabs, self.zc_entries = None, None, ()
+        self.cur, self.up = 0, None                    # buffer (0 static / 1 stage) the table points to / of the pending upload
+        self.read_done = [None, None]                  # event after the last replay that read the features of buffer 0 / 1
 
     @classmethod
     def layout(cls, tensors, used_rows=None):
@@ -76,21 +82,61 @@ class InputArena:
             plan.append(list(sg))
         return spec, [tuple(x) for x in plan], off
 
+    def enable_zero_copy(self, table, feat_idx):
+        """``table``: the device int64 array of feature-block addresses the captured kernels read (one per tensor of
+        ``feat_idx``, indices into the arena's tensors, currently pointing into ``static``).  Enabled only when every one
+        of those tensors lies inside a pitched entry of the upload plan and no other tensor does."""
+        pitched = [k for k, (_, pitch, _, _) in enumerate(self.plan) if pitch]
+        covered = set()
+        for k in pitched:
+            o, pitch, _, h = self.plan[k]
+            covered |= {i for i, (off, _, _) in enumerate(self.spec) if o <= off < o + pitch * h}
+        if not pitched or covered != set(feat_idx) or table.numel() != len(feat_idx):
+            return False
+        offs = [self.spec[i][0] for i in feat_idx]
+        self.zc_tabs = [torch.tensor([b.data_ptr() + o for o in offs], dtype=torch.int64).to(self.device)
+                        for b in (self.static, self.stage)]
+        assert torch.equal(self.zc_tabs[0], table), "the feature table does not point into the static arena"
+        self.zc_table, self.zc_entries = table, tuple(pitched)
+        return True
+
+    def reset_zero_copy(self):
+        """Point the table back at the static arena (a synchronous ``load`` writes the static views); current stream."""
+        if self.zc_table is not None and self.cur != 0:
+            self.zc_table.copy_(self.zc_tabs[0], non_blocking=True)
+            self.cur = 0
+
+    def mark_read(self):
+        """Call after enqueueing a replay: the buffer the table points to may be overwritten only after this event."""
+        if self.zc_table is not None:
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream(self.device))
+            self.read_done[self.cur] = ev
+
     def upload(self):
-        """pinned host arena -> device staging arena on the CURRENT stream: one copy per plan entry (3 at the headline
-        configuration: ids/masks, the pitched feature block, labels/noise)."""
+        """pinned host arena -> device on the CURRENT stream: one copy per plan entry (ids/masks, the pitched feature
+        block, labels).  The feature block goes straight into the buffer the step is NOT reading (zero-copy), the rest into
+        the staging arena."""
         be = Fn.be()
         hp, dp = self.host.data_ptr(), self.stage.data_ptr()
-        for o, pitch, w, h in self.plan:
-            be.memcpy2d_h2d(dp + o, pitch or w, hp + o, pitch or w, w, h)
+        tgt = (1 - self.cur) if self.zc_table is not None else None
+        for k, (o, pitch, w, h) in enumerate(self.plan):
+            base = (self.static, self.stage)[tgt].data_ptr() if (tgt is not None and k in self.zc_entries) else dp
+            be.memcpy2d_h2d(base + o, pitch or w, hp + o, pitch or w, w, h)
+        self.up = tgt
 
     def commit(self):
-        """device staging arena -> static arena on the CURRENT stream, along the same plan as ``upload``: the rows that are
-        never uploaded are not moved either (40 MB of the 295 MB at the headline configuration)."""
+        """Make the uploaded batch the one the captured step reads, on the CURRENT stream: staging -> static along the upload
+        plan for the small pieces; the feature blocks only switch the pointer table (or, without zero-copy, move too)."""
         be = Fn.be()
         sp, dp = self.stage.data_ptr(), self.static.data_ptr()
-        for o, pitch, w, h in self.plan:
+        for k, (o, pitch, w, h) in enumerate(self.plan):
+            if self.up is not None and k in self.zc_entries:
+                continue
             be.memcpy2d_d2d(dp + o, pitch or w, sp + o, pitch or w, w, h)
+        if self.up is not None:
+            self.zc_table.copy_(self.zc_tabs[self.up], non_blocking=True)
+            self.cur, self.up = self.up, None
 
     def _views(self, buf):
         out = []
@@ -179,11 +225,18 @@ class GraphedTrainStep:
         Fn.WEIGHTS.invalidate()     # the refresh of the compute-dtype weight copies (one multi-tensor cast) is captured too
         Fn.WEIGHTS.prepare()        # ... its pointer tables are uploaded before the capture starts
         model.zero_grad(set_to_none=True)
+        feat_table = Fn.be()._feat_ptrs(self.static[1])[0] if feats else None     # built by the warm-up steps, read by the graph
         with torch.cuda.graph(self.graph):
             self.loss = self._eager(zero=False)
         torch.cuda.synchronize(dev)
         # the graph reads (GEMM operands) and rewrites (the captured weight refresh) the cached weight copies by address
         self._weight_buffers = Fn.WEIGHTS.buffers() + list(Fn.be()._w_cache.values())
+        self._feat_table = None
+        if feats and os.environ.get("SVPC_ARENA_ZEROCOPY", "1") != "0":
+            # the table of feature-block addresses the captured LN(3072) kernels read (kept alive here: the graph reads it)
+            self._feat_table = feat_table
+            if Fn.be()._feat_ptrs(self.static[1])[0] is feat_table:          # the very tensor the captured kernels were given
+                self.arena.enable_zero_copy(feat_table, [i for i, t in enumerate(flat) if id(t) in feats])
 
     def _clone(self, a):
         if isinstance(a, torch.Tensor):
@@ -209,6 +262,7 @@ class GraphedTrainStep:
 
     def load(self, args, gumbel_noise=None):
         """Copy a batch (host-pinned or device tensors) into the static buffers; asynchronous on the current stream."""
+        self.arena.reset_zero_copy()
         for dst, src in zip(self.static, args):
             if isinstance(dst, torch.Tensor):
                 dst.copy_(src, non_blocking=True)
@@ -282,13 +336,17 @@ class GraphedTrainStep:
         return _HostScalar(slot, ev, flags)
 
     def run_prefetched(self):
+        if not isinstance(self._pf.pairs, InputArena):
+            self.arena.reset_zero_copy()        # per-tensor staging lands in the static views
         self._pf.commit()
         d = self._pf_dict
         if d is not None and d is not self.static[9] and self.plan.mode != "video":
             if not self.plan.update_tokens(d):
                 raise ValueError("ingr_id_dict has a different number of copy tokens than the captured batch: re-capture")
             self.static[9] = d
-        return self.run()
+        loss = self.run()
+        self.arena.mark_read()
+        return loss
 
 
 class _HostScalar:
@@ -339,6 +397,8 @@ class _Prefetcher:
             self.stream.wait_event(self.consumed)
         else:
             self.stream.wait_stream(cur)
+        if arena.zc_table is not None and arena.read_done[1 - arena.cur] is not None:
+            self.stream.wait_event(arena.read_done[1 - arena.cur])      # the last replay that read the target feature buffer
         with torch.cuda.stream(self.stream):
             arena.upload()
             self.staged.record(self.stream)

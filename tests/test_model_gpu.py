@@ -184,9 +184,16 @@ def test_prefetch_pipeline_matches_load():
         for f in a_args[1]:
             f[:, cfg.max_v_len:] = float("nan")      # text rows of the feature blocks: never uploaded, never read
         assert step.arena.h2d_nbytes < step.arena.nbytes
+        assert step.arena.zc_table is not None       # feature blocks: uploaded into alternating buffers, table switched
+        before = step.arena.cur
         step.prefetch(a_args, a_noise)
         v = float(step.run_prefetched())
+        assert step.arena.cur == 1 - before
         assert abs(v - want[which]) <= 1e-6 * abs(want[which]), (which, v, want)
+    # a synchronous load() after the pipeline writes the static arena: the table must point back at it
+    step.load(*hosts[1])
+    assert abs(float(step.run()) - want[1]) <= 1e-6 * abs(want[1])
+    assert step.arena.cur == 0
 
 
 def test_graph_survives_optimizer_step_and_decode():
