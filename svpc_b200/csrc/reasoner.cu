@@ -220,6 +220,7 @@ __global__ void __launch_bounds__(RS_THREADS) reasoner_bwd_kernel(
 // shared memory instead of being block-reduced, and a thread OWNS a column d of the entity matrix through the
 // column-wise phases, so a step needs two block barriers.
 // ------------------------------------------------------------------------------------------------
+#define RS_MAXSTEPS 64      // steps of a video whose per-step scalars the pipelined kernels keep in shared memory
 __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
 }
@@ -252,18 +253,26 @@ __global__ void __launch_bounds__(RS_THREADS) reasoner_fwd_pipe_kernel(int D, in
   stage_async(E, E0 + (long long)g0 * D, ni * D);
   stage_async(wb, w2v + (long long)n0 * D, (n1 - n0) * D);
   cp_async_commit();
+  // per-step scalars of the whole video up front (a global load inside the step loop is an exposed L2 round trip per step)
+  __shared__ float s_cl[3 * RS_MAXSTEPS], s_w4[RS_MAXSTEPS];
+  __shared__ int s_eo[RS_MAXSTEPS];
+  for (int k = threadIdx.x; k < min(n1 - n0, RS_MAXSTEPS); k += RS_THREADS) {
+    s_cl[3 * k] = clog[3 * (n0 + k)]; s_cl[3 * k + 1] = clog[3 * (n0 + k) + 1]; s_cl[3 * k + 2] = clog[3 * (n0 + k) + 2];
+    s_w4[k] = w4s[n0 + k];
+    s_eo[k] = clip_ent_off[n0 + k];
+  }
   for (int i = threadIdx.x; i < 2 * max_ni; i += RS_THREADS) eb[i] = 0.f;
   cp_async_wait_all();
   __syncthreads();
   for (int n = n0; n < n1; ++n) {
-    const int cur = (n - n0) & 1;
+    const int cur = (n - n0) & 1, k = n - n0;
     const float* w = wb + (size_t)(n - n0) * D;
     float* e = eb + cur * max_ni;
     const float* ep = eb + (cur ^ 1) * max_ni;
-    // scalars of this step: issued now, consumed after the barrier
-    const float l0 = clog[3 * n], l1 = clog[3 * n + 1], l2 = clog[3 * n + 2];
-    const float w4 = w4s[n];
-    const long long eo = clip_ent_off[n];
+    const bool st = k < RS_MAXSTEPS;
+    const float l0 = st ? s_cl[3 * k] : clog[3 * n], l1 = st ? s_cl[3 * k + 1] : clog[3 * n + 1], l2 = st ? s_cl[3 * k + 2] : clog[3 * n + 2];
+    const float w4 = st ? s_w4[k] : w4s[n];
+    const long long eo = st ? s_eo[k] : clip_ent_off[n];
     // (1) e_i = sigmoid(E_i . w): one warp per entity row
     for (int i = warp; i < ni; i += RS_THREADS / 32) {
       float s = 0.f;
@@ -278,6 +287,7 @@ __global__ void __launch_bounds__(RS_THREADS) reasoner_fwd_pipe_kernel(int D, in
     const float c0 = x0 / (x0 + x1 + x2), c1 = x1 / (x0 + x1 + x2);
     float asum = 0.f;
     for (int i = 0; i < ni; ++i) asum += c0 * e[i] + c1 * ep[i];
+    const float inv_asum = 1.f / asum;
     if (threadIdx.x < ni) {
       const int i = threadIdx.x;
       ent[eo + i] = e[i];
@@ -286,7 +296,7 @@ __global__ void __launch_bounds__(RS_THREADS) reasoner_fwd_pipe_kernel(int D, in
     // (3) the thread that owns column d: ebar_d, k_d, and the update of E[:, d]
     for (int d = threadIdx.x; d < D; d += RS_THREADS) {
       float s = 0.f;
-      for (int i = 0; i < ni; ++i) s = fmaf((c0 * e[i] + c1 * ep[i]) / asum, E[i * D + d], s);
+      for (int i = 0; i < ni; ++i) s = fmaf((c0 * e[i] + c1 * ep[i]) * inv_asum, E[i * D + d], s);
       ebar_out[(long long)n * D + d] = s;
       const float kk = w4 * s;
       const float kd = kk > 0.f ? kk : 0.f;
@@ -330,10 +340,15 @@ __global__ void __launch_bounds__(RS_THREADS) reasoner_bwd_pipe_kernel(
     for (int i = threadIdx.x; i < ni * D; i += RS_THREADS) dE0[(long long)g0 * D + i] = 0.f;
     return;
   }
+  // entity-row offsets of the video's steps up front: the staging addresses of every step depend on them
+  __shared__ int s_eo[RS_MAXSTEPS];
+  for (int k = threadIdx.x; k < min(n1 - n0, RS_MAXSTEPS); k += RS_THREADS) s_eo[k] = clip_ent_off[n0 + k];
+  __syncthreads();
+  auto eo_of = [&](int n) -> long long { return (n - n0 < RS_MAXSTEPS) ? s_eo[n - n0] : clip_ent_off[n]; };
   auto stage_step = [&](int n, int buf) {
-    const float* Eprev = (n == n0) ? E0 + (long long)g0 * D : Es + (long long)clip_ent_off[n - 1] * D;
+    const float* Eprev = (n == n0) ? E0 + (long long)g0 * D : Es + eo_of(n - 1) * D;
     stage_async(Epb + buf * ND, Eprev, ni * D);
-    stage_async(dEsb + buf * ND, d_Es + (long long)clip_ent_off[n] * D, ni * D);
+    stage_async(dEsb + buf * ND, d_Es + eo_of(n) * D, ni * D);
     stage_async(vecb + buf * 3 * D, ebar + (long long)n * D, D);
     stage_async(vecb + buf * 3 * D + D, d_ebar + (long long)n * D, D);
     stage_async(vecb + buf * 3 * D + 2 * D, w2v + (long long)n * D, D);
@@ -342,10 +357,10 @@ __global__ void __launch_bounds__(RS_THREADS) reasoner_bwd_pipe_kernel(
   float r_a = 0.f, r_e = 0.f, r_ep = 0.f, r_de = 0.f;
   auto load_small = [&](int n) {
     if ((int)threadIdx.x < ni) {
-      const long long eo = clip_ent_off[n];
+      const long long eo = eo_of(n);
       r_a = a_saved[eo + threadIdx.x];
       r_e = ent[eo + threadIdx.x];
-      r_ep = (n == n0) ? 0.f : ent[clip_ent_off[n - 1] + threadIdx.x];
+      r_ep = (n == n0) ? 0.f : ent[eo_of(n - 1) + threadIdx.x];
       r_de = d_ent[eo + threadIdx.x];
     }
   };
@@ -423,12 +438,13 @@ __global__ void __launch_bounds__(RS_THREADS) reasoner_bwd_pipe_kernel(
     const float c0 = x0 / (x0 + x1 + x2), c1 = x1 / (x0 + x1 + x2), c2 = x2 / (x0 + x1 + x2);
     float asum = 0.f;
     for (int i = 0; i < ni; ++i) asum += av[i];
+    const float inv_asum = 1.f / asum;
     float tdot = 0.f;
-    for (int i = 0; i < ni; ++i) tdot = fmaf(dan[i], av[i] / asum, tdot);
+    for (int i = 0; i < ni; ++i) tdot = fmaf(dan[i], av[i] * inv_asum, tdot);
     if (threadIdx.x == 0) {
       float p0 = 0.f, p1 = 0.f, t4 = 0.f;
       for (int i = 0; i < ni; ++i) {
-        const float dai = da[i] + (dan[i] - tdot) / asum;
+        const float dai = da[i] + (dan[i] - tdot) * inv_asum;
         p0 = fmaf(dai, ev[i], p0);
         p1 = fmaf(dai, epv[i], p1);
       }
@@ -441,7 +457,7 @@ __global__ void __launch_bounds__(RS_THREADS) reasoner_bwd_pipe_kernel(
     }
     if ((int)threadIdx.x < ni) {
       const int i = threadIdx.x;
-      den_out[i] = c1 * (da[i] + (dan[i] - tdot) / asum);      // read by step n - 1 (other buffer: no hazard with den_in)
+      den_out[i] = c1 * (da[i] + (dan[i] - tdot) * inv_asum);   // read by step n - 1 (other buffer: no hazard with den_in)
     }
     // (D) column owner: dw2v_d = sum_i dz_i Ep[i][d]; dE_prev[:, d] = (1 - a_i) dE + an_i d ebar_d + dz_i w_d
     for (int d = threadIdx.x; d < D; d += RS_THREADS) {
@@ -449,11 +465,11 @@ __global__ void __launch_bounds__(RS_THREADS) reasoner_bwd_pipe_kernel(
       float s = 0.f;
       for (int i = 0; i < ni; ++i) {
         const float ai = av[i], ei = ev[i];
-        const float dai = da[i] + (dan[i] - tdot) / asum;
+        const float dai = da[i] + (dan[i] - tdot) * inv_asum;
         const float dei = c0 * dai + dev_[i] + den_in[i];
         const float dzi = dei * ei * (1.f - ei);
         s = fmaf(dzi, Ep[i * D + d], s);
-        dE[i * D + d] = (1.f - ai) * dE[i * D + d] + (ai / asum) * debd + dzi * wd;
+        dE[i * D + d] = (1.f - ai) * dE[i * D + d] + (ai * inv_asum) * debd + dzi * wd;
       }
       dw2v[(long long)n * D + d] = s;
     }

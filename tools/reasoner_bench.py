@@ -41,7 +41,7 @@ def graph_time(fn, reps=50):
     return e0.elapsed_time(e1) / reps * 1e3
 
 
-out = {"mode": os.environ.get("SVPC_REASONER_PIPE", "2"),
+out = {"mode": os.environ.get("SVPC_REASONER_PIPE", "1"),
        "fwd_us": round(graph_time(lambda: cb.reasoner_fwd(E0, lay, w2v, clog, w4s)), 1),
        "bwd_us": round(graph_time(lambda: cb.reasoner_bwd(d_ent, d_ebar, d_Es, E0, lay, w2v, clog, w4s, ent, ebar, Es, saved)), 1)}
 print(json.dumps(out))
