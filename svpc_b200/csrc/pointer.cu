@@ -545,7 +545,29 @@ __global__ void __launch_bounds__(PG_THREADS) pointer_bwd_reduce_kernel(
     beta[i] = b;
   }
   __syncthreads();
-  for (int d = threadIdx.x; d < D; d += PG_THREADS) {
+  if (ni <= 16) {          // usual case: every ingredient's sum in registers, ONE pass over the clip's decoder rows
+    for (int d = blockIdx.y * PG_THREADS + threadIdx.x; d < D; d += gridDim.y * PG_THREADS) {
+      const float w2 = wpgen[D + d];
+      float a[16];
+#pragma unroll
+      for (int k = 0; k < 16; ++k) a[k] = 0.f;
+#pragma unroll 5
+      for (int l = 0; l < Lt; ++l) {
+        const float x = ldf(dec + ((long long)n * Lt + l) * D + d);
+#pragma unroll
+        for (int k = 0; k < 16; ++k)
+          if (k < ni) a[k] = fmaf(dsc[l * max_ni + k], x, a[k]);
+      }
+#pragma unroll
+      for (int k = 0; k < 16; ++k)
+        if (k < ni) {
+          atomicAdd(dG + (long long)(src + k) * D + d, a[k]);
+          atomicAdd(dE + (long long)(src + k) * D + d, beta[k] * w2);
+        }
+    }
+    return;
+  }
+  for (int d = blockIdx.y * PG_THREADS + threadIdx.x; d < D; d += gridDim.y * PG_THREADS) {
     const float w2 = wpgen[D + d];
     for (int i0 = 0; i0 < ni; i0 += 4) {        // 4 ingredients per pass over the clip's decoder rows
       float a[4] = {0.f, 0.f, 0.f, 0.f};
@@ -628,7 +650,7 @@ extern "C" int svpc_pointer_bwd(int n_clips, int Lt, int D, int V, int max_ni, i
           tok_ids, wpgen, logits, ldl, labels, smoothing, P, alpha, pgen, dP, dloss, (T*)ddec, du, dlogits, dscore_ws);
     }
     cudaFuncSetAttribute(pointer_bwd_reduce_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
-    svpc_launch(pointer_bwd_reduce_kernel<T>, n_clips, PG_THREADS, smem2, st, Lt, D, max_ni, (const T*)dec, clip_src_off, clip_ni,
+    svpc_launch(pointer_bwd_reduce_kernel<T>, dim3(n_clips, svpc_cdiv(D, PG_THREADS)), PG_THREADS, smem2, st, Lt, D, max_ni, (const T*)dec, clip_src_off, clip_ni,
                                                                    wpgen, alpha, du, dscore_ws, dG, dE);
   });
   int rc = svpc_check_launch("pointer_bwd");
@@ -780,6 +802,82 @@ __global__ void __launch_bounds__(PG_THREADS) gumbel_fwd_kernel(int Lt, int V, c
   if (threadIdx.x == 0) { idx_out[r] = best; yval_out[r] = yv; }
 }
 
+// Training shapes: one WARP per (clip, text position) row, eight rows per CTA.  The per-row CTA above keeps 8 rows in flight
+// per SM and pays three dependent L2 round trips plus two block barriers per row; here 64 rows are in flight per SM, the row
+// is read eight columns per lane at a time, and the reductions are warp shuffles.
+__global__ void __launch_bounds__(PG_THREADS) gumbel_fwd_rows_kernel(int n_rows, int Lt, int V, const float* __restrict__ P,
+                                                                     const float* __restrict__ g,
+                                                                     const int* __restrict__ clip_P_off,
+                                                                     const int* __restrict__ clip_vx, float tau,
+                                                                     int* __restrict__ idx_out, float* __restrict__ yval_out) {
+  svpc_pdl_sync();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int r = blockIdx.x * (PG_THREADS / 32) + warp;
+  if (r >= n_rows) return;
+  const int n = r / Lt, l = r - n * Lt, vx = clip_vx[n];
+  const long long poff = clip_P_off[n];
+  const float* prow = P + poff + (long long)l * vx;
+  const float* grow = g + poff + (long long)l * vx;
+  float mx = -INFINITY;
+  int best = 0x7fffffff;
+  float se = 0.f;
+  if (vx <= 32 * PR_NV) {
+    // the whole row in registers: every load of the row is issued at once, log / scale computed once per element (the
+    // kernel is bound by its instruction count, not by memory: ~35 instead of ~70 instructions per element)
+    float z[PR_NV];
+#pragma unroll
+    for (int k0 = 0; k0 < PR_NV; k0 += 8) {
+      float pv[8], gv[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int v = lane + 32 * (k0 + u);
+        pv[u] = v < vx ? prow[v] : 1.f;
+        gv[u] = v < vx ? grow[v] : 0.f;
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int v = lane + 32 * (k0 + u);
+        z[k0 + u] = v < vx ? (logf(pv[u] + 1e-12f) + gv[u]) / tau : -INFINITY;     // same expression as the reference's
+        if (z[k0 + u] > mx) { mx = z[k0 + u]; best = v; }
+      }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+      const float om = __shfl_xor_sync(0xffffffffu, mx, o);
+      const int ob = __shfl_xor_sync(0xffffffffu, best, o);
+      if (om > mx || (om == mx && ob < best)) { mx = om; best = ob; }
+    }
+#pragma unroll
+    for (int k2 = 0; k2 < PR_NV; ++k2) se += expf(z[k2] - mx);        // exp(-inf) = 0 for the padding
+  } else {
+    for (int v0 = lane; v0 < vx; v0 += 256) {
+      float pv[8], gv[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int v = v0 + 32 * u;
+        pv[u] = v < vx ? prow[v] : 1.f;
+        gv[u] = v < vx ? grow[v] : 0.f;
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int v = v0 + 32 * u;
+        const float zz = (logf(pv[u] + 1e-12f) + gv[u]) / tau;
+        if (v < vx && zz > mx) { mx = zz; best = v; }
+      }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+      const float om = __shfl_xor_sync(0xffffffffu, mx, o);
+      const int ob = __shfl_xor_sync(0xffffffffu, best, o);
+      if (om > mx || (om == mx && ob < best)) { mx = om; best = ob; }
+    }
+    for (int v = lane; v < vx; v += 32) se += expf((logf(prow[v] + 1e-12f) + grow[v]) / tau - mx);
+  }
+  if (best >= vx) best = 0;          // a row of NaNs compares false everywhere: never hand out an index outside the row
+  se = warp_sum(se);
+  const float y = 1.0f / se;                 // y_soft at its argmax
+  const float yv = (1.0f - y) + y;           // y_hard - y_soft.detach() + y_soft
+  if (lane == 0) { idx_out[r] = best; yval_out[r] = yv; }
+}
+
 // One CTA per clip: masked mean over the text positions of yv * Emb[argmax] (positions in order, as the reference sums)
 __global__ void __launch_bounds__(PG_THREADS) gumbel_mean_kernel(int Lt, int V, int W, const float* __restrict__ emb,
                                                                  const float* __restrict__ text_mask,
@@ -818,6 +916,137 @@ __global__ void __launch_bounds__(PG_THREADS) gumbel_tv_kernel(int V, int W, con
     for (int w = lane; w < W; w += 32) s = fmaf(e[w], dxm[w], s);
     s = warp_sum(s);
     if (lane == 0) tv[(long long)n * V + v] = s;
+  }
+}
+
+// tv[n][v] = Emb[v] . dxmean[n] for training shapes: a CTA owns 32 clips (one per LANE, their dxmean rows in shared memory
+// with an odd pitch) and TV_VPB vocabulary entries (their Emb rows in shared memory too); a warp reads one Emb row as
+// broadcast 16-byte reads and every lane
+// accumulates its own clip's dot product - each Emb row is read once per 32 clips instead of once per clip, and there is no
+// shuffle reduction.
+#define TV_CLIPS 32
+#define TV_VPB 40
+__global__ void __launch_bounds__(PG_THREADS) gumbel_tv_clips_kernel(int n_clips, int V, int W, const float* __restrict__ emb,
+                                                                     const float* __restrict__ dxmean, float* __restrict__ tv) {
+  svpc_pdl_sync();
+  extern __shared__ __align__(16) float dxm[];   // TV_CLIPS x (W + 1), then the CTA's Emb rows
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int c0 = blockIdx.y * TV_CLIPS, pitch = W + 1;
+  float* semb = dxm + (((size_t)TV_CLIPS * pitch + 3) & ~(size_t)3);      // TV_VPB x W (W % 4 == 0), 16-byte aligned rows
+  for (int i = threadIdx.x; i < TV_CLIPS * W; i += PG_THREADS) {
+    const int c = i / W, w = i - c * W;
+    dxm[c * pitch + w] = c0 + c < n_clips ? dxmean[(long long)(c0 + c) * W + w] : 0.f;
+  }
+  {   // this CTA's Emb rows: contiguous in global memory, copied with every thread's loads in flight
+    const int v0 = blockIdx.x * TV_VPB, nv = min(V - v0, TV_VPB);
+    const float4* src = reinterpret_cast<const float4*>(emb + (long long)v0 * W);
+    float4* dst = reinterpret_cast<float4*>(semb);
+    for (int i = threadIdx.x; i < nv * W / 4; i += PG_THREADS) dst[i] = __ldg(src + i);
+  }
+  __syncthreads();
+  const float* mine = dxm + lane * pitch;
+  const int vbeg = blockIdx.x * TV_VPB, vend = min(V, vbeg + TV_VPB);
+  for (int v = vbeg + warp; v < vend; v += PG_THREADS / 32) {
+    const float* e = semb + (size_t)(v - vbeg) * W;
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+    for (int w = 0; w < W; w += 4) {
+      const float4 ev = *reinterpret_cast<const float4*>(e + w);          // broadcast read
+      s0 = fmaf(ev.x, mine[w], s0); s1 = fmaf(ev.y, mine[w + 1], s1);
+      s2 = fmaf(ev.z, mine[w + 2], s2); s3 = fmaf(ev.w, mine[w + 3], s3);
+    }
+    if (c0 + lane < n_clips) tv[(long long)(c0 + lane) * V + v] = (s0 + s1) + (s2 + s3);
+  }
+}
+
+// Backward, one warp per (clip, text position) row (see gumbel_fwd_rows_kernel)
+__global__ void __launch_bounds__(PG_THREADS) gumbel_bwd_rows_kernel(int n_rows, int Lt, int V, int W, const float* __restrict__ P,
+                                                                     const float* __restrict__ g,
+                                                                     const int* __restrict__ clip_P_off,
+                                                                     const int* __restrict__ clip_vx, float tau,
+                                                                     const float* __restrict__ text_mask,
+                                                                     const int* __restrict__ idx_in,
+                                                                     const float* __restrict__ yval_in,
+                                                                     const float* __restrict__ dxmean,
+                                                                     const float* __restrict__ tv_all, float* __restrict__ dP,
+                                                                     float* __restrict__ demb) {
+  svpc_pdl_sync();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int r = blockIdx.x * (PG_THREADS / 32) + warp;
+  if (r >= n_rows) return;
+  const int n = r / Lt, l = r - n * Lt, vx = clip_vx[n];
+  const long long poff = clip_P_off[n];
+  const float* prow = P + poff + (long long)l * vx;
+  const float* grow = g + poff + (long long)l * vx;
+  const float* tv = tv_all + (long long)n * V;
+  float* drow = dP + poff + (long long)l * vx;
+  const float msk = text_mask[r];
+  const int best = idx_in[r];
+  float cnt = 0.f;
+  for (int k = lane; k < Lt; k += 32) cnt += (text_mask[(long long)n * Lt + k] == 1.0f) ? 1.f : 0.f;
+  cnt = warp_sum(cnt);
+  if (msk != 1.0f) {
+    for (int v = lane; v < vx; v += 32) drow[v] = 0.f;
+    return;
+  }
+  const float mx = (logf(prow[best] + 1e-12f) + grow[best]) / tau;
+  const float inv_cnt = 1.f / cnt, inv_tau = 1.f / tau;
+  float se = 0.f, sd = 0.f;
+  if (vx <= 32 * PR_NV) {
+    // the row's e = exp(z - max) and P in registers: one log / exp per element instead of two (instruction-bound kernel)
+    float ev[PR_NV], pc[PR_NV];
+#pragma unroll
+    for (int k0 = 0; k0 < PR_NV; k0 += 8) {
+      float gv[8], tvv[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int v = lane + 32 * (k0 + u);
+        pc[k0 + u] = v < vx ? prow[v] : 1.f;
+        gv[u] = v < vx ? grow[v] : 0.f;
+        tvv[u] = v < V ? tv[v] : 0.f;
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int v = lane + 32 * (k0 + u);
+        const float e = v < vx ? expf((logf(pc[k0 + u] + 1e-12f) + gv[u]) / tau - mx) : 0.f;
+        ev[k0 + u] = e;
+        se += e;
+        sd = fmaf(e, tvv[u], sd);
+      }
+    }
+    se = warp_sum(se);
+    sd = warp_sum(sd);
+    const float inv = 1.f / se;
+    const float sdot = sd * inv * inv_cnt;              // sum_v y_v dy_v
+#pragma unroll
+    for (int k0 = 0; k0 < PR_NV; k0 += 8) {
+      float tvv[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) tvv[u] = lane + 32 * (k0 + u) < V ? tv[lane + 32 * (k0 + u)] : 0.f;
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int v = lane + 32 * (k0 + u);
+        if (v < vx) drow[v] = ev[k0 + u] * inv * (tvv[u] * inv_cnt - sdot) * inv_tau / (pc[k0 + u] + 1e-12f);
+      }
+    }
+  } else {
+    for (int v = lane; v < vx; v += 32) {
+      const float e = expf((logf(prow[v] + 1e-12f) + grow[v]) / tau - mx);
+      se += e;
+      if (v < V) sd = fmaf(e, tv[v], sd);
+    }
+    se = warp_sum(se);
+    sd = warp_sum(sd);
+    const float inv = 1.f / se;
+    const float sdot = sd * inv * inv_cnt;
+    for (int v = lane; v < vx; v += 32) {
+      const float y = expf((logf(prow[v] + 1e-12f) + grow[v]) / tau - mx) * inv;
+      const float dy = v < V ? tv[v] * inv_cnt : 0.f;
+      drow[v] = y * (dy - sdot) * inv_tau / (prow[v] + 1e-12f);
+    }
+  }
+  if (best < V) {
+    const float c = yval_in[r] / cnt;
+    for (int w = lane; w < W; w += 32) atomicAdd(demb + (long long)best * W + w, c * dxmean[(long long)n * W + w]);
   }
 }
 
@@ -901,7 +1130,12 @@ extern "C" int svpc_gumbel_fwd(int n_clips, int Lt, int V, int W, const float* P
                                int* idx, float* yval, svpc_stream_t stream) {
   if (n_clips <= 0) return SVPC_OK;
   cudaStream_t st = (cudaStream_t)stream;
-  svpc_launch(gumbel_fwd_kernel, dim3(Lt, n_clips), PG_THREADS, 0, st, Lt, V, P, g, clip_P_off, clip_vx, tau, idx, yval);
+  const int n_rows = n_clips * Lt;
+  if (ptr_rows_route(Lt, n_clips, V))
+    svpc_launch(gumbel_fwd_rows_kernel, svpc_cdiv(n_rows, PG_THREADS / 32), PG_THREADS, 0, st, n_rows, Lt, V, P, g, clip_P_off, clip_vx,
+                tau, idx, yval);
+  else
+    svpc_launch(gumbel_fwd_kernel, dim3(Lt, n_clips), PG_THREADS, 0, st, Lt, V, P, g, clip_P_off, clip_vx, tau, idx, yval);
   int rc = svpc_check_launch("gumbel_fwd");
   if (rc) return rc;
   svpc_launch(gumbel_mean_kernel, n_clips, PG_THREADS, 0, st, Lt, V, W, emb, text_mask, idx, yval, xmean);
@@ -916,10 +1150,23 @@ extern "C" int svpc_gumbel_bwd(int n_clips, int Lt, int V, int W, const float* P
   cudaMemsetAsync(demb, 0, sizeof(float) * (size_t)V * W, st);
   if (n_clips <= 0) return SVPC_OK;
   SVPC_REQUIRE(tv_ws != nullptr, "gumbel_bwd: tv_ws (n_clips * V floats) is required");
-  svpc_launch(gumbel_tv_kernel, dim3(svpc_cdiv(V, 64), n_clips), PG_THREADS, sizeof(float) * (size_t)W, st, V, W, emb, dxmean, tv_ws);
+  const bool rows = ptr_rows_route(Lt, n_clips, V);
+  const size_t smem_tv = sizeof(float) * (TV_CLIPS * ((size_t)W + 1) + 4 + (size_t)TV_VPB * W);
+  const bool tv_clips = rows && smem_tv <= 160 * 1024 && W % 4 == 0 && (((uintptr_t)emb) & 15) == 0;
+  if (tv_clips) cudaFuncSetAttribute(gumbel_tv_clips_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_tv);
+  if (tv_clips)
+    svpc_launch(gumbel_tv_clips_kernel, dim3(svpc_cdiv(V, TV_VPB), svpc_cdiv(n_clips, TV_CLIPS)), PG_THREADS, smem_tv, st, n_clips, V, W,
+                emb, dxmean, tv_ws);
+  else
+    svpc_launch(gumbel_tv_kernel, dim3(svpc_cdiv(V, 64), n_clips), PG_THREADS, sizeof(float) * (size_t)W, st, V, W, emb, dxmean, tv_ws);
   int rc = svpc_check_launch("gumbel_tv");
   if (rc) return rc;
-  svpc_launch(gumbel_bwd_kernel, dim3(Lt, n_clips), PG_THREADS, 0, st, Lt, V, W, P, g, clip_P_off, clip_vx, tau, text_mask, idx, yval,
-                                                             dxmean, tv_ws, dP, demb);
+  const int n_rows = n_clips * Lt;
+  if (rows)
+    svpc_launch(gumbel_bwd_rows_kernel, svpc_cdiv(n_rows, PG_THREADS / 32), PG_THREADS, 0, st, n_rows, Lt, V, W, P, g, clip_P_off,
+                clip_vx, tau, text_mask, idx, yval, dxmean, tv_ws, dP, demb);
+  else
+    svpc_launch(gumbel_bwd_kernel, dim3(Lt, n_clips), PG_THREADS, 0, st, Lt, V, W, P, g, clip_P_off, clip_vx, tau, text_mask, idx, yval,
+                dxmean, tv_ws, dP, demb);
   return svpc_check_launch("gumbel_bwd");
 }

@@ -467,8 +467,9 @@ def test_softmax_ls(cb, tb):
               tb.softmax_ls_bwd(dp, dloss, logits, labels, V, 0.1, rP), 1e-4)
 
 
-def test_gumbel(cb, tb):
-    lay, dec, G, E, w, bb, logits, P_numel, Nc, Lt, V = _pointer_case(F32, False)
+@pytest.mark.parametrize("big", [False, True])
+def test_gumbel(cb, tb, big):
+    lay, dec, G, E, w, bb, logits, P_numel, Nc, Lt, V = _pointer_case(F32, False, big)
     P, _, _ = cb.pointer_fwd(dec, G, E, w, bb, logits, lay)
     g = -torch.log(torch.empty(P_numel).exponential_(generator=torch.Generator().manual_seed(3))).to(DEV)
     emb = rnd(V, 24, scale=0.4, seed=8)
