@@ -68,6 +68,7 @@ def parse():
     ap.add_argument("--ragged", action="store_true", help="headline step on the ragged batch of SURVEY 8d (train task)")
     ap.add_argument("--fp32-features", action="store_true",
                     help="bf16 path: keep the clip features fp32 in the input arena (default: the loader hands them over as bf16)")
+    ap.add_argument("--trace", default=None, help="diagnostic: write the kernel timeline of 3 replays (start us, end us, name) to this file")
     ap.add_argument("--inject-noise", action="store_true",
                     help="upload the Gumbel noise of the re-simulator with the batch instead of drawing it on the device")
     ap.add_argument("--verify-ddp", action="store_true",
@@ -619,6 +620,24 @@ def main():
         loss = tb.run()
     torch.cuda.synchronize()
     assert torch.isfinite(loss).all(), "non-finite loss"
+
+    if args.trace:
+        # diagnostic: kernel timeline of 3 replays through the torch profiler (CUPTI), summarised per stream on rank 0
+        from torch.profiler import profile, ProfilerActivity
+        if world > 1:
+            dist.barrier()
+        with profile(activities=[ProfilerActivity.CUDA]) as prof:
+            for _ in range(3):
+                tb.run()
+            torch.cuda.synchronize()
+        if rank == 0:
+            ev = [e for e in prof.events() if e.device_type.name == "CUDA" or "cuda" in str(e.device_type).lower()]
+            rows = sorted(((e.time_range.start, e.time_range.end, e.name) for e in ev), key=lambda r: r[0])
+            with open(args.trace, "w") as f:
+                for a, b, n in rows:
+                    f.write(f"{a:.3f}\t{b:.3f}\t{n}\n")
+            print(json.dumps({"trace": args.trace, "events": len(rows)}))
+        return finish(world)
 
     # ---- parity of the timed model: eval-mode loss on the timed batch against the CPU oracle (rank 0)
     parity = None

@@ -11,7 +11,7 @@ import os
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libsvpc_b200.so")
+LIB_PATH = os.environ.get("SVPC_LIB_PATH") or os.path.join(_HERE, "libsvpc_b200.so")     # (override: A/B runs of two builds)
 
 F32, BF16 = 0, 1
 _DT = {torch.float32: F32, torch.bfloat16: BF16}

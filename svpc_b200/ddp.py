@@ -80,6 +80,11 @@ class GradAllReducer:
         self._work = []
         self._handed = set()                             # slots given to a weight-gradient GEMM in the current backward pass
         self._comm = {}                                  # device -> communication stream
+        # parameters that get no gradient in the current model mode (dead reference parameters, modules a mode does not
+        # run): learned from the first backward pass (agreed between the ranks) - a bucket that holds one is then launched
+        # as soon as its LIVE parameters are ready instead of at finish(), where its all-reduce overlaps nothing
+        self._absent = None
+        self._need = [len(b) for b in self.buckets]
         self._hooks = [p.register_post_accumulate_grad_hook(self._on_grad) for p in self.params]
         self.enabled = dist.is_available() and dist.is_initialized() and dist.get_world_size(self.group) > 1
         if self.enabled:
@@ -119,9 +124,12 @@ class GradAllReducer:
         if not self.enabled:
             return
         bi = self.bucket_of[p]
+        if self._absent is not None and p in self._absent:
+            raise RuntimeError("GradAllReducer: a parameter that had no gradient in the first backward pass got one now "
+                               "(the set of live parameters changed, e.g. another model mode): call reset_absent() first")
         self._ready[bi].add(p)
-        if not self._launched[bi] and len(self._ready[bi]) == len(self.buckets[bi]):
-            self._launch(bi, self.buckets[bi])
+        if not self._launched[bi] and len(self._ready[bi]) == self._need[bi]:
+            self._launch(bi, [q for q in self.buckets[bi] if q in self._ready[bi]])
 
     def _launch(self, bi, params):
         self._launched[bi] = True
@@ -165,6 +173,8 @@ class GradAllReducer:
         for bi, b in enumerate(self.buckets):
             if not self._launched[bi]:
                 self._launch(bi, [p for p in b if p in self._ready[bi]])
+        if self._absent is None:
+            self._learn_absent()
         for dev, cs in self._comm.items():
             torch.cuda.current_stream(dev).wait_stream(cs)
         for h, params in self._work:
@@ -175,6 +185,20 @@ class GradAllReducer:
         self._handed = set()
         self._ready = [set() for _ in self.buckets]
         self._launched = [False] * len(self.buckets)
+
+    def _learn_absent(self):
+        """After the first backward pass: the parameters without a gradient ON EVERY RANK (one small MAX all-reduce)."""
+        dev = self.params[0].device
+        has = torch.tensor([1 if p in self._ready[self.bucket_of[p]] else 0 for p in self.params], dtype=torch.int32, device=dev)
+        dist.all_reduce(has, op=dist.ReduceOp.MAX, group=self.group)
+        has = has.cpu().tolist()
+        self._absent = {p for p, h in zip(self.params, has) if not h}
+        self._need = [sum(1 for p in b if p not in self._absent) for b in self.buckets]
+
+    def reset_absent(self):
+        """Forget which parameters get no gradient (call when the model mode or the set of trained modules changes)."""
+        self._absent = None
+        self._need = [len(b) for b in self.buckets]
 
     def remove(self):
         for h in self._hooks:

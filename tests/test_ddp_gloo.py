@@ -63,10 +63,19 @@ def _worker(rank, world, port, mode, out_path):
         red = GradAllReducer(m, bucket_bytes=1 << 16)
         assert red.enabled and len(red.buckets) > 1
         mine = _slice_batch(full, [b for b in range(4) if b % world == rank])
-        m.zero_grad(set_to_none=True)
-        loss = m(*forward_args(mine), gumbel_noise=mine["gumbel"])[0]
-        loss.backward()
-        red.finish()
+        # two iterations: the first one learns which parameters get no gradient in this mode; in the second every bucket
+        # with a live parameter must have been launched from the hooks, before finish()
+        for it in range(2):
+            m.zero_grad(set_to_none=True)
+            loss = m(*forward_args(mine), gumbel_noise=mine["gumbel"])[0]
+            loss.backward()
+            if it == 1:
+                assert red._absent is not None and all(l or n == 0 for l, n in zip(red._launched, red._need)), \
+                    (red._launched, red._need)
+                if mode == "video":
+                    assert len(red._absent) > 0
+            red.finish()
+            assert all(p.grad is None for p in red._absent)
         tot = loss.detach().clone()
         dist.all_reduce(tot)
         if rank == 0:
