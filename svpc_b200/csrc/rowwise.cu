@@ -109,6 +109,25 @@ __device__ __forceinline__ void ld8(const bf16* p, float (&v)[8]) {
 #pragma unroll
   for (int i = 0; i < 4; ++i) { v[2 * i] = __low2float(h[i]); v[2 * i + 1] = __high2float(h[i]); }
 }
+// raw 8-element vectors: the load is issued without touching its result (a conversion right behind the load makes the thread
+// wait there, before its other loads are even issued); cvt8 unpacks later
+struct Raw8f { float4 a, b; };
+struct Raw8h { uint4 u; };
+__device__ __forceinline__ void ldraw8(const float* p, Raw8f& r) {
+  r.a = *reinterpret_cast<const float4*>(p); r.b = *reinterpret_cast<const float4*>(p + 4);
+}
+__device__ __forceinline__ void ldraw8(const bf16* p, Raw8h& r) { r.u = *reinterpret_cast<const uint4*>(p); }
+__device__ __forceinline__ void cvt8(const Raw8f& r, float (&v)[8]) {
+  v[0] = r.a.x; v[1] = r.a.y; v[2] = r.a.z; v[3] = r.a.w; v[4] = r.b.x; v[5] = r.b.y; v[6] = r.b.z; v[7] = r.b.w;
+}
+__device__ __forceinline__ void cvt8(const Raw8h& r, float (&v)[8]) {
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&r.u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) { v[2 * i] = __low2float(h[i]); v[2 * i + 1] = __high2float(h[i]); }
+}
+template <typename T> struct Raw8;
+template <> struct Raw8<float> { typedef Raw8f type; };
+template <> struct Raw8<bf16> { typedef Raw8h type; };
 __device__ __forceinline__ void st8(float* p, const float (&v)[8]) {
   *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
   *reinterpret_cast<float4*>(p + 4) = make_float4(v[4], v[5], v[6], v[7]);
@@ -343,30 +362,44 @@ __global__ void __launch_bounds__(256) act_bwd_vec_kernel(int rows, int cols, co
 #pragma unroll
   for (int e = 0; e < 8; ++e) acc[e] = 0.f;
   if (c0 < cols) {
-    for (int r = blockIdx.y * 8 + ty; r < rows; r += gridDim.y * 8) {
-      const long long o = (long long)r * cols + c0;
-      float g[8], y[8];
-      ld8(dy + o, g);
-      if (dropping) {                    // cols % 8 == 0 and c0 % 8 == 0: o is even, (o + e, o + e + 1) are aligned pairs
+    const int rstep = gridDim.y * 8;
+    constexpr int NR = 4;     // rows per iteration: every 16-byte load of the iteration is issued (row index clamped) before any is used
+    for (int r0 = blockIdx.y * 8 + ty; r0 < rows; r0 += NR * rstep) {
+      typename Raw8<T>::type gr[NR], yr[NR];
 #pragma unroll
-        for (int e = 0; e < 8; e += 2) {
-          float s0, s1;
-          svpc_drop_scale2(dkey, drop.p, dinv, (unsigned long long)(o + e), s0, s1);
-          g[e] *= s0; g[e + 1] *= s1;
-        }
+      for (int u = 0; u < NR; ++u) {
+        const long long o = (long long)min(r0 + u * rstep, rows - 1) * cols + c0;
+        ldraw8(dy + o, gr[u]);
+        if (act != SVPC_ACT_NONE) ldraw8(ref + o, yr[u]);
       }
-      if (act != SVPC_ACT_NONE) {
-        ld8(ref + o, y);
 #pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          if (act == SVPC_ACT_RELU) g[e] = y[e] > 0.f ? g[e] : 0.f;
-          else if (act == SVPC_ACT_GELU) g[e] *= svpc_gelu_grad(y[e]);
-          else g[e] *= y[e] * (1.f - y[e]);
+      for (int u = 0; u < NR; ++u) {
+        const int r = r0 + u * rstep;
+        if (r >= rows) break;
+        const long long o = (long long)r * cols + c0;
+        float g[8], y[8];
+        cvt8(gr[u], g);
+        if (dropping) {                    // cols % 8 == 0 and c0 % 8 == 0: o is even, (o + e, o + e + 1) are aligned pairs
+#pragma unroll
+          for (int e = 0; e < 8; e += 2) {
+            float s0, s1;
+            svpc_drop_scale2(dkey, drop.p, dinv, (unsigned long long)(o + e), s0, s1);
+            g[e] *= s0; g[e + 1] *= s1;
+          }
         }
-      }
-      if (dz) st8(dz + o, g);
+        if (act != SVPC_ACT_NONE) {
+          cvt8(yr[u], y);
 #pragma unroll
-      for (int e = 0; e < 8; ++e) acc[e] += g[e];
+          for (int e = 0; e < 8; ++e) {
+            if (act == SVPC_ACT_RELU) g[e] = y[e] > 0.f ? g[e] : 0.f;
+            else if (act == SVPC_ACT_GELU) g[e] *= svpc_gelu_grad(y[e]);
+            else g[e] *= y[e] * (1.f - y[e]);
+          }
+        }
+        if (dz) st8(dz + o, g);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) acc[e] += g[e];
+      }
     }
   }
 #pragma unroll
@@ -968,11 +1001,11 @@ extern "C" int svpc_video_ln_pack(int n_clips, int B, int L, int Lv, int F, cons
 
 // Backward of the train-mode staging y = drop(xhat * gamma + beta): dgamma[c] = sum_r dy*scale*xhat, dbeta[c] = sum_r dy*scale
 // (the features are inputs: no gradient flows further).  xhat is recomputed from the raw features and the saved statistics.
-// Layout: a CTA owns a 256-column slab (lane = 8 contiguous columns: one 16-byte bf16 load of dy, two float4 loads of the
-// features) for a strided set of rows (8 row lanes); column sums over the row lanes through shared memory, one red.global
+// Layout: a CTA owns a 256-column slab (lane = 8 contiguous columns: one 16-byte bf16 load of dy, one or two 16-byte loads of
+// the features) for a strided set of rows (8 row lanes, four rows per iteration with all their loads issued up front); column sums over the row lanes through shared memory, one red.global
 // per column per CTA.
 template <typename T, typename TF>
-__global__ void __launch_bounds__(256) video_ln_affine_bwd_kernel(int n_rows, int B, int L, int Lv, int F,
+__global__ void __launch_bounds__(256, 3) video_ln_affine_bwd_kernel(int n_rows, int B, int L, int Lv, int F,
                                                                   const long long* __restrict__ feat_ptrs,
                                                                   const int* __restrict__ clip_t,
                                                                   const int* __restrict__ clip_b,
@@ -992,35 +1025,38 @@ __global__ void __launch_bounds__(256) video_ln_affine_bwd_kernel(int n_rows, in
   for (int e = 0; e < 8; ++e) { ag[e] = 0.f; ab[e] = 0.f; }
   if (c0 < F) {
     const int rstep = gridDim.y * 8;
-    for (int r0 = blockIdx.y * 8 + ty; r0 < n_rows; r0 += 2 * rstep) {      // two rows per iteration: four loads in flight
-      float d[2][8], x[2][8], mu[2], rs[2];
-      bool has[2];
+    constexpr int NR = 4;       // rows per iteration: 2 * NR 16-byte loads issued (unconditionally, row index clamped) before any is used
+    for (int r0 = blockIdx.y * 8 + ty; r0 < n_rows; r0 += NR * rstep) {
+      typename Raw8<T>::type dr[NR];
+      typename Raw8<TF>::type xr[NR];
+      float mu[NR], rs[NR];
 #pragma unroll
-      for (int u = 0; u < 2; ++u) {
-        const int r = r0 + u * rstep;
-        has[u] = r < n_rows;
-        if (has[u]) {
-          const int n = r / Lv, row = r - n * Lv;
-          const TF* src = reinterpret_cast<const TF*>(feat_ptrs[clip_t[n]]) + ((long long)clip_b[n] * L + row) * F + c0;
-          mu[u] = mean[r]; rs[u] = rstd[r];
-          ld8(dy + (long long)r * F + c0, d[u]);
-          ld8(src, x[u]);
-        }
+      for (int u = 0; u < NR; ++u) {
+        const int r = min(r0 + u * rstep, n_rows - 1);
+        const int n = r / Lv, row = r - n * Lv;
+        const TF* src = reinterpret_cast<const TF*>(feat_ptrs[clip_t[n]]) + ((long long)clip_b[n] * L + row) * F + c0;
+        mu[u] = mean[r]; rs[u] = rstd[r];
+        ldraw8(dy + (long long)r * F + c0, dr[u]);
+        ldraw8(src, xr[u]);
       }
 #pragma unroll
-      for (int u = 0; u < 2; ++u) {
-        if (!has[u]) break;
+      for (int u = 0; u < NR; ++u) {
         const int r = r0 + u * rstep;
-        if (dropping) {
+        if (r < n_rows) {
+          float d[8], x[8];
+          cvt8(dr[u], d);
+          cvt8(xr[u], x);
+          if (dropping) {
 #pragma unroll
-          for (int e = 0; e < 8; e += 2) {
-            float s0, s1;
-            svpc_drop_scale2(dkey, drop.p, dinv, (unsigned long long)r * F + c0 + e, s0, s1);
-            d[u][e] *= s0; d[u][e + 1] *= s1;
+            for (int e = 0; e < 8; e += 2) {
+              float s0, s1;
+              svpc_drop_scale2(dkey, drop.p, dinv, (unsigned long long)r * F + c0 + e, s0, s1);
+              d[e] *= s0; d[e + 1] *= s1;
+            }
           }
-        }
 #pragma unroll
-        for (int e = 0; e < 8; ++e) { ag[e] = fmaf(d[u][e], (x[u][e] - mu[u]) * rs[u], ag[e]); ab[e] += d[u][e]; }
+          for (int e = 0; e < 8; ++e) { ag[e] = fmaf(d[e], (x[e] - mu[u]) * rs[u], ag[e]); ab[e] += d[e]; }
+        }
       }
     }
   }
@@ -1052,7 +1088,7 @@ extern "C" int svpc_video_ln_affine_bwd(int n_clips, int B, int L, int Lv, int F
   const SvpcDrop drop{drop_p > 0.f ? drop_seed : nullptr, drop_site, drop_p};
   const int n_rows = n_clips * Lv;
   const int gx = svpc_cdiv(F, 256);
-  dim3 grid(gx, svpc_imin(svpc_cdiv(n_rows, 8), svpc_cdiv(SVPC_NUM_SMS * 8, gx)));
+  dim3 grid(gx, svpc_imin(svpc_cdiv(n_rows, 8), svpc_cdiv(SVPC_NUM_SMS * 3, gx)));      // one wave at 3 CTAs per SM
   SVPC_DISPATCH(dt, T, SVPC_DISPATCH(dt_feat, TF, (svpc_launch(video_ln_affine_bwd_kernel<T, TF>, grid, 256, 0, st,
       n_rows, B, L, Lv, F, feat_ptrs, clip_t, clip_b, mean, rstd, (const T*)dy, dgamma, dbeta, drop))));
   return svpc_check_launch("video_ln_affine_bwd");
