@@ -76,6 +76,16 @@ def _worker(rank, world, port, mode, out_path):
                     assert len(red._absent) > 0
             red.finish()
             assert all(p.grad is None for p in red._absent)
+        if red._absent:
+            # a gradient for a parameter that was learned to be dead must not be dropped silently
+            dead = next(iter(red._absent))
+            try:
+                red._on_grad(dead)
+                raise AssertionError("expected a RuntimeError for a gradient on a dead parameter")
+            except RuntimeError as e:
+                assert "reset_absent" in str(e)
+            red.reset_absent()
+            assert red._absent is None and red._need == [len(b) for b in red.buckets]
         tot = loss.detach().clone()
         dist.all_reduce(tot)
         if rank == 0:
